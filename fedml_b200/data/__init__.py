@@ -1,0 +1,201 @@
+"""``fedml.data`` — dataset entry points.
+
+``load(args) -> (dataset8, class_num)`` keeps the reference contract
+(data/data_loader.py:29-322): ``dataset8 = [train_num, test_num, train_global, test_global,
+train_local_num_dict, train_local_dict, test_local_dict, class_num]`` and side effects on
+``args`` (``client_num_in_total`` is overwritten for naturally-partitioned sets).  The packed
+:class:`FederatedDataset` behind the tuple is attached as ``args._federated_dataset`` /
+returned by :func:`load_federated` for the device-resident simulators.
+"""
+from __future__ import annotations
+
+import json
+import logging
+import os
+import pickle
+
+import numpy as np
+import torch
+
+from . import synthetic as S
+from .federated_dataset import FederatedDataset, combine_batches, merge_to_single_client
+
+__all__ = ["load", "load_federated", "load_cross_silo", "FederatedDataset", "split_data_for_dist_trainers",
+           "load_poisoned_dataset_from_edge_case_examples"]
+
+_NATURAL = {"mnist", "femnist", "fed_cifar100", "shakespeare", "fed_shakespeare", "stackoverflow_lr",
+            "stackoverflow_nwp", "gld23k", "gld160k", "synthetic_1_1", "synthetic_0_0", "synthetic_0.5_0.5",
+            "synthetic_iid"}
+
+
+def _try_real_mnist(cache_dir):
+    """LEAF JSON ``{users, user_data{x,y}}`` if the files are present (MNIST/data_loader.py:32-72)."""
+    tr, te = os.path.join(cache_dir, "MNIST", "train"), os.path.join(cache_dir, "MNIST", "test")
+    if not (os.path.isdir(tr) and os.path.isdir(te)):
+        return None
+
+    def read(d):
+        users, data = [], {}
+        for f in sorted(os.listdir(d)):
+            if f.endswith(".json"):
+                with open(os.path.join(d, f)) as fh:
+                    blob = json.load(fh)
+                users.extend(blob["users"]); data.update(blob["user_data"])
+        return users, data
+
+    users, trd = read(tr)
+    _, ted = read(te)
+    xs = [np.asarray(trd[u]["x"], dtype=np.float32) for u in users]
+    ys = [np.asarray(trd[u]["y"], dtype=np.int64) for u in users]
+    txs = [np.asarray(ted[u]["x"], dtype=np.float32) for u in users]
+    tys = [np.asarray(ted[u]["y"], dtype=np.int64) for u in users]
+    off = lambda a: np.concatenate([[0], np.cumsum([len(v) for v in a])])
+    cat = lambda a: torch.from_numpy(np.concatenate(a))
+    return FederatedDataset(cat(xs), cat(ys), off(ys), cat(txs), cat(tys), off(tys), 10, None, "mnist")
+
+
+def _try_real_cifar10(cache_dir):
+    d = os.path.join(cache_dir, "cifar-10-batches-py")
+    if not os.path.isdir(d):
+        return None
+    def rd(name):
+        with open(os.path.join(d, name), "rb") as fh:
+            blob = pickle.load(fh, encoding="bytes")
+        x = np.asarray(blob[b"data"], dtype=np.uint8).reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1)
+        return x, np.asarray(blob[b"labels"], dtype=np.int64)
+    parts = [rd(f"data_batch_{i}") for i in range(1, 6)]
+    xtr = np.concatenate([p[0] for p in parts]); ytr = np.concatenate([p[1] for p in parts])
+    xte, yte = rd("test_batch")
+    return tuple(torch.from_numpy(np.ascontiguousarray(a)) for a in (xtr, ytr, xte, yte))
+
+
+def load_federated(args) -> FederatedDataset:
+    name = str(args.dataset).lower()
+    seed = int(getattr(args, "random_seed", 0))
+    n_clients = int(getattr(args, "client_num_in_total", 10))
+    pm, pa = getattr(args, "partition_method", "homo"), float(getattr(args, "partition_alpha", 0.5))
+    cache = getattr(args, "data_cache_dir", "./data")
+    small = int(getattr(args, "synthetic_train_size", 0) or 0)
+    if name == "mnist":
+        ds = None if getattr(args, "synthetic_data", True) is True and not os.path.isdir(os.path.join(cache, "MNIST")) \
+            else _try_real_mnist(cache)
+        if ds is None:
+            nat = int(getattr(args, "mnist_client_num", 1000))
+            ds = S.make_mnist_like(client_num=nat, total_train=small or 61664, seed=seed)
+    elif name == "femnist":
+        ds = S.make_femnist_like(client_num=int(getattr(args, "femnist_client_num", 3400)), seed=seed,
+                                 total_train=small or 340000)
+    elif name in ("cifar10", "cifar100", "cinic10"):
+        cnum = 100 if name == "cifar100" else 10
+        mean, std = (S.CIFAR100_MEAN, S.CIFAR100_STD) if name == "cifar100" else (S.CIFAR10_MEAN, S.CIFAR10_STD)
+        ntr = small or (90000 if name == "cinic10" else 50000)
+        nte = max(100, ntr // 5)
+        real = _try_real_cifar10(cache) if name == "cifar10" else None
+        if real is not None:
+            from ..core.non_iid_partition import homo_partition, non_iid_partition_with_dirichlet_distribution
+            xtr, ytr, xte, yte = real
+            st = np.random.get_state(); np.random.seed(10)
+            part = homo_partition(len(ytr), n_clients) if pm == "homo" else \
+                non_iid_partition_with_dirichlet_distribution(ytr.numpy(), n_clients, 10, pa)
+            np.random.set_state(st)
+            x, y, offs = S._pack_by_partition(xtr, ytr, part)
+            ds = FederatedDataset(x, y, offs, xte, yte, None, 10, S.ImageNormalize(mean, std), name)
+        else:
+            ds = S.make_cifar_like(n_clients, pm, pa, cnum, ntr, nte, 32, seed, name, mean, std)
+    elif name == "fed_cifar100":
+        ds = S.make_cifar_like(int(getattr(args, "fed_cifar100_client_num", 500)), "hetero", 0.1, 100,
+                               small or 50000, 10000 if not small else max(100, small // 5), 24, seed,
+                               name, S.CIFAR100_MEAN, S.CIFAR100_STD)
+    elif name in ("ilsvrc2012", "imagenet", "gld23k", "gld160k"):
+        clients = {"gld23k": 233, "gld160k": 1262}.get(name, n_clients)
+        classes = {"gld23k": 203, "gld160k": 2028}.get(name, 1000)
+        hw = int(getattr(args, "image_size", 224))
+        ntr = small or 2048
+        ds = S.make_cifar_like(clients, "homo" if name.startswith("il") or name == "imagenet" else "hetero", pa,
+                               classes, ntr, max(64, ntr // 8), hw, seed, name, S.IMAGENET_MEAN, S.IMAGENET_STD)
+    elif name in ("shakespeare", "fed_shakespeare"):
+        ds = S.make_char_lm(715 if not small else max(4, small // 64), 80, 90, 64, seed, name,
+                            next_token_only=(name == "shakespeare"))
+    elif name == "stackoverflow_nwp":
+        ds = S.make_char_lm(int(getattr(args, "stackoverflow_client_num", 1000)), 20, 10004, 32, seed, name,
+                            next_token_only=False)
+    elif name == "stackoverflow_lr":
+        ds = S.make_stackoverflow_lr(int(getattr(args, "stackoverflow_client_num", 200)), seed=seed)
+    elif name.startswith("synthetic"):
+        parts = name.replace("synthetic", "").strip("_").split("_")
+        iid = "iid" in parts
+        ab = [float(p) for p in parts if p.replace(".", "", 1).isdigit()] or [1.0, 1.0]
+        ds = S.make_synthetic_ab(ab[0], ab[-1], 30, seed=seed, iid=iid)
+    elif name in ("fednlp", "20news", "agnews", "sst2", "text_classification", "fednlp_text"):
+        classes = {"20news": 20, "agnews": 4, "sst2": 2}.get(name, int(getattr(args, "num_labels", 4)))
+        ds = S.make_text_classification(n_clients, int(getattr(args, "max_seq_length", 128)), 30522, classes,
+                                        int(getattr(args, "samples_per_client", 32)), seed, name)
+    elif name in ("pascal_voc", "coco_seg", "cityscapes"):
+        ds = S.make_segmentation(n_clients, seed=seed, name=name)
+    else:
+        raise ValueError(f"unknown dataset {args.dataset!r}")
+    if name in _NATURAL or name.startswith("synthetic"):
+        args.client_num_in_total = ds.client_num
+    return ds
+
+
+def load(args):
+    logging.info("load_data. dataset_name = %s", args.dataset)
+    centralized = int(args.client_num_in_total) == 1 and getattr(args, "training_type", "") != "cross_silo"
+    ds = load_federated(args)
+    bs = int(args.batch_size)
+    image_like = ds.transform is not None           # CIFAR-style loaders use drop_last=True (cifar10/data_loader.py:209-214)
+    dataset8 = ds.as_tuple(bs, drop_last=image_like and bs > 0)
+    if centralized:
+        dataset8 = merge_to_single_client(dataset8)
+        args.client_num_in_total = 1
+    args._federated_dataset = ds
+    return dataset8, ds.class_num
+
+
+def split_data_for_dist_trainers(batches, n_dist_trainer):
+    """Chunk one client's batch list over the processes of a silo
+    (reference: data/data_loader_cross_silo.py:9-55)."""
+    batches = list(batches)
+    n = max(1, int(n_dist_trainer))
+    return [batches[i::n] for i in range(n)]
+
+
+def load_cross_silo(args):
+    """Like :func:`load`, but each client's train data becomes a list indexed by
+    ``proc_rank_in_silo`` when the silo runs several trainer processes (hierarchical scenario)."""
+    dataset8, class_num = load(args)
+    n_proc = int(getattr(args, "n_proc_in_silo", 1) or 1)
+    if getattr(args, "scenario", "horizontal") == "hierarchical" and n_proc > 1:
+        train_local = dataset8[5]
+        dataset8[5] = {c: split_data_for_dist_trainers(train_local[c], n_proc) for c in train_local.keys()}
+    return dataset8, class_num
+
+
+def load_poisoned_dataset_from_edge_case_examples(args):
+    """Backdoor ("edge-case") data for the robust-FedAvg runner: a poisoned train loader, a clean
+    test loader and a targeted-task test loader (edge_case_examples/data_loader.py:393-).  The
+    real Southwest-airline / ARDIS sets cannot be downloaded; the synthetic stand-in stamps a
+    trigger patch on samples of one class and relabels them to ``target_label``."""
+    ds = getattr(args, "_federated_dataset", None) or load_federated(args)
+    bs = int(args.batch_size)
+    target = int(getattr(args, "target_label", 9)) % ds.class_num
+    g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) + 17)
+    n = min(512, ds.x.shape[0])
+    idx = torch.randperm(ds.x.shape[0], generator=g)[:n]
+    xp, yp = ds.x[idx].clone(), torch.full((n,), target, dtype=torch.int64)
+    if xp.dim() == 4:            # NHWC uint8 images: bright 4x4 corner patch
+        xp[:, :4, :4, :] = 255
+    else:
+        xp[:, :16] = xp.max()
+    nt = min(256, ds.x_test.shape[0])
+    xt = ds.x_test[:nt].clone()
+    if xt.dim() == 4:
+        xt[:, :4, :4, :] = 255
+    else:
+        xt[:, :16] = xt.max()
+    yt = torch.full((nt,), target, dtype=torch.int64)
+    poisoned_train = ds.batches(xp, yp, bs, drop_last=False)
+    clean_test = ds.batches(ds.x_test, ds.y_test, bs)
+    targeted_test = ds.batches(xt, yt, bs)
+    return poisoned_train, clean_test, targeted_test, n
