@@ -1,0 +1,196 @@
+// K5/K6: coordinate-wise median and trimmed mean; K7 helpers (pack + scores).  See include/fedml_b200.h.
+//
+// Selection strategy: a tile of TILE coordinates x K clients is staged in shared memory as
+// keys[k][t] (thread index t fastest => conflict-free), floats mapped to order-preserving uint32
+// keys.  Each coordinate is owned by SPLIT=4 adjacent lanes which cooperatively run a bitwise
+// (radix-2, MSB first) selection for the wanted order statistics: 32 passes of K/4 compares per
+// lane + 2 shuffles.  No sort, no global scratch, every HBM/NVLink byte is read exactly once.
+#include "common.cuh"
+#include "../include/fedml_b200.h"
+
+#define SEL_THREADS 256
+#define SEL_SPLIT 4
+#define SEL_TILE (SEL_THREADS / SEL_SPLIT)  // 64 coordinates per block-iteration
+#define SEL_LD (SEL_TILE + 8)               // row stride: the 4 lanes of a coordinate (k, k+1, k+2, k+3) hit 4 different banks
+
+__device__ __forceinline__ uint32_t f2key(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key2f(uint32_t k) {
+  uint32_t u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(u);
+}
+
+// k-th smallest key (0-based rank) of column `col`; the SPLIT lanes of a coordinate call it together.
+__device__ __forceinline__ uint32_t select_rank(const uint32_t* keys, int K, int col, int sub, int rank) {
+  uint32_t prefix = 0;  // bits decided so far
+  int remaining = rank; // rank inside the candidate set that matches `prefix` on the decided bits
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t mask_hi = bit == 31 ? 0u : (0xffffffffu << (bit + 1));
+    int cnt0 = 0;  // candidates whose current bit is 0
+    for (int k = sub; k < K; k += SEL_SPLIT) {
+      const uint32_t x = keys[(size_t)k * SEL_LD + col];
+      const bool cand = ((x ^ prefix) & mask_hi) == 0u;
+      cnt0 += (cand && !((x >> bit) & 1u)) ? 1 : 0;
+    }
+    cnt0 += __shfl_xor_sync(0xffffffffu, cnt0, 1);
+    cnt0 += __shfl_xor_sync(0xffffffffu, cnt0, 2);
+    if (remaining >= cnt0) {
+      remaining -= cnt0;
+      prefix |= (1u << bit);
+    }
+  }
+  return prefix;
+}
+
+__global__ void __launch_bounds__(SEL_THREADS) robust_select_kernel(const float* const* __restrict__ rows, int K,
+                                                                    int64_t j0, int64_t j1, int mode, int trim,
+                                                                    float* const* __restrict__ outs, int n_out) {
+  extern __shared__ uint32_t keys[];  // [K][SEL_LD]
+  const int tid = threadIdx.x;
+  const int col = tid / SEL_SPLIT, sub = tid % SEL_SPLIT;
+  const int64_t ntiles = (j1 - j0 + SEL_TILE - 1) / SEL_TILE;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t base = j0 + tile * SEL_TILE;
+    const int width = (int)min((int64_t)SEL_TILE, j1 - base);
+    __syncthreads();  // previous tile fully consumed
+    // stage: consecutive threads read consecutive coordinates of one client row (coalesced 256 B)
+    for (int idx = tid; idx < K * SEL_TILE; idx += SEL_THREADS) {
+      const int k = idx / SEL_TILE, t = idx % SEL_TILE;
+      float x = 0.f;
+      if (t < width) {
+        const float* src = rows[k] + base + t;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(x) : "l"(src) : "memory");
+      }
+      keys[(size_t)k * SEL_LD + t] = f2key(x);
+    }
+    __syncthreads();
+    float result;
+    if (mode == 0) {
+      result = key2f(select_rank(keys, K, col, sub, (K - 1) / 2));
+    } else {
+      const uint32_t klo = select_rank(keys, K, col, sub, trim);
+      const uint32_t khi = select_rank(keys, K, col, sub, K - trim - 1);
+      if (klo == khi) {
+        result = key2f(klo);
+      } else {
+        float sum = 0.f;
+        int lt_lo = 0, eq_lo = 0, lt_hi = 0;
+        for (int k = sub; k < K; k += SEL_SPLIT) {
+          const uint32_t x = keys[(size_t)k * SEL_LD + col];
+          lt_lo += x < klo;
+          eq_lo += x == klo;
+          lt_hi += x < khi;
+          if (x > klo && x < khi) sum += key2f(x);
+        }
+#pragma unroll
+        for (int o = 1; o < SEL_SPLIT; o <<= 1) {
+          sum += __shfl_xor_sync(0xffffffffu, sum, o);
+          lt_lo += __shfl_xor_sync(0xffffffffu, lt_lo, o);
+          eq_lo += __shfl_xor_sync(0xffffffffu, eq_lo, o);
+          lt_hi += __shfl_xor_sync(0xffffffffu, lt_hi, o);
+        }
+        const int n_lo = lt_lo + eq_lo - trim;       // copies of v_lo with rank >= trim
+        const int n_hi = (K - trim) - lt_hi;         // copies of v_hi with rank <  K - trim
+        sum += (float)n_lo * key2f(klo) + (float)n_hi * key2f(khi);
+        result = sum / (float)(K - 2 * trim);
+      }
+    }
+    if (sub == 0 && col < width) {
+      for (int o = 0; o < n_out; ++o) outs[o][base + col] = result;
+    }
+  }
+}
+
+extern "C" int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t j0, int64_t j1, int32_t mode,
+                                int32_t trim, float* const* outs_dev, int32_t n_out, fb_stream_t stream) {
+  FB_REQUIRE(rows_dev && outs_dev && K >= 1 && j1 >= j0 && n_out >= 1, "fb_robust_select: bad arguments");
+  FB_REQUIRE(mode == 0 || (trim >= 0 && 2 * trim < K), "fb_robust_select: trim removes every client");
+  const size_t smem = (size_t)K * SEL_LD * sizeof(uint32_t);
+  if (smem > 220 * 1024) {
+    fb_set_error("fb_robust_select: K=%d exceeds the %d clients that fit one shared-memory tile", K,
+                 (int)(220 * 1024 / (SEL_LD * sizeof(uint32_t))));
+    return FB_ERR_LIMIT;
+  }
+  if (j1 == j0) return FB_OK;
+  FB_CHECK_CUDA(cudaFuncSetAttribute(robust_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, robust_select_kernel, SEL_THREADS, smem);
+  if (per_sm < 1) per_sm = 1;
+  const int64_t ntiles = (j1 - j0 + SEL_TILE - 1) / SEL_TILE;
+  int64_t grid = (int64_t)per_sm * fb_num_sms();
+  if (grid > ntiles) grid = ntiles;
+  robust_select_kernel<<<(int)grid, SEL_THREADS, smem, (cudaStream_t)stream>>>(rows_dev, K, j0, j1, mode, trim,
+                                                                                outs_dev, n_out);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- K7: pack for the Gram GEMM
+// dst_hi[k][j-j0] = bf16(x), dst_lo = bf16(x - float(hi)) with x = rows[k][j] - ref[j].
+__global__ void __launch_bounds__(256) krum_pack_kernel(const float* const* __restrict__ rows,
+                                                        const float* __restrict__ ref, int64_t j0, int64_t n,
+                                                        __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo,
+                                                        int64_t ld) {
+  const int k = blockIdx.y;
+  const float* row = rows[k];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < ld; i += (int64_t)gridDim.x * blockDim.x) {
+    float x = 0.f;
+    if (i < n) {
+      asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(x) : "l"(row + j0 + i) : "memory");
+      if (ref) x -= __ldg(ref + j0 + i);
+    }
+    const __nv_bfloat16 h = __float2bfloat16_rn(x);
+    hi[(size_t)k * ld + i] = h;
+    if (lo) lo[(size_t)k * ld + i] = __float2bfloat16_rn(x - __bfloat162float(h));
+  }
+}
+extern "C" int fb_krum_pack(const float* const* rows_dev, int32_t K, const float* ref, int64_t j0, int64_t j1,
+                            void* dst_hi, void* dst_lo, int64_t ld_dst, fb_stream_t stream) {
+  FB_REQUIRE(rows_dev && dst_hi && K >= 1 && K <= 65535 && j1 > j0 && ld_dst >= j1 - j0, "fb_krum_pack: bad arguments");
+  int gx = (int)((ld_dst + 255) / 256);
+  int lim = (fb_num_sms() * 8 + K - 1) / K;
+  if (gx > lim) gx = lim < 1 ? 1 : lim;
+  krum_pack_kernel<<<dim3(gx, K), 256, 0, (cudaStream_t)stream>>>(rows_dev, ref, j0, j1 - j0, (__nv_bfloat16*)dst_hi,
+                                                                  (__nv_bfloat16*)dst_lo, ld_dst);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- K7: scores from the Gram matrix
+// one block per client i: d2(i,j) = g_ii + g_jj - 2 g_ij; sum of the nn smallest (j != i).
+__global__ void __launch_bounds__(256) krum_scores_kernel(const float* __restrict__ gram, int K, int nn,
+                                                          float* __restrict__ scores) {
+  extern __shared__ float d2[];  // [K]
+  __shared__ float red[33];
+  const int i = blockIdx.x, tid = threadIdx.x;
+  const float gii = gram[(size_t)i * K + i];
+  for (int j = tid; j < K; j += blockDim.x) {
+    float v = gii + gram[(size_t)j * K + j] - 2.f * gram[(size_t)i * K + j];
+    d2[j] = (j == i) ? INFINITY : fmaxf(v, 0.f);
+  }
+  __syncthreads();
+  // rank-by-counting: element j is among the nn smallest iff fewer than nn elements precede it
+  // in (value, index) order — exact with ties, O(K^2 / threads) per block, K <= a few thousand.
+  float acc = 0.f;
+  for (int j = tid; j < K; j += blockDim.x) {
+    const float v = d2[j];
+    int before = 0;
+    for (int t = 0; t < K; ++t) {
+      const float u = d2[t];
+      before += (u < v) || (u == v && t < j);
+    }
+    if (before < nn && j != i) acc += v;
+  }
+  const float tot = block_sum(acc, red);
+  if (tid == 0) scores[i] = tot;
+}
+extern "C" int fb_krum_scores(const float* gram, int32_t K, int32_t f, float* scores, fb_stream_t stream) {
+  FB_REQUIRE(gram && scores && K >= 1 && K <= 8192, "fb_krum_scores: bad arguments");
+  int nn = K - f - 2;
+  if (nn < 1) nn = 1;
+  krum_scores_kernel<<<K, 256, (size_t)K * sizeof(float), (cudaStream_t)stream>>>(gram, K, nn, scores);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}

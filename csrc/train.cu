@@ -1,0 +1,240 @@
+// K11 / K15: fused multi-client optimizer step, softmax cross-entropy fwd+bwd, fused evaluation counters.
+// See include/fedml_b200.h.
+#include "common.cuh"
+#include "../include/fedml_b200.h"
+
+static inline int ew_grid(int64_t nvec) {
+  int64_t want = (nvec + 255) / 256, cap = (int64_t)fb_num_sms() * 8;
+  if (want < 1) want = 1;
+  return (int)(want < cap ? want : cap);
+}
+
+// ---------------------------------------------------------------- stacked SGD (+wd, momentum, FedProx, FedNova)
+__global__ void __launch_bounds__(256)
+sgd_step_stacked_kernel(float* __restrict__ w, const float* __restrict__ g, int64_t ld, int C, int64_t nvec_row,
+                        const float* __restrict__ lr_dev, float wd, float momentum, float dampening, int nesterov,
+                        float* __restrict__ mom, int first_step, float mu, const float* __restrict__ anchor,
+                        float* __restrict__ cum) {
+  const int64_t total = nvec_row * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i / nvec_row);
+    const int64_t j = (i - (int64_t)c * nvec_row) * 4;
+    const float lr = __ldg(lr_dev + c);
+    if (lr == 0.f) continue;  // frozen client (finished its local steps)
+    const size_t off = (size_t)c * ld + j;
+    float4 ww = *reinterpret_cast<const float4*>(w + off);
+    float4 d = ld_stream4(g + off);
+    if (wd != 0.f) { d.x += wd * ww.x; d.y += wd * ww.y; d.z += wd * ww.z; d.w += wd * ww.w; }
+    if (momentum != 0.f) {
+      float4 b;
+      if (first_step) {
+        b = d;
+      } else {
+        b = *reinterpret_cast<const float4*>(mom + off);
+        const float k = 1.f - dampening;
+        b.x = momentum * b.x + k * d.x; b.y = momentum * b.y + k * d.y;
+        b.z = momentum * b.z + k * d.z; b.w = momentum * b.w + k * d.w;
+      }
+      *reinterpret_cast<float4*>(mom + off) = b;
+      if (nesterov) { d.x += momentum * b.x; d.y += momentum * b.y; d.z += momentum * b.z; d.w += momentum * b.w; }
+      else d = b;
+    }
+    if (mu != 0.f) {
+      const float4 a = *reinterpret_cast<const float4*>(anchor + j);
+      d.x += mu * (ww.x - a.x); d.y += mu * (ww.y - a.y); d.z += mu * (ww.z - a.z); d.w += mu * (ww.w - a.w);
+    }
+    if (cum) {
+      float4 cg = *reinterpret_cast<const float4*>(cum + off);
+      cg.x += lr * d.x; cg.y += lr * d.y; cg.z += lr * d.z; cg.w += lr * d.w;
+      *reinterpret_cast<float4*>(cum + off) = cg;
+    }
+    ww.x -= lr * d.x; ww.y -= lr * d.y; ww.z -= lr * d.z; ww.w -= lr * d.w;
+    *reinterpret_cast<float4*>(w + off) = ww;
+  }
+}
+
+extern "C" int fb_sgd_step_stacked(float* w, const float* g, int64_t ld, int32_t C, int64_t n, const float* lr_dev,
+                                   float weight_decay, float momentum, float dampening, int32_t nesterov,
+                                   float* mom_buf, int32_t first_step, float mu, const float* anchor, float* cum_grad,
+                                   fb_stream_t stream) {
+  FB_REQUIRE(w && g && lr_dev && C >= 1 && n > 0 && n % 4 == 0 && ld % 4 == 0 && ld >= n, "fb_sgd_step_stacked: bad shape");
+  FB_REQUIRE(momentum == 0.f || mom_buf, "fb_sgd_step_stacked: momentum needs mom_buf");
+  FB_REQUIRE(mu == 0.f || anchor, "fb_sgd_step_stacked: mu needs the anchor (global) model");
+  sgd_step_stacked_kernel<<<ew_grid(n / 4 * C), 256, 0, (cudaStream_t)stream>>>(
+      w, g, ld, C, n / 4, lr_dev, weight_decay, momentum, dampening, nesterov, mom_buf, first_step, mu, anchor, cum_grad);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+__global__ void __launch_bounds__(256)
+sgd_step_stacked_bf16g_kernel(float* __restrict__ w, const __nv_bfloat16* __restrict__ g, int64_t ld, int64_t ld_g,
+                              int C, int64_t nvec_row, const float* __restrict__ lr_dev, float wd, float mu,
+                              const float* __restrict__ anchor) {
+  const int64_t total = nvec_row * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i / nvec_row);
+    const int64_t j = (i - (int64_t)c * nvec_row) * 4;
+    const float lr = __ldg(lr_dev + c);
+    if (lr == 0.f) continue;
+    const size_t off = (size_t)c * ld + j;
+    float4 ww = *reinterpret_cast<const float4*>(w + off);
+    const uint2 raw = __ldg(reinterpret_cast<const uint2*>(g + (size_t)c * ld_g + j));
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+    float4 d = make_float4(a.x, a.y, b.x, b.y);
+    if (wd != 0.f) { d.x += wd * ww.x; d.y += wd * ww.y; d.z += wd * ww.z; d.w += wd * ww.w; }
+    if (mu != 0.f) {
+      const float4 an = *reinterpret_cast<const float4*>(anchor + j);
+      d.x += mu * (ww.x - an.x); d.y += mu * (ww.y - an.y); d.z += mu * (ww.z - an.z); d.w += mu * (ww.w - an.w);
+    }
+    ww.x -= lr * d.x; ww.y -= lr * d.y; ww.z -= lr * d.z; ww.w -= lr * d.w;
+    *reinterpret_cast<float4*>(w + off) = ww;
+  }
+}
+extern "C" int fb_sgd_step_stacked_bf16g(float* w, const void* g_bf16, int64_t ld, int64_t ld_g, int32_t C, int64_t n,
+                                         const float* lr_dev, float weight_decay, float mu, const float* anchor,
+                                         fb_stream_t stream) {
+  FB_REQUIRE(w && g_bf16 && lr_dev && C >= 1 && n > 0 && n % 4 == 0 && ld % 4 == 0 && ld_g % 4 == 0,
+             "fb_sgd_step_stacked_bf16g: bad shape");
+  FB_REQUIRE(mu == 0.f || anchor, "fb_sgd_step_stacked_bf16g: mu needs the anchor (global) model");
+  sgd_step_stacked_bf16g_kernel<<<ew_grid(n / 4 * C), 256, 0, (cudaStream_t)stream>>>(
+      w, (const __nv_bfloat16*)g_bf16, ld, ld_g, C, n / 4, lr_dev, weight_decay, mu, anchor);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- softmax cross-entropy (one warp per row)
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+
+__global__ void __launch_bounds__(256)
+softmax_xent_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, int64_t R, int ncls,
+                    int64_t ignore_index, int pre_sigmoid, const float* __restrict__ row_scale, int64_t rows_per_group,
+                    float* __restrict__ loss_rows, float* __restrict__ dlogits) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp0; r < R; r += nwarps) {
+    const float* row = logits + (size_t)r * ncls;
+    const int64_t y = labels[r];
+    const bool ignored = (y == ignore_index) || y < 0 || y >= ncls;
+    float mx = -INFINITY;
+    for (int c = lane; c < ncls; c += 32) {
+      float z = row[c];
+      if (pre_sigmoid) z = sigmoidf_(z);
+      mx = fmaxf(mx, z);
+    }
+    mx = warp_max(mx);
+    float se = 0.f;
+    for (int c = lane; c < ncls; c += 32) {
+      float z = row[c];
+      if (pre_sigmoid) z = sigmoidf_(z);
+      se += __expf(z - mx);
+    }
+    se = warp_sum(se);
+    const float lse = mx + __logf(se);
+    if (loss_rows && lane == 0) {
+      float zy = 0.f;
+      if (!ignored) {
+        zy = row[y];
+        if (pre_sigmoid) zy = sigmoidf_(zy);
+      }
+      loss_rows[r] = ignored ? 0.f : (lse - zy);
+    }
+    if (dlogits) {
+      const float sc = ignored ? 0.f : (row_scale ? __ldg(row_scale + r / rows_per_group) : 1.f / (float)R);
+      for (int c = lane; c < ncls; c += 32) {
+        float z = row[c], s = 0.f;
+        if (pre_sigmoid) { s = sigmoidf_(z); z = s; }
+        float gsm = (__expf(z - lse) - (c == y ? 1.f : 0.f)) * sc;
+        if (pre_sigmoid) gsm *= s * (1.f - s);
+        dlogits[(size_t)r * ncls + c] = gsm;
+      }
+    }
+  }
+}
+extern "C" int fb_softmax_xent(const float* logits, const int64_t* labels, int64_t R, int32_t ncls,
+                               int64_t ignore_index, int32_t pre_sigmoid, const float* row_scale,
+                               int64_t rows_per_group, float* loss_rows, float* dlogits, fb_stream_t stream) {
+  FB_REQUIRE(logits && labels && R > 0 && ncls > 0, "fb_softmax_xent: bad shape");
+  if (rows_per_group < 1) rows_per_group = 1;
+  int64_t want = (R * 32 + 255) / 256, cap = (int64_t)fb_num_sms() * 8;
+  int grid = (int)(want < cap ? want : cap);
+  softmax_xent_kernel<<<grid < 1 ? 1 : grid, 256, 0, (cudaStream_t)stream>>>(
+      logits, labels, R, ncls, ignore_index, pre_sigmoid, row_scale, rows_per_group, loss_rows, dlogits);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- fused evaluation counters
+// counts = [correct, total, tp[ncls], fp[ncls], fn[ncls]]
+__global__ void __launch_bounds__(256)
+eval_counts_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, int64_t R, int ncls,
+                   int pre_sigmoid, uint32_t* __restrict__ counts, float* __restrict__ loss_sum) {
+  __shared__ float red[33];
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  float loss_acc = 0.f;
+  uint32_t correct = 0, total = 0;
+  for (int64_t r = warp0; r < R; r += nwarps) {
+    const float* row = logits + (size_t)r * ncls;
+    const int64_t y = labels[r];
+    float mx = -INFINITY;
+    int arg = 0x7fffffff;
+    for (int c = lane; c < ncls; c += 32) {
+      float z = row[c];
+      if (pre_sigmoid) z = sigmoidf_(z);
+      if (z > mx) { mx = z; arg = c; }
+    }
+    // warp arg-max, lowest index wins ties (torch.max / argmax behaviour on the first maximal element)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+    }
+    float se = 0.f;
+    for (int c = lane; c < ncls; c += 32) {
+      float z = row[c];
+      if (pre_sigmoid) z = sigmoidf_(z);
+      se += __expf(z - mx);
+    }
+    se = warp_sum(se);
+    if (lane == 0 && y >= 0 && y < ncls) {
+      float zy = row[y];
+      if (pre_sigmoid) zy = sigmoidf_(zy);
+      loss_acc += mx + __logf(se) - zy;
+      total += 1;
+      if (arg == (int)y) {
+        correct += 1;
+        atomicAdd(counts + 2 + y, 1u);
+      } else {
+        atomicAdd(counts + 2 + ncls + arg, 1u);       // false positive for the predicted class
+        atomicAdd(counts + 2 + 2 * ncls + y, 1u);     // false negative for the true class
+      }
+    }
+  }
+  const float bl = block_sum(loss_acc, red);
+  const float bc = block_sum((float)correct, red);
+  const float bt = block_sum((float)total, red);
+  if (threadIdx.x == 0) {
+    atomicAdd(loss_sum, bl);
+    atomicAdd(counts + 0, (uint32_t)(bc + 0.5f));
+    atomicAdd(counts + 1, (uint32_t)(bt + 0.5f));
+  }
+}
+extern "C" int fb_eval_counts(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int32_t pre_sigmoid,
+                              uint32_t* counts, float* loss_sum, fb_stream_t stream) {
+  FB_REQUIRE(logits && labels && counts && loss_sum && R > 0 && ncls > 0, "fb_eval_counts: bad shape");
+  int64_t want = (R * 32 + 255) / 256, cap = (int64_t)fb_num_sms() * 4;
+  int grid = (int)(want < cap ? want : cap);
+  eval_counts_kernel<<<grid < 1 ? 1 : grid, 256, 0, (cudaStream_t)stream>>>(logits, labels, R, ncls, pre_sigmoid, counts,
+                                                                            loss_sum);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}

@@ -1,0 +1,263 @@
+"""Python front-end of the hand-written sm_100a kernels (``csrc/*.cu``).
+
+Every function takes CUDA tensors, validates shapes/dtypes, and launches on the current
+stream.  There is no eager fallback here: CPU tensors must use the oracles in
+``fedml_b200.core.aggregation`` — a CUDA tensor with a missing library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import native as N
+from .native import FB_OPT, FbRoundParams, NativeError, check, count_launch, lib, ptr, stream_ptr
+
+f32, i64, i32, u32, u64 = C.c_float, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64
+vp = C.c_void_p
+
+
+def _req(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise NativeError(f"{name}: expected a CUDA tensor")
+    if t.dtype != dtype:
+        raise NativeError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+    return t
+
+
+def _rows(stack: torch.Tensor):
+    """[C, ld-strided] 2-D view -> (ptr, ld, C)."""
+    if stack.dim() != 2 or stack.stride(1) != 1:
+        raise NativeError("stacked tensor must be 2-D with unit inner stride")
+    return ptr(stack), stack.stride(0) if stack.shape[0] > 1 else max(stack.stride(0), stack.shape[1]), stack.shape[0]
+
+
+# --------------------------------------------------------------------------- K4 / broadcast
+def weighted_accumulate(clients: torch.Tensor, weights: torch.Tensor, out: torch.Tensor, scale: float = 1.0,
+                        beta: float = 0.0):
+    """out = beta*out + scale * sum_c weights[c] * clients[c]   (clients fp32 or bf16 [C, P])."""
+    p, ld, Cn = _rows(clients)
+    P = out.numel()
+    _req(weights, torch.float32, "weights"); _req(out, torch.float32, "out")
+    fn = lib().fb_weighted_accumulate if clients.dtype == torch.float32 else lib().fb_weighted_accumulate_bf16
+    check(fn(vp(p), i64(ld), i32(Cn), vp(ptr(weights)), f32(scale), f32(beta), vp(ptr(out)), i64(P),
+             vp(stream_ptr(out.device))), "weighted_accumulate")
+    count_launch()
+    return out
+
+
+def broadcast_rows(src: torch.Tensor, rows: torch.Tensor):
+    p, ld, Cn = _rows(rows)
+    check(lib().fb_broadcast_rows(vp(ptr(_req(src, torch.float32, "src"))), vp(p), i64(ld), i32(Cn), i64(src.numel()),
+                                  vp(stream_ptr(src.device))), "broadcast_rows")
+    count_launch()
+    return rows
+
+
+# --------------------------------------------------------------------------- K3
+def server_opt(w, avg, m, v, opt: str, lr, momentum=0.0, beta1=0.9, beta2=0.99, eps=1e-3, step=1, nesterov=False,
+               grad_scale=1.0):
+    bc1 = 1.0 - beta1 ** step
+    bc2 = 1.0 - beta2 ** step
+    check(lib().fb_server_opt(vp(ptr(w)), vp(ptr(avg)), vp(ptr(m)), vp(ptr(v)), i64(w.numel()), i32(FB_OPT[opt.lower()]),
+                              i32(int(nesterov)), f32(lr), f32(momentum), f32(beta1), f32(beta2), f32(eps), f32(bc1),
+                              f32(bc2), f32(grad_scale), vp(stream_ptr(w.device))), "server_opt")
+    count_launch()
+    return w
+
+
+# --------------------------------------------------------------------------- K2 pieces
+def sqnorm_diff(clients: torch.Tensor, ref: torch.Tensor, n: Optional[int] = None) -> torch.Tensor:
+    p, ld, Cn = _rows(clients)
+    n = ref.numel() if n is None else n
+    out = torch.empty(Cn, dtype=torch.float32, device=clients.device)
+    check(lib().fb_sqnorm_diff(vp(p), i64(ld), i32(Cn), vp(ptr(ref)), i64(n), vp(ptr(out)),
+                               vp(stream_ptr(out.device))), "sqnorm_diff")
+    count_launch(2)
+    return out
+
+
+def philox_normal(n: int, seed: int, stream_id: int, substream: int, device) -> torch.Tensor:
+    out = torch.empty(n, dtype=torch.float32, device=device)
+    check(lib().fb_philox_normal(vp(ptr(out)), i64(n), u64(seed), u32(stream_id), u32(substream),
+                                 vp(stream_ptr(device))), "philox_normal")
+    count_launch()
+    return out
+
+
+# --------------------------------------------------------------------------- K1 fused round
+def round_grid(P: int, G: int, emulated: int = 1) -> int:
+    return int(lib().fb_round_grid(i64(P), i32(G), i32(emulated)))
+
+
+def round_flag_bytes(G: int) -> int:
+    return int(lib().fb_round_flag_bytes(i32(G)))
+
+
+def round_launch(params: FbRoundParams, device=None):
+    check(lib().fb_round_launch(C.byref(params), vp(stream_ptr(device))), "round_launch")
+    count_launch()
+
+
+def round_launch_emulated(params: Sequence[FbRoundParams], P: int, device):
+    """All ranks in one cooperative launch on one GPU (tests; see B200_PROFILING "kernels that wait
+    on one another must not be separate launches on one GPU")."""
+    G = len(params)
+    arr = (FbRoundParams * G)(*params)
+    nbytes = C.sizeof(arr)
+    host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+    dev = host.to(device)
+    check(lib().fb_round_launch_emulated(vp(ptr(dev)), i32(G), i64(P), vp(stream_ptr(device))),
+          "round_launch_emulated")
+    count_launch()
+    torch.cuda.current_stream(device).synchronize()   # keep `dev` alive until the kernel has read it
+    return nbytes
+
+
+def peer_barrier(peer_flags_dev: torch.Tensor, rank: int, G: int, epoch: int, slot: int = 0):
+    check(lib().fb_peer_barrier(vp(ptr(peer_flags_dev)), i32(rank), i32(G), u32(epoch), i32(slot),
+                                vp(stream_ptr(peer_flags_dev.device))), "peer_barrier")
+    count_launch()
+
+
+# --------------------------------------------------------------------------- K5 / K6
+def ptr_table(ptrs: Sequence[int], device) -> torch.Tensor:
+    return torch.tensor(list(ptrs), dtype=torch.int64).to(device)
+
+
+def robust_select(rows_table: torch.Tensor, K: int, j0: int, j1: int, mode: str, trim: int,
+                  outs_table: torch.Tensor, n_out: int):
+    m = {"median": 0, "trimmed_mean": 1}[mode]
+    check(lib().fb_robust_select(vp(ptr(rows_table)), i32(K), i64(j0), i64(j1), i32(m), i32(trim),
+                                 vp(ptr(outs_table)), i32(n_out), vp(stream_ptr(rows_table.device))), "robust_select")
+    count_launch()
+
+
+def coordinate_median(stack: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Lower median over dim 0 of a [K, P] fp32 stack (rows may be strided)."""
+    return _select_local(stack, "median", 0, out)
+
+
+def trimmed_mean(stack: torch.Tensor, trim: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    return _select_local(stack, "trimmed_mean", trim, out)
+
+
+def _select_local(stack, mode, trim, out):
+    _req(stack, torch.float32, "stack")
+    K, P = stack.shape
+    out = torch.empty(P, dtype=torch.float32, device=stack.device) if out is None else out
+    rows = ptr_table([stack.data_ptr() + k * stack.stride(0) * 4 for k in range(K)], stack.device)
+    outs = ptr_table([out.data_ptr()], stack.device)
+    robust_select(rows, K, 0, P, mode, trim, outs, 1)
+    return out
+
+
+# --------------------------------------------------------------------------- K7
+def krum_pack(rows_table: torch.Tensor, K: int, ref: Optional[torch.Tensor], j0: int, j1: int, ld: int,
+              split: bool = True):
+    dev = rows_table.device
+    hi = torch.empty((K, ld), dtype=torch.bfloat16, device=dev)
+    lo = torch.empty((K, ld), dtype=torch.bfloat16, device=dev) if split else None
+    check(lib().fb_krum_pack(vp(ptr(rows_table)), i32(K), vp(ptr(ref)), i64(j0), i64(j1), vp(ptr(hi)), vp(ptr(lo)),
+                             i64(ld), vp(stream_ptr(dev))), "krum_pack")
+    count_launch()
+    return hi, lo
+
+
+def krum_scores(gram: torch.Tensor, f: int) -> torch.Tensor:
+    K = gram.shape[0]
+    scores = torch.empty(K, dtype=torch.float32, device=gram.device)
+    check(lib().fb_krum_scores(vp(ptr(_req(gram.contiguous(), torch.float32, "gram"))), i32(K), i32(f),
+                               vp(ptr(scores)), vp(stream_ptr(gram.device))), "krum_scores")
+    count_launch()
+    return scores
+
+
+# --------------------------------------------------------------------------- K8
+def ff_quantize(x: torch.Tensor, scale: float, p: int) -> torch.Tensor:
+    q = torch.empty(x.shape, dtype=torch.int32, device=x.device)
+    check(lib().fb_ff_quantize(vp(ptr(_req(x.contiguous(), torch.float32, "x"))), i64(x.numel()), f32(scale), u32(p),
+                               vp(ptr(q)), vp(stream_ptr(x.device))), "ff_quantize")
+    count_launch()
+    return q
+
+
+def ff_dequantize(q: torch.Tensor, scale: float, p: int) -> torch.Tensor:
+    x = torch.empty(q.shape, dtype=torch.float32, device=q.device)
+    check(lib().fb_ff_dequantize(vp(ptr(q)), i64(q.numel()), f32(1.0 / scale), u32(p), vp(ptr(x)),
+                                 vp(stream_ptr(q.device))), "ff_dequantize")
+    count_launch()
+    return x
+
+
+def ff_matmul(U: torch.Tensor, X: torch.Tensor, p: int) -> torch.Tensor:
+    """(U @ X) mod p for int32 field elements; U [n_out, n_in], X [n_in, d]."""
+    n_out, n_in = U.shape
+    d = X.shape[1]
+    out = torch.empty((n_out, d), dtype=torch.int32, device=X.device)
+    check(lib().fb_ff_matmul(vp(ptr(U.contiguous())), i32(n_out), i32(n_in), vp(ptr(X)), i64(d), i64(X.stride(0)), u32(p),
+                             vp(ptr(out)), i64(d), vp(stream_ptr(X.device))), "ff_matmul")
+    count_launch()
+    return out
+
+
+def ff_mask(x: torch.Tensor, seeds: Sequence[int], signs: Sequence[int], p: int) -> torch.Tensor:
+    dev = x.device
+    y = torch.empty_like(x)
+    s = torch.tensor([int(v) - (1 << 64) if int(v) >= (1 << 63) else int(v) for v in seeds], dtype=torch.int64).to(dev)
+    g = torch.tensor(list(signs), dtype=torch.int32).to(dev)
+    check(lib().fb_ff_mask(vp(ptr(x)), i64(x.numel()), vp(ptr(s)), vp(ptr(g)), i32(len(seeds)), u32(p), vp(ptr(y)),
+                           vp(stream_ptr(dev))), "ff_mask")
+    count_launch()
+    return y
+
+
+def ff_add_(acc: torch.Tensor, x: torch.Tensor, p: int) -> torch.Tensor:
+    check(lib().fb_ff_add(vp(ptr(acc)), vp(ptr(x)), i64(acc.numel()), u32(p), vp(stream_ptr(acc.device))), "ff_add")
+    count_launch()
+    return acc
+
+
+# --------------------------------------------------------------------------- K11 / K15
+def sgd_step_stacked(w: torch.Tensor, g: torch.Tensor, n: int, lr: torch.Tensor, weight_decay=0.0, momentum=0.0,
+                     dampening=0.0, nesterov=False, mom_buf=None, first_step=False, mu=0.0, anchor=None,
+                     cum_grad=None):
+    p, ld, Cn = _rows(w)
+    if g.dtype == torch.bfloat16:
+        check(lib().fb_sgd_step_stacked_bf16g(vp(p), vp(ptr(g)), i64(ld), i64(g.stride(0)), i32(Cn), i64(n),
+                                              vp(ptr(lr)), f32(weight_decay), f32(mu), vp(ptr(anchor)),
+                                              vp(stream_ptr(w.device))), "sgd_step_stacked_bf16g")
+    else:
+        if g.stride(0) != w.stride(0) and Cn > 1:
+            raise NativeError("sgd_step_stacked: w and g must share the row stride")
+        check(lib().fb_sgd_step_stacked(vp(p), vp(ptr(g)), i64(ld), i32(Cn), i64(n), vp(ptr(lr)), f32(weight_decay),
+                                        f32(momentum), f32(dampening), i32(int(nesterov)), vp(ptr(mom_buf)),
+                                        i32(int(first_step)), f32(mu), vp(ptr(anchor)), vp(ptr(cum_grad)),
+                                        vp(stream_ptr(w.device))), "sgd_step_stacked")
+    count_launch()
+    return w
+
+
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, ignore_index=-100, pre_sigmoid=False,
+                 row_scale: Optional[torch.Tensor] = None, rows_per_group: int = 1, want_loss=True, want_grad=True):
+    """logits [R, ncls] fp32 contiguous; returns (loss_rows or None, dlogits or None)."""
+    _req(logits, torch.float32, "logits"); _req(labels, torch.int64, "labels")
+    R, ncls = logits.shape
+    loss = torch.empty(R, dtype=torch.float32, device=logits.device) if want_loss else None
+    grad = torch.empty_like(logits) if want_grad else None
+    check(lib().fb_softmax_xent(vp(ptr(logits)), vp(ptr(labels)), i64(R), i32(ncls), i64(ignore_index),
+                                i32(int(pre_sigmoid)), vp(ptr(row_scale)), i64(rows_per_group), vp(ptr(loss)),
+                                vp(ptr(grad)), vp(stream_ptr(logits.device))), "softmax_xent")
+    count_launch()
+    return loss, grad
+
+
+def eval_counts(logits: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor, loss_sum: torch.Tensor,
+                pre_sigmoid=False):
+    """Accumulates [correct, total, tp.., fp.., fn..] (int32 view of uint32) and the loss sum."""
+    R, ncls = logits.shape
+    check(lib().fb_eval_counts(vp(ptr(_req(logits, torch.float32, "logits"))), vp(ptr(labels)), i64(R), i32(ncls),
+                               i32(int(pre_sigmoid)), vp(ptr(counts)), vp(ptr(loss_sum)),
+                               vp(stream_ptr(logits.device))), "eval_counts")
+    count_launch()

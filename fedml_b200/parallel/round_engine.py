@@ -1,0 +1,218 @@
+"""Driver of the fused FL round kernel (csrc/round.cu).
+
+One ``RoundEngine`` per rank owns the peer-visible buffers (global model, partial sums, flags),
+the server-optimizer moments and the DP scratch, and turns "these C client models with these
+weights" into one cooperative kernel launch that leaves the new global model on every rank.
+It replaces the reference's aggregate-on-rank-0-then-send path (FedAVGAggregator.aggregate +
+MPI model messages) — there is no NCCL call on the round path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from .. import ops
+from ..ops.native import FB_OPT, FB_ROUND_MAX_BLOCKS, FbRoundParams
+from .arena import ArenaLayout
+from .symmetric import SymmetricRegion
+
+
+@dataclass
+class ServerOptConfig:
+    name: str = "none"          # none | sgd | adam | adagrad | yogi
+    lr: float = 1.0
+    momentum: float = 0.0
+    beta1: float = 0.9
+    beta2: float = 0.99
+    eps: float = 1e-3
+    nesterov: bool = False
+
+    @classmethod
+    def from_args(cls, args, enabled: bool):
+        if not enabled:
+            return cls()
+        name = str(getattr(args, "server_optimizer", "sgd")).lower()
+        name = {"fedadam": "adam", "fedyogi": "yogi", "fedadagrad": "adagrad"}.get(name, name)
+        return cls(name, float(getattr(args, "server_lr", 1.0)), float(getattr(args, "server_momentum", 0.0)),
+                   float(getattr(args, "server_beta1", 0.9)), float(getattr(args, "server_beta2", 0.99)),
+                   float(getattr(args, "server_eps", 1e-3)))
+
+
+@dataclass
+class DPConfig:
+    clip: float = 0.0
+    sigma: float = 0.0
+    seed: int = 0
+
+
+class RoundEngine:
+    TWO_SHOT_BYTES = 8 << 20    # above this the reduce is bandwidth-bound: shard it
+
+    def __init__(self, layout: ArenaLayout, device, group=None, opt: Optional[ServerOptConfig] = None,
+                 dp: Optional[DPConfig] = None, two_shot: Optional[bool] = None, max_clients: int = 1024,
+                 provider: str = "auto"):
+        self.layout, self.device = layout, torch.device(device)
+        self.P, self.P_train = layout.P, layout.P_train
+        self.opt = opt or ServerOptConfig()
+        self.dp = dp or DPConfig()
+        flag_bytes = ops.round_flag_bytes(64)
+        need = 2 * self.P * 4 + flag_bytes + 4096
+        self.region = SymmetricRegion(need, self.device, group, provider)
+        self.G, self.rank = self.region.world, self.region.rank
+        self.region.carve("global", self.P * 4)
+        self.region.carve("partial", self.P * 4)
+        self.region.carve("flags", flag_bytes)
+        self.global_model = self.region.tensor("global")
+        self.partial = self.region.tensor("partial")
+        self.region.tensor("flags", torch.int32).zero_()
+        self.two_shot = (self.P * 4 >= self.TWO_SHOT_BYTES) if two_shot is None else bool(two_shot)
+        if self.G > 1:
+            self._peer_partial = self.region.peer_table("partial")
+            self._peer_global = self.region.peer_table("global")
+            self._peer_flags = self.region.peer_table("flags")
+        else:
+            self._peer_partial = self._peer_global = self._peer_flags = None
+        z = lambda: torch.zeros(self.P_train, dtype=torch.float32, device=self.device)
+        self.m = z() if (self.opt.name in ("adam", "yogi") or (self.opt.name == "sgd" and self.opt.momentum)) else None
+        self.v = z() if self.opt.name in ("adam", "yogi", "adagrad") else None
+        self.grid = ops.round_grid(self.P, self.G)
+        self.max_clients = max_clients
+        self.sqnorm_part = torch.zeros(self.grid * max_clients, dtype=torch.float32, device=self.device)
+        self.clip_scale = torch.zeros(max_clients, dtype=torch.float32, device=self.device)
+        self.grid_bar = torch.zeros(4, dtype=torch.int32, device=self.device)
+        self.epoch = 0
+        self.opt_step = 0
+        self.clip_calls = 0
+        self.region.barrier()
+
+    # ------------------------------------------------------------------
+    def set_global(self, flat: torch.Tensor):
+        self.global_model.copy_(flat.to(self.device, torch.float32))
+
+    def aggregate(self, clients: Optional[torch.Tensor], weights: Optional[torch.Tensor], inv_total: float,
+                  client_base: int = 0, round_idx: int = 0, weights_buf: Optional[torch.Tensor] = None,
+                  inv_total_buf: Optional[float] = None, self_coef: float = 0.0, grad_scale: float = 1.0,
+                  use_opt: bool = True) -> torch.Tensor:
+        """Launch the fused round.  ``clients``: fp32 [C, ld>=P] rows (or None when this rank drew no
+        client this round); ``weights``: fp32 [C] on the device.  Returns the (updated in place)
+        global model of this rank."""
+        p = FbRoundParams()
+        Cn = 0 if clients is None else clients.shape[0]
+        if Cn > self.max_clients:
+            raise ValueError(f"{Cn} clients exceed max_clients={self.max_clients}")
+        if Cn:
+            p.clients = clients.data_ptr()
+            p.ld = clients.stride(0) if Cn > 1 else max(clients.stride(0), self.P)
+            p.weights = weights.data_ptr()
+            p.weights_buf = weights_buf.data_ptr() if weights_buf is not None else None
+        p.C, p.client_base = Cn, client_base
+        p.P, p.P_train = self.P, self.P_train
+        p.inv_total = inv_total
+        p.inv_total_buf = inv_total if inv_total_buf is None else inv_total_buf
+        p.self_coef = self_coef
+        p.global_model, p.partial = self.global_model.data_ptr(), self.partial.data_ptr()
+        if self.G > 1:
+            p.peer_partial, p.peer_global = self._peer_partial.data_ptr(), self._peer_global.data_ptr()
+            p.peer_flags = self._peer_flags.data_ptr()
+        p.rank, p.G = self.rank, self.G
+        self.epoch += 1
+        p.epoch, p.two_shot = self.epoch, int(self.two_shot and self.G > 1)
+        p.clip_bound, p.noise_std = self.dp.clip, self.dp.sigma
+        p.seed, p.round = self.dp.seed, round_idx
+        o = self.opt if use_opt else ServerOptConfig()
+        p.opt = FB_OPT[o.name]
+        if p.opt:
+            self.opt_step += 1
+        p.nesterov, p.lr, p.momentum = int(o.nesterov), o.lr, o.momentum
+        p.beta1, p.beta2, p.eps = o.beta1, o.beta2, o.eps
+        p.bias_corr1 = 1.0 - o.beta1 ** max(self.opt_step, 1)
+        p.bias_corr2 = 1.0 - o.beta2 ** max(self.opt_step, 1)
+        p.grad_scale = grad_scale
+        p.m = self.m.data_ptr() if self.m is not None else None
+        p.v = self.v.data_ptr() if self.v is not None else None
+        if self.dp.clip > 0:
+            self.clip_calls += 1
+            p.sqnorm_part, p.clip_scale_out = self.sqnorm_part.data_ptr(), self.clip_scale.data_ptr()
+            p.grid_bar, p.grid_bar_target = self.grid_bar.data_ptr(), self.grid * self.clip_calls
+        ops.round_launch(p, self.device)
+        return self.global_model
+
+    # ------------------------------------------------------------------ checkpoint helpers
+    def state_dict(self):
+        return {"global": self.global_model.detach().cpu(), "m": None if self.m is None else self.m.cpu(),
+                "v": None if self.v is None else self.v.cpu(), "opt_step": self.opt_step}
+
+    def load_state_dict(self, sd):
+        self.global_model.copy_(sd["global"])
+        if self.m is not None and sd.get("m") is not None:
+            self.m.copy_(sd["m"])
+        if self.v is not None and sd.get("v") is not None:
+            self.v.copy_(sd["v"])
+        self.opt_step = int(sd.get("opt_step", 0))
+
+
+def emulated_round(clients_per_rank, weights_per_rank, global_model: torch.Tensor, P_train: int, inv_total: float,
+                   two_shot: bool, opt: ServerOptConfig = None, dp: DPConfig = None, m=None, v=None, opt_step=1,
+                   round_idx=0, epoch=1, state=None, self_coef=0.0, grad_scale=1.0, weights_buf_per_rank=None,
+                   inv_total_buf=None):
+    """Run G emulated ranks of the round kernel in ONE cooperative launch on one GPU.
+
+    Returns the list of per-rank global models after the round.  Used by the GPU tests to exercise
+    the multi-rank protocol (flags, one-/two-shot, determinism) without several GPUs."""
+    dev = global_model.device
+    G = len(clients_per_rank)
+    P = global_model.numel()
+    opt, dp = opt or ServerOptConfig(), dp or DPConfig()
+    st = state if state is not None else {}
+    if "globals" not in st:
+        st["globals"] = [global_model.clone() for _ in range(G)]
+        st["partials"] = [torch.zeros(P, device=dev) for _ in range(G)]
+        st["flags"] = [torch.zeros(ops.round_flag_bytes(G) // 4, dtype=torch.int32, device=dev) for _ in range(G)]
+        need_m = opt.name in ("adam", "yogi") or (opt.name == "sgd" and opt.momentum)
+        st["m"] = [(m.clone() if m is not None else torch.zeros(P_train, device=dev)) if need_m else None for _ in range(G)]
+        st["v"] = [(v.clone() if v is not None else torch.zeros(P_train, device=dev))
+                   if opt.name in ("adam", "yogi", "adagrad") else None for _ in range(G)]
+        st["grid_bar"] = [torch.zeros(4, dtype=torch.int32, device=dev) for _ in range(G)]
+        st["clip_calls"] = 0
+    grid = ops.round_grid(P, G, G)
+    tab = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64).to(dev)
+    t_partial, t_global, t_flags = tab(st["partials"]), tab(st["globals"]), tab(st["flags"])
+    if dp.clip > 0:
+        st["clip_calls"] += 1
+    params, keep = [], []
+    base = 0
+    for r in range(G):
+        p = FbRoundParams()
+        cl, wt = clients_per_rank[r], weights_per_rank[r]
+        Cn = 0 if cl is None else cl.shape[0]
+        if Cn:
+            p.clients, p.ld, p.weights = cl.data_ptr(), (cl.stride(0) if Cn > 1 else max(cl.stride(0), P)), wt.data_ptr()
+            if weights_buf_per_rank is not None:
+                p.weights_buf = weights_buf_per_rank[r].data_ptr()
+        p.C, p.client_base, p.P, p.P_train = Cn, base, P, P_train
+        base += Cn
+        p.inv_total = inv_total
+        p.inv_total_buf = inv_total if inv_total_buf is None else inv_total_buf
+        p.self_coef, p.grad_scale = self_coef, grad_scale
+        p.global_model, p.partial = st["globals"][r].data_ptr(), st["partials"][r].data_ptr()
+        p.peer_partial, p.peer_global, p.peer_flags = t_partial.data_ptr(), t_global.data_ptr(), t_flags.data_ptr()
+        p.rank, p.G, p.epoch, p.two_shot = r, G, epoch, int(two_shot and G > 1)
+        p.clip_bound, p.noise_std, p.seed, p.round = dp.clip, dp.sigma, dp.seed, round_idx
+        p.opt, p.nesterov, p.lr, p.momentum = FB_OPT[opt.name], int(opt.nesterov), opt.lr, opt.momentum
+        p.beta1, p.beta2, p.eps = opt.beta1, opt.beta2, opt.eps
+        p.bias_corr1, p.bias_corr2 = 1.0 - opt.beta1 ** opt_step, 1.0 - opt.beta2 ** opt_step
+        p.m = st["m"][r].data_ptr() if st["m"][r] is not None else None
+        p.v = st["v"][r].data_ptr() if st["v"][r] is not None else None
+        if dp.clip > 0:
+            sq = torch.zeros(grid * max(Cn, 1), dtype=torch.float32, device=dev)
+            cs = torch.zeros(max(Cn, 1), dtype=torch.float32, device=dev)
+            keep += [sq, cs]
+            p.sqnorm_part, p.clip_scale_out = sq.data_ptr(), cs.data_ptr()
+            p.grid_bar, p.grid_bar_target = st["grid_bar"][r].data_ptr(), grid * st["clip_calls"]
+        params.append(p)
+    ops.round_launch_emulated(params, P, dev)
+    st["_keep"] = keep
+    return st["globals"], st

@@ -1,0 +1,268 @@
+/* fedml_b200 native library — C ABI.
+ *
+ * One shared object (fedml_b200/native/libfedml_b200.so, sm_100a only) holds every hand-written
+ * kernel of the framework.  All entry points take raw device pointers and a CUDA stream, return 0
+ * on success or a negative FB_ERR_* code (text via fb_last_error()), and never allocate device
+ * memory: scratch buffers are supplied by the caller, sized by the *_scratch_bytes helpers.
+ * Python binds these with ctypes (fedml_b200/ops/native.py); C/C++ callers include this header.
+ *
+ * The reference (Cossack9989/FedML, python/fedml) has no native code at all; each
+ * declaration cites the Python call site whose work the kernel takes over.
+ */
+#ifndef FEDML_B200_H
+#define FEDML_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* fb_stream_t;
+
+const char* fb_last_error(void);
+int fb_version(void);
+int fb_device_sm_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Host runtime: shareable device allocations (CUDA IPC), peer access, pinned staging memory.
+ * These back fedml_b200.parallel.symmetric when torch's symmetric-memory rendezvous is unavailable;
+ * the reference's counterpart is ProcessGroupManager (cross_silo/hierarchical/process_group_manager.py:30-34).
+ * ------------------------------------------------------------------------------------------- */
+int fb_dev_malloc(void** out, int64_t bytes);      /* zero-filled cudaMalloc */
+int fb_dev_free(void* p);
+int fb_ipc_handle_bytes(void);
+int fb_ipc_get_handle(void* dev_ptr, void* handle_out);
+int fb_ipc_open_handle(const void* handle, void** out);
+int fb_ipc_close_handle(void* p);
+int fb_enable_peer_access(int peer_device);
+int fb_host_alloc_pinned(void** out, int64_t bytes);
+int fb_host_free_pinned(void* p);
+
+/* ---------------------------------------------------------------------------------------------
+ * K1+K2+K3+K4  Fused FL round kernel: per-client weighting, optional DP clip + Gaussian noise,
+ * local accumulation, cross-GPU reduction over peer (NVLink/NVSwitch) memory, server-optimizer
+ * step and redistribution of the new global model — one cooperative launch per rank, no NCCL.
+ * Replaces: FedAvgAPI._aggregate (fedavg/fedavg_api.py:206-221), FedAVGAggregator.aggregate
+ * (mpi_p2p_mp/fedavg/FedAVGAggregator.py:68-97), the MPI model send/recv (communication/mpi/*.py),
+ * RobustAggregator.norm_diff_clipping/add_noise (core/robustness/robust_aggregation.py:47-63),
+ * FedOpt server step (fedopt/fedopt_api.py:134-186), FedNova aggregate (fednova_trainer.py:136-164).
+ * ------------------------------------------------------------------------------------------- */
+enum { FB_OPT_NONE = 0, FB_OPT_SGD = 1, FB_OPT_ADAM = 2, FB_OPT_ADAGRAD = 3, FB_OPT_YOGI = 4 };
+
+typedef struct {
+  /* this rank's clients */
+  const float* clients;        /* [C][ld] fp32 stacked client models (NULL iff C == 0) */
+  int64_t ld;                  /* row stride in floats, multiple of 4 */
+  int32_t C;                   /* clients resident on this rank */
+  int32_t client_base;         /* global index of this rank's first client (keys the DP noise stream) */
+  const float* weights;        /* [C] aggregation weight of each client for [0, P_train) (e.g. n_i) */
+  const float* weights_buf;    /* [C] weights for [P_train, P) (BN buffers); NULL = same as weights */
+  int64_t P;                   /* model length in floats, multiple of 4 */
+  int64_t P_train;             /* leading trainable-parameter region (clip / noise / optimizer), multiple of 4 */
+  float inv_total;             /* scale applied to the summed weights for [0,P_train) (1 / sum n_i over ALL ranks) */
+  float inv_total_buf;         /* same for [P_train, P) */
+  float self_coef;             /* avg += self_coef * w_global on [0,P_train) (FedNova: 1 - sum coef_i; else 0) */
+  /* global model and cross-rank plumbing */
+  float* global_model;         /* [P] in: w(t), out: w(t+1); peers write into it in two-shot mode */
+  float* partial;              /* [P] this rank's partial sum, readable by peers */
+  float* const* peer_partial;  /* device array [G] of every rank's `partial` (NULL iff G == 1) */
+  float* const* peer_global;   /* device array [G] of every rank's `global_model` */
+  uint32_t* const* peer_flags; /* device array [G] of every rank's flag buffer: uint32[2][G][FB_ROUND_MAX_BLOCKS] */
+  int32_t rank, G;
+  uint32_t epoch;              /* strictly increasing across calls, same on all ranks, starts at 1 */
+  int32_t two_shot;            /* 0: every rank reduces the whole vector; 1: rank r reduces shard r and pushes it */
+  /* DP */
+  float clip_bound;            /* <= 0 disables clipping */
+  float noise_std;             /* <= 0 disables noise */
+  uint64_t seed;
+  uint32_t round;
+  /* server optimizer on g = (w - avg) * grad_scale */
+  int32_t opt;                 /* FB_OPT_* */
+  int32_t nesterov;
+  float lr, momentum, beta1, beta2, eps, bias_corr1, bias_corr2, grad_scale;
+  float* m;                    /* [P_train] first moment / momentum buffer (NULL if unused) */
+  float* v;                    /* [P_train] second moment (NULL if unused) */
+  /* scratch */
+  float* sqnorm_part;          /* [nblocks][C] per-block squared-norm partials (only when clipping) */
+  float* clip_scale_out;       /* [C] optional: the clip factor applied to every client (NULL to skip) */
+  uint32_t* grid_bar;          /* [1] zero-initialised counter for the intra-rank barrier */
+  uint32_t grid_bar_target;    /* nblocks * (number of clipped calls so far + 1) */
+} FbRoundParams;
+
+#define FB_ROUND_MAX_BLOCKS 1024
+
+/* Grid used for a model of P floats on G ranks (identical on every rank by construction). */
+int fb_round_grid(int64_t P, int32_t G, int32_t emulated_ranks);
+/* Bytes of the per-rank flag buffer (zero it once at set-up). */
+int64_t fb_round_flag_bytes(int32_t G);
+/* One rank of the round.  Every rank must launch with the same P, G, epoch, two_shot. */
+int fb_round_launch(const FbRoundParams* p, fb_stream_t stream);
+/* Test/emulation entry: run all G ranks as ONE cooperative launch on one GPU (blockIdx.y = rank).
+ * `params_dev` is a device array of G FbRoundParams whose peer_* arrays point at local buffers. */
+int fb_round_launch_emulated(const FbRoundParams* params_dev, int32_t G, int64_t P, fb_stream_t stream);
+
+/* K4 stand-alone: out[j] = beta*out[j] + scale * sum_c w[c] * X[c][j]  (local streaming accumulate). */
+int fb_weighted_accumulate(const float* clients, int64_t ld, int32_t C, const float* weights, float scale,
+                           float beta, float* out, int64_t P, fb_stream_t stream);
+/* bf16 client rows, fp32 accumulate. */
+int fb_weighted_accumulate_bf16(const void* clients_bf16, int64_t ld, int32_t C, const float* weights, float scale,
+                                float beta, float* out, int64_t P, fb_stream_t stream);
+/* rows[c][j] = src[j] for all c: broadcast the global model into the stacked client arena. */
+int fb_broadcast_rows(const float* src, float* rows, int64_t ld, int32_t C, int64_t P, fb_stream_t stream);
+
+/* K3 stand-alone server optimizer on one rank: w <- opt(w, avg). */
+int fb_server_opt(float* w, const float* avg, float* m, float* v, int64_t n, int32_t opt, int32_t nesterov,
+                  float lr, float momentum, float beta1, float beta2, float eps, float bias_corr1, float bias_corr2,
+                  float grad_scale, fb_stream_t stream);
+
+/* K2 stand-alone pieces (also used by tests as oracles for the fused path). */
+int fb_sqnorm_diff(const float* clients, int64_t ld, int32_t C, const float* ref, int64_t n, float* out_sq,
+                   fb_stream_t stream);                                   /* out_sq[c] = ||X[c][:n] - ref||^2 */
+int fb_philox_normal(float* out, int64_t n, uint64_t seed, uint32_t stream_id, uint32_t substream,
+                     fb_stream_t stream);                                 /* n multiple of 4 */
+
+/* Cross-rank barrier over peer flag buffers (1 block).  `slot` in [0, 8). */
+int fb_peer_barrier(uint32_t* const* peer_flags, int32_t rank, int32_t G, uint32_t epoch, int32_t slot,
+                    fb_stream_t stream);
+int64_t fb_peer_barrier_flag_bytes(int32_t G);
+
+/* ---------------------------------------------------------------------------------------------
+ * K5/K6  Coordinate-wise median / trimmed mean over K client rows that may live on different GPUs.
+ * Replaces RobustAggregator.coordinate_median_agg (robust_aggregation.py:65-99); trimmed mean is
+ * absent from the reference (Yin et al. 2018).  rows[k] may be peer-mapped pointers, so the
+ * "transpose" that brings all K values of a coordinate together happens inside the kernel loads.
+ * mode 0: lower median (torch.median tie rule); mode 1: mean of the values with rank in [trim, K-trim).
+ * Coordinates [j0, j1) are processed and written to every pointer in outs[0..n_out).
+ * ------------------------------------------------------------------------------------------- */
+int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t j0, int64_t j1, int32_t mode, int32_t trim,
+                     float* const* outs_dev, int32_t n_out, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K7  Krum: pack (centre + bf16 hi/lo split) and Gram matrix on tcgen05 tensor cores, then scores.
+ * Absent from the reference (Blanchard et al. 2017).
+ * ------------------------------------------------------------------------------------------- */
+/* dst_hi/lo[k][j - j0] = split_bf16(rows[k][j] - ref[j]) for j in [j0, j1); dst row stride ld_dst (elements). */
+int fb_krum_pack(const float* const* rows_dev, int32_t K, const float* ref, int64_t j0, int64_t j1, void* dst_hi,
+                 void* dst_lo, int64_t ld_dst, fb_stream_t stream);
+/* gram[K][K] (fp32) += A A^T over the packed columns; split-K partials reduced inside via atomics-free
+ * workspace of fb_gram_workspace_bytes.  Uses hi*hi + hi*lo + lo*hi when lo != NULL. */
+int64_t fb_gram_workspace_bytes(int32_t K, int64_t n_cols);
+int fb_gram_bf16(const void* a_hi, const void* a_lo, int32_t K, int64_t n_cols, int64_t ld, float* gram,
+                 void* workspace, fb_stream_t stream);
+/* scores[i] = sum of the (K - f - 2) smallest d2(i, j), j != i, with d2 from the Gram matrix. */
+int fb_krum_scores(const float* gram, int32_t K, int32_t f, float* scores, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K8  Secure-aggregation arithmetic in GF(p), p < 2^31 (reference: turboaggregate/mpc_function.py:4-281).
+ * ------------------------------------------------------------------------------------------- */
+/* q[i] = round(x[i] * scale) mod p  (negative values wrap to p - |.|);  inverse for dequantize. */
+int fb_ff_quantize(const float* x, int64_t n, float scale, uint32_t p, uint32_t* q, fb_stream_t stream);
+int fb_ff_dequantize(const uint32_t* q, int64_t n, float inv_scale, uint32_t p, float* x, fb_stream_t stream);
+/* out[i][d] = sum_j U[i][j] * X[j][d] mod p  — LCC/BGW encode and decode (mpc_function.py:62-75,111-136,201-217). */
+int fb_ff_matmul(const uint32_t* U, int32_t n_out, int32_t n_in, const uint32_t* X, int64_t d, int64_t ldx,
+                 uint32_t p, uint32_t* out, int64_t ldo, fb_stream_t stream);
+/* y = x + sum_{s} sign[s] * PRG(seed[s]) mod p — pairwise additive masks expanded in registers. */
+int fb_ff_mask(const uint32_t* x, int64_t n, const uint64_t* seeds_dev, const int32_t* signs_dev, int32_t n_seeds,
+               uint32_t p, uint32_t* y, fb_stream_t stream);
+/* acc = (acc + x) mod p */
+int fb_ff_add(uint32_t* acc, const uint32_t* x, int64_t n, uint32_t p, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K11  Fused multi-client optimizer step and losses (reference: one torch.optim kernel per tensor per
+ * step, my_model_trainer_classification.py:26-37; CrossEntropyLoss, BCELoss, KLDivLoss fedgkt/utils.py:78-124).
+ * ------------------------------------------------------------------------------------------- */
+/* For every client c and j < n:  d = g + wd*w (+ momentum) + mu*(w - anchor[j]);  w -= lr[c]*d.
+ * Optional FedNova accumulators: cum[c][j] += lr[c]*d.  lr[c] == 0 freezes a client. Rows share stride ld. */
+int fb_sgd_step_stacked(float* w, const float* g, int64_t ld, int32_t C, int64_t n, const float* lr_dev,
+                        float weight_decay, float momentum, float dampening, int32_t nesterov, float* mom_buf,
+                        int32_t first_step, float mu, const float* anchor, float* cum_grad, fb_stream_t stream);
+/* Same for bf16 gradients (fp32 master weights). */
+int fb_sgd_step_stacked_bf16g(float* w, const void* g_bf16, int64_t ld, int64_t ld_g, int32_t C, int64_t n,
+                              const float* lr_dev, float weight_decay, float mu, const float* anchor,
+                              fb_stream_t stream);
+/* Softmax cross-entropy over rows: logits [R][ncls] fp32, labels int64 [R] (ignore_index skips a row).
+ * loss_rows[R] (optional), dlogits[R][ncls] = (softmax - onehot) * row_scale[r / rows_per_group]
+ * (row_scale NULL -> 1/R). pre_sigmoid != 0 applies sigmoid to the logits first (the reference's LR model,
+ * model/linear/lr.py:10) and back-propagates through it. */
+int fb_softmax_xent(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int64_t ignore_index,
+                    int32_t pre_sigmoid, const float* row_scale, int64_t rows_per_group, float* loss_rows,
+                    float* dlogits, fb_stream_t stream);
+/* K15 fused evaluation: counters[0]=correct, [1]=loss_sum, [2]=total, then tp[ncls], fp[ncls], fn[ncls]
+ * (all float64-free: uint32 counts in `counts`, float loss in `loss_sum`). Accumulates into the outputs. */
+int fb_eval_counts(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int32_t pre_sigmoid,
+                   uint32_t* counts /* [2 + 3*ncls]: correct,total,tp..,fp..,fn.. */, float* loss_sum,
+                   fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K9  Grouped GEMM on tcgen05 tensor cores with TMEM accumulators and TMA-fed operands.
+ * For every group g:  D_g[M][N] = A_g[M][K] * B_g[N][K]^T  (bf16 in, fp32 accumulate, bf16 or fp32 out).
+ * Replaces per-client cuBLAS nn.Linear / 1x1-conv calls.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+  const void* a;      /* bf16 [G][M][K], K contiguous; group stride a_gs elements */
+  const void* b;      /* bf16 [G][N][K], K contiguous; group stride b_gs elements */
+  void* d;            /* [G][M][N], N contiguous; group stride d_gs elements */
+  const float* bias;  /* optional fp32 [G][N] (group stride bias_gs) */
+  int64_t a_gs, b_gs, d_gs, bias_gs;
+  int32_t G, M, N, K; /* K multiple of 8 (TMA 16-byte rows); any M, N */
+  int32_t lda, ldb, ldd; /* row strides in elements (multiples of 8 for bf16, 4 for fp32 out) */
+  int32_t d_fp32;     /* 1: fp32 output, 0: bf16 output */
+  int32_t relu;       /* fused ReLU epilogue */
+  int32_t accumulate; /* D += result (fp32 output only) */
+} FbGroupedGemm;
+int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K10 helpers: NHWC im2col / col2im for 3x3 convolutions batched over clients, fused per-client
+ * BatchNorm (+ReLU, +residual) forward/backward on [C][M][ch] activations.
+ * ------------------------------------------------------------------------------------------- */
+int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+                           int32_t stride, fb_stream_t stream);
+int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+                           int32_t stride, fb_stream_t stream);
+/* y = relu?(gamma*(x-mean)*rstd + beta (+res)); statistics per (client, channel) over M rows.
+ * x,y,res: bf16 [C][M][ch]; gamma/beta/running_*: fp32 [C][ch] rows with stride ld_p; save_mean/rstd fp32 [C][ch]. */
+int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch, const float* gamma,
+                      const float* beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
+                      const float* active, float momentum, float eps, int32_t relu, int32_t training,
+                      float* save_mean, float* save_rstd, fb_stream_t stream);
+/* dx (and dres = masked dy) from dy; dgamma/dbeta fp32 [C][ch] with stride ld_g. y is the forward output
+ * (needed for the ReLU mask). */
+int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C, int64_t M,
+                      int32_t ch, const float* gamma, int64_t ld_p, const float* save_mean, const float* save_rstd,
+                      int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K13  Cheetah data-parallel gradient all-reduce fused with the SGD(+momentum) step
+ * (reference: DDP bucketed NCCL all-reduce + torch.optim, cross_silo/hierarchical/trainer_dist_adapter.py:66).
+ * Rank r reduces shard r of the gradient bucket from all peers, updates the fp32 master shard and
+ * pushes the new parameters to every rank — one launch, no NCCL.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+  float* const* peer_grad;    /* [G] each rank's gradient bucket (fp32 [n]) */
+  float* const* peer_param;   /* [G] each rank's parameter bucket (fp32 [n]) */
+  uint32_t* const* peer_flags;/* [G] flag buffers (fb_round_flag_bytes) */
+  float* mom;                 /* [n] momentum (only shard of this rank is touched), may be NULL */
+  int64_t n;                  /* multiple of 4 */
+  int32_t rank, G;
+  uint32_t epoch;
+  float lr, momentum, weight_decay, inv_world;
+  int32_t nesterov;
+} FbDpStepParams;
+int fb_dp_allreduce_step(const FbDpStepParams* p, fb_stream_t stream);
+int fb_dp_allreduce_step_emulated(const FbDpStepParams* params_dev, int32_t G, int64_t n, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K14  HS-FedAvg amplitude normalisation (reference: single_process/hs_fedavg/hs_fft.py:8-84):
+ * per image/channel 2-D DFT, swap amplitude with the running mean amplitude, inverse DFT.
+ * H, W powers of two up to 512. amp_run [ch][H][W] updated with `momentum` when update_running != 0.
+ * ------------------------------------------------------------------------------------------- */
+int fb_amp_normalize(const float* x, float* y, int32_t n_img, int32_t ch, int32_t H, int32_t W, float* amp_run,
+                     float* amp_batch_mean, float momentum, int32_t update_running, int32_t have_running,
+                     void* workspace, fb_stream_t stream);
+int64_t fb_amp_normalize_workspace_bytes(int32_t n_img, int32_t ch, int32_t H, int32_t W);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDML_B200_H */

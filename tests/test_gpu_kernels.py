@@ -1,0 +1,301 @@
+"""Numerics of the hand-written sm_100a kernels against plain PyTorch fp32/fp64 oracles."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _lib(native_lib):
+    return native_lib
+
+
+def _stack(C, P, ld=None, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    ld = ld or P
+    buf = torch.randn(C, ld, generator=g).to(DEV)
+    return buf[:, :P] if ld != P else buf, buf
+
+
+def test_weighted_accumulate_fp32_and_bf16():
+    from fedml_b200 import ops
+    C, P = 13, 4 * 1237
+    x, _ = _stack(C, P, ld=P + 64)
+    w = torch.rand(C, device=DEV) * 50 + 1
+    out = torch.full((P,), 3.0, device=DEV)
+    ops.weighted_accumulate(x, w, out, scale=0.25, beta=0.5)
+    ref = 0.5 * 3.0 + 0.25 * (w[:, None].double() * x.double()).sum(0)
+    torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-4)
+    xb = x.to(torch.bfloat16).contiguous()
+    out2 = torch.zeros(P, device=DEV)
+    ops.weighted_accumulate(xb, w, out2)
+    ref2 = (w[:, None].double() * xb.double()).sum(0)
+    torch.testing.assert_close(out2.double(), ref2, rtol=1e-5, atol=1e-3)
+
+
+def test_broadcast_rows():
+    from fedml_b200 import ops
+    P, C = 4 * 999, 7
+    src = torch.randn(P, device=DEV)
+    rows = torch.zeros(C, P + 8, device=DEV)
+    ops.broadcast_rows(src, rows[:, :P])
+    assert torch.equal(rows[:, :P], src.expand(C, P))
+    assert float(rows[:, P:].abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("name,kw", [("sgd", {}), ("sgd", {"momentum": 0.9}), ("adam", {}), ("yogi", {}), ("adagrad", {})])
+def test_server_opt_matches_oracle(name, kw):
+    from fedml_b200 import ops
+    from fedml_b200.core.aggregation import ServerOptimizer
+    n = 4 * 511
+    torch.manual_seed(1)
+    w0 = torch.randn(n)
+    oracle = ServerOptimizer(name, lr=0.1, momentum=kw.get("momentum", 0.0), beta1=0.9, beta2=0.99, eps=1e-3)
+    w_ref = {"p": w0.clone()}
+    w = w0.clone().to(DEV)
+    m = torch.zeros(n, device=DEV); v = torch.zeros(n, device=DEV)
+    for step in range(1, 4):
+        avg = w_ref["p"] - 0.05 * torch.randn(n)
+        w_ref = oracle.step(w_ref, {"p": avg}, ["p"])
+        ops.server_opt(w, avg.to(DEV), m, v, name, lr=0.1, momentum=kw.get("momentum", 0.0), beta1=0.9, beta2=0.99,
+                       eps=1e-3, step=step)
+        torch.testing.assert_close(w.cpu(), w_ref["p"], rtol=2e-5, atol=2e-6)
+
+
+def test_sqnorm_diff_and_philox():
+    from fedml_b200 import ops
+    C, P = 5, 4 * 3001
+    x, _ = _stack(C, P)
+    ref = torch.randn(P, device=DEV)
+    sq = ops.sqnorm_diff(x, ref)
+    torch.testing.assert_close(sq.double(), ((x - ref).double() ** 2).sum(1), rtol=1e-5, atol=1e-3)
+    z = ops.philox_normal(1 << 20, seed=1234, stream_id=3, substream=7, device=DEV)
+    assert abs(float(z.mean())) < 5e-3 and abs(float(z.std()) - 1.0) < 5e-3
+    z2 = ops.philox_normal(1 << 20, seed=1234, stream_id=3, substream=7, device=DEV)
+    assert torch.equal(z, z2)
+    z3 = ops.philox_normal(1 << 20, seed=1234, stream_id=3, substream=8, device=DEV)
+    assert abs(float((z * z3).mean())) < 5e-3
+
+
+def _oracle_round(clients, weights, g, P_train, clip, sigma, seed, round_idx, opt_cfg, m, v, step, inv_total):
+    """fp64 restatement of the fused round for all clients of all ranks concatenated."""
+    from fedml_b200 import ops
+    X = torch.cat([c for c in clients if c is not None], 0).double()
+    w = torch.cat([c for c in weights if c is not None], 0).double()
+    gd = g.double()
+    contrib = X.clone()
+    if clip > 0 or sigma > 0:
+        diff = X[:, :P_train] - gd[:P_train]
+        if clip > 0:
+            nrm = diff.norm(dim=1)
+            diff = diff / torch.clamp(nrm / clip, min=1.0)[:, None]
+        contrib[:, :P_train] = gd[:P_train] + diff
+        if sigma > 0:
+            for c in range(X.shape[0]):
+                z = ops.philox_normal(g.numel(), seed, round_idx, c, g.device)[:P_train].double()
+                contrib[c, :P_train] += sigma * z
+    avg = (w[:, None] * contrib).sum(0) * inv_total
+    return avg
+
+
+@pytest.mark.parametrize("G,two_shot", [(1, False), (2, False), (2, True), (4, False), (4, True)])
+@pytest.mark.parametrize("dp", [False, True])
+def test_round_kernel_emulated_matches_oracle(G, two_shot, dp):
+    from fedml_b200.parallel.round_engine import DPConfig, ServerOptConfig, emulated_round
+    P, P_train = 4 * 5003, 4 * 4500
+    torch.manual_seed(G * 10 + int(two_shot))
+    g = torch.randn(P, device=DEV)
+    counts = [5, 0, 3, 4][:G] if G > 1 else [6]
+    clients = [(g + 0.1 * torch.randn(c, P, device=DEV)) if c else None for c in counts]
+    weights = [(torch.randint(10, 100, (c,), device=DEV).float()) if c else None for c in counts]
+    total = sum(float(w.sum()) for w in weights if w is not None)
+    dpc = DPConfig(clip=2.0, sigma=0.01, seed=99) if dp else DPConfig()
+    outs, _ = emulated_round(clients, weights, g, P_train, 1.0 / total, two_shot, dp=dpc, round_idx=3)
+    ref = _oracle_round(clients, weights, g, P_train, dpc.clip, dpc.sigma, dpc.seed, 3, None, None, None, 1, 1.0 / total)
+    for r in range(G):
+        torch.testing.assert_close(outs[r].double(), ref, rtol=1e-5, atol=2e-5)
+    for r in range(1, G):   # every rank holds the bit-identical model
+        assert torch.equal(outs[0], outs[r])
+
+
+def test_round_kernel_g_invariance_and_fedadam():
+    """Same clients split over 1, 2 and 4 emulated ranks give the same FedAdam result (tolerance:
+    partial sums are grouped differently), and two consecutive rounds keep moments consistent."""
+    from fedml_b200.core.aggregation import ServerOptimizer
+    from fedml_b200.parallel.round_engine import ServerOptConfig, emulated_round
+    P, P_train, K = 4 * 2048, 4 * 2000, 8
+    torch.manual_seed(7)
+    g0 = torch.randn(P, device=DEV)
+    opt = ServerOptConfig("adam", lr=0.05, beta1=0.9, beta2=0.99, eps=1e-3)
+    results = []
+    for G in (1, 2, 4):
+        g = g0.clone()
+        state = None
+        for rnd in range(2):
+            torch.manual_seed(100 + rnd)
+            X = g0 + 0.05 * torch.randn(K, P, device=DEV)
+            w = torch.arange(1, K + 1, device=DEV).float()
+            per = K // G
+            clients = [X[r * per:(r + 1) * per] for r in range(G)]
+            weights = [w[r * per:(r + 1) * per].contiguous() for r in range(G)]
+            outs, state = emulated_round(clients, weights, g, P_train, 1.0 / float(w.sum()), G > 1 and rnd == 1, opt=opt,
+                                         opt_step=rnd + 1, epoch=rnd + 1, state=state)
+        results.append(outs[0].clone())
+    # Adam divides by sqrt(v): a last-bit difference in the fp32 partial-sum grouping is amplified
+    # where g ~ 0, hence the looser bound than for plain averaging
+    torch.testing.assert_close(results[0], results[1], rtol=1e-3, atol=5e-4)
+    torch.testing.assert_close(results[0], results[2], rtol=1e-3, atol=5e-4)
+    # oracle for the G=1 path
+    oracle = ServerOptimizer("adam", lr=0.05, beta1=0.9, beta2=0.99, eps=1e-3)
+    wref = {"p": g0[:P_train].cpu().clone(), "b": g0[P_train:].cpu().clone()}
+    for rnd in range(2):
+        torch.manual_seed(100 + rnd)
+        X = (g0 + 0.05 * torch.randn(K, P, device=DEV)).cpu()
+        w = torch.arange(1, K + 1).float()
+        avg = (w[:, None] * X).sum(0) / w.sum()
+        wref = oracle.step(wref, {"p": avg[:P_train], "b": avg[P_train:]}, ["p"])
+    torch.testing.assert_close(results[0][:P_train].cpu(), wref["p"], rtol=1e-3, atol=5e-4)
+    torch.testing.assert_close(results[0][P_train:].cpu(), wref["b"], rtol=1e-5, atol=1e-5)
+
+
+def test_round_engine_single_rank_api():
+    from fedml_b200.models import LogisticRegression
+    from fedml_b200.parallel.arena import ArenaLayout
+    from fedml_b200.parallel.round_engine import RoundEngine
+    model = LogisticRegression(784, 10)
+    layout = ArenaLayout(model)
+    eng = RoundEngine(layout, DEV)
+    flat = layout.flatten(model.state_dict(), device=DEV)
+    eng.set_global(flat)
+    C = 9
+    stack = flat[None, :].repeat(C, 1) + 0.01 * torch.randn(C, layout.P, device=DEV)
+    w = torch.rand(C, device=DEV) + 0.5
+    out = eng.aggregate(stack, w, 1.0 / float(w.sum()))
+    ref = (w[:, None].double() * stack.double()).sum(0) / w.double().sum()
+    torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-6)
+    sd = layout.unflatten(out)
+    assert list(sd.keys()) == list(model.state_dict().keys())
+
+
+@pytest.mark.parametrize("K", [1, 2, 7, 10, 64, 257])
+def test_median_and_trimmed_mean(K):
+    from fedml_b200 import ops
+    P = 1000 + K
+    torch.manual_seed(K)
+    x = torch.randn(K, P, device=DEV)
+    x[:, :50] = torch.randint(0, 3, (K, 50), device=DEV).float()   # heavy ties
+    med = ops.coordinate_median(x)
+    assert torch.equal(med, torch.median(x, dim=0).values)
+    for trim in {0, K // 10, (K - 1) // 2}:
+        if 2 * trim >= K:
+            continue
+        tm = ops.trimmed_mean(x, trim)
+        ref = torch.sort(x.double(), dim=0).values[trim:K - trim].mean(0)
+        torch.testing.assert_close(tm.double(), ref, rtol=1e-5, atol=1e-5)
+
+
+def test_krum_scores_vs_oracle():
+    from fedml_b200 import ops
+    from fedml_b200.core.aggregation import krum_scores
+    K, P, f = 20, 512, 3
+    torch.manual_seed(0)
+    x = torch.randn(K, P, device=DEV)
+    x[:f] += 5.0
+    gram = (x.double() @ x.double().t()).float()
+    s = ops.krum_scores(gram, f)
+    ref = krum_scores(x.cpu(), f)
+    torch.testing.assert_close(s.cpu().double(), ref, rtol=2e-3, atol=1e-1)
+    assert int(torch.argmin(s)) == int(torch.argmin(ref))
+
+
+def test_finite_field_ops():
+    from fedml_b200 import ops
+    p = 2 ** 31 - 1
+    rng = np.random.default_rng(0)
+    x = torch.randn(10007, device=DEV) * 3
+    q = ops.ff_quantize(x, 2 ** 16, p)
+    qn = np.round(x.cpu().numpy().astype(np.float64) * 2 ** 16).astype(np.int64) % p
+    assert np.array_equal(q.cpu().numpy().astype(np.int64) & 0xFFFFFFFF, qn)
+    back = ops.ff_dequantize(q, 2 ** 16, p)
+    torch.testing.assert_close(back, x, rtol=0, atol=1.0 / 2 ** 16)
+    U = rng.integers(0, p, size=(6, 9), dtype=np.int64)
+    X = rng.integers(0, p, size=(9, 1001), dtype=np.int64)
+    out = ops.ff_matmul(torch.from_numpy(U.astype(np.int32)).to(DEV), torch.from_numpy(X.astype(np.int32)).to(DEV), p)
+    ref = np.zeros((6, 1001), dtype=object)
+    for i in range(6):
+        for j in range(9):
+            ref[i] = (ref[i] + int(U[i, j]) * X[j].astype(object)) % p
+    assert np.array_equal(out.cpu().numpy().astype(np.int64), ref.astype(np.int64))
+    # pairwise masks cancel
+    a = ops.ff_mask(q, [11, 22], [1, 1], p)
+    b = ops.ff_mask(q, [11, 22], [-1, -1], p)
+    s = ops.ff_add_(a.clone(), b, p)
+    two_q = (2 * qn) % p
+    assert np.array_equal(s.cpu().numpy().astype(np.int64) & 0xFFFFFFFF, two_q)
+    assert not torch.equal(a, q)
+
+
+def test_sgd_step_stacked_variants():
+    from fedml_b200 import ops
+    C, P, n = 6, 4 * 300, 4 * 250
+    torch.manual_seed(3)
+    w = torch.randn(C, P, device=DEV); g = torch.randn(C, P, device=DEV)
+    lr = torch.tensor([0.1, 0.2, 0.0, 0.05, 0.1, 0.3], device=DEV)
+    anchor = torch.randn(P, device=DEV)
+    w0 = w.clone()
+    ops.sgd_step_stacked(w, g, n, lr, weight_decay=0.01, mu=0.1, anchor=anchor)
+    d = g[:, :n] + 0.01 * w0[:, :n] + 0.1 * (w0[:, :n] - anchor[:n])
+    ref = w0.clone(); ref[:, :n] -= lr[:, None] * d
+    torch.testing.assert_close(w, ref, rtol=1e-5, atol=1e-6)
+    assert torch.equal(w[2], w0[2])
+    # momentum + FedNova cum_grad, two steps
+    w = w0.clone(); buf = torch.zeros_like(w); cum = torch.zeros_like(w)
+    ref_w = w0.clone(); ref_buf = None; ref_cum = torch.zeros_like(w)
+    for step in range(2):
+        g = torch.randn(C, P, device=DEV)
+        ops.sgd_step_stacked(w, g, n, lr, momentum=0.9, mom_buf=buf, first_step=(step == 0), cum_grad=cum)
+        d = g[:, :n]
+        ref_buf = d.clone() if ref_buf is None else 0.9 * ref_buf + d
+        act = (lr != 0)[:, None]
+        ref_cum[:, :n] += torch.where(act, lr[:, None] * ref_buf, torch.zeros_like(ref_buf))
+        ref_w[:, :n] -= lr[:, None] * ref_buf
+    torch.testing.assert_close(w, ref_w, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(cum, ref_cum, rtol=1e-5, atol=1e-6)
+    # bf16 gradients
+    w = w0.clone(); gb = torch.randn(C, P, device=DEV).to(torch.bfloat16)
+    ops.sgd_step_stacked(w, gb, n, lr)
+    ref = w0.clone(); ref[:, :n] -= lr[:, None] * gb[:, :n].float()
+    torch.testing.assert_close(w, ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("ncls,pre_sigmoid", [(10, False), (10, True), (62, False), (1000, False)])
+def test_softmax_xent_and_eval(ncls, pre_sigmoid):
+    from fedml_b200 import ops
+    R = 77
+    torch.manual_seed(ncls)
+    logits = torch.randn(R, ncls, device=DEV) * 3
+    labels = torch.randint(0, ncls, (R,), device=DEV)
+    loss, grad = ops.softmax_xent(logits, labels, pre_sigmoid=pre_sigmoid)
+    lg = logits.clone().requires_grad_(True)
+    z = torch.sigmoid(lg) if pre_sigmoid else lg
+    ref_rows = torch.nn.functional.cross_entropy(z, labels, reduction="none")
+    ref_rows.mean().backward()
+    torch.testing.assert_close(loss, ref_rows.detach(), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(grad, lg.grad, rtol=1e-3, atol=1e-6)
+    counts = torch.zeros(2 + 3 * ncls, dtype=torch.int32, device=DEV)
+    loss_sum = torch.zeros(1, device=DEV)
+    ops.eval_counts(logits, labels, counts, loss_sum, pre_sigmoid=pre_sigmoid)
+    pred = z.detach().argmax(1)
+    assert int(counts[0]) == int((pred == labels).sum()) and int(counts[1]) == R
+    torch.testing.assert_close(loss_sum[0], ref_rows.detach().sum(), rtol=1e-4, atol=1e-3)
+    tp = torch.bincount(labels[pred == labels], minlength=ncls)
+    fp = torch.bincount(pred[pred != labels], minlength=ncls)
+    fn = torch.bincount(labels[pred != labels], minlength=ncls)
+    assert torch.equal(counts[2:2 + ncls].long(), tp)
+    assert torch.equal(counts[2 + ncls:2 + 2 * ncls].long(), fp)
+    assert torch.equal(counts[2 + 2 * ncls:].long(), fn)
