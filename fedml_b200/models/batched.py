@@ -1,0 +1,451 @@
+"""Client-batched ("stacked") model execution: C co-resident clients advance one SGD step together.
+
+The reference trains the sampled clients one after another, each step being ~170 cuDNN/cuBLAS
+launches on tiny tensors (launch-bound).  Here the C clients that share a GPU are
+executed as ONE network whose every layer has a leading client dimension: activations are
+``[C, B, H, W, ch]`` (NHWC, bf16 on the GPU), parameters are ``[C, *shape]`` strided views into the
+stacked fp32 arena (``ArenaLayout.stacked_views``), convolutions become grouped GEMMs (1x1: directly,
+3x3: im2col), BatchNorm statistics are per (client, channel).  Forward *and* backward are written
+out explicitly (no autograd): every tensor is a static buffer, so a whole step is CUDA-graph
+capturable and every primitive can be a hand-written kernel.
+
+Primitive back-ends: :class:`TorchBackend` (plain PyTorch, any device/dtype — the CPU oracle path
+used by the tests) and :class:`NativeBackend` (sm_100a kernels from ``csrc/``: fused BN(+ReLU+residual)
+forward/backward, im2col/col2im, tcgen05 grouped GEMM).  Module/parameter names are taken from the
+reference-compatible ``nn.Module`` so arena segments line up with ``state_dict`` keys
+(model/cv/resnet.py:87-264, model/linear/lr.py:4-11).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .cv import BasicBlock, Bottleneck, LogisticRegression, ResNet
+
+
+# ============================================================================ back-ends
+class TorchBackend:
+    """Reference implementation of the batched primitives in plain PyTorch."""
+    name = "torch"
+
+    def __init__(self, dtype=torch.float32):
+        self.dtype = dtype
+
+    # ---- GEMMs (client-batched) -------------------------------------------------
+    def gemm_nt(self, a, b, out_dtype=None, relu=False):
+        """a [C,M,K] x b [C,N,K]^T -> [C,M,N]"""
+        y = torch.bmm(a, b.transpose(1, 2))
+        if relu:
+            y = torch.relu_(y)
+        return y if out_dtype is None else y.to(out_dtype)
+
+    def gemm_nn(self, a, b, out_dtype=None):
+        """a [C,M,N] x b [C,N,K] -> [C,M,K]"""
+        y = torch.bmm(a, b)
+        return y if out_dtype is None else y.to(out_dtype)
+
+    def gemm_tn(self, a, b, out_dtype=torch.float32):
+        """a [C,M,N]^T x b [C,M,K] -> [C,N,K]  (weight gradients; fp32 result)"""
+        return torch.bmm(a.transpose(1, 2), b).to(out_dtype)
+
+    # ---- im2col / col2im for 3x3, pad 1 (NHWC) ------------------------------------
+    def im2col3x3(self, x, stride):
+        C, B, H, W, ch = x.shape
+        Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+        xp = F.pad(x, (0, 0, 1, 1, 1, 1))
+        win = xp.unfold(2, 3, stride).unfold(3, 3, stride)          # [C,B,Ho,Wo,ch,3,3]
+        return win.permute(0, 1, 2, 3, 5, 6, 4).reshape(C, B * Ho * Wo, 9 * ch)
+
+    def col2im3x3(self, dcols, B, H, W, ch, stride):
+        C = dcols.shape[0]
+        Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+        d = dcols.view(C, B, Ho, Wo, 3, 3, ch)
+        dxp = torch.zeros(C, B, H + 2, W + 2, ch, dtype=dcols.dtype, device=dcols.device)
+        for kh in range(3):
+            for kw in range(3):
+                dxp[:, :, kh:kh + stride * Ho:stride, kw:kw + stride * Wo:stride, :] += d[:, :, :, :, kh, kw, :]
+        return dxp[:, :, 1:H + 1, 1:W + 1, :].contiguous()
+
+    # ---- BatchNorm (+residual, +ReLU) ---------------------------------------------
+    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
+        """x [C,B,H,W,ch]; gamma/beta/rm/rv [C,ch] fp32 (views, rm/rv updated in place); nbt [C] fp32."""
+        C = x.shape[0]
+        ch = x.shape[-1]
+        xf = x.float().reshape(C, -1, ch)
+        M = xf.shape[1]
+        if training:
+            mean = xf.mean(dim=1)
+            var = xf.var(dim=1, unbiased=False)
+            a = active.view(C, 1) * momentum
+            rm.add_(a * (mean - rm))
+            rv.add_(a * (var * (M / max(M - 1, 1)) - rv))
+            nbt.add_(active)
+        else:
+            mean, var = rm, rv
+        rstd = torch.rsqrt(var + eps)
+        y = (xf - mean[:, None, :]) * (rstd * gamma)[:, None, :] + beta[:, None, :]
+        y = y.view(x.shape)
+        if res is not None:
+            y = y + res.float()
+        if relu:
+            y = torch.relu(y)
+        return y.to(x.dtype), mean, rstd
+
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres):
+        C = x.shape[0]
+        ch = x.shape[-1]
+        dyf = dy.float()
+        if relu:
+            dyf = dyf * (y > 0)
+        dres = dyf.to(dy.dtype) if want_dres else None
+        d2 = dyf.reshape(C, -1, ch)
+        M = d2.shape[1]
+        xhat = (x.float().reshape(C, -1, ch) - mean[:, None, :]) * rstd[:, None, :]
+        dbeta = d2.sum(dim=1)
+        dgamma = (d2 * xhat).sum(dim=1)
+        dx = (gamma * rstd)[:, None, :] * (d2 - dbeta[:, None, :] / M - xhat * dgamma[:, None, :] / M)
+        return dx.view(x.shape).to(x.dtype), dres, dgamma, dbeta
+
+    # ---- loss ---------------------------------------------------------------------
+    def xent(self, logits, labels, pre_sigmoid=False, row_scale=None):
+        """logits [C,B,ncls] fp32, labels [C,B] (-1 = padding row) -> (loss per client [C], dlogits [C,B,ncls]).
+        ``row_scale`` [C] = 1 / (valid rows of that client); None means 1/B."""
+        C, B, ncls = logits.shape
+        lg = logits.detach().clone().requires_grad_(True)
+        z = torch.sigmoid(lg) if pre_sigmoid else lg
+        rows = F.cross_entropy(z.view(C * B, ncls), labels.reshape(-1), reduction="none", ignore_index=-1).view(C, B)
+        scale = torch.full((C,), 1.0 / B, dtype=torch.float32, device=logits.device) if row_scale is None else row_scale
+        loss = rows.sum(dim=1) * scale
+        loss.sum().backward()
+        return loss.detach(), lg.grad
+
+    def normalize_images(self, x_u8, mean, std):
+        """uint8 [C,B,H,W,3] -> normalised activations in the compute dtype."""
+        return ((x_u8.float() / 255.0 - mean) / std).to(self.dtype)
+
+
+class NativeBackend(TorchBackend):
+    """sm_100a kernels for the bandwidth-bound primitives; GEMMs go to the tcgen05 grouped GEMM when
+    the shape is supported by the kernel and to cuBLAS ``bmm`` otherwise (recorded in ``fallbacks``)."""
+    name = "native"
+
+    def __init__(self, dtype=torch.bfloat16, use_tc_gemm=True):
+        super().__init__(dtype)
+        from .. import ops
+        self.ops = ops
+        self.use_tc_gemm = use_tc_gemm and hasattr(ops, "grouped_gemm")
+        self.fallbacks: Dict[str, int] = {}
+
+    def _fb(self, what):
+        self.fallbacks[what] = self.fallbacks.get(what, 0) + 1
+
+    def gemm_nt(self, a, b, out_dtype=None, relu=False):
+        if self.use_tc_gemm and self.ops.grouped_gemm_supported(a, b):
+            return self.ops.grouped_gemm(a, b, out_dtype or a.dtype, relu=relu)
+        self._fb("gemm_nt")
+        return super().gemm_nt(a, b, out_dtype, relu)
+
+    def gemm_nn(self, a, b, out_dtype=None):
+        # [C,M,N] x [C,N,K]: the kernel wants both operands K-major -> use b^T copies prepared by the layer
+        self._fb("gemm_nn")
+        return super().gemm_nn(a, b, out_dtype)
+
+    def gemm_tn(self, a, b, out_dtype=torch.float32):
+        self._fb("gemm_tn")
+        return super().gemm_tn(a, b, out_dtype)
+
+    def im2col3x3(self, x, stride):
+        if hasattr(self.ops, "im2col3x3") and x.dtype == torch.bfloat16:
+            return self.ops.im2col3x3(x, stride)
+        self._fb("im2col")
+        return super().im2col3x3(x, stride)
+
+    def col2im3x3(self, dcols, B, H, W, ch, stride):
+        if hasattr(self.ops, "col2im3x3") and dcols.dtype == torch.bfloat16:
+            return self.ops.col2im3x3(dcols, B, H, W, ch, stride)
+        self._fb("col2im")
+        return super().col2im3x3(dcols, B, H, W, ch, stride)
+
+    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
+        if hasattr(self.ops, "bn_fwd_stacked") and x.dtype == torch.bfloat16:
+            return self.ops.bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
+        self._fb("bn_fwd")
+        return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
+
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres):
+        if hasattr(self.ops, "bn_bwd_stacked") and x.dtype == torch.bfloat16:
+            return self.ops.bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres)
+        self._fb("bn_bwd")
+        return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres)
+
+    def xent(self, logits, labels, pre_sigmoid=False, row_scale=None):
+        C, B, ncls = logits.shape
+        scale = torch.full((C,), 1.0 / B, dtype=torch.float32, device=logits.device) if row_scale is None else row_scale
+        loss_rows, grad = self.ops.softmax_xent(logits.reshape(C * B, ncls).contiguous(), labels.reshape(-1),
+                                                ignore_index=-1, pre_sigmoid=pre_sigmoid, row_scale=scale,
+                                                rows_per_group=B)
+        return loss_rows.view(C, B).sum(dim=1) * scale, grad.view(C, B, ncls)
+
+
+# ============================================================================ layers
+class _Conv:
+    def __init__(self, name, k, stride, cin, cout, need_dx=True):
+        self.name, self.k, self.stride, self.cin, self.cout, self.need_dx = name, k, stride, cin, cout, need_dx
+        self.wname = name + ".weight"
+
+    def prep(self, W, dtype):
+        """fp32 master [C,cout,cin,k,k] -> compute-dtype matrix [C, cout, k*k*cin] in (kh,kw,cin) order."""
+        w = W[self.wname]
+        C = w.shape[0]
+        if self.k == 1:
+            return w.reshape(C, self.cout, self.cin).to(dtype)
+        return w.permute(0, 1, 3, 4, 2).reshape(C, self.cout, self.k * self.k * self.cin).to(dtype)
+
+    def _cols(self, be, x):
+        C, B, H, W_, _ = x.shape
+        s = self.stride
+        if self.k == 1:
+            xs = x if s == 1 else x[:, :, ::s, ::s, :]
+            Ho, Wo = xs.shape[2], xs.shape[3]
+            return xs.reshape(C, B * Ho * Wo, self.cin), Ho, Wo
+        Ho, Wo = (H - 1) // s + 1, (W_ - 1) // s + 1
+        return be.im2col3x3(x, s), Ho, Wo
+
+    def fwd(self, be, x, Wm):
+        C, B = x.shape[0], x.shape[1]
+        cols, Ho, Wo = self._cols(be, x)
+        return be.gemm_nt(cols, Wm).view(C, B, Ho, Wo, self.cout)
+
+    def bwd(self, be, dy, x, Wm, gW):
+        C, B, H, W_, _ = x.shape
+        cols, Ho, Wo = self._cols(be, x)
+        dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
+        dWm = be.gemm_tn(dy2, cols)                                   # [C, cout, kk*cin] fp32
+        if self.k == 1:
+            gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1))
+        else:
+            gW.copy_(dWm.view(C, self.cout, self.k, self.k, self.cin).permute(0, 1, 4, 2, 3))
+        if not self.need_dx:
+            return None
+        dcols = be.gemm_nn(dy2, Wm)                                   # [C, M, kk*cin]
+        if self.k == 1:
+            if self.stride == 1:
+                return dcols.view(C, B, H, W_, self.cin)
+            dx = torch.zeros(C, B, H, W_, self.cin, dtype=dcols.dtype, device=dcols.device)
+            dx[:, :, ::self.stride, ::self.stride, :] = dcols.view(C, B, Ho, Wo, self.cin)
+            return dx
+        return be.col2im3x3(dcols, B, H, W_, self.cin, self.stride)
+
+
+class _BN:
+    def __init__(self, name, ch, momentum=0.1, eps=1e-5):
+        self.name, self.ch, self.momentum, self.eps = name, ch, momentum, eps
+
+    def fwd(self, be, x, W, active, relu, res=None, training=True):
+        n = self.name
+        return be.bn_fwd(x, res, W[n + ".weight"], W[n + ".bias"], W[n + ".running_mean"], W[n + ".running_var"],
+                         W[n + ".num_batches_tracked"], active, self.momentum, self.eps, relu, training)
+
+    def bwd(self, be, dy, x, y, W, G, mean, rstd, relu, want_dres):
+        n = self.name
+        dx, dres, dgamma, dbeta = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres)
+        G[n + ".weight"].copy_(dgamma)
+        G[n + ".bias"].copy_(dbeta)
+        return dx, dres
+
+
+class _Block:
+    """BasicBlock (2 convs) or Bottleneck (3 convs) with optional conv+BN downsample."""
+
+    def __init__(self, prefix: str, mod: nn.Module):
+        self.prefix = prefix
+        self.convs: List[_Conv] = []
+        self.bns: List[_BN] = []
+        n = 3 if isinstance(mod, Bottleneck) else 2
+        for i in range(1, n + 1):
+            c = getattr(mod, f"conv{i}")
+            self.convs.append(_Conv(f"{prefix}.conv{i}", c.kernel_size[0], c.stride[0], c.in_channels, c.out_channels))
+            self.bns.append(_BN(f"{prefix}.bn{i}", c.out_channels, getattr(mod, f"bn{i}").momentum,
+                                getattr(mod, f"bn{i}").eps))
+        self.ds = None
+        if mod.downsample is not None:
+            c, b = mod.downsample[0], mod.downsample[1]
+            self.ds = (_Conv(f"{prefix}.downsample.0", 1, c.stride[0], c.in_channels, c.out_channels),
+                       _BN(f"{prefix}.downsample.1", c.out_channels, b.momentum, b.eps))
+
+    def all_convs(self):
+        return self.convs + ([self.ds[0]] if self.ds else [])
+
+    def fwd(self, be, x, W, Wm, active, training, tape):
+        saved = {"x": x}
+        h = x
+        n = len(self.convs)
+        if self.ds is not None:
+            dconv, dbn = self.ds
+            a = dconv.fwd(be, x, Wm[dconv.name])
+            idt, m, r = dbn.fwd(be, a, W, active, relu=False, training=training)
+            saved["ds"] = (a, idt, m, r)
+        else:
+            idt = x
+        for i, (conv, bn) in enumerate(zip(self.convs, self.bns)):
+            a = conv.fwd(be, h, Wm[conv.name])
+            last = i == n - 1
+            y, m, r = bn.fwd(be, a, W, active, relu=True, res=idt if last else None, training=training)
+            saved[i] = (h, a, y, m, r)
+            h = y
+        if tape is not None:
+            tape.append(saved)
+        return h
+
+    def bwd(self, be, dy, W, Wm, G, saved):
+        n = len(self.convs)
+        d = dy
+        d_idt = None
+        for i in reversed(range(n)):
+            conv, bn = self.convs[i], self.bns[i]
+            h, a, y, m, r = saved[i]
+            last = i == n - 1
+            da, dres = bn.bwd(be, d, a, y, W, G, m, r, relu=True, want_dres=last)
+            if last:
+                d_idt = dres
+            d = conv.bwd(be, da, h, Wm[conv.name], G[conv.wname])
+        if self.ds is not None:
+            dconv, dbn = self.ds
+            a, idt, m, r = saved["ds"]
+            da, _ = dbn.bwd(be, d_idt, a, idt, W, G, m, r, relu=False, want_dres=False)
+            d = d + dconv.bwd(be, da, saved["x"], Wm[dconv.name], G[dconv.wname])
+        else:
+            d = d + d_idt
+        return d
+
+
+# ============================================================================ models
+class BatchedModel:
+    """Interface the NCCL simulator drives."""
+    input_kind = "flat"
+
+    def prepare(self, W):                       # per-step weight staging (dtype casts / re-layouts)
+        raise NotImplementedError
+
+    def train_step(self, x, y, W, G, active, row_scale=None):   # -> per-client mean loss [C]; grads written into G
+        raise NotImplementedError
+
+    def logits(self, x, W):                     # eval-mode forward
+        raise NotImplementedError
+
+
+class BatchedLogisticRegression(BatchedModel):
+    """C logistic-regression clients; sigmoid-then-CE numerics of the reference (lr.py:10)."""
+
+    def __init__(self, module: LogisticRegression, backend: TorchBackend):
+        self.be = backend
+        self.in_dim, self.out_dim = module.linear.in_features, module.linear.out_features
+        self.pre_sigmoid = True
+
+    def prepare(self, W):
+        return {"w": W["linear.weight"].to(self.be.dtype)}
+
+    def _fwd(self, x, W, Wm):
+        C = x.shape[0]
+        xin = x.reshape(C, x.shape[1], -1).to(self.be.dtype)
+        return xin, self.be.gemm_nt(xin, Wm["w"], out_dtype=torch.float32) + W["linear.bias"][:, None, :]
+
+    def train_step(self, x, y, W, G, active, row_scale=None):
+        Wm = self.prepare(W)
+        xin, logits = self._fwd(x, W, Wm)
+        loss, dlog = self.be.xent(logits, y, pre_sigmoid=True, row_scale=row_scale)
+        G["linear.weight"].copy_(self.be.gemm_tn(dlog.to(self.be.dtype), xin))
+        G["linear.bias"].copy_(dlog.sum(dim=1))
+        return loss
+
+    def logits(self, x, W):
+        return self._fwd(x, W, self.prepare(W))[1]
+
+
+class BatchedResNet(BatchedModel):
+    """CIFAR-stem / 3x3-stem ResNets (ResNet-56 Bottleneck, ResNet-18 BasicBlock) over C clients."""
+    input_kind = "image_u8_nhwc"
+
+    def __init__(self, module: ResNet, backend: TorchBackend, mean=None, std=None):
+        self.be = backend
+        if getattr(module, "stem", "cifar") != "cifar" and not isinstance(getattr(module, "maxpool", None), nn.Identity):
+            raise NotImplementedError("batched ResNet supports 3x3 stems without max-pool (CIFAR-sized inputs)")
+        c1 = module.conv1
+        self.stem_conv = _Conv("conv1", c1.kernel_size[0], c1.stride[0], c1.in_channels, c1.out_channels, need_dx=False)
+        self.stem_bn = _BN("bn1", c1.out_channels, module.bn1.momentum, module.bn1.eps)
+        self.blocks: List[_Block] = []
+        for li in range(1, module.num_stages + 1):
+            for bi, blk in enumerate(getattr(module, f"layer{li}")):
+                self.blocks.append(_Block(f"layer{li}.{bi}", blk))
+        self.feat_dim, self.ncls = module.fc.in_features, module.fc.out_features
+        self.convs = [self.stem_conv] + [c for b in self.blocks for c in b.all_convs()]
+        self.mean = torch.tensor(mean if mean is not None else (0.4914, 0.4822, 0.4465), dtype=torch.float32)
+        self.std = torch.tensor(std if std is not None else (0.2470, 0.2435, 0.2616), dtype=torch.float32)
+
+    def prepare(self, W):
+        dt = self.be.dtype
+        Wm = {c.name: c.prep(W, dt) for c in self.convs}
+        Wm["fc"] = W["fc.weight"].to(dt)
+        return Wm
+
+    def _input(self, x):
+        if x.dtype == torch.uint8:
+            if self.mean.device != x.device:     # one-time move; must not happen inside a CUDA-graph capture
+                self.mean, self.std = self.mean.to(x.device), self.std.to(x.device)
+            return self.be.normalize_images(x, self.mean, self.std)
+        return x.to(self.be.dtype)
+
+    def _forward(self, x, W, Wm, active, training, tape):
+        be = self.be
+        x = self._input(x)
+        a = self.stem_conv.fwd(be, x, Wm["conv1"])
+        h, m, r = self.stem_bn.fwd(be, a, W, active, relu=True, training=training)
+        if tape is not None:
+            tape.append((x, a, h, m, r))
+        for blk in self.blocks:
+            h = blk.fwd(be, h, W, Wm, active, training, tape)
+        C, B = h.shape[0], h.shape[1]
+        feat = h.float().mean(dim=(2, 3)).to(be.dtype)                 # [C,B,feat]
+        logits = be.gemm_nt(feat, Wm["fc"], out_dtype=torch.float32) + W["fc.bias"][:, None, :]
+        return logits, feat, h
+
+    def train_step(self, x, y, W, G, active, row_scale=None):
+        be = self.be
+        Wm = self.prepare(W)
+        tape: list = []
+        logits, feat, h_last = self._forward(x, W, Wm, active, True, tape)
+        loss, dlog = be.xent(logits, y, row_scale=row_scale)
+        dlog_c = dlog.to(be.dtype)
+        G["fc.weight"].copy_(be.gemm_tn(dlog_c, feat))
+        G["fc.bias"].copy_(dlog.sum(dim=1))
+        dfeat = be.gemm_nn(dlog_c, Wm["fc"])                           # [C,B,feat]
+        C, B, H, W_, ch = h_last.shape
+        d = (dfeat.float() / (H * W_)).to(be.dtype)[:, :, None, None, :].expand(C, B, H, W_, ch).contiguous()
+        for blk, saved in zip(reversed(self.blocks), reversed(tape[1:])):
+            d = blk.bwd(be, d, W, Wm, G, saved)
+        x0, a, hstem, m, r = tape[0]
+        da, _ = self.stem_bn.bwd(be, d, a, hstem, W, G, m, r, relu=True, want_dres=False)
+        self.stem_conv.bwd(be, da, x0, Wm["conv1"], G["conv1.weight"])
+        return loss
+
+    def logits(self, x, W):
+        C = x.shape[0]
+        active = torch.zeros(C, dtype=torch.float32, device=x.device)
+        return self._forward(x, W, self.prepare(W), active, False, None)[0]
+
+
+def make_batched(module: nn.Module, backend: TorchBackend) -> Optional[BatchedModel]:
+    """Batched executor for ``module`` or None when the family has no batched implementation yet
+    (the simulator then falls back to per-client eager training on arena-bound parameters)."""
+    if isinstance(module, LogisticRegression):
+        return BatchedLogisticRegression(module, backend)
+    if isinstance(module, ResNet) and module.group_norm == 0 and not module.KD:
+        try:
+            return BatchedResNet(module, backend)
+        except NotImplementedError:
+            return None
+    return None

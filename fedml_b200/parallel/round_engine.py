@@ -59,12 +59,13 @@ class RoundEngine:
         self.opt = opt or ServerOptConfig()
         self.dp = dp or DPConfig()
         flag_bytes = ops.round_flag_bytes(64)
-        need = 2 * self.P * 4 + flag_bytes + 4096
+        need = 2 * self.P * 4 + flag_bytes + 8 * 64 * 4 + 4096
         self.region = SymmetricRegion(need, self.device, group, provider)
         self.G, self.rank = self.region.world, self.region.rank
         self.region.carve("global", self.P * 4)
         self.region.carve("partial", self.P * 4)
         self.region.carve("flags", flag_bytes)
+        self.region.carve("barflags", 8 * 64 * 4)
         self.global_model = self.region.tensor("global")
         self.partial = self.region.tensor("partial")
         self.region.tensor("flags", torch.int32).zero_()
@@ -73,6 +74,7 @@ class RoundEngine:
             self._peer_partial = self.region.peer_table("partial")
             self._peer_global = self.region.peer_table("global")
             self._peer_flags = self.region.peer_table("flags")
+            self._peer_bar = self.region.peer_table("barflags")
         else:
             self._peer_partial = self._peer_global = self._peer_flags = None
         z = lambda: torch.zeros(self.P_train, dtype=torch.float32, device=self.device)
@@ -84,11 +86,18 @@ class RoundEngine:
         self.clip_scale = torch.zeros(max_clients, dtype=torch.float32, device=self.device)
         self.grid_bar = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.epoch = 0
+        self.bar_epoch = 0
         self.opt_step = 0
         self.clip_calls = 0
         self.region.barrier()
 
     # ------------------------------------------------------------------
+    def device_barrier(self, slot: int = 0):
+        """Cross-rank barrier executed on the stream (flag writes over peer memory, no host sync)."""
+        if self.G > 1:
+            self.bar_epoch += 1
+            ops.peer_barrier(self._peer_bar, self.rank, self.G, self.bar_epoch, slot)
+
     def set_global(self, flat: torch.Tensor):
         self.global_model.copy_(flat.to(self.device, torch.float32))
 

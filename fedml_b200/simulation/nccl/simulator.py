@@ -1,0 +1,610 @@
+"""The multi-GPU ("NCCL") Parrot simulator — a stub in the reference, the product path here.
+
+Reference state: ``SimulatorNCCL.__init__`` sets ``self.simulator = None`` (simulation/simulator.py:100-108)
+and ``simulation/nccl/README.md`` only says "AllReduce-based Federated Learning with Resource
+Scheduling".  Semantics are therefore lifted from the SP/MPI FedAvg loops:
+per round ``np.random.seed(round)`` client sampling, sample-count weighting over every state entry,
+periodic evaluation — identical for any number of GPUs.
+
+Design (one process per GPU, ``torch.distributed`` only for bootstrap):
+  * the K sampled clients are assigned to ranks by LPT scheduling on their sample counts
+    (core/schedule/scheduler.py semantics);
+  * each rank keeps its clients' models as rows of a device-resident fp32 stack ``[C, P]`` (no
+    ``state_dict`` copies, no D2H), broadcasts the global model into the rows, and trains all rows
+    together with the client-batched executor (models/batched.py) under a CUDA graph — or, for model
+    families / custom trainers without a batched implementation, one client at a time on
+    arena-bound parameters;
+  * inputs come from the packed host dataset through one pinned staging buffer and ONE H2D copy per
+    round and rank;
+  * the round ends with ONE fused kernel (csrc/round.cu) that weights, clips/noises, reduces across
+    GPUs over peer memory, applies the server optimizer and leaves the new global model on every
+    rank; robust aggregators (median / trimmed mean / Krum) use csrc/robust.cu on peer rows.
+On a CPU-only box the same control flow runs with the PyTorch oracles and a gloo all-reduce, which
+is what the multi-process CPU tests exercise.
+"""
+from __future__ import annotations
+
+import logging
+import math
+import os
+import time
+from collections import OrderedDict
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ...core import aggregation as A
+from ...core.schedule import schedule_clients
+from ...constants import canonical_optimizer_name
+from ...models.batched import NativeBackend, TorchBackend, make_batched
+from ...ops import native as _native
+from ...parallel.arena import ArenaLayout, bind_module_to_flat
+from ...utils.metrics import MetricsSink
+from ..sp.fedavg_api import client_sampling
+from ..trainers import create_model_trainer
+
+
+def _dist_setup(device: torch.device):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        backend = "nccl" if device.type == "cuda" else "gloo"
+        kw = {"device_id": device} if device.type == "cuda" else {}
+        dist.init_process_group(backend=backend, rank=int(os.environ.get("RANK", "0")), world_size=world, **kw)
+    if dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+class PhaseTimer:
+    """CUDA-event timers per phase; ``summary`` reduces to the max over ranks (measurement rule of
+    BASELINE.json: multi-GPU numbers are device times, max over ranks)."""
+
+    def __init__(self, device):
+        self.device, self.cuda = device, device.type == "cuda"
+        self.pending: Dict[str, list] = {}
+        self.totals: Dict[str, float] = {}
+
+    def start(self, name):
+        if self.cuda:
+            ev = torch.cuda.Event(enable_timing=True); ev.record()
+        else:
+            ev = time.perf_counter()
+        self.pending.setdefault(name, []).append([ev, None])
+
+    def stop(self, name):
+        if self.cuda:
+            ev = torch.cuda.Event(enable_timing=True); ev.record()
+        else:
+            ev = time.perf_counter()
+        self.pending[name][-1][1] = ev
+
+    def collect(self):
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        for name, pairs in self.pending.items():
+            for a, b in pairs:
+                if b is None:
+                    continue
+                ms = a.elapsed_time(b) if self.cuda else (b - a) * 1e3
+                self.totals[name] = self.totals.get(name, 0.0) + ms
+        self.pending = {}
+        return dict(self.totals)
+
+
+class NCCLSimulator:
+    def __init__(self, args, device, dataset, model, model_trainer=None, server_aggregator=None):
+        self.args = args
+        self.device = torch.device(device)
+        self.rank, self.world = _dist_setup(self.device)
+        self.cuda = self.device.type == "cuda"
+        if self.cuda:
+            torch.cuda.set_device(self.device)
+        ds = list(dataset)
+        (self.train_num, self.test_num, self.train_global, self.test_global, self.local_num, self.train_local,
+         self.test_local, self.class_num) = ds[:8]
+        self.fed = getattr(args, "_federated_dataset", None)
+        self.model = model
+        self.layout = ArenaLayout(model)
+        self.P, self.P_train = self.layout.P, self.layout.P_train
+        self.alg = canonical_optimizer_name(getattr(args, "federated_optimizer", "FedAvg"))
+        self.robust = str(getattr(args, "robust_agg", "none") or "none").lower()
+        dt = str(getattr(args, "defense_type", "") or "").lower()
+        if self.alg == "FedAvg_robust" and self.robust == "none" and dt:
+            self.robust = {"norm_diff_clipping": "clip", "weak_dp": "weak_dp", "median": "median",
+                           "coordinate_median": "median", "trimmed_mean": "trimmed_mean", "krum": "krum",
+                           "multi_krum": "krum"}.get(dt, "none")
+        self.metrics = MetricsSink(args) if self.rank == 0 else None
+        self.timer = PhaseTimer(self.device)
+        self.history: List[dict] = []
+        self.custom_trainer = model_trainer
+        self.K = min(int(args.client_num_per_round), int(args.client_num_in_total))
+        self.C_max = int(math.ceil(self.K / self.world))
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+        self._build_engine()
+        self._build_executor()
+        self.round_idx = 0
+
+    # ------------------------------------------------------------------ set-up
+    def _build_engine(self):
+        args = self.args
+        flat0 = self.layout.flatten(self.model.state_dict())
+        clip = float(getattr(args, "dp_clip", 0.0) or 0.0)
+        sigma = float(getattr(args, "dp_sigma", 0.0) or 0.0)
+        if self.robust in ("clip", "weak_dp"):
+            clip = clip or float(getattr(args, "norm_bound", 5.0))
+            if self.robust == "weak_dp":
+                sigma = sigma or float(getattr(args, "stddev", 0.025))
+        self.dp_clip, self.dp_sigma = clip, sigma
+        use_opt = self.alg == "FedOpt"
+        if self.cuda:
+            from ...parallel.round_engine import DPConfig, RoundEngine, ServerOptConfig
+            two_shot = getattr(args, "two_shot", None)
+            self.engine = RoundEngine(self.layout, self.device, opt=ServerOptConfig.from_args(args, use_opt),
+                                      dp=DPConfig(clip, sigma, int(getattr(args, "random_seed", 0))),
+                                      two_shot=two_shot, max_clients=max(self.C_max, 1),
+                                      provider=str(getattr(args, "symmetric_provider", "auto")))
+            self.engine.set_global(flat0)
+            self.global_flat = self.engine.global_model
+            need_peer_rows = self.robust in ("median", "trimmed_mean", "krum") and self.world > 1
+            if need_peer_rows:
+                from ...parallel.symmetric import SymmetricRegion
+                self.stack_region = SymmetricRegion(self.C_max * self.P * 4 + 4096, self.device,
+                                                    provider=self.engine.region.provider)
+                self.stack_region.carve("stack", self.C_max * self.P * 4)
+                self.stack = self.stack_region.tensor("stack").view(self.C_max, self.P)
+            else:
+                self.stack_region = None
+                self.stack = torch.zeros(self.C_max, self.P, dtype=torch.float32, device=self.device)
+        else:
+            self.engine = None
+            self.global_flat = flat0.clone()
+            self.stack = torch.zeros(self.C_max, self.P, dtype=torch.float32)
+            self.server_opt = A.ServerOptimizer(
+                getattr(args, "server_optimizer", "sgd"), lr=float(getattr(args, "server_lr", 1.0)),
+                momentum=float(getattr(args, "server_momentum", 0.0)), beta1=float(getattr(args, "server_beta1", 0.9)),
+                beta2=float(getattr(args, "server_beta2", 0.99)), eps=float(getattr(args, "server_eps", 1e-3))) \
+                if use_opt else None
+        self.grad_stack = torch.zeros_like(self.stack)
+        self.W = self.layout.stacked_views(self.stack)
+        self.G = self.layout.stacked_views(self.grad_stack)
+
+    def _build_executor(self):
+        args = self.args
+        self.batched = None
+        if self.custom_trainer is None and bool(getattr(args, "batched_clients", True)):
+            if self.cuda:
+                dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "fp16": torch.float16}[
+                    str(getattr(args, "compute_dtype", "bf16")).lower()]
+                backend = NativeBackend(dtype)
+            else:
+                backend = TorchBackend(torch.float32)
+            self.batched = make_batched(self.model, backend)
+        if self.batched is None:
+            self.seq_model = self.model.to(self.device)
+            self.seq_flat = torch.zeros(self.P, dtype=torch.float32, device=self.device)
+            bind_module_to_flat(self.seq_model, self.layout, self.seq_flat)
+            self.seq_trainer = self.custom_trainer or create_model_trainer(self.seq_model, args)
+        self.lr = float(getattr(args, "learning_rate", getattr(args, "lr", 0.03)))
+        self.momentum = float(getattr(args, "momentum", 0.0) or 0.0) if self.alg == "FedNova" or \
+            str(getattr(args, "client_optimizer", "sgd")).lower() == "sgd_momentum" else 0.0
+        self.wd = float(getattr(args, "wd", 0.0) or 0.0) if self.alg == "FedNova" else 0.0
+        self.mu = float(getattr(args, "fedprox_mu", 0.0) or getattr(args, "mu", 0.0) or 0.0) \
+            if self.alg in ("FedProx", "FedNova") else 0.0
+        if self.alg == "FedProx" and self.mu == 0.0:
+            self.mu = 0.1
+        self.mom_stack = torch.zeros_like(self.stack) if self.momentum else None
+        self.graph = None
+        self.use_graph = self.cuda and bool(getattr(args, "use_cuda_graphs", True)) and self.batched is not None
+        self._static = None
+        self.global_momentum = None   # FedNova gmf buffer (server side)
+
+    # ------------------------------------------------------------------ data staging
+    def _client_arrays(self, cid):
+        if self.fed is not None:
+            return self.fed.client_slice(cid)
+        batches = self.train_local[cid]
+        return torch.cat([b[0] for b in batches]), torch.cat([b[1] for b in batches])
+
+    def _stage_round_inputs(self, my_clients: List[int], round_idx: int):
+        """Build X [C, S, B, ...], Y [C, S, B] (-1 padded), steps [C] on the host (pinned), one H2D."""
+        args = self.args
+        bs = int(args.batch_size)
+        drop_last = self.fed is not None and self.fed.transform is not None and bs > 0
+        C = self.C_max
+        per = []
+        for pos, cid in enumerate(my_clients):
+            x, y = self._client_arrays(cid)
+            n = x.shape[0]
+            b = n if bs <= 0 else bs
+            if drop_last:
+                steps = n // b
+                if steps and bool(getattr(args, "shuffle_clients", True)):
+                    g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) * 1000003 + round_idx * 1009 + cid)
+                    perm = torch.randperm(n, generator=g)[:steps * b]
+                    x, y = x[perm], y[perm]
+                else:
+                    x, y = x[:steps * b], y[:steps * b]
+            else:
+                steps = (n + b - 1) // b
+            per.append((x, y, steps, b, n))
+        B = max([p[3] for p in per], default=max(bs, 1))
+        S = max([p[2] for p in per], default=0)
+        if not per or S == 0:
+            return None
+        xs0 = per[0][0]
+        X = torch.zeros((C, S, B) + tuple(xs0.shape[1:]), dtype=xs0.dtype)
+        Y = torch.full((C, S, B) + tuple(per[0][1].shape[1:]), -1, dtype=torch.int64)
+        steps_t = torch.zeros(C, dtype=torch.int64)
+        valid = torch.ones(C, S, dtype=torch.float32)
+        for pos, (x, y, steps, b, n) in enumerate(per):
+            steps_t[pos] = steps
+            for s in range(steps):
+                lo, hi = s * b, min((s + 1) * b, x.shape[0])
+                X[pos, s, :hi - lo] = x[lo:hi]
+                Y[pos, s, :hi - lo] = y[lo:hi]
+                valid[pos, s] = max(hi - lo, 1)
+        if self.cuda:
+            Xp, Yp = X.pin_memory(), Y.pin_memory()
+            Xd = Xp.to(self.device, non_blocking=True)
+            Yd = Yp.to(self.device, non_blocking=True)
+            self.h2d_bytes += Xp.numel() * Xp.element_size() + Yp.numel() * Yp.element_size()
+            self._keep_pinned = (Xp, Yp)
+        else:
+            Xd, Yd = X, Y
+        return Xd, Yd, steps_t, (1.0 / valid).to(self.device), S
+
+    # ------------------------------------------------------------------ local training
+    def _sgd(self, C, lr_vec, first_step):
+        n = self.P_train
+        anchor = self.global_flat if self.mu else None
+        if self.cuda:
+            from ... import ops
+            ops.sgd_step_stacked(self.stack[:C], self.grad_stack[:C], n, lr_vec, weight_decay=self.wd,
+                                 momentum=self.momentum, mom_buf=self.mom_stack, first_step=first_step, mu=self.mu,
+                                 anchor=anchor)
+        else:
+            w, g = self.stack[:C, :n], self.grad_stack[:C, :n]
+            d = g + self.wd * w if self.wd else g.clone()
+            if self.momentum:
+                buf = self.mom_stack[:C, :n]
+                if first_step:
+                    buf.copy_(d)
+                else:
+                    buf.mul_(self.momentum).add_(d)
+                d = buf.clone()
+            if self.mu:
+                d = d + self.mu * (w - anchor[:n])
+            w.sub_(lr_vec[:C, None] * d)
+
+    def _step_body(self, st):
+        loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
+        self._sgd(self.C_max, st["lr"], False)
+        st["loss"].copy_(loss)
+
+    def _train_batched(self, staged, n_local):
+        Xd, Yd, steps_t, inv_valid, S = staged
+        C = self.C_max
+        epochs = int(getattr(self.args, "epochs", 1))
+        dev = self.device
+        if self._static is None or self._static["x"].shape != Xd[:, 0].shape:
+            self._static = {"x": torch.empty_like(Xd[:, 0]), "y": torch.empty_like(Yd[:, 0]),
+                            "active": torch.zeros(C, dtype=torch.float32, device=dev),
+                            "lr": torch.zeros(C, dtype=torch.float32, device=dev),
+                            "scale": torch.zeros(C, dtype=torch.float32, device=dev),
+                            "loss": torch.zeros(C, dtype=torch.float32, device=dev)}
+            self.graph = None
+        st = self._static
+        steps_dev = steps_t.to(dev)
+        first = True
+        for _ in range(epochs):
+            for s in range(S):
+                act = (steps_dev > s).to(torch.float32)
+                st["x"].copy_(Xd[:, s]); st["y"].copy_(Yd[:, s])
+                st["active"].copy_(act); st["lr"].copy_(act * self.lr); st["scale"].copy_(inv_valid[:, s])
+                if self.momentum and first:
+                    loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
+                    self._sgd(C, st["lr"], True)
+                    st["loss"].copy_(loss)
+                elif self.use_graph:
+                    if self.graph is None:
+                        self._capture(st)
+                    self.graph.replay()
+                    _native.count_launch(self._graph_launches)   # kernels of ours inside the replayed graph
+                else:
+                    self._step_body(st)
+                first = False
+        return st["loss"]
+
+    def _capture(self, st):
+        # warm-up on a side stream (allocator + lazy kernel loading), then capture one step
+        backup = self.stack.clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._step_body(st)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.stack.copy_(backup)          # warm-up steps must not advance the models
+        self.graph = torch.cuda.CUDAGraph()
+        before = _native.LAUNCHES[0]
+        with torch.cuda.graph(self.graph):
+            self._step_body(st)
+        self._graph_launches = _native.LAUNCHES[0] - before
+        _native.LAUNCHES[0] = before
+        self.stack.copy_(backup)          # capture does not execute, but keep the invariant explicit
+
+    def _train_sequential(self, my_clients, round_idx):
+        """Per-client eager training on arena-bound parameters (custom trainers / unbatched families)."""
+        for pos, cid in enumerate(my_clients):
+            self.seq_flat.copy_(self.global_flat)
+            self.seq_trainer.set_id(cid)
+            self.seq_trainer.train(self.train_local[cid], self.device, self.args)
+            self.stack[pos].copy_(self.seq_flat)
+
+    # ------------------------------------------------------------------ one round
+    def train_one_round(self, round_idx: int):
+        args = self.args
+        N = int(args.client_num_in_total)
+        sampled = client_sampling(round_idx, N, self.K)
+        sizes = [int(self.local_num[c]) for c in sampled]
+        assign = schedule_clients(sizes, self.world)
+        my_pos = assign[self.rank]
+        my_clients = [sampled[p] for p in my_pos]
+        C_real = len(my_clients)
+        dev = self.device
+        t = self.timer
+        t.start("h2d")
+        staged = self._stage_round_inputs(my_clients, round_idx) if self.batched is not None and C_real else None
+        t.stop("h2d")
+        # every row starts from the global model (dummy rows too: they carry weight 0)
+        t.start("train")
+        if self.cuda:
+            from ... import ops
+            ops.broadcast_rows(self.global_flat, self.stack)
+        else:
+            self.stack.copy_(self.global_flat[None, :].expand_as(self.stack))
+        if self.batched is not None:
+            if staged is not None:
+                self._train_batched(staged, sizes)
+        else:
+            self._train_sequential(my_clients, round_idx)
+        t.stop("train")
+        # ---- aggregation
+        t.start("aggregate")
+        weights = torch.zeros(self.C_max, dtype=torch.float32)
+        for i, p in enumerate(my_pos):
+            weights[i] = sizes[p]
+        total = float(sum(sizes))
+        self._aggregate(weights.to(dev), total, my_pos, sizes, round_idx)
+        t.stop("aggregate")
+        self.round_idx = round_idx + 1
+
+    def _fednova_coefs(self, sizes, my_pos):
+        """Host-side FedNova scalars (fednova.py:114-167, client.py:50-65): lockstep local steps make
+        a_i a closed form of (steps, momentum, lr*mu)."""
+        args = self.args
+        bs = int(args.batch_size)
+        total = float(sum(sizes))
+        coefs, taus = [], []
+        for n in sizes:
+            steps = (n // bs if (self.fed is not None and self.fed.transform is not None) else math.ceil(n / max(bs, 1))) \
+                * int(getattr(args, "epochs", 1)) if bs > 0 else int(getattr(args, "epochs", 1))
+            a, cnt = 0.0, 0.0
+            etamu = self.lr * self.mu
+            for _ in range(max(steps, 0)):
+                if self.momentum:
+                    cnt = cnt * self.momentum + 1.0
+                    a += cnt
+                if etamu:
+                    a = a * (1.0 - etamu) + 1.0
+                if not self.momentum and not etamu:
+                    a += 1.0
+            ratio = n / total
+            tau = steps * ratio if self.mu != 0 else a * ratio
+            coefs.append(ratio / a if a else 0.0)
+            taus.append(tau)
+        tau_eff = sum(taus)
+        return [c * tau_eff for c in coefs]
+
+    def _aggregate(self, weights, total, my_pos, sizes, round_idx):
+        args = self.args
+        base = sum(len(a) for a in schedule_clients(sizes, self.world)[:self.rank])
+        if self.robust in ("median", "trimmed_mean", "krum"):
+            return self._aggregate_robust(weights, total, my_pos, sizes, round_idx)
+        if self.alg == "FedNova":
+            coefs = self._fednova_coefs(sizes, my_pos)
+            cw = torch.zeros(self.C_max, dtype=torch.float32)
+            for i, p in enumerate(my_pos):
+                cw[i] = coefs[p]
+            self_coef = 1.0 - float(sum(coefs))
+            gmf = float(getattr(args, "gmf", 0.0) or 0.0)
+            if self.cuda:
+                eng = self.engine
+                if gmf and eng.opt.name != "sgd":
+                    from ...parallel.round_engine import ServerOptConfig
+                    eng.opt = ServerOptConfig("sgd", lr=self.lr, momentum=gmf)
+                    eng.m = torch.zeros(self.P_train, dtype=torch.float32, device=self.device)
+                eng.aggregate(self.stack, cw.to(self.device), 1.0, base, round_idx, weights_buf=weights,
+                              inv_total_buf=1.0 / total, self_coef=self_coef,
+                              grad_scale=(1.0 / self.lr) if gmf else 1.0, use_opt=bool(gmf))
+            else:
+                part = (cw[:, None] * self.stack).sum(0)
+                part_b = (weights[:, None] * self.stack).sum(0) / total
+                if self.world > 1:
+                    dist.all_reduce(part); dist.all_reduce(part_b)
+                Pt = self.P_train
+                avg = part[:Pt] + self_coef * self.global_flat[:Pt]
+                if gmf:
+                    g = (self.global_flat[:Pt] - avg) / self.lr
+                    self.global_momentum = g if self.global_momentum is None else self.global_momentum * gmf + g
+                    avg = self.global_flat[:Pt] - self.lr * self.global_momentum
+                self.global_flat[:Pt] = avg
+                self.global_flat[Pt:] = part_b[Pt:]
+            return
+        if self.cuda:
+            self.engine.aggregate(self.stack, weights, 1.0 / total, base, round_idx)
+            return
+        # CPU oracle path (gloo)
+        stack = self.stack
+        if self.dp_clip > 0 or self.dp_sigma > 0:
+            Pt = self.P_train
+            diff = stack[:, :Pt] - self.global_flat[:Pt]
+            if self.dp_clip > 0:
+                diff = diff / torch.clamp(diff.norm(dim=1) / self.dp_clip, min=1.0)[:, None]
+            contrib = stack.clone()
+            contrib[:, :Pt] = self.global_flat[:Pt] + diff
+            if self.dp_sigma > 0:
+                g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) * 7919 + round_idx * 131 + self.rank)
+                contrib[:, :Pt] += self.dp_sigma * torch.randn(contrib[:, :Pt].shape, generator=g)
+            stack = contrib
+        part = (weights[:, None] * stack).sum(0) / total
+        if self.world > 1:
+            dist.all_reduce(part)
+        if self.server_opt is not None:
+            Pt = self.P_train
+            new = self.server_opt.step({"p": self.global_flat[:Pt]}, {"p": part[:Pt]}, ["p"])["p"]
+            self.global_flat[:Pt] = new
+            self.global_flat[Pt:] = part[Pt:]
+        else:
+            self.global_flat.copy_(part)
+
+    def _aggregate_robust(self, weights, total, my_pos, sizes, round_idx):
+        """Median / trimmed mean / Krum over all K client rows (they live on G GPUs)."""
+        args = self.args
+        K = len(sizes)
+        trim = int(math.floor(float(getattr(args, "trim_ratio", 0.1)) * K))
+        f = int(getattr(args, "krum_f", 0) or round(float(getattr(args, "byzantine_fraction", 0.0)) * K))
+        m = int(getattr(args, "krum_m", 1) or 1)
+        self._inject_byzantine(my_pos, K, round_idx)
+        if not self.cuda:
+            rows = self.stack[:len(my_pos)]
+            if self.world > 1:
+                gathered = [None] * self.world
+                dist.all_gather_object(gathered, (my_pos, rows))
+                allrows = torch.zeros(K, self.P)
+                for pos, r in gathered:
+                    for i, p in enumerate(pos):
+                        allrows[p] = r[i]
+            else:
+                allrows = torch.zeros(K, self.P)
+                for i, p in enumerate(my_pos):
+                    allrows[p] = rows[i]
+            if self.robust == "median":
+                self.global_flat.copy_(torch.median(allrows, dim=0).values)
+            elif self.robust == "trimmed_mean":
+                srt = torch.sort(allrows, dim=0).values
+                self.global_flat.copy_(srt[trim:K - trim].mean(0))
+            else:
+                scores = A.krum_scores(allrows[:, :self.P_train], f)
+                chosen = A.krum_select(scores, m)
+                w = torch.tensor([float(sizes[i]) for i in chosen])
+                self.global_flat.copy_((w[:, None] * allrows[chosen]).sum(0) / w.sum())
+            return
+        from ...parallel import robust_engine
+        robust_engine.aggregate(self, self.robust, K, trim, f, m, my_pos, sizes, round_idx)
+
+    def _inject_byzantine(self, my_pos, K, round_idx):
+        frac = float(getattr(self.args, "byzantine_fraction", 0.0) or 0.0)
+        n_bad = int(round(frac * K))
+        if not n_bad:
+            return
+        kind = str(getattr(self.args, "byzantine_attack", "sign_flip"))
+        Pt = self.P_train
+        for i, p in enumerate(my_pos):
+            if p < n_bad:   # the first n_bad sampled positions are malicious (deterministic, G-invariant)
+                row, g = self.stack[i, :Pt], self.global_flat[:Pt]
+                if kind == "sign_flip":
+                    row.copy_(g - (row - g))
+                elif kind == "scaled":
+                    row.copy_(g + 10.0 * (row - g))
+                elif kind == "gaussian":
+                    gen = torch.Generator(device=row.device).manual_seed(round_idx * 7919 + p)
+                    row.copy_(g + torch.randn(row.shape, generator=gen, device=row.device))
+                elif kind == "zero":
+                    row.zero_()
+
+    # ------------------------------------------------------------------ evaluation
+    @torch.no_grad()
+    def evaluate(self, round_idx: int):
+        """Global-model accuracy/loss over every client's train and test split (SP semantics,
+        fedavg_api.py:238-326).  All clients share the global model at this point, so the per-client
+        loop of the reference collapses into batched inference over the packed arrays."""
+        stats = {"round": round_idx}
+        if self.fed is None:
+            return stats
+        sd = self.layout.unflatten(self.global_flat)
+        model = self.model.to(self.device)
+        model.load_state_dict(sd)
+        model.eval()
+        cap = int(getattr(self.args, "eval_sample_cap", 0) or 0)
+        for split, (x, y) in (("train", (self.fed.x, self.fed.y)), ("test", (self.fed.x_test, self.fed.y_test))):
+            n = x.shape[0] if not cap else min(cap, x.shape[0])
+            lo = (n * self.rank) // self.world
+            hi = (n * (self.rank + 1)) // self.world
+            correct = torch.zeros((), device=self.device); loss = torch.zeros((), device=self.device)
+            bs = 2048
+            for i in range(lo, hi, bs):
+                xb, yb = x[i:min(i + bs, hi)], y[i:min(i + bs, hi)]
+                xb = self.fed._prep(xb).to(self.device, non_blocking=True)
+                yb = yb.to(self.device, non_blocking=True)
+                out = model(xb)
+                loss += torch.nn.functional.cross_entropy(out, yb, reduction="sum")
+                correct += (out.argmax(1) == yb).sum()
+            vec = torch.stack([correct, loss, torch.tensor(float(hi - lo), device=self.device)])
+            if self.world > 1:
+                dist.all_reduce(vec)
+            stats[f"{split}_acc"] = float(vec[0] / vec[2].clamp_min(1))
+            stats[f"{split}_loss"] = float(vec[1] / vec[2].clamp_min(1))
+        self.history.append(stats)
+        if self.metrics is not None:
+            self.metrics.log({"Train/Acc": stats["train_acc"], "Train/Loss": stats["train_loss"],
+                              "Test/Acc": stats["test_acc"], "Test/Loss": stats["test_loss"], "round": round_idx})
+        return stats
+
+    # ------------------------------------------------------------------ driver
+    def train(self):
+        args = self.args
+        start = 0
+        if bool(getattr(args, "resume", False)) and getattr(args, "checkpoint_dir", None):
+            start = self.resume(args.checkpoint_dir)
+        for round_idx in range(start, int(args.comm_round)):
+            self.train_one_round(round_idx)
+            freq = int(getattr(args, "frequency_of_the_test", 1) or 1)
+            if freq > 0 and (round_idx == int(args.comm_round) - 1 or round_idx % freq == 0):
+                self.evaluate(round_idx)
+            every = int(getattr(args, "checkpoint_every", 0) or 0)
+            if every and getattr(args, "checkpoint_dir", None) and (round_idx + 1) % every == 0 and self.rank == 0:
+                self.save(args.checkpoint_dir)
+        return self.global_state_dict()
+
+    def global_state_dict(self):
+        return self.layout.unflatten(self.global_flat.detach().cpu())
+
+    def save(self, cdir):
+        from ...utils.checkpoint import save_run_state
+        extra = {"engine": self.engine.state_dict()} if self.engine is not None else \
+            {"server_opt": self.server_opt.state_dict() if self.server_opt is not None else None}
+        save_run_state(cdir, self.round_idx, self.global_state_dict(), extra)
+
+    def resume(self, cdir) -> int:
+        from ...utils.checkpoint import load_run_state
+        st = load_run_state(cdir, restore_rng=False)
+        if st is None:
+            return 0
+        flat = self.layout.flatten(st["state_dict"])
+        if self.engine is not None:
+            self.engine.set_global(flat)
+            if st["extra"].get("engine"):
+                self.engine.load_state_dict(st["extra"]["engine"])
+        else:
+            self.global_flat.copy_(flat)
+            if self.server_opt is not None and st["extra"].get("server_opt"):
+                self.server_opt.load_state_dict(st["extra"]["server_opt"])
+        self.round_idx = int(st["round"])
+        return self.round_idx
