@@ -529,3 +529,74 @@ extern "C" int fb_peer_barrier(uint32_t* const* peer_flags, int32_t rank, int32_
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+
+// ---------------------------------------------------------------- allocation-free single-GPU round
+// Same kernel as fb_round_launch on one rank, but the scratch it needs for clipping (per-block
+// squared-norm partials and the intra-grid barrier counter) lives in a fixed device array that is
+// part of this library's image instead of being supplied by the caller.  See the declaration of
+// fb_round_single_noalloc in include/fedml_b200.h for who this is for and what the limits are.
+#define FB_NOALLOC_MAX_CLIENTS 64
+#define FB_NOALLOC_COUNTER_FLOATS 64  /* the barrier counter gets its own 256-byte line at the front */
+#define FB_NOALLOC_SCRATCH_FLOATS (FB_NOALLOC_COUNTER_FLOATS + FB_ROUND_MAX_BLOCKS * FB_NOALLOC_MAX_CLIENTS)
+
+static __device__ __align__(256) float g_noalloc_scratch[FB_NOALLOC_SCRATCH_FLOATS];  // 256.25 KiB on every GPU that loads the library
+
+// Device address of g_noalloc_scratch per device.  In host code the symbol name is only a handle for
+// the runtime; the address a kernel can dereference has to be asked for, with that device current.
+static float* g_noalloc_ptr[64] = {nullptr};
+
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  FB_CHECK_CUDA(cudaGetDevice(&dev));
+  FB_REQUIRE(dev >= 0 && dev < 64, "fb_round_single_noalloc: device ordinal %d not supported", dev);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    FB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    FB_REQUIRE(p != nullptr, "fb_round_single_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return FB_OK;
+}
+
+extern "C" int fb_round_single_noalloc_max_clients(void) { return FB_NOALLOC_MAX_CLIENTS; }
+
+extern "C" int fb_round_single_noalloc(const float* clients, int64_t ld, int32_t C, const float* weights,
+                                       float inv_total, float clip_bound, float* global_model, int64_t P,
+                                       int64_t P_train, float* clip_scale_out, fb_stream_t stream) {
+  if (C > FB_NOALLOC_MAX_CLIENTS) {
+    fb_set_error("fb_round_single_noalloc: %d clients exceed the built-in scratch limit of %d; use fb_round_launch "
+                 "with caller-provided scratch for larger rounds", C, FB_NOALLOC_MAX_CLIENTS);
+    return FB_ERR_LIMIT;
+  }
+  FB_REQUIRE(C >= 1, "fb_round_single_noalloc: need at least one client");
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  FbRoundParams p;
+  memset(&p, 0, sizeof(p));
+  p.clients = clients; p.ld = ld; p.C = C; p.weights = weights;
+  p.P = P; p.P_train = P_train;
+  p.inv_total = inv_total; p.inv_total_buf = inv_total;
+  p.global_model = global_model;
+  p.partial = global_model;   // never touched when G == 1; only has to be non-null for the argument check
+  p.rank = 0; p.G = 1; p.epoch = 1;
+  p.clip_bound = clip_bound;
+  p.opt = FB_OPT_NONE; p.grad_scale = 1.f; p.bias_corr1 = 1.f; p.bias_corr2 = 1.f;
+  p.grid_bar = reinterpret_cast<uint32_t*>(scratch);
+  p.sqnorm_part = scratch + FB_NOALLOC_COUNTER_FLOATS;
+  p.clip_scale_out = clip_scale_out;
+  rc = round_check(&p);
+  if (rc) return rc;
+  const int grid = fb_round_grid(P, 1, 1);
+  FB_REQUIRE(grid <= FB_ROUND_MAX_BLOCKS, "fb_round_single_noalloc: grid exceeds the scratch layout");
+  p.grid_bar_target = (uint32_t)grid;
+  // The array remembers the previous call: the barrier counter has to start from zero every time.  The
+  // per-block partials are fully rewritten by the kernel before it reads them, so they need no clearing.
+  FB_CHECK_CUDA(cudaMemsetAsync(scratch, 0, FB_NOALLOC_COUNTER_FLOATS * sizeof(float), (cudaStream_t)stream));
+  const size_t smem = (64 + (size_t)C) * sizeof(float);
+  void* args[] = {&p};
+  FB_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)round_kernel, dim3(grid), dim3(ROUND_THREADS), args, smem,
+                                            (cudaStream_t)stream));
+  return FB_OK;
+}

@@ -101,6 +101,37 @@ int fb_round_launch(const FbRoundParams* p, fb_stream_t stream);
  * `params_dev` is a device array of G FbRoundParams whose peer_* arrays point at local buffers. */
 int fb_round_launch_emulated(const FbRoundParams* params_dev, int32_t G, int64_t P, fb_stream_t stream);
 
+/* Allocation-free single-GPU round.  No counterpart in the reference (which has no native code and
+ * aggregates on the CPU); it is fb_round_launch for one rank with the clipping scratch built in.
+ *
+ * Who needs it: hosts that may not allocate device memory when a round is aggregated.  Examples are an
+ * embedding application that handed all free HBM to its own pool at start-up (a later cudaMalloc fails or
+ * fragments that pool), a loop that cannot accept the device-wide stall cudaMalloc/cudaFree imply, and
+ * plug-in code whose host forbids allocator calls after initialisation.  Such callers cannot provide the
+ * `sqnorm_part` / `grid_bar` scratch that fb_round_launch asks for, and this entry point does not ask:
+ * the scratch is a fixed 256.25 KiB array inside the library image, present on every GPU that loads the
+ * library until the process exits.  Inputs and outputs still belong to the caller.  Nothing here calls
+ * cudaMalloc, cudaFree or any allocating library routine.
+ *
+ *   global_model[j] <- sum_c weights[c] * inv_total * (g + s_c * (clients[c][j] - g))   for j <  P_train
+ *   global_model[j] <- sum_c weights[c] * inv_total * clients[c][j]                     for j >= P_train
+ *   with g = global_model[j] on entry and s_c = 1 / max(1, ||clients[c][:P_train] - g||_2 / clip_bound)
+ *   (clip_bound <= 0: s_c = 1).  clip_scale_out (optional, [C]) receives s_c.
+ *
+ * Limits and rules:
+ *  - at most fb_round_single_noalloc_max_clients() (= 64) clients per call; more is refused with
+ *    FB_ERR_LIMIT and a message naming fb_round_launch as the way out.  P, P_train, ld as for fb_round_launch.
+ *  - The first call on each device looks up the device address of the built-in array (with that device
+ *    current) and remembers it; make that first call outside any stream capture.
+ *  - All calls on a device share the one array, and it keeps what the previous call left: the entry point
+ *    clears the barrier counter itself on `stream` before the launch.  Two calls whose kernels can overlap
+ *    on the GPU (different streams, no dependency between them) race on it — serialise them.
+ */
+int fb_round_single_noalloc_max_clients(void);
+int fb_round_single_noalloc(const float* clients, int64_t ld, int32_t C, const float* weights, float inv_total,
+                            float clip_bound, float* global_model, int64_t P, int64_t P_train,
+                            float* clip_scale_out, fb_stream_t stream);
+
 /* K4 stand-alone: out[j] = beta*out[j] + scale * sum_c w[c] * X[c][j]  (local streaming accumulate). */
 int fb_weighted_accumulate(const float* clients, int64_t ld, int32_t C, const float* weights, float scale,
                            float beta, float* out, int64_t P, fb_stream_t stream);
