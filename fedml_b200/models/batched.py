@@ -143,6 +143,10 @@ class NativeBackend(TorchBackend):
     def _fb(self, what):
         self.fallbacks[what] = self.fallbacks.get(what, 0) + 1
 
+    @staticmethod
+    def _bn_ok(ch):
+        return 8 <= ch <= 2048 and 2048 % ch == 0
+
     def gemm_nt(self, a, b, out_dtype=None, relu=False):
         if self.use_tc_gemm and self.ops.grouped_gemm_supported(a, b):
             return self.ops.grouped_gemm(a, b, out_dtype or a.dtype, relu=relu)
@@ -159,25 +163,25 @@ class NativeBackend(TorchBackend):
         return super().gemm_tn(a, b, out_dtype)
 
     def im2col3x3(self, x, stride):
-        if hasattr(self.ops, "im2col3x3") and x.dtype == torch.bfloat16:
+        if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
             return self.ops.im2col3x3(x, stride)
         self._fb("im2col")
         return super().im2col3x3(x, stride)
 
     def col2im3x3(self, dcols, B, H, W, ch, stride):
-        if hasattr(self.ops, "col2im3x3") and dcols.dtype == torch.bfloat16:
+        if dcols.dtype == torch.bfloat16 and ch % 8 == 0:
             return self.ops.col2im3x3(dcols, B, H, W, ch, stride)
         self._fb("col2im")
         return super().col2im3x3(dcols, B, H, W, ch, stride)
 
     def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
-        if hasattr(self.ops, "bn_fwd_stacked") and x.dtype == torch.bfloat16:
+        if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
             return self.ops.bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
         self._fb("bn_fwd")
         return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
 
     def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres):
-        if hasattr(self.ops, "bn_bwd_stacked") and x.dtype == torch.bfloat16:
+        if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
             return self.ops.bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres)
         self._fb("bn_bwd")
         return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres)

@@ -261,3 +261,77 @@ def eval_counts(logits: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor
                                i32(int(pre_sigmoid)), vp(ptr(counts)), vp(ptr(loss_sum)),
                                vp(stream_ptr(logits.device))), "eval_counts")
     count_launch()
+
+
+# --------------------------------------------------------------------------- K10 helpers (client-stacked conv nets)
+_bn_scratch = {}
+
+
+def _scratch_for(device, n_floats):
+    key = str(device)
+    buf = _bn_scratch.get(key)
+    if buf is None or buf.numel() < n_floats:
+        buf = torch.empty(max(n_floats, 1 << 16), dtype=torch.float32, device=device)
+        _bn_scratch[key] = buf
+    return buf
+
+
+def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
+    """x [C,B,H,W,ch] bf16 contiguous -> (y, save_mean [C,ch], save_rstd [C,ch]); running stats updated in place."""
+    Cn, ch = x.shape[0], x.shape[-1]
+    M = x.numel() // (Cn * ch)
+    x = x.contiguous()
+    y = torch.empty_like(x)
+    mean = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    rstd = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
+    check(lib().fb_bn_fwd_stacked(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)), i32(Cn),
+                                  i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(rm)),
+                                  vp(ptr(rv)), i64(rm.stride(0)), vp(ptr(active)), f32(momentum), f32(eps),
+                                  i32(int(relu)), i32(int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
+                                  vp(stream_ptr(x.device))), "bn_fwd_stacked")
+    count_launch(2 if training else 1)
+    if training:
+        nbt.add_(active.view(nbt.shape) if active is not None else 1.0)
+    return y, mean, rstd
+
+
+def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres):
+    Cn, ch = x.shape[0], x.shape[-1]
+    M = x.numel() // (Cn * ch)
+    dy = dy.contiguous()
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    dgamma = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    dbeta = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
+    check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
+                                  i32(ch), vp(ptr(gamma)), i64(gamma.stride(0)), vp(ptr(mean)), vp(ptr(rstd)),
+                                  i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ch), vp(ptr(scratch)),
+                                  vp(stream_ptr(x.device))), "bn_bwd_stacked")
+    count_launch(2)
+    return dx, dres, dgamma, dbeta
+
+
+def im2col3x3(x, stride):
+    """x [C,B,H,W,ch] bf16 (ch % 8 == 0) -> cols [C, B*Ho*Wo, 9*ch]"""
+    Cn, B, H, W, ch = x.shape
+    if ch % 8:
+        raise NativeError("im2col3x3: ch must be a multiple of 8")
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    x = x.contiguous()
+    cols = torch.empty((Cn, B * Ho * Wo, 9 * ch), dtype=x.dtype, device=x.device)
+    check(lib().fb_im2col3x3_nhwc_bf16(vp(ptr(x)), vp(ptr(cols)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
+                                       vp(stream_ptr(x.device))), "im2col3x3")
+    count_launch()
+    return cols
+
+
+def col2im3x3(dcols, B, H, W, ch, stride):
+    Cn = dcols.shape[0]
+    dcols = dcols.contiguous()
+    dx = torch.empty((Cn, B, H, W, ch), dtype=dcols.dtype, device=dcols.device)
+    check(lib().fb_col2im3x3_nhwc_bf16(vp(ptr(dcols)), vp(ptr(dx)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
+                                       vp(stream_ptr(dcols.device))), "col2im3x3")
+    count_launch()
+    return dx

@@ -252,16 +252,20 @@ int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, int32_t H, 
 int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch,
                            int32_t stride, fb_stream_t stream);
 /* y = relu?(gamma*(x-mean)*rstd + beta (+res)); statistics per (client, channel) over M rows.
- * x,y,res: bf16 [C][M][ch]; gamma/beta/running_*: fp32 [C][ch] rows with stride ld_p; save_mean/rstd fp32 [C][ch]. */
+ * x,y,res: bf16 [C][M][ch] (ch a power of two in [8, 2048]); gamma/beta: fp32 rows with stride ld_p;
+ * running_mean/var: fp32 rows with stride ld_r, updated when training (scaled by active[c], NULL = all active);
+ * save_mean/save_rstd: fp32 [C][ch]; scratch: fb_bn_scratch_floats(C, M, ch) floats (training only).
+ * Replaces nn.BatchNorm2d + ReLU + residual add of every reference block (model/cv/resnet.py:116-136). */
+int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch);
 int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch, const float* gamma,
                       const float* beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                       const float* active, float momentum, float eps, int32_t relu, int32_t training,
-                      float* save_mean, float* save_rstd, fb_stream_t stream);
-/* dx (and dres = masked dy) from dy; dgamma/dbeta fp32 [C][ch] with stride ld_g. y is the forward output
- * (needed for the ReLU mask). */
+                      float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream);
+/* dx (and dres = ReLU-masked dy, optional) from dy; dgamma/dbeta fp32 rows with stride ld_g. y is the forward
+ * output (needed for the ReLU mask). */
 int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C, int64_t M,
                       int32_t ch, const float* gamma, int64_t ld_p, const float* save_mean, const float* save_rstd,
-                      int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, fb_stream_t stream);
+                      int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, float* scratch, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K13  Cheetah data-parallel gradient all-reduce fused with the SGD(+momentum) step

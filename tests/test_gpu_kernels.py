@@ -299,3 +299,59 @@ def test_softmax_xent_and_eval(ncls, pre_sigmoid):
     assert torch.equal(counts[2:2 + ncls].long(), tp)
     assert torch.equal(counts[2 + ncls:2 + 2 * ncls].long(), fp)
     assert torch.equal(counts[2 + 2 * ncls:].long(), fn)
+
+
+@pytest.mark.parametrize("ch,M,relu,with_res", [(16, 640, True, False), (64, 10240, True, True), (256, 333, False, False),
+                                                (512, 64, True, True)])
+def test_bn_stacked_fwd_bwd_vs_torch_backend(ch, M, relu, with_res):
+    from fedml_b200 import ops
+    from fedml_b200.models.batched import TorchBackend
+    C, P = 5, 4096
+    torch.manual_seed(ch + M)
+    B, H, W = 1, 1, M
+    x = (torch.randn(C, B, H, W, ch, device=DEV) * 2 + 0.5).to(torch.bfloat16)
+    res = torch.randn(C, B, H, W, ch, device=DEV).to(torch.bfloat16) if with_res else None
+    arena = torch.randn(C, P, device=DEV)
+    gamma, beta = arena[:, :ch], arena[:, ch:2 * ch]
+    rm0, rv0 = torch.randn(C, ch, device=DEV), torch.rand(C, ch, device=DEV) + 0.5
+    active = torch.tensor([1.0, 0.0, 1.0, 1.0, 0.0], device=DEV)
+    be = TorchBackend(torch.bfloat16)
+    rm_a, rv_a, nbt_a = rm0.clone(), rv0.clone(), torch.zeros(C, device=DEV)
+    rm_b, rv_b, nbt_b = rm0.clone(), rv0.clone(), torch.zeros(C, device=DEV)
+    y_ref, mean_ref, rstd_ref = be.bn_fwd(x, res, gamma, beta, rm_a, rv_a, nbt_a, active, 0.1, 1e-5, relu, True)
+    y, mean, rstd = ops.bn_fwd_stacked(x, res, gamma, beta, rm_b, rv_b, nbt_b, active, 0.1, 1e-5, relu, True)
+    torch.testing.assert_close(mean, mean_ref, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(rstd, rstd_ref, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(y.float(), y_ref.float(), rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(rm_b, rm_a, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(rv_b, rv_a, rtol=1e-3, atol=1e-4)
+    assert torch.equal(nbt_b, active)
+    dy = torch.randn_like(x)
+    dx_ref, dres_ref, dg_ref, db_ref = be.bn_bwd(dy, x, y, gamma, mean, rstd, relu, with_res)
+    dx, dres, dg, db = ops.bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, with_res)
+    torch.testing.assert_close(db, db_ref, rtol=1e-3, atol=1e-2)
+    torch.testing.assert_close(dg, dg_ref, rtol=1e-3, atol=2e-2)
+    torch.testing.assert_close(dx.float(), dx_ref.float(), rtol=3e-2, atol=3e-2)
+    if with_res:
+        torch.testing.assert_close(dres.float(), dres_ref.float(), rtol=1e-2, atol=1e-2)
+    # eval mode uses the running statistics
+    y_e_ref, _, _ = be.bn_fwd(x, res, gamma, beta, rm_a, rv_a, nbt_a, active, 0.1, 1e-5, relu, False)
+    y_e, _, _ = ops.bn_fwd_stacked(x, res, gamma, beta, rm_b, rv_b, nbt_b, active, 0.1, 1e-5, relu, False)
+    torch.testing.assert_close(y_e.float(), y_e_ref.float(), rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("H,ch,stride", [(32, 16, 1), (16, 32, 2), (8, 64, 1), (7, 8, 2)])
+def test_im2col_col2im_vs_torch_backend(H, ch, stride):
+    from fedml_b200 import ops
+    from fedml_b200.models.batched import TorchBackend
+    C, B = 3, 2
+    torch.manual_seed(H)
+    x = torch.randn(C, B, H, H, ch, device=DEV).to(torch.bfloat16)
+    be = TorchBackend(torch.bfloat16)
+    cols_ref = be.im2col3x3(x, stride)
+    cols = ops.im2col3x3(x, stride)
+    assert torch.equal(cols, cols_ref)
+    d = torch.randn_like(cols)
+    dx_ref = be.col2im3x3(d.float(), B, H, H, ch, stride)
+    dx = ops.col2im3x3(d, B, H, H, ch, stride)
+    torch.testing.assert_close(dx.float(), dx_ref, rtol=1e-2, atol=2e-2)
