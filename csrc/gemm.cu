@@ -1,0 +1,397 @@
+// K9: grouped GEMM on 5th-generation tensor cores (tcgen05.mma), accumulators in TMEM, operands staged by
+// TMA with 128-byte swizzle.  See include/fedml_b200.h.
+//
+//   for every group g:  D_g[M][N] = op(A_g) * op(B_g)     bf16 operands, fp32 accumulate, bf16/fp32 output
+//
+// Two operand layouts share one kernel template:
+//   NT  (MN_MAJOR = false): A_g is [M][K], B_g is [N][K], K contiguous            (forward / dgrad / Gram)
+//   TN  (MN_MAJOR = true ): A_g is [K][M], B_g is [K][N], M resp. N contiguous    (weight gradients)
+//
+// Persistent, warp-specialised CTA of 192 threads (one per SM):
+//   warp 0     TMA producer   (one elected lane): global -> smem ring of STAGES k-blocks (BK = 64)
+//   warp 1     MMA issuer     (one elected lane): tcgen05.mma 128 x BN x 16 from smem descriptors into one of
+//                             two TMEM accumulator buffers; tcgen05.commit releases smem slots / publishes tiles
+//   warps 2-5  epilogue       : tcgen05.ld (32 lanes x 16 columns per instruction) -> registers -> bias / ReLU ->
+//                             16-byte global stores, overlapped with the main loop of the next tile
+// Tiles are (group, m-tile, n-tile) triples walked with a grid-stride; partial tiles rely on TMA zero fill for
+// loads and on predication for stores, so any M, N and any K that is a multiple of 8 work.
+#include "common.cuh"
+#include "../include/fedml_b200.h"
+#include <cuda.h>
+
+#define GEMM_BM 128
+#define GEMM_BK 64
+#define GEMM_STAGES 4
+#define GEMM_THREADS 192
+#define GEMM_A_BYTES (GEMM_BM * 128)
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, void* smem_dst, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], kind::f16 (bf16 inputs, fp32 accumulate)
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version field = 1
+//   K-major : rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused
+//   MN-major: 64-element (128 B) MN chunks `lbo_bytes` apart, 8-row K groups 1024 B apart (SBO)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128, N = bn; majors: 0 = K, 1 = MN
+__device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn) {
+  uint32_t d = 0;
+  d |= 1u << 4;                       // c_format = F32
+  d |= 1u << 7;                       // a_format = BF16
+  d |= 1u << 10;                      // b_format = BF16
+  d |= (uint32_t)(a_mn & 1) << 15;
+  d |= (uint32_t)(b_mn & 1) << 16;
+  d |= (uint32_t)(bn >> 3) << 17;     // N / 8
+  d |= (uint32_t)(GEMM_BM >> 4) << 24;  // M / 16
+  return d;
+}
+
+struct GemmArgs {
+  void* d;
+  const float* bias;
+  int64_t d_gs, bias_gs;
+  int G, M, N, K;
+  int ldd, d_fp32, relu;
+  int BN;          // n-tile width (multiple of 16, <= 256)
+  int BNpad;       // smem rows/chunks reserved for B (BN, rounded to 64 for MN-major)
+  int m_tiles, n_tiles, k_blocks;
+  int tmem_cols;
+};
+
+template <bool MN_MAJOR>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128B swizzle atoms
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const uint32_t b_bytes = (uint32_t)a.BNpad * 128u;
+  const uint32_t stage_bytes = GEMM_A_BYTES + b_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)GEMM_STAGES * stage_bytes);
+  uint64_t* empty_bar = full_bar + GEMM_STAGES;
+  uint64_t* tmem_full = empty_bar + GEMM_STAGES;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = a.G * a.m_tiles * a.n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < GEMM_STAGES; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tmem_full + i, 1);
+      mbar_init(tmem_empty + i, 4);   // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)a.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
+        for (int kb = 0; kb < a.k_blocks; ++kb) {
+          mbar_wait(empty_bar + stage, phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * stage_bytes;
+          uint8_t* sb = sa + GEMM_A_BYTES;
+          mbar_expect_tx(full_bar + stage, stage_bytes);
+          if (!MN_MAJOR) {
+            tma_load_3d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g);
+            tma_load_3d(&tmB, sb, full_bar + stage, kb * GEMM_BK, nt * a.BN, g);
+          } else {
+            for (int i = 0; i < GEMM_BM / 64; ++i)
+              tma_load_3d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g);
+            for (int i = 0; i < a.BNpad / 64; ++i)
+              tma_load_3d(&tmB, sb + (size_t)i * GEMM_BK * 128, full_bar + stage, nt * a.BN + i * 64, kb * GEMM_BK, g);
+          }
+          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(a.BN, MN_MAJOR, MN_MAJOR);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * a.BN);
+        for (int kb = 0; kb < a.k_blocks; ++kb) {
+          mbar_wait(full_bar + stage, phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t sb = sa + GEMM_A_BYTES;
+          const int k_rem = a.K - kb * GEMM_BK;
+          const int k_steps = k_rem >= GEMM_BK ? GEMM_BK / 16 : (k_rem + 15) / 16;
+          for (int k = 0; k < k_steps; ++k) {
+            uint64_t ad, bd;
+            if (!MN_MAJOR) {
+              ad = make_smem_desc(sa + k * 32, 16, 1024);
+              bd = make_smem_desc(sb + k * 32, 16, 1024);
+            } else {
+              ad = make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024);
+              bd = make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024);
+            }
+            umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + stage);   // smem slot reusable once these MMAs have read it
+          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tmem_full + acc);       // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================================== epilogue (4 warps; warp % 4 selects the TMEM lane quarter)
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
+      mbar_wait(tmem_full + acc, acc_phase);
+      tc_fence_after();
+      const int row = mt * GEMM_BM + q * 32 + lane;
+      const bool row_ok = row < a.M;
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * a.BN) + ((uint32_t)(q * 32) << 16);
+      const float* bias = a.bias ? a.bias + (size_t)g * a.bias_gs : nullptr;
+      for (int c0 = 0; c0 < a.BN; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld16(taddr + (uint32_t)c0, r);
+        tmem_ld_wait();
+        const int col0 = nt * a.BN + c0;
+        if (!row_ok || col0 >= a.N) continue;
+        float f[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
+        if (bias) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (col0 + i < a.N) f[i] += __ldg(bias + col0 + i);
+        }
+        if (a.relu) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+        }
+        const bool full = col0 + 16 <= a.N;
+        if (a.d_fp32) {
+          float* dst = reinterpret_cast<float*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
+          if (full && (a.ldd & 3) == 0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+          } else {
+            for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = f[i];
+          }
+        } else {
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
+          if (full && (a.ldd & 7) == 0) {
+            uint4 o0, o1;
+            __nv_bfloat162* h0 = reinterpret_cast<__nv_bfloat162*>(&o0);
+            __nv_bfloat162* h1 = reinterpret_cast<__nv_bfloat162*>(&o1);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              h0[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+              h1[i] = __floats2bfloat162_rn(f[8 + 2 * i], f[8 + 2 * i + 1]);
+            }
+            *reinterpret_cast<uint4*>(dst) = o0;
+            *reinterpret_cast<uint4*>(dst + 8) = o1;
+          } else {
+            for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = __float2bfloat16_rn(f[i]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty + acc);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+  }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  }
+  return fn;
+}
+
+// 3-D bf16 tensor map: dims (inner, rows, groups), box (64, box_rows, 1), 128B swizzle, zero OOB fill
+static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t groups, uint64_t row_stride_elems,
+                    uint64_t group_stride_elems, uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[3] = {inner, rows, groups};
+  cuuint64_t strides[2] = {row_stride_elems * 2, (groups > 1 ? group_stride_elems : row_stride_elems * rows) * 2};
+  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  FB_REQUIRE((strides[0] % 16) == 0 && (strides[1] % 16) == 0 && ((uintptr_t)base % 16) == 0,
+             "grouped GEMM operands need 16-byte aligned base pointers and strides");
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code %d", (int)r);
+  return FB_OK;
+}
+
+static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream) {
+  FB_REQUIRE(p && p->a && p->b && p->d, "fb_grouped_gemm: null operand");
+  FB_REQUIRE(p->G >= 1 && p->M >= 1 && p->N >= 1 && p->K >= 1, "fb_grouped_gemm: empty problem");
+  FB_REQUIRE(p->accumulate == 0, "fb_grouped_gemm: accumulate is not implemented");
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.d = p->d; a.bias = p->bias; a.d_gs = p->d_gs; a.bias_gs = p->bias_gs;
+  a.G = p->G; a.M = p->M; a.N = p->N; a.K = p->K; a.ldd = p->ldd; a.d_fp32 = p->d_fp32; a.relu = p->relu;
+  int bn = (p->N + 15) / 16 * 16;
+  if (bn > 256) {
+    // split N evenly into tiles of at most 256 columns (multiple of 16)
+    int nt = (p->N + 255) / 256;
+    bn = ((p->N + nt - 1) / nt + 15) / 16 * 16;
+  }
+  a.BN = bn;
+  a.BNpad = mn_major ? (bn + 63) / 64 * 64 : bn;
+  a.n_tiles = (p->N + bn - 1) / bn;
+  a.m_tiles = (p->M + GEMM_BM - 1) / GEMM_BM;
+  a.k_blocks = (p->K + GEMM_BK - 1) / GEMM_BK;
+  int cols = 32;
+  while (cols < 2 * bn) cols <<= 1;
+  a.tmem_cols = cols;
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!mn_major) {
+    FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm: lda/ldb must be multiples of 8 elements");
+    rc = make_map(&tmA, p->a, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->G, (uint64_t)p->lda, (uint64_t)p->a_gs, GEMM_BM);
+    if (rc) return rc;
+    rc = make_map(&tmB, p->b, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->G, (uint64_t)p->ldb, (uint64_t)p->b_gs,
+                  (uint32_t)a.BN);
+    if (rc) return rc;
+  } else {
+    FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm_tn: lda/ldb must be multiples of 8 elements");
+    rc = make_map(&tmA, p->a, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->G, (uint64_t)p->lda, (uint64_t)p->a_gs, GEMM_BK);
+    if (rc) return rc;
+    rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->G, (uint64_t)p->ldb, (uint64_t)p->b_gs, GEMM_BK);
+    if (rc) return rc;
+  }
+  const size_t smem = (size_t)GEMM_STAGES * (GEMM_A_BYTES + (size_t)a.BNpad * 128) + 1024 /*align slack*/ + 256 /*barriers*/;
+  const int total = a.G * a.m_tiles * a.n_tiles;
+  int grid = fb_num_sms();
+  if (grid > total) grid = total;
+  if (mn_major) {
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grouped_gemm_kernel<true><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, a);
+  } else {
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grouped_gemm_kernel<false><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, a);
+  }
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, false, stream); }
+extern "C" int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, true, stream); }

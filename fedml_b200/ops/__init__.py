@@ -335,3 +335,111 @@ def col2im3x3(dcols, B, H, W, ch, stride):
                                        vp(stream_ptr(dcols.device))), "col2im3x3")
     count_launch()
     return dx
+
+
+# --------------------------------------------------------------------------- K9 grouped GEMM (tcgen05 / TMEM / TMA)
+from .native import FbGroupedGemm  # noqa: E402
+
+
+def _gemm_operand_ok(t):
+    return (t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 3 and t.stride(2) == 1 and t.stride(1) % 8 == 0
+            and (t.shape[0] == 1 or t.stride(0) % 8 == 0) and t.data_ptr() % 16 == 0)
+
+
+def grouped_gemm_supported(a, b) -> bool:
+    """NT form: a [G,M,K], b [G,N,K] bf16, K-contiguous, 16-byte aligned rows."""
+    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.shape[2] == b.shape[2] and a.shape[2] % 8 == 0 \
+        and a.shape[0] == b.shape[0]
+
+
+def grouped_gemm_tn_supported(a, b) -> bool:
+    """TN form: a [G,K,M], b [G,K,N] bf16, M/N-contiguous with M % 8 == 0 == N % 8."""
+    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.shape[1] == b.shape[1] and a.shape[0] == b.shape[0] \
+        and a.shape[2] % 8 == 0 and b.shape[2] % 8 == 0
+
+
+def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name):
+    d = torch.empty((G, M, N), dtype=out_dtype, device=a.device)
+    p = FbGroupedGemm()
+    p.a, p.b, p.d = a.data_ptr(), b.data_ptr(), d.data_ptr()
+    p.bias = bias.data_ptr() if bias is not None else None
+    p.a_gs, p.b_gs, p.d_gs = a.stride(0), b.stride(0), M * N
+    p.bias_gs = bias.stride(0) if bias is not None else 0
+    p.G, p.M, p.N, p.K = G, M, N, K
+    p.lda, p.ldb, p.ldd = a.stride(1), b.stride(1), N
+    p.d_fp32, p.relu, p.accumulate = int(out_dtype == torch.float32), int(relu), 0
+    check(fn(C.byref(p), vp(stream_ptr(a.device))), name)
+    count_launch()
+    return d
+
+
+def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
+    """d[g] = a[g] @ b[g]^T   (a [G,M,K], b [G,N,K]) on the tcgen05 tensor cores."""
+    if not grouped_gemm_supported(a, b):
+        raise NativeError("grouped_gemm: unsupported operand layout")
+    G, M, K = a.shape
+    return _launch_gemm(lib().fb_grouped_gemm_bf16, a, b, G, M, b.shape[1], K, out_dtype, relu, bias, "grouped_gemm")
+
+
+def grouped_gemm_tn(a, b, out_dtype=torch.float32):
+    """d[g] = a[g]^T @ b[g]   (a [G,K,M], b [G,K,N]): weight gradients without transposing activations."""
+    if not grouped_gemm_tn_supported(a, b):
+        raise NativeError("grouped_gemm_tn: unsupported operand layout")
+    G, K, M = a.shape
+    return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, b.shape[2], K, out_dtype, False, None,
+                        "grouped_gemm_tn")
+
+
+def gram_bf16(hi: torch.Tensor, lo: Optional[torch.Tensor] = None, split: int = 0) -> torch.Tensor:
+    """K x K Gram matrix of the rows of ``hi (+ lo)`` [K, n] bf16 with fp32 accumulation.  Rows must be padded
+    with zeros to a multiple of 64 columns (``krum_pack`` does).  The long reduction dimension is cut into
+    ``split`` slices that run as groups of the grouped GEMM (split-K across CTAs); the fp32 partials are summed
+    by the streaming accumulate kernel.  With ``lo`` the product is hi*hi^T + hi*lo^T + lo*hi^T (bf16 hi/lo
+    split of fp32 inputs; the lo*lo^T term is below fp32 round-off)."""
+    K, n = hi.shape
+    ld = hi.stride(0)
+    if n % 64 or ld % 8:
+        raise NativeError("gram_bf16: rows must be zero-padded to a multiple of 64 columns")
+    if split <= 0:
+        tiles = ((K + 127) // 128) * ((K + 255) // 256)
+        split = max(1, min(n // 2048, (2 * 148 + tiles - 1) // tiles))
+    chunk = ((n + split - 1) // split + 63) // 64 * 64
+    split = (n + chunk - 1) // chunk
+    tail = n - (split - 1) * chunk
+    dev = hi.device
+
+    def run(x, y):
+        d = torch.empty((split, K, K), dtype=torch.float32, device=dev)
+        p = FbGroupedGemm()
+        p.a, p.b, p.d = x.data_ptr(), y.data_ptr(), d.data_ptr()
+        p.a_gs = p.b_gs = chunk
+        p.d_gs = K * K
+        p.G, p.M, p.N, p.K = split, K, K, chunk
+        p.lda = p.ldb = ld
+        p.ldd, p.d_fp32 = K, 1
+        if tail != chunk:                      # shorter last slice: its own launch with a smaller K
+            if split > 1:
+                p.G = split - 1
+                check(lib().fb_grouped_gemm_bf16(C.byref(p), vp(stream_ptr(dev))), "gram_bf16")
+                count_launch()
+            q = FbGroupedGemm.from_buffer_copy(p)
+            q.a, q.b = x.data_ptr() + (split - 1) * chunk * 2, y.data_ptr() + (split - 1) * chunk * 2
+            q.d = d.data_ptr() + (split - 1) * K * K * 4
+            q.G, q.K = 1, tail
+            check(lib().fb_grouped_gemm_bf16(C.byref(q), vp(stream_ptr(dev))), "gram_bf16 tail")
+        else:
+            check(lib().fb_grouped_gemm_bf16(C.byref(p), vp(stream_ptr(dev))), "gram_bf16")
+        count_launch()
+        if split == 1:
+            return d[0]
+        if (K * K) % 4:
+            return d.sum(0)
+        out = torch.empty(K * K, dtype=torch.float32, device=dev)
+        weighted_accumulate(d.view(split, K * K), torch.ones(split, dtype=torch.float32, device=dev), out)
+        return out.view(K, K)
+
+    g = run(hi, hi)
+    if lo is not None:
+        hl = run(hi, lo)
+        g = g + hl + hl.t()
+    return g

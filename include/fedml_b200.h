@@ -242,6 +242,9 @@ typedef struct {
   int32_t accumulate; /* D += result (fp32 output only) */
 } FbGroupedGemm;
 int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
+/* Weight-gradient form: D_g[M][N] = A_g^T * B_g with A_g stored [K][M] and B_g stored [K][N] (M resp. N contiguous,
+ * row strides lda/ldb); the operands are fed to the tensor cores MN-major, so activations need no transpose. */
+int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K10 helpers: NHWC im2col / col2im for 3x3 convolutions batched over clients, fused per-client

@@ -355,3 +355,56 @@ def test_im2col_col2im_vs_torch_backend(H, ch, stride):
     dx_ref = be.col2im3x3(d.float(), B, H, H, ch, stride)
     dx = ops.col2im3x3(d, B, H, H, ch, stride)
     torch.testing.assert_close(dx.float(), dx_ref, rtol=1e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("G,M,N,K", [(1, 128, 16, 64), (3, 200, 16, 16), (2, 1000, 64, 144), (2, 640, 256, 64),
+                                     (1, 130, 10, 256), (2, 256, 288, 32), (4, 2560, 32, 288), (1, 512, 512, 1024)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_grouped_gemm_nt_tcgen05(G, M, N, K, out_dtype):
+    from fedml_b200 import ops
+    torch.manual_seed(M + N + K)
+    a = torch.randn(G, M, K, device=DEV).to(torch.bfloat16)
+    b = torch.randn(G, N, K, device=DEV).to(torch.bfloat16)
+    d = ops.grouped_gemm(a, b, out_dtype)
+    ref = torch.bmm(a.float(), b.float().transpose(1, 2))
+    tol = dict(rtol=2e-2, atol=2e-1) if out_dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-2)
+    torch.testing.assert_close(d.float(), ref, **tol)
+
+
+def test_grouped_gemm_nt_bias_relu_and_strided_groups():
+    from fedml_b200 import ops
+    G, M, N, K = 3, 300, 48, 80
+    big = torch.randn(G, M + 10, K + 8, device=DEV).to(torch.bfloat16)
+    a = big[:, :M, :K]                      # strided rows (lda = K + 8) and group stride
+    b = torch.randn(G, N, K, device=DEV).to(torch.bfloat16)
+    bias = torch.randn(G, N, device=DEV)
+    d = ops.grouped_gemm(a, b, torch.float32, relu=True, bias=bias)
+    ref = torch.relu(torch.bmm(a.float(), b.float().transpose(1, 2)) + bias[:, None, :])
+    torch.testing.assert_close(d, ref, rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("G,Kred,M,N", [(1, 64, 64, 64), (2, 640, 16, 144), (3, 1000, 64, 16), (2, 2560, 128, 576),
+                                        (1, 100, 256, 64), (2, 128, 200, 72)])
+def test_grouped_gemm_tn_tcgen05(G, Kred, M, N):
+    from fedml_b200 import ops
+    torch.manual_seed(Kred + M + N)
+    a = torch.randn(G, Kred, M, device=DEV).to(torch.bfloat16)
+    b = torch.randn(G, Kred, N, device=DEV).to(torch.bfloat16)
+    d = ops.grouped_gemm_tn(a, b)
+    ref = torch.bmm(a.float().transpose(1, 2), b.float())
+    torch.testing.assert_close(d, ref, rtol=1e-3, atol=2e-2)
+
+
+@pytest.mark.parametrize("K,n", [(20, 5000), (64, 100000), (130, 33000)])
+def test_gram_split_k_matches_fp64(K, n):
+    from fedml_b200 import ops
+    torch.manual_seed(K)
+    x = torch.randn(K, n, device=DEV) * 0.01
+    ld = (n + 63) // 64 * 64
+    rows = ops.ptr_table([x.data_ptr() + k * n * 4 for k in range(K)], DEV)
+    hi, lo = ops.krum_pack(rows, K, None, 0, n, ld, split=True)
+    g = ops.gram_bf16(hi, lo)
+    ref = (x.double() @ x.double().t())
+    torch.testing.assert_close(g.double(), ref, rtol=1e-4, atol=1e-6)
+    g_hi = ops.gram_bf16(hi, None)
+    torch.testing.assert_close(g_hi.double(), ref, rtol=3e-2, atol=1e-4)
