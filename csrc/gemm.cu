@@ -18,10 +18,12 @@
 #include "common.cuh"
 #include "../include/fedml_b200.h"
 #include <cuda.h>
+#include <stdlib.h>
 
 #define GEMM_BM 128
 #define GEMM_BK 64
-#define GEMM_STAGES 4
+#define GEMM_MAX_STAGES 8
+#define GEMM_STAGING_BYTES (4 * 2 * 4096)   /* per epilogue warp: two 4 KiB store buffers */
 #define GEMM_THREADS 192
 #define GEMM_A_BYTES (GEMM_BM * 128)
 
@@ -135,19 +137,26 @@ struct GemmArgs {
   int BNpad;       // smem rows/chunks reserved for B (BN, rounded to 64 for MN-major)
   int m_tiles, n_tiles, k_blocks;
   int tmem_cols;
+  int stages;       // smem ring depth (2..GEMM_MAX_STAGES), as many as fit
+  int tma_store;    // 1: epilogue stages tiles in smem and stores them with TMA (coalesced, clipped at the edges)
+  int chunk_cols;   // columns per TMA store box
+  int chunk_bytes;  // bytes per staged row (128 => SWIZZLE_128B box, else unswizzled)
 };
 
 template <bool MN_MAJOR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const GemmArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const uint32_t b_bytes = (uint32_t)a.BNpad * 128u;
   const uint32_t stage_bytes = GEMM_A_BYTES + b_bytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)GEMM_STAGES * stage_bytes);
-  uint64_t* empty_bar = full_bar + GEMM_STAGES;
-  uint64_t* tmem_full = empty_bar + GEMM_STAGES;
+  const int STAGES = a.stages;
+  uint8_t* staging = smem + (size_t)STAGES * stage_bytes;            // 1024-aligned: stage_bytes is a multiple of 2048
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + GEMM_STAGING_BYTES);
+  uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
+  uint64_t* tmem_full = empty_bar + GEMM_MAX_STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
@@ -157,7 +166,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    for (int s = 0; s < GEMM_STAGES; ++s) {
+    if (a.tma_store) tma_prefetch_desc(&tmD);
+    for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
     }
@@ -194,7 +204,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int i = 0; i < a.BNpad / 64; ++i)
               tma_load_3d(&tmB, sb + (size_t)i * GEMM_BK * 128, full_bar + stage, nt * a.BN + i * 64, kb * GEMM_BK, g);
           }
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -227,7 +237,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
           }
           umma_commit(empty_bar + stage);   // smem slot reusable once these MMAs have read it
-          if (++stage == GEMM_STAGES) { stage = 0; phase ^= 1; }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         umma_commit(tmem_full + acc);       // accumulator complete -> epilogue
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -238,6 +248,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int q = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint8_t* my_stage = staging + (size_t)q * 2 * 4096;
+    int sbuf = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
       mbar_wait(tmem_full + acc, acc_phase);
@@ -246,48 +258,93 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool row_ok = row < a.M;
       const uint32_t taddr = tmem_base + (uint32_t)(acc * a.BN) + ((uint32_t)(q * 32) << 16);
       const float* bias = a.bias ? a.bias + (size_t)g * a.bias_gs : nullptr;
-      for (int c0 = 0; c0 < a.BN; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld16(taddr + (uint32_t)c0, r);
-        tmem_ld_wait();
-        const int col0 = nt * a.BN + c0;
-        if (!row_ok || col0 >= a.N) continue;
-        float f[16];
+      if (a.tma_store) {
+        // TMEM -> registers -> (bias, ReLU, convert) -> swizzled smem rows -> one TMA store per 32-row x chunk box
+        const int CW = a.chunk_cols, RB = a.chunk_bytes;
+        const int lds = CW / 16;   // tcgen05.ld.x16 per chunk: 4 (bf16, 64 cols), 2 (fp32, 32 cols) or fewer
+        for (int c0 = 0; c0 < a.BN; c0 += CW) {
+          uint32_t r[64];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
-        if (bias) {
+          for (int i = 0; i < 4; ++i)
+            if (i < lds) tmem_ld16(taddr + (uint32_t)(c0 + 16 * i), r + 16 * i);
+          tmem_ld_wait();
+          const int col0 = nt * a.BN + c0;
+          if (col0 >= a.N) continue;
+          uint8_t* buf = my_stage + (size_t)sbuf * 4096;
+          // the TMA store that last read this buffer (two chunks ago) must have finished reading it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (col0 + i < a.N) f[i] += __ldg(bias + col0 + i);
-        }
-        if (a.relu) {
+          for (int i = 0; i < 4; ++i) {
+            if (i < lds) {
+              float f[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
-        }
-        const bool full = col0 + 16 <= a.N;
-        if (a.d_fp32) {
-          float* dst = reinterpret_cast<float*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
-          if (full && (a.ldd & 3) == 0) {
+              for (int e = 0; e < 16; ++e) f[e] = __uint_as_float(r[16 * i + e]);
+              if (bias) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              *reinterpret_cast<float4*>(dst + 4 * i) = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-          } else {
-            for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = f[i];
-          }
-        } else {
-          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
-          if (full && (a.ldd & 7) == 0) {
-            uint4 o0, o1;
-            __nv_bfloat162* h0 = reinterpret_cast<__nv_bfloat162*>(&o0);
-            __nv_bfloat162* h1 = reinterpret_cast<__nv_bfloat162*>(&o1);
+                for (int e = 0; e < 16; ++e)
+                  if (col0 + 16 * i + e < a.N) f[e] += __ldg(bias + col0 + 16 * i + e);
+              }
+              if (a.relu) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              h0[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-              h1[i] = __floats2bfloat162_rn(f[8 + 2 * i], f[8 + 2 * i + 1]);
+                for (int e = 0; e < 16; ++e) f[e] = fmaxf(f[e], 0.f);
+              }
+              if (a.d_fp32) {
+#pragma unroll
+                for (int sidx = 0; sidx < 4; ++sidx) {
+                  int slot = 4 * i + sidx;
+                  if (RB == 128) slot ^= (lane & 7);
+                  *reinterpret_cast<float4*>(buf + lane * RB + slot * 16) =
+                      make_float4(f[4 * sidx], f[4 * sidx + 1], f[4 * sidx + 2], f[4 * sidx + 3]);
+                }
+              } else {
+#pragma unroll
+                for (int sidx = 0; sidx < 2; ++sidx) {
+                  uint4 o;
+                  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(f[8 * sidx + 2 * e], f[8 * sidx + 2 * e + 1]);
+                  int slot = 2 * i + sidx;
+                  if (RB == 128) slot ^= (lane & 7);
+                  *reinterpret_cast<uint4*>(buf + lane * RB + slot * 16) = o;
+                }
+              }
             }
-            *reinterpret_cast<uint4*>(dst) = o0;
-            *reinterpret_cast<uint4*>(dst + 8) = o1;
+          }
+          fence_async_proxy();   // generic-proxy smem writes -> visible to the TMA (async proxy)
+          __syncwarp();
+          if (lane == 0) {
+            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(&tmD),
+                         "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          sbuf ^= 1;
+        }
+      } else {
+        for (int c0 = 0; c0 < a.BN; c0 += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + (uint32_t)c0, r);
+          tmem_ld_wait();
+          const int col0 = nt * a.BN + c0;
+          if (!row_ok || col0 >= a.N) continue;
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
+          if (bias) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (col0 + i < a.N) f[i] += __ldg(bias + col0 + i);
+          }
+          if (a.relu) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          if (a.d_fp32) {
+            float* dst = reinterpret_cast<float*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
+            for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = f[i];
           } else {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
             for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = __float2bfloat16_rn(f[i]);
           }
         }
@@ -297,6 +354,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (lane == 0) mbar_arrive(tmem_empty + acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (a.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores complete before exit
   }
   tc_fence_before();
   __syncthreads();
@@ -340,6 +398,23 @@ static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t r
   return FB_OK;
 }
 
+// 3-D output map: dims (N, M, groups), box (chunk_cols, 32, 1); swizzled when a staged row is exactly 128 bytes
+static int make_store_map(CUtensorMap* m, void* base, int fp32, uint64_t N, uint64_t M, uint64_t groups, uint64_t ldd,
+                          uint64_t group_stride_elems, uint32_t chunk_cols, bool swizzle128) {
+  PFN_encodeTiled enc = get_encode();
+  FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  const uint64_t es = fp32 ? 4 : 2;
+  cuuint64_t dims[3] = {N, M, groups};
+  cuuint64_t strides[2] = {ldd * es, (groups > 1 ? group_stride_elems : ldd * M) * es};
+  cuuint32_t box[3] = {chunk_cols, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box,
+                   estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (output) failed with code %d", (int)r);
+  return FB_OK;
+}
+
 static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream) {
   FB_REQUIRE(p && p->a && p->b && p->d, "fb_grouped_gemm: null operand");
   FB_REQUIRE(p->G >= 1 && p->M >= 1 && p->N >= 1 && p->K >= 1, "fb_grouped_gemm: empty problem");
@@ -349,12 +424,17 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
   a.d = p->d; a.bias = p->bias; a.d_gs = p->d_gs; a.bias_gs = p->bias_gs;
   a.G = p->G; a.M = p->M; a.N = p->N; a.K = p->K; a.ldd = p->ldd; a.d_fp32 = p->d_fp32; a.relu = p->relu;
   int bn = (p->N + 15) / 16 * 16;
-  if (bn > 256) {
-    // split N evenly into tiles of at most 256 columns (multiple of 16)
+  if (bn > 64) {
+    // n-tiles of at most 256 columns, multiples of 64 so that every TMA store box lies inside its own tile
     int nt = (p->N + 255) / 256;
-    bn = ((p->N + nt - 1) / nt + 15) / 16 * 16;
+    bn = ((p->N + nt - 1) / nt + 63) / 64 * 64;
   }
   a.BN = bn;
+  const uint64_t es = p->d_fp32 ? 4 : 2;
+  a.tma_store = (((uint64_t)p->ldd * es) % 16 == 0) && (((uint64_t)p->d_gs * es) % 16 == 0 || p->G == 1) &&
+                ((uintptr_t)p->d % 16 == 0);
+  a.chunk_cols = p->d_fp32 ? (bn >= 32 ? 32 : 16) : (bn >= 64 ? 64 : bn);
+  a.chunk_bytes = a.chunk_cols * (int)es;
   a.BNpad = mn_major ? (bn + 63) / 64 * 64 : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
   a.m_tiles = (p->M + GEMM_BM - 1) / GEMM_BM;
@@ -378,16 +458,41 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
     rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->G, (uint64_t)p->ldb, (uint64_t)p->b_gs, GEMM_BK);
     if (rc) return rc;
   }
-  const size_t smem = (size_t)GEMM_STAGES * (GEMM_A_BYTES + (size_t)a.BNpad * 128) + 1024 /*align slack*/ + 256 /*barriers*/;
+  const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
+  const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/;
+  // two co-resident CTAs per SM hide each other's per-tile latencies (TMEM allows it while 2 x tmem_cols <= 512)
+  static int force_ctas = -1;
+  if (force_ctas < 0) {
+    const char* e = getenv("FB_GEMM_CTAS_PER_SM");
+    force_ctas = e ? atoi(e) : 0;
+  }
+  int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  if (force_ctas == 1 || force_ctas == 2) ctas_per_sm = (force_ctas == 2 && a.tmem_cols <= 256) ? 2 : 1;
+  int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
+  if (stages < 3 && ctas_per_sm == 2) {
+    ctas_per_sm = 1;
+    stages = (int)((227 * 1024 - fixed) / stage_bytes);
+  }
+  if (stages > GEMM_MAX_STAGES) stages = GEMM_MAX_STAGES;
+  FB_REQUIRE(stages >= 2, "fb_grouped_gemm: tile does not fit shared memory");
+  a.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  CUtensorMap tmD;
+  memset(&tmD, 0, sizeof(tmD));
+  if (a.tma_store) {
+    rc = make_store_map(&tmD, p->d, p->d_fp32, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)p->G, (uint64_t)p->ldd,
+                        (uint64_t)p->d_gs, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
+    if (rc) return rc;
+  }
   const int total = a.G * a.m_tiles * a.n_tiles;
-  int grid = fb_num_sms();
+  int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
   if (mn_major) {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<true><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, a);
+    grouped_gemm_kernel<true><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   } else {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<false><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, a);
+    grouped_gemm_kernel<false><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   }
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;

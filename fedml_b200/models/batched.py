@@ -43,8 +43,10 @@ class TorchBackend:
             y = torch.relu_(y)
         return y if out_dtype is None else y.to(out_dtype)
 
-    def gemm_nn(self, a, b, out_dtype=None):
-        """a [C,M,N] x b [C,N,K] -> [C,M,K]"""
+    want_transposed_weights = False
+
+    def gemm_nn(self, a, b, out_dtype=None, b_t=None):
+        """a [C,M,N] x b [C,N,K] -> [C,M,K]   (``b_t`` = b^T [C,K,N], used by back-ends that want K-major operands)"""
         y = torch.bmm(a, b)
         return y if out_dtype is None else y.to(out_dtype)
 
@@ -153,12 +155,19 @@ class NativeBackend(TorchBackend):
         self._fb("gemm_nt")
         return super().gemm_nt(a, b, out_dtype, relu)
 
-    def gemm_nn(self, a, b, out_dtype=None):
-        # [C,M,N] x [C,N,K]: the kernel wants both operands K-major -> use b^T copies prepared by the layer
+    want_transposed_weights = True
+
+    def gemm_nn(self, a, b, out_dtype=None, b_t=None):
+        # [C,M,N] x [C,N,K]: the tensor-core kernel wants K-major operands -> a x (b^T)^T with the b^T copy
+        # the layer prepared together with the weights
+        if self.use_tc_gemm and b_t is not None and self.ops.grouped_gemm_supported(a, b_t):
+            return self.ops.grouped_gemm(a, b_t, out_dtype or a.dtype)
         self._fb("gemm_nn")
         return super().gemm_nn(a, b, out_dtype)
 
     def gemm_tn(self, a, b, out_dtype=torch.float32):
+        if self.use_tc_gemm and out_dtype == torch.float32 and self.ops.grouped_gemm_tn_supported(a, b):
+            return self.ops.grouped_gemm_tn(a, b)
         self._fb("gemm_tn")
         return super().gemm_tn(a, b, out_dtype)
 
@@ -197,17 +206,25 @@ class NativeBackend(TorchBackend):
 
 # ============================================================================ layers
 class _Conv:
-    def __init__(self, name, k, stride, cin, cout, need_dx=True):
-        self.name, self.k, self.stride, self.cin, self.cout, self.need_dx = name, k, stride, cin, cout, need_dx
+    def __init__(self, name, k, stride, cin, cout, need_dx=True, cin_pad=None):
+        self.name, self.k, self.stride, self.cout, self.need_dx = name, k, stride, cout, need_dx
+        self.cin_real = cin
+        self.cin = cin_pad or cin            # channels of the activation tensor this conv consumes
         self.wname = name + ".weight"
 
-    def prep(self, W, dtype):
-        """fp32 master [C,cout,cin,k,k] -> compute-dtype matrix [C, cout, k*k*cin] in (kh,kw,cin) order."""
+    def prep(self, W, dtype, transposed=False):
+        """fp32 master [C,cout,cin,k,k] -> compute-dtype matrix [C, cout, k*k*cin] in (kh,kw,cin) order
+        (+ its transpose [C, k*k*cin, cout] when the back-end wants K-major dgrad operands)."""
         w = W[self.wname]
         C = w.shape[0]
+        if self.cin != self.cin_real:
+            w = F.pad(w, (0, 0, 0, 0, 0, self.cin - self.cin_real))
         if self.k == 1:
-            return w.reshape(C, self.cout, self.cin).to(dtype)
-        return w.permute(0, 1, 3, 4, 2).reshape(C, self.cout, self.k * self.k * self.cin).to(dtype)
+            wm = w.reshape(C, self.cout, self.cin).to(dtype)
+        else:
+            wm = w.permute(0, 1, 3, 4, 2).reshape(C, self.cout, self.k * self.k * self.cin).to(dtype)
+        wt = wm.transpose(1, 2).contiguous() if (transposed and self.need_dx) else None
+        return wm, wt
 
     def _cols(self, be, x):
         C, B, H, W_, _ = x.shape
@@ -222,7 +239,7 @@ class _Conv:
     def fwd(self, be, x, Wm):
         C, B = x.shape[0], x.shape[1]
         cols, Ho, Wo = self._cols(be, x)
-        return be.gemm_nt(cols, Wm).view(C, B, Ho, Wo, self.cout)
+        return be.gemm_nt(cols, Wm[0]).view(C, B, Ho, Wo, self.cout)
 
     def bwd(self, be, dy, x, Wm, gW):
         C, B, H, W_, _ = x.shape
@@ -230,12 +247,12 @@ class _Conv:
         dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
         dWm = be.gemm_tn(dy2, cols)                                   # [C, cout, kk*cin] fp32
         if self.k == 1:
-            gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1))
+            gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1)[:, :, :self.cin_real])
         else:
-            gW.copy_(dWm.view(C, self.cout, self.k, self.k, self.cin).permute(0, 1, 4, 2, 3))
+            gW.copy_(dWm.view(C, self.cout, self.k, self.k, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
         if not self.need_dx:
             return None
-        dcols = be.gemm_nn(dy2, Wm)                                   # [C, M, kk*cin]
+        dcols = be.gemm_nn(dy2, Wm[0], b_t=Wm[1])                     # [C, M, kk*cin]
         if self.k == 1:
             if self.stride == 1:
                 return dcols.view(C, B, H, W_, self.cin)
@@ -379,7 +396,9 @@ class BatchedResNet(BatchedModel):
         if getattr(module, "stem", "cifar") != "cifar" and not isinstance(getattr(module, "maxpool", None), nn.Identity):
             raise NotImplementedError("batched ResNet supports 3x3 stems without max-pool (CIFAR-sized inputs)")
         c1 = module.conv1
-        self.stem_conv = _Conv("conv1", c1.kernel_size[0], c1.stride[0], c1.in_channels, c1.out_channels, need_dx=False)
+        pad = 8 if (isinstance(backend, NativeBackend) and c1.in_channels % 8) else None
+        self.stem_conv = _Conv("conv1", c1.kernel_size[0], c1.stride[0], c1.in_channels, c1.out_channels, need_dx=False,
+                               cin_pad=pad)
         self.stem_bn = _BN("bn1", c1.out_channels, module.bn1.momentum, module.bn1.eps)
         self.blocks: List[_Block] = []
         for li in range(1, module.num_stages + 1):
@@ -392,7 +411,8 @@ class BatchedResNet(BatchedModel):
 
     def prepare(self, W):
         dt = self.be.dtype
-        Wm = {c.name: c.prep(W, dt) for c in self.convs}
+        tr = self.be.want_transposed_weights
+        Wm = {c.name: c.prep(W, dt, tr) for c in self.convs}
         Wm["fc"] = W["fc.weight"].to(dt)
         return Wm
 
@@ -400,8 +420,12 @@ class BatchedResNet(BatchedModel):
         if x.dtype == torch.uint8:
             if self.mean.device != x.device:     # one-time move; must not happen inside a CUDA-graph capture
                 self.mean, self.std = self.mean.to(x.device), self.std.to(x.device)
-            return self.be.normalize_images(x, self.mean, self.std)
-        return x.to(self.be.dtype)
+            x = self.be.normalize_images(x, self.mean, self.std)
+        else:
+            x = x.to(self.be.dtype)
+        if self.stem_conv.cin != x.shape[-1]:
+            x = F.pad(x, (0, self.stem_conv.cin - x.shape[-1]))       # zero channels so that K = 9*8 feeds TMA
+        return x
 
     def _forward(self, x, W, Wm, active, training, tape):
         be = self.be

