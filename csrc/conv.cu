@@ -189,18 +189,21 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
-                    const float* __restrict__ rstd, int relu, float* __restrict__ partial) {
+                    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    int64_t ld_p, int relu, float* __restrict__ partial) {
   __shared__ float smem[BN_THREADS * 16];
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
   const size_t cbase = (size_t)c * M * ch;
   const int coff = (tid * BN_VEC) % ch;
-  float mu[8], rs[8];
+  float mu[8], rs[8], ga[8], be[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     mu[i] = mean[(size_t)c * ch + coff + i];
     rs[i] = rstd[(size_t)c * ch + coff + i];
+    ga[i] = gamma[(size_t)c * ld_p + coff + i];
+    be[i] = beta ? beta[(size_t)c * ld_p + coff + i] : 0.f;
   }
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
@@ -209,10 +212,15 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     unpack8(ldg16(dy + cbase + v * BN_VEC), d);
     unpack8(ldg16(x + cbase + v * BN_VEC), xv);
     if (relu) {
-      float yv[8];
-      unpack8(ldg16(y + cbase + v * BN_VEC), yv);
+      if (y) {   // residual block output: the mask needs the stored forward output
+        float yv[8];
+        unpack8(ldg16(y + cbase + v * BN_VEC), yv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+        for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+      } else {   // plain BN+ReLU: recompute the sign from x instead of streaming y again
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] = ((xv[i] - mu[i]) * rs[i] * ga[i] + be[i]) > 0.f ? d[i] : 0.f;
+      }
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -227,8 +235,9 @@ __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
                     int64_t M, int ch, int S, const float* __restrict__ partial, const float* __restrict__ gamma,
-                    int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
-                    float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g) {
+                    const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
+                    const float* __restrict__ rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    int64_t ld_g) {
   extern __shared__ float sm[];  // k1[ch] = gamma*rstd, k2[ch] = dbeta/M, k3[ch] = dgamma/M * rstd ... see below
   float* s_g = sm;               // gamma * rstd
   float* s_db = sm + ch;         // dbeta / M
@@ -253,7 +262,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
   const size_t cbase = (size_t)c * M * ch;
   const int coff = (tid * BN_VEC) % ch;
-  float g[8], db[8], dg[8], mu[8], rs[8];
+  float g[8], db[8], dg[8], mu[8], rs[8], be[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     g[i] = s_g[coff + i];
@@ -261,6 +270,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     dg[i] = s_dg[coff + i];
     mu[i] = mean[(size_t)c * ch + coff + i];
     rs[i] = rstd[(size_t)c * ch + coff + i];
+    be[i] = beta ? beta[(size_t)c * ld_p + coff + i] : 0.f;
   }
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
   for (int64_t v = v0 + tid; v < v1; v += BN_THREADS) {
@@ -268,10 +278,15 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     unpack8(ldg16(dy + cbase + v * BN_VEC), d);
     unpack8(ldg16(x + cbase + v * BN_VEC), xv);
     if (relu) {
-      float yv[8];
-      unpack8(ldg16(y + cbase + v * BN_VEC), yv);
+      if (y) {
+        float yv[8];
+        unpack8(ldg16(y + cbase + v * BN_VEC), yv);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+        for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] = ((xv[i] - mu[i]) * g[i] + be[i]) > 0.f ? d[i] : 0.f;
+      }
     }
     if (dres) *reinterpret_cast<uint4*>(dres + cbase + v * BN_VEC) = pack8(d);
     float o[8];
@@ -282,21 +297,22 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 }
 
 extern "C" int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C,
-                                 int64_t M, int32_t ch, const float* gamma, int64_t ld_p, const float* save_mean,
+                                 int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
+                                 const float* save_mean,
                                  const float* save_rstd, int32_t relu, float* dgamma, float* dbeta, int64_t ld_g,
                                  float* scratch, fb_stream_t stream) {
   FB_REQUIRE(dy && x && dx && gamma && save_mean && save_rstd && dgamma && dbeta && scratch && C >= 1 && C <= 65535,
              "fb_bn_bwd_stacked: bad arguments");
-  FB_REQUIRE(!relu || y, "fb_bn_bwd_stacked: the ReLU mask needs the forward output");
+  FB_REQUIRE(!relu || y || beta, "fb_bn_bwd_stacked: the ReLU mask needs the forward output or beta to recompute it");
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   const int S = bn_slices(C, M, ch);
   bn_bwd_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, relu,
-      scratch);
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
+      beta, ld_p, relu, scratch);
   FB_CHECK_CUDA(cudaGetLastError());
   bn_bwd_apply_kernel<<<dim3(S, C), BN_THREADS, 3 * ch * sizeof(float), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
-      (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
+      (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

@@ -97,7 +97,7 @@ class TorchBackend:
             y = torch.relu(y)
         return y.to(x.dtype), mean, rstd
 
-    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres):
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True):
         C = x.shape[0]
         ch = x.shape[-1]
         dyf = dy.float()
@@ -189,9 +189,10 @@ class NativeBackend(TorchBackend):
         self._fb("bn_fwd")
         return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
 
-    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres):
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True):
         if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
-            return self.ops.bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres)
+            skip_y = relu and not had_res and beta is not None   # mask recomputed from x: one stream less
+            return self.ops.bn_bwd_stacked(dy, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta)
         self._fb("bn_bwd")
         return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres)
 
@@ -273,7 +274,8 @@ class _BN:
 
     def bwd(self, be, dy, x, y, W, G, mean, rstd, relu, want_dres):
         n = self.name
-        dx, dres, dgamma, dbeta = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres)
+        dx, dres, dgamma, dbeta = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres,
+                                            beta=W[n + ".bias"], had_res=want_dres)
         G[n + ".weight"].copy_(dgamma)
         G[n + ".bias"].copy_(dbeta)
         return dx, dres

@@ -296,7 +296,8 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
     return y, mean, rstd
 
 
-def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres):
+def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None):
+    """``y=None`` (+ ``beta``) recomputes the ReLU mask from x — only valid when the forward had no residual."""
     Cn, ch = x.shape[0], x.shape[-1]
     M = x.numel() // (Cn * ch)
     dy = dy.contiguous()
@@ -306,8 +307,8 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres):
     dbeta = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
     check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
-                                  i32(ch), vp(ptr(gamma)), i64(gamma.stride(0)), vp(ptr(mean)), vp(ptr(rstd)),
-                                  i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ch), vp(ptr(scratch)),
+                                  i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
+                                  vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ch), vp(ptr(scratch)),
                                   vp(stream_ptr(x.device))), "bn_bwd_stacked")
     count_launch(2)
     return dx, dres, dgamma, dbeta

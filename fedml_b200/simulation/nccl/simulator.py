@@ -211,52 +211,122 @@ class NCCLSimulator:
         return torch.cat([b[0] for b in batches]), torch.cat([b[1] for b in batches])
 
     def _stage_round_inputs(self, my_clients: List[int], round_idx: int):
-        """Build X [C, S, B, ...], Y [C, S, B] (-1 padded), steps [C] on the host (pinned), one H2D."""
+        """Inputs of one round for this rank: X [C, S, B, ...], Y [C, S, B] (-1 = padding), steps [C].
+
+        Host side: ONE vectorised gather (``index_select`` with a [C*S*B] index built from the packed
+        dataset's client offsets) straight into a persistent pinned staging buffer, then ONE async H2D
+        copy on a side stream.  Two staging slots alternate so the next round can be staged while the
+        current one trains (see ``_prefetch``)."""
         args = self.args
         bs = int(args.batch_size)
-        drop_last = self.fed is not None and self.fed.transform is not None and bs > 0
+        C = self.C_max
+        if self.fed is None:
+            return self._stage_round_inputs_generic(my_clients, round_idx)
+        drop_last = self.fed.transform is not None and bs > 0
+        offs = self.fed.client_offsets
+        plans = []
+        for cid in my_clients:
+            n = int(offs[cid + 1] - offs[cid])
+            b = n if bs <= 0 else bs
+            steps = n // b if drop_last else (n + b - 1) // b
+            plans.append((cid, n, b, steps))
+        B = max([p[2] for p in plans], default=max(bs, 1))
+        S = max([p[3] for p in plans], default=0)
+        if not plans or S == 0:
+            return None
+        idx = torch.zeros(C, S * B, dtype=torch.int64)
+        valid = torch.zeros(C, S, B, dtype=torch.bool)
+        steps_t = torch.zeros(C, dtype=torch.int64)
+        shuffle = drop_last and bool(getattr(args, "shuffle_clients", True))
+        for pos, (cid, n, b, steps) in enumerate(plans):
+            if shuffle:
+                g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) * 1000003 + round_idx * 1009 + cid)
+                local = torch.randperm(n, generator=g)
+            else:
+                local = torch.arange(n)
+            take = min(n, steps * b)
+            # lay the client's samples out step-major with B slots per step (ragged last batch stays padded)
+            for s_ in range(steps):
+                lo, hi = s_ * b, min((s_ + 1) * b, take)
+                idx[pos, s_ * B:s_ * B + (hi - lo)] = local[lo:hi] + int(offs[cid])
+                valid[pos, s_, :hi - lo] = True
+            steps_t[pos] = steps
+        slot = self._stage_slot = (getattr(self, "_stage_slot", 1) + 1) % 2
+        nrow = C * S * B
+        xs, ys = self.fed.x, self.fed.y
+        key = (nrow, tuple(xs.shape[1:]), xs.dtype, tuple(ys.shape[1:]))
+        if getattr(self, "_pinned_key", None) != key:
+            pin = self.cuda
+            self._pinned = [(torch.empty((nrow,) + tuple(xs.shape[1:]), dtype=xs.dtype, pin_memory=pin),
+                             torch.empty((nrow,) + tuple(ys.shape[1:]), dtype=ys.dtype, pin_memory=pin)) for _ in range(2)]
+            self._pinned_key = key
+            self._pinned_events = [None, None]
+        Xp, Yp = self._pinned[slot]
+        if self.cuda and self._pinned_events[slot] is not None:
+            self._pinned_events[slot].synchronize()        # the previous H2D out of this slot has finished
+        flat = idx.view(-1)
+        torch.index_select(xs, 0, flat, out=Xp)
+        torch.index_select(ys, 0, flat, out=Yp)
+        Yp.view(C, S, B, *ys.shape[1:])[~valid] = -1
+        inv_valid = 1.0 / valid.sum(dim=2).clamp_min(1).to(torch.float32)
+        if self.cuda:
+            if getattr(self, "_copy_stream", None) is None:
+                self._copy_stream = torch.cuda.Stream(self.device)
+            with torch.cuda.stream(self._copy_stream):
+                Xd = Xp.to(self.device, non_blocking=True).view(C, S, B, *xs.shape[1:])
+                Yd = Yp.to(self.device, non_blocking=True).view(C, S, B, *ys.shape[1:])
+                inv_d = inv_valid.to(self.device, non_blocking=True)
+                steps_d = steps_t.to(self.device, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            self._pinned_events[slot] = ev
+            self.h2d_bytes += Xp.numel() * Xp.element_size() + Yp.numel() * Yp.element_size()
+        else:
+            Xd, Yd = Xp.view(C, S, B, *xs.shape[1:]).clone(), Yp.view(C, S, B, *ys.shape[1:]).clone()
+            inv_d, steps_d, ev = inv_valid, steps_t, None
+        return Xd, Yd, steps_d, inv_d, S, ev
+
+    def _stage_round_inputs_generic(self, my_clients, round_idx):
+        """Fallback for datasets handed over only as the 8-tuple (lists of batches / DataLoaders)."""
         C = self.C_max
         per = []
-        for pos, cid in enumerate(my_clients):
-            x, y = self._client_arrays(cid)
-            n = x.shape[0]
-            b = n if bs <= 0 else bs
-            if drop_last:
-                steps = n // b
-                if steps and bool(getattr(args, "shuffle_clients", True)):
-                    g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) * 1000003 + round_idx * 1009 + cid)
-                    perm = torch.randperm(n, generator=g)[:steps * b]
-                    x, y = x[perm], y[perm]
-                else:
-                    x, y = x[:steps * b], y[:steps * b]
-            else:
-                steps = (n + b - 1) // b
-            per.append((x, y, steps, b, n))
-        B = max([p[3] for p in per], default=max(bs, 1))
-        S = max([p[2] for p in per], default=0)
-        if not per or S == 0:
+        for cid in my_clients:
+            batches = list(self.train_local[cid])
+            per.append(batches)
+        S = max((len(b) for b in per), default=0)
+        if S == 0:
             return None
-        xs0 = per[0][0]
-        X = torch.zeros((C, S, B) + tuple(xs0.shape[1:]), dtype=xs0.dtype)
-        Y = torch.full((C, S, B) + tuple(per[0][1].shape[1:]), -1, dtype=torch.int64)
+        B = max(b[0].shape[0] for bl in per for b in bl)
+        x0, y0 = per[0][0]
+        X = torch.zeros((C, S, B) + tuple(x0.shape[1:]), dtype=x0.dtype)
+        Y = torch.full((C, S, B) + tuple(y0.shape[1:]), -1, dtype=torch.int64)
         steps_t = torch.zeros(C, dtype=torch.int64)
-        valid = torch.ones(C, S, dtype=torch.float32)
-        for pos, (x, y, steps, b, n) in enumerate(per):
-            steps_t[pos] = steps
-            for s in range(steps):
-                lo, hi = s * b, min((s + 1) * b, x.shape[0])
-                X[pos, s, :hi - lo] = x[lo:hi]
-                Y[pos, s, :hi - lo] = y[lo:hi]
-                valid[pos, s] = max(hi - lo, 1)
+        valid = torch.ones(C, S)
+        for pos, bl in enumerate(per):
+            steps_t[pos] = len(bl)
+            for s_, (xb, yb) in enumerate(bl):
+                X[pos, s_, :xb.shape[0]] = xb
+                Y[pos, s_, :yb.shape[0]] = yb
+                valid[pos, s_] = xb.shape[0]
+        dev = self.device
         if self.cuda:
-            Xp, Yp = X.pin_memory(), Y.pin_memory()
-            Xd = Xp.to(self.device, non_blocking=True)
-            Yd = Yp.to(self.device, non_blocking=True)
-            self.h2d_bytes += Xp.numel() * Xp.element_size() + Yp.numel() * Yp.element_size()
-            self._keep_pinned = (Xp, Yp)
-        else:
-            Xd, Yd = X, Y
-        return Xd, Yd, steps_t, (1.0 / valid).to(self.device), S
+            self.h2d_bytes += X.numel() * X.element_size() + Y.numel() * Y.element_size()
+        return X.to(dev), Y.to(dev), steps_t.to(dev), (1.0 / valid).to(dev), S, None
+
+    def _round_plan(self, round_idx: int):
+        N = int(self.args.client_num_in_total)
+        sampled = client_sampling(round_idx, N, self.K)
+        sizes = [int(self.local_num[c]) for c in sampled]
+        assign = schedule_clients(sizes, self.world)
+        my_pos = assign[self.rank]
+        return sampled, sizes, assign, my_pos, [sampled[p] for p in my_pos]
+
+    def _prefetch(self, round_idx: int):
+        """Stage the inputs of a future round while the GPU is still busy with the current one."""
+        if self.batched is None or round_idx >= int(self.args.comm_round):
+            return
+        plan = self._round_plan(round_idx)
+        self._prefetched = (round_idx, plan, self._stage_round_inputs(plan[4], round_idx) if plan[4] else None)
 
     # ------------------------------------------------------------------ local training
     def _sgd(self, C, lr_vec, first_step):
@@ -287,7 +357,9 @@ class NCCLSimulator:
         st["loss"].copy_(loss)
 
     def _train_batched(self, staged, n_local):
-        Xd, Yd, steps_t, inv_valid, S = staged
+        Xd, Yd, steps_dev, inv_valid, S, ev = staged
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)       # inputs were copied on the side stream
         C = self.C_max
         epochs = int(getattr(self.args, "epochs", 1))
         dev = self.device
@@ -299,7 +371,6 @@ class NCCLSimulator:
                             "loss": torch.zeros(C, dtype=torch.float32, device=dev)}
             self.graph = None
         st = self._static
-        steps_dev = steps_t.to(dev)
         first = True
         for _ in range(epochs):
             for s in range(S):
@@ -350,18 +421,17 @@ class NCCLSimulator:
     # ------------------------------------------------------------------ one round
     def train_one_round(self, round_idx: int):
         args = self.args
-        N = int(args.client_num_in_total)
-        sampled = client_sampling(round_idx, N, self.K)
-        sizes = [int(self.local_num[c]) for c in sampled]
-        assign = schedule_clients(sizes, self.world)
-        my_pos = assign[self.rank]
-        my_clients = [sampled[p] for p in my_pos]
-        C_real = len(my_clients)
-        dev = self.device
+        pre = getattr(self, "_prefetched", None)
         t = self.timer
         t.start("h2d")
-        staged = self._stage_round_inputs(my_clients, round_idx) if self.batched is not None and C_real else None
+        if pre is not None and pre[0] == round_idx:
+            (sampled, sizes, assign, my_pos, my_clients), staged = pre[1], pre[2]
+        else:
+            sampled, sizes, assign, my_pos, my_clients = self._round_plan(round_idx)
+            staged = self._stage_round_inputs(my_clients, round_idx) if self.batched is not None and my_clients else None
+        self._prefetched = None
         t.stop("h2d")
+        dev = self.device
         # every row starts from the global model (dummy rows too: they carry weight 0)
         t.start("train")
         if self.cuda:
@@ -381,9 +451,12 @@ class NCCLSimulator:
         for i, p in enumerate(my_pos):
             weights[i] = sizes[p]
         total = float(sum(sizes))
-        self._aggregate(weights.to(dev), total, my_pos, sizes, round_idx)
+        self._aggregate(weights.to(dev, non_blocking=True), total, my_pos, sizes, round_idx)
         t.stop("aggregate")
         self.round_idx = round_idx + 1
+        # the GPU is still working through this round: use the host time to stage the next one
+        if bool(getattr(args, "prefetch_inputs", True)):
+            self._prefetch(round_idx + 1)
 
     def _fednova_coefs(self, sizes, my_pos):
         """Host-side FedNova scalars (fednova.py:114-167, client.py:50-65): lockstep local steps make

@@ -264,10 +264,12 @@ int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_
                       const float* beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                       const float* active, float momentum, float eps, int32_t relu, int32_t training,
                       float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream);
-/* dx (and dres = ReLU-masked dy, optional) from dy; dgamma/dbeta fp32 rows with stride ld_g. y is the forward
- * output (needed for the ReLU mask). */
+/* dx (and dres = ReLU-masked dy, optional) from dy; dgamma/dbeta fp32 rows with stride ld_g.  The ReLU mask comes
+ * from y (forward output; required when the forward had a residual input) or, when y is NULL, is recomputed from
+ * x, gamma and beta so that the output tensor is not streamed again. */
 int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C, int64_t M,
-                      int32_t ch, const float* gamma, int64_t ld_p, const float* save_mean, const float* save_rstd,
+                      int32_t ch, const float* gamma, const float* beta, int64_t ld_p, const float* save_mean,
+                      const float* save_rstd,
                       int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, float* scratch, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
