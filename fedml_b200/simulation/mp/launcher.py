@@ -71,14 +71,21 @@ class _ThreadedSimulation:
                 errors.append((rank, exc))
                 raise
 
-        threads = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(1, size)]
+        threads = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(0, size)]
         for t in threads:
             t.start()
-        work(0)
-        for t in threads:
-            t.join(timeout=600)
+        import time
+        deadline = time.time() + float(getattr(self.args, "simulation_timeout_s", 3600))
+        # fail fast: one crashed rank would leave the others blocked in their receive loops forever
+        while any(t.is_alive() for t in threads):
+            if errors:
+                InProcHub.reset(getattr(self.args, "run_id", 0))
+                raise RuntimeError(f"rank {errors[0][0]} failed") from errors[0][1]
+            if time.time() > deadline:
+                raise TimeoutError("multi-process simulation (threaded) timed out")
+            time.sleep(0.02)
         if errors:
-            raise errors[0][1]
+            raise RuntimeError(f"rank {errors[0][0]} failed") from errors[0][1]
         return self.results.get(0)
 
 
