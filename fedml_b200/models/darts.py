@@ -1,0 +1,145 @@
+"""DARTS search space for FedNAS (reference: model/cv/darts/*.py, 2507 LoC: model_search.py, operations.py,
+genotypes.py, architect.py).  A compact but complete differentiable-NAS network: mixed operations over the
+standard primitive set, normal/reduction cells with continuous architecture parameters ``alphas_normal`` /
+``alphas_reduce`` (exposed through ``arch_parameters()``), ``genotype()`` decoding by the top-2 strongest
+non-``none`` edges per node."""
+from collections import namedtuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+Genotype = namedtuple("Genotype", "normal normal_concat reduce reduce_concat")
+PRIMITIVES = ["none", "max_pool_3x3", "avg_pool_3x3", "skip_connect", "sep_conv_3x3", "sep_conv_5x5", "dil_conv_3x3",
+              "dil_conv_5x5"]
+
+
+class _Zero(nn.Module):
+    def __init__(self, stride):
+        super().__init__()
+        self.stride = stride
+
+    def forward(self, x):
+        return x.mul(0.0) if self.stride == 1 else x[:, :, ::self.stride, ::self.stride].mul(0.0)
+
+
+class _FactorizedReduce(nn.Module):
+    def __init__(self, ci, co):
+        super().__init__()
+        self.c1 = nn.Conv2d(ci, co // 2, 1, 2, 0, bias=False)
+        self.c2 = nn.Conv2d(ci, co - co // 2, 1, 2, 0, bias=False)
+        self.bn = nn.BatchNorm2d(co, affine=False)
+
+    def forward(self, x):
+        x = F.relu(x)
+        shifted = F.pad(x, (0, 1, 0, 1))[:, :, 1:, 1:]
+        return self.bn(torch.cat([self.c1(x), self.c2(shifted)], 1))
+
+
+def _sep(ci, co, k, s, p):
+    return nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, ci, k, s, p, groups=ci, bias=False), nn.Conv2d(ci, ci, 1, bias=False),
+                         nn.BatchNorm2d(ci, affine=False), nn.ReLU(False), nn.Conv2d(ci, ci, k, 1, p, groups=ci, bias=False),
+                         nn.Conv2d(ci, co, 1, bias=False), nn.BatchNorm2d(co, affine=False))
+
+
+def _dil(ci, co, k, s, p, d):
+    return nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, ci, k, s, p, dilation=d, groups=ci, bias=False),
+                         nn.Conv2d(ci, co, 1, bias=False), nn.BatchNorm2d(co, affine=False))
+
+
+OPS = {
+    "none": lambda C, s: _Zero(s),
+    "avg_pool_3x3": lambda C, s: nn.Sequential(nn.AvgPool2d(3, s, 1, count_include_pad=False), nn.BatchNorm2d(C, affine=False)),
+    "max_pool_3x3": lambda C, s: nn.Sequential(nn.MaxPool2d(3, s, 1), nn.BatchNorm2d(C, affine=False)),
+    "skip_connect": lambda C, s: nn.Identity() if s == 1 else _FactorizedReduce(C, C),
+    "sep_conv_3x3": lambda C, s: _sep(C, C, 3, s, 1),
+    "sep_conv_5x5": lambda C, s: _sep(C, C, 5, s, 2),
+    "dil_conv_3x3": lambda C, s: _dil(C, C, 3, s, 2, 2),
+    "dil_conv_5x5": lambda C, s: _dil(C, C, 5, s, 4, 2),
+}
+
+
+class MixedOp(nn.Module):
+    def __init__(self, C, stride):
+        super().__init__()
+        self._ops = nn.ModuleList(OPS[p](C, stride) for p in PRIMITIVES)
+
+    def forward(self, x, weights):
+        return sum(w * op(x) for w, op in zip(weights, self._ops))
+
+
+class Cell(nn.Module):
+    def __init__(self, steps, multiplier, Cpp, Cp, C, reduction, reduction_prev):
+        super().__init__()
+        self.reduction, self._steps, self._multiplier = reduction, steps, multiplier
+        self.pre0 = _FactorizedReduce(Cpp, C) if reduction_prev else \
+            nn.Sequential(nn.ReLU(False), nn.Conv2d(Cpp, C, 1, bias=False), nn.BatchNorm2d(C, affine=False))
+        self.pre1 = nn.Sequential(nn.ReLU(False), nn.Conv2d(Cp, C, 1, bias=False), nn.BatchNorm2d(C, affine=False))
+        self._ops = nn.ModuleList()
+        for i in range(steps):
+            for j in range(2 + i):
+                self._ops.append(MixedOp(C, 2 if reduction and j < 2 else 1))
+
+    def forward(self, s0, s1, weights):
+        states, off = [self.pre0(s0), self.pre1(s1)], 0
+        for _ in range(self._steps):
+            s = sum(self._ops[off + j](h, weights[off + j]) for j, h in enumerate(states))
+            off += len(states)
+            states.append(s)
+        return torch.cat(states[-self._multiplier:], dim=1)
+
+
+class Network(nn.Module):
+    """DARTS search network (``model_search.Network``)."""
+
+    def __init__(self, C=8, num_classes=10, layers=3, steps=2, multiplier=2, stem_multiplier=3):
+        super().__init__()
+        self._steps, self._multiplier = steps, multiplier
+        Cc = stem_multiplier * C
+        self.stem = nn.Sequential(nn.Conv2d(3, Cc, 3, padding=1, bias=False), nn.BatchNorm2d(Cc))
+        Cpp, Cp, Cc = Cc, Cc, C
+        self.cells, red_prev = nn.ModuleList(), False
+        for i in range(layers):
+            red = layers >= 3 and i in (layers // 3, 2 * layers // 3)
+            if red:
+                Cc *= 2
+            self.cells.append(Cell(steps, multiplier, Cpp, Cp, Cc, red, red_prev))
+            red_prev = red
+            Cpp, Cp = Cp, multiplier * Cc
+        self.classifier = nn.Linear(Cp, num_classes)
+        k = sum(2 + i for i in range(steps))
+        self.alphas_normal = nn.Parameter(1e-3 * torch.randn(k, len(PRIMITIVES)))
+        self.alphas_reduce = nn.Parameter(1e-3 * torch.randn(k, len(PRIMITIVES)))
+
+    def arch_parameters(self):
+        return [self.alphas_normal, self.alphas_reduce]
+
+    def weight_parameters(self):
+        ids = {id(p) for p in self.arch_parameters()}
+        return [p for p in self.parameters() if id(p) not in ids]
+
+    def forward(self, x):
+        s0 = s1 = self.stem(x)
+        for cell in self.cells:
+            w = F.softmax(self.alphas_reduce if cell.reduction else self.alphas_normal, dim=-1)
+            s0, s1 = s1, cell(s0, s1, w)
+        return self.classifier(F.adaptive_avg_pool2d(s1, 1).flatten(1))
+
+    def genotype(self):
+        none = PRIMITIVES.index("none")
+
+        def parse(weights):
+            gene, n, start = [], 2, 0
+            for i in range(self._steps):
+                end = start + n
+                W = weights[start:end]
+                edges = sorted(range(i + 2), key=lambda x: -max(W[x][k] for k in range(len(W[x])) if k != none))[:2]
+                for j in edges:
+                    k_best = max((k for k in range(len(W[j])) if k != none), key=lambda k: W[j][k])
+                    gene.append((PRIMITIVES[k_best], j))
+                start, n = end, n + 1
+            return gene
+
+        concat = list(range(2 + self._steps - self._multiplier, self._steps + 2))
+        return Genotype(parse(F.softmax(self.alphas_normal, -1).tolist()), concat,
+                        parse(F.softmax(self.alphas_reduce, -1).tolist()), concat)

@@ -1,0 +1,64 @@
+"""FedNAS — federated DARTS (reference: mpi_p2p_mp/fednas/*.py, 894 LoC): in the search stage clients alternate
+architecture-alpha steps (on a held-out half of their data) and weight steps (FedNASTrainer.py:43-165); the
+server averages weights *and* alphas (FedNASAggregator.py:66-123) and records the genotype every round."""
+import torch
+import torch.nn as nn
+
+from ...core.alg_frame import ClientTrainer
+from ...models.darts import Network
+from .fedavg import FedML_FedAvg_distributed
+
+
+class FedNASTrainer(ClientTrainer):
+    def get_model_params(self):
+        return {k: v.detach().clone() for k, v in self.model.state_dict().items()}
+
+    def set_model_params(self, p):
+        self.model.load_state_dict(p)
+
+    def train(self, train_data, device, args):
+        m = self.model.to(device)
+        m.train()
+        batches = list(train_data)
+        half = max(1, len(batches) // 2)
+        w_batches, a_batches = batches[:half], batches[half:] or batches[:half]
+        crit = nn.CrossEntropyLoss()
+        w_opt = torch.optim.SGD(m.weight_parameters(), lr=float(getattr(args, "learning_rate", 0.025)), momentum=0.9,
+                                weight_decay=float(getattr(args, "weight_decay", 3e-4)))
+        a_opt = torch.optim.Adam(m.arch_parameters(), lr=float(getattr(args, "arch_learning_rate", 3e-4)), betas=(0.5, 0.999),
+                                 weight_decay=float(getattr(args, "arch_weight_decay", 1e-3)))
+        search = str(getattr(args, "stage", "search")) == "search"
+        for _ in range(int(getattr(args, "epochs", 1))):
+            for i, (x, y) in enumerate(w_batches):
+                if search:   # first-order DARTS: alpha step on validation data, then weight step on training data
+                    xa, ya = a_batches[i % len(a_batches)]
+                    a_opt.zero_grad(set_to_none=True)
+                    crit(m(xa.to(device)), ya.to(device)).backward()
+                    a_opt.step()
+                w_opt.zero_grad(set_to_none=True)
+                crit(m(x.to(device)), y.to(device)).backward()
+                nn.utils.clip_grad_norm_(m.weight_parameters(), float(getattr(args, "grad_clip", 5.0)))
+                w_opt.step()
+
+    def test(self, test_data, device, args):
+        m = self.model.to(device)
+        m.eval()
+        c = l = n = 0.0
+        with torch.no_grad():
+            for x, y in test_data:
+                o = m(x.to(device))
+                l += float(nn.functional.cross_entropy(o, y.to(device), reduction="sum"))
+                c += float((o.argmax(1).cpu() == y).sum())
+                n += len(y)
+        return {"test_correct": c, "test_loss": l, "test_total": n, "genotype": str(m.genotype())}
+
+
+def FedML_FedNAS_distributed(args, process_id, worker_number, comm, device, dataset, model=None, model_trainer=None,  # noqa: N802
+                             backend="INPROC", **kw):
+    if not isinstance(model, Network):
+        model = Network(C=int(getattr(args, "init_channels", 8)), num_classes=dataset[7], layers=int(getattr(args, "layers", 3)))
+    out = FedML_FedAvg_distributed(args, process_id, worker_number, comm, device, dataset, model,
+                                   model_trainer or FedNASTrainer(model, args), backend=backend, **kw)
+    if process_id == 0:
+        out.genotype = out.trainer.model.genotype()
+    return out
