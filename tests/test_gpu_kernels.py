@@ -415,3 +415,43 @@ def test_gram_split_k_matches_fp64(K, n):
     torch.testing.assert_close(g.double(), ref, rtol=1e-4, atol=1e-6)
     g_hi = ops.gram_bf16(hi, None)
     torch.testing.assert_close(g_hi.double(), ref, rtol=3e-2, atol=2e-3)   # bf16-only operands: ~1e-4 rounding noise per entry
+
+
+@pytest.mark.parametrize("G", [1, 2, 4])
+def test_dp_allreduce_step_emulated(G):
+    """Cheetah kernel: G emulated ranks in one cooperative launch == mean-gradient SGD with momentum on every replica."""
+    import ctypes as C
+    from fedml_b200 import ops
+    from fedml_b200.ops.native import FbDpStepParams, check, lib, stream_ptr
+    n = 4 * 3001
+    torch.manual_seed(G)
+    w0 = torch.randn(n, device=DEV)
+    params = [w0.clone() for _ in range(G)]
+    grads = [torch.randn(n, device=DEV) for _ in range(G)]
+    moms = [torch.zeros(n, device=DEV) for _ in range(G)]
+    flags = [torch.zeros(ops.round_flag_bytes(G) // 4, dtype=torch.int32, device=DEV) for _ in range(G)]
+    tab = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64, device=DEV)
+    tg, tp, tf = tab(grads), tab(params), tab(flags)
+    ref_w, ref_m = w0.clone(), torch.zeros(n, device=DEV)
+    for step in range(1, 3):
+        for g in grads:
+            g.copy_(torch.randn(n, device=DEV))
+        ps = []
+        for r in range(G):
+            p = FbDpStepParams()
+            p.peer_grad, p.peer_param, p.peer_flags, p.mom = tg.data_ptr(), tp.data_ptr(), tf.data_ptr(), moms[r].data_ptr()
+            p.n, p.rank, p.G, p.epoch = n, r, G, step
+            p.lr, p.momentum, p.weight_decay, p.inv_world, p.nesterov = 0.1, 0.9, 0.01, 1.0 / G, 0
+            ps.append(p)
+        arr = (FbDpStepParams * G)(*ps)
+        dev_arr = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(DEV)
+        check(lib().fb_dp_allreduce_step_emulated(C.c_void_p(dev_arr.data_ptr()), C.c_int32(G), C.c_int64(n),
+                                                  C.c_void_p(stream_ptr(torch.device(DEV)))), "dp emulated")
+        torch.cuda.synchronize()
+        gmean = torch.stack(grads).mean(0) + 0.01 * ref_w
+        ref_m = 0.9 * ref_m + gmean
+        ref_w = ref_w - 0.1 * ref_m
+        for r in range(G):
+            torch.testing.assert_close(params[r], ref_w, rtol=1e-5, atol=1e-5)
+        for r in range(1, G):
+            assert torch.equal(params[0], params[r])
