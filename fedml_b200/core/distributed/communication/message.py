@@ -134,6 +134,9 @@ def _jsonable(obj):
         return int(obj)
     if isinstance(obj, (np.floating,)):
         return float(obj)
+    if isinstance(obj, (bytes, bytearray)):
+        import base64
+        return {"__b64": base64.b64encode(bytes(obj)).decode()}
     return obj
 
 

@@ -23,8 +23,9 @@ import numpy as np
 
 
 def lpt_assign(workloads: Sequence[float], speeds: Sequence[float], memory: Sequence[float] = None,
-               ) -> List[List[int]]:
-    """Greedy LPT: biggest job first onto the resource whose finishing cost stays smallest."""
+               max_count: int = 0) -> List[List[int]]:
+    """Greedy LPT: biggest job first onto the resource whose finishing cost stays smallest.
+    ``max_count`` > 0 caps the number of jobs per resource (the client-batched executor sizes its stacks by it)."""
     x = np.asarray(workloads, dtype=np.float64)
     y = np.asarray(speeds, dtype=np.float64)
     order = np.argsort(-x, kind="stable")
@@ -33,6 +34,8 @@ def lpt_assign(workloads: Sequence[float], speeds: Sequence[float], memory: Sequ
     out: List[List[int]] = [[] for _ in y]
     for j in order:
         cost = load + y * x[j]
+        if max_count > 0:
+            cost = np.where(count >= max_count, np.inf, cost)
         # tie-break on job count so equal workloads spread evenly (keeps lockstep batches square)
         r = int(np.lexsort((count, cost))[0])
         out[r].append(int(j))
@@ -127,4 +130,5 @@ class scheduler:  # noqa: N801 - reference class name
 def schedule_clients(sample_counts: Sequence[int], n_gpus: int, speeds: Sequence[float] = None) -> List[List[int]]:
     """Round-path entry point: positions (0..K-1) of the sampled clients per GPU rank."""
     speeds = np.ones(n_gpus) if speeds is None else np.asarray(speeds, dtype=np.float64)
-    return lpt_assign(sample_counts, speeds)
+    cap = (len(sample_counts) + n_gpus - 1) // n_gpus
+    return lpt_assign(sample_counts, speeds, max_count=cap)

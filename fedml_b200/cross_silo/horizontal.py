@@ -158,6 +158,7 @@ class FedMLClientManager(ClientManager):
         self.events = MLOpsProfilerEvent.get_instance(args)
         self.mlops = MLOpsMetrics.get_instance(args)
         self.has_sent_online_msg = False
+        self._got_model = False
 
     def register_message_receive_handlers(self):
         self.register_message_receive_handler(MyMessage.MSG_TYPE_CONNECTION_IS_READY, self.handle_message_connection_ready)
@@ -170,6 +171,21 @@ class FedMLClientManager(ClientManager):
         if not self.has_sent_online_msg:
             self.has_sent_online_msg = True
             self.send_client_status(0)
+            # pub/sub transports drop messages published before the server has subscribed: repeat the ONLINE
+            # report until the first model arrives (the server de-duplicates by sender)
+            import threading
+
+            def again():
+                while not self._got_model and self.com_manager_status != "STOPPED":
+                    time.sleep(0.5)
+                    if not self._got_model:
+                        try:
+                            self.send_client_status(0)
+                        except Exception:  # noqa: BLE001 - transport already closed
+                            return
+
+            self._got_model = False
+            threading.Thread(target=again, daemon=True).start()
 
     def send_client_status(self, receive_id, status="ONLINE"):
         m = Message(MyMessage.MSG_TYPE_C2S_CLIENT_STATUS, self.rank, receive_id)
@@ -179,11 +195,13 @@ class FedMLClientManager(ClientManager):
 
     def handle_message_init(self, msg_params):
         self.round_idx = 0
+        self._got_model = True
         self.mlops.report_client_training_status(getattr(self.args, "edge_id", self.rank), "TRAINING")
         self._train_on(msg_params)
 
     def handle_message_receive_model_from_server(self, msg_params):
         self.round_idx += 1
+        self._got_model = True
         self._train_on(msg_params)
 
     def handle_message_finish(self, msg_params):

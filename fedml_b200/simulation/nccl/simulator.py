@@ -412,10 +412,16 @@ class NCCLSimulator:
 
     def _train_sequential(self, my_clients, round_idx):
         """Per-client eager training on arena-bound parameters (custom trainers / unbatched families)."""
+        int_segs = [sg for sg in self.layout.segments if sg.kind == "int_buffer"]
+        bufs = dict(self.seq_model.named_buffers())
         for pos, cid in enumerate(my_clients):
             self.seq_flat.copy_(self.global_flat)
+            for sg in int_segs:       # integer buffers (num_batches_tracked) are not views of the arena: sync by hand
+                bufs[sg.name].copy_(self.global_flat[sg.offset:sg.offset + sg.numel].view(sg.shape).round().to(sg.dtype))
             self.seq_trainer.set_id(cid)
             self.seq_trainer.train(self.train_local[cid], self.device, self.args)
+            for sg in int_segs:
+                self.seq_flat[sg.offset:sg.offset + sg.numel] = bufs[sg.name].reshape(-1).to(torch.float32)
             self.stack[pos].copy_(self.seq_flat)
 
     # ------------------------------------------------------------------ one round

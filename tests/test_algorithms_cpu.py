@@ -1,0 +1,259 @@
+"""CPU tests: simulators, algorithm zoo, the reference's two CI equivalence oracles, NCCL-simulator control flow."""
+import copy
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import fedml
+from fedml.simulation import SimulatorMPI, SimulatorNCCL, SimulatorSingleProcess
+from fedml_b200.arguments import Arguments
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPU = torch.device("cpu")
+
+
+def mk(**kw):
+    base = dict(dataset="mnist", model="lr", client_num_per_round=4, comm_round=3, batch_size=10, learning_rate=0.03,
+                frequency_of_the_test=2, synthetic_train_size=1500, mnist_client_num=12, log_level="WARNING", eval_client_cap=4,
+                simulation_timeout_s=120)
+    base.update(kw)
+    return fedml.init(Arguments.from_dict(base))
+
+
+def build(a):
+    ds, out = fedml.data.load(a)
+    return ds, fedml.model.create(a, out)
+
+
+def test_client_sampling_is_the_reference_rule():
+    from fedml_b200.simulation.sp.fedavg_api import client_sampling
+    np.random.seed(5)
+    ref = np.random.choice(range(1000), 10, replace=False).tolist()
+    assert client_sampling(5, 1000, 10) == ref
+    assert client_sampling(3, 7, 7) == list(range(7))
+
+
+def test_fedavg_full_batch_all_clients_equals_centralized():
+    """Reference CI oracle (ci/CI-script-fedavg.sh:42-47): full batch, 1 epoch, every client every round ==
+    centralized gradient descent on the union (LR is linear in the averaged gradient)."""
+    a = mk(batch_size=-1, client_num_per_round=12, comm_round=5, frequency_of_the_test=100)
+    ds, model = build(a)
+    fed_model = copy.deepcopy(model)
+    sim = SimulatorSingleProcess(a, CPU, ds, fed_model)
+    w_fed = sim.run()
+    fedds = a._federated_dataset
+    cen = copy.deepcopy(model)
+    opt = torch.optim.SGD(cen.parameters(), lr=0.03)
+    sizes = torch.tensor(fedds.client_sizes(), dtype=torch.float32)
+    for _ in range(5):          # one FedAvg round of full-batch clients == one step on the size-weighted mean of client losses
+        opt.zero_grad()
+        loss = sum(sizes[c] / sizes.sum() * torch.nn.functional.cross_entropy(cen(fedds.client_slice(c)[0]), fedds.client_slice(c)[1])
+                   for c in range(12))
+        loss.backward(); opt.step()
+    for k, v in cen.state_dict().items():
+        torch.testing.assert_close(w_fed[k], v, rtol=1e-4, atol=1e-5)
+
+
+def test_hierarchical_matches_flat_fedavg_oracle():
+    """Reference CI oracle (:50-58): (global, group) rounds = (2,5) and (5,2) land within 1e-3 of each other in train accuracy."""
+    accs = []
+    for g, q in ((2, 5), (5, 2)):
+        a = mk(federated_optimizer="HierarchicalFL", batch_size=-1, client_num_per_round=12, global_comm_round=g,
+               group_comm_round=q, group_num=1, frequency_of_the_test=100, learning_rate=0.03, eval_client_cap=12)
+        ds, model = build(a)
+        torch.manual_seed(0); [p.data.normal_(0, 0.01) for p in model.parameters()]
+        sim = SimulatorSingleProcess(a, CPU, ds, model); sim.run()
+        accs.append(sim.fl_trainer.history[-1]["train_acc"])
+    assert abs(accs[0] - accs[1]) < 1e-3
+
+
+@pytest.mark.parametrize("alg,extra", [("FedAvg", {}), ("FedOpt", {"server_optimizer": "adam", "server_lr": 0.01}),
+                                       ("FedProx", {"fedprox_mu": 0.1}), ("FedNova", {"momentum": 0.9}),
+                                       ("FedAvg_robust", {"defense_type": "median", "byzantine_fraction": 0.25}),
+                                       ("turbo_aggregate", {}), ("S_FedAvg", {}), ("HS_FedAvg", {"client_num_per_round": 3})])
+def test_sp_algorithms_run_and_learn(alg, extra):
+    a = mk(federated_optimizer=alg, **extra)
+    ds, model = build(a)
+    sim = SimulatorSingleProcess(a, CPU, ds, model)
+    sim.run()
+    h = sim.fl_trainer.history
+    assert len(h) >= 2 and np.isfinite(h[-1]["test_loss"]) and h[-1]["test_loss"] <= h[0]["test_loss"] + 0.05
+
+
+def test_fedprox_proximal_term_pulls_towards_global():
+    from fedml_b200.simulation.trainers import ModelTrainerCLS
+    a0, a1 = mk(epochs=3), mk(epochs=3, fedprox_mu=5.0, federated_optimizer="FedProx")
+    ds, model = build(a0)
+    w0 = copy.deepcopy(model.state_dict())
+    d = []
+    for a in (a0, a1):
+        m = copy.deepcopy(model); t = ModelTrainerCLS(m, a); t.train(ds[5][0], CPU, a)
+        d.append(sum(float((m.state_dict()[k] - w0[k]).norm()) for k in w0))
+    assert d[1] < d[0]
+
+
+def test_fednova_equals_fedavg_for_equal_steps_plain_sgd():
+    """tau_i identical and no momentum/prox => FedNova's normalised average reduces to FedAvg."""
+    res = []
+    for alg in ("FedAvg", "FedNova"):
+        a = mk(federated_optimizer=alg, batch_size=-1, comm_round=2)
+        ds, model = build(a)
+        torch.manual_seed(0); [p.data.normal_(0, 0.01) for p in model.parameters()]
+        res.append(SimulatorSingleProcess(a, CPU, ds, model).run())
+    for k in res[0]:
+        torch.testing.assert_close(res[0][k].float(), res[1][k].float(), rtol=1e-4, atol=1e-5)
+
+
+def test_decentralized_dsgd_and_pushsum_reach_consensus():
+    for kw in ({}, {"mode": "PUSHSUM", "b_symmetric": False}):
+        a = mk(federated_optimizer="decentralized_fl", client_num_in_total=8, iteration_number=150, **kw)
+        ds, model = build(a)
+        sim = SimulatorSingleProcess(a, CPU, ds, model); sim.run()
+        t = sim.fl_trainer
+        assert t.regret[-1] < t.regret[5] and t.consensus_distance() < 0.1
+
+
+def test_vertical_fl_sp_learns():
+    a = mk(federated_optimizer="classical_vertical", comm_round=3)
+    sim = SimulatorSingleProcess(a, CPU, None, None); sim.run()
+    assert sim.fl_trainer.history[-1]["test_acc"] > 0.8
+
+
+def test_nccl_simulator_cpu_path_matches_sp_fedavg():
+    """The multi-GPU simulator's control flow on CPU (batched clients, torch back-end) reproduces SP FedAvg."""
+    a = mk(batch_size=10, comm_round=2, frequency_of_the_test=100)
+    ds, model = build(a)
+    w_sp = SimulatorSingleProcess(a, CPU, ds, copy.deepcopy(model)).run()
+    a2 = copy.copy(a); a2.backend = "NCCL"
+    sim = SimulatorNCCL(a2, CPU, ds, copy.deepcopy(model)); w_nc = sim.run()
+    for k in w_sp:
+        torch.testing.assert_close(w_nc[k].float(), w_sp[k].float(), rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("alg,extra", [("FedOpt", {"server_optimizer": "yogi", "server_lr": 0.01}), ("FedProx", {}), ("FedNova", {"momentum": 0.5}),
+                                       ("FedAvg", {"robust_agg": "trimmed_mean", "byzantine_fraction": 0.25}),
+                                       ("FedAvg", {"robust_agg": "krum", "byzantine_fraction": 0.25, "krum_m": 2}),
+                                       ("FedAvg", {"dp_clip": 1.0, "dp_sigma": 0.001})])
+def test_nccl_simulator_algorithm_variants_cpu(alg, extra):
+    a = mk(federated_optimizer=alg, backend="NCCL", **extra)
+    ds, model = build(a)
+    sim = SimulatorNCCL(a, CPU, ds, model); sim.run()
+    h = sim.simulator.history
+    assert np.isfinite(h[-1]["test_loss"]) and h[-1]["test_acc"] >= 0.0
+
+
+def test_nccl_simulator_resnet_batched_cpu_and_sequential_fallback_agree():
+    kw = dict(dataset="cifar10", model="resnet56", client_num_in_total=4, client_num_per_round=2, synthetic_train_size=64,
+              batch_size=8, comm_round=1, frequency_of_the_test=100, backend="NCCL", shuffle_clients=False)
+    a = mk(**kw)
+    ds, out = fedml.data.load(a)
+    from fedml_b200.models.cv import Bottleneck, ResNet
+    model = ResNet(Bottleneck, [1, 1, 1], num_classes=10)
+    w_b = SimulatorNCCL(a, CPU, ds, copy.deepcopy(model)).run()
+    a2 = copy.copy(a); a2.batched_clients = False
+    w_s = SimulatorNCCL(a2, CPU, ds, copy.deepcopy(model)).run()
+    for k in w_b:
+        torch.testing.assert_close(w_b[k].float(), w_s[k].float(), rtol=5e-3, atol=5e-4, msg=lambda m, k=k: f"{k}: {m}")
+
+
+def test_nccl_simulator_two_ranks_gloo_is_g_invariant(tmp_path):
+    """world_size 2 over gloo on CPU == world_size 1 (same seeds => same sampled clients => same global model)."""
+    script = tmp_path / "w.py"
+    script.write_text(f"""
+import os, sys, json, torch
+sys.path.insert(0, {ROOT!r})
+import fedml
+from fedml_b200.arguments import Arguments
+a = fedml.init(Arguments.from_dict(dict(dataset="mnist", model="lr", client_num_per_round=6, comm_round=2, batch_size=10, learning_rate=0.03,
+    frequency_of_the_test=100, synthetic_train_size=1500, mnist_client_num=12, log_level="WARNING", backend="NCCL", federated_optimizer="FedOpt",
+    server_optimizer="adam", server_lr=0.01)))
+ds, out = fedml.data.load(a); torch.manual_seed(0); model = fedml.model.create(a, out)
+from fedml.simulation import SimulatorNCCL
+w = SimulatorNCCL(a, torch.device("cpu"), ds, model).run()
+if int(os.environ.get("RANK", "0")) == 0:
+    torch.save(w, sys.argv[1])
+""")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    one, two = str(tmp_path / "one.pt"), str(tmp_path / "two.pt")
+    subprocess.run([sys.executable, str(script), one], check=True, timeout=300, env=env)
+    subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                    "--master-port", "29721", str(script), two], check=True, timeout=300, env=env)
+    w1, w2 = torch.load(one), torch.load(two)
+    for k in w1:
+        torch.testing.assert_close(w1[k], w2[k], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("alg,kw", [("FedAvg", {}), ("FedOpt", {"server_optimizer": "sgd", "server_lr": 1.0}), ("turbo_aggregate", {}),
+                                    ("base_framework", {}), ("decentralized_fl", {"worker_num": 4, "comm_round": 4}),
+                                    ("classical_vertical", {"worker_num": 2}), ("FedGAN", {"model": "gan"})])
+def test_mp_simulator_algorithms_threaded(alg, kw):
+    a = mk(federated_optimizer=alg, backend="MPI", worker_num=kw.pop("worker_num", 3), client_num_per_round=3, comm_round=kw.pop("comm_round", 2),
+           run_id=f"mp-{alg}", ci=1, frequency_of_the_test=1, **kw)
+    ds, model = build(a)
+    r = SimulatorMPI(a, CPU, ds, model).run()
+    assert r is not None and len(r.history) >= 1
+
+
+def test_mp_fedavg_equals_sp_fedavg():
+    a = mk(comm_round=2, client_num_per_round=3, frequency_of_the_test=100)
+    ds, model = build(a)
+    w_sp = SimulatorSingleProcess(a, CPU, ds, copy.deepcopy(model)).run()
+    a2 = copy.copy(a); a2.backend, a2.worker_num, a2.run_id, a2.ci = "MPI", 3, "mp-eq", 1
+    agg = SimulatorMPI(a2, CPU, ds, copy.deepcopy(model)).run()
+    w_mp = agg.get_global_model_params()
+    for k in w_sp:
+        torch.testing.assert_close(w_mp[k].float(), w_sp[k].float(), rtol=1e-5, atol=1e-6)
+
+
+def test_split_nn_fedgkt_fednas_fedseg_smoke():
+    import torch.nn as nn
+    mlp = nn.Sequential(nn.Linear(784, 32), nn.ReLU(), nn.Linear(32, 10))
+    a = mk(federated_optimizer="split_nn", backend="MPI", worker_num=2, client_num_per_round=2, epochs=1, split_cut=2, run_id="sn")
+    ds, _ = build(a)
+    r = SimulatorMPI(a, CPU, ds, mlp).run()
+    assert len(r.history) == 2
+    for alg, kw in (("FedGKT", dict(dataset="cifar10", checkpoint_dir="/tmp/fb_gkt_t")), ("FedNAS", dict(dataset="cifar10", layers=2)),
+                    ("FedSeg", dict(dataset="pascal_voc", model="segnet"))):
+        a = mk(federated_optimizer=alg, backend="MPI", worker_num=2, client_num_per_round=2, client_num_in_total=2, comm_round=1,
+               synthetic_train_size=32, batch_size=8, run_id=alg, ci=1, frequency_of_the_test=1, **kw)
+        ds, model = build(a)
+        r = SimulatorMPI(a, CPU, ds, model).run()
+        assert len(r.history) >= 1
+    assert os.path.exists("/tmp/fb_gkt_t/last.pth") and "state_dict" in torch.load("/tmp/fb_gkt_t/last.pth", weights_only=False)
+
+
+def test_fedml_runner_and_one_line_api(tmp_path):
+    y = tmp_path / "fedml_config.yaml"
+    y.write_text(open(os.path.join(ROOT, "fedml_b200/config/simulation_sp/fedml_config.yaml")).read()
+                 .replace("comm_round: 200", "comm_round: 2").replace("client_num_in_total: 1000", "client_num_in_total: 1000\n  synthetic_train_size: 1500\n  mnist_client_num: 12\n  eval_client_cap: 2"))
+    w = fedml.run_simulation(argv=["--cf", str(y)])
+    assert "linear.weight" in w
+    a = mk()
+    ds, model = build(a)
+    assert "linear.weight" in fedml.FedMLRunner(a, CPU, ds, model).run()
+
+
+def test_custom_client_trainer_and_server_aggregator_hooks():
+    from fedml import ClientTrainer, ServerAggregator
+    calls = {"train": 0, "agg": 0}
+
+    class T(ClientTrainer):
+        def get_model_params(self): return {k: v.clone() for k, v in self.model.state_dict().items()}
+        def set_model_params(self, p): self.model.load_state_dict(p)
+        def train(self, d, dev, args): calls["train"] += 1
+        def test(self, d, dev, args): return {"test_correct": 1, "test_loss": 0.0, "test_total": 1}
+
+    class S(ServerAggregator):
+        def get_model_params(self): return self.model.state_dict()
+        def set_model_params(self, p): self.model.load_state_dict(p)
+        def test(self, d, dev, args): return {}
+        def aggregate(self, lst): calls["agg"] += 1; return super().aggregate(lst)
+
+    a = mk(comm_round=2)
+    ds, model = build(a)
+    fedml.FedMLRunner(a, CPU, ds, model, client_trainer=T(model, a), server_aggregator=S(model, a)).run()
+    assert calls["train"] == 8 and calls["agg"] == 2

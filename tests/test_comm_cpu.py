@@ -1,0 +1,266 @@
+"""CPU tests: transports, managers, cross-silo / cross-device over every backend, secure aggregation, MLOps, CLI."""
+import json
+import os
+import shutil
+import threading
+import time
+
+import numpy as np
+import pytest
+import torch
+
+import fedml
+from fedml_b200.arguments import Arguments
+from fedml_b200.core.distributed.communication import create_comm_manager
+from fedml_b200.core.distributed.communication.broker import BrokerClient, LocalBroker
+from fedml_b200.core.distributed.communication.inproc import InProcHub
+from fedml_b200.core.distributed.communication.message import Message
+from fedml_b200.core.distributed.communication.observer import Observer
+
+PORT = [53000]
+
+
+def next_port(n=10):
+    PORT[0] += n
+    return PORT[0]
+
+
+@pytest.fixture(scope="module")
+def broker():
+    b = LocalBroker()
+    port = b.start()
+    yield port
+    b.stop()
+
+
+class _Collect(Observer):
+    def __init__(self):
+        self.got = []
+        self.ev = threading.Event()
+
+    def receive_message(self, t, p):
+        self.got.append((t, p))
+        if t == 9:
+            self.ev.set()
+
+
+@pytest.mark.parametrize("backend", ["INPROC", "TCP", "GRPC", "MQTT", "MQTT_S3"])
+def test_transport_roundtrip_with_tensor_payload(backend, broker, tmp_path):
+    args = Arguments.from_dict(dict(run_id=f"rt-{backend}", tcp_base_port=next_port(), grpc_base_port=next_port(), mqtt_port=broker,
+                                    object_store_dir=str(tmp_path / "store"), client_id_list="[1]"))
+    InProcHub.reset(args.run_id)
+    server = create_comm_manager(args, 0, 2, backend)
+    client = create_comm_manager(args, 1, 2, backend)
+    cs, cc = _Collect(), _Collect()
+    server.add_observer(cs); client.add_observer(cc)
+    ts = [threading.Thread(target=m.handle_receive_message, daemon=True) for m in (server, client)]
+    [t.start() for t in ts]
+    payload = {"w": torch.arange(12, dtype=torch.float32).view(3, 4), "n": torch.tensor(3)}
+    m = Message(9, 1, 0); m.add_params("model_params", payload); m.add_params("num_samples", 17)
+    client.send_message(m)
+    assert cs.ev.wait(20)
+    t, p = [g for g in cs.got if g[0] == 9][0]
+    assert p["num_samples"] == 17 and torch.equal(torch.as_tensor(p["model_params"]["w"]).float(), payload["w"])
+    back = Message(9, 0, 1); back.add_params("model_params", payload)
+    server.send_message(back)
+    assert cc.ev.wait(20)
+    server.stop_receive_message(); client.stop_receive_message()
+
+
+def test_broker_last_will_and_status_manager(broker):
+    from fedml_b200.core.distributed.communication.mqtt_backends import MqttS3StatusManager
+    got = []
+    watcher = BrokerClient("127.0.0.1", broker); watcher.on_message = lambda t, p: got.append((t, json.loads(p))); watcher.subscribe("W/topic")
+    dying = BrokerClient("127.0.0.1", broker, will_topic="W/topic", will_payload={"ID": 7, "stat": "Offline"})
+    dying._sock.shutdown(2)                      # abrupt death, no "bye"
+    deadline = time.time() + 5
+    while not got and time.time() < deadline:
+        time.sleep(0.02)
+    assert got and got[0][1]["ID"] == 7
+    sm = MqttS3StatusManager(Arguments.from_dict(dict(mqtt_port=broker)))
+    seen = []
+    class O:
+        def receive_message(self, t, p): seen.append((t, p))
+    sm.add_observer(O()); sm.subscribe("fl_client/mlops/status"); sm.send_message_json("fl_client/mlops/status", {"edge_id": 1, "status": "TRAINING"})
+    deadline = time.time() + 5
+    while not seen and time.time() < deadline:
+        time.sleep(0.02)
+    assert seen and json.loads(seen[0][1])["status"] == "TRAINING"
+    sm.stop()
+
+
+def _run_cross_silo(backend, broker, tmp_path, **kw):
+    base = dict(training_type="cross_silo", dataset="mnist", model="lr", client_num_in_total=2, client_num_per_round=2, client_id_list="[1, 2]",
+                comm_round=2, batch_size=10, learning_rate=0.03, frequency_of_the_test=1, synthetic_train_size=1200, mnist_client_num=2,
+                backend=backend, mqtt_port=broker, log_level="WARNING", run_id=f"cs-{backend}-{kw.get('tag', '')}", grpc_base_port=next_port(),
+                tcp_base_port=next_port(), object_store_dir=str(tmp_path / "store"), using_mlops=True,
+                global_model_file_path=str(tmp_path / "global_model.pt"))
+    base.update(kw)
+    InProcHub.reset(base["run_id"])
+    res, errs = {}, []
+
+    def role(rank):
+        try:
+            a = fedml.init(Arguments.from_dict(dict(base, rank=rank)))
+            ds, out = fedml.data.load_cross_silo(a)
+            torch.manual_seed(0)
+            model = fedml.model.create(a, out)
+            res[rank] = (fedml.cross_silo.Server if rank == 0 else fedml.cross_silo.Client)(a, torch.device("cpu"), ds, model).run()
+        except BaseException as exc:  # noqa: BLE001
+            errs.append(exc); raise
+
+    ranks = kw.get("ranks", (0, 1, 2))
+    ts = [threading.Thread(target=role, args=(r,), daemon=True) for r in ranks]
+    [t.start() for t in ts]
+    [t.join(90) for t in ts]
+    assert not errs, errs
+    return res
+
+
+@pytest.mark.parametrize("backend", ["INPROC", "TCP", "GRPC", "MQTT_S3"])
+def test_cross_silo_horizontal_handshake_and_rounds(backend, broker, tmp_path):
+    res = _run_cross_silo(backend, broker, tmp_path)
+    h = res[0].history
+    assert len(h) == 2 and np.isfinite(h[-1]["test_loss"])
+    sd = torch.load(str(tmp_path / "global_model.pt"), weights_only=False)      # reference checkpoint format
+    assert list(sd.keys()) == ["linear.weight", "linear.bias"]
+
+
+def test_cross_silo_backends_agree(broker, tmp_path):
+    a = _run_cross_silo("INPROC", broker, tmp_path, tag="a")[0].get_global_model_params()
+    b = _run_cross_silo("MQTT_S3", broker, tmp_path, tag="b")[0].get_global_model_params()
+    for k in a:
+        torch.testing.assert_close(a[k], b[k])
+
+
+def test_round_deadline_partial_aggregation(broker, tmp_path):
+    """A silo that never answers: the server aggregates what arrived after the deadline with re-normalised weights
+    (the reference waits forever)."""
+    from fedml_b200.cross_silo.horizontal import FedMLClientManager
+
+    orig = FedMLClientManager._train_on
+
+    def lazy(self, msg_params):
+        if self.rank == 2:
+            return                      # dead client: online, but never uploads
+        return orig(self, msg_params)
+
+    FedMLClientManager._train_on = lazy
+    try:
+        t0 = time.time()
+        res = _run_cross_silo("INPROC", broker, tmp_path, tag="dl", round_deadline_s=1.0, comm_round=1)
+        assert len(res[0].history) == 1 and time.time() - t0 < 60
+    finally:
+        FedMLClientManager._train_on = orig
+
+
+def test_cross_device_server_with_file_models(broker, tmp_path):
+    from fedml_b200.cross_device.mnn_file import read_mnn_as_tensor_dict, read_mnn_like, write_mnn_like
+    base = dict(training_type="cross_device", dataset="mnist", model="lenet", client_num_in_total=2, client_num_per_round=2, client_id_list="[1, 2]",
+                comm_round=2, batch_size=10, synthetic_train_size=300, mnist_client_num=2, backend="MQTT_S3_MNN", mqtt_port=broker, log_level="WARNING",
+                run_id="cd-t", object_store_dir=str(tmp_path / "store"), model_file_cache_folder=str(tmp_path / "cache"),
+                global_model_file_path=str(tmp_path / "global.mnn"))
+    args = fedml.init(Arguments.from_dict(base))
+    ds, out = fedml.data.load(args)
+    model = fedml.model.create(args, out)
+    fedml.model.create_mnn_lenet5_model(str(tmp_path / "lenet.mnn"))
+    assert len(read_mnn_as_tensor_dict(str(tmp_path / "lenet.mnn"))) == len(model.state_dict())
+    srv = fedml.cross_device.ServerMNN(args, torch.device("cpu"), ds[3], model)
+
+    class Phone(Observer):
+        def __init__(s, rank):
+            a = Arguments.from_dict(dict(base, rank=rank)); a.model_file_cache_folder = str(tmp_path / f"phone{rank}")
+            s.rank, s.cm = rank, create_comm_manager(a, rank, 3, "MQTT_S3_MNN"); s.cm.add_observer(s)
+
+        def receive_message(s, t, p):
+            if t in (1, 2):
+                sd = {k: v + 0.01 * s.rank for k, v in read_mnn_like(p["model_params"]).items()}
+                path = str(tmp_path / f"phone{s.rank}" / "up.mnn"); write_mnn_like(path, sd)
+                m = Message(3, s.rank, 0); m.add_params("model_params", path); m.add_params("num_samples", 10 * s.rank); s.cm.send_message(m)
+            elif t == 6:
+                s.cm.stop_receive_message()
+
+    phones = [Phone(1), Phone(2)]
+    [threading.Thread(target=p.cm.handle_receive_message, daemon=True).start() for p in phones]
+    init = {k: v.clone() for k, v in model.state_dict().items()}
+    agg = srv.run()
+    assert len(agg.history) == 2
+    final = read_mnn_like(str(tmp_path / "global.mnn"))
+    # two rounds of (+0.01*1 weighted 10, +0.01*2 weighted 20) => +2 * 0.01 * 5/3
+    k = "fc2.bias"
+    torch.testing.assert_close(final[k], init[k] + 2 * 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)
+
+
+def test_mpc_toolbox_and_secure_aggregation():
+    from fedml_b200.core.security import mpc_function as M
+    from fedml_b200.core.security.secagg import prg_mask, secure_weighted_mean
+    p = M.DEFAULT_PRIME
+    assert M.modular_inv(12345, p) * 12345 % p == 1 and M.divmod(10, 5, p) == 2
+    rs = np.random.RandomState(0)
+    X = rs.randint(0, p, size=(4, 5))
+    sh = M.BGW_encoding(X, 7, 2, p, rs)
+    assert np.array_equal(M.BGW_decoding(sh[[1, 3, 6]], [1, 3, 6], p)[0], X % p)
+    assert not np.array_equal(sh[0], X % p)                                       # a single share reveals nothing useful
+    Xl = rs.randint(0, p, size=(6, 3))
+    enc = M.LCC_encoding(Xl, 8, 2, 0, p, rs)
+    assert np.array_equal(M.LCC_decoding(enc[[0, 2]], 1, 8, 2, 0, [0, 2], p).reshape(6, 3), Xl % p)
+    pts_a, pts_b = [1, 2, 3], [4, 5, 6, 7]
+    e2 = M.LCC_encoding_with_points(Xl[:3], pts_a, pts_b, p)
+    assert np.array_equal(M.LCC_decoding_with_points(e2[:3], pts_b[:3], pts_a, p), Xl[:3] % p)
+    assert np.all(M.Gen_Additive_SS(10, 4, p, rs).sum(0) % p == 0)
+    sk1, sk2 = 1234567, 7654321
+    assert M.my_key_agreement(sk1, M.my_pk_gen(sk2, p, 7), p, 7) == M.my_key_agreement(sk2, M.my_pk_gen(sk1, p, 7), p, 7)
+    assert np.array_equal(prg_mask(99, 1001, p), prg_mask(99, 1001, p)) and prg_mask(99, 8, p).max() < p
+    ups = [torch.randn(500) for _ in range(5)]
+    w = [3.0, 1.0, 2.0, 5.0, 4.0]
+    ref = sum(wi * u for wi, u in zip(w, ups)) / sum(w)
+    assert float((secure_weighted_mean(ups, w) - ref).abs().max()) < 1e-3
+    alive = [0, 1, 3, 4]
+    ref2 = sum(w[i] * ups[i] for i in alive) / sum(w[i] for i in alive)
+    assert float((secure_weighted_mean(ups, w, dropped=[2]) - ref2).abs().max()) < 1e-3
+
+
+def test_mlops_events_metrics_and_sysstats():
+    from fedml_b200.core.mlops import MLOpsMetrics, MLOpsProfilerEvent, SysStats
+    a = Arguments.from_dict(dict(using_mlops=True, run_id=5, edge_id=3))
+    ev = MLOpsProfilerEvent.get_instance(a)
+    ev.log_event_started("train", "0"); ev.log_event_ended("train", "0")
+    sent = ev.messenger.sent
+    assert [t for t, _ in sent] == ["/mlops/events"] * 2
+    first, last = json.loads(sent[0][1]), json.loads(sent[1][1])
+    assert first["event_name"] == "train" and "started_time" in first and "ended_time" in last and first["run_id"] == 5
+    mm = MLOpsMetrics.get_instance(a)
+    assert mm.report_client_training_status(3, "TRAINING")[0] == "fl_client/mlops/3/status"
+    assert mm.report_server_training_metric({"accuracy": 0.5})[0] == "fl_server/mlops/training_progress_and_eval"
+    assert "timestamp" in SysStats().produce_info(5, 3)
+
+
+def test_cli_version_build_and_package_materialisation(tmp_path):
+    from click.testing import CliRunner
+    from fedml_b200.cli.cli import cli, materialise_package
+    r = CliRunner().invoke(cli, ["version"])
+    assert r.exit_code == 0 and "fedml version" in r.output
+    src, cfg, out = tmp_path / "src", tmp_path / "cfg", tmp_path / "out"
+    src.mkdir(); cfg.mkdir()
+    (src / "main.py").write_text("print('client entry')\n")
+    (cfg / "fedml_config.yaml").write_text("train_args:\n  client_num_in_total: 1\n  run_id: x\ncomm_args:\n  backend: MQTT_S3\n")
+    r = CliRunner().invoke(cli, ["build", "-t", "client", "-sf", str(src), "-ep", "main.py", "-cf", str(cfg), "-df", str(out)])
+    assert r.exit_code == 0, r.output
+    z = out / "dist-packages" / "client-package.zip"
+    assert z.exists()
+    entry, conf, dyn = materialise_package(str(z), str(tmp_path / "work"), {"RUN_ID": 42, "CLIENT_INDEX": 2, "CLIENT_ID_LIST": "[7, 8]",
+                                                                             "CLIENT_NUM": 2, "MQTT_CONFIG_PATH": "", "S3_CONFIG_PATH": "",
+                                                                             "LOG_FILE_DIR": "/tmp"})
+    import yaml
+    user = yaml.safe_load(open(conf))
+    assert os.path.exists(entry) and str(dyn["rank"]) == "2" and str(user["train_args"]["client_num_in_total"]) == "2"
+    assert str(user["train_args"]["run_id"]) == "42"
+
+
+def test_hs_fft_matches_numpy_oracle():
+    from fedml_b200.simulation.sp.hs_fft import amplitude_normalize, amplitude_normalize_numpy
+    x = torch.rand(4, 3, 16, 16)
+    run = torch.rand(3, 16, 16)
+    a, b, c = amplitude_normalize(x, run)
+    a2, b2, c2 = amplitude_normalize_numpy(x.numpy(), run.numpy())
+    assert np.abs(a.numpy() - a2).max() < 1e-4 and np.abs(b.numpy() - b2).max() < 1e-4

@@ -1,0 +1,250 @@
+"""CPU tests: config, data contract, model zoo, partitioners, topology, scheduler, aggregation oracles, codec."""
+import copy
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import fedml
+from fedml_b200.arguments import Arguments, SCHEMA, load_arguments, substitute_fedsys_vars
+from fedml_b200.core import aggregation as A
+
+
+def mk(**kw):
+    base = dict(dataset="mnist", model="lr", client_num_per_round=4, comm_round=2, batch_size=10, learning_rate=0.03,
+                frequency_of_the_test=1, synthetic_train_size=1500, mnist_client_num=12, log_level="WARNING")
+    base.update(kw)
+    return fedml.init(Arguments.from_dict(base))
+
+
+def test_arguments_yaml_flattening_and_defaults(tmp_path):
+    y = tmp_path / "c.yaml"
+    y.write_text("common_args:\n  training_type: simulation\n  random_seed: 3\ntrain_args:\n  comm_round: '7'\n  my_custom_key: [1, 2]\n"
+                 "comm_args:\n  backend: single_process\n")
+    a = load_arguments(argv=["--cf", str(y), "--rank", "2", "--run_id", "abc"])
+    assert a.random_seed == 3 and a.comm_round == 7 and a.my_custom_key == [1, 2] and a.rank == 2 and a.run_id == "abc"
+    assert a.client_optimizer == SCHEMA["client_optimizer"][1]           # default filled in
+    d = load_arguments("simulation", "single_process", argv=[])
+    assert d.dataset == "mnist" and d.model == "lr" and d.client_num_per_round == 10   # packaged default yaml
+    assert substitute_fedsys_vars("run ${FEDSYS.RUN_ID}", {"RUN_ID": 9}) == "run 9"
+
+
+def test_hierarchical_overlay_yaml(tmp_path):
+    (tmp_path / "server.yaml").write_text("x:\n  extra_key: server\n")
+    (tmp_path / "silo1.yaml").write_text("x:\n  extra_key: silo1\n  n_proc_in_silo: 2\n")
+    main = tmp_path / "m.yaml"
+    main.write_text("common_args:\n  training_type: cross_silo\n  scenario: hierarchical\n"
+                    f"  server_config_path: {tmp_path}/server.yaml\n  client_silo_config_paths: [{tmp_path}/silo1.yaml]\n")
+    a0 = load_arguments("cross_silo", None, argv=["--cf", str(main), "--rank", "0"])
+    a1 = load_arguments("cross_silo", None, argv=["--cf", str(main), "--rank", "1"])
+    assert a0.extra_key == "server" and a1.extra_key == "silo1" and a1.n_proc_in_silo == 2
+
+
+def test_data_contract_and_shapes():
+    a = mk()
+    ds, ncls = fedml.data.load(a)
+    assert len(ds) == 8 and ncls == 10 and a.client_num_in_total == 12         # natural partition overrides the count
+    train_num, test_num, tg, teg, nums, tl, tel, c = ds
+    assert sum(nums.values()) == train_num
+    x, y = tl[3][0]
+    assert x.shape[1:] == (784,) and x.dtype == torch.float32 and y.dtype == torch.int64 and x.shape[0] <= 10
+    assert len(set(torch.cat([b[1] for b in tl[3]]).tolist())) <= 2              # two digits per device
+    a2 = mk(dataset="cifar10", model="resnet56", client_num_in_total=7, partition_method="hetero", partition_alpha=0.5,
+            synthetic_train_size=700)
+    ds2, n2 = fedml.data.load(a2)
+    xb, yb = ds2[5][0][0]
+    assert xb.shape == (10, 3, 32, 32) and xb.dtype == torch.float32 and len(ds2[5]) == 7
+    assert abs(float(xb.mean())) < 3.0
+    fed = a2._federated_dataset
+    assert fed.x.dtype == torch.uint8 and fed.client_sizes().sum() == 700 and fed.test_offsets is None
+
+
+def test_centralized_and_full_batch_switches():
+    a = mk(client_num_in_total=1)
+    ds, _ = fedml.data.load(a)
+    assert list(ds[5].keys()) == [0] and a.client_num_in_total == 1
+    from fedml_b200.data import combine_batches
+    merged = combine_batches(ds[5][0])
+    assert len(merged) == 1 and merged[0][0].shape[0] == ds[4][0]
+
+
+@pytest.mark.parametrize("name,dataset,params,entries", [
+    ("lr", "mnist", 7850, 2), ("cnn", "femnist", 1206590, 8), ("resnet56", "cifar10", 591322, 350),
+    ("rnn", "shakespeare", 822570, 11), ("rnn", "stackoverflow_nwp", 4053428, 9)])
+def test_model_zoo_sizes_match_reference(name, dataset, params, entries):
+    out = {"mnist": 10, "femnist": 62, "cifar10": 10, "shakespeare": 90, "stackoverflow_nwp": 10004}[dataset]
+    m = fedml.model.create(Arguments.from_dict(dict(model=name, dataset=dataset)), out)
+    assert sum(p.numel() for p in m.parameters()) == params and len(m.state_dict()) == entries
+
+
+def test_resnet_state_dict_keys_are_reference_names_and_distilbert_size():
+    sd = fedml.model.create(Arguments.from_dict(dict(model="resnet56", dataset="cifar10")), 10).state_dict()
+    for k in ("conv1.weight", "bn1.running_mean", "layer1.0.conv1.weight", "layer1.0.downsample.0.weight",
+              "layer3.5.bn3.num_batches_tracked", "fc.bias"):
+        assert k in sd
+    assert sd["bn1.num_batches_tracked"].dtype == torch.int64
+    r18 = fedml.model.create(Arguments.from_dict(dict(model="resnet18", dataset="imagenet")), 10)
+    assert sum(p.numel() for p in r18.parameters()) == 11181642 and len(r18.state_dict()) == 122
+    from fedml_b200.models import distilbert
+    d = distilbert(20)
+    assert sum(p.numel() for p in d.parameters()) == 66968852 and len(d.state_dict()) == 104
+    assert "distilbert.transformer.layer.5.ffn.lin2.weight" in d.state_dict()
+
+
+def test_lr_keeps_sigmoid_before_cross_entropy():
+    m = fedml.model.create(Arguments.from_dict(dict(model="lr", dataset="mnist")), 10)
+    out = m(torch.randn(4, 784) * 100)
+    assert float(out.min()) >= 0 and float(out.max()) <= 1
+
+
+def test_dirichlet_partition_matches_reference_procedure():
+    from fedml_b200.core.non_iid_partition import non_iid_partition_with_dirichlet_distribution, record_data_stats
+    labels = np.random.RandomState(0).randint(0, 10, 5000)
+    np.random.seed(10)
+    part = non_iid_partition_with_dirichlet_distribution(labels, 8, 10, 0.5)
+    sizes = [len(v) for v in part.values()]
+    assert sum(sizes) == 5000 and min(sizes) >= 10 and len(set(sum(map(list, part.values()), []))) == 5000
+    np.random.seed(10)
+    again = non_iid_partition_with_dirichlet_distribution(labels, 8, 10, 0.5)
+    assert all(list(part[i]) == list(again[i]) for i in range(8))               # same seed, same split
+    stats = record_data_stats(labels, part)
+    assert sum(sum(s.values()) for s in stats.values()) == 5000
+
+
+def test_topology_managers_row_stochastic_without_networkx():
+    from fedml_b200.core.distributed.topology import AsymmetricTopologyManager, SymmetricTopologyManager
+    t = SymmetricTopologyManager(8, 4); t.generate_topology()
+    W = np.asarray(t.topology)
+    assert np.allclose(W.sum(1), 1) and np.allclose(W, W.T) is not None and (np.diag(W) > 0).all()
+    assert sorted(t.get_in_neighbor_idx_list(0)) == [1, 2, 6, 7]
+    np.random.seed(0)
+    a = AsymmetricTopologyManager(8, 2, 2); a.generate_topology()
+    assert np.allclose(np.asarray(a.topology).sum(1), 1)
+    assert set(a.get_out_neighbor_idx_list(3)) >= {2, 4}
+
+
+def test_scheduler_reference_example_and_lpt():
+    from fedml_b200.core.schedule import scheduler, schedule_clients
+    s = scheduler(np.array([1, 2, 3, 5, 7, 14]), np.array([1, 5]), np.array([15, 100]))
+    plan = s.DP_schedule(1)
+    assigned = sorted(j for res in plan for bunch in res.values() for j in bunch)
+    assert assigned == [0, 1, 2, 3, 4, 5]
+    big = scheduler(np.arange(1, 101), np.ones(8), np.full(8, 1e9))            # reference recursion would blow the stack
+    plan = big.DP_schedule(0)
+    loads = [sum(np.arange(1, 101)[j] for b in res.values() for j in b) for res in plan]
+    assert max(loads) - min(loads) <= 100 and sum(loads) == 5050
+    groups = schedule_clients([50] * 100, 8)
+    assert sorted(len(g) for g in groups) == [12, 12, 12, 12, 13, 13, 13, 13]
+
+
+def _sd(seed, bn=True):
+    torch.manual_seed(seed)
+    net = torch.nn.Sequential(torch.nn.Linear(6, 4), torch.nn.BatchNorm1d(4) if bn else torch.nn.Identity())
+    sd = net.state_dict()
+    if bn:
+        sd["1.num_batches_tracked"] = torch.tensor(seed + 1)
+        sd["1.running_mean"] = torch.randn(4)
+    return sd
+
+
+def test_fedavg_aggregate_weights_every_entry_including_int_counters():
+    locs = [(10, _sd(0)), (30, _sd(1))]
+    agg = A.fedavg_aggregate(locs)
+    for k in locs[0][1]:
+        ref = (10 * locs[0][1][k].float() + 30 * locs[1][1][k].float()) / 40
+        torch.testing.assert_close(agg[k].float(), ref)
+    back = A.cast_like(agg, locs[0][1])
+    assert back["1.num_batches_tracked"].dtype == torch.int64
+
+
+@pytest.mark.parametrize("name", ["sgd", "adam", "adagrad"])
+def test_server_optimizer_matches_torch_optim(name):
+    torch.manual_seed(0)
+    w = {"p": torch.randn(20)}
+    opt = A.ServerOptimizer(name, lr=0.1, momentum=0.9 if name == "sgd" else 0.0, beta1=0.9, beta2=0.99, eps=1e-3)
+    p = torch.nn.Parameter(w["p"].clone())
+    topt = {"sgd": lambda: torch.optim.SGD([p], lr=0.1, momentum=0.9), "adam": lambda: torch.optim.Adam([p], lr=0.1, betas=(0.9, 0.99), eps=1e-3),
+            "adagrad": lambda: torch.optim.Adagrad([p], lr=0.1, eps=1e-3)}[name]()
+    for _ in range(3):
+        avg = {"p": w["p"] - 0.1 * torch.randn(20)}
+        p.grad = (p.detach() - avg["p"]).clone()             # pseudo-gradient of the reference (fedopt_api.py:173-186)
+        topt.step()
+        w = opt.step(w, avg, ["p"])
+        torch.testing.assert_close(w["p"], p.detach(), rtol=1e-5, atol=1e-6)
+
+
+def test_robust_aggregators_clip_median_trimmed_krum():
+    g = _sd(0, bn=False)
+    honest = [(10, {k: v + 0.01 * torch.randn_like(v) for k, v in g.items()}) for _ in range(8)]
+    bad = [(10, {k: v + 50.0 for k, v in g.items()}) for _ in range(2)]
+    allc = bad + honest
+    clipped = A.norm_diff_clip(bad[0][1], g, 1.0)
+    assert abs(float(torch.linalg.vector_norm(A.vectorize_weight(clipped) - A.vectorize_weight(g))) - 1.0) < 1e-4
+    for agg in (A.coordinate_median(allc), A.trimmed_mean(allc, 0.2), A.krum(allc, f=2, m=1), A.krum(allc, f=2, m=4)):
+        assert float((A.vectorize_weight(agg) - A.vectorize_weight(g)).abs().max()) < 0.1
+    assert float((A.vectorize_weight(A.fedavg_aggregate(allc)) - A.vectorize_weight(g)).abs().max()) > 5   # plain mean is poisoned
+    even = [(1, {"w": torch.tensor([float(i)])}) for i in (1, 2, 3, 4)]
+    assert float(A.coordinate_median(even)["w"]) == 2.0            # lower median, like torch.median
+    from fedml_b200.core.robustness import RobustAggregator
+    ra = RobustAggregator(Arguments.from_dict(dict(defense_type="weak_dp", norm_bound=1.0, stddev=0.0)))
+    out = ra.defend(allc, g)
+    assert float((A.vectorize_weight(out) - A.vectorize_weight(g)).abs().max()) < 1.0
+
+
+def test_message_binary_codec_and_json():
+    from fedml_b200.core.distributed.communication.message import Message
+    m = Message(3, 1, 0)
+    m.add_params("model_params", {"a": torch.randn(3, 4), "n": torch.tensor(7), "h": torch.randn(2).to(torch.bfloat16)})
+    m.add_params("arr", np.arange(5)); m.add_params("nested", [1, (2, 3), {"k": b"raw"}])
+    m2 = Message.from_bytes(m.to_bytes())
+    assert m2.get_type() == 3 and m2.get_sender_id() == 1
+    assert torch.equal(m2.get("model_params")["a"], m.get("model_params")["a"]) and m2.get("model_params")["h"].dtype == torch.bfloat16
+    assert list(m2.get("arr")) == [0, 1, 2, 3, 4] and m2.get("nested")[1] == (2, 3) and m2.get("nested")[2]["k"] == b"raw"
+    m3 = Message(); m3.init_from_json_string(m.to_json())
+    assert m3.get("model_params")["a"][0][0] == pytest.approx(float(m.get("model_params")["a"][0, 0]))
+
+
+def test_arena_roundtrip_and_layout_regions():
+    from fedml_b200.parallel.arena import ArenaLayout, bind_module_to_flat
+    m = fedml.model.create(Arguments.from_dict(dict(model="resnet56", dataset="cifar10")), 10)
+    lay = ArenaLayout(m)
+    assert lay.P % 4 == 0 and lay.P_train % 4 == 0 and lay.P_train >= 591322
+    flat = lay.flatten(m.state_dict())
+    sd = lay.unflatten(flat)
+    for k, v in m.state_dict().items():
+        assert torch.equal(sd[k], v) and sd[k].dtype == v.dtype
+    names = [s.name for s in lay.segments if s.offset < lay.P_train]
+    assert all(A.is_weight_param(n) for n in names)
+    small = torch.nn.Sequential(torch.nn.Linear(5, 3), torch.nn.BatchNorm1d(3))
+    lay2 = ArenaLayout(small); f2 = torch.zeros(lay2.P); g2 = torch.zeros(lay2.P)
+    bind_module_to_flat(small, lay2, f2, g2)
+    small(torch.randn(4, 5)).sum().backward()
+    assert float(g2.abs().sum()) > 0 and small[0].weight.data_ptr() == f2.data_ptr()
+
+
+def test_checkpoint_format_and_resume(tmp_path):
+    from fedml_b200.utils.checkpoint import load_state_dict, save_checkpoint, save_state_dict
+    m = fedml.model.create(Arguments.from_dict(dict(model="resnet56", dataset="cifar10")), 10)
+    p = str(tmp_path / "global_model.pt")
+    save_state_dict(p, m.state_dict())
+    raw = torch.load(p, weights_only=False)
+    assert list(raw.keys()) == list(m.state_dict().keys())                      # plain OrderedDict, reference key names
+    wrapped = str(tmp_path / "ck"); save_checkpoint({"state_dict": {"module." + k: v for k, v in m.state_dict().items()},
+                                                      "optim_dict": {}, "epoch": 3, "test_accTop1": 0.5, "test_accTop5": 0.9}, True, wrapped)
+    sd = load_state_dict(os.path.join(wrapped, "best.pth"))
+    m.load_state_dict(sd)
+    from fedml.simulation import SimulatorSingleProcess
+    a = mk(federated_optimizer="FedOpt", server_optimizer="adam", server_lr=0.01, comm_round=4, checkpoint_dir=str(tmp_path / "run"),
+           checkpoint_every=2, eval_client_cap=2)
+    ds, out = fedml.data.load(a)
+    init = fedml.model.create(a, out)
+    full = SimulatorSingleProcess(a, torch.device("cpu"), ds, copy.deepcopy(init)); w_full = full.run()
+    a2 = copy.copy(a); a2.comm_round = 2
+    SimulatorSingleProcess(a2, torch.device("cpu"), ds, copy.deepcopy(init)).run()      # "crashes" after round 2
+    a3 = copy.copy(a); a3.comm_round = 4
+    res = SimulatorSingleProcess(a3, torch.device("cpu"), ds, fedml.model.create(a, out))   # fresh process, fresh init
+    assert res.fl_trainer.resume(str(tmp_path / "run"))
+    w_res = res.run()
+    for k in w_full:
+        torch.testing.assert_close(w_res[k].float(), w_full[k].float(), rtol=1e-5, atol=1e-6)   # server-opt moments + round idx restored
