@@ -64,13 +64,20 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, f
   const __nv_bfloat16* base = x + (size_t)c * M * ch;
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
-  for (int64_t v = v0 + tid; v < v1; v += BN_THREADS) {
-    float f[8];
-    unpack8(ldg16(base + v * BN_VEC), f);
+  for (int64_t v = v0 + tid; v < v1; v += 4 * BN_THREADS) {   // 4 independent 16-byte loads in flight per thread
+    uint4 r[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      a[i] += f[i];
-      b[i] += f[i] * f[i];
+    for (int u = 0; u < 4; ++u)
+      r[u] = (v + u * BN_THREADS < v1) ? ldg16(base + (v + u * BN_THREADS) * BN_VEC) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float f[8];
+      unpack8(r[u], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a[i] += f[i];
+        b[i] += f[i] * f[i];
+      }
     }
   }
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
@@ -132,28 +139,36 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     sh[i] = shift[coff + i];
   }
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
-  for (int64_t v = v0 + tid; v < v1; v += BN_THREADS) {
-    float f[8];
-    unpack8(ldg16(x + cbase + v * BN_VEC), f);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) f[i] = f[i] * sc[i] + sh[i];
+  for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {    // two vectors (x and res each) in flight per thread
+    const int64_t vb = v + BN_THREADS;
+    const bool two = vb < v1;
+    const uint4 xa = ldg16(x + cbase + v * BN_VEC);
+    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
+    uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
     if (res) {
-      float r[8];
-      unpack8(ldg16(res + cbase + v * BN_VEC), r);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) f[i] += r[i];
+      ra = ldg16(res + cbase + v * BN_VEC);
+      if (two) rb = ldg16(res + cbase + vb * BN_VEC);
     }
-    if (relu) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      float f[8], r[8];
+      unpack8(u ? xb : xa, f);
+      unpack8(u ? rb : ra, r);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        f[i] = f[i] * sc[i] + sh[i] + r[i];
+        if (relu) f[i] = fmaxf(f[i], 0.f);
+      }
+      *reinterpret_cast<uint4*>(y + cbase + (u ? vb : v) * BN_VEC) = pack8(f);
     }
-    *reinterpret_cast<uint4*>(y + cbase + v * BN_VEC) = pack8(f);
   }
 }
 
 static int bn_slices(int C, int64_t M, int ch) {
-  // enough CTAs to fill the machine twice, but at least 2048 elements (one sweep) per CTA iteration
-  int64_t want = (2 * (int64_t)fb_num_sms() + C - 1) / C;
+  // ~6 CTAs per SM in flight (these kernels are pure streaming: occupancy = bytes in flight), but at least
+  // four sweeps of 2048 elements per CTA so the per-CTA prologue stays amortised
+  int64_t want = (6 * (int64_t)fb_num_sms() + C - 1) / C;
   int64_t max_s = (M * ch + 8191) / 8192;
   if (want > max_s) want = max_s;
   if (want < 1) want = 1;
@@ -197,35 +212,50 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
   const size_t cbase = (size_t)c * M * ch;
   const int coff = (tid * BN_VEC) % ch;
-  float mu[8], rs[8], ga[8], be[8];
+  // mask recompute (no y): relu input = x*g + k with g = gamma*rstd, k = beta - mean*g
+  float g[8], k[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    mu[i] = mean[(size_t)c * ch + coff + i];
-    rs[i] = rstd[(size_t)c * ch + coff + i];
-    ga[i] = gamma[(size_t)c * ld_p + coff + i];
-    be[i] = beta ? beta[(size_t)c * ld_p + coff + i] : 0.f;
+    const float mu = mean[(size_t)c * ch + coff + i], rs = rstd[(size_t)c * ch + coff + i];
+    g[i] = gamma[(size_t)c * ld_p + coff + i] * rs;
+    k[i] = (beta ? beta[(size_t)c * ld_p + coff + i] : 0.f) - mu * g[i];
   }
+  // partial sums of dy' and dy'*x (raw x): the apply kernel turns them into dbeta and dgamma = rstd*(S_dx - mean*S_d)
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
-  for (int64_t v = v0 + tid; v < v1; v += BN_THREADS) {
-    float d[8], xv[8];
-    unpack8(ldg16(dy + cbase + v * BN_VEC), d);
-    unpack8(ldg16(x + cbase + v * BN_VEC), xv);
-    if (relu) {
-      if (y) {   // residual block output: the mask needs the stored forward output
-        float yv[8];
-        unpack8(ldg16(y + cbase + v * BN_VEC), yv);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
-      } else {   // plain BN+ReLU: recompute the sign from x instead of streaming y again
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d[i] = ((xv[i] - mu[i]) * rs[i] * ga[i] + be[i]) > 0.f ? d[i] : 0.f;
-      }
+  for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {
+    const int64_t vb = v + BN_THREADS;
+    const bool two = vb < v1;
+    const uint4 da = ldg16(dy + cbase + v * BN_VEC), xa = ldg16(x + cbase + v * BN_VEC);
+    const uint4 db_ = two ? ldg16(dy + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
+    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
+    uint4 ya = make_uint4(0, 0, 0, 0), yb = ya;
+    if (relu && y) {
+      ya = ldg16(y + cbase + v * BN_VEC);
+      if (two) yb = ldg16(y + cbase + vb * BN_VEC);
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      a[i] += d[i];
-      b[i] += d[i] * (xv[i] - mu[i]) * rs[i];
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      float d[8], xv[8];
+      unpack8(u ? db_ : da, d);
+      unpack8(u ? xb : xa, xv);
+      if (relu) {
+        if (y) {
+          float yv[8];
+          unpack8(u ? yb : ya, yv);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = (xv[i] * g[i] + k[i]) > 0.f ? d[i] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a[i] += d[i];
+        b[i] += d[i] * xv[i];
+      }
     }
   }
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
@@ -238,61 +268,80 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
                     const float* __restrict__ rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta,
                     int64_t ld_g) {
-  extern __shared__ float sm[];  // k1[ch] = gamma*rstd, k2[ch] = dbeta/M, k3[ch] = dgamma/M * rstd ... see below
-  float* s_g = sm;               // gamma * rstd
-  float* s_db = sm + ch;         // dbeta / M
-  float* s_dg = sm + 2 * ch;     // dgamma / M
+  extern __shared__ float sm[];  // per channel: A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g
+  float* s_A = sm;
+  float* s_B = sm + ch;
+  float* s_C = sm + 2 * ch;
+  float* s_K = sm + 3 * ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   for (int k = tid; k < ch; k += BN_THREADS) {
-    float db = 0.f, dg = 0.f;
+    float sd = 0.f, sdx = 0.f;
     for (int j = 0; j < S; ++j) {
-      db += partial[((size_t)c * S + j) * 2 * ch + k];
-      dg += partial[((size_t)c * S + j) * 2 * ch + ch + k];
+      sd += partial[((size_t)c * S + j) * 2 * ch + k];
+      sdx += partial[((size_t)c * S + j) * 2 * ch + ch + k];
     }
+    const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
+    const float dbt = sd, dgm = rs * (sdx - mu * sd);
     if (s == 0) {
-      dbeta[(size_t)c * ld_g + k] = db;
-      dgamma[(size_t)c * ld_g + k] = dg;
+      dbeta[(size_t)c * ld_g + k] = dbt;
+      dgamma[(size_t)c * ld_g + k] = dgm;
     }
-    s_g[k] = gamma[(size_t)c * ld_p + k] * rstd[(size_t)c * ch + k];
-    s_db[k] = db / (float)M;
-    s_dg[k] = dg / (float)M;
+    const float g = gamma[(size_t)c * ld_p + k] * rs;
+    const float B = -g * rs * dgm / (float)M;
+    s_A[k] = g;
+    s_B[k] = B;
+    s_C[k] = -g * dbt / (float)M - mu * B;
+    s_K[k] = (beta ? beta[(size_t)c * ld_p + k] : 0.f) - mu * g;
   }
   __syncthreads();
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
   const size_t cbase = (size_t)c * M * ch;
   const int coff = (tid * BN_VEC) % ch;
-  float g[8], db[8], dg[8], mu[8], rs[8], be[8];
+  float A[8], B[8], Cc[8], K[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    g[i] = s_g[coff + i];
-    db[i] = s_db[coff + i];
-    dg[i] = s_dg[coff + i];
-    mu[i] = mean[(size_t)c * ch + coff + i];
-    rs[i] = rstd[(size_t)c * ch + coff + i];
-    be[i] = beta ? beta[(size_t)c * ld_p + coff + i] : 0.f;
+    A[i] = s_A[coff + i];
+    B[i] = s_B[coff + i];
+    Cc[i] = s_C[coff + i];
+    K[i] = s_K[coff + i];
   }
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
-  for (int64_t v = v0 + tid; v < v1; v += BN_THREADS) {
-    float d[8], xv[8];
-    unpack8(ldg16(dy + cbase + v * BN_VEC), d);
-    unpack8(ldg16(x + cbase + v * BN_VEC), xv);
-    if (relu) {
-      if (y) {
-        float yv[8];
-        unpack8(ldg16(y + cbase + v * BN_VEC), yv);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) d[i] = ((xv[i] - mu[i]) * g[i] + be[i]) > 0.f ? d[i] : 0.f;
-      }
+  for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {
+    const int64_t vb = v + BN_THREADS;
+    const bool two = vb < v1;
+    const uint4 da = ldg16(dy + cbase + v * BN_VEC), xa = ldg16(x + cbase + v * BN_VEC);
+    const uint4 db_ = two ? ldg16(dy + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
+    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
+    uint4 ya = make_uint4(0, 0, 0, 0), yb = ya;
+    if (relu && y) {
+      ya = ldg16(y + cbase + v * BN_VEC);
+      if (two) yb = ldg16(y + cbase + vb * BN_VEC);
     }
-    if (dres) *reinterpret_cast<uint4*>(dres + cbase + v * BN_VEC) = pack8(d);
-    float o[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o[i] = g[i] * (d[i] - db[i] - (xv[i] - mu[i]) * rs[i] * dg[i]);
-    *reinterpret_cast<uint4*>(dx + cbase + v * BN_VEC) = pack8(o);
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+      const int64_t vv = u ? vb : v;
+      float d[8], xv[8];
+      unpack8(u ? db_ : da, d);
+      unpack8(u ? xb : xa, xv);
+      if (relu) {
+        if (y) {
+          float yv[8];
+          unpack8(u ? yb : ya, yv);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = yv[i] > 0.f ? d[i] : 0.f;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) d[i] = (xv[i] * A[i] + K[i]) > 0.f ? d[i] : 0.f;
+        }
+      }
+      if (dres) *reinterpret_cast<uint4*>(dres + cbase + vv * BN_VEC) = pack8(d);
+      float o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = d[i] * A[i] + xv[i] * B[i] + Cc[i];   // = g*(d - dbeta/M - xhat*dgamma/M)
+      *reinterpret_cast<uint4*>(dx + cbase + vv * BN_VEC) = pack8(o);
+    }
   }
 }
 
@@ -310,7 +359,7 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, v
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
       beta, ld_p, relu, scratch);
   FB_CHECK_CUDA(cudaGetLastError());
-  bn_bwd_apply_kernel<<<dim3(S, C), BN_THREADS, 3 * ch * sizeof(float), (cudaStream_t)stream>>>(
+  bn_bwd_apply_kernel<<<dim3(S, C), BN_THREADS, 4 * ch * sizeof(float), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
       (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
   FB_CHECK_CUDA(cudaGetLastError());
@@ -322,16 +371,17 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, v
 __global__ void __launch_bounds__(256)
 im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int64_t total_vec, int H, int W,
                  int Ho, int Wo, int ch, int stride) {
-  const int cv = ch / 8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t t = i;
-    const int c8 = (int)(t % cv); t /= cv;
-    const int kw = (int)(t % 3); t /= 3;
-    const int kh = (int)(t % 3); t /= 3;
-    const int wo = (int)(t % Wo); t /= Wo;
-    const int ho = (int)(t % Ho); t /= Ho;
-    const int64_t n = t;
-    const int h = ho * stride + kh - 1, w = wo * stride + kw - 1;
+  // all index arithmetic in 32 bits (64-bit div/mod per vector made this kernel ALU-bound); the host
+  // guarantees total_vec < 2^32
+  const uint32_t cv = ch / 8, per_pix = 9u * cv, per_row = per_pix * (uint32_t)Wo, per_img = per_row * (uint32_t)Ho;
+  const uint32_t total = (uint32_t)total_vec;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const uint32_t n = i / per_img, r0 = i - n * per_img;
+    const uint32_t ho = r0 / per_row, r1 = r0 - ho * per_row;
+    const uint32_t wo = r1 / per_pix, r2 = r1 - wo * per_pix;
+    const uint32_t tap = r2 / cv, c8 = r2 - tap * cv;
+    const int kh = (int)(tap / 3u), kw = (int)(tap - (tap / 3u) * 3u);
+    const int h = (int)ho * stride + kh - 1, w = (int)wo * stride + kw - 1;
     uint4 v = make_uint4(0, 0, 0, 0);
     if (h >= 0 && h < H && w >= 0 && w < W) v = ldg16(x + (((size_t)n * H + h) * W + w) * ch + (size_t)c8 * 8);
     *reinterpret_cast<uint4*>(cols + (size_t)i * 8) = v;
@@ -343,6 +393,7 @@ extern "C" int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, 
              "fb_im2col3x3_nhwc_bf16: bad arguments (ch must be a multiple of 8)");
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   const int64_t total = (int64_t)n_img * Ho * Wo * 9 * (ch / 8);
+  FB_REQUIRE(total < 4294967296LL, "fb_im2col3x3_nhwc_bf16: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
   im2col3x3_kernel<<<(int)(grid < cap ? grid : cap), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, (__nv_bfloat16*)cols, total, H, W, Ho, Wo, ch, stride);
@@ -354,13 +405,14 @@ extern "C" int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, 
 __global__ void __launch_bounds__(256)
 col2im3x3_kernel(const __nv_bfloat16* __restrict__ cols, __nv_bfloat16* __restrict__ dx, int64_t total_vec, int H, int W,
                  int Ho, int Wo, int ch, int stride) {
-  const int cv = ch / 8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t t = i;
-    const int c8 = (int)(t % cv); t /= cv;
-    const int w = (int)(t % W); t /= W;
-    const int h = (int)(t % H); t /= H;
-    const int64_t n = t;
+  const uint32_t cv = ch / 8, per_row = cv * (uint32_t)W, per_img = per_row * (uint32_t)H;
+  const uint32_t total = (uint32_t)total_vec;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const uint32_t n = i / per_img, r0 = i - n * per_img;
+    const int h = (int)(r0 / per_row);
+    const uint32_t r1 = r0 - (uint32_t)h * per_row;
+    const int w = (int)(r1 / cv);
+    const uint32_t c8 = r1 - (uint32_t)w * cv;
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
     for (int kh = 0; kh < 3; ++kh) {
@@ -389,6 +441,8 @@ extern "C" int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img,
              "fb_col2im3x3_nhwc_bf16: bad arguments (ch must be a multiple of 8)");
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   const int64_t total = (int64_t)n_img * H * W * (ch / 8);
+  FB_REQUIRE(total < 4294967296LL && (int64_t)n_img * Ho * Wo * 9 * (ch / 8) < 4294967296LL,
+             "fb_col2im3x3_nhwc_bf16: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
   col2im3x3_kernel<<<(int)(grid < cap ? grid : cap), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)cols, (__nv_bfloat16*)dx, total, H, W, Ho, Wo, ch, stride);
