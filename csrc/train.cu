@@ -238,3 +238,42 @@ extern "C" int fb_eval_counts(const float* logits, const int64_t* labels, int64_
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+
+// ---------------------------------------------------------------- conv / linear weight staging (one launch per step)
+// For every listed layer: fp32 master weights [cout][cin][kh][kw] of every client (rows of the stacked arena) ->
+//   Wm  bf16 [cout][k*k*cin_pad]   ((kh,kw,cin) order = the im2col column order, zero-padded input channels)
+//   WmT bf16 [k*k*cin_pad][cout]   (K-major operand for the dgrad GEMM), optional
+// Segment table (int64 x 8 per layer): src_off, cout, cin, cin_pad, k, dst_off, dstT_off (-1: none), n = cout*k*k*cin_pad
+__global__ void __launch_bounds__(256)
+stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16* __restrict__ stage, int64_t stage_ld,
+                     const int64_t* __restrict__ table, int n_layers) {
+  const int c = blockIdx.y;
+  const float* row = arena + (size_t)c * ld;
+  __nv_bfloat16* out = stage + (size_t)c * stage_ld;
+  for (int l = blockIdx.z; l < n_layers; l += gridDim.z) {
+    const int64_t* t = table + (size_t)l * 8;
+    const int64_t src = t[0], dst = t[5], dstT = t[6];
+    const int cout = (int)t[1], cin = (int)t[2], cinp = (int)t[3], k = (int)t[4], n = (int)t[7];
+    const int kk = k * k, kdim = kk * cinp;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+      const int co = e / kdim, r = e - co * kdim;
+      const int tap = r / cinp, ci = r - tap * cinp;
+      const float v = ci < cin ? row[src + ((size_t)co * cin + ci) * kk + tap] : 0.f;
+      const __nv_bfloat16 h = __float2bfloat16_rn(v);
+      out[dst + e] = h;
+      if (dstT >= 0) out[dstT + (size_t)r * cout + co] = h;
+    }
+  }
+}
+extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage, int64_t stage_ld,
+                                     const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
+  FB_REQUIRE(arena && stage && table_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_stage_conv_weights: bad arguments");
+  int gx = (max_n + 255) / 256;
+  if (gx > 16) gx = 16;
+  if (gx < 1) gx = 1;
+  int gz = n_layers < 64 ? n_layers : 64;
+  stage_weights_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(arena, ld, (__nv_bfloat16*)stage, stage_ld,
+                                                                         table_dev, n_layers);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}

@@ -50,9 +50,13 @@ class TorchBackend:
         y = torch.bmm(a, b)
         return y if out_dtype is None else y.to(out_dtype)
 
-    def gemm_tn(self, a, b, out_dtype=torch.float32):
-        """a [C,M,N]^T x b [C,M,K] -> [C,N,K]  (weight gradients; fp32 result)"""
-        return torch.bmm(a.transpose(1, 2), b).to(out_dtype)
+    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None):
+        """a [C,M,N]^T x b [C,M,K] -> [C,N,K]  (weight gradients; fp32 result, optionally written into ``out``)"""
+        r = torch.bmm(a.transpose(1, 2), b).to(out_dtype)
+        if out is not None:
+            out.copy_(r)
+            return out
+        return r
 
     # ---- im2col / col2im for 3x3, pad 1 (NHWC) ------------------------------------
     def im2col3x3(self, x, stride):
@@ -97,7 +101,8 @@ class TorchBackend:
             y = torch.relu(y)
         return y.to(x.dtype), mean, rstd
 
-    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True):
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True, dgamma_out=None,
+               dbeta_out=None):
         C = x.shape[0]
         ch = x.shape[-1]
         dyf = dy.float()
@@ -110,6 +115,8 @@ class TorchBackend:
         dbeta = d2.sum(dim=1)
         dgamma = (d2 * xhat).sum(dim=1)
         dx = (gamma * rstd)[:, None, :] * (d2 - dbeta[:, None, :] / M - xhat * dgamma[:, None, :] / M)
+        if dgamma_out is not None:
+            dgamma_out.copy_(dgamma); dbeta_out.copy_(dbeta)
         return dx.view(x.shape).to(x.dtype), dres, dgamma, dbeta
 
     # ---- loss ---------------------------------------------------------------------
@@ -165,11 +172,15 @@ class NativeBackend(TorchBackend):
         self._fb("gemm_nn")
         return super().gemm_nn(a, b, out_dtype)
 
-    def gemm_tn(self, a, b, out_dtype=torch.float32):
+    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None):
         if self.use_tc_gemm and out_dtype == torch.float32 and self.ops.grouped_gemm_tn_supported(a, b):
-            return self.ops.grouped_gemm_tn(a, b)
+            r = self.ops.grouped_gemm_tn(a, b, out=out)
+            if out is not None and r is not out:
+                out.copy_(r)
+                return out
+            return r
         self._fb("gemm_tn")
-        return super().gemm_tn(a, b, out_dtype)
+        return super().gemm_tn(a, b, out_dtype, out)
 
     def im2col3x3(self, x, stride):
         if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
@@ -189,12 +200,14 @@ class NativeBackend(TorchBackend):
         self._fb("bn_fwd")
         return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
 
-    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True):
+    def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True, dgamma_out=None,
+               dbeta_out=None):
         if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
             skip_y = relu and not had_res and beta is not None   # mask recomputed from x: one stream less
-            return self.ops.bn_bwd_stacked(dy, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta)
+            return self.ops.bn_bwd_stacked(dy, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta,
+                                           dgamma_out=dgamma_out, dbeta_out=dbeta_out)   # grads land in the arena
         self._fb("bn_bwd")
-        return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres)
+        return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres, dgamma_out=dgamma_out, dbeta_out=dbeta_out)
 
     def xent(self, logits, labels, pre_sigmoid=False, row_scale=None):
         C, B, ncls = logits.shape
@@ -246,8 +259,14 @@ class _Conv:
         C, B, H, W_, _ = x.shape
         cols, Ho, Wo = self._cols(be, x)
         dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
-        dWm = be.gemm_tn(dy2, cols)                                   # [C, cout, kk*cin] fp32
-        if self.k == 1:
+        if self.k == 1 and self.cin == self.cin_real:
+            be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin))    # straight into the gradient arena
+            dWm = None
+        else:
+            dWm = be.gemm_tn(dy2, cols)                               # [C, cout, kk*cin] fp32
+        if dWm is None:
+            pass
+        elif self.k == 1:
             gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1)[:, :, :self.cin_real])
         else:
             gW.copy_(dWm.view(C, self.cout, self.k, self.k, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
@@ -274,10 +293,8 @@ class _BN:
 
     def bwd(self, be, dy, x, y, W, G, mean, rstd, relu, want_dres):
         n = self.name
-        dx, dres, dgamma, dbeta = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres,
-                                            beta=W[n + ".bias"], had_res=want_dres)
-        G[n + ".weight"].copy_(dgamma)
-        G[n + ".bias"].copy_(dbeta)
+        dx, dres, _, _ = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres, beta=W[n + ".bias"],
+                                   had_res=want_dres, dgamma_out=G[n + ".weight"], dbeta_out=G[n + ".bias"])
         return dx, dres
 
 
@@ -414,9 +431,46 @@ class BatchedResNet(BatchedModel):
     def prepare(self, W):
         dt = self.be.dtype
         tr = self.be.want_transposed_weights
+        if isinstance(self.be, NativeBackend) and dt == torch.bfloat16 and getattr(W, "arena", None) is not None:
+            return self._prepare_staged(W)
         Wm = {c.name: c.prep(W, dt, tr) for c in self.convs}
         Wm["fc"] = W["fc.weight"].to(dt)
         return Wm
+
+    def _prepare_staged(self, W):
+        """All conv / fc weights of all clients -> bf16 GEMM operands with ONE kernel launch."""
+        arena, layout = W.arena, W.layout
+        C = arena.shape[0]
+        key = (arena.data_ptr(), C)
+        st = getattr(self, "_stage", None)
+        if st is None or st["key"] != key:
+            rows, off, plan = [], 0, {}
+            al = lambda v: (v + 7) // 8 * 8   # noqa: E731  16-byte aligned segments for TMA
+            for c in self.convs:
+                seg = layout.by_name[c.wname]
+                n = c.cout * c.k * c.k * c.cin
+                dst = off; off = al(off + n)
+                dstT = -1
+                if c.need_dx:
+                    dstT = off; off = al(off + n)
+                rows.append([seg.offset, c.cout, c.cin_real, c.cin, c.k, dst, dstT, n])
+                plan[c.name] = (dst, dstT, c.cout, c.k * c.k * c.cin)
+            seg = layout.by_name["fc.weight"]
+            n = self.ncls * self.feat_dim
+            rows.append([seg.offset, self.ncls, self.feat_dim, self.feat_dim, 1, off, -1, n])
+            plan["fc"] = (off, -1, self.ncls, self.feat_dim)
+            off = al(off + n)
+            stage = torch.zeros((C, off), dtype=torch.bfloat16, device=arena.device)
+            table = torch.tensor(rows, dtype=torch.int64).to(arena.device)
+            views = {}
+            for name, (dst, dstT, cout, kdim) in plan.items():
+                wm = stage[:, dst:dst + cout * kdim].view(C, cout, kdim)
+                wt = stage[:, dstT:dstT + cout * kdim].view(C, kdim, cout) if dstT >= 0 else None
+                views[name] = wm if name == "fc" else (wm, wt)
+            st = self._stage = {"key": key, "stage": stage, "table": table, "views": views, "n": len(rows),
+                                "max_n": max(r[7] for r in rows)}
+        self.be.ops.stage_conv_weights(arena, st["stage"], st["table"], st["n"], st["max_n"])
+        return st["views"]
 
     def _input(self, x):
         if x.dtype == torch.uint8:

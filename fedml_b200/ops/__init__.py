@@ -296,19 +296,22 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
     return y, mean, rstd
 
 
-def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None):
-    """``y=None`` (+ ``beta``) recomputes the ReLU mask from x — only valid when the forward had no residual."""
+def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None):
+    """``y=None`` (+ ``beta``) recomputes the ReLU mask from x — only valid when the forward had no residual.
+    ``dgamma_out`` / ``dbeta_out``: fp32 [C, ch] strided views (e.g. rows of the gradient arena) written in place."""
     Cn, ch = x.shape[0], x.shape[-1]
     M = x.numel() // (Cn * ch)
     dy = dy.contiguous()
     dx = torch.empty_like(x)
     dres = torch.empty_like(x) if want_dres else None
-    dgamma = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
-    dbeta = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    direct = dgamma_out is not None and dbeta_out is not None and dgamma_out.stride(0) == dbeta_out.stride(0)
+    dgamma = dgamma_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    dbeta = dbeta_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
+    ld_g = dgamma.stride(0) if Cn > 1 else max(dgamma.stride(0), ch)
     scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
     check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
                                   i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
-                                  vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ch), vp(ptr(scratch)),
+                                  vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ld_g), vp(ptr(scratch)),
                                   vp(stream_ptr(x.device))), "bn_bwd_stacked")
     count_launch(2)
     return dx, dres, dgamma, dbeta
@@ -359,12 +362,12 @@ def grouped_gemm_tn_supported(a, b) -> bool:
         and a.shape[2] % 8 == 0 and b.shape[2] % 8 == 0
 
 
-def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name):
-    d = torch.empty((G, M, N), dtype=out_dtype, device=a.device)
+def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None):
+    d = torch.empty((G, M, N), dtype=out_dtype, device=a.device) if out is None else out
     p = FbGroupedGemm()
     p.a, p.b, p.d = a.data_ptr(), b.data_ptr(), d.data_ptr()
     p.bias = bias.data_ptr() if bias is not None else None
-    p.a_gs, p.b_gs, p.d_gs = a.stride(0), b.stride(0), M * N
+    p.a_gs, p.b_gs, p.d_gs = a.stride(0), b.stride(0), (M * N if out is None else (d.stride(0) if G > 1 else M * N))
     p.bias_gs = bias.stride(0) if bias is not None else 0
     p.G, p.M, p.N, p.K = G, M, N, K
     p.lda, p.ldb, p.ldd = a.stride(1), b.stride(1), N
@@ -382,7 +385,7 @@ def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
     return _launch_gemm(lib().fb_grouped_gemm_bf16, a, b, G, M, b.shape[1], K, out_dtype, relu, bias, "grouped_gemm")
 
 
-def grouped_gemm_tn(a, b, out_dtype=torch.float32):
+def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None):
     """d[g] = a[g]^T @ b[g]   (a [G,K,M], b [G,K,N]): weight gradients without transposing activations.
     The output is tiny and the reduction long, so when there are fewer tiles than CTA slots the reduction
     dimension is cut into slices that run as extra groups (split-K) and the fp32 partials are summed."""
@@ -398,10 +401,17 @@ def grouped_gemm_tn(a, b, out_dtype=torch.float32):
             if kb % cand == 0 and kb // cand >= 4 and tiles * cand <= 1184:
                 S = cand
                 break
+    # ``out``: fp32 [G, M, N] view with contiguous [M, N] blocks (e.g. a 1x1-conv gradient inside the arena)
+    if out is not None and not (out.dtype == torch.float32 and out.stride(2) == 1 and out.stride(1) == N
+                                and out.data_ptr() % 16 == 0 and (G == 1 or out.stride(0) % 4 == 0)):
+        out = None
     if S == 1:
-        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn")
+        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn",
+                            out=out if out_dtype == torch.float32 else None)
     part = _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
                         K // S, torch.float32, False, None, "grouped_gemm_tn")
+    if out is not None:
+        return torch.sum(part.view(G, S, M, N), dim=1, out=out)
     return part.view(G, S, M, N).sum(dim=1).to(out_dtype)
 
 
@@ -458,3 +468,11 @@ def gram_bf16(hi: torch.Tensor, lo: Optional[torch.Tensor] = None, split: int = 
         hl = run(hi, lo)
         g = g + hl + hl.t()
     return g
+
+
+def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Tensor, n_layers: int, max_n: int):
+    """arena fp32 [C, ld] -> stage bf16 [C, stage_ld] following the int64 [n_layers, 8] device table."""
+    check(lib().fb_stage_conv_weights(vp(ptr(arena)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(stage)),
+                                      i64(stage.stride(0)), vp(ptr(table)), i32(n_layers), i32(max_n),
+                                      vp(stream_ptr(arena.device))), "stage_conv_weights")
+    count_launch()

@@ -37,6 +37,11 @@ def _pad4(n: int) -> int:
     return (n + 3) // 4 * 4
 
 
+class StackedViews(OrderedDict):
+    arena = None
+    layout = None
+
+
 class ArenaLayout:
     def __init__(self, model_or_state, param_names: Optional[Iterable[str]] = None):
         if isinstance(model_or_state, nn.Module):
@@ -89,9 +94,12 @@ class ArenaLayout:
         return OrderedDict((s.name, flat[s.offset:s.offset + s.numel].view(s.shape)) for s in self.segments)
 
     def stacked_views(self, stack: torch.Tensor) -> "OrderedDict[str, torch.Tensor]":
-        """[C, P(+pad)] client stack -> {name: [C, *shape]} strided zero-copy views."""
+        """[C, P(+pad)] client stack -> {name: [C, *shape]} strided zero-copy views.  The returned dict also
+        carries ``.arena`` (the stack) and ``.layout`` so kernels that walk the whole arena can find it."""
         C = stack.shape[0]
-        return OrderedDict((s.name, stack[:, s.offset:s.offset + s.numel].view(C, *s.shape)) for s in self.segments)
+        out = StackedViews((s.name, stack[:, s.offset:s.offset + s.numel].view(C, *s.shape)) for s in self.segments)
+        out.arena, out.layout = stack, self
+        return out
 
     def param_segments(self) -> List[Segment]:
         return [s for s in self.segments if s.kind == "param"]

@@ -218,6 +218,12 @@ int fb_sgd_step_stacked_bf16g(float* w, const void* g_bf16, int64_t ld, int64_t 
 int fb_softmax_xent(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int64_t ignore_index,
                     int32_t pre_sigmoid, const float* row_scale, int64_t rows_per_group, float* loss_rows,
                     float* dlogits, fb_stream_t stream);
+/* One-launch staging of every conv / linear weight of every client for a training step: fp32 master rows of
+ * the stacked arena -> bf16 GEMM operands in (kh,kw,cin) order (+ transposed copies for dgrad).  table_dev: int64
+ * [n_layers][8] = {src_off, cout, cin, cin_pad, k, dst_off, dstT_off or -1, cout*k*k*cin_pad}.  Replaces ~3 small
+ * cast/permute kernels per layer per step. */
+int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage_bf16, int64_t stage_ld,
+                          const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream);
 /* K15 fused evaluation: counters[0]=correct, [1]=loss_sum, [2]=total, then tp[ncls], fp[ncls], fn[ncls]
  * (all float64-free: uint32 counts in `counts`, float loss in `loss_sum`). Accumulates into the outputs. */
 int fb_eval_counts(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int32_t pre_sigmoid,
