@@ -154,17 +154,27 @@ __device__ __forceinline__ float4 local_accumulate(const FbRoundParams& p, const
     }
   } else {
     const float4 g = *reinterpret_cast<const float4*>(p.global_model + j);
-    for (int c = 0; c < C; ++c) {
-      float4 x = ld_stream4(p.clients + (size_t)c * p.ld + j);
-      const float sc = clip ? s_scale[c] : 1.f;
-      float4 y = make_float4(g.x + sc * (x.x - g.x), g.y + sc * (x.y - g.y), g.z + sc * (x.z - g.z),
-                             g.w + sc * (x.w - g.w));
-      if (noise) {
-        float4 z = philox_normal4(p.seed, p.round, (uint32_t)(p.client_base + c), (uint64_t)v);
-        y.x += p.noise_std * z.x; y.y += p.noise_std * z.y; y.z += p.noise_std * z.z; y.w += p.noise_std * z.w;
+    for (int c0 = 0; c0 < C; c0 += 4) {
+      const int nc = min(4, C - c0);
+      float4 x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (u < nc) x[u] = ld_stream4(p.clients + (size_t)(c0 + u) * p.ld + j);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < nc) {
+          const int c = c0 + u;
+          const float sc = clip ? s_scale[c] : 1.f;
+          float4 y = make_float4(g.x + sc * (x[u].x - g.x), g.y + sc * (x[u].y - g.y), g.z + sc * (x[u].z - g.z),
+                                 g.w + sc * (x[u].w - g.w));
+          if (noise) {
+            float4 z = philox_normal4(p.seed, p.round, (uint32_t)(p.client_base + c), (uint64_t)v);
+            y.x += p.noise_std * z.x; y.y += p.noise_std * z.y; y.z += p.noise_std * z.z; y.w += p.noise_std * z.w;
+          }
+          const float w = __ldg(wt + c);
+          acc.x += w * y.x; acc.y += w * y.y; acc.z += w * y.z; acc.w += w * y.w;
+        }
       }
-      float w = __ldg(wt + c);
-      acc.x += w * y.x; acc.y += w * y.y; acc.z += w * y.z; acc.w += w * y.w;
     }
   }
   return acc;
@@ -186,23 +196,33 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
 
   // ---- phase 0: per-client clip factors s_c = 1 / max(1, ||x_c - w||_2 / bound) over [0, Pt)
   if (clip && C > 0) {
-    for (int c = 0; c < C; ++c) {
-      const float* row = p.clients + (size_t)c * p.ld;
-      float acc = 0.f;
+    for (int c0 = 0; c0 < C; c0 += 4) {     // four client rows per sweep: four independent 128-bit loads in flight
+      const int nc = min(4, C - c0);
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
       for (int s = 0; s < G; ++s) {
         const int64_t lo = (int64_t)s * S4, hi = min(lo + S4, nvec);
         for (int64_t v = lo + (int64_t)block * T + tid; v < hi; v += stride) {
           const int64_t j = v * 4;
           if (j < Pt) {
-            float4 x = ld_stream4(row + j);
-            float4 w = *reinterpret_cast<const float4*>(p.global_model + j);
-            float a = x.x - w.x, b = x.y - w.y, cc = x.z - w.z, d = x.w - w.w;
-            acc += a * a + b * b + cc * cc + d * d;
+            const float4 w = *reinterpret_cast<const float4*>(p.global_model + j);
+            float4 x[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (u < nc) x[u] = ld_stream4(p.clients + (size_t)(c0 + u) * p.ld + j);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              if (u < nc) {
+                const float a = x[u].x - w.x, b = x[u].y - w.y, cc = x[u].z - w.z, d = x[u].w - w.w;
+                acc[u] += a * a + b * b + cc * cc + d * d;
+              }
+            }
           }
         }
       }
-      float tot = block_sum(acc, red);
-      if (tid == 0) p.sqnorm_part[(size_t)block * C + c] = tot;
+      for (int u = 0; u < nc; ++u) {
+        const float tot = block_sum(acc[u], red);
+        if (tid == 0) p.sqnorm_part[(size_t)block * C + c0 + u] = tot;
+      }
     }
     rank_grid_barrier(p.grid_bar, p.grid_bar_target);
     for (int c = tid; c < C; c += T) {
@@ -237,6 +257,10 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
   float* sec = (p.opt == FB_OPT_ADAM || p.opt == FB_OPT_YOGI || p.opt == FB_OPT_ADAGRAD) ? p.v : nullptr;
   if (p.opt == FB_OPT_ADAGRAD) mom = nullptr;
   const int s_begin = p.two_shot ? rank : 0, s_end = p.two_shot ? rank + 1 : G;
+  const bool use_mc = G > 1 && p.two_shot && p.mc_partial != nullptr && p.mc_global != nullptr;
+  const float* pp[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) pp[q] = (G > 1 && q < G) ? p.peer_partial[q] : nullptr;
   for (int s = s_begin; s < s_end; ++s) {
     const int64_t lo = (int64_t)s * S4, hi = min(lo + S4, nvec);
     for (int64_t v = lo + (int64_t)block * T + tid; v < hi; v += stride) {
@@ -244,6 +268,23 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
       float4 tot = make_float4(0, 0, 0, 0);
       if (G == 1) {
         tot = local_accumulate(p, j, v, dp, clip, noise, wts, wts_b, s_scale);
+      } else if (use_mc) {
+        // NVLS: the switch reduces the G replicas of this 16-byte word and returns the sum (one load instead of G)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(tot.x), "=f"(tot.y), "=f"(tot.z), "=f"(tot.w)
+                     : "l"(p.mc_partial + j)
+                     : "memory");
+      } else if (G <= 8) {
+        // all peer loads are issued before the first add so that G NVLink round trips overlap
+        float4 xs[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < G) xs[q] = (q == rank) ? *reinterpret_cast<const float4*>(p.partial + j) : ld_relaxed_sys4(pp[q] + j);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < G) { tot.x += xs[q].x; tot.y += xs[q].y; tot.z += xs[q].z; tot.w += xs[q].w; }
+        }
       } else {
         for (int q = 0; q < G; ++q) {
           float4 x = (q == rank) ? *reinterpret_cast<const float4*>(p.partial + j)
@@ -254,6 +295,11 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
       const bool train = j < Pt;
       const float inv = train ? p.inv_total : p.inv_total_buf;
       float4 avg = make_float4(tot.x * inv, tot.y * inv, tot.z * inv, tot.w * inv);
+      if (train && p.agg_noise_std > 0.f) {
+        // one Gaussian draw on the aggregate: identical in distribution to summing the per-client draws
+        const float4 z = philox_normal4(p.seed, p.round, 0x00A66E6u, (uint64_t)v);
+        avg.x += p.agg_noise_std * z.x; avg.y += p.agg_noise_std * z.y; avg.z += p.agg_noise_std * z.z; avg.w += p.agg_noise_std * z.w;
+      }
       float4 out = avg;
       if (train && (p.opt != FB_OPT_NONE || p.self_coef != 0.f)) {
         const float4 w = *reinterpret_cast<const float4*>(p.global_model + j);
@@ -262,7 +308,11 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
         }
         out = opt_apply4(o, w, avg, mom, sec, j);
       }
-      if (p.two_shot && G > 1) {
+      if (use_mc) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.mc_global + j), "f"(out.x),
+                     "f"(out.y), "f"(out.z), "f"(out.w)
+                     : "memory");
+      } else if (p.two_shot && G > 1) {
         for (int q = 0; q < G; ++q) st4((q == rank ? p.global_model : p.peer_global[q]) + j, out);
       } else {
         st4(p.global_model + j, out);
@@ -276,12 +326,12 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
   if (G > 1) block_signal_and_wait(p.peer_flags, 1, rank, G, block, p.epoch);
 }
 
-__global__ void __launch_bounds__(ROUND_THREADS) round_kernel(const FbRoundParams p) {
+__global__ void __launch_bounds__(ROUND_THREADS, 2) round_kernel(const FbRoundParams p) {
   extern __shared__ float smem[];
   round_body(p, blockIdx.x, gridDim.x, smem, smem + 64);
 }
 
-__global__ void __launch_bounds__(ROUND_THREADS) round_kernel_emulated(const FbRoundParams* __restrict__ ps) {
+__global__ void __launch_bounds__(ROUND_THREADS, 2) round_kernel_emulated(const FbRoundParams* __restrict__ ps) {
   extern __shared__ float smem[];
   __shared__ FbRoundParams sp;
   if (threadIdx.x == 0) sp = ps[blockIdx.y];

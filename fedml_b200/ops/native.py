@@ -37,6 +37,7 @@ class FbRoundParams(C.Structure):
         ("bias_corr1", C.c_float), ("bias_corr2", C.c_float), ("grad_scale", C.c_float),
         ("m", C.c_void_p), ("v", C.c_void_p), ("sqnorm_part", C.c_void_p), ("clip_scale_out", C.c_void_p),
         ("grid_bar", C.c_void_p), ("grid_bar_target", C.c_uint32),
+        ("mc_partial", C.c_void_p), ("mc_global", C.c_void_p), ("agg_noise_std", C.c_float),
     ]
 
 

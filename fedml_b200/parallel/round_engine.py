@@ -46,6 +46,7 @@ class DPConfig:
     clip: float = 0.0
     sigma: float = 0.0
     seed: int = 0
+    aggregate_noise: bool = False   # one draw on the aggregate (same output distribution, no per-client RNG cost)
 
 
 class RoundEngine:
@@ -53,7 +54,7 @@ class RoundEngine:
 
     def __init__(self, layout: ArenaLayout, device, group=None, opt: Optional[ServerOptConfig] = None,
                  dp: Optional[DPConfig] = None, two_shot: Optional[bool] = None, max_clients: int = 1024,
-                 provider: str = "auto"):
+                 provider: str = "auto", use_multicast: bool = True):
         self.layout, self.device = layout, torch.device(device)
         self.P, self.P_train = layout.P, layout.P_train
         self.opt = opt or ServerOptConfig()
@@ -75,8 +76,12 @@ class RoundEngine:
             self._peer_global = self.region.peer_table("global")
             self._peer_flags = self.region.peer_table("flags")
             self._peer_bar = self.region.peer_table("barflags")
+            mc = self.region.multicast_ptr if use_multicast else 0
+            self._mc_partial = mc + self.region._names["partial"][0] if mc else 0
+            self._mc_global = mc + self.region._names["global"][0] if mc else 0
         else:
             self._peer_partial = self._peer_global = self._peer_flags = None
+            self._mc_partial = self._mc_global = 0
         z = lambda: torch.zeros(self.P_train, dtype=torch.float32, device=self.device)
         self.m = z() if (self.opt.name in ("adam", "yogi") or (self.opt.name == "sgd" and self.opt.momentum)) else None
         self.v = z() if self.opt.name in ("adam", "yogi", "adagrad") else None
@@ -104,7 +109,7 @@ class RoundEngine:
     def aggregate(self, clients: Optional[torch.Tensor], weights: Optional[torch.Tensor], inv_total: float,
                   client_base: int = 0, round_idx: int = 0, weights_buf: Optional[torch.Tensor] = None,
                   inv_total_buf: Optional[float] = None, self_coef: float = 0.0, grad_scale: float = 1.0,
-                  use_opt: bool = True) -> torch.Tensor:
+                  use_opt: bool = True, weight_sq_sum: Optional[float] = None) -> torch.Tensor:
         """Launch the fused round.  ``clients``: fp32 [C, ld>=P] rows (or None when this rank drew no
         client this round); ``weights``: fp32 [C] on the device.  Returns the (updated in place)
         global model of this rank."""
@@ -130,7 +135,12 @@ class RoundEngine:
         self.epoch += 1
         p.epoch, p.two_shot = self.epoch, int(self.two_shot and self.G > 1)
         p.clip_bound, p.noise_std = self.dp.clip, self.dp.sigma
+        if self.dp.aggregate_noise and self.dp.sigma > 0 and weight_sq_sum is not None:
+            # sum_i (w_i * inv_total) * sigma * z_i  ~  N(0, sigma^2 * inv_total^2 * sum_i w_i^2)
+            p.noise_std, p.agg_noise_std = 0.0, self.dp.sigma * inv_total * float(weight_sq_sum) ** 0.5
         p.seed, p.round = self.dp.seed, round_idx
+        if p.two_shot and self._mc_partial:
+            p.mc_partial, p.mc_global = self._mc_partial, self._mc_global
         o = self.opt if use_opt else ServerOptConfig()
         p.opt = FB_OPT[o.name]
         if p.opt:

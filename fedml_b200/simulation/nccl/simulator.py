@@ -145,7 +145,9 @@ class NCCLSimulator:
             from ...parallel.round_engine import DPConfig, RoundEngine, ServerOptConfig
             two_shot = getattr(args, "two_shot", None)
             self.engine = RoundEngine(self.layout, self.device, opt=ServerOptConfig.from_args(args, use_opt),
-                                      dp=DPConfig(clip, sigma, int(getattr(args, "random_seed", 0))),
+                                      dp=DPConfig(clip, sigma, int(getattr(args, "random_seed", 0)),
+                                                  aggregate_noise=str(getattr(args, "dp_noise_mode", "per_client")) == "aggregate"),
+                                      use_multicast=bool(getattr(args, "use_multicast", True)),
                                       two_shot=two_shot, max_clients=max(self.C_max, 1),
                                       provider=str(getattr(args, "symmetric_provider", "auto")))
             self.engine.set_global(flat0)
@@ -527,7 +529,8 @@ class NCCLSimulator:
                 self.global_flat[Pt:] = part_b[Pt:]
             return
         if self.cuda:
-            self.engine.aggregate(self.stack, weights, 1.0 / total, base, round_idx)
+            self.engine.aggregate(self.stack, weights, 1.0 / total, base, round_idx,
+                                  weight_sq_sum=float(sum(float(n) * float(n) for n in sizes)))
             return
         # CPU oracle path (gloo)
         stack = self.stack

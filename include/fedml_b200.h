@@ -87,6 +87,13 @@ typedef struct {
   float* clip_scale_out;       /* [C] optional: the clip factor applied to every client (NULL to skip) */
   uint32_t* grid_bar;          /* [1] zero-initialised counter for the intra-rank barrier */
   uint32_t grid_bar_target;    /* nblocks * (number of clipped calls so far + 1) */
+  /* NVLS (optional, two-shot only): multicast addresses of `partial` and `global_model` bound over all G ranks.
+   * When both are set the shard reduce is one multimem.ld_reduce (in-switch sum) and the redistribution one
+   * multimem.st, instead of G peer loads and G peer stores. */
+  float* mc_partial;
+  float* mc_global;
+  float agg_noise_std;         /* > 0: add N(0, agg_noise_std^2) once to the aggregate of [0,P_train) (same distribution
+                                  as per-client noise when set to sigma * sqrt(sum_i (w_i*inv_total)^2)) */
 } FbRoundParams;
 
 #define FB_ROUND_MAX_BLOCKS 1024
