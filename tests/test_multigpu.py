@@ -25,3 +25,14 @@ def test_round_engine_and_cheetah_on_real_ranks():
             assert v["err"] < (2e-3 if "adam" in k else 2e-5), (k, v)
         if k.startswith("cheetah_"):
             assert v < 1e-5, (k, v)
+        if k.startswith("sim_"):
+            assert v["identical"] and v["finite"], (k, v)
+    # the G-rank result equals what one GPU computes for the same seeds (G-invariance of the simulator)
+    one = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "multigpu_worker.py")], capture_output=True, text=True, timeout=600,
+                         env=dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT="29613"))
+    line1 = [l for l in one.stdout.splitlines() if l.startswith("MULTIGPU_RESULT ")]
+    assert one.returncode == 0 and line1, one.stdout[-2000:] + one.stderr[-2000:]
+    res1 = json.loads(line1[0][len("MULTIGPU_RESULT "):])
+    for k in res:
+        if k.startswith("sim_"):
+            assert abs(res[k]["norm"] - res1[k]["norm"]) <= 2e-3 * max(1.0, res1[k]["norm"]), (k, res[k], res1[k])
