@@ -89,11 +89,13 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 int64_t M, int ch, int S, const float* __restrict__ partial, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                 const float* __restrict__ active, float momentum, float eps, int relu, int training,
-                float* __restrict__ save_mean, float* __restrict__ save_rstd) {
+                float* __restrict__ save_mean, float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n) {
   extern __shared__ float sm[];  // scale[ch], shift[ch]
   float* scale = sm;
   float* shift = sm + ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
+    num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
   for (int k = tid; k < ch; k += BN_THREADS) {
     float mean, var;
     if (training) {
@@ -182,7 +184,7 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
                                  const float* gamma, const float* beta, int64_t ld_p, float* running_mean,
                                  float* running_var, int64_t ld_r, const float* active, float momentum, float eps,
                                  int32_t relu, int32_t training, float* save_mean, float* save_rstd, float* scratch,
-                                 fb_stream_t stream) {
+                                 float* num_batches_tracked, int64_t ld_n, fb_stream_t stream) {
   FB_REQUIRE(x && y && gamma && beta && C >= 1 && C <= 65535 && M >= 1, "fb_bn_fwd_stacked: bad arguments");
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_fwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   FB_REQUIRE(running_mean && running_var, "fb_bn_fwd_stacked: running statistics missing");
@@ -194,7 +196,7 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
   }
   bn_apply_kernel<<<dim3(S, C), BN_THREADS, 2 * ch * sizeof(float), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p,
-      running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd);
+      running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd, num_batches_tracked, ld_n);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -202,7 +204,8 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
 // ---------------------------------------------------------------- BN backward
 // stage 1: partial[c][s][2][ch] = (sum dy', sum dy' * xhat), dy' = dy masked by the ReLU of the forward output
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+                    const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, int relu, float* __restrict__ partial) {
@@ -240,6 +243,12 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
       float d[8], xv[8];
       unpack8(u ? db_ : da, d);
       unpack8(u ? xb : xa, xv);
+      if (dy2) {   // gradient arriving over a second path (residual branch): summed on load instead of by a separate kernel
+        float e[8];
+        unpack8(ldg16(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] += e[i];
+      }
       if (relu) {
         if (y) {
           float yv[8];
@@ -262,7 +271,8 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 }
 
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+                    const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
                     int64_t M, int ch, int S, const float* __restrict__ partial, const float* __restrict__ gamma,
                     const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
@@ -325,6 +335,12 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
       float d[8], xv[8];
       unpack8(u ? db_ : da, d);
       unpack8(u ? xb : xa, xv);
+      if (dy2) {   // gradient arriving over a second path (residual branch): summed on load instead of by a separate kernel
+        float e[8];
+        unpack8(ldg16(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] += e[i];
+      }
       if (relu) {
         if (y) {
           float yv[8];
@@ -345,7 +361,7 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
 }
 
-extern "C" int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C,
+extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t C,
                                  int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
                                  const float* save_mean,
                                  const float* save_rstd, int32_t relu, float* dgamma, float* dbeta, int64_t ld_g,
@@ -356,11 +372,11 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, v
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   const int S = bn_slices(C, M, ch);
   bn_bwd_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
       beta, ld_p, relu, scratch);
   FB_CHECK_CUDA(cudaGetLastError());
   bn_bwd_apply_kernel<<<dim3(S, C), BN_THREADS, 4 * ch * sizeof(float), (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
       (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;

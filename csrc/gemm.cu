@@ -141,6 +141,8 @@ struct GemmArgs {
   int tma_store;    // 1: epilogue stages tiles in smem and stores them with TMA (coalesced, clipped at the edges)
   int chunk_cols;   // columns per TMA store box
   int chunk_bytes;  // bytes per staged row (128 => SWIZZLE_128B box, else unswizzled)
+  int reduce_add;   // 1: TMA reduce-store (fp32 add) instead of a plain store: split-K slices accumulate in place
+  int group_div;    // output group = group / group_div (split-K slices of one problem share an output)
 };
 
 template <bool MN_MAJOR>
@@ -314,9 +316,15 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           fence_async_proxy();   // generic-proxy smem writes -> visible to the TMA (async proxy)
           __syncwarp();
           if (lane == 0) {
-            asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(&tmD),
-                         "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g)
-                         : "memory");
+            if (a.reduce_add) {
+              asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+                           ::"l"(&tmD), "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g / a.group_div)
+                           : "memory");
+            } else {
+              asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(&tmD),
+                           "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g)
+                           : "memory");
+            }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           sbuf ^= 1;
@@ -418,7 +426,9 @@ static int make_store_map(CUtensorMap* m, void* base, int fp32, uint64_t N, uint
 static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream) {
   FB_REQUIRE(p && p->a && p->b && p->d, "fb_grouped_gemm: null operand");
   FB_REQUIRE(p->G >= 1 && p->M >= 1 && p->N >= 1 && p->K >= 1, "fb_grouped_gemm: empty problem");
-  FB_REQUIRE(p->accumulate == 0, "fb_grouped_gemm: accumulate is not implemented");
+  const int group_div = p->out_group_div > 0 ? p->out_group_div : 1;
+  FB_REQUIRE(p->accumulate == 0 || p->d_fp32, "fb_grouped_gemm: accumulate needs an fp32 output");
+  FB_REQUIRE(p->G % group_div == 0, "fb_grouped_gemm: G must be a multiple of out_group_div");
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.d = p->d; a.bias = p->bias; a.d_gs = p->d_gs; a.bias_gs = p->bias_gs;
@@ -435,6 +445,9 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
                 ((uintptr_t)p->d % 16 == 0);
   a.chunk_cols = p->d_fp32 ? (bn >= 32 ? 32 : 16) : (bn >= 64 ? 64 : bn);
   a.chunk_bytes = a.chunk_cols * (int)es;
+  a.reduce_add = p->accumulate ? 1 : 0;
+  a.group_div = group_div;
+  FB_REQUIRE(!a.reduce_add || a.tma_store, "fb_grouped_gemm: accumulate needs a 16-byte aligned output (TMA reduce-store)");
   a.BNpad = mn_major ? (bn + 63) / 64 * 64 : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
   a.m_tiles = (p->M + GEMM_BM - 1) / GEMM_BM;
@@ -480,7 +493,7 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
   CUtensorMap tmD;
   memset(&tmD, 0, sizeof(tmD));
   if (a.tma_store) {
-    rc = make_store_map(&tmD, p->d, p->d_fp32, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)p->G, (uint64_t)p->ldd,
+    rc = make_store_map(&tmD, p->d, p->d_fp32, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)(p->G / group_div), (uint64_t)p->ldd,
                         (uint64_t)p->d_gs, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
     if (rc) return rc;
   }

@@ -18,6 +18,7 @@ reference-compatible ``nn.Module`` so arena segments line up with ``state_dict``
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -50,7 +51,9 @@ class TorchBackend:
         y = torch.bmm(a, b)
         return y if out_dtype is None else y.to(out_dtype)
 
-    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None):
+    grads_prezeroed = False
+
+    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
         """a [C,M,N]^T x b [C,M,K] -> [C,N,K]  (weight gradients; fp32 result, optionally written into ``out``)"""
         r = torch.bmm(a.transpose(1, 2), b).to(out_dtype)
         if out is not None:
@@ -103,12 +106,13 @@ class TorchBackend:
 
     def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True, dgamma_out=None,
                dbeta_out=None):
+        """``dy`` may be a pair of tensors (gradient arriving over the main and the residual path): they are summed."""
         C = x.shape[0]
         ch = x.shape[-1]
-        dyf = dy.float()
+        dyf = (dy[0].float() + dy[1].float()) if isinstance(dy, tuple) else dy.float()
         if relu:
             dyf = dyf * (y > 0)
-        dres = dyf.to(dy.dtype) if want_dres else None
+        dres = dyf.to(x.dtype) if want_dres else None
         d2 = dyf.reshape(C, -1, ch)
         M = d2.shape[1]
         xhat = (x.float().reshape(C, -1, ch) - mean[:, None, :]) * rstd[:, None, :]
@@ -172,15 +176,19 @@ class NativeBackend(TorchBackend):
         self._fb("gemm_nn")
         return super().gemm_nn(a, b, out_dtype)
 
-    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None):
+    def gemm_tn(self, a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
         if self.use_tc_gemm and out_dtype == torch.float32 and self.ops.grouped_gemm_tn_supported(a, b):
-            r = self.ops.grouped_gemm_tn(a, b, out=out)
+            r = self.ops.grouped_gemm_tn(a, b, out=out, out_is_zeroed=out_is_zeroed)
             if out is not None and r is not out:
                 out.copy_(r)
                 return out
             return r
         self._fb("gemm_tn")
         return super().gemm_tn(a, b, out_dtype, out)
+
+    # split-K weight-gradient slices reduce-add into a gradient arena zeroed once per step (FB_PREZERO_GRADS=0:
+    # fp32 partial buffers + a separate sum, for A/B timing)
+    grads_prezeroed = os.environ.get("FB_PREZERO_GRADS", "1") != "0"
 
     def im2col3x3(self, x, stride):
         if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
@@ -204,8 +212,9 @@ class NativeBackend(TorchBackend):
                dbeta_out=None):
         if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
             skip_y = relu and not had_res and beta is not None   # mask recomputed from x: one stream less
-            return self.ops.bn_bwd_stacked(dy, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta,
-                                           dgamma_out=dgamma_out, dbeta_out=dbeta_out)   # grads land in the arena
+            d1, d2 = dy if isinstance(dy, tuple) else (dy, None)
+            return self.ops.bn_bwd_stacked(d1, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta,
+                                           dgamma_out=dgamma_out, dbeta_out=dbeta_out, dy2=d2)   # grads land in the arena
         self._fb("bn_bwd")
         return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres, dgamma_out=dgamma_out, dbeta_out=dbeta_out)
 
@@ -260,10 +269,15 @@ class _Conv:
         cols, Ho, Wo = self._cols(be, x)
         dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
         if self.k == 1 and self.cin == self.cin_real:
-            be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin))    # straight into the gradient arena
+            # straight into the gradient arena (zeroed once per step, so split-K slices can reduce-add in place)
+            be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin), out_is_zeroed=be.grads_prezeroed)
             dWm = None
         else:
-            dWm = be.gemm_tn(dy2, cols)                               # [C, cout, kk*cin] fp32
+            scratch = getattr(self, "_dw_scratch", None)
+            if be.grads_prezeroed and scratch is not None and scratch.shape[0] == C:
+                dWm = be.gemm_tn(dy2, cols, out=scratch, out_is_zeroed=True)
+            else:
+                dWm = be.gemm_tn(dy2, cols)                           # [C, cout, kk*cin] fp32
         if dWm is None:
             pass
         elif self.k == 1:
@@ -357,10 +371,10 @@ class _Block:
             dconv, dbn = self.ds
             a, idt, m, r = saved["ds"]
             da, _ = dbn.bwd(be, d_idt, a, idt, W, G, m, r, relu=False, want_dres=False)
-            d = d + dconv.bwd(be, da, saved["x"], Wm[dconv.name], G[dconv.wname])
+            d = (d, dconv.bwd(be, da, saved["x"], Wm[dconv.name], G[dconv.wname]))
         else:
-            d = d + d_idt
-        return d
+            d = (d, d_idt)
+        return d          # (main path, residual path): the consumer (a BN backward) sums them while loading
 
 
 # ============================================================================ models
@@ -497,9 +511,30 @@ class BatchedResNet(BatchedModel):
         logits = be.gemm_nt(feat, Wm["fc"], out_dtype=torch.float32) + W["fc.bias"][:, None, :]
         return logits, feat, h
 
+    def _zero_grads(self, G):
+        """One memset for the gradient arena and one for the 3x3 weight-gradient scratch (split-K slices of the
+        weight-gradient GEMMs reduce-add into them)."""
+        arena = getattr(G, "arena", None)
+        if arena is None or not self.be.grads_prezeroed:
+            return
+        arena[:, :G.layout.P_train].zero_()
+        C = arena.shape[0]
+        big = getattr(self, "_dw_big", None)
+        need = [c for c in self.convs if not (c.k == 1 and c.cin == c.cin_real)]
+        if big is None or big.shape[0] != C:
+            sizes = [(c.cout * c.k * c.k * c.cin + 3) // 4 * 4 for c in need]
+            big = self._dw_big = torch.zeros((C, sum(sizes)), dtype=torch.float32, device=arena.device)
+            off = 0
+            for c, n in zip(need, sizes):
+                c._dw_scratch = big[:, off:off + c.cout * c.k * c.k * c.cin].view(C, c.cout, c.k * c.k * c.cin)
+                off += n
+        else:
+            big.zero_()
+
     def train_step(self, x, y, W, G, active, row_scale=None):
         be = self.be
         Wm = self.prepare(W)
+        self._zero_grads(G)
         tape: list = []
         logits, feat, h_last = self._forward(x, W, Wm, active, True, tape)
         loss, dlog = be.xent(logits, y, row_scale=row_scale)

@@ -289,19 +289,19 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
                                   i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(rm)),
                                   vp(ptr(rv)), i64(rm.stride(0)), vp(ptr(active)), f32(momentum), f32(eps),
                                   i32(int(relu)), i32(int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
+                                  vp(ptr(nbt)), i64(nbt.stride(0) if nbt is not None and nbt.dim() else 1),
                                   vp(stream_ptr(x.device))), "bn_fwd_stacked")
     count_launch(2 if training else 1)
-    if training:
-        nbt.add_(active.view(nbt.shape) if active is not None else 1.0)
     return y, mean, rstd
 
 
-def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None):
+def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None, dy2=None):
     """``y=None`` (+ ``beta``) recomputes the ReLU mask from x — only valid when the forward had no residual.
     ``dgamma_out`` / ``dbeta_out``: fp32 [C, ch] strided views (e.g. rows of the gradient arena) written in place."""
     Cn, ch = x.shape[0], x.shape[-1]
     M = x.numel() // (Cn * ch)
     dy = dy.contiguous()
+    dy2 = dy2.contiguous() if dy2 is not None else None
     dx = torch.empty_like(x)
     dres = torch.empty_like(x) if want_dres else None
     direct = dgamma_out is not None and dbeta_out is not None and dgamma_out.stride(0) == dbeta_out.stride(0)
@@ -309,7 +309,7 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgam
     dbeta = dbeta_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     ld_g = dgamma.stride(0) if Cn > 1 else max(dgamma.stride(0), ch)
     scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
-    check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
+    check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
                                   i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
                                   vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ld_g), vp(ptr(scratch)),
                                   vp(stream_ptr(x.device))), "bn_bwd_stacked")
@@ -362,16 +362,16 @@ def grouped_gemm_tn_supported(a, b) -> bool:
         and a.shape[2] % 8 == 0 and b.shape[2] % 8 == 0
 
 
-def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None):
+def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, accumulate=False, group_div=1):
     d = torch.empty((G, M, N), dtype=out_dtype, device=a.device) if out is None else out
     p = FbGroupedGemm()
     p.a, p.b, p.d = a.data_ptr(), b.data_ptr(), d.data_ptr()
     p.bias = bias.data_ptr() if bias is not None else None
-    p.a_gs, p.b_gs, p.d_gs = a.stride(0), b.stride(0), (M * N if out is None else (d.stride(0) if G > 1 else M * N))
+    p.a_gs, p.b_gs, p.d_gs = a.stride(0), b.stride(0), (M * N if out is None else (d.stride(0) if d.shape[0] > 1 else M * N))
     p.bias_gs = bias.stride(0) if bias is not None else 0
     p.G, p.M, p.N, p.K = G, M, N, K
     p.lda, p.ldb, p.ldd = a.stride(1), b.stride(1), N
-    p.d_fp32, p.relu, p.accumulate = int(out_dtype == torch.float32), int(relu), 0
+    p.d_fp32, p.relu, p.accumulate, p.out_group_div = int(out_dtype == torch.float32), int(relu), int(accumulate), group_div
     check(fn(C.byref(p), vp(stream_ptr(a.device))), name)
     count_launch()
     return d
@@ -385,7 +385,7 @@ def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
     return _launch_gemm(lib().fb_grouped_gemm_bf16, a, b, G, M, b.shape[1], K, out_dtype, relu, bias, "grouped_gemm")
 
 
-def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None):
+def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
     """d[g] = a[g]^T @ b[g]   (a [G,K,M], b [G,K,N]): weight gradients without transposing activations.
     The output is tiny and the reduction long, so when there are fewer tiles than CTA slots the reduction
     dimension is cut into slices that run as extra groups (split-K) and the fp32 partials are summed."""
@@ -408,6 +408,10 @@ def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None):
     if S == 1:
         return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn",
                             out=out if out_dtype == torch.float32 else None)
+    if out is not None and out_is_zeroed:
+        # split-K slices reduce-add straight into the (pre-zeroed) output with TMA reduce-stores: no partial buffer
+        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
+                            K // S, torch.float32, False, None, "grouped_gemm_tn", out=out, accumulate=True, group_div=S)
     part = _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
                         K // S, torch.float32, False, None, "grouped_gemm_tn")
     if out is not None:

@@ -252,7 +252,8 @@ typedef struct {
   int32_t lda, ldb, ldd; /* row strides in elements (multiples of 8 for bf16, 4 for fp32 out) */
   int32_t d_fp32;     /* 1: fp32 output, 0: bf16 output */
   int32_t relu;       /* fused ReLU epilogue */
-  int32_t accumulate; /* D += result (fp32 output only) */
+  int32_t accumulate; /* D += result (fp32 output only; TMA reduce-store, so concurrent groups may target one output) */
+  int32_t out_group_div; /* > 1: groups g and g' with g / div == g' / div write the same output block (split-K slices) */
 } FbGroupedGemm;
 int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 /* Weight-gradient form: D_g[M][N] = A_g^T * B_g with A_g stored [K][M] and B_g stored [K][N] (M resp. N contiguous,
@@ -276,11 +277,13 @@ int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch);
 int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch, const float* gamma,
                       const float* beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                       const float* active, float momentum, float eps, int32_t relu, int32_t training,
-                      float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream);
+                      float* save_mean, float* save_rstd, float* scratch, float* num_batches_tracked /* fp32 [C] rows, stride ld_n; may be NULL */,
+                      int64_t ld_n, fb_stream_t stream);
 /* dx (and dres = ReLU-masked dy, optional) from dy; dgamma/dbeta fp32 rows with stride ld_g.  The ReLU mask comes
  * from y (forward output; required when the forward had a residual input) or, when y is NULL, is recomputed from
  * x, gamma and beta so that the output tensor is not streamed again. */
-int fb_bn_bwd_stacked(const void* dy, const void* x, const void* y, void* dx, void* dres, int32_t C, int64_t M,
+int fb_bn_bwd_stacked(const void* dy, const void* dy2 /* optional second gradient summed on load */, const void* x,
+                      const void* y, void* dx, void* dres, int32_t C, int64_t M,
                       int32_t ch, const float* gamma, const float* beta, int64_t ld_p, const float* save_mean,
                       const float* save_rstd,
                       int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, float* scratch, fb_stream_t stream);

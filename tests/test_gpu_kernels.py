@@ -486,3 +486,19 @@ def test_native_batched_resnet_step_matches_torch_backend():
     rel = (gn - gt).norm(dim=1) / gt.norm(dim=1)
     assert float(rel.max()) < 0.2, rel
     torch.testing.assert_close(outs["native"][2][:, layout.P_train:], outs["torch"][2][:, layout.P_train:], rtol=5e-2, atol=5e-2)
+
+
+def test_grouped_gemm_tn_split_k_reduce_add_in_place():
+    """Split-K slices accumulate with TMA reduce-stores into a pre-zeroed strided output (rows of a gradient arena)."""
+    from fedml_b200 import ops
+    G, Kred, M, N, P = 3, 2560, 32, 64, 4096
+    torch.manual_seed(0)
+    a = torch.randn(G, Kred, M, device=DEV).to(torch.bfloat16)
+    b = torch.randn(G, Kred, N, device=DEV).to(torch.bfloat16)
+    arena = torch.zeros(G, P, device=DEV)
+    out = arena[:, 128:128 + M * N].view(G, M, N)
+    r = ops.grouped_gemm_tn(a, b, out=out, out_is_zeroed=True)
+    assert r.data_ptr() == out.data_ptr()
+    ref = torch.bmm(a.float().transpose(1, 2), b.float())
+    torch.testing.assert_close(out, ref, rtol=1e-3, atol=5e-2)
+    assert float(arena[:, :128].abs().sum()) == 0 and float(arena[:, 128 + M * N:].abs().sum()) == 0
