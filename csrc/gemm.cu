@@ -3,9 +3,12 @@
 //
 //   for every group g:  D_g[M][N] = op(A_g) * op(B_g)     bf16 operands, fp32 accumulate, bf16/fp32 output
 //
-// Two operand layouts share one kernel template:
-//   NT  (MN_MAJOR = false): A_g is [M][K], B_g is [N][K], K contiguous            (forward / dgrad / Gram)
-//   TN  (MN_MAJOR = true ): A_g is [K][M], B_g is [K][N], M resp. N contiguous    (weight gradients)
+// Three operand layouts share one kernel template (MODE bit 0: A MN-major, bit 1: B MN-major):
+//   NT  (MODE 0): A_g is [M][K], B_g is [N][K], K contiguous                      (forward / Gram / Q*K^T)
+//   TN  (MODE 3): A_g is [K][M], B_g is [K][N], M resp. N contiguous              (weight gradients, P^T*dO)
+//   NN  (MODE 2): A_g is [M][K], B_g is [K][N]                                    (data gradients, P*V)
+// Groups may be two-level (outer, inner) with independent strides (4-D tensor maps), so attention heads are
+// addressed in place inside [batch][seq][heads*dh] buffers.
 //
 // Persistent, warp-specialised CTA of 192 threads (one per SM):
 //   warp 0     TMA producer   (one elected lane): global -> smem ring of STAGES k-blocks (BK = 64)
@@ -63,6 +66,12 @@ __device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, void* smem_d
   asm volatile(
       "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, void* smem_dst, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
@@ -143,9 +152,13 @@ struct GemmArgs {
   int chunk_bytes;  // bytes per staged row (128 => SWIZZLE_128B box, else unswizzled)
   int reduce_add;   // 1: TMA reduce-store (fp32 add) instead of a plain store: split-K slices accumulate in place
   int group_div;    // output group = group / group_div (split-K slices of one problem share an output)
+  int gi;           // inner group count of the two-level group index (g = outer * gi + inner); G when one level
+  int gi_out;       // same for the output group index
+  int64_t d_gs2;    // outer output group stride (pointer-store path)
 };
 
-template <bool MN_MAJOR>
+// MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory)
+template <int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmArgs a) {
@@ -162,6 +175,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
+  constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = a.G * a.m_tiles * a.n_tiles;
 
@@ -197,14 +211,18 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint8_t* sa = smem + (size_t)stage * stage_bytes;
           uint8_t* sb = sa + GEMM_A_BYTES;
           mbar_expect_tx(full_bar + stage, stage_bytes);
-          if (!MN_MAJOR) {
-            tma_load_3d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g);
-            tma_load_3d(&tmB, sb, full_bar + stage, kb * GEMM_BK, nt * a.BN, g);
+          const int g0 = g % a.gi, g1 = g / a.gi;
+          if (!A_MN) {
+            tma_load_4d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g0, g1);
           } else {
             for (int i = 0; i < GEMM_BM / 64; ++i)
-              tma_load_3d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g);
+              tma_load_4d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g0, g1);
+          }
+          if (!B_MN) {
+            tma_load_4d(&tmB, sb, full_bar + stage, kb * GEMM_BK, nt * a.BN, g0, g1);
+          } else {
             for (int i = 0; i < a.BNpad / 64; ++i)
-              tma_load_3d(&tmB, sb + (size_t)i * GEMM_BK * 128, full_bar + stage, nt * a.BN + i * 64, kb * GEMM_BK, g);
+              tma_load_4d(&tmB, sb + (size_t)i * GEMM_BK * 128, full_bar + stage, nt * a.BN + i * 64, kb * GEMM_BK, g0, g1);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -213,7 +231,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = make_idesc(a.BN, MN_MAJOR, MN_MAJOR);
+      const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -228,14 +246,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int k_rem = a.K - kb * GEMM_BK;
           const int k_steps = k_rem >= GEMM_BK ? GEMM_BK / 16 : (k_rem + 15) / 16;
           for (int k = 0; k < k_steps; ++k) {
-            uint64_t ad, bd;
-            if (!MN_MAJOR) {
-              ad = make_smem_desc(sa + k * 32, 16, 1024);
-              bd = make_smem_desc(sb + k * 32, 16, 1024);
-            } else {
-              ad = make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024);
-              bd = make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024);
-            }
+            const uint64_t ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
             umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
           }
           umma_commit(empty_bar + stage);   // smem slot reusable once these MMAs have read it
@@ -260,6 +272,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool row_ok = row < a.M;
       const uint32_t taddr = tmem_base + (uint32_t)(acc * a.BN) + ((uint32_t)(q * 32) << 16);
       const float* bias = a.bias ? a.bias + (size_t)g * a.bias_gs : nullptr;
+      const int og = g / a.group_div, og0 = og % a.gi_out, og1 = og / a.gi_out;
       if (a.tma_store) {
         // TMEM -> registers -> (bias, ReLU, convert) -> swizzled smem rows -> one TMA store per 32-row x chunk box
         const int CW = a.chunk_cols, RB = a.chunk_bytes;
@@ -317,12 +330,12 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           __syncwarp();
           if (lane == 0) {
             if (a.reduce_add) {
-              asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
-                           ::"l"(&tmD), "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g / a.group_div)
+              asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                           ::"l"(&tmD), "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(og0), "r"(og1)
                            : "memory");
             } else {
-              asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(&tmD),
-                           "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(g)
+              asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(&tmD),
+                           "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(og0), "r"(og1)
                            : "memory");
             }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -349,10 +362,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
           }
           if (a.d_fp32) {
-            float* dst = reinterpret_cast<float*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
+            float* dst = reinterpret_cast<float*>(a.d) + (size_t)og1 * a.d_gs2 + (size_t)og0 * a.d_gs + (size_t)row * a.ldd + col0;
             for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = f[i];
           } else {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(a.d) + (size_t)g * a.d_gs + (size_t)row * a.ldd + col0;
+            __nv_bfloat16* dst =
+                reinterpret_cast<__nv_bfloat16*>(a.d) + (size_t)og1 * a.d_gs2 + (size_t)og0 * a.d_gs + (size_t)row * a.ldd + col0;
             for (int i = 0; i < 16 && col0 + i < a.N; ++i) dst[i] = __float2bfloat16_rn(f[i]);
           }
         }
@@ -388,47 +402,57 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
-// 3-D bf16 tensor map: dims (inner, rows, groups), box (64, box_rows, 1), 128B swizzle, zero OOB fill
-static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t groups, uint64_t row_stride_elems,
-                    uint64_t group_stride_elems, uint32_t box_rows) {
+// 4-D bf16 tensor map: dims (inner, rows, inner groups, outer groups), box (64, box_rows, 1, 1), 128B swizzle,
+// zero OOB fill.  A dimension of extent 1 gets a harmless dense stride.
+static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t gi, uint64_t go,
+                    uint64_t row_stride_elems, uint64_t gs_elems, uint64_t gs2_elems, uint32_t box_rows) {
   PFN_encodeTiled enc = get_encode();
   FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-  cuuint64_t dims[3] = {inner, rows, groups};
-  cuuint64_t strides[2] = {row_stride_elems * 2, (groups > 1 ? group_stride_elems : row_stride_elems * rows) * 2};
-  cuuint32_t box[3] = {64, box_rows, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  FB_REQUIRE((strides[0] % 16) == 0 && (strides[1] % 16) == 0 && ((uintptr_t)base % 16) == 0,
+  cuuint64_t dims[4] = {inner, rows, gi, go};
+  const uint64_t dense = row_stride_elems * rows;
+  cuuint64_t strides[3] = {row_stride_elems * 2, (gi > 1 ? gs_elems : dense) * 2, (go > 1 ? gs2_elems : dense * gi) * 2};
+  cuuint32_t box[4] = {64, box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  FB_REQUIRE((strides[0] % 16) == 0 && (strides[1] % 16) == 0 && (strides[2] % 16) == 0 && ((uintptr_t)base % 16) == 0,
              "grouped GEMM operands need 16-byte aligned base pointers and strides");
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code %d", (int)r);
   return FB_OK;
 }
 
-// 3-D output map: dims (N, M, groups), box (chunk_cols, 32, 1); swizzled when a staged row is exactly 128 bytes
-static int make_store_map(CUtensorMap* m, void* base, int fp32, uint64_t N, uint64_t M, uint64_t groups, uint64_t ldd,
-                          uint64_t group_stride_elems, uint32_t chunk_cols, bool swizzle128) {
+// 4-D output map: dims (N, M, inner groups, outer groups), box (chunk_cols, 32, 1, 1); swizzled when a staged row is
+// exactly 128 bytes
+static int make_store_map(CUtensorMap* m, void* base, int fp32, uint64_t N, uint64_t M, uint64_t gi, uint64_t go, uint64_t ldd,
+                          uint64_t gs_elems, uint64_t gs2_elems, uint32_t chunk_cols, bool swizzle128) {
   PFN_encodeTiled enc = get_encode();
   FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   const uint64_t es = fp32 ? 4 : 2;
-  cuuint64_t dims[3] = {N, M, groups};
-  cuuint64_t strides[2] = {ldd * es, (groups > 1 ? group_stride_elems : ldd * M) * es};
-  cuuint32_t box[3] = {chunk_cols, 32, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, base, dims, strides, box,
+  cuuint64_t dims[4] = {N, M, gi, go};
+  const uint64_t dense = ldd * M;
+  cuuint64_t strides[3] = {ldd * es, (gi > 1 ? gs_elems : dense) * es, (go > 1 ? gs2_elems : dense * gi) * es};
+  cuuint32_t box[4] = {chunk_cols, 32, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box,
                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                    CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (output) failed with code %d", (int)r);
   return FB_OK;
 }
 
-static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream) {
+static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
+  const bool a_mn = (mode & 1) != 0, b_mn = (mode & 2) != 0;
   FB_REQUIRE(p && p->a && p->b && p->d, "fb_grouped_gemm: null operand");
   FB_REQUIRE(p->G >= 1 && p->M >= 1 && p->N >= 1 && p->K >= 1, "fb_grouped_gemm: empty problem");
   const int group_div = p->out_group_div > 0 ? p->out_group_div : 1;
   FB_REQUIRE(p->accumulate == 0 || p->d_fp32, "fb_grouped_gemm: accumulate needs an fp32 output");
   FB_REQUIRE(p->G % group_div == 0, "fb_grouped_gemm: G must be a multiple of out_group_div");
+  FB_REQUIRE(group_div == 1 || p->accumulate, "fb_grouped_gemm: out_group_div > 1 needs accumulate");
+  const int gi = p->group_inner > 0 ? p->group_inner : p->G;
+  FB_REQUIRE(p->G % gi == 0, "fb_grouped_gemm: G must be a multiple of group_inner");
+  FB_REQUIRE(group_div == 1 || gi == p->G, "fb_grouped_gemm: out_group_div and group_inner are mutually exclusive");
+  const int go = p->G / gi;
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.d = p->d; a.bias = p->bias; a.d_gs = p->d_gs; a.bias_gs = p->bias_gs;
@@ -441,14 +465,17 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
   }
   a.BN = bn;
   const uint64_t es = p->d_fp32 ? 4 : 2;
-  a.tma_store = (((uint64_t)p->ldd * es) % 16 == 0) && (((uint64_t)p->d_gs * es) % 16 == 0 || p->G == 1) &&
-                ((uintptr_t)p->d % 16 == 0);
+  a.gi = gi;
+  a.gi_out = gi / group_div;
+  a.d_gs2 = p->d_gs2;
+  a.tma_store = (((uint64_t)p->ldd * es) % 16 == 0) && (((uint64_t)p->d_gs * es) % 16 == 0 || a.gi_out == 1) &&
+                (((uint64_t)p->d_gs2 * es) % 16 == 0 || go == 1) && ((uintptr_t)p->d % 16 == 0);
   a.chunk_cols = p->d_fp32 ? (bn >= 32 ? 32 : 16) : (bn >= 64 ? 64 : bn);
   a.chunk_bytes = a.chunk_cols * (int)es;
   a.reduce_add = p->accumulate ? 1 : 0;
   a.group_div = group_div;
   FB_REQUIRE(!a.reduce_add || a.tma_store, "fb_grouped_gemm: accumulate needs a 16-byte aligned output (TMA reduce-store)");
-  a.BNpad = mn_major ? (bn + 63) / 64 * 64 : bn;
+  a.BNpad = b_mn ? (bn + 63) / 64 * 64 : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
   a.m_tiles = (p->M + GEMM_BM - 1) / GEMM_BM;
   a.k_blocks = (p->K + GEMM_BK - 1) / GEMM_BK;
@@ -457,20 +484,21 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
   a.tmem_cols = cols;
   CUtensorMap tmA, tmB;
   int rc;
-  if (!mn_major) {
-    FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm: lda/ldb must be multiples of 8 elements");
-    rc = make_map(&tmA, p->a, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)p->G, (uint64_t)p->lda, (uint64_t)p->a_gs, GEMM_BM);
-    if (rc) return rc;
-    rc = make_map(&tmB, p->b, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)p->G, (uint64_t)p->ldb, (uint64_t)p->b_gs,
-                  (uint32_t)a.BN);
-    if (rc) return rc;
-  } else {
-    FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm_tn: lda/ldb must be multiples of 8 elements");
-    rc = make_map(&tmA, p->a, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)p->G, (uint64_t)p->lda, (uint64_t)p->a_gs, GEMM_BK);
-    if (rc) return rc;
-    rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)p->G, (uint64_t)p->ldb, (uint64_t)p->b_gs, GEMM_BK);
-    if (rc) return rc;
-  }
+  FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm: lda/ldb must be multiples of 8 elements");
+  if (!a_mn)
+    rc = make_map(&tmA, p->a, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)gi, (uint64_t)go, (uint64_t)p->lda, (uint64_t)p->a_gs,
+                  (uint64_t)p->a_gs2, GEMM_BM);
+  else
+    rc = make_map(&tmA, p->a, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)gi, (uint64_t)go, (uint64_t)p->lda, (uint64_t)p->a_gs,
+                  (uint64_t)p->a_gs2, GEMM_BK);
+  if (rc) return rc;
+  if (!b_mn)
+    rc = make_map(&tmB, p->b, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
+                  (uint64_t)p->b_gs2, (uint32_t)a.BN);
+  else
+    rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
+                  (uint64_t)p->b_gs2, GEMM_BK);
+  if (rc) return rc;
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
   const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/;
   // two co-resident CTAs per SM hide each other's per-tile latencies (TMEM allows it while 2 x tmem_cols <= 512)
@@ -493,23 +521,27 @@ static int launch_gemm(const FbGroupedGemm* p, bool mn_major, fb_stream_t stream
   CUtensorMap tmD;
   memset(&tmD, 0, sizeof(tmD));
   if (a.tma_store) {
-    rc = make_store_map(&tmD, p->d, p->d_fp32, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)(p->G / group_div), (uint64_t)p->ldd,
-                        (uint64_t)p->d_gs, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
+    rc = make_store_map(&tmD, p->d, p->d_fp32, (uint64_t)p->N, (uint64_t)p->M, (uint64_t)a.gi_out, (uint64_t)go, (uint64_t)p->ldd,
+                        (uint64_t)p->d_gs, (uint64_t)p->d_gs2, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
     if (rc) return rc;
   }
   const int total = a.G * a.m_tiles * a.n_tiles;
   int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
-  if (mn_major) {
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<true><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+  if (mode == 3) {
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grouped_gemm_kernel<3><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+  } else if (mode == 2) {
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grouped_gemm_kernel<2><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   } else {
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<false><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    grouped_gemm_kernel<0><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   }
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
 
-extern "C" int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, false, stream); }
-extern "C" int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, true, stream); }
+extern "C" int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 0, stream); }
+extern "C" int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 3, stream); }
+extern "C" int fb_grouped_gemm_nn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 2, stream); }

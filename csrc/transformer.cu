@@ -1,0 +1,631 @@
+// K12 helpers: client-stacked transformer-encoder kernels (DistilBERT family) around the tcgen05 grouped GEMM.
+// See include/fedml_b200.h.  The GEMM-shaped work (QKV / output / FFN projections, Q*K^T, P*V and every
+// gradient product) runs on fb_grouped_gemm_{bf16,tn_bf16,nn_bf16} with two-level (batch, head) groups; the
+// kernels here are the bandwidth-bound glue, each a single pass over bf16 activations with fp32 arithmetic:
+//
+//   embed_gather / embed_bwd     word + position embedding rows of the fp32 arena -> bf16, and its scatter-add
+//   add_ln_fwd / ln_bwd          (residual add +) LayerNorm, one warp per token row, statistics in registers
+//   softmax_fwd / softmax_bwd    scaled, key-masked softmax over fp32 score rows -> bf16 probabilities
+//   act_fwd / act_bwd            exact (erf) GELU and ReLU
+//   dropout                      Philox-keyed inverted dropout (the backward pass re-derives the same mask)
+//   colsum                       bias gradients (column sums of bf16 gradient matrices), deterministic
+//
+// Layout: activations are [C clients][R = B*S token rows][D], D fastest; per-client parameters are rows of the
+// stacked fp32 arena (row stride ld).  Everything is deterministic except embed_bwd's word-row scatter, which
+// uses fp32 atomics (repeated tokens collide).
+#include "common.cuh"
+#include "../include/fedml_b200.h"
+
+#define TF_THREADS 256
+#define TF_WARPS 8
+#define LN_MAXV 4      /* 8-element vectors per lane: D <= 32 * 8 * 4 = 1024 */
+
+namespace {
+
+__device__ __forceinline__ void unpack8(const uint4& r, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 r;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return r;
+}
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void ld8f(const float* p, float* f) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+  f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ float bf16_round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ---------------------------------------------------------------- embeddings
+// out[c][r][:] = word[c][ids[c][r]][:] + pos[c][r % S][:]
+__global__ void __launch_bounds__(TF_THREADS)
+embed_gather_kernel(const int64_t* __restrict__ ids, const float* __restrict__ word, const float* __restrict__ pos,
+                    int64_t ld, __nv_bfloat16* __restrict__ out, int64_t R, int S, int D, int vocab) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
+  const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
+  if (r >= R) return;
+  int64_t id = ids[(size_t)c * R + r];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const float* w = word + (size_t)c * ld + (size_t)id * D;
+  const float* p = pos + (size_t)c * ld + (size_t)(r % S) * D;
+  __nv_bfloat16* o = out + ((size_t)c * R + r) * D;
+  for (int k = lane * 8; k < D; k += 256) {
+    float a[8], b[8];
+    ld8f(w + k, a);
+    ld8f(p + k, b);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) a[e] += b[e];
+    *reinterpret_cast<uint4*>(o + k) = pack8(a);
+  }
+}
+
+// gword[c][ids[c][r]][:] += dz[c][r][:]   (fp32 atomics: tokens repeat)
+__global__ void __launch_bounds__(TF_THREADS)
+embed_word_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dz, float* __restrict__ gword,
+                      int64_t ld, int64_t R, int D, int vocab) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
+  const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
+  if (r >= R) return;
+  int64_t id = ids[(size_t)c * R + r];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  float* g = gword + (size_t)c * ld + (size_t)id * D;
+  const __nv_bfloat16* d = dz + ((size_t)c * R + r) * D;
+  for (int k = lane * 8; k < D; k += 256) {
+    float f[8];
+    unpack8(ldg16(d + k), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) atomicAdd(g + k + e, f[e]);
+  }
+}
+
+// gpos[c][s][:] = sum_b dz[c][b*S + s][:]   (deterministic: one thread owns 8 columns of one position)
+__global__ void __launch_bounds__(TF_THREADS)
+embed_pos_bwd_kernel(const __nv_bfloat16* __restrict__ dz, float* __restrict__ gpos, int64_t ld, int B, int S, int D) {
+  const int c = blockIdx.y;
+  const int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x;     // vector index inside [S][D/8]
+  const int nv = D / 8;
+  if (v >= (int64_t)S * nv) return;
+  const int s = (int)(v / nv), k = (int)(v % nv) * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int b = 0; b < B; ++b) {
+    float f[8];
+    unpack8(ldg16(dz + (((size_t)c * B + b) * S + s) * D + k), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] += f[e];
+  }
+  float* g = gpos + (size_t)c * ld + (size_t)s * D + k;
+  *reinterpret_cast<float4*>(g) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  *reinterpret_cast<float4*>(g + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+}
+
+// ---------------------------------------------------------------- (add +) LayerNorm forward
+// z = bf16(a + b)  (b optional);  y = (z - mean) * rstd * gamma + beta.  One warp per token row; the row lives in
+// registers (LN_MAXV vectors of 8 per lane), statistics are exact two-pass over the bf16-rounded z so that the
+// backward pass, which re-reads z, sees the same x-hat.
+__global__ void __launch_bounds__(TF_THREADS)
+add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ z,
+                  __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                  const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p, int64_t R, int D, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
+  const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
+  if (r >= R) return;
+  const int nv = D >> 3;
+  const size_t base = ((size_t)c * R + r) * D;
+  float v[LN_MAXV][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+      unpack8(ldg16(a + base + idx * 8), v[i]);
+      if (b) {
+        float t[8];
+        unpack8(ldg16(b + base + idx * 8), t);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[i][e] = bf16_round(v[i][e] + t[e]);
+        if (z) *reinterpret_cast<uint4*>(z + base + idx * 8) = pack8(v[i]);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) sum += v[i][e];
+    }
+  }
+  const float mean = warp_sum(sum) / (float)D;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i)
+    if (i * 32 + lane < nv) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float d = v[i][e] - mean;
+        sq += d * d;
+      }
+    }
+  const float rstd = rsqrtf(warp_sum(sq) / (float)D + eps);
+  if (lane == 0) {
+    mean_out[(size_t)c * R + r] = mean;
+    rstd_out[(size_t)c * R + r] = rstd;
+  }
+  const float* g = gamma + (size_t)c * ld_p;
+  const float* bt = beta + (size_t)c * ld_p;
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+      float gg[8], bb[8], o[8];
+      ld8f(g + idx * 8, gg);
+      ld8f(bt + idx * 8, bb);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = (v[i][e] - mean) * rstd * gg[e] + bb[e];
+      *reinterpret_cast<uint4*>(y + base + idx * 8) = pack8(o);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- LayerNorm backward
+// g = (dy + dy2) * gamma;  dz = rstd * (g - mean_D(g) - xhat * mean_D(g * xhat));  per-CTA partial sums of
+// dgamma = sum_rows (dy + dy2) * xhat and dbeta = sum_rows (dy + dy2) go to partial[c][slice][2][D].
+__global__ void __launch_bounds__(TF_THREADS)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ z,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
+              int64_t ld_p, __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, int64_t R, int D, int slices) {
+  __shared__ float red[2 * 32 * 8 * LN_MAXV];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y, s = blockIdx.x;
+  const int nv = D >> 3;
+  const int64_t rows_per = (R + slices - 1) / slices;
+  const int64_t r0 = (int64_t)s * rows_per, r1 = min(R, r0 + rows_per);
+  float gam[LN_MAXV][8], ag[LN_MAXV][8], ab[LN_MAXV][8];
+#pragma unroll
+  for (int i = 0; i < LN_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ag[i][e] = ab[i][e] = gam[i][e] = 0.f;
+    if (idx < nv) ld8f(gamma + (size_t)c * ld_p + idx * 8, gam[i]);
+  }
+  const float invD = 1.f / (float)D;
+  for (int64_t r = r0 + warp; r < r1; r += TF_WARPS) {
+    const size_t base = ((size_t)c * R + r) * D;
+    const float mean = mean_in[(size_t)c * R + r], rstd = rstd_in[(size_t)c * R + r];
+    float d[LN_MAXV][8], xh[LN_MAXV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+      const int idx = i * 32 + lane;
+      if (idx < nv) {
+        unpack8(ldg16(dy + base + idx * 8), d[i]);
+        if (dy2) {
+          float t[8];
+          unpack8(ldg16(dy2 + base + idx * 8), t);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) d[i][e] += t[e];
+        }
+        unpack8(ldg16(z + base + idx * 8), xh[i]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          xh[i][e] = (xh[i][e] - mean) * rstd;
+          ag[i][e] += d[i][e] * xh[i][e];
+          ab[i][e] += d[i][e];
+          const float g = d[i][e] * gam[i][e];
+          s1 += g;
+          s2 += g * xh[i][e];
+        }
+      }
+    }
+    s1 = warp_sum(s1) * invD;
+    s2 = warp_sum(s2) * invD;
+#pragma unroll
+    for (int i = 0; i < LN_MAXV; ++i) {
+      const int idx = i * 32 + lane;
+      if (idx < nv) {
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = rstd * (d[i][e] * gam[i][e] - s1 - xh[i][e] * s2);
+        *reinterpret_cast<uint4*>(dz + base + idx * 8) = pack8(o);
+      }
+    }
+  }
+  // deterministic cross-warp reduction: warps add their registers into shared memory one after another
+  for (int w = 0; w < TF_WARPS; ++w) {
+    if (warp == w) {
+#pragma unroll
+      for (int i = 0; i < LN_MAXV; ++i)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int k = (i * 32 + lane) * 8 + e;
+          if (w == 0) {
+            red[k] = ag[i][e];
+            red[32 * 8 * LN_MAXV + k] = ab[i][e];
+          } else {
+            red[k] += ag[i][e];
+            red[32 * 8 * LN_MAXV + k] += ab[i][e];
+          }
+        }
+    }
+    __syncthreads();
+  }
+  float* out = partial + ((size_t)c * slices + s) * 2 * D;
+  for (int k = threadIdx.x; k < D; k += TF_THREADS) {
+    out[k] = red[k];
+    out[D + k] = red[32 * 8 * LN_MAXV + k];
+  }
+}
+
+__global__ void __launch_bounds__(TF_THREADS)
+ln_bwd_finish_kernel(const float* __restrict__ partial, int slices, int D, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     int64_t ld_g) {
+  const int c = blockIdx.y, k = blockIdx.x * TF_THREADS + threadIdx.x;
+  if (k >= 2 * D) return;
+  float acc = 0.f;
+  for (int s = 0; s < slices; ++s) acc += partial[((size_t)c * slices + s) * 2 * D + k];
+  if (k < D) dgamma[(size_t)c * ld_g + k] = acc;
+  else dbeta[(size_t)c * ld_g + (k - D)] = acc;
+}
+
+// ---------------------------------------------------------------- dropout mask
+// Eight keep/drop decisions for the 8-element vector `v` of a tensor: one Philox block keyed (seed, step, site),
+// one 16-bit uniform per element.  Forward and backward passes regenerate identical masks from the same key.
+struct DropKey {
+  uint64_t seed;
+  uint32_t site, step, thresh;
+  float keep_scale;
+};
+__device__ __forceinline__ DropKey make_drop_key(float p, uint64_t seed, uint32_t site, const uint32_t* step_dev) {
+  DropKey k;
+  k.seed = seed;
+  k.site = site;
+  k.step = step_dev ? *step_dev : 0u;
+  k.thresh = (uint32_t)(p * 65536.f);
+  k.keep_scale = 1.f / (1.f - p);
+  return k;
+}
+__device__ __forceinline__ void drop_apply8(const DropKey& k, int64_t v, float* f) {
+  const Philox4 r = philox4x32_10((uint32_t)v, (uint32_t)((uint64_t)v >> 32), k.site, k.step, (uint32_t)k.seed,
+                                  (uint32_t)(k.seed >> 32));
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const uint32_t u = (w[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+    f[e] = u >= k.thresh ? f[e] * k.keep_scale : 0.f;
+  }
+}
+
+// ---------------------------------------------------------------- attention softmax
+// P[row][j] = softmax_j(scale * scores[row][j] + (key_mask[j] ? 0 : -inf));  Pd = dropout(P) when p > 0.
+// rows = groups * S with group = (client*batch) * H + head; key_mask is [client*batch][S] (1 = attend) or null.
+// One warp per row, a lane owns SM_MAXV vectors of 8 consecutive keys (S % 8 == 0, S <= 256 * SM_MAXV).
+#define SM_MAXV 2
+__global__ void __launch_bounds__(TF_THREADS)
+softmax_fwd_kernel(const float* __restrict__ scores, __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ Pd,
+                   const float* __restrict__ key_mask, int64_t rows, int S, int H, float scale, float p, uint64_t seed,
+                   uint32_t site, const uint32_t* __restrict__ step_dev) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * TF_WARPS + warp;
+  if (row >= rows) return;
+  const int nv = S >> 3;
+  const float* src = scores + (size_t)row * S;
+  const float* mk = key_mask ? key_mask + (size_t)(row / S / H) * S : nullptr;
+  float v[SM_MAXV][8];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < SM_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[i][e] = -INFINITY;
+    if (idx < nv) {
+      float m[8];
+      ld8f(src + idx * 8, v[i]);
+      if (mk) ld8f(mk + idx * 8, m);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        v[i][e] = (mk && m[e] == 0.f) ? -INFINITY : v[i][e] * scale;
+        mx = fmaxf(mx, v[i][e]);
+      }
+    }
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < SM_MAXV; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      v[i][e] = (mx == -INFINITY) ? 0.f : __expf(v[i][e] - mx);
+      sum += v[i][e];
+    }
+  sum = warp_sum(sum);
+  const float inv = sum > 0.f ? 1.f / sum : 0.f;
+  const DropKey key = make_drop_key(p, seed, site, step_dev);
+#pragma unroll
+  for (int i = 0; i < SM_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[i][e] = bf16_round(v[i][e] * inv);
+      *reinterpret_cast<uint4*>(P + (size_t)row * S + idx * 8) = pack8(v[i]);
+      if (p > 0.f) {
+        drop_apply8(key, (int64_t)row * nv + idx, v[i]);
+        *reinterpret_cast<uint4*>(Pd + (size_t)row * S + idx * 8) = pack8(v[i]);
+      }
+    }
+  }
+}
+
+// dS = scale * P * (dP' - sum_j dP'_j P_j)   with dP' = dropout-backward(dP) when p > 0
+__global__ void __launch_bounds__(TF_THREADS)
+softmax_bwd_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ dS,
+                   int64_t rows, int S, float scale, float p, uint64_t seed, uint32_t site,
+                   const uint32_t* __restrict__ step_dev) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * TF_WARPS + warp;
+  if (row >= rows) return;
+  const int nv = S >> 3;
+  const DropKey key = make_drop_key(p, seed, site, step_dev);
+  float pv[SM_MAXV][8], gv[SM_MAXV][8];
+  float dot = 0.f;
+#pragma unroll
+  for (int i = 0; i < SM_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) pv[i][e] = gv[i][e] = 0.f;
+    if (idx < nv) {
+      unpack8(ldg16(P + (size_t)row * S + idx * 8), pv[i]);
+      ld8f(dP + (size_t)row * S + idx * 8, gv[i]);
+      if (p > 0.f) drop_apply8(key, (int64_t)row * nv + idx, gv[i]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) dot += pv[i][e] * gv[i][e];
+    }
+  }
+  dot = warp_sum(dot);
+#pragma unroll
+  for (int i = 0; i < SM_MAXV; ++i) {
+    const int idx = i * 32 + lane;
+    if (idx < nv) {
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = scale * pv[i][e] * (gv[i][e] - dot);
+      *reinterpret_cast<uint4*>(dS + (size_t)row * S + idx * 8) = pack8(o);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- activations / dropout / bias gradients
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_grad(float x) {
+  return 0.5f * (1.f + erff(x * 0.70710678118654752f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+
+// mode 0: ReLU, 1: GELU (erf)
+__global__ void __launch_bounds__(TF_THREADS)
+act_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t nvec, int mode) {
+  for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
+    float f[8];
+    unpack8(ldg16(x + v * 8), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = mode ? gelu_f(f[e]) : fmaxf(f[e], 0.f);
+    *reinterpret_cast<uint4*>(y + v * 8) = pack8(f);
+  }
+}
+// dx = dy * act'(x)   (x = pre-activation)
+__global__ void __launch_bounds__(TF_THREADS)
+act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dx,
+               int64_t nvec, int mode) {
+  for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
+    float f[8], g[8];
+    unpack8(ldg16(x + v * 8), f);
+    unpack8(ldg16(dy + v * 8), g);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) g[e] *= mode ? gelu_grad(f[e]) : (f[e] > 0.f ? 1.f : 0.f);
+    *reinterpret_cast<uint4*>(dx + v * 8) = pack8(g);
+  }
+}
+
+// y = dropout(x (+ x2)): inverted dropout, mask from drop_apply8 over the flattened tensor
+__global__ void __launch_bounds__(TF_THREADS)
+dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, __nv_bfloat16* __restrict__ y,
+               int64_t nvec, float p, uint64_t seed, uint32_t site, const uint32_t* __restrict__ step_dev) {
+  const DropKey key = make_drop_key(p, seed, site, step_dev);
+  for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
+    float f[8];
+    unpack8(ldg16(x + v * 8), f);
+    if (x2) {
+      float t[8];
+      unpack8(ldg16(x2 + v * 8), t);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] += t[e];
+    }
+    drop_apply8(key, v, f);
+    *reinterpret_cast<uint4*>(y + v * 8) = pack8(f);
+  }
+}
+
+// out[c][n] = sum_r x[c][r][n]: 32 row lanes x 8 column vectors per CTA, fixed summation order
+__global__ void __launch_bounds__(TF_THREADS)
+colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t R, int N, int64_t ldx, int64_t cs, float* __restrict__ out,
+              int64_t ld_o) {
+  __shared__ float red[32][65];
+  const int c = blockIdx.y, tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+  const int col = blockIdx.x * 64 + tx * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (col < N) {
+    const __nv_bfloat16* base = x + (size_t)c * cs + col;
+    for (int64_t r = ty; r < R; r += 32) {
+      float f[8];
+      unpack8(ldg16(base + (size_t)r * ldx), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += f[e];
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[ty][tx * 8 + e] = acc[e];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float s = 0.f;
+    for (int r = 0; r < 32; ++r) s += red[r][threadIdx.x];
+    const int n = blockIdx.x * 64 + threadIdx.x;
+    if (n < N) out[(size_t)c * ld_o + n] = s;
+  }
+}
+
+static int ew_grid(int64_t nvec) {
+  int64_t g = (nvec + TF_THREADS - 1) / TF_THREADS;
+  const int64_t cap = (int64_t)fb_num_sms() * 16;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+// ================================================================ C ABI
+#define TF_ALIGNED16(p) (((uintptr_t)(p) & 15) == 0)
+
+extern "C" int fb_embed_gather(const int64_t* ids, const float* word, const float* pos, int64_t ld, void* out_bf16,
+                               int32_t C, int64_t R, int32_t S, int32_t D, int32_t vocab, fb_stream_t stream) {
+  FB_REQUIRE(ids && word && pos && out_bf16, "fb_embed_gather: null pointer");
+  FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && S >= 1 && R % S == 0 && D >= 8 && D % 8 == 0 && vocab >= 1,
+             "fb_embed_gather: bad shape");
+  FB_REQUIRE(ld % 4 == 0 && TF_ALIGNED16(word) && TF_ALIGNED16(pos) && TF_ALIGNED16(out_bf16),
+             "fb_embed_gather: tables and output must be 16-byte aligned");
+  embed_gather_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      ids, word, pos, ld, (__nv_bfloat16*)out_bf16, R, S, D, vocab);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_embed_bwd(const int64_t* ids, const void* dz_bf16, float* gword, float* gpos, int64_t ld, int32_t C,
+                            int64_t R, int32_t S, int32_t D, int32_t vocab, fb_stream_t stream) {
+  FB_REQUIRE(ids && dz_bf16 && gword && gpos, "fb_embed_bwd: null pointer");
+  FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && S >= 1 && R % S == 0 && D >= 8 && D % 8 == 0 && vocab >= 1,
+             "fb_embed_bwd: bad shape");
+  FB_REQUIRE(ld % 4 == 0 && TF_ALIGNED16(gpos) && TF_ALIGNED16(dz_bf16), "fb_embed_bwd: buffers must be 16-byte aligned");
+  embed_word_bwd_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      ids, (const __nv_bfloat16*)dz_bf16, gword, ld, R, D, vocab);
+  const int64_t nv = (int64_t)S * (D / 8);
+  embed_pos_bwd_kernel<<<dim3((unsigned)((nv + TF_THREADS - 1) / TF_THREADS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dz_bf16, gpos, ld, (int)(R / S), S, D);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_add_ln_fwd(const void* a, const void* b, void* z, void* y, float* mean, float* rstd, const float* gamma,
+                             const float* beta, int64_t ld_p, int32_t C, int64_t R, int32_t D, float eps,
+                             fb_stream_t stream) {
+  FB_REQUIRE(a && y && mean && rstd && gamma && beta, "fb_add_ln_fwd: null pointer");
+  FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && D >= 8 && D % 8 == 0 && D <= 256 * LN_MAXV,
+             "fb_add_ln_fwd: D must be a multiple of 8 and at most %d", 256 * LN_MAXV);
+  FB_REQUIRE(ld_p % 4 == 0 && TF_ALIGNED16(gamma) && TF_ALIGNED16(beta) && TF_ALIGNED16(a) && TF_ALIGNED16(y),
+             "fb_add_ln_fwd: buffers must be 16-byte aligned");
+  add_ln_fwd_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)z, (__nv_bfloat16*)y, mean, rstd, gamma, beta, ld_p, R,
+      D, eps);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+static int ln_slices(int C, int64_t R) {
+  int64_t want = (4 * (int64_t)fb_num_sms() + C - 1) / C;
+  const int64_t max_s = (R + 31) / 32;   // at least four rows per warp
+  if (want > max_s) want = max_s;
+  if (want < 1) want = 1;
+  if (want > 128) want = 128;
+  return (int)want;
+}
+extern "C" int64_t fb_ln_bwd_scratch_floats(int32_t C, int64_t R, int32_t D) { return (int64_t)C * ln_slices(C, R) * 2 * D; }
+
+extern "C" int fb_ln_bwd(const void* dy, const void* dy2, const void* z, const float* mean, const float* rstd,
+                         const float* gamma, int64_t ld_p, void* dz, float* dgamma, float* dbeta, int64_t ld_g,
+                         float* scratch, int32_t C, int64_t R, int32_t D, fb_stream_t stream) {
+  FB_REQUIRE(dy && z && mean && rstd && gamma && dz && dgamma && dbeta && scratch, "fb_ln_bwd: null pointer");
+  FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && D >= 8 && D % 8 == 0 && D <= 256 * LN_MAXV,
+             "fb_ln_bwd: D must be a multiple of 8 and at most %d", 256 * LN_MAXV);
+  FB_REQUIRE(ld_p % 4 == 0 && TF_ALIGNED16(gamma) && TF_ALIGNED16(dy) && TF_ALIGNED16(z) && TF_ALIGNED16(dz),
+             "fb_ln_bwd: buffers must be 16-byte aligned");
+  const int S = ln_slices(C, R);
+  ln_bwd_kernel<<<dim3(S, C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)z, mean, rstd, gamma, ld_p, (__nv_bfloat16*)dz,
+      scratch, R, D, S);
+  ln_bwd_finish_kernel<<<dim3((2 * D + TF_THREADS - 1) / TF_THREADS, C), TF_THREADS, 0, (cudaStream_t)stream>>>(scratch, S, D, dgamma,
+                                                                                                            dbeta, ld_g);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_attn_softmax_fwd(const float* scores, void* P_bf16, void* Pdrop_bf16, const float* key_mask, int64_t groups,
+                                   int32_t S, int32_t H, float scale, float p, uint64_t seed, uint32_t site,
+                                   const uint32_t* step_dev, fb_stream_t stream) {
+  FB_REQUIRE(scores && P_bf16 && groups >= 1 && H >= 1, "fb_attn_softmax_fwd: bad arguments");
+  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= 256 * SM_MAXV, "fb_attn_softmax_fwd: S must be a multiple of 8 and at most %d",
+             256 * SM_MAXV);
+  FB_REQUIRE(p >= 0.f && p < 1.f && (p == 0.f || Pdrop_bf16), "fb_attn_softmax_fwd: dropout needs 0 <= p < 1 and a Pdrop buffer");
+  FB_REQUIRE(TF_ALIGNED16(scores) && TF_ALIGNED16(P_bf16) && TF_ALIGNED16(Pdrop_bf16) && TF_ALIGNED16(key_mask),
+             "fb_attn_softmax_fwd: buffers must be 16-byte aligned");
+  const int64_t rows = groups * S;
+  softmax_fwd_kernel<<<(unsigned)((rows + TF_WARPS - 1) / TF_WARPS), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      scores, (__nv_bfloat16*)P_bf16, (__nv_bfloat16*)Pdrop_bf16, key_mask, rows, S, H, scale, p, seed, site, step_dev);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_attn_softmax_bwd(const float* dP, const void* P_bf16, void* dS_bf16, int64_t groups, int32_t S, float scale,
+                                   float p, uint64_t seed, uint32_t site, const uint32_t* step_dev, fb_stream_t stream) {
+  FB_REQUIRE(dP && P_bf16 && dS_bf16 && groups >= 1, "fb_attn_softmax_bwd: bad arguments");
+  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= 256 * SM_MAXV, "fb_attn_softmax_bwd: S must be a multiple of 8 and at most %d",
+             256 * SM_MAXV);
+  FB_REQUIRE(p >= 0.f && p < 1.f, "fb_attn_softmax_bwd: 0 <= p < 1");
+  FB_REQUIRE(TF_ALIGNED16(dP) && TF_ALIGNED16(P_bf16) && TF_ALIGNED16(dS_bf16), "fb_attn_softmax_bwd: buffers must be 16-byte aligned");
+  const int64_t rows = groups * S;
+  softmax_bwd_kernel<<<(unsigned)((rows + TF_WARPS - 1) / TF_WARPS), TF_THREADS, 0, (cudaStream_t)stream>>>(
+      dP, (const __nv_bfloat16*)P_bf16, (__nv_bfloat16*)dS_bf16, rows, S, scale, p, seed, site, step_dev);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_act_fwd(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
+  FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(y),
+             "fb_act_fwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
+  act_fwd_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8, mode);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_act_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream) {
+  FB_REQUIRE(dy && x && dx && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(dy) &&
+                 TF_ALIGNED16(dx),
+             "fb_act_bwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
+  act_bwd_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
+                                                                       (__nv_bfloat16*)dx, n / 8, mode);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_dropout_bf16(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
+                               const uint32_t* step_dev, fb_stream_t stream) {
+  FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && p >= 0.f && p < 1.f && TF_ALIGNED16(x) && TF_ALIGNED16(x2) && TF_ALIGNED16(y),
+             "fb_dropout_bf16: n must be a multiple of 8, buffers 16-byte aligned, 0 <= p < 1");
+  dropout_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)x2,
+                                                                       (__nv_bfloat16*)y, n / 8, p, seed, site, step_dev);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_colsum_bf16(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
+                              int64_t ld_o, fb_stream_t stream) {
+  FB_REQUIRE(x && out && C >= 1 && C <= 65535 && R >= 1 && N >= 8 && N % 8 == 0 && ldx % 8 == 0 && client_stride % 8 == 0 &&
+                 TF_ALIGNED16(x),
+             "fb_colsum_bf16: N, ldx and the client stride must be multiples of 8, x 16-byte aligned");
+  colsum_kernel<<<dim3((N + 63) / 64, C), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, R, N, ldx, client_stride,
+                                                                              out, ld_o);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}

@@ -140,6 +140,99 @@ class TorchBackend:
         """uint8 [C,B,H,W,3] -> normalised activations in the compute dtype."""
         return ((x_u8.float() / 255.0 - mean) / std).to(self.dtype)
 
+    # ---- transformer primitives (models/batched_nlp.py) -----------------------------------
+    def mm(self, mode, a, b, out=None, out_dtype=None, bias=None, relu=False):
+        """Grouped product over any leading dims: nt = a b^T, nn = a b, tn = a^T b (fp32 accumulate)."""
+        af, bf = a.float(), b.float()
+        if mode == "nt":
+            y = af @ bf.transpose(-1, -2)
+        elif mode == "nn":
+            y = af @ bf
+        else:
+            y = af.transpose(-1, -2) @ bf
+        if bias is not None:
+            y = y + bias[..., None, :]
+        if relu:
+            y = torch.relu(y)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y.to(out_dtype or a.dtype)
+
+    def embed_fwd(self, ids, word, pos, S):
+        C, R = ids.shape
+        D = word.shape[2]
+        w = torch.gather(word, 1, ids[..., None].expand(C, R, D))
+        return (w + pos[:, :S].repeat(1, R // S, 1)).to(self.dtype)
+
+    def embed_bwd(self, ids, dz, gword, gpos, S):
+        """gword must be zero on entry (sparse scatter-add); gpos is overwritten."""
+        C, R = ids.shape
+        D = gword.shape[2]
+        gword.scatter_add_(1, ids[..., None].expand(C, R, D), dz.float())
+        gpos.zero_()
+        gpos[:, :S] = dz.float().view(C, R // S, S, D).sum(dim=1)
+
+    def ln_fwd(self, a, b, gamma, beta, eps):
+        z = a if b is None else (a.float() + b.float()).to(a.dtype)
+        zf = z.float()
+        mean = zf.mean(dim=-1)
+        rstd = torch.rsqrt(zf.var(dim=-1, unbiased=False) + eps)
+        y = (zf - mean[..., None]) * rstd[..., None] * gamma[:, None, :] + beta[:, None, :]
+        return y.to(a.dtype), z, mean, rstd
+
+    def ln_bwd(self, dy, dy2, z, mean, rstd, gamma, dgamma_out, dbeta_out):
+        d = dy.float() if dy2 is None else dy.float() + dy2.float()
+        xh = (z.float() - mean[..., None]) * rstd[..., None]
+        dgamma_out.copy_((d * xh).sum(dim=1))
+        dbeta_out.copy_(d.sum(dim=1))
+        g = d * gamma[:, None, :]
+        dz = rstd[..., None] * (g - g.mean(dim=-1, keepdim=True) - xh * (g * xh).mean(dim=-1, keepdim=True))
+        return dz.to(z.dtype)
+
+    def _drop_mask(self, shape, p, seed, site, step, device):
+        g = torch.Generator(device="cpu").manual_seed((int(seed) * 1000003 + int(site) * 7919 + int(step)) % (2 ** 63))
+        return (torch.rand(shape, generator=g) >= p).to(device)
+
+    def dropout(self, x, p, seed, site, step_dev=None, x2=None):
+        if x2 is not None:
+            x = (x.float() + x2.float()).to(x.dtype)
+        if p <= 0:
+            return x
+        step = int(step_dev.item()) if step_dev is not None else 0
+        return (x.float() * self._drop_mask(x.shape, p, seed, site, step, x.device) / (1.0 - p)).to(x.dtype)
+
+    def softmax_fwd(self, scores, key_mask, H, scale, p=0.0, seed=0, site=0, step_dev=None):
+        """scores fp32 [CB,H,S,S]; key_mask [CB,S] (1 = attend) -> (P, dropout(P)) in the compute dtype."""
+        s = scores.float() * scale
+        if key_mask is not None:
+            s = s.masked_fill(key_mask[:, None, None, :] == 0, float("-inf"))
+        P = torch.softmax(s, dim=-1).to(self.dtype)
+        return P, (self.dropout(P, p, seed, site, step_dev) if p > 0 else P)
+
+    def softmax_bwd(self, dP, P, scale, p=0.0, seed=0, site=0, step_dev=None):
+        g = dP.float()
+        if p > 0:
+            step = int(step_dev.item()) if step_dev is not None else 0
+            g = g * self._drop_mask(g.shape, p, seed, site, step, g.device) / (1.0 - p)
+        Pf = P.float()
+        return (scale * Pf * (g - (g * Pf).sum(dim=-1, keepdim=True))).to(self.dtype)
+
+    def act_fwd(self, x, kind):
+        return (F.gelu(x.float()) if kind == "gelu" else torch.relu(x.float())).to(x.dtype)
+
+    def act_bwd(self, dy, x, kind):
+        xf = x.float()
+        if kind == "gelu":
+            d = 0.5 * (1 + torch.erf(xf * 0.7071067811865476)) + xf * torch.exp(-0.5 * xf * xf) * 0.3989422804014327
+        else:
+            d = (xf > 0).float()
+        return (dy.float() * d).to(x.dtype)
+
+    def colsum(self, x, out):
+        out.copy_(x.float().sum(dim=1))
+        return out
+
 
 class NativeBackend(TorchBackend):
     """sm_100a kernels for the bandwidth-bound primitives; GEMMs go to the tcgen05 grouped GEMM when
@@ -225,6 +318,89 @@ class NativeBackend(TorchBackend):
                                                 ignore_index=-1, pre_sigmoid=pre_sigmoid, row_scale=scale,
                                                 rows_per_group=B)
         return loss_rows.view(C, B).sum(dim=1) * scale, grad.view(C, B, ncls)
+
+    # ---- transformer primitives: csrc/transformer.cu + the NT/NN/TN grouped GEMM ------------
+    def _tf(self):
+        t = getattr(self, "_tf_ops", None)
+        if t is None:
+            from ..ops import transformer as t
+            self._tf_ops = t
+        return t
+
+    def mm(self, mode, a, b, out=None, out_dtype=None, bias=None, relu=False):
+        t = self._tf()
+        if self.use_tc_gemm and t.mm_supported(mode, a, b, out) and (bias is None or a.dim() == 3):
+            return t.mm(mode, a, b, out=out, out_dtype=out_dtype or a.dtype, bias=bias, relu=relu)
+        self._fb("mm_" + mode)
+        return super().mm(mode, a, b, out, out_dtype, bias, relu)
+
+    def embed_fwd(self, ids, word, pos, S):
+        if self.dtype == torch.bfloat16 and word.shape[2] % 8 == 0:
+            return self._tf().embed_gather(ids, word, pos, S)
+        self._fb("embed_fwd")
+        return super().embed_fwd(ids, word, pos, S)
+
+    def embed_bwd(self, ids, dz, gword, gpos, S):
+        if dz.dtype == torch.bfloat16 and gword.shape[2] % 8 == 0:
+            return self._tf().embed_bwd(ids, dz, gword, gpos, S)
+        self._fb("embed_bwd")
+        return super().embed_bwd(ids, dz, gword, gpos, S)
+
+    @staticmethod
+    def _ln_ok(x):
+        return x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0 and x.shape[-1] <= 1024
+
+    def ln_fwd(self, a, b, gamma, beta, eps):
+        if self._ln_ok(a):
+            return self._tf().add_ln_fwd(a, b, gamma, beta, eps)
+        self._fb("ln_fwd")
+        return super().ln_fwd(a, b, gamma, beta, eps)
+
+    def ln_bwd(self, dy, dy2, z, mean, rstd, gamma, dgamma_out, dbeta_out):
+        if self._ln_ok(z):
+            return self._tf().ln_bwd(dy, dy2, z, mean, rstd, gamma, dgamma_out, dbeta_out)
+        self._fb("ln_bwd")
+        return super().ln_bwd(dy, dy2, z, mean, rstd, gamma, dgamma_out, dbeta_out)
+
+    def dropout(self, x, p, seed, site, step_dev=None, x2=None):
+        if p <= 0 and x2 is None:
+            return x
+        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+            return self._tf().dropout(x, p, seed, site, step_dev, x2)
+        self._fb("dropout")
+        return super().dropout(x, p, seed, site, step_dev, x2)
+
+    def softmax_fwd(self, scores, key_mask, H, scale, p=0.0, seed=0, site=0, step_dev=None):
+        S = scores.shape[-1]
+        if self.dtype == torch.bfloat16 and scores.dtype == torch.float32 and S % 8 == 0 and S <= 512:
+            return self._tf().attn_softmax_fwd(scores.contiguous(), key_mask, H, scale, p, seed, site, step_dev)
+        self._fb("softmax_fwd")
+        return super().softmax_fwd(scores, key_mask, H, scale, p, seed, site, step_dev)
+
+    def softmax_bwd(self, dP, P, scale, p=0.0, seed=0, site=0, step_dev=None):
+        S = P.shape[-1]
+        if P.dtype == torch.bfloat16 and dP.dtype == torch.float32 and S % 8 == 0 and S <= 512:
+            return self._tf().attn_softmax_bwd(dP.contiguous(), P, scale, p, seed, site, step_dev)
+        self._fb("softmax_bwd")
+        return super().softmax_bwd(dP, P, scale, p, seed, site, step_dev)
+
+    def act_fwd(self, x, kind):
+        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+            return self._tf().act_fwd(x, kind)
+        self._fb("act_fwd")
+        return super().act_fwd(x, kind)
+
+    def act_bwd(self, dy, x, kind):
+        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+            return self._tf().act_bwd(dy, x, kind)
+        self._fb("act_bwd")
+        return super().act_bwd(dy, x, kind)
+
+    def colsum(self, x, out):
+        if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
+            return self._tf().colsum(x, out)
+        self._fb("colsum")
+        return super().colsum(x, out)
 
 
 # ============================================================================ layers
@@ -565,6 +741,13 @@ def make_batched(module: nn.Module, backend: TorchBackend) -> Optional[BatchedMo
     if isinstance(module, ResNet) and module.group_norm == 0 and not module.KD:
         try:
             return BatchedResNet(module, backend)
+        except NotImplementedError:
+            return None
+    from .nlp import DistilBertForSequenceClassification
+    if isinstance(module, DistilBertForSequenceClassification):
+        from .batched_nlp import BatchedDistilBert
+        try:
+            return BatchedDistilBert(module, backend)
         except NotImplementedError:
             return None
     return None

@@ -48,6 +48,7 @@ class FbGroupedGemm(C.Structure):
         ("G", C.c_int32), ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32),
         ("lda", C.c_int32), ("ldb", C.c_int32), ("ldd", C.c_int32),
         ("d_fp32", C.c_int32), ("relu", C.c_int32), ("accumulate", C.c_int32), ("out_group_div", C.c_int32),
+        ("group_inner", C.c_int32), ("a_gs2", C.c_int64), ("b_gs2", C.c_int64), ("d_gs2", C.c_int64),
     ]
 
 

@@ -2,8 +2,9 @@
  *
  * One shared object (fedml_b200/native/libfedml_b200.so, sm_100a only) holds every hand-written
  * kernel of the framework.  All entry points take raw device pointers and a CUDA stream, return 0
- * on success or a negative FB_ERR_* code (text via fb_last_error()), and never allocate device
- * memory: scratch buffers are supplied by the caller, sized by the *_scratch_bytes helpers.
+ * on success or a negative FB_ERR_* code (text via fb_last_error()).  Kernels never allocate device
+ * memory: scratch buffers are supplied by the caller, sized by the *_scratch_bytes helpers (the
+ * only allocating calls are the explicit fb_dev_malloc / IPC helpers of the host section).
  * Python binds these with ctypes (fedml_b200/ops/native.py); C/C++ callers include this header.
  *
  * The reference (Cossack9989/FedML, python/fedml) has no native code at all; each
@@ -254,11 +255,64 @@ typedef struct {
   int32_t relu;       /* fused ReLU epilogue */
   int32_t accumulate; /* D += result (fp32 output only; TMA reduce-store, so concurrent groups may target one output) */
   int32_t out_group_div; /* > 1: groups g and g' with g / div == g' / div write the same output block (split-K slices) */
+  int32_t group_inner;   /* > 0: two-level groups, g = outer * group_inner + inner; operand base = outer * x_gs2 +
+                          * inner * x_gs.  Lets attention heads be addressed in place inside [batch][seq][heads*dh]
+                          * buffers (4-D tensor maps) without split/merge-heads copies.  0: one level (x_gs only). */
+  int64_t a_gs2, b_gs2, d_gs2;
 } FbGroupedGemm;
 int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 /* Weight-gradient form: D_g[M][N] = A_g^T * B_g with A_g stored [K][M] and B_g stored [K][N] (M resp. N contiguous,
  * row strides lda/ldb); the operands are fed to the tensor cores MN-major, so activations need no transpose. */
 int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream);
+/* Row-major x row-major form: D_g[M][N] = A_g[M][K] * B_g[K][N] (A K-major, B fed MN-major, row stride ldb).
+ * Data gradients of nn.Linear (dX = dY * W with W stored [out][in]) and attention's P*V / dS*K products use
+ * it, so neither weights nor activations are ever transposed in memory. */
+int fb_grouped_gemm_nn_bf16(const FbGroupedGemm* p, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K12  Client-stacked transformer-encoder kernels (DistilBERT: reference model/nlp via FedNLP,
+ * python/fedml/model/nlp + app/fednlp).  Activations are bf16 [C clients][R = B*S rows][D]; parameters are
+ * fp32 rows of the stacked arena (row stride ld elements).  The projections and the attention products run
+ * on the grouped GEMMs above (two-level (batch, head) groups address Q/K/V heads in place); these kernels
+ * are the single-pass glue between them.  Replaces the per-client nn.Embedding / nn.LayerNorm /
+ * softmax / GELU / dropout ATen launches of `MyModelTrainer.train` (my_model_trainer_classification.py:21-70
+ * driving a transformers DistilBertForSequenceClassification).
+ * ------------------------------------------------------------------------------------------- */
+/* out[c][r][:] = word[c][ids[c][r]][:] + pos[c][r % S][:]   (ids int64 [C][R], tables fp32 in the arena) */
+int fb_embed_gather(const int64_t* ids, const float* word, const float* pos, int64_t ld, void* out_bf16, int32_t C,
+                    int64_t R, int32_t S, int32_t D, int32_t vocab, fb_stream_t stream);
+/* gword[c][ids[c][r]][:] += dz[c][r][:] (fp32 atomics; gword must be pre-zeroed);  gpos[c][s][:] = sum_b dz */
+int fb_embed_bwd(const int64_t* ids, const void* dz_bf16, float* gword, float* gpos, int64_t ld, int32_t C, int64_t R,
+                 int32_t S, int32_t D, int32_t vocab, fb_stream_t stream);
+/* z = a + b (b, z optional); y = LayerNorm(z) * gamma + beta; saves per-row mean / rstd.  D % 8 == 0, D <= 1024. */
+int fb_add_ln_fwd(const void* a, const void* b, void* z, void* y, float* mean, float* rstd, const float* gamma,
+                  const float* beta, int64_t ld_p, int32_t C, int64_t R, int32_t D, float eps, fb_stream_t stream);
+int64_t fb_ln_bwd_scratch_floats(int32_t C, int64_t R, int32_t D);
+/* dz from dy (+ dy2, an optional second gradient stream summed on load) and the saved z / mean / rstd;
+ * dgamma / dbeta fp32 [C][D] with row stride ld_g (e.g. rows of the gradient arena); deterministic. */
+int fb_ln_bwd(const void* dy, const void* dy2, const void* z, const float* mean, const float* rstd, const float* gamma,
+              int64_t ld_p, void* dz, float* dgamma, float* dbeta, int64_t ld_g, float* scratch, int32_t C, int64_t R,
+              int32_t D, fb_stream_t stream);
+/* P = softmax(scale * scores + key mask) over rows of fp32 scores [groups][S][S]; group = (c*B + b) * H + h;
+ * key_mask fp32 [C*B][S] (1 = attend) or NULL.  S % 8 == 0, S <= 512.  With p > 0 the attention-dropout copy
+ * Pdrop = dropout(P) is written as well (mask keyed (seed, *step_dev, site), see fb_dropout_bf16). */
+int fb_attn_softmax_fwd(const float* scores, void* P_bf16, void* Pdrop_bf16, const float* key_mask, int64_t groups,
+                        int32_t S, int32_t H, float scale, float p, uint64_t seed, uint32_t site,
+                        const uint32_t* step_dev, fb_stream_t stream);
+/* dS = scale * P * (dP' - rowsum(dP' * P)), dP' = dropout-backward(dP) under the same key */
+int fb_attn_softmax_bwd(const float* dP, const void* P_bf16, void* dS_bf16, int64_t groups, int32_t S, float scale,
+                        float p, uint64_t seed, uint32_t site, const uint32_t* step_dev, fb_stream_t stream);
+/* elementwise activation on bf16 (mode 0 ReLU, 1 exact GELU) and its backward from the pre-activation x */
+int fb_act_fwd(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream);
+int fb_act_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream);
+/* y = dropout(x (+ x2)): inverted dropout, Philox mask keyed (seed, *step_dev, site) and indexed by element, so
+ * calling it on the gradient with the same key is the backward pass.  step_dev (device uint32, may be NULL) lets
+ * a captured CUDA graph draw fresh masks on every replay. */
+int fb_dropout_bf16(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
+                    const uint32_t* step_dev, fb_stream_t stream);
+/* bias gradients: out[c][n] = sum_r x[c][r][n], x bf16 rows of stride ldx, clients client_stride apart */
+int fb_colsum_bf16(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
+                   int64_t ld_o, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K10 helpers: NHWC im2col / col2im for 3x3 convolutions batched over clients, fused per-client

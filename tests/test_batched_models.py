@@ -84,3 +84,73 @@ def test_batched_lr_matches_autograd():
         assert abs(float(l) - float(loss[c])) < 1e-5
         torch.testing.assert_close(G["linear.weight"][c], m.linear.weight.grad, rtol=1e-4, atol=1e-6)
         torch.testing.assert_close(G["linear.bias"][c], m.linear.bias.grad, rtol=1e-4, atol=1e-6)
+
+
+def _tiny_bert(dropout=0.0):
+    from fedml_b200.models.nlp import DistilBertForSequenceClassification
+    return DistilBertForSequenceClassification(num_labels=5, seq_classif_dropout=dropout, vocab_size=97, dim=32, n_layers=2,
+                                               n_heads=4, hidden_dim=64, max_pos=24, dropout=dropout,
+                                               attention_dropout=dropout)
+
+
+def test_batched_distilbert_matches_autograd():
+    """Explicit client-batched DistilBERT forward/backward == autograd of the reference-named module (padding tokens,
+    key mask, ignored rows included)."""
+    C, B, S = 3, 4, 16
+    torch.manual_seed(0)
+    models = [_tiny_bert() for _ in range(C)]
+    for m in models:      # non-trivial LayerNorm affine parameters and biases
+        for n, p in m.named_parameters():
+            if "LayerNorm" in n or "layer_norm" in n or n.endswith(".bias"):
+                p.data.add_(0.1 * torch.randn_like(p))
+    layout = ArenaLayout(models[0])
+    stack = torch.stack([layout.flatten(m.state_dict()) for m in models])
+    W, G = layout.stacked_views(stack), layout.stacked_views(torch.zeros_like(stack))
+    bm = make_batched(models[0], TorchBackend(torch.float32))
+    assert bm is not None and bm.input_kind == "token_ids"
+    ids = torch.randint(1, 97, (C, B, S))
+    ids[:, :, 12:] = 0                     # padding tail -> key mask
+    ids[0, 1, 5:] = 0
+    y = torch.randint(0, 5, (C, B))
+    y[1, 3] = -1                            # padded row of a ragged last batch
+    scale = 1.0 / (y >= 0).sum(dim=1).float()
+    loss = bm.train_step(ids, y, W, G, torch.ones(C), row_scale=scale)
+    for c, m in enumerate(models):
+        m.train()
+        out = m(ids[c])
+        l = F.cross_entropy(out, y[c], ignore_index=-1)
+        l.backward()
+        assert abs(float(l) - float(loss[c])) < 1e-4
+        for name, p in m.named_parameters():
+            torch.testing.assert_close(G[name][c], p.grad, rtol=2e-3, atol=2e-5, msg=lambda s, n=name: f"{n}: {s}")
+    lg = bm.logits(ids, W)
+    for c, m in enumerate(models):
+        m.eval()
+        torch.testing.assert_close(lg[c], m(ids[c]), rtol=1e-3, atol=1e-4)
+
+
+def test_batched_distilbert_dropout_masks_are_consistent():
+    """With dropout on, the explicit backward uses the same masks as the forward: a finite-difference probe of the
+    loss along the analytic gradient direction matches (the step counter is frozen for the probe)."""
+    C, B, S = 2, 3, 8
+    torch.manual_seed(3)
+    model = _tiny_bert(dropout=0.25)
+    layout = ArenaLayout(model)
+    stack = torch.stack([layout.flatten(model.state_dict()) for _ in range(C)])
+    gstack = torch.zeros_like(stack)
+    bm = make_batched(model, TorchBackend(torch.float32))
+    ids = torch.randint(1, 97, (C, B, S)); y = torch.randint(0, 5, (C, B))
+    l0 = bm.train_step(ids, y, layout.stacked_views(stack), layout.stacked_views(gstack), torch.ones(C))
+    step = int(bm._step_dev.item())
+    direction = gstack / gstack.norm()
+    eps = 2e-2
+
+    def probe(sign):
+        bm._step_dev.fill_(step - 1)          # same masks as the analytic step
+        return bm.train_step(ids, y, layout.stacked_views(stack + sign * eps * direction),
+                             layout.stacked_views(torch.zeros_like(gstack)), torch.ones(C)).double().sum()
+
+    fd = float(probe(+1) - probe(-1)) / (2 * eps)
+    an = float((gstack.double() * direction.double()).sum())
+    assert an > 0 and abs(fd - an) < 0.03 * an, (fd, an)
+    assert l0.shape == (C,)
