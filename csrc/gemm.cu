@@ -459,9 +459,22 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   a.G = p->G; a.M = p->M; a.N = p->N; a.K = p->K; a.ldd = p->ldd; a.d_fp32 = p->d_fp32; a.relu = p->relu;
   int bn = (p->N + 15) / 16 * 16;
   if (bn > 64) {
-    // n-tiles of at most 256 columns, multiples of 64 so that every TMA store box lies inside its own tile
-    int nt = (p->N + 255) / 256;
-    bn = ((p->N + nt - 1) / nt + 63) / 64 * 64;
+    // n-tiles of at most 256 columns, multiples of 64 so that every TMA store box lies inside its own tile.  When the
+    // 256-wide tiling leaves the last wave of tiles mostly empty, 128-wide tiles balance the SMs better (cost in
+    // column units per SM: waves x (tile width + fixed per-tile overhead)); ties go to the wider tile, which
+    // re-reads A less often.
+    const int64_t base = (int64_t)p->G * ((p->M + GEMM_BM - 1) / GEMM_BM);
+    const int sms = fb_num_sms();
+    int64_t cost[2];
+    int cand[2];
+    for (int i = 0; i < 2; ++i) {
+      const int cap = i == 0 ? 256 : 128;
+      const int nt = (p->N + cap - 1) / cap;
+      cand[i] = ((p->N + nt - 1) / nt + 63) / 64 * 64;
+      const int64_t tiles = base * ((p->N + cand[i] - 1) / cand[i]);
+      cost[i] = ((tiles + sms - 1) / sms) * (cand[i] + 24);
+    }
+    bn = (cost[1] * 108 < cost[0] * 100) ? cand[1] : cand[0];
   }
   a.BN = bn;
   const uint64_t es = p->d_fp32 ? 4 : 2;

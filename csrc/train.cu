@@ -255,6 +255,23 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
     const int64_t src = t[0], dst = t[5], dstT = t[6];
     const int cout = (int)t[1], cin = (int)t[2], cinp = (int)t[3], k = (int)t[4], n = (int)t[7];
     const int kk = k * k, kdim = kk * cinp;
+    if (k == 1 && cin == cinp && dstT < 0 && (n & 7) == 0 && (src & 3) == 0 && (dst & 7) == 0 && (ld & 3) == 0 &&
+        (stage_ld & 7) == 0) {
+      // plain fp32 -> bf16 cast of a linear layer / 1x1 conv: 32-byte loads, 16-byte stores
+      const float4* s4 = reinterpret_cast<const float4*>(row + src);
+      uint4* d4 = reinterpret_cast<uint4*>(out + dst);
+      for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < (n >> 3); v += gridDim.x * blockDim.x) {
+        const float4 a = __ldg(s4 + 2 * v), b = __ldg(s4 + 2 * v + 1);
+        uint4 o;
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&o);
+        h2[0] = __floats2bfloat162_rn(a.x, a.y);
+        h2[1] = __floats2bfloat162_rn(a.z, a.w);
+        h2[2] = __floats2bfloat162_rn(b.x, b.y);
+        h2[3] = __floats2bfloat162_rn(b.z, b.w);
+        d4[v] = o;
+      }
+      continue;
+    }
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
       const int co = e / kdim, r = e - co * kdim;
       const int tap = r / cinp, ci = r - tap * cinp;
@@ -269,7 +286,8 @@ extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, 
                                      const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
   FB_REQUIRE(arena && stage && table_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_stage_conv_weights: bad arguments");
   int gx = (max_n + 255) / 256;
-  if (gx > 16) gx = 16;
+  const int gx_cap = max_n >= (1 << 18) ? 64 : 16;   // big linear layers: more CTAs per (client, layer) slice
+  if (gx > gx_cap) gx = gx_cap;
   if (gx < 1) gx = 1;
   int gz = n_layers < 64 ? n_layers : 64;
   stage_weights_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(arena, ld, (__nv_bfloat16*)stage, stage_ld,

@@ -15,6 +15,7 @@
 // uses fp32 atomics (repeated tokens collide).
 #include "common.cuh"
 #include "../include/fedml_b200.h"
+#include <stdlib.h>
 
 #define TF_THREADS 256
 #define TF_WARPS 8
@@ -77,7 +78,7 @@ embed_gather_kernel(const int64_t* __restrict__ ids, const float* __restrict__ w
 // gword[c][ids[c][r]][:] += dz[c][r][:]   (fp32 atomics: tokens repeat)
 __global__ void __launch_bounds__(TF_THREADS)
 embed_word_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dz, float* __restrict__ gword,
-                      int64_t ld, int64_t R, int D, int vocab) {
+                      int64_t ld, int64_t R, int D, int vocab, const float* __restrict__ client_scale) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
   const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
   if (r >= R) return;
@@ -85,11 +86,13 @@ embed_word_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __re
   id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
   float* g = gword + (size_t)c * ld + (size_t)id * D;
   const __nv_bfloat16* d = dz + ((size_t)c * R + r) * D;
+  const float sc = client_scale ? client_scale[c] : 1.f;
+  if (sc == 0.f) return;
   for (int k = lane * 8; k < D; k += 256) {
     float f[8];
     unpack8(ldg16(d + k), f);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) atomicAdd(g + k + e, f[e]);
+    for (int e = 0; e < 8; ++e) atomicAdd(g + k + e, f[e] * sc);
   }
 }
 
@@ -179,88 +182,86 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __re
 // ---------------------------------------------------------------- LayerNorm backward
 // g = (dy + dy2) * gamma;  dz = rstd * (g - mean_D(g) - xhat * mean_D(g * xhat));  per-CTA partial sums of
 // dgamma = sum_rows (dy + dy2) * xhat and dbeta = sum_rows (dy + dy2) go to partial[c][slice][2][D].
-__global__ void __launch_bounds__(TF_THREADS)
+// The running dgamma / dbeta sums of a warp live in its private slice of shared memory (lane-contiguous float4
+// slots, conflict-free), not in registers: the row itself (NV vectors of 8 per lane, twice) is all a thread holds,
+// which keeps three CTAs resident per SM.
+template <int NV>
+__global__ void __launch_bounds__(TF_THREADS, 2)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ z,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               int64_t ld_p, __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, int64_t R, int D, int slices) {
-  __shared__ float red[2 * 32 * 8 * LN_MAXV];
+  extern __shared__ float4 acc4[];                 // [warp][quantity q][vector i][half][lane] float4
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y, s = blockIdx.x;
   const int nv = D >> 3;
   const int64_t rows_per = (R + slices - 1) / slices;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(R, r0 + rows_per);
-  float gam[LN_MAXV][8], ag[LN_MAXV][8], ab[LN_MAXV][8];
+  float4* mine = acc4 + (size_t)warp * (2 * NV * 2 * 32);
 #pragma unroll
-  for (int i = 0; i < LN_MAXV; ++i) {
-    const int idx = i * 32 + lane;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) ag[i][e] = ab[i][e] = gam[i][e] = 0.f;
-    if (idx < nv) ld8f(gamma + (size_t)c * ld_p + idx * 8, gam[i]);
-  }
+  for (int j = 0; j < 2 * NV * 2; ++j) mine[j * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* gam = gamma + (size_t)c * ld_p;
   const float invD = 1.f / (float)D;
   for (int64_t r = r0 + warp; r < r1; r += TF_WARPS) {
     const size_t base = ((size_t)c * R + r) * D;
     const float mean = mean_in[(size_t)c * R + r], rstd = rstd_in[(size_t)c * R + r];
-    float d[LN_MAXV][8], xh[LN_MAXV][8];
+    float g[NV][8], xh[NV][8];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       const int idx = i * 32 + lane;
       if (idx < nv) {
-        unpack8(ldg16(dy + base + idx * 8), d[i]);
+        float gm[8];
+        unpack8(ldg16(dy + base + idx * 8), g[i]);
         if (dy2) {
           float t[8];
           unpack8(ldg16(dy2 + base + idx * 8), t);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) d[i][e] += t[e];
+          for (int e = 0; e < 8; ++e) g[i][e] += t[e];
         }
         unpack8(ldg16(z + base + idx * 8), xh[i]);
+        ld8f(gam + idx * 8, gm);
+        float4 a0 = mine[((0 * NV + i) * 2 + 0) * 32 + lane], a1 = mine[((0 * NV + i) * 2 + 1) * 32 + lane];
+        float4 b0 = mine[((1 * NV + i) * 2 + 0) * 32 + lane], b1 = mine[((1 * NV + i) * 2 + 1) * 32 + lane];
+        float* pa0 = &a0.x; float* pa1 = &a1.x; float* pb0 = &b0.x; float* pb1 = &b1.x;
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           xh[i][e] = (xh[i][e] - mean) * rstd;
-          ag[i][e] += d[i][e] * xh[i][e];
-          ab[i][e] += d[i][e];
-          const float g = d[i][e] * gam[i][e];
-          s1 += g;
-          s2 += g * xh[i][e];
+          const float d = g[i][e];
+          if (e < 4) { pa0[e] += d * xh[i][e]; pb0[e] += d; }
+          else { pa1[e - 4] += d * xh[i][e]; pb1[e - 4] += d; }
+          g[i][e] = d * gm[e];
+          s1 += g[i][e];
+          s2 += g[i][e] * xh[i][e];
         }
+        mine[((0 * NV + i) * 2 + 0) * 32 + lane] = a0; mine[((0 * NV + i) * 2 + 1) * 32 + lane] = a1;
+        mine[((1 * NV + i) * 2 + 0) * 32 + lane] = b0; mine[((1 * NV + i) * 2 + 1) * 32 + lane] = b1;
       }
     }
     s1 = warp_sum(s1) * invD;
     s2 = warp_sum(s2) * invD;
 #pragma unroll
-    for (int i = 0; i < LN_MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       const int idx = i * 32 + lane;
       if (idx < nv) {
         float o[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = rstd * (d[i][e] * gam[i][e] - s1 - xh[i][e] * s2);
+        for (int e = 0; e < 8; ++e) o[e] = rstd * (g[i][e] - s1 - xh[i][e] * s2);
         *reinterpret_cast<uint4*>(dz + base + idx * 8) = pack8(o);
       }
     }
   }
-  // deterministic cross-warp reduction: warps add their registers into shared memory one after another
-  for (int w = 0; w < TF_WARPS; ++w) {
-    if (warp == w) {
-#pragma unroll
-      for (int i = 0; i < LN_MAXV; ++i)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int k = (i * 32 + lane) * 8 + e;
-          if (w == 0) {
-            red[k] = ag[i][e];
-            red[32 * 8 * LN_MAXV + k] = ab[i][e];
-          } else {
-            red[k] += ag[i][e];
-            red[32 * 8 * LN_MAXV + k] += ab[i][e];
-          }
-        }
-    }
-    __syncthreads();
-  }
+  __syncthreads();
+  // fixed-order sum over the 8 warps; slot j of a warp's slice holds column ((i*32 + l)*8 + half*4 + e)
+  const float* accf = reinterpret_cast<const float*>(acc4);
+  constexpr int PER_WARP = 2 * NV * 2 * 32 * 4;
   float* out = partial + ((size_t)c * slices + s) * 2 * D;
-  for (int k = threadIdx.x; k < D; k += TF_THREADS) {
-    out[k] = red[k];
-    out[D + k] = red[32 * 8 * LN_MAXV + k];
+  for (int j = threadIdx.x; j < PER_WARP; j += TF_THREADS) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < TF_WARPS; ++w) t += accf[w * PER_WARP + j];
+    const int e = j & 3, l = (j >> 2) & 31, half = (j >> 7) & 1, qi = j >> 8;   // qi = q * NV + i
+    const int q = qi / NV, i = qi - q * NV;
+    const int col = (i * 32 + l) * 8 + half * 4 + e;
+    if (col < D) out[q * D + col] = t;
   }
 }
 
@@ -306,26 +307,41 @@ __device__ __forceinline__ void drop_apply8(const DropKey& k, int64_t v, float* 
 // ---------------------------------------------------------------- attention softmax
 // P[row][j] = softmax_j(scale * scores[row][j] + (key_mask[j] ? 0 : -inf));  Pd = dropout(P) when p > 0.
 // rows = groups * S with group = (client*batch) * H + head; key_mask is [client*batch][S] (1 = attend) or null.
-// One warp per row, a lane owns SM_MAXV vectors of 8 consecutive keys (S % 8 == 0, S <= 256 * SM_MAXV).
-#define SM_MAXV 2
+// LPR lanes own one row (32 / LPR rows per warp, so short sequences keep every lane busy); a lane holds VPL
+// vectors of 8 consecutive keys.  S % 8 == 0, S <= 8 * LPR * VPL.
+template <int LPR>
+__device__ __forceinline__ float sub_sum(float v) {
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <int LPR>
+__device__ __forceinline__ float sub_max(float v) {
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+template <int LPR, int VPL>
 __global__ void __launch_bounds__(TF_THREADS)
 softmax_fwd_kernel(const float* __restrict__ scores, __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ Pd,
                    const float* __restrict__ key_mask, int64_t rows, int S, int H, float scale, float p, uint64_t seed,
                    uint32_t site, const uint32_t* __restrict__ step_dev) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * TF_WARPS + warp;
-  if (row >= rows) return;
+  constexpr int RPW = 32 / LPR;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, l = lane % LPR;
+  const int64_t row = ((int64_t)blockIdx.x * TF_WARPS + warp) * RPW + lane / LPR;
+  const bool valid = row < rows;
   const int nv = S >> 3;
   const float* src = scores + (size_t)row * S;
   const float* mk = key_mask ? key_mask + (size_t)(row / S / H) * S : nullptr;
-  float v[SM_MAXV][8];
+  float v[VPL][8];
   float mx = -INFINITY;
 #pragma unroll
-  for (int i = 0; i < SM_MAXV; ++i) {
-    const int idx = i * 32 + lane;
+  for (int i = 0; i < VPL; ++i) {
+    const int idx = i * LPR + l;
 #pragma unroll
     for (int e = 0; e < 8; ++e) v[i][e] = -INFINITY;
-    if (idx < nv) {
+    if (valid && idx < nv) {
       float m[8];
       ld8f(src + idx * 8, v[i]);
       if (mk) ld8f(mk + idx * 8, m);
@@ -336,22 +352,22 @@ softmax_fwd_kernel(const float* __restrict__ scores, __nv_bfloat16* __restrict__
       }
     }
   }
-  mx = warp_max(mx);
+  mx = sub_max<LPR>(mx);
   float sum = 0.f;
 #pragma unroll
-  for (int i = 0; i < SM_MAXV; ++i)
+  for (int i = 0; i < VPL; ++i)
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       v[i][e] = (mx == -INFINITY) ? 0.f : __expf(v[i][e] - mx);
       sum += v[i][e];
     }
-  sum = warp_sum(sum);
+  sum = sub_sum<LPR>(sum);
   const float inv = sum > 0.f ? 1.f / sum : 0.f;
   const DropKey key = make_drop_key(p, seed, site, step_dev);
 #pragma unroll
-  for (int i = 0; i < SM_MAXV; ++i) {
-    const int idx = i * 32 + lane;
-    if (idx < nv) {
+  for (int i = 0; i < VPL; ++i) {
+    const int idx = i * LPR + l;
+    if (valid && idx < nv) {
 #pragma unroll
       for (int e = 0; e < 8; ++e) v[i][e] = bf16_round(v[i][e] * inv);
       *reinterpret_cast<uint4*>(P + (size_t)row * S + idx * 8) = pack8(v[i]);
@@ -364,23 +380,25 @@ softmax_fwd_kernel(const float* __restrict__ scores, __nv_bfloat16* __restrict__
 }
 
 // dS = scale * P * (dP' - sum_j dP'_j P_j)   with dP' = dropout-backward(dP) when p > 0
+template <int LPR, int VPL>
 __global__ void __launch_bounds__(TF_THREADS)
 softmax_bwd_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ dS,
                    int64_t rows, int S, float scale, float p, uint64_t seed, uint32_t site,
                    const uint32_t* __restrict__ step_dev) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * TF_WARPS + warp;
-  if (row >= rows) return;
+  constexpr int RPW = 32 / LPR;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, l = lane % LPR;
+  const int64_t row = ((int64_t)blockIdx.x * TF_WARPS + warp) * RPW + lane / LPR;
+  const bool valid = row < rows;
   const int nv = S >> 3;
   const DropKey key = make_drop_key(p, seed, site, step_dev);
-  float pv[SM_MAXV][8], gv[SM_MAXV][8];
+  float pv[VPL][8], gv[VPL][8];
   float dot = 0.f;
 #pragma unroll
-  for (int i = 0; i < SM_MAXV; ++i) {
-    const int idx = i * 32 + lane;
+  for (int i = 0; i < VPL; ++i) {
+    const int idx = i * LPR + l;
 #pragma unroll
     for (int e = 0; e < 8; ++e) pv[i][e] = gv[i][e] = 0.f;
-    if (idx < nv) {
+    if (valid && idx < nv) {
       unpack8(ldg16(P + (size_t)row * S + idx * 8), pv[i]);
       ld8f(dP + (size_t)row * S + idx * 8, gv[i]);
       if (p > 0.f) drop_apply8(key, (int64_t)row * nv + idx, gv[i]);
@@ -388,11 +406,11 @@ softmax_bwd_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict
       for (int e = 0; e < 8; ++e) dot += pv[i][e] * gv[i][e];
     }
   }
-  dot = warp_sum(dot);
+  dot = sub_sum<LPR>(dot);
 #pragma unroll
-  for (int i = 0; i < SM_MAXV; ++i) {
-    const int idx = i * 32 + lane;
-    if (idx < nv) {
+  for (int i = 0; i < VPL; ++i) {
+    const int idx = i * LPR + l;
+    if (valid && idx < nv) {
       float o[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) o[e] = scale * pv[i][e] * (gv[i][e] - dot);
@@ -400,6 +418,18 @@ softmax_bwd_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict
     }
   }
 }
+
+// pick (lanes per row, vectors per lane) for a sequence length; invokes LAUNCH(LPR, VPL)
+#define SM_DISPATCH(S, LAUNCH)          \
+  do {                                  \
+    const int nv_ = (S) >> 3;           \
+    if (nv_ > 32) { LAUNCH(32, 2); }    \
+    else if (nv_ > 16) { LAUNCH(32, 1); } \
+    else if (nv_ > 8) { LAUNCH(16, 1); }  \
+    else if (nv_ > 4) { LAUNCH(8, 1); }   \
+    else { LAUNCH(4, 1); }              \
+  } while (0)
+#define SM_MAX_S 512
 
 // ---------------------------------------------------------------- activations / dropout / bias gradients
 __device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
@@ -504,13 +534,13 @@ extern "C" int fb_embed_gather(const int64_t* ids, const float* word, const floa
 }
 
 extern "C" int fb_embed_bwd(const int64_t* ids, const void* dz_bf16, float* gword, float* gpos, int64_t ld, int32_t C,
-                            int64_t R, int32_t S, int32_t D, int32_t vocab, fb_stream_t stream) {
+                            int64_t R, int32_t S, int32_t D, int32_t vocab, const float* word_scale, fb_stream_t stream) {
   FB_REQUIRE(ids && dz_bf16 && gword && gpos, "fb_embed_bwd: null pointer");
   FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && S >= 1 && R % S == 0 && D >= 8 && D % 8 == 0 && vocab >= 1,
              "fb_embed_bwd: bad shape");
   FB_REQUIRE(ld % 4 == 0 && TF_ALIGNED16(gpos) && TF_ALIGNED16(dz_bf16), "fb_embed_bwd: buffers must be 16-byte aligned");
   embed_word_bwd_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      ids, (const __nv_bfloat16*)dz_bf16, gword, ld, R, D, vocab);
+      ids, (const __nv_bfloat16*)dz_bf16, gword, ld, R, D, vocab, word_scale);
   const int64_t nv = (int64_t)S * (D / 8);
   embed_pos_bwd_kernel<<<dim3((unsigned)((nv + TF_THREADS - 1) / TF_THREADS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dz_bf16, gpos, ld, (int)(R / S), S, D);
@@ -534,11 +564,20 @@ extern "C" int fb_add_ln_fwd(const void* a, const void* b, void* z, void* y, flo
 }
 
 static int ln_slices(int C, int64_t R) {
-  int64_t want = (4 * (int64_t)fb_num_sms() + C - 1) / C;
-  const int64_t max_s = (R + 31) / 32;   // at least four rows per warp
+  static int rows_per_warp = 0, ctas_per_sm = 0;
+  if (!rows_per_warp) {
+    const char* e = getenv("FB_LN_ROWS_PER_WARP");
+    rows_per_warp = e ? atoi(e) : 4;
+    if (rows_per_warp < 1) rows_per_warp = 1;
+    e = getenv("FB_LN_CTAS_PER_SM");
+    ctas_per_sm = e ? atoi(e) : 4;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+  }
+  int64_t want = ((int64_t)ctas_per_sm * fb_num_sms() + C - 1) / C;
+  const int64_t max_s = (R + TF_WARPS * rows_per_warp - 1) / (TF_WARPS * rows_per_warp);
   if (want > max_s) want = max_s;
   if (want < 1) want = 1;
-  if (want > 128) want = 128;
+  if (want > 256) want = 256;
   return (int)want;
 }
 extern "C" int64_t fb_ln_bwd_scratch_floats(int32_t C, int64_t R, int32_t D) { return (int64_t)C * ln_slices(C, R) * 2 * D; }
@@ -552,9 +591,20 @@ extern "C" int fb_ln_bwd(const void* dy, const void* dy2, const void* z, const f
   FB_REQUIRE(ld_p % 4 == 0 && TF_ALIGNED16(gamma) && TF_ALIGNED16(dy) && TF_ALIGNED16(z) && TF_ALIGNED16(dz),
              "fb_ln_bwd: buffers must be 16-byte aligned");
   const int S = ln_slices(C, R);
-  ln_bwd_kernel<<<dim3(S, C), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)z, mean, rstd, gamma, ld_p, (__nv_bfloat16*)dz,
-      scratch, R, D, S);
+  const int NV = (D + 255) / 256;
+#define FB_LN_BWD(NVV)                                                                                                      \
+  do {                                                                                                                      \
+    const int smem = TF_WARPS * 2 * NVV * 2 * 32 * 16;                                                                      \
+    FB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<NVV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));              \
+    ln_bwd_kernel<NVV><<<dim3(S, C), TF_THREADS, smem, (cudaStream_t)stream>>>(                                              \
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)z, mean, rstd, gamma, ld_p,              \
+        (__nv_bfloat16*)dz, scratch, R, D, S);                                                                              \
+  } while (0)
+  if (NV == 1) FB_LN_BWD(1);
+  else if (NV == 2) FB_LN_BWD(2);
+  else if (NV == 3) FB_LN_BWD(3);
+  else FB_LN_BWD(4);
+#undef FB_LN_BWD
   ln_bwd_finish_kernel<<<dim3((2 * D + TF_THREADS - 1) / TF_THREADS, C), TF_THREADS, 0, (cudaStream_t)stream>>>(scratch, S, D, dgamma,
                                                                                                             dbeta, ld_g);
   FB_CHECK_CUDA(cudaGetLastError());
@@ -565,14 +615,18 @@ extern "C" int fb_attn_softmax_fwd(const float* scores, void* P_bf16, void* Pdro
                                    int32_t S, int32_t H, float scale, float p, uint64_t seed, uint32_t site,
                                    const uint32_t* step_dev, fb_stream_t stream) {
   FB_REQUIRE(scores && P_bf16 && groups >= 1 && H >= 1, "fb_attn_softmax_fwd: bad arguments");
-  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= 256 * SM_MAXV, "fb_attn_softmax_fwd: S must be a multiple of 8 and at most %d",
-             256 * SM_MAXV);
+  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= SM_MAX_S, "fb_attn_softmax_fwd: S must be a multiple of 8 and at most %d",
+             SM_MAX_S);
   FB_REQUIRE(p >= 0.f && p < 1.f && (p == 0.f || Pdrop_bf16), "fb_attn_softmax_fwd: dropout needs 0 <= p < 1 and a Pdrop buffer");
   FB_REQUIRE(TF_ALIGNED16(scores) && TF_ALIGNED16(P_bf16) && TF_ALIGNED16(Pdrop_bf16) && TF_ALIGNED16(key_mask),
              "fb_attn_softmax_fwd: buffers must be 16-byte aligned");
   const int64_t rows = groups * S;
-  softmax_fwd_kernel<<<(unsigned)((rows + TF_WARPS - 1) / TF_WARPS), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      scores, (__nv_bfloat16*)P_bf16, (__nv_bfloat16*)Pdrop_bf16, key_mask, rows, S, H, scale, p, seed, site, step_dev);
+#define FB_SM_FWD(LPR, VPL)                                                                                               \
+  softmax_fwd_kernel<LPR, VPL><<<(unsigned)((rows + TF_WARPS * (32 / LPR) - 1) / (TF_WARPS * (32 / LPR))), TF_THREADS, 0,    \
+                                 (cudaStream_t)stream>>>(scores, (__nv_bfloat16*)P_bf16, (__nv_bfloat16*)Pdrop_bf16, key_mask, \
+                                                         rows, S, H, scale, p, seed, site, step_dev)
+  SM_DISPATCH(S, FB_SM_FWD);
+#undef FB_SM_FWD
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -580,13 +634,17 @@ extern "C" int fb_attn_softmax_fwd(const float* scores, void* P_bf16, void* Pdro
 extern "C" int fb_attn_softmax_bwd(const float* dP, const void* P_bf16, void* dS_bf16, int64_t groups, int32_t S, float scale,
                                    float p, uint64_t seed, uint32_t site, const uint32_t* step_dev, fb_stream_t stream) {
   FB_REQUIRE(dP && P_bf16 && dS_bf16 && groups >= 1, "fb_attn_softmax_bwd: bad arguments");
-  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= 256 * SM_MAXV, "fb_attn_softmax_bwd: S must be a multiple of 8 and at most %d",
-             256 * SM_MAXV);
+  FB_REQUIRE(S >= 8 && S % 8 == 0 && S <= SM_MAX_S, "fb_attn_softmax_bwd: S must be a multiple of 8 and at most %d",
+             SM_MAX_S);
   FB_REQUIRE(p >= 0.f && p < 1.f, "fb_attn_softmax_bwd: 0 <= p < 1");
   FB_REQUIRE(TF_ALIGNED16(dP) && TF_ALIGNED16(P_bf16) && TF_ALIGNED16(dS_bf16), "fb_attn_softmax_bwd: buffers must be 16-byte aligned");
   const int64_t rows = groups * S;
-  softmax_bwd_kernel<<<(unsigned)((rows + TF_WARPS - 1) / TF_WARPS), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      dP, (const __nv_bfloat16*)P_bf16, (__nv_bfloat16*)dS_bf16, rows, S, scale, p, seed, site, step_dev);
+#define FB_SM_BWD(LPR, VPL)                                                                                            \
+  softmax_bwd_kernel<LPR, VPL><<<(unsigned)((rows + TF_WARPS * (32 / LPR) - 1) / (TF_WARPS * (32 / LPR))), TF_THREADS, 0, \
+                                 (cudaStream_t)stream>>>(dP, (const __nv_bfloat16*)P_bf16, (__nv_bfloat16*)dS_bf16, rows, S, \
+                                                         scale, p, seed, site, step_dev)
+  SM_DISPATCH(S, FB_SM_BWD);
+#undef FB_SM_BWD
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

@@ -165,11 +165,13 @@ class TorchBackend:
         w = torch.gather(word, 1, ids[..., None].expand(C, R, D))
         return (w + pos[:, :S].repeat(1, R // S, 1)).to(self.dtype)
 
-    def embed_bwd(self, ids, dz, gword, gpos, S):
-        """gword must be zero on entry (sparse scatter-add); gpos is overwritten."""
+    def embed_bwd(self, ids, dz, gword, gpos, S, word_scale=None):
+        """gword += word_scale[c] * scatter(dz) (gradient rows: zero on entry; or the parameter rows with
+        word_scale = -lr, the fused sparse SGD update); gpos is overwritten."""
         C, R = ids.shape
         D = gword.shape[2]
-        gword.scatter_add_(1, ids[..., None].expand(C, R, D), dz.float())
+        src = dz.float() if word_scale is None else dz.float() * word_scale[:, None, None]
+        gword.scatter_add_(1, ids[..., None].expand(C, R, D), src)
         gpos.zero_()
         gpos[:, :S] = dz.float().view(C, R // S, S, D).sum(dim=1)
 
@@ -340,11 +342,11 @@ class NativeBackend(TorchBackend):
         self._fb("embed_fwd")
         return super().embed_fwd(ids, word, pos, S)
 
-    def embed_bwd(self, ids, dz, gword, gpos, S):
+    def embed_bwd(self, ids, dz, gword, gpos, S, word_scale=None):
         if dz.dtype == torch.bfloat16 and gword.shape[2] % 8 == 0:
-            return self._tf().embed_bwd(ids, dz, gword, gpos, S)
+            return self._tf().embed_bwd(ids, dz, gword, gpos, S, word_scale)
         self._fb("embed_bwd")
-        return super().embed_bwd(ids, dz, gword, gpos, S)
+        return super().embed_bwd(ids, dz, gword, gpos, S, word_scale)
 
     @staticmethod
     def _ln_ok(x):

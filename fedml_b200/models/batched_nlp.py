@@ -49,6 +49,7 @@ class BatchedDistilBert(BatchedModel):
         self.seed = int(seed)
         self.pad_id = 0
         self._step_dev = None
+        self.sparse_lr = None
         if self.D % 8 or self.dh % 8 or self.F % 8:
             raise NotImplementedError("batched DistilBERT needs dim, head dim and FFN dim to be multiples of 8")
 
@@ -243,10 +244,24 @@ class BatchedDistilBert(BatchedModel):
             d, d2 = self._drop(d, self.p_hidden, 0, True, x2=d2), None
         de = be.ln_bwd(d, d2, z0, m0, r0, W["distilbert.embeddings.LayerNorm.weight"],
                        G["distilbert.embeddings.LayerNorm.weight"], G["distilbert.embeddings.LayerNorm.bias"])
-        gword = G["distilbert.embeddings.word_embeddings.weight"]
-        gword.zero_()
-        be.embed_bwd(ids2, de, gword, G["distilbert.embeddings.position_embeddings.weight"], S)
+        wname = "distilbert.embeddings.word_embeddings.weight"
+        if self.sparse_lr is not None:
+            # plain SGD: apply w[token] -= lr * dz row by row; the dense vocab x D gradient is never built and the
+            # optimizer kernel skips the segment (``sparse_sgd_segment``)
+            be.embed_bwd(ids2, de, W[wname], G["distilbert.embeddings.position_embeddings.weight"], S,
+                         word_scale=-self.sparse_lr)
+        else:
+            G[wname].zero_()
+            be.embed_bwd(ids2, de, G[wname], G["distilbert.embeddings.position_embeddings.weight"], S)
         return loss
+
+    # ------------------------------------------------------------------ sparse embedding update
+    sparse_sgd_segment = "distilbert.embeddings.word_embeddings.weight"
+
+    def set_sparse_sgd(self, lr_dev):
+        """``lr_dev`` [C] (device, per-client step size, 0 = frozen client) switches the word-embedding update to the
+        fused sparse form; None restores dense gradients.  Only valid for plain SGD (no momentum / decay / prox)."""
+        self.sparse_lr = lr_dev
 
     def logits(self, x, W):
         return self._forward(x, W, self.prepare(W), False, None)[0]

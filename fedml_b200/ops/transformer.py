@@ -127,8 +127,10 @@ def embed_gather(ids: torch.Tensor, word: torch.Tensor, pos: torch.Tensor, S: in
     return out
 
 
-def embed_bwd(ids: torch.Tensor, dz: torch.Tensor, gword: torch.Tensor, gpos: torch.Tensor, S: int):
-    """Scatter-add dz into the (pre-zeroed) word-embedding gradient rows; position gradients are written."""
+def embed_bwd(ids: torch.Tensor, dz: torch.Tensor, gword: torch.Tensor, gpos: torch.Tensor, S: int,
+              word_scale: Optional[torch.Tensor] = None):
+    """Scatter-add ``word_scale[c] * dz`` into the word rows (pre-zeroed gradient rows, or the parameter rows with
+    word_scale = -lr for the fused sparse SGD update); position gradients are written."""
     Cn, R = ids.shape
     vocab, D = gword.shape[1], gword.shape[2]
     ld = gword.stride(0) if Cn > 1 else 4
@@ -137,7 +139,8 @@ def embed_bwd(ids: torch.Tensor, dz: torch.Tensor, gword: torch.Tensor, gpos: to
     if gpos.shape[1] > S:
         gpos[:, S:].zero_()
     check(lib().fb_embed_bwd(vp(ptr(ids.contiguous())), vp(ptr(dz.contiguous())), vp(ptr(gword)), vp(ptr(gpos)), i64(ld),
-                             i32(Cn), i64(R), i32(S), i32(D), i32(vocab), vp(stream_ptr(ids.device))), "embed_bwd")
+                             i32(Cn), i64(R), i32(S), i32(D), i32(vocab), vp(ptr(word_scale)), vp(stream_ptr(ids.device))),
+          "embed_bwd")
     count_launch(2)
 
 

@@ -331,9 +331,35 @@ class NCCLSimulator:
         self._prefetched = (round_idx, plan, self._stage_round_inputs(plan[4], round_idx) if plan[4] else None)
 
     # ------------------------------------------------------------------ local training
+    def _sparse_sgd_range(self):
+        """[a, b) of the arena whose update the batched executor applies itself in sparse form (word embeddings under
+        plain SGD: only the rows of tokens that occur are touched), or None."""
+        if not hasattr(self, "_sparse_range"):
+            rng = None
+            name = getattr(self.batched, "sparse_sgd_segment", None)
+            plain = not (self.momentum or self.wd or self.mu)
+            if name and plain and bool(getattr(self.args, "sparse_embedding_sgd", True)):
+                seg = self.layout.by_name[name]
+                if seg.offset % 4 == 0 and (seg.offset + seg.numel) % 4 == 0:
+                    rng = (seg.offset, seg.offset + seg.numel)
+            self._sparse_range = rng
+        return self._sparse_range
+
     def _sgd(self, C, lr_vec, first_step):
         n = self.P_train
         anchor = self.global_flat if self.mu else None
+        skip = self._sparse_sgd_range() if self.batched is not None else None
+        if skip is not None:
+            # dense optimizer step on the two sides of the sparsely-updated segment
+            for a, b in ((0, skip[0]), (skip[1], n)):
+                if b <= a:
+                    continue
+                if self.cuda:
+                    from ... import ops
+                    ops.sgd_step_stacked(self.stack[:C, a:b], self.grad_stack[:C, a:b], b - a, lr_vec)
+                else:
+                    self.stack[:C, a:b].sub_(lr_vec[:C, None] * self.grad_stack[:C, a:b])
+            return
         if self.cuda:
             from ... import ops
             ops.sgd_step_stacked(self.stack[:C], self.grad_stack[:C], n, lr_vec, weight_decay=self.wd,
@@ -354,6 +380,8 @@ class NCCLSimulator:
             w.sub_(lr_vec[:C, None] * d)
 
     def _step_body(self, st):
+        if self._sparse_sgd_range() is not None:
+            self.batched.set_sparse_sgd(st["lr"])
         loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
         self._sgd(self.C_max, st["lr"], False)
         st["loss"].copy_(loss)

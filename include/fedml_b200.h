@@ -281,9 +281,12 @@ int fb_grouped_gemm_nn_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 /* out[c][r][:] = word[c][ids[c][r]][:] + pos[c][r % S][:]   (ids int64 [C][R], tables fp32 in the arena) */
 int fb_embed_gather(const int64_t* ids, const float* word, const float* pos, int64_t ld, void* out_bf16, int32_t C,
                     int64_t R, int32_t S, int32_t D, int32_t vocab, fb_stream_t stream);
-/* gword[c][ids[c][r]][:] += dz[c][r][:] (fp32 atomics; gword must be pre-zeroed);  gpos[c][s][:] = sum_b dz */
+/* gword[c][ids[c][r]][:] += word_scale[c] * dz[c][r][:] (fp32 atomics; word_scale NULL = 1);  gpos[c][s][:] =
+ * sum_b dz.  With gword = the (pre-zeroed) gradient rows this is the embedding backward; with gword = the
+ * word-embedding PARAMETER rows and word_scale[c] = -lr[c] it is the fused sparse SGD update of plain SGD: only the
+ * rows of tokens that occur are touched and the dense vocab x D gradient is never materialised. */
 int fb_embed_bwd(const int64_t* ids, const void* dz_bf16, float* gword, float* gpos, int64_t ld, int32_t C, int64_t R,
-                 int32_t S, int32_t D, int32_t vocab, fb_stream_t stream);
+                 int32_t S, int32_t D, int32_t vocab, const float* word_scale, fb_stream_t stream);
 /* z = a + b (b, z optional); y = LayerNorm(z) * gamma + beta; saves per-row mean / rstd.  D % 8 == 0, D <= 1024. */
 int fb_add_ln_fwd(const void* a, const void* b, void* z, void* y, float* mean, float* rstd, const float* gamma,
                   const float* beta, int64_t ld_p, int32_t C, int64_t R, int32_t D, float eps, fb_stream_t stream);

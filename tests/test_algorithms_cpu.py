@@ -160,6 +160,25 @@ def test_nccl_simulator_resnet_batched_cpu_and_sequential_fallback_agree():
         torch.testing.assert_close(w_b[k].float(), w_s[k].float(), rtol=5e-3, atol=5e-4, msg=lambda m, k=k: f"{k}: {m}")
 
 
+def test_nccl_simulator_distilbert_batched_cpu_and_sequential_fallback_agree():
+    """FedNLP text classification: the client-batched DistilBERT executor and per-client eager training produce the
+    same global model (dropout off so that both paths are deterministic)."""
+    kw = dict(dataset="20news", model="distilbert", client_num_in_total=4, client_num_per_round=2, synthetic_train_size=32,
+              max_seq_length=16, batch_size=4, comm_round=1, frequency_of_the_test=100, backend="NCCL", shuffle_clients=False)
+    a = mk(**kw)
+    ds, out = fedml.data.load(a)
+    from fedml_b200.models.nlp import DistilBertForSequenceClassification
+    model = DistilBertForSequenceClassification(num_labels=out, seq_classif_dropout=0.0, vocab_size=30522, dim=32, n_layers=2,
+                                                n_heads=4, hidden_dim=64, max_pos=32, dropout=0.0, attention_dropout=0.0)
+    sim_b = SimulatorNCCL(a, CPU, ds, copy.deepcopy(model))
+    assert sim_b.simulator.batched is not None and sim_b.simulator.batched.input_kind == "token_ids"
+    w_b = sim_b.run()
+    a2 = copy.copy(a); a2.batched_clients = False
+    w_s = SimulatorNCCL(a2, CPU, ds, copy.deepcopy(model)).run()
+    for k in w_b:
+        torch.testing.assert_close(w_b[k].float(), w_s[k].float(), rtol=5e-3, atol=5e-5, msg=lambda m, k=k: f"{k}: {m}")
+
+
 def test_nccl_simulator_two_ranks_gloo_is_g_invariant(tmp_path):
     """world_size 2 over gloo on CPU == world_size 1 (same seeds => same sampled clients => same global model)."""
     script = tmp_path / "w.py"

@@ -129,6 +129,12 @@ def test_embed_and_layernorm_kernels():
     tb.embed_bwd(ids, dz.float(), gw_ref, gp_ref, S)
     torch.testing.assert_close(gword, gw_ref, rtol=1e-4, atol=1e-3)
     torch.testing.assert_close(gpos, gp_ref, rtol=1e-4, atol=1e-3)
+    # fused sparse SGD: the same scatter applied to the parameter rows with word_scale = -lr (0 freezes a client)
+    lr = torch.tensor([0.1, 0.0, 0.3], device=DEV)
+    w_before = word.clone()
+    nb.embed_bwd(ids, dz, word, gpos, S, word_scale=-lr)
+    torch.testing.assert_close(word, w_before - lr[:, None, None] * gw_ref, rtol=1e-4, atol=1e-4)
+    assert torch.equal(word[1], w_before[1])
     assert not nb.fallbacks, nb.fallbacks
 
 
