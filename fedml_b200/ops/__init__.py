@@ -480,3 +480,28 @@ def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Te
                                       i64(stage.stride(0)), vp(ptr(table)), i32(n_layers), i32(max_n),
                                       vp(stream_ptr(arena.device))), "stage_conv_weights")
     count_launch()
+
+
+# --------------------------------------------------------------------------- K14 amplitude normalisation (hand-written FFT)
+def amp_normalize_supported(x: torch.Tensor) -> bool:
+    ok = lambda v: 8 <= v <= 512 and (v & (v - 1)) == 0   # noqa: E731
+    return x.is_cuda and x.dim() == 4 and ok(x.shape[2]) and ok(x.shape[3]) and x.shape[0] * x.shape[1] <= 65535
+
+
+def amp_normalize(x: torch.Tensor, amp_running: Optional[torch.Tensor] = None, momentum: float = 0.1):
+    """x [B, ch, H, W] -> (x rebuilt from the running amplitude and its own phase, new running amplitude [ch,H,W],
+    batch-mean amplitude [ch,H,W]); shared-memory radix-2 FFTs, fp32 complex."""
+    if not amp_normalize_supported(x):
+        raise NativeError("amp_normalize: expected CUDA [B, ch, H, W] with power-of-two H, W in [8, 512]")
+    B, ch, H, W = x.shape
+    xf = x.to(torch.float32).contiguous()
+    y = torch.empty_like(xf)
+    amp_new = amp_running.to(torch.float32).clone().contiguous() if amp_running is not None else \
+        torch.empty((ch, H, W), dtype=torch.float32, device=x.device)
+    batch = torch.empty((ch, H, W), dtype=torch.float32, device=x.device)
+    ws = torch.empty((B * ch * H * W * 2,), dtype=torch.float32, device=x.device)
+    check(lib().fb_amp_normalize(vp(ptr(xf)), vp(ptr(y)), i32(B), i32(ch), i32(H), i32(W), vp(ptr(amp_new)), vp(ptr(batch)),
+                                 f32(momentum), i32(1), i32(int(amp_running is not None)), vp(ptr(ws)),
+                                 vp(stream_ptr(x.device))), "amp_normalize")
+    count_launch(5)
+    return y.to(x.dtype), amp_new, batch

@@ -2,14 +2,19 @@
 
 For every image channel: 2-D FFT -> amplitude / phase; the batch's mean amplitude updates a running amplitude
 (momentum 0.1); the image is rebuilt from the *running* amplitude and its own phase.  The reference does this
-in NumPy complex128 on the CPU per batch; here it is ``torch.fft`` (cuFFT on the GPU), which is the CUDA
-restatement of the same maths — the NumPy version below is kept as the oracle."""
+in NumPy complex128 on the CPU per batch; on the GPU it is the hand-written shared-memory FFT kernel K14
+(``csrc/fft.cu``, ``ops.amp_normalize``); CPU tensors and sizes the kernel does not cover go through ``torch.fft``.
+The NumPy version below is kept as the oracle."""
 import numpy as np
 import torch
 
 
 def amplitude_normalize(x: torch.Tensor, amp_running: torch.Tensor = None, momentum: float = 0.1):
     """x [B,C,H,W] float -> (x_normalised, new_running_amp [C,H,W], batch_mean_amp [C,H,W])."""
+    if x.is_cuda:
+        from ... import ops
+        if ops.amp_normalize_supported(x):
+            return ops.amp_normalize(x, amp_running, momentum)
     f = torch.fft.fft2(x.to(torch.float32), dim=(-2, -1))
     amp, pha = f.abs(), torch.angle(f)
     batch_amp = amp.mean(dim=0)

@@ -502,3 +502,25 @@ def test_grouped_gemm_tn_split_k_reduce_add_in_place():
     ref = torch.bmm(a.float().transpose(1, 2), b.float())
     torch.testing.assert_close(out, ref, rtol=1e-3, atol=5e-2)
     assert float(arena[:, :128].abs().sum()) == 0 and float(arena[:, 128 + M * N:].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("B,ch,H,W", [(4, 3, 64, 32), (2, 3, 512, 512), (3, 1, 8, 128)])
+def test_amp_normalize_fft_kernel_matches_numpy_oracle(B, ch, H, W):
+    """K14: shared-memory radix-2 FFT amplitude normalisation vs the reference's NumPy complex128 maths."""
+    from fedml_b200 import ops
+    from fedml_b200.simulation.sp.hs_fft import amplitude_normalize, amplitude_normalize_numpy
+    torch.manual_seed(0)
+    x = torch.rand(B, ch, H, W, device=DEV)
+    run = torch.rand(ch, H, W, device=DEV) * 50
+    launches = ops.native.LAUNCHES[0] if hasattr(ops, "native") else None
+    y0, a0, b0 = amplitude_normalize(x)                       # first batch: running amplitude = batch mean
+    r0, ra0, rb0 = amplitude_normalize_numpy(x.cpu().numpy())
+    y1, a1, b1 = amplitude_normalize(x, run, momentum=0.1)
+    r1, ra1, rb1 = amplitude_normalize_numpy(x.cpu().numpy(), run.cpu().numpy().astype(np.float64), 0.1)
+    scale = float(np.abs(rb0).max())
+    for got, ref in ((b0, rb0), (a0, ra0), (a1, ra1), (b1, rb1)):
+        np.testing.assert_allclose(got.cpu().numpy(), ref, rtol=2e-4, atol=2e-5 * scale)
+    np.testing.assert_allclose(y0.cpu().numpy(), r0, rtol=1e-3, atol=2e-4)
+    np.testing.assert_allclose(y1.cpu().numpy(), r1, rtol=1e-3, atol=2e-4 * max(1.0, float(np.abs(r1).max())))
+    from fedml_b200.ops import native
+    assert launches is None or native.LAUNCHES[0] > launches      # the hand-written kernel ran, not torch.fft
