@@ -53,6 +53,16 @@ class TorchBackend:
 
     grads_prezeroed = False
 
+    # ---- side branch for work that is off the critical path of the backward chain (weight gradients) ----------
+    def side(self, *keep):
+        """Context manager: run the enclosed ops concurrently with the caller's stream when the back-end has a side
+        stream (``keep``: tensors produced on the main stream that the branch reads).  No-op here."""
+        import contextlib
+        return contextlib.nullcontext()
+
+    def join(self):
+        """Make the caller's stream wait for everything issued under :meth:`side`."""
+
     def gemm_tn(self, a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
         """a [C,M,N]^T x b [C,M,K] -> [C,N,K]  (weight gradients; fp32 result, optionally written into ``out``)"""
         r = torch.bmm(a.transpose(1, 2), b).to(out_dtype)
@@ -251,6 +261,28 @@ class NativeBackend(TorchBackend):
     def _fb(self, what):
         self.fallbacks[what] = self.fallbacks.get(what, 0) + 1
 
+    # weight-gradient branch: a second stream (a parallel branch of the captured CUDA graph).  At the small client
+    # counts a GPU sees when a round is sharded over 8 GPUs the kernels do not fill the machine, so the im2col +
+    # wgrad GEMM + scatter of a layer overlap the dgrad / BN chain of the layers below it.
+    use_side_stream = os.environ.get("FB_SIDE_STREAM", "1") != "0"
+
+    def side(self, *keep):
+        import contextlib
+        if not (self.use_side_stream and torch.cuda.is_available()):
+            return contextlib.nullcontext()
+        if getattr(self, "_side", None) is None:
+            self._side, self._keep, self._forked = torch.cuda.Stream(), [], False
+        self._side.wait_stream(torch.cuda.current_stream())
+        self._keep.extend(keep)          # main-stream tensors the branch reads stay allocated until join()
+        self._forked = True
+        return torch.cuda.stream(self._side)
+
+    def join(self):
+        if getattr(self, "_forked", False):
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._keep.clear()
+            self._forked = False
+
     @staticmethod
     def _bn_ok(ch):
         return 8 <= ch <= 2048 and 2048 % ch == 0
@@ -442,26 +474,30 @@ class _Conv:
         cols, Ho, Wo = self._cols(be, x)
         return be.gemm_nt(cols, Wm[0]).view(C, B, Ho, Wo, self.cout)
 
-    def bwd(self, be, dy, x, Wm, gW):
-        C, B, H, W_, _ = x.shape
-        cols, Ho, Wo = self._cols(be, x)
-        dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
+    def _wgrad(self, be, dy2, x, gW):
+        C = x.shape[0]
+        cols, _, _ = self._cols(be, x)
         if self.k == 1 and self.cin == self.cin_real:
             # straight into the gradient arena (zeroed once per step, so split-K slices can reduce-add in place)
             be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin), out_is_zeroed=be.grads_prezeroed)
-            dWm = None
+            return
+        scratch = getattr(self, "_dw_scratch", None)
+        if be.grads_prezeroed and scratch is not None and scratch.shape[0] == C:
+            dWm = be.gemm_tn(dy2, cols, out=scratch, out_is_zeroed=True)
         else:
-            scratch = getattr(self, "_dw_scratch", None)
-            if be.grads_prezeroed and scratch is not None and scratch.shape[0] == C:
-                dWm = be.gemm_tn(dy2, cols, out=scratch, out_is_zeroed=True)
-            else:
-                dWm = be.gemm_tn(dy2, cols)                           # [C, cout, kk*cin] fp32
-        if dWm is None:
-            pass
-        elif self.k == 1:
+            dWm = be.gemm_tn(dy2, cols)                               # [C, cout, kk*cin] fp32
+        if self.k == 1:
             gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1)[:, :, :self.cin_real])
         else:
             gW.copy_(dWm.view(C, self.cout, self.k, self.k, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
+
+    def bwd(self, be, dy, x, Wm, gW):
+        C, B, H, W_, _ = x.shape
+        s = self.stride
+        Ho, Wo = (H - 1) // s + 1, (W_ - 1) // s + 1
+        dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
+        with be.side(dy2, x):                                         # im2col + wgrad GEMM + scatter: off the dgrad chain
+            self._wgrad(be, dy2, x, gW)
         if not self.need_dx:
             return None
         dcols = be.gemm_nn(dy2, Wm[0], b_t=Wm[1])                     # [C, M, kk*cin]
@@ -727,6 +763,7 @@ class BatchedResNet(BatchedModel):
         x0, a, hstem, m, r = tape[0]
         da, _ = self.stem_bn.bwd(be, d, a, hstem, W, G, m, r, relu=True, want_dres=False)
         self.stem_conv.bwd(be, da, x0, Wm["conv1"], G["conv1.weight"])
+        be.join()
         return loss
 
     def logits(self, x, W):
