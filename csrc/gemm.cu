@@ -114,13 +114,14 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version field = 1
 //   K-major : rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused
 //   MN-major: 64-element (128 B) MN chunks `lbo_bytes` apart, 8-row K groups 1024 B apart (SBO)
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t swizzle_code = 2 /* 2: 128B, 4: 64B, 6: 32B */) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+  d |= (uint64_t)swizzle_code << 61;
   return d;
 }
 // instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128, N = bn; majors: 0 = K, 1 = MN
@@ -155,9 +156,14 @@ struct GemmArgs {
   int gi;           // inner group count of the two-level group index (g = outer * gi + inner); G when one level
   int gi_out;       // same for the output group index
   int64_t d_gs2;    // outer output group stride (pointer-store path)
+  // MODE 4 (implicit 3x3 convolution, see fb_conv3x3_bf16): A tiles are gathered by TMA from the NHWC activation
+  int cv_B, cv_HoWo, cv_Wo, cv_stride, cv_flip;   // images per group, output plane, output width, conv stride, flipped taps
+  int cv_kblk, cv_kcs;                            // channels per k-block (16 / 32 / 64), k-blocks per tap
+  int cv_b_inner_off, cv_b_row_off;               // per-tap coordinate offsets into the weight map
+  int cv_sbo, cv_swz;                             // 8-row group stride (bytes) and descriptor swizzle code
 };
 
-// MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory)
+// MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory); MODE 4: implicit 3x3 conv
 template <int MODE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -175,7 +181,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0;
+  constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0, CONV = MODE == 4;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = a.G * a.m_tiles * a.n_tiles;
 
@@ -206,6 +212,28 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
+        if (CONV) {
+          // 128 consecutive output pixels of group g: image n0 (a tile spans 128 / (Ho*Wo) images when the plane is
+          // smaller), output rows from ho0.  One k-block per (tap, channel block): the tap's shifted input window
+          // is one TMA box (padding = out-of-bounds zero fill, stride = element strides of the map).
+          const int p0 = mt * GEMM_BM;
+          const int n0 = g * a.cv_B + p0 / a.cv_HoWo, ho0 = (p0 % a.cv_HoWo) / a.cv_Wo;
+          const uint32_t inner_bytes = (uint32_t)a.cv_kblk * 2u;
+          for (int kb = 0; kb < a.k_blocks; ++kb) {
+            const int tap = kb / a.cv_kcs, kc = kb - tap * a.cv_kcs;
+            const int kh = tap / 3, kw = tap - kh * 3;
+            const int wt = a.cv_flip ? 8 - tap : tap;
+            mbar_wait(empty_bar + stage, phase ^ 1);
+            uint8_t* sa = smem + (size_t)stage * stage_bytes;
+            uint8_t* sb = sa + GEMM_A_BYTES;
+            mbar_expect_tx(full_bar + stage, (GEMM_BM + (uint32_t)a.BN) * inner_bytes);
+            tma_load_4d(&tmA, sa, full_bar + stage, kc * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
+            tma_load_4d(&tmB, sb, full_bar + stage, kc * a.cv_kblk + wt * a.cv_b_inner_off, nt * a.BN + wt * a.cv_b_row_off,
+                        g, 0);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          continue;
+        }
         for (int kb = 0; kb < a.k_blocks; ++kb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * stage_bytes;
@@ -244,10 +272,16 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
           const uint32_t sb = sa + GEMM_A_BYTES;
           const int k_rem = a.K - kb * GEMM_BK;
-          const int k_steps = k_rem >= GEMM_BK ? GEMM_BK / 16 : (k_rem + 15) / 16;
+          const int k_steps = CONV ? a.cv_kblk / 16 : (k_rem >= GEMM_BK ? GEMM_BK / 16 : (k_rem + 15) / 16);
           for (int k = 0; k < k_steps; ++k) {
-            const uint64_t ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+            uint64_t ad, bd;
+            if (CONV) {
+              ad = make_smem_desc(sa + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
+              bd = make_smem_desc(sb + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
+            } else {
+              ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+              bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+            }
             umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
           }
           umma_commit(empty_bar + stage);   // smem slot reusable once these MMAs have read it
@@ -551,6 +585,114 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     grouped_gemm_kernel<0><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   }
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- implicit 3x3 convolution (MODE 4)
+static CUtensorMapSwizzle swizzle_for(int inner_bytes) {
+  return inner_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+}
+
+extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
+  FB_REQUIRE(p && p->x && p->w && p->y, "fb_conv3x3_bf16: null operand");
+  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_bf16: empty problem");
+  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_bf16: stride must be 1 or 2");
+  FB_REQUIRE(!(p->dgrad && p->stride != 1), "fb_conv3x3_bf16: the data-gradient form needs stride 1");
+  FB_REQUIRE(p->cin >= 16 && p->cin % 16 == 0 && (p->cin <= 64 ? (p->cin & (p->cin - 1)) == 0 : p->cin % 64 == 0),
+             "fb_conv3x3_bf16: input channels must be 16, 32 or a multiple of 64 (got %d)", p->cin);
+  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_bf16: output channels must be a multiple of 8");
+  const int s = p->stride;
+  const int Ho = (p->H - 1) / s + 1, Wo = (p->W - 1) / s + 1;
+  FB_REQUIRE(Wo <= 128 && (Wo & (Wo - 1)) == 0 && (Ho & (Ho - 1)) == 0 && Wo * s <= 256,
+             "fb_conv3x3_bf16: output plane must be a power of two per side, at most 128 wide (got %d x %d)", Ho, Wo);
+  const int plane = Ho * Wo;
+  const int bh = plane >= GEMM_BM ? GEMM_BM / Wo : Ho;          // output rows per tile
+  const int bn = plane >= GEMM_BM ? 1 : GEMM_BM / plane;        // images per tile
+  FB_REQUIRE(bh >= 1 && bh * s <= 256 && bn <= 256, "fb_conv3x3_bf16: unsupported plane shape");
+  PFN_encodeTiled enc = get_encode();
+  FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->w % 16) == 0 && ((uintptr_t)p->y % 16) == 0 && p->w_gs % 8 == 0,
+             "fb_conv3x3_bf16: operands must be 16-byte aligned");
+
+  const int kblk = p->cin < 64 ? p->cin : 64;
+  const int inner_bytes = kblk * 2;
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.d = p->y; a.bias = nullptr;
+  a.G = p->G; a.M = p->B * plane; a.N = p->cout; a.K = 9 * p->cin;
+  a.ldd = p->cout; a.d_fp32 = 0; a.relu = 0;
+  a.d_gs = (int64_t)a.M * a.N;
+  int bn_cols = (p->cout + 15) / 16 * 16;
+  if (bn_cols > 64) {
+    const int nt = (p->cout + 255) / 256;
+    bn_cols = ((p->cout + nt - 1) / nt + 63) / 64 * 64;
+  }
+  a.BN = bn_cols; a.BNpad = bn_cols;
+  a.gi = p->G; a.gi_out = p->G; a.group_div = 1; a.d_gs2 = 0;
+  a.tma_store = ((uint64_t)p->cout * 2) % 16 == 0;
+  a.chunk_cols = bn_cols >= 64 ? 64 : bn_cols;
+  a.chunk_bytes = a.chunk_cols * 2;
+  a.n_tiles = (p->cout + bn_cols - 1) / bn_cols;
+  a.m_tiles = (a.M + GEMM_BM - 1) / GEMM_BM;
+  a.cv_B = p->B; a.cv_HoWo = plane; a.cv_Wo = Wo; a.cv_stride = s; a.cv_flip = p->dgrad ? 1 : 0;
+  a.cv_kblk = kblk; a.cv_kcs = p->cin / kblk; a.k_blocks = 9 * a.cv_kcs;
+  a.cv_sbo = 8 * inner_bytes;
+  a.cv_swz = inner_bytes == 32 ? 6 : inner_bytes == 64 ? 4 : 2;
+  // weights: forward [G][cout][9*cin] (tap-major columns); data gradient [G][9*cout_fwd][cin_fwd] = per tap a
+  // [N = this call's cout][K = this call's cin] matrix, rows tap*cout + n
+  a.cv_b_inner_off = p->dgrad ? 0 : p->cin;
+  a.cv_b_row_off = p->dgrad ? p->cout : 0;
+  int cols = 32;
+  while (cols < 2 * bn_cols) cols <<= 1;
+  a.tmem_cols = cols;
+
+  CUtensorMap tmA, tmB, tmD;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)p->cin, (cuuint64_t)p->W, (cuuint64_t)p->H, (cuuint64_t)p->G * p->B};
+    cuuint64_t strides[3] = {(cuuint64_t)p->cin * 2, (cuuint64_t)p->cin * p->W * 2, (cuuint64_t)p->cin * p->W * p->H * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
+    CUresult r = enc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv input) failed with code %d", (int)r);
+  }
+  {
+    const uint64_t inner = p->dgrad ? (uint64_t)p->cin : (uint64_t)9 * p->cin;
+    const uint64_t rows = p->dgrad ? (uint64_t)9 * p->cout : (uint64_t)p->cout;
+    cuuint64_t dims[4] = {inner, rows, (cuuint64_t)p->G, 1};
+    cuuint64_t strides[3] = {inner * 2, (cuuint64_t)(p->G > 1 ? p->w_gs : inner * rows) * 2, inner * rows * p->G * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)bn_cols, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv weights) failed with code %d", (int)r);
+  }
+  memset(&tmD, 0, sizeof(tmD));
+  if (a.tma_store) {
+    int rc = make_store_map(&tmD, p->y, 0, (uint64_t)p->cout, (uint64_t)a.M, (uint64_t)p->G, 1, (uint64_t)p->cout,
+                            (uint64_t)a.d_gs, 0, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
+    if (rc) return rc;
+  }
+  const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
+  const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
+  int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
+  if (stages < 3 && ctas_per_sm == 2) {
+    ctas_per_sm = 1;
+    stages = (int)((227 * 1024 - fixed) / stage_bytes);
+  }
+  if (stages > GEMM_MAX_STAGES) stages = GEMM_MAX_STAGES;
+  FB_REQUIRE(stages >= 2, "fb_conv3x3_bf16: tile does not fit shared memory");
+  a.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  const int total = a.G * a.m_tiles * a.n_tiles;
+  int grid = fb_num_sms() * ctas_per_sm;
+  if (grid > total) grid = total;
+  FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grouped_gemm_kernel<4><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

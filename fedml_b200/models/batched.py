@@ -53,6 +53,10 @@ class TorchBackend:
 
     grads_prezeroed = False
 
+    def conv3x3_ok(self, x, cout, stride):
+        """True when the back-end has an implicit-GEMM 3x3 convolution for this shape (else im2col + GEMM)."""
+        return False
+
     # ---- side branch for work that is off the critical path of the backward chain (weight gradients) ----------
     def side(self, *keep):
         """Context manager: run the enclosed ops concurrently with the caller's stream when the back-end has a side
@@ -260,6 +264,17 @@ class NativeBackend(TorchBackend):
 
     def _fb(self, what):
         self.fallbacks[what] = self.fallbacks.get(what, 0) + 1
+
+    use_implicit_conv = os.environ.get("FB_IMPLICIT_CONV", "1") != "0"
+
+    def conv3x3_ok(self, x, cout, stride):
+        return self.use_tc_gemm and self.use_implicit_conv and self.ops.conv3x3_supported(x, cout, stride)
+
+    def conv3x3(self, x, wm, stride):
+        return self.ops.conv3x3(x, wm, stride)
+
+    def conv3x3_dgrad(self, dy, wt):
+        return self.ops.conv3x3_dgrad(dy.contiguous(), wt)
 
     # weight-gradient branch: a second stream (a parallel branch of the captured CUDA graph).  At the small client
     # counts a GPU sees when a round is sharded over 8 GPUs the kernels do not fill the machine, so the im2col +
@@ -471,6 +486,8 @@ class _Conv:
 
     def fwd(self, be, x, Wm):
         C, B = x.shape[0], x.shape[1]
+        if self.k == 3 and be.conv3x3_ok(x, self.cout, self.stride):
+            return be.conv3x3(x, Wm[0], self.stride)                  # implicit GEMM: no im2col buffer
         cols, Ho, Wo = self._cols(be, x)
         return be.gemm_nt(cols, Wm[0]).view(C, B, Ho, Wo, self.cout)
 
@@ -500,6 +517,8 @@ class _Conv:
             self._wgrad(be, dy2, x, gW)
         if not self.need_dx:
             return None
+        if self.k == 3 and s == 1 and Wm[1] is not None and be.conv3x3_ok(dy, self.cin, 1):
+            return be.conv3x3_dgrad(dy, Wm[1])                        # implicit GEMM with flipped taps: no col2im
         dcols = be.gemm_nn(dy2, Wm[0], b_t=Wm[1])                     # [C, M, kk*cin]
         if self.k == 1:
             if self.stride == 1:

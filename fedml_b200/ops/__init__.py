@@ -505,3 +505,46 @@ def amp_normalize(x: torch.Tensor, amp_running: Optional[torch.Tensor] = None, m
                                  vp(stream_ptr(x.device))), "amp_normalize")
     count_launch(5)
     return y.to(x.dtype), amp_new, batch
+
+
+# --------------------------------------------------------------------------- implicit 3x3 convolution (tcgen05, TMA-gathered taps)
+def conv3x3_supported(x: torch.Tensor, cout: int, stride: int) -> bool:
+    """x [C, B, H, W, cin] bf16 NHWC."""
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 5 and x.is_contiguous() and stride in (1, 2)):
+        return False
+    _, _, H, W, cin = x.shape
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    pow2 = lambda v: v >= 1 and (v & (v - 1)) == 0   # noqa: E731
+    ok_c = cin in (16, 32) or (cin >= 64 and cin % 64 == 0)
+    return ok_c and cout % 8 == 0 and cout >= 8 and pow2(Ho) and pow2(Wo) and Wo <= 128 and Wo * stride <= 256
+
+
+def _conv3x3(x, w, cout, stride, dgrad):
+    from .native import FbConv3x3
+    Cn, B, H, W, cin = x.shape
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    y = torch.empty((Cn, B, Ho, Wo, cout), dtype=torch.bfloat16, device=x.device)
+    p = FbConv3x3()
+    p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+    p.w_gs = w.stride(0)
+    p.G, p.B, p.H, p.W, p.cin, p.cout, p.stride, p.dgrad = Cn, B, H, W, cin, cout, stride, int(dgrad)
+    check(lib().fb_conv3x3_bf16(C.byref(p), vp(stream_ptr(x.device))), "conv3x3")
+    count_launch()
+    return y
+
+
+def conv3x3(x: torch.Tensor, wm: torch.Tensor, stride: int = 1) -> torch.Tensor:
+    """Implicit-GEMM 3x3 convolution, pad 1: x [C,B,H,W,cin] bf16, wm [C, cout, 9*cin] ((kh,kw,cin) columns)."""
+    cout = wm.shape[1]
+    if not conv3x3_supported(x, cout, stride) or wm.shape[2] != 9 * x.shape[-1] or wm.stride(2) != 1 \
+            or wm.stride(1) != wm.shape[2]:
+        raise NativeError("conv3x3: unsupported operand layout")
+    return _conv3x3(x, wm, cout, stride, False)
+
+
+def conv3x3_dgrad(dy: torch.Tensor, wt: torch.Tensor) -> torch.Tensor:
+    """Input gradient of a stride-1 3x3 convolution: dy [C,B,H,W,cout], wt [C, 9*cin, cout] (transposed staging copy)."""
+    cin = wt.shape[1] // 9
+    if not conv3x3_supported(dy, cin, 1) or wt.shape[2] != dy.shape[-1] or wt.stride(2) != 1 or wt.stride(1) != wt.shape[2]:
+        raise NativeError("conv3x3_dgrad: unsupported operand layout")
+    return _conv3x3(dy, wt, cin, 1, True)

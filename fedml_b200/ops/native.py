@@ -52,6 +52,14 @@ class FbGroupedGemm(C.Structure):
     ]
 
 
+class FbConv3x3(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p), ("w_gs", C.c_int64),
+        ("G", C.c_int32), ("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32),
+        ("stride", C.c_int32), ("dgrad", C.c_int32),
+    ]
+
+
 class FbDpStepParams(C.Structure):
     _fields_ = [
         ("peer_grad", C.c_void_p), ("peer_param", C.c_void_p), ("peer_flags", C.c_void_p), ("mom", C.c_void_p),

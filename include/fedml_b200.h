@@ -264,6 +264,23 @@ int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 /* Weight-gradient form: D_g[M][N] = A_g^T * B_g with A_g stored [K][M] and B_g stored [K][N] (M resp. N contiguous,
  * row strides lda/ldb); the operands are fed to the tensor cores MN-major, so activations need no transpose. */
 int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream);
+/* Implicit 3x3 convolution (pad 1) on the same tensor-core pipeline: no im2col / col2im buffers.  For every group g
+ * (client) and image b < B:  y[g][b][ho][wo][:] = sum_{kh,kw} x[g][b][ho*s+kh-1][wo*s+kw-1][:] * W_g[kh][kw].
+ * The producer warp gathers each tap's shifted input window with one 4-D TMA box (padding = out-of-bounds zero fill,
+ * stride = element strides of the tensor map); nine taps x channel blocks accumulate into one TMEM tile.
+ *   forward:        w = bf16 [G][cout][9*cin]  ((kh,kw,cin) column order, as staged for the explicit path)
+ *   data gradient:  call with x = dy [.., cout_fwd], cin = cout_fwd, cout = cin_fwd, dgrad = 1 and
+ *                   w = bf16 [G][9*cin_fwd][cout_fwd] (the transposed staging copy); taps are flipped (stride 1 only).
+ * cin in {16, 32, 64k}; cout % 8 == 0; output plane sides powers of two, width <= 128.  Replaces
+ * nn.Conv2d(3x3) forward / input-gradient calls of the reference's ResNets (model/cv/resnet.py:48-51). */
+typedef struct {
+  const void* x;     /* bf16 [G*B][H][W][cin] */
+  const void* w;     /* see above; group stride w_gs elements */
+  void* y;           /* bf16 [G*B][Ho][Wo][cout] */
+  int64_t w_gs;
+  int32_t G, B, H, W, cin, cout, stride, dgrad;
+} FbConv3x3;
+int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream);
 /* Row-major x row-major form: D_g[M][N] = A_g[M][K] * B_g[K][N] (A K-major, B fed MN-major, row stride ldb).
  * Data gradients of nn.Linear (dX = dY * W with W stored [out][in]) and attention's P*V / dS*K products use
  * it, so neither weights nor activations are ever transposed in memory. */

@@ -524,3 +524,28 @@ def test_amp_normalize_fft_kernel_matches_numpy_oracle(B, ch, H, W):
     np.testing.assert_allclose(y1.cpu().numpy(), r1, rtol=1e-3, atol=2e-4 * max(1.0, float(np.abs(r1).max())))
     from fedml_b200.ops import native
     assert launches is None or native.LAUNCHES[0] > launches      # the hand-written kernel ran, not torch.fft
+
+
+@pytest.mark.parametrize("B,H,cin,cout,stride", [(10, 32, 16, 16, 1), (4, 16, 32, 32, 1), (10, 32, 32, 32, 2), (6, 8, 64, 64, 1),
+                                                  (4, 8, 128, 128, 1), (8, 16, 64, 128, 2), (2, 4, 256, 64, 1)])
+def test_implicit_conv3x3_forward_and_dgrad(B, H, cin, cout, stride):
+    """tcgen05 implicit-GEMM 3x3 convolution (TMA-gathered taps, no im2col) vs F.conv2d, forward and input gradient."""
+    import torch.nn.functional as F
+    from fedml_b200 import ops
+    torch.manual_seed(0)
+    C = 3
+    x = torch.randn(C, B, H, H, cin, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(C, cout, cin, 3, 3, device=DEV) * 0.1).to(torch.bfloat16)
+    wm = w.permute(0, 1, 3, 4, 2).reshape(C, cout, 9 * cin).contiguous()
+    assert ops.conv3x3_supported(x, cout, stride)
+    y = ops.conv3x3(x, wm, stride)
+    for c in range(C):
+        ref = F.conv2d(x[c].float().permute(0, 3, 1, 2), w[c].float(), stride=stride, padding=1).permute(0, 2, 3, 1)
+        torch.testing.assert_close(y[c].float(), ref, rtol=2e-2, atol=2e-2 * float(ref.abs().max()))
+    if stride == 1:
+        dy = torch.randn(C, B, H, H, cout, device=DEV).to(torch.bfloat16)
+        wt = wm.transpose(1, 2).contiguous()                        # [C, 9*cin, cout]
+        dx = ops.conv3x3_dgrad(dy, wt)
+        for c in range(C):
+            ref = F.conv_transpose2d(dy[c].float().permute(0, 3, 1, 2), w[c].float(), stride=1, padding=1).permute(0, 2, 3, 1)
+            torch.testing.assert_close(dx[c].float(), ref, rtol=2e-2, atol=2e-2 * float(ref.abs().max()))
