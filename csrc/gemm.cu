@@ -161,6 +161,7 @@ struct GemmArgs {
   int cv_kblk, cv_kcs;                            // channels per k-block (16 / 32 / 64), k-blocks per tap
   int cv_b_inner_off, cv_b_row_off;               // per-tap coordinate offsets into the weight map
   int cv_sbo, cv_swz;                             // 8-row group stride (bytes) and descriptor swizzle code
+  int cv_tpt;                                     // MODE 5: taps per n-tile (9, 3 or 1)
 };
 
 // MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory); MODE 4: implicit 3x3 conv
@@ -181,7 +182,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0, CONV = MODE == 4;
+  constexpr bool CONV = MODE == 4, WGRAD = MODE == 5;   // 5: TN form whose B operand is gathered from the NHWC activation
+  constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0 || WGRAD;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = a.G * a.m_tiles * a.n_tiles;
 
@@ -238,8 +240,31 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(empty_bar + stage, phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * stage_bytes;
           uint8_t* sb = sa + GEMM_A_BYTES;
-          mbar_expect_tx(full_bar + stage, stage_bytes);
           const int g0 = g % a.gi, g1 = g / a.gi;
+          if (WGRAD) {
+            // weight gradient of a 3x3 convolution: k-block = 64 consecutive output pixels of this (client, K-slice)
+            // group; n-tile = (tap, channel chunk); B = the tap's shifted input window, gathered MN-major by TMA
+            const uint32_t row_bytes = (uint32_t)a.cv_kblk * 2u;
+            const int subs = a.BN / a.cv_kblk;                       // 64-row B chunks per k-block (taps x channel blocks)
+            const int per_tap = subs / a.cv_tpt;
+            const int a_chunks = min(GEMM_BM / 64, (a.M - mt * GEMM_BM + 63) / 64);   // rows of D beyond cout are never stored
+            mbar_expect_tx(full_bar + stage, (uint32_t)a_chunks * GEMM_BK * 128u + (uint32_t)subs * GEMM_BK * row_bytes);
+            for (int i = 0; i < a_chunks; ++i)
+              tma_load_4d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g0, g1);
+            const int tap0 = a.cv_tpt > 1 ? nt * a.cv_tpt : nt / a.cv_kcs;
+            const int cc = a.cv_tpt > 1 ? 0 : nt - tap0 * a.cv_kcs;
+            const int p0 = (g % a.group_div) * a.K + kb * GEMM_BK;
+            const int n0 = (g / a.group_div) * a.cv_B + p0 / a.cv_HoWo, ho0 = (p0 % a.cv_HoWo) / a.cv_Wo;
+            for (int i = 0; i < subs; ++i) {
+              const int tap = tap0 + i / per_tap, sub = i - (i / per_tap) * per_tap;
+              const int kh = tap / 3, kw = tap - kh * 3;
+              tma_load_4d(&tmB, sb + (size_t)i * GEMM_BK * row_bytes, full_bar + stage,
+                          cc * (a.BN / a.cv_tpt) + sub * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            continue;
+          }
+          mbar_expect_tx(full_bar + stage, stage_bytes);
           if (!A_MN) {
             tma_load_4d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g0, g1);
           } else {
@@ -278,6 +303,10 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (CONV) {
               ad = make_smem_desc(sa + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
               bd = make_smem_desc(sb + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
+            } else if (WGRAD) {
+              const uint32_t row_bytes = (uint32_t)a.cv_kblk * 2u;
+              ad = make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024);
+              bd = make_smem_desc(sb + k * 16 * row_bytes, GEMM_BK * row_bytes, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
             } else {
               ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
               bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
@@ -693,6 +722,99 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   if (grid > total) grid = total;
   FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   grouped_gemm_kernel<4><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream) {
+  FB_REQUIRE(p && p->x && p->dy && p->dw, "fb_conv3x3_wgrad_bf16: null operand");
+  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_wgrad_bf16: empty problem");
+  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_wgrad_bf16: stride must be 1 or 2");
+  FB_REQUIRE(p->cin >= 16 && p->cin % 16 == 0 && (p->cin <= 64 ? (p->cin & (p->cin - 1)) == 0 : (p->cin % 64 == 0)) &&
+                 (p->cin <= 256 || p->cin % 256 == 0),
+             "fb_conv3x3_wgrad_bf16: input channels must be 16, 32, 64, 128, 192, 256 or a multiple of 256 (got %d)", p->cin);
+  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_wgrad_bf16: output channels must be a multiple of 8");
+  const int s = p->stride;
+  const int Ho = (p->H - 1) / s + 1, Wo = (p->W - 1) / s + 1;
+  FB_REQUIRE(Wo <= 64 && (Wo & (Wo - 1)) == 0 && (Ho & (Ho - 1)) == 0,
+             "fb_conv3x3_wgrad_bf16: output plane must be a power of two per side, at most 64 wide (got %d x %d)", Ho, Wo);
+  const int plane = Ho * Wo;
+  const int S = p->split > 0 ? p->split : 1;
+  const int64_t Ktot = (int64_t)p->B * plane;
+  FB_REQUIRE(Ktot % ((int64_t)S * GEMM_BK) == 0, "fb_conv3x3_wgrad_bf16: B*Ho*Wo must be a multiple of 64 x split");
+  const int Ks = (int)(Ktot / S);
+  const int bh = plane >= GEMM_BK ? GEMM_BK / Wo : Ho;
+  const int bn = plane >= GEMM_BK ? 1 : GEMM_BK / plane;
+  PFN_encodeTiled enc = get_encode();
+  FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->dy % 16) == 0 && ((uintptr_t)p->dw % 16) == 0 &&
+                 (p->G == 1 || p->dw_gs % 4 == 0),
+             "fb_conv3x3_wgrad_bf16: operands must be 16-byte aligned");
+  const int kblk = p->cin < 64 ? p->cin : 64;
+  const int row_bytes = kblk * 2;
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.d = p->dw; a.bias = nullptr;
+  a.G = p->G * S; a.M = p->cout; a.N = 9 * p->cin; a.K = Ks;
+  a.ldd = 9 * p->cin; a.d_fp32 = 1; a.relu = 0;
+  a.d_gs = p->dw_gs; a.d_gs2 = 0;
+  // taps per n-tile: all nine when they fit one 256-column tile, else three, else one tap (and a channel chunk);
+  // dy (the A operand) is then streamed 1 / 3 / 9 times
+  const int tpt = 9 * p->cin <= 256 ? 9 : (3 * p->cin <= 256 ? 3 : 1);
+  const int bn_tap = p->cin < 256 ? p->cin : 256;
+  a.cv_tpt = tpt;
+  a.BN = tpt * bn_tap;
+  a.BNpad = (a.BN + 63) / 64 * 64;
+  a.gi = a.G; a.group_div = S; a.gi_out = p->G;
+  a.tma_store = 1;
+  a.reduce_add = (S > 1 || p->accumulate) ? 1 : 0;
+  a.chunk_cols = a.BN >= 32 ? 32 : 16;
+  a.chunk_bytes = a.chunk_cols * 4;
+  a.cv_kcs = p->cin / bn_tap;
+  a.n_tiles = (9 / tpt) * a.cv_kcs;
+  a.m_tiles = (p->cout + GEMM_BM - 1) / GEMM_BM;
+  a.k_blocks = Ks / GEMM_BK;
+  a.cv_B = p->B; a.cv_HoWo = plane; a.cv_Wo = Wo; a.cv_stride = s;
+  a.cv_kblk = kblk;
+  a.cv_sbo = 8 * row_bytes;
+  a.cv_swz = row_bytes == 32 ? 6 : row_bytes == 64 ? 4 : 2;
+  int cols = 32;
+  while (cols < 2 * a.BN) cols <<= 1;
+  a.tmem_cols = cols;
+  CUtensorMap tmA, tmB, tmD;
+  int rc = make_map(&tmA, p->dy, (uint64_t)p->cout, (uint64_t)Ks, (uint64_t)a.G, 1, (uint64_t)p->cout, (uint64_t)Ks * p->cout, 0,
+                    GEMM_BK);
+  if (rc) return rc;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)p->cin, (cuuint64_t)p->W, (cuuint64_t)p->H, (cuuint64_t)p->G * p->B};
+    cuuint64_t strides[3] = {(cuuint64_t)p->cin * 2, (cuuint64_t)p->cin * p->W * 2, (cuuint64_t)p->cin * p->W * p->H * 2};
+    cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
+    CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(row_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (wgrad input) failed with code %d", (int)r);
+  }
+  rc = make_store_map(&tmD, p->dw, 1, (uint64_t)a.N, (uint64_t)a.M, (uint64_t)p->G, 1, (uint64_t)a.ldd, (uint64_t)p->dw_gs, 0,
+                      (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
+  if (rc) return rc;
+  const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
+  const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
+  int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
+  if (stages < 3 && ctas_per_sm == 2) {
+    ctas_per_sm = 1;
+    stages = (int)((227 * 1024 - fixed) / stage_bytes);
+  }
+  if (stages > GEMM_MAX_STAGES) stages = GEMM_MAX_STAGES;
+  FB_REQUIRE(stages >= 2, "fb_conv3x3_wgrad_bf16: tile does not fit shared memory");
+  a.stages = stages;
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  const int total = a.G * a.m_tiles * a.n_tiles;
+  int grid = fb_num_sms() * ctas_per_sm;
+  if (grid > total) grid = total;
+  FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  grouped_gemm_kernel<5><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

@@ -57,6 +57,9 @@ class TorchBackend:
         """True when the back-end has an implicit-GEMM 3x3 convolution for this shape (else im2col + GEMM)."""
         return False
 
+    def conv3x3_wgrad_ok(self, x, dy, stride):
+        return False
+
     # ---- side branch for work that is off the critical path of the backward chain (weight gradients) ----------
     def side(self, *keep):
         """Context manager: run the enclosed ops concurrently with the caller's stream when the back-end has a side
@@ -272,6 +275,17 @@ class NativeBackend(TorchBackend):
 
     def conv3x3(self, x, wm, stride):
         return self.ops.conv3x3(x, wm, stride)
+
+    # implicit weight gradients pay off when a pixel's channel vector fills a 128-byte line (cin >= 64); for narrower
+    # layers the 32/64-byte TMA gathers cost more than the im2col buffer they avoid (measured, profiles/README.md)
+    implicit_wgrad_min_cin = int(os.environ.get("FB_IMPLICIT_WGRAD_MIN_CIN", "64"))
+
+    def conv3x3_wgrad_ok(self, x, dy, stride):
+        return self.use_tc_gemm and self.use_implicit_conv and x.shape[-1] >= self.implicit_wgrad_min_cin \
+            and self.ops.conv3x3_wgrad_supported(x, dy, stride)
+
+    def conv3x3_wgrad(self, x, dy, stride, out=None, out_is_zeroed=False):
+        return self.ops.conv3x3_wgrad(x, dy, stride, out=out, out_is_zeroed=out_is_zeroed)
 
     def conv3x3_dgrad(self, dy, wt):
         return self.ops.conv3x3_dgrad(dy.contiguous(), wt)
@@ -491,8 +505,14 @@ class _Conv:
         cols, Ho, Wo = self._cols(be, x)
         return be.gemm_nt(cols, Wm[0]).view(C, B, Ho, Wo, self.cout)
 
-    def _wgrad(self, be, dy2, x, gW):
+    def _wgrad(self, be, dy2, x, gW, dy=None):
         C = x.shape[0]
+        if self.k == 3 and dy is not None and be.conv3x3_wgrad_ok(x, dy, self.stride):
+            scratch = getattr(self, "_dw_scratch", None)              # implicit GEMM: shifted windows gathered by TMA
+            ok = be.grads_prezeroed and scratch is not None and scratch.shape[0] == C
+            dWm = be.conv3x3_wgrad(x, dy, self.stride, out=scratch if ok else None, out_is_zeroed=ok)
+            gW.copy_(dWm.view(C, self.cout, 3, 3, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
+            return
         cols, _, _ = self._cols(be, x)
         if self.k == 1 and self.cin == self.cin_real:
             # straight into the gradient arena (zeroed once per step, so split-K slices can reduce-add in place)
@@ -514,7 +534,7 @@ class _Conv:
         Ho, Wo = (H - 1) // s + 1, (W_ - 1) // s + 1
         dy2 = dy.reshape(C, B * Ho * Wo, self.cout)
         with be.side(dy2, x):                                         # im2col + wgrad GEMM + scatter: off the dgrad chain
-            self._wgrad(be, dy2, x, gW)
+            self._wgrad(be, dy2, x, gW, dy if dy.is_contiguous() else None)
         if not self.need_dx:
             return None
         if self.k == 3 and s == 1 and Wm[1] is not None and be.conv3x3_ok(dy, self.cin, 1):

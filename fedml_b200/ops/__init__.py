@@ -548,3 +548,53 @@ def conv3x3_dgrad(dy: torch.Tensor, wt: torch.Tensor) -> torch.Tensor:
     if not conv3x3_supported(dy, cin, 1) or wt.shape[2] != dy.shape[-1] or wt.stride(2) != 1 or wt.stride(1) != wt.shape[2]:
         raise NativeError("conv3x3_dgrad: unsupported operand layout")
     return _conv3x3(dy, wt, cin, 1, True)
+
+
+def conv3x3_wgrad_supported(x: torch.Tensor, dy: torch.Tensor, stride: int) -> bool:
+    if not (x.is_cuda and x.dtype == torch.bfloat16 and dy.dtype == torch.bfloat16 and x.dim() == 5 and x.is_contiguous()
+            and dy.is_contiguous() and stride in (1, 2)):
+        return False
+    _, B, H, W, cin = x.shape
+    cout = dy.shape[-1]
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    pow2 = lambda v: v >= 1 and (v & (v - 1)) == 0   # noqa: E731
+    ok_c = cin in (16, 32, 64, 128, 192, 256) or (cin > 256 and cin % 256 == 0)
+    return ok_c and cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 64 and (B * Ho * Wo) % 64 == 0 \
+        and tuple(dy.shape[:4]) == (x.shape[0], B, Ho, Wo)
+
+
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, stride: int = 1, out: Optional[torch.Tensor] = None,
+                  out_is_zeroed: bool = False) -> torch.Tensor:
+    """Weight gradient of the implicit 3x3 convolution: x [C,B,H,W,cin], dy [C,B,Ho,Wo,cout] ->
+    fp32 [C, cout, 9*cin] ((kh,kw,cin) columns).  The pixel reduction is split across CTAs when there are few tiles;
+    the slices reduce-add into ``out`` (zeroed here unless the caller already did)."""
+    from .native import FbConv3x3Wgrad
+    if not conv3x3_wgrad_supported(x, dy, stride):
+        raise NativeError("conv3x3_wgrad: unsupported operand layout")
+    Cn, B, H, W, cin = x.shape
+    cout = dy.shape[-1]
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    tpt = 9 if 9 * cin <= 256 else (3 if 3 * cin <= 256 else 1)     # taps per tile, as in the kernel launcher
+    tiles = Cn * ((cout + 127) // 128) * (9 // tpt) * (cin // min(cin, 256))
+    kb = B * Ho * Wo // 64
+    S = 1
+    if tiles < 296:
+        for cand in (16, 10, 8, 5, 4, 2):
+            if kb % cand == 0 and kb // cand >= 4 and tiles * cand <= 1184:
+                S = cand
+                break
+    if out is None:
+        out = torch.zeros((Cn, cout, 9 * cin), dtype=torch.float32, device=x.device) if S > 1 else \
+            torch.empty((Cn, cout, 9 * cin), dtype=torch.float32, device=x.device)
+    elif S > 1 and not out_is_zeroed:
+        out.zero_()
+    if not (out.dtype == torch.float32 and out.stride(2) == 1 and out.stride(1) == 9 * cin and out.data_ptr() % 16 == 0
+            and (Cn == 1 or out.stride(0) % 4 == 0)):
+        raise NativeError("conv3x3_wgrad: output must be fp32 [C, cout, 9*cin] with contiguous blocks")
+    p = FbConv3x3Wgrad()
+    p.x, p.dy, p.dw = x.data_ptr(), dy.data_ptr(), out.data_ptr()
+    p.dw_gs = out.stride(0) if Cn > 1 else cout * 9 * cin
+    p.G, p.B, p.H, p.W, p.cin, p.cout, p.stride, p.split, p.accumulate = Cn, B, H, W, cin, cout, stride, S, 0
+    check(lib().fb_conv3x3_wgrad_bf16(C.byref(p), vp(stream_ptr(x.device))), "conv3x3_wgrad")
+    count_launch()
+    return out

@@ -60,6 +60,14 @@ class FbConv3x3(C.Structure):
     ]
 
 
+class FbConv3x3Wgrad(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("dy", C.c_void_p), ("dw", C.c_void_p), ("dw_gs", C.c_int64),
+        ("G", C.c_int32), ("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32),
+        ("stride", C.c_int32), ("split", C.c_int32), ("accumulate", C.c_int32),
+    ]
+
+
 class FbDpStepParams(C.Structure):
     _fields_ = [
         ("peer_grad", C.c_void_p), ("peer_param", C.c_void_p), ("peer_flags", C.c_void_p), ("mom", C.c_void_p),

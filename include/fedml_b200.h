@@ -281,6 +281,20 @@ typedef struct {
   int32_t G, B, H, W, cin, cout, stride, dgrad;
 } FbConv3x3;
 int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream);
+/* Weight gradient of the same convolution, also without an im2col buffer:
+ *   dw[g][co][(kh,kw,ci)] (+)= sum_{b,ho,wo} dy[g][b][ho][wo][co] * x[g][b][ho*s+kh-1][wo*s+kw-1][ci]
+ * dy is fed MN-major as in fb_grouped_gemm_tn_bf16, the shifted input windows are gathered MN-major by TMA; a tile is one
+ * (tap, channel chunk) of one client.  split > 1 cuts the pixel reduction into slices that reduce-add (TMA) into dw,
+ * which must then be zero on entry; accumulate != 0 adds to dw as well.  Output plane sides powers of two, width <= 64;
+ * B*Ho*Wo % (64*split) == 0. */
+typedef struct {
+  const void* x;     /* bf16 [G*B][H][W][cin] */
+  const void* dy;    /* bf16 [G*B][Ho][Wo][cout] */
+  float* dw;         /* fp32 [G][cout][9*cin], group stride dw_gs elements */
+  int64_t dw_gs;
+  int32_t G, B, H, W, cin, cout, stride, split, accumulate;
+} FbConv3x3Wgrad;
+int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream);
 /* Row-major x row-major form: D_g[M][N] = A_g[M][K] * B_g[K][N] (A K-major, B fed MN-major, row stride ldb).
  * Data gradients of nn.Linear (dX = dY * W with W stored [out][in]) and attention's P*V / dS*K products use
  * it, so neither weights nor activations are ever transposed in memory. */

@@ -549,3 +549,27 @@ def test_implicit_conv3x3_forward_and_dgrad(B, H, cin, cout, stride):
         for c in range(C):
             ref = F.conv_transpose2d(dy[c].float().permute(0, 3, 1, 2), w[c].float(), stride=1, padding=1).permute(0, 2, 3, 1)
             torch.testing.assert_close(dx[c].float(), ref, rtol=2e-2, atol=2e-2 * float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("C,B,H,cin,cout,stride", [(3, 10, 32, 16, 16, 1), (40, 4, 16, 32, 32, 1), (3, 10, 32, 32, 32, 2),
+                                                    (2, 6, 8, 64, 64, 1), (2, 4, 8, 128, 128, 1), (3, 8, 16, 64, 128, 2),
+                                                    (2, 16, 4, 256, 64, 1)])
+def test_implicit_conv3x3_wgrad(C, B, H, cin, cout, stride):
+    """Weight gradient without im2col: dy MN-major x TMA-gathered input windows, split-K reduce-add, vs autograd."""
+    import torch.nn.functional as F
+    from fedml_b200 import ops
+    torch.manual_seed(0)
+    x = torch.randn(C, B, H, H, cin, device=DEV).to(torch.bfloat16)
+    Ho = (H - 1) // stride + 1
+    dy = torch.randn(C, B, Ho, Ho, cout, device=DEV).to(torch.bfloat16)
+    assert ops.conv3x3_wgrad_supported(x, dy, stride)
+    arena = torch.zeros(C, cout * 9 * cin + 64, device=DEV)
+    out = arena[:, 32:32 + cout * 9 * cin].view(C, cout, 9 * cin)
+    dw = ops.conv3x3_wgrad(x, dy, stride, out=out, out_is_zeroed=True)
+    for c in range(min(C, 3)):
+        w = torch.zeros(cout, cin, 3, 3, device=DEV, requires_grad=True)
+        y = F.conv2d(x[c].float().permute(0, 3, 1, 2), w, stride=stride, padding=1)
+        y.backward(dy[c].float().permute(0, 3, 1, 2))
+        ref = w.grad.permute(0, 2, 3, 1).reshape(cout, 9 * cin)
+        torch.testing.assert_close(dw[c], ref, rtol=2e-2, atol=2e-2 * float(ref.abs().max()))
+    assert float(arena[:, :32].abs().sum()) == 0 and float(arena[:, 32 + cout * 9 * cin:].abs().sum()) == 0
