@@ -7,6 +7,7 @@
 // channels, so per-channel partial sums live in registers for the whole walk.
 #include "common.cuh"
 #include "../include/fedml_b200.h"
+#include <stdlib.h>
 
 #define BN_THREADS 256
 #define BN_VEC 8
@@ -55,9 +56,8 @@ __device__ __forceinline__ void reduce_channel_pairs(const float* a, const float
 
 // ---------------------------------------------------------------- BN forward
 // stage 1: partial[c][s][2][ch] = (sum x, sum x^2) over the rows of slice s
-__global__ void __launch_bounds__(BN_THREADS)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial) {
-  __shared__ float smem[BN_THREADS * 16];
+__device__ __forceinline__ void
+bn_stats_body(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial, float* smem) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
@@ -84,13 +84,13 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, f
 }
 
 // stage 2: finish the statistics (every CTA redundantly, S is small), update running stats, apply
-__global__ void __launch_bounds__(BN_THREADS)
-bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
-                int64_t M, int ch, int S, const float* __restrict__ partial, const float* __restrict__ gamma,
+__device__ __forceinline__ void
+bn_apply_body(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+                int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                 const float* __restrict__ active, float momentum, float eps, int relu, int training,
-                float* __restrict__ save_mean, float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n) {
-  extern __shared__ float sm[];  // scale[ch], shift[ch]
+                float* __restrict__ save_mean, float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n,
+                float* sm /* scale[ch], shift[ch] */) {
   float* scale = sm;
   float* shift = sm + ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
@@ -101,8 +101,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     if (training) {
       float su = 0.f, sq = 0.f;
       for (int j = 0; j < S; ++j) {
-        su += partial[((size_t)c * S + j) * 2 * ch + k];
-        sq += partial[((size_t)c * S + j) * 2 * ch + ch + k];
+        su += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);        // L2: written by sibling CTAs in the fused kernel
+        sq += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
       }
       mean = su / (float)M;
       var = fmaxf(sq / (float)M - mean * mean, 0.f);
@@ -178,6 +178,74 @@ static int bn_slices(int C, int64_t M, int ch) {
   return (int)want;
 }
 
+// ---------------------------------------------------------------- kernels: two-pass and fused single-launch forms
+__global__ void __launch_bounds__(BN_THREADS)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial) {
+  __shared__ float smem[BN_THREADS * 16];
+  bn_stats_body(x, M, ch, S, partial, smem);
+}
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+                int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+                int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
+                float momentum, float eps, int relu, int training, float* __restrict__ save_mean,
+                float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n) {
+  extern __shared__ float sm[];
+  bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu,
+                training, save_mean, save_rstd, num_batches_tracked, ld_n, sm);
+}
+
+// Barrier among the S CTAs of one client (blockIdx.y): {arrival count, generation} per client, self-resetting, so
+// the state survives from launch to launch (and CUDA-graph replays) without host involvement.  Sound because CTAs
+// are dispatched in linear block order (a client's CTAs are adjacent, earlier clients first) and S is far below the
+// number of resident CTA slots.  One BN kernel at a time per device (they share this state and the scratch).
+static __device__ unsigned g_bn_barrier[2 * 65536];
+__device__ __forceinline__ void client_barrier(int S) {
+  __syncthreads();
+  if (S > 1 && threadIdx.x == 0) {
+    unsigned* st = g_bn_barrier + 2 * blockIdx.y;
+    __threadfence();                                   // publish this CTA's partial sums
+    const unsigned gen = ld_acquire_gpu(st + 1);
+    if (atomicAdd(st, 1u) == (unsigned)S - 1) {
+      st[0] = 0;
+      __threadfence();
+      atomicAdd(st + 1, 1u);
+    } else {
+      while (ld_acquire_gpu(st + 1) == gen) __nanosleep(32);
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// stats -> per-client barrier -> apply in ONE launch: the second read of x comes from L2 (a client's slice was just
+// streamed by its sibling CTAs) and a BN layer costs one kernel instead of two
+__global__ void __launch_bounds__(BN_THREADS)
+bn_fwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+                    int64_t M, int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
+                    float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
+                    float* num_batches_tracked, int64_t ld_n) {
+  __shared__ float smem[BN_THREADS * 16];
+  extern __shared__ float sm[];
+  bn_stats_body(x, M, ch, S, partial, smem);
+  client_barrier(S);
+  bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu, 1,
+                save_mean, save_rstd, num_batches_tracked, ld_n, sm);
+}
+
+// The fused form wins when the layer is large (second pass served by L2, 1-2 % on the 100-client bench) and loses when
+// it is small (the in-kernel barrier costs more than a kernel boundary inside a CUDA graph: +6 % at 13 clients), so
+// it is chosen by activation size.  FB_BN_FUSED=0 / 1 forces one form.
+static bool bn_fused_enabled(int64_t act_bytes) {
+  static int v = -2;
+  if (v == -2) {
+    const char* e = getenv("FB_BN_FUSED");
+    v = e ? (atoi(e) == 0 ? 0 : 1) : -1;
+  }
+  return v >= 0 ? v == 1 : act_bytes >= (int64_t)48 << 20;
+}
+
 extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * 64 * 2 * ch; }
 
 extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch,
@@ -190,6 +258,13 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
   FB_REQUIRE(running_mean && running_var, "fb_bn_fwd_stacked: running statistics missing");
   FB_REQUIRE(!training || scratch, "fb_bn_fwd_stacked: training needs the partial-sum scratch");
   const int S = bn_slices(C, M, ch);
+  if (training && bn_fused_enabled((int64_t)C * M * ch * 2)) {
+    bn_fwd_fused_kernel<<<dim3(S, C), BN_THREADS, 2 * ch * sizeof(float), (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
+        running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n);
+    FB_CHECK_CUDA(cudaGetLastError());
+    return FB_OK;
+  }
   if (training) {
     bn_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, M, ch, S, scratch);
     FB_CHECK_CUDA(cudaGetLastError());
@@ -203,13 +278,12 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
 
 // ---------------------------------------------------------------- BN backward
 // stage 1: partial[c][s][2][ch] = (sum dy', sum dy' * xhat), dy' = dy masked by the ReLU of the forward output
-__global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+__device__ __forceinline__ void
+bn_bwd_stats_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
                     const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
-                    int64_t ld_p, int relu, float* __restrict__ partial) {
-  __shared__ float smem[BN_THREADS * 16];
+                    int64_t ld_p, int relu, float* __restrict__ partial, float* smem) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
@@ -270,15 +344,15 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
 }
 
-__global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+__device__ __forceinline__ void
+bn_bwd_apply_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
                     const __nv_bfloat16* __restrict__ x,
                     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
-                    int64_t M, int ch, int S, const float* __restrict__ partial, const float* __restrict__ gamma,
+                    int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma,
                     const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
                     const float* __restrict__ rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                    int64_t ld_g) {
-  extern __shared__ float sm[];  // per channel: A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g
+                    int64_t ld_g, float* sm) {
+  // sm, per channel: A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g
   float* s_A = sm;
   float* s_B = sm + ch;
   float* s_C = sm + 2 * ch;
@@ -287,8 +361,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   for (int k = tid; k < ch; k += BN_THREADS) {
     float sd = 0.f, sdx = 0.f;
     for (int j = 0; j < S; ++j) {
-      sd += partial[((size_t)c * S + j) * 2 * ch + k];
-      sdx += partial[((size_t)c * S + j) * 2 * ch + ch + k];
+      sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
+      sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
     }
     const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
     const float dbt = sd, dgm = rs * (sdx - mu * sd);
@@ -361,6 +435,36 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
 }
 
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
+                    const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
+                    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
+                    int relu, float* __restrict__ partial) {
+  __shared__ float smem[BN_THREADS * 16];
+  bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
+}
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
+                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int64_t M,
+                    int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g) {
+  extern __shared__ float sm[];
+  bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
+}
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
+                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int64_t M,
+                    int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
+                    const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
+                    float* __restrict__ dbeta, int64_t ld_g) {
+  __shared__ float smem[BN_THREADS * 16];
+  extern __shared__ float sm[];
+  bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
+  client_barrier(S);
+  bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
+}
+
 extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t C,
                                  int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
                                  const float* save_mean,
@@ -371,6 +475,13 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x,
   FB_REQUIRE(!relu || y || beta, "fb_bn_bwd_stacked: the ReLU mask needs the forward output or beta to recompute it");
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   const int S = bn_slices(C, M, ch);
+  if (bn_fused_enabled((int64_t)C * M * ch * 2)) {
+    bn_bwd_fused_kernel<<<dim3(S, C), BN_THREADS, 4 * ch * sizeof(float), (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
+        (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
+    FB_CHECK_CUDA(cudaGetLastError());
+    return FB_OK;
+  }
   bn_bwd_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
       beta, ld_p, relu, scratch);

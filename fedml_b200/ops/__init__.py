@@ -267,6 +267,18 @@ def eval_counts(logits: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor
 _bn_scratch = {}
 
 
+import os as _os
+
+_BN_FUSED_ENV = _os.environ.get("FB_BN_FUSED")
+
+
+def _bn_fused(x) -> bool:
+    """Mirror of bn_fused_enabled() in csrc/conv.cu (stats + apply in one launch for large layers)."""
+    if _BN_FUSED_ENV is not None:
+        return _BN_FUSED_ENV != "0"
+    return x.numel() * 2 >= 48 << 20
+
+
 def _scratch_for(device, n_floats):
     key = str(device)
     buf = _bn_scratch.get(key)
@@ -291,7 +303,7 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
                                   i32(int(relu)), i32(int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
                                   vp(ptr(nbt)), i64(nbt.stride(0) if nbt is not None and nbt.dim() else 1),
                                   vp(stream_ptr(x.device))), "bn_fwd_stacked")
-    count_launch(2 if training else 1)
+    count_launch(1 if (not training or _bn_fused(x)) else 2)
     return y, mean, rstd
 
 
@@ -313,7 +325,7 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgam
                                   i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
                                   vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ld_g), vp(ptr(scratch)),
                                   vp(stream_ptr(x.device))), "bn_bwd_stacked")
-    count_launch(2)
+    count_launch(1 if _bn_fused(x) else 2)
     return dx, dres, dgamma, dbeta
 
 
