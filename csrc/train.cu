@@ -272,6 +272,44 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
       }
       continue;
     }
+    if (k == 3) {
+      // 3 x 3 weights: (cout 32) x (cin 32) x 9 tiles through shared memory, so the fp32 rows are read in contiguous
+      // runs and both bf16 layouts are written in contiguous runs (the element-wise form below strides by 9 floats on
+      // the read side and by cout on the transposed write side: 8x / 16x sector amplification on big layers).  All
+      // index arithmetic divides by compile-time constants.
+      __shared__ float tile[32 * 289];   // [cout 32][cin 32][tap 9] + 1 pad per row: every access pattern below is conflict-free
+      constexpr int KK = 9, RUN = 32 * KK;
+      const int n_cb = (cout + 31) / 32, n_ib = (cinp + 31) / 32;
+      for (int t = blockIdx.x; t < n_cb * n_ib; t += gridDim.x) {
+        const int co0 = (t / n_ib) * 32, ci0 = (t % n_ib) * 32;
+        __syncthreads();
+#pragma unroll 12
+        for (int i = threadIdx.x; i < 32 * RUN; i += 256) {            // 36 independent loads per thread: keep them in flight
+          const int co = i / RUN, r = i - co * RUN;
+          const int ci = r / KK, tap = r - ci * KK;
+          float v = 0.f;
+          if (co0 + co < cout && ci0 + ci < cin) v = __ldg(row + src + ((size_t)(co0 + co) * cin + ci0 + ci) * KK + tap);
+          tile[co * 289 + r] = v;
+        }
+        __syncthreads();
+        const int lane = threadIdx.x & 31;
+#pragma unroll 12
+        for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {                 // Wm: a warp writes 32 input channels
+          const int co = q / KK, tap = q - co * KK;
+          if (co0 + co < cout && ci0 + lane < cinp)
+            out[dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + lane] = __float2bfloat16_rn(tile[co * 289 + lane * 9 + tap]);
+        }
+        if (dstT >= 0) {
+#pragma unroll 12
+          for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {               // WmT: a warp writes 32 output channels
+            const int tap = q >> 5, ci = q & 31;
+            if (co0 + lane < cout && ci0 + ci < cinp)
+              out[dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane] = __float2bfloat16_rn(tile[lane * 289 + ci * 9 + tap]);
+          }
+        }
+      }
+      continue;
+    }
     for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
       const int co = e / kdim, r = e - co * kdim;
       const int tap = r / cinp, ci = r - tap * cinp;
@@ -292,6 +330,68 @@ extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, 
   int gz = n_layers < 64 ? n_layers : 64;
   stage_weights_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(arena, ld, (__nv_bfloat16*)stage, stage_ld,
                                                                          table_dev, n_layers);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// ---------------------------------------------------------------- weight-gradient un-staging (one launch per step)
+// The k x k weight-gradient GEMMs produce dW in the GEMM layout fp32 [cout][(kh,kw,cin_pad)] (scratch rows); the
+// gradient arena wants the parameter layout [cout][cin][kh][kw].  Table (int64 x 8 per layer): src_off (scratch),
+// cout, cin, cin_pad, k, dst_off (arena), unused, unused.  Same shared-memory tiling as the staging kernel, the other
+// way round.  Replaces one strided permute-copy launch per convolution per step.
+__global__ void __launch_bounds__(256)
+unstage_grads_kernel(const float* __restrict__ scratch, int64_t scratch_ld, float* __restrict__ grads, int64_t ld,
+                     const int64_t* __restrict__ table, int n_layers) {
+  __shared__ float tile[32 * 289];   // [cout 32][cin 32][tap 9] + 1 pad per row: every access pattern below is conflict-free
+  const int c = blockIdx.y;
+  const float* in = scratch + (size_t)c * scratch_ld;
+  float* out = grads + (size_t)c * ld;
+  for (int l = blockIdx.z; l < n_layers; l += gridDim.z) {
+    const int64_t* t = table + (size_t)l * 8;
+    const int64_t src = t[0], dst = t[5];
+    const int cout = (int)t[1], cin = (int)t[2], cinp = (int)t[3], k = (int)t[4];
+    const int kk = k * k;
+    const int n_cb = (cout + 31) / 32, n_ib = (cin + 31) / 32;
+    if (k != 3) {                                                     // generic (rare): element-wise
+      const int kdim = kk * cinp;
+      for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < cout * kk * cin; e += gridDim.x * blockDim.x) {
+        const int co = e / (kk * cin), r = e - co * (kk * cin);
+        const int ci = r / kk, tap = r - ci * kk;
+        out[dst + e] = in[src + (size_t)co * kdim + (size_t)tap * cinp + ci];
+      }
+      continue;
+    }
+    constexpr int KK = 9, RUN = 32 * KK;
+    for (int tl = blockIdx.x; tl < n_cb * n_ib; tl += gridDim.x) {
+      const int co0 = (tl / n_ib) * 32, ci0 = (tl % n_ib) * 32;
+      const int lane = threadIdx.x & 31;
+      __syncthreads();
+#pragma unroll 12
+      for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {                   // a warp reads 32 input channels (36 loads in flight)
+        const int co = q / KK, tap = q - co * KK;
+        float v = 0.f;
+        if (co0 + co < cout && ci0 + lane < cin) v = __ldg(in + src + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + lane);
+        tile[co * 289 + lane * 9 + tap] = v;
+      }
+      __syncthreads();
+#pragma unroll 12
+      for (int i = threadIdx.x; i < 32 * RUN; i += 256) {                     // contiguous (ci, tap) runs per cout
+        const int co = i / RUN, r = i - co * RUN;
+        const int ci = r / KK, tap = r - ci * KK;
+        if (co0 + co < cout && ci0 + ci < cin) out[dst + ((size_t)(co0 + co) * cin + ci0 + ci) * KK + tap] = tile[co * 289 + r];
+      }
+    }
+  }
+}
+extern "C" int fb_unstage_conv_grads(const float* scratch, int64_t scratch_ld, float* grads, int64_t ld, int32_t C,
+                                     const int64_t* table_dev, int32_t n_layers, int32_t max_tiles, fb_stream_t stream) {
+  FB_REQUIRE(scratch && grads && table_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_unstage_conv_grads: bad arguments");
+  int gx = max_tiles < 1 ? 1 : (max_tiles > 64 ? 64 : max_tiles);
+  int gz = (8 * fb_num_sms()) / (gx * C);
+  if (gz > n_layers) gz = n_layers;
+  if (gz > 64) gz = 64;
+  if (gz < 1) gz = 1;
+  unstage_grads_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(scratch, scratch_ld, grads, ld, table_dev, n_layers);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

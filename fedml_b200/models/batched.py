@@ -507,22 +507,27 @@ class _Conv:
 
     def _wgrad(self, be, dy2, x, gW, dy=None):
         C = x.shape[0]
+        pz = getattr(self, "_pz", be.grads_prezeroed)                 # gradient arena / scratch zeroed for this step?
+        scratch = getattr(self, "_dw_scratch", None)
+        if scratch is not None and scratch.shape[0] != C:
+            scratch = None
+        defer = scratch is not None and getattr(self, "_defer_scatter", False)   # one un-staging launch per step instead
         if self.k == 3 and dy is not None and be.conv3x3_wgrad_ok(x, dy, self.stride):
-            scratch = getattr(self, "_dw_scratch", None)              # implicit GEMM: shifted windows gathered by TMA
-            ok = be.grads_prezeroed and scratch is not None and scratch.shape[0] == C
-            dWm = be.conv3x3_wgrad(x, dy, self.stride, out=scratch if ok else None, out_is_zeroed=ok)
-            gW.copy_(dWm.view(C, self.cout, 3, 3, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
+            dWm = be.conv3x3_wgrad(x, dy, self.stride, out=scratch, out_is_zeroed=pz and scratch is not None)
+            if not defer:                                             # implicit GEMM: shifted windows gathered by TMA
+                gW.copy_(dWm.view(C, self.cout, 3, 3, self.cin)[..., :self.cin_real].permute(0, 1, 4, 2, 3))
             return
         cols, _, _ = self._cols(be, x)
         if self.k == 1 and self.cin == self.cin_real:
-            # straight into the gradient arena (zeroed once per step, so split-K slices can reduce-add in place)
-            be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin), out_is_zeroed=be.grads_prezeroed)
+            # straight into the gradient arena (split-K slices reduce-add in place when it was zeroed for the step)
+            be.gemm_tn(dy2, cols, out=gW.view(C, self.cout, self.cin), out_is_zeroed=pz)
             return
-        scratch = getattr(self, "_dw_scratch", None)
-        if be.grads_prezeroed and scratch is not None and scratch.shape[0] == C:
-            dWm = be.gemm_tn(dy2, cols, out=scratch, out_is_zeroed=True)
+        if scratch is not None:
+            dWm = be.gemm_tn(dy2, cols, out=scratch, out_is_zeroed=pz)
         else:
             dWm = be.gemm_tn(dy2, cols)                               # [C, cout, kk*cin] fp32
+        if defer:
+            return
         if self.k == 1:
             gW.copy_(dWm.view(C, self.cout, self.cin, 1, 1)[:, :, :self.cin_real])
         else:
@@ -765,24 +770,49 @@ class BatchedResNet(BatchedModel):
         return logits, feat, h
 
     def _zero_grads(self, G):
-        """One memset for the gradient arena and one for the 3x3 weight-gradient scratch (split-K slices of the
-        weight-gradient GEMMs reduce-add into them)."""
+        """Per-step gradient bookkeeping of the native back-end.  Weight-gradient GEMMs of k x k (and channel-padded)
+        convolutions write the GEMM layout into one scratch stack; one un-staging launch per step scatters it into the
+        gradient arena.  For models whose arena is small the arena and the scratch are zeroed (two memsets) so that
+        split-K slices can reduce-add in place; for big models (ResNet-18 x 64 clients = 2.9 GB) zeroing would cost
+        more than the partial-buffer reduction it avoids."""
         arena = getattr(G, "arena", None)
-        if arena is None or not self.be.grads_prezeroed:
+        if arena is None or not isinstance(self.be, NativeBackend):
             return
-        arena[:, :G.layout.P_train].zero_()
         C = arena.shape[0]
+        P_train = G.layout.P_train
+        pz = bool(self.be.grads_prezeroed) and C * P_train * 4 <= (1 << 30)
         big = getattr(self, "_dw_big", None)
         need = [c for c in self.convs if not (c.k == 1 and c.cin == c.cin_real)]
         if big is None or big.shape[0] != C:
             sizes = [(c.cout * c.k * c.k * c.cin + 3) // 4 * 4 for c in need]
             big = self._dw_big = torch.zeros((C, sum(sizes)), dtype=torch.float32, device=arena.device)
-            off = 0
+            off, rows = 0, []
             for c, n in zip(need, sizes):
                 c._dw_scratch = big[:, off:off + c.cout * c.k * c.k * c.cin].view(C, c.cout, c.k * c.k * c.cin)
+                seg = G.layout.by_name[c.wname]
+                rows.append([off, c.cout, c.cin_real, c.cin, c.k, seg.offset, 0, 0])
+                c._defer_scatter = c.k * c.k <= 9
                 off += n
-        else:
+            self._unstage = None
+            if rows and all(c._defer_scatter for c in need):
+                self._unstage = (torch.tensor(rows, dtype=torch.int64).to(arena.device), len(rows),
+                                 max(((r[1] + 31) // 32) * ((r[2] + 31) // 32) for r in rows))
+            else:
+                for c in need:
+                    c._defer_scatter = False
+        elif pz:
             big.zero_()
+        if pz:
+            arena[:, :P_train].zero_()
+        for c in self.convs:
+            c._pz = pz
+
+    def _scatter_grads(self, G):
+        """GEMM-layout weight gradients -> parameter layout in the arena (one launch; on the weight-gradient branch)."""
+        un = getattr(self, "_unstage", None)
+        if un is not None:
+            with self.be.side():
+                self.be.ops.unstage_conv_grads(self._dw_big, G.arena, un[0], un[1], un[2])
 
     def train_step(self, x, y, W, G, active, row_scale=None):
         be = self.be
@@ -802,6 +832,7 @@ class BatchedResNet(BatchedModel):
         x0, a, hstem, m, r = tape[0]
         da, _ = self.stem_bn.bwd(be, d, a, hstem, W, G, m, r, relu=True, want_dres=False)
         self.stem_conv.bwd(be, da, x0, Wm["conv1"], G["conv1.weight"])
+        self._scatter_grads(G)
         be.join()
         return loss
 

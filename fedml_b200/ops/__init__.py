@@ -494,6 +494,14 @@ def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Te
     count_launch()
 
 
+def unstage_conv_grads(scratch: torch.Tensor, grads: torch.Tensor, table: torch.Tensor, n_layers: int, max_tiles: int):
+    """GEMM-layout weight gradients (rows of ``scratch`` fp32 [C, *]) -> parameter layout inside the gradient arena."""
+    check(lib().fb_unstage_conv_grads(vp(ptr(scratch)), i64(scratch.stride(0)), vp(ptr(grads)), i64(grads.stride(0)),
+                                      i32(grads.shape[0]), vp(ptr(table)), i32(n_layers), i32(max_tiles),
+                                      vp(stream_ptr(grads.device))), "unstage_conv_grads")
+    count_launch()
+
+
 # --------------------------------------------------------------------------- K14 amplitude normalisation (hand-written FFT)
 def amp_normalize_supported(x: torch.Tensor) -> bool:
     ok = lambda v: 8 <= v <= 512 and (v & (v - 1)) == 0   # noqa: E731

@@ -232,6 +232,12 @@ int fb_softmax_xent(const float* logits, const int64_t* labels, int64_t R, int32
  * cast/permute kernels per layer per step. */
 int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage_bf16, int64_t stage_ld,
                           const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream);
+/* The inverse direction for k x k weight gradients: GEMM-layout fp32 [cout][(kh,kw,cin_pad)] rows of a scratch stack
+ * -> parameter layout [cout][cin][kh][kw] inside the gradient arena, all listed layers of all clients in one launch.
+ * table_dev: int64 [n_layers][8] = {src_off, cout, cin, cin_pad, k, dst_off, 0, 0}; max_tiles = largest
+ * ceil(cout/32)*ceil(cin/32) of a layer. */
+int fb_unstage_conv_grads(const float* scratch, int64_t scratch_ld, float* grads, int64_t ld, int32_t C,
+                          const int64_t* table_dev, int32_t n_layers, int32_t max_tiles, fb_stream_t stream);
 /* K15 fused evaluation: counters[0]=correct, [1]=loss_sum, [2]=total, then tp[ncls], fp[ncls], fn[ncls]
  * (all float64-free: uint32 counts in `counts`, float loss in `loss_sum`). Accumulates into the outputs. */
 int fb_eval_counts(const float* logits, const int64_t* labels, int64_t R, int32_t ncls, int32_t pre_sigmoid,
