@@ -280,11 +280,12 @@ def _bn_fused(x) -> bool:
 
 
 def _scratch_for(device, n_floats):
-    key = str(device)
+    """Partial-sum scratch, one buffer per (device, stream): client groups that train concurrently on several
+    streams (fedml_b200/simulation/nccl) must not share it."""
+    key = (str(device), torch.cuda.current_stream(device).cuda_stream)
     buf = _bn_scratch.get(key)
     if buf is None or buf.numel() < n_floats:
-        buf = torch.empty(max(n_floats, 1 << 16), dtype=torch.float32, device=device)
-        _bn_scratch[key] = buf
+        buf = _bn_scratch[key] = torch.empty(max(n_floats, 1 << 16), dtype=torch.float32, device=device)
     return buf
 
 

@@ -21,7 +21,7 @@ _SCRATCH = {}
 
 
 def _scratch(device, n_floats: int) -> torch.Tensor:
-    key = (device.type, device.index)
+    key = (device.type, device.index, torch.cuda.current_stream(device).cuda_stream)   # per stream: see ops._scratch_for
     buf = _SCRATCH.get(key)
     if buf is None or buf.numel() < n_floats:
         buf = _SCRATCH[key] = torch.empty(max(n_floats, 1 << 16), dtype=torch.float32, device=device)

@@ -345,8 +345,10 @@ class NCCLSimulator:
             self._sparse_range = rng
         return self._sparse_range
 
-    def _sgd(self, C, lr_vec, first_step):
+    def _sgd(self, C, lr_vec, first_step, rows=None):
+        """Fused multi-client optimizer step on arena rows [r0, r1) (default: the first C rows)."""
         n = self.P_train
+        r0, r1 = rows if rows is not None else (0, C)
         anchor = self.global_flat if self.mu else None
         skip = self._sparse_sgd_range() if self.batched is not None else None
         if skip is not None:
@@ -356,20 +358,21 @@ class NCCLSimulator:
                     continue
                 if self.cuda:
                     from ... import ops
-                    ops.sgd_step_stacked(self.stack[:C, a:b], self.grad_stack[:C, a:b], b - a, lr_vec)
+                    ops.sgd_step_stacked(self.stack[r0:r1, a:b], self.grad_stack[r0:r1, a:b], b - a, lr_vec)
                 else:
-                    self.stack[:C, a:b].sub_(lr_vec[:C, None] * self.grad_stack[:C, a:b])
+                    self.stack[r0:r1, a:b].sub_(lr_vec[:r1 - r0, None] * self.grad_stack[r0:r1, a:b])
             return
         if self.cuda:
             from ... import ops
-            ops.sgd_step_stacked(self.stack[:C], self.grad_stack[:C], n, lr_vec, weight_decay=self.wd,
-                                 momentum=self.momentum, mom_buf=self.mom_stack, first_step=first_step, mu=self.mu,
-                                 anchor=anchor)
+            ops.sgd_step_stacked(self.stack[r0:r1], self.grad_stack[r0:r1], n, lr_vec, weight_decay=self.wd,
+                                 momentum=self.momentum, mom_buf=None if self.mom_stack is None else self.mom_stack[r0:r1],
+                                 first_step=first_step, mu=self.mu, anchor=anchor)
         else:
-            w, g = self.stack[:C, :n], self.grad_stack[:C, :n]
+            C = r1 - r0
+            w, g = self.stack[r0:r1, :n], self.grad_stack[r0:r1, :n]
             d = g + self.wd * w if self.wd else g.clone()
             if self.momentum:
-                buf = self.mom_stack[:C, :n]
+                buf = self.mom_stack[r0:r1, :n]
                 if first_step:
                     buf.copy_(d)
                 else:
@@ -379,8 +382,52 @@ class NCCLSimulator:
                 d = d + self.mu * (w - anchor[:n])
             w.sub_(lr_vec[:C, None] * d)
 
+    def _client_groups(self):
+        """Optional (``client_groups`` > 1): split the clients of this GPU into groups that advance on separate
+        streams; inside the captured CUDA graph these are parallel branches.  Each group has its own executor
+        (staging buffers, side stream, scratch).  Off by default, see the measurement note below."""
+        if not hasattr(self, "_groups"):
+            C = self.C_max
+            want = int(getattr(self.args, "client_groups", 0) or os.environ.get("FB_CLIENT_GROUPS", "0") or 0)
+            if want <= 0:
+                # measured on B200 (ResNet-56, 13 / 25 / 50 clients): 2-4 groups are 1-8 % SLOWER than one group, because
+                # every kernel already sizes its grid to the whole GPU; kept as an option for models with tiny layers
+                want = 1
+            want = max(1, min(want, C))
+            groups = []
+            if self.cuda and want > 1 and not self.momentum:
+                from ...models.batched import NativeBackend, make_batched
+                bounds = [round(i * C / want) for i in range(want + 1)]
+                for g in range(want):
+                    a, b = bounds[g], bounds[g + 1]
+                    if b <= a:
+                        continue
+                    ex = make_batched(self.model, NativeBackend(self.batched.be.dtype))
+                    groups.append({"rows": (a, b), "exec": ex, "stream": torch.cuda.Stream(self.device),
+                                   "W": self.layout.stacked_views(self.stack[a:b]),
+                                   "G": self.layout.stacked_views(self.grad_stack[a:b])})
+            self._groups = groups
+        return self._groups
+
     def _step_body(self, st):
-        if self._sparse_sgd_range() is not None:
+        sparse = self._sparse_sgd_range() is not None
+        groups = self._client_groups()
+        if groups:
+            cur = torch.cuda.current_stream()
+            for gr in groups:
+                a, b = gr["rows"]
+                gr["stream"].wait_stream(cur)
+                with torch.cuda.stream(gr["stream"]):
+                    if sparse:
+                        gr["exec"].set_sparse_sgd(st["lr"][a:b])
+                    loss = gr["exec"].train_step(st["x"][a:b], st["y"][a:b], gr["W"], gr["G"], st["active"][a:b],
+                                                 st["scale"][a:b])
+                    self._sgd(b - a, st["lr"][a:b], False, rows=(a, b))
+                    st["loss"][a:b].copy_(loss)
+            for gr in groups:
+                cur.wait_stream(gr["stream"])
+            return
+        if sparse:
             self.batched.set_sparse_sgd(st["lr"])
         loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
         self._sgd(self.C_max, st["lr"], False)
