@@ -43,6 +43,44 @@ static inline int fb_num_sms() {
   return sms[dev];
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch (PDL)
+// Kernels of the local training step form one long dependent chain of small launches.  Launched with the
+// programmatic-stream-serialization attribute, kernel N+1 is scheduled while kernel N drains: its CTAs run their
+// prologue (barrier init, TMEM allocation, tensor-map prefetch, index setup) and then block in pdl_wait() until every
+// CTA of kernel N has finished and its memory is visible.  Every kernel launched this way calls pdl_wait() before its
+// first global-memory access and pdl_trigger() right after, so the chain never reads stale data.  Stream capture turns
+// the attribute into programmatic edges of the CUDA graph.  FB_PDL=0 turns the attribute off (plain launches).
+#include <stdlib.h>
+#include <utility>
+static inline int fb_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FB_PDL");
+    v = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return v;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t fb_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                        Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = fb_pdl_enabled();
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -182,6 +182,8 @@ static int bn_slices(int C, int64_t M, int ch) {
 __global__ void __launch_bounds__(BN_THREADS)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial) {
   __shared__ float smem[BN_THREADS * 16];
+  pdl_wait();
+  pdl_trigger();
   bn_stats_body(x, M, ch, S, partial, smem);
 }
 __global__ void __launch_bounds__(BN_THREADS)
@@ -191,6 +193,8 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 float momentum, float eps, int relu, int training, float* __restrict__ save_mean,
                 float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n) {
   extern __shared__ float sm[];
+  pdl_wait();
+  pdl_trigger();
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu,
                 training, save_mean, save_rstd, num_batches_tracked, ld_n, sm);
 }
@@ -228,6 +232,8 @@ bn_fwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     float* num_batches_tracked, int64_t ld_n) {
   __shared__ float smem[BN_THREADS * 16];
   extern __shared__ float sm[];
+  pdl_wait();
+  pdl_trigger();
   bn_stats_body(x, M, ch, S, partial, smem);
   client_barrier(S);
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu, 1,
@@ -259,19 +265,19 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
   FB_REQUIRE(!training || scratch, "fb_bn_fwd_stacked: training needs the partial-sum scratch");
   const int S = bn_slices(C, M, ch);
   if (training && bn_fused_enabled((int64_t)C * M * ch * 2)) {
-    bn_fwd_fused_kernel<<<dim3(S, C), BN_THREADS, 2 * ch * sizeof(float), (cudaStream_t)stream>>>(
+    FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
-        running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n);
+        running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
   if (training) {
-    bn_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, M, ch, S, scratch);
+    FB_CHECK_CUDA(fb_launch_pdl(bn_stats_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, M, ch, S, scratch));
     FB_CHECK_CUDA(cudaGetLastError());
   }
-  bn_apply_kernel<<<dim3(S, C), BN_THREADS, 2 * ch * sizeof(float), (cudaStream_t)stream>>>(
+  FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
       (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p,
-      running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd, num_batches_tracked, ld_n);
+      running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd, num_batches_tracked, ld_n));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -441,6 +447,8 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                     int relu, float* __restrict__ partial) {
   __shared__ float smem[BN_THREADS * 16];
+  pdl_wait();
+  pdl_trigger();
   bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
 }
 __global__ void __launch_bounds__(BN_THREADS)
@@ -450,6 +458,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g) {
   extern __shared__ float sm[];
+  pdl_wait();
+  pdl_trigger();
   bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
 }
 __global__ void __launch_bounds__(BN_THREADS)
@@ -460,6 +470,8 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     float* __restrict__ dbeta, int64_t ld_g) {
   __shared__ float smem[BN_THREADS * 16];
   extern __shared__ float sm[];
+  pdl_wait();
+  pdl_trigger();
   bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
   client_barrier(S);
   bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
@@ -476,19 +488,19 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x,
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   const int S = bn_slices(C, M, ch);
   if (bn_fused_enabled((int64_t)C * M * ch * 2)) {
-    bn_bwd_fused_kernel<<<dim3(S, C), BN_THREADS, 4 * ch * sizeof(float), (cudaStream_t)stream>>>(
+    FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
-        (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
+        (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
-  bn_bwd_stats_kernel<<<dim3(S, C), BN_THREADS, 0, (cudaStream_t)stream>>>(
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_stats_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, 
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
-      beta, ld_p, relu, scratch);
+      beta, ld_p, relu, scratch));
   FB_CHECK_CUDA(cudaGetLastError());
-  bn_bwd_apply_kernel<<<dim3(S, C), BN_THREADS, 4 * ch * sizeof(float), (cudaStream_t)stream>>>(
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_apply_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
-      (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g);
+      (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -502,6 +514,8 @@ im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict_
   // guarantees total_vec < 2^32
   const uint32_t cv = ch / 8, per_pix = 9u * cv, per_row = per_pix * (uint32_t)Wo, per_img = per_row * (uint32_t)Ho;
   const uint32_t total = (uint32_t)total_vec;
+  pdl_wait();
+  pdl_trigger();
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const uint32_t n = i / per_img, r0 = i - n * per_img;
     const uint32_t ho = r0 / per_row, r1 = r0 - ho * per_row;
@@ -522,8 +536,8 @@ extern "C" int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, 
   const int64_t total = (int64_t)n_img * Ho * Wo * 9 * (ch / 8);
   FB_REQUIRE(total < 4294967296LL, "fb_im2col3x3_nhwc_bf16: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
-  im2col3x3_kernel<<<(int)(grid < cap ? grid : cap), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)cols, total, H, W, Ho, Wo, ch, stride);
+  FB_CHECK_CUDA(fb_launch_pdl(im2col3x3_kernel, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)cols, total, H, W, Ho, Wo, ch, stride));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -534,6 +548,8 @@ col2im3x3_kernel(const __nv_bfloat16* __restrict__ cols, __nv_bfloat16* __restri
                  int Ho, int Wo, int ch, int stride) {
   const uint32_t cv = ch / 8, per_row = cv * (uint32_t)W, per_img = per_row * (uint32_t)H;
   const uint32_t total = (uint32_t)total_vec;
+  pdl_wait();
+  pdl_trigger();
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const uint32_t n = i / per_img, r0 = i - n * per_img;
     const int h = (int)(r0 / per_row);
@@ -571,8 +587,8 @@ extern "C" int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img,
   FB_REQUIRE(total < 4294967296LL && (int64_t)n_img * Ho * Wo * 9 * (ch / 8) < 4294967296LL,
              "fb_col2im3x3_nhwc_bf16: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
-  col2im3x3_kernel<<<(int)(grid < cap ? grid : cap), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)cols, (__nv_bfloat16*)dx, total, H, W, Ho, Wo, ch, stride);
+  FB_CHECK_CUDA(fb_launch_pdl(col2im3x3_kernel, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      (const __nv_bfloat16*)cols, (__nv_bfloat16*)dx, total, H, W, Ho, Wo, ch, stride));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

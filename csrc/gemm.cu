@@ -206,6 +206,10 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // programmatic dependent launch: everything above overlapped the tail of the previous kernel; operands (and the
+  // output buffer) may only be touched once that kernel has completed
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -606,13 +610,13 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   if (grid > total) grid = total;
   if (mode == 3) {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<3><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<3>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   } else if (mode == 2) {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<2><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<2>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   } else {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    grouped_gemm_kernel<0><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<0>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   }
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
@@ -721,7 +725,7 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
   FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  grouped_gemm_kernel<4><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+  FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<4>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -814,7 +818,7 @@ extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream
   int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
   FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  grouped_gemm_kernel<5><<<grid, GEMM_THREADS, smem, (cudaStream_t)stream>>>(tmA, tmB, tmD, a);
+  FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<5>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
