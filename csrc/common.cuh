@@ -49,14 +49,14 @@ static inline int fb_num_sms() {
 // prologue (barrier init, TMEM allocation, tensor-map prefetch, index setup) and then block in pdl_wait() until every
 // CTA of kernel N has finished and its memory is visible.  Every kernel launched this way calls pdl_wait() before its
 // first global-memory access and pdl_trigger() right after, so the chain never reads stale data.  Stream capture turns
-// the attribute into programmatic edges of the CUDA graph.  FB_PDL=1 turns the attribute on (default: plain launches).
+// the attribute into programmatic edges of the CUDA graph.  FB_PDL=0 turns the attribute off (plain launches).
 #include <stdlib.h>
 #include <utility>
 static inline int fb_pdl_enabled() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("FB_PDL");
-    v = (e && atoi(e) != 0) ? 1 : 0;   // opt-in until validated on the target box
+    v = (e && atoi(e) == 0) ? 0 : 1;
   }
   return v;
 }

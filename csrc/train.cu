@@ -15,6 +15,8 @@ sgd_step_stacked_kernel(float* __restrict__ w, const float* __restrict__ g, int6
                         const float* __restrict__ lr_dev, float wd, float momentum, float dampening, int nesterov,
                         float* __restrict__ mom, int first_step, float mu, const float* __restrict__ anchor,
                         float* __restrict__ cum) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int64_t total = nvec_row * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i / nvec_row);
@@ -60,8 +62,8 @@ extern "C" int fb_sgd_step_stacked(float* w, const float* g, int64_t ld, int32_t
   FB_REQUIRE(w && g && lr_dev && C >= 1 && n > 0 && n % 4 == 0 && ld % 4 == 0 && ld >= n, "fb_sgd_step_stacked: bad shape");
   FB_REQUIRE(momentum == 0.f || mom_buf, "fb_sgd_step_stacked: momentum needs mom_buf");
   FB_REQUIRE(mu == 0.f || anchor, "fb_sgd_step_stacked: mu needs the anchor (global) model");
-  sgd_step_stacked_kernel<<<ew_grid(n / 4 * C), 256, 0, (cudaStream_t)stream>>>(
-      w, g, ld, C, n / 4, lr_dev, weight_decay, momentum, dampening, nesterov, mom_buf, first_step, mu, anchor, cum_grad);
+  FB_CHECK_CUDA(fb_launch_pdl(sgd_step_stacked_kernel, dim3(ew_grid(n / 4 * C)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      w, g, ld, C, n / 4, lr_dev, weight_decay, momentum, dampening, nesterov, mom_buf, first_step, mu, anchor, cum_grad));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -70,6 +72,8 @@ __global__ void __launch_bounds__(256)
 sgd_step_stacked_bf16g_kernel(float* __restrict__ w, const __nv_bfloat16* __restrict__ g, int64_t ld, int64_t ld_g,
                               int C, int64_t nvec_row, const float* __restrict__ lr_dev, float wd, float mu,
                               const float* __restrict__ anchor) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int64_t total = nvec_row * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i / nvec_row);
@@ -97,8 +101,8 @@ extern "C" int fb_sgd_step_stacked_bf16g(float* w, const void* g_bf16, int64_t l
   FB_REQUIRE(w && g_bf16 && lr_dev && C >= 1 && n > 0 && n % 4 == 0 && ld % 4 == 0 && ld_g % 4 == 0,
              "fb_sgd_step_stacked_bf16g: bad shape");
   FB_REQUIRE(mu == 0.f || anchor, "fb_sgd_step_stacked_bf16g: mu needs the anchor (global) model");
-  sgd_step_stacked_bf16g_kernel<<<ew_grid(n / 4 * C), 256, 0, (cudaStream_t)stream>>>(
-      w, (const __nv_bfloat16*)g_bf16, ld, ld_g, C, n / 4, lr_dev, weight_decay, mu, anchor);
+  FB_CHECK_CUDA(fb_launch_pdl(sgd_step_stacked_bf16g_kernel, dim3(ew_grid(n / 4 * C)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      w, (const __nv_bfloat16*)g_bf16, ld, ld_g, C, n / 4, lr_dev, weight_decay, mu, anchor));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -115,6 +119,8 @@ __global__ void __launch_bounds__(256)
 softmax_xent_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, int64_t R, int ncls,
                     int64_t ignore_index, int pre_sigmoid, const float* __restrict__ row_scale, int64_t rows_per_group,
                     float* __restrict__ loss_rows, float* __restrict__ dlogits) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -164,8 +170,8 @@ extern "C" int fb_softmax_xent(const float* logits, const int64_t* labels, int64
   if (rows_per_group < 1) rows_per_group = 1;
   int64_t want = (R * 32 + 255) / 256, cap = (int64_t)fb_num_sms() * 8;
   int grid = (int)(want < cap ? want : cap);
-  softmax_xent_kernel<<<grid < 1 ? 1 : grid, 256, 0, (cudaStream_t)stream>>>(
-      logits, labels, R, ncls, ignore_index, pre_sigmoid, row_scale, rows_per_group, loss_rows, dlogits);
+  FB_CHECK_CUDA(fb_launch_pdl(softmax_xent_kernel, dim3(grid < 1 ? 1 : grid), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      logits, labels, R, ncls, ignore_index, pre_sigmoid, row_scale, rows_per_group, loss_rows, dlogits));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -175,6 +181,8 @@ extern "C" int fb_softmax_xent(const float* logits, const int64_t* labels, int64
 __global__ void __launch_bounds__(256)
 eval_counts_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, int64_t R, int ncls,
                    int pre_sigmoid, uint32_t* __restrict__ counts, float* __restrict__ loss_sum) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   __shared__ float red[33];
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -233,8 +241,8 @@ extern "C" int fb_eval_counts(const float* logits, const int64_t* labels, int64_
   FB_REQUIRE(logits && labels && counts && loss_sum && R > 0 && ncls > 0, "fb_eval_counts: bad shape");
   int64_t want = (R * 32 + 255) / 256, cap = (int64_t)fb_num_sms() * 4;
   int grid = (int)(want < cap ? want : cap);
-  eval_counts_kernel<<<grid < 1 ? 1 : grid, 256, 0, (cudaStream_t)stream>>>(logits, labels, R, ncls, pre_sigmoid, counts,
-                                                                            loss_sum);
+  FB_CHECK_CUDA(fb_launch_pdl(eval_counts_kernel, dim3(grid < 1 ? 1 : grid), dim3(256), (size_t)(0), (cudaStream_t)stream, logits, labels, R, ncls, pre_sigmoid, counts,
+                                                                            loss_sum));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -247,6 +255,8 @@ extern "C" int fb_eval_counts(const float* logits, const int64_t* labels, int64_
 __global__ void __launch_bounds__(256)
 stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16* __restrict__ stage, int64_t stage_ld,
                      const int64_t* __restrict__ table, int n_layers) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int c = blockIdx.y;
   const float* row = arena + (size_t)c * ld;
   __nv_bfloat16* out = stage + (size_t)c * stage_ld;
@@ -328,8 +338,8 @@ extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, 
   if (gx > gx_cap) gx = gx_cap;
   if (gx < 1) gx = 1;
   int gz = n_layers < 64 ? n_layers : 64;
-  stage_weights_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(arena, ld, (__nv_bfloat16*)stage, stage_ld,
-                                                                         table_dev, n_layers);
+  FB_CHECK_CUDA(fb_launch_pdl(stage_weights_kernel, dim3(dim3(gx, C, gz)), dim3(256), (size_t)(0), (cudaStream_t)stream, arena, ld, (__nv_bfloat16*)stage, stage_ld,
+                                                                         table_dev, n_layers));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -342,6 +352,8 @@ extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, 
 __global__ void __launch_bounds__(256)
 unstage_grads_kernel(const float* __restrict__ scratch, int64_t scratch_ld, float* __restrict__ grads, int64_t ld,
                      const int64_t* __restrict__ table, int n_layers) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   __shared__ float tile[32 * 289];   // [cout 32][cin 32][tap 9] + 1 pad per row: every access pattern below is conflict-free
   const int c = blockIdx.y;
   const float* in = scratch + (size_t)c * scratch_ld;
@@ -391,7 +403,7 @@ extern "C" int fb_unstage_conv_grads(const float* scratch, int64_t scratch_ld, f
   if (gz > n_layers) gz = n_layers;
   if (gz > 64) gz = 64;
   if (gz < 1) gz = 1;
-  unstage_grads_kernel<<<dim3(gx, C, gz), 256, 0, (cudaStream_t)stream>>>(scratch, scratch_ld, grads, ld, table_dev, n_layers);
+  FB_CHECK_CUDA(fb_launch_pdl(unstage_grads_kernel, dim3(dim3(gx, C, gz)), dim3(256), (size_t)(0), (cudaStream_t)stream, scratch, scratch_ld, grads, ld, table_dev, n_layers));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

@@ -57,6 +57,8 @@ __device__ __forceinline__ float warp_max(float v) {
 __global__ void __launch_bounds__(TF_THREADS)
 embed_gather_kernel(const int64_t* __restrict__ ids, const float* __restrict__ word, const float* __restrict__ pos,
                     int64_t ld, __nv_bfloat16* __restrict__ out, int64_t R, int S, int D, int vocab) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
   const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
   if (r >= R) return;
@@ -79,6 +81,8 @@ embed_gather_kernel(const int64_t* __restrict__ ids, const float* __restrict__ w
 __global__ void __launch_bounds__(TF_THREADS)
 embed_word_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dz, float* __restrict__ gword,
                       int64_t ld, int64_t R, int D, int vocab, const float* __restrict__ client_scale) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
   const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
   if (r >= R) return;
@@ -99,6 +103,8 @@ embed_word_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __re
 // gpos[c][s][:] = sum_b dz[c][b*S + s][:]   (deterministic: one thread owns 8 columns of one position)
 __global__ void __launch_bounds__(TF_THREADS)
 embed_pos_bwd_kernel(const __nv_bfloat16* __restrict__ dz, float* __restrict__ gpos, int64_t ld, int B, int S, int D) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int c = blockIdx.y;
   const int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x;     // vector index inside [S][D/8]
   const int nv = D / 8;
@@ -124,6 +130,8 @@ __global__ void __launch_bounds__(TF_THREADS)
 add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ z,
                   __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out,
                   const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p, int64_t R, int D, float eps) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y;
   const int64_t r = (int64_t)blockIdx.x * TF_WARPS + warp;
   if (r >= R) return;
@@ -190,6 +198,8 @@ __global__ void __launch_bounds__(TF_THREADS, 2)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ z,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               int64_t ld_p, __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, int64_t R, int D, int slices) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   extern __shared__ float4 acc4[];                 // [warp][quantity q][vector i][half][lane] float4
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.y, s = blockIdx.x;
   const int nv = D >> 3;
@@ -268,6 +278,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 __global__ void __launch_bounds__(TF_THREADS)
 ln_bwd_finish_kernel(const float* __restrict__ partial, int slices, int D, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      int64_t ld_g) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const int c = blockIdx.y, k = blockIdx.x * TF_THREADS + threadIdx.x;
   if (k >= 2 * D) return;
   float acc = 0.f;
@@ -327,6 +339,8 @@ __global__ void __launch_bounds__(TF_THREADS)
 softmax_fwd_kernel(const float* __restrict__ scores, __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ Pd,
                    const float* __restrict__ key_mask, int64_t rows, int S, int H, float scale, float p, uint64_t seed,
                    uint32_t site, const uint32_t* __restrict__ step_dev) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   constexpr int RPW = 32 / LPR;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, l = lane % LPR;
   const int64_t row = ((int64_t)blockIdx.x * TF_WARPS + warp) * RPW + lane / LPR;
@@ -385,6 +399,8 @@ __global__ void __launch_bounds__(TF_THREADS)
 softmax_bwd_kernel(const float* __restrict__ dP, const __nv_bfloat16* __restrict__ P, __nv_bfloat16* __restrict__ dS,
                    int64_t rows, int S, float scale, float p, uint64_t seed, uint32_t site,
                    const uint32_t* __restrict__ step_dev) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   constexpr int RPW = 32 / LPR;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, l = lane % LPR;
   const int64_t row = ((int64_t)blockIdx.x * TF_WARPS + warp) * RPW + lane / LPR;
@@ -440,6 +456,8 @@ __device__ __forceinline__ float gelu_grad(float x) {
 // mode 0: ReLU, 1: GELU (erf)
 __global__ void __launch_bounds__(TF_THREADS)
 act_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t nvec, int mode) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8];
     unpack8(ldg16(x + v * 8), f);
@@ -452,6 +470,8 @@ act_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ 
 __global__ void __launch_bounds__(TF_THREADS)
 act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dx,
                int64_t nvec, int mode) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8], g[8];
     unpack8(ldg16(x + v * 8), f);
@@ -466,6 +486,8 @@ act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __rest
 __global__ void __launch_bounds__(TF_THREADS)
 dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, __nv_bfloat16* __restrict__ y,
                int64_t nvec, float p, uint64_t seed, uint32_t site, const uint32_t* __restrict__ step_dev) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   const DropKey key = make_drop_key(p, seed, site, step_dev);
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8];
@@ -485,6 +507,8 @@ dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restr
 __global__ void __launch_bounds__(TF_THREADS)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t R, int N, int64_t ldx, int64_t cs, float* __restrict__ out,
               int64_t ld_o) {
+  pdl_wait();      // programmatic dependent launch: see common.cuh
+  pdl_trigger();
   __shared__ float red[32][65];
   const int c = blockIdx.y, tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
   const int col = blockIdx.x * 64 + tx * 8;
@@ -527,8 +551,8 @@ extern "C" int fb_embed_gather(const int64_t* ids, const float* word, const floa
              "fb_embed_gather: bad shape");
   FB_REQUIRE(ld % 4 == 0 && TF_ALIGNED16(word) && TF_ALIGNED16(pos) && TF_ALIGNED16(out_bf16),
              "fb_embed_gather: tables and output must be 16-byte aligned");
-  embed_gather_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      ids, word, pos, ld, (__nv_bfloat16*)out_bf16, R, S, D, vocab);
+  FB_CHECK_CUDA(fb_launch_pdl(embed_gather_kernel, dim3(dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, 
+      ids, word, pos, ld, (__nv_bfloat16*)out_bf16, R, S, D, vocab));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -539,11 +563,11 @@ extern "C" int fb_embed_bwd(const int64_t* ids, const void* dz_bf16, float* gwor
   FB_REQUIRE(C >= 1 && C <= 65535 && R >= 1 && S >= 1 && R % S == 0 && D >= 8 && D % 8 == 0 && vocab >= 1,
              "fb_embed_bwd: bad shape");
   FB_REQUIRE(ld % 4 == 0 && TF_ALIGNED16(gpos) && TF_ALIGNED16(dz_bf16), "fb_embed_bwd: buffers must be 16-byte aligned");
-  embed_word_bwd_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      ids, (const __nv_bfloat16*)dz_bf16, gword, ld, R, D, vocab, word_scale);
+  FB_CHECK_CUDA(fb_launch_pdl(embed_word_bwd_kernel, dim3(dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, 
+      ids, (const __nv_bfloat16*)dz_bf16, gword, ld, R, D, vocab, word_scale));
   const int64_t nv = (int64_t)S * (D / 8);
-  embed_pos_bwd_kernel<<<dim3((unsigned)((nv + TF_THREADS - 1) / TF_THREADS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dz_bf16, gpos, ld, (int)(R / S), S, D);
+  FB_CHECK_CUDA(fb_launch_pdl(embed_pos_bwd_kernel, dim3(dim3((unsigned)((nv + TF_THREADS - 1) / TF_THREADS), C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, 
+      (const __nv_bfloat16*)dz_bf16, gpos, ld, (int)(R / S), S, D));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -556,9 +580,9 @@ extern "C" int fb_add_ln_fwd(const void* a, const void* b, void* z, void* y, flo
              "fb_add_ln_fwd: D must be a multiple of 8 and at most %d", 256 * LN_MAXV);
   FB_REQUIRE(ld_p % 4 == 0 && TF_ALIGNED16(gamma) && TF_ALIGNED16(beta) && TF_ALIGNED16(a) && TF_ALIGNED16(y),
              "fb_add_ln_fwd: buffers must be 16-byte aligned");
-  add_ln_fwd_kernel<<<dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C), TF_THREADS, 0, (cudaStream_t)stream>>>(
+  FB_CHECK_CUDA(fb_launch_pdl(add_ln_fwd_kernel, dim3(dim3((unsigned)((R + TF_WARPS - 1) / TF_WARPS), C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, 
       (const __nv_bfloat16*)a, (const __nv_bfloat16*)b, (__nv_bfloat16*)z, (__nv_bfloat16*)y, mean, rstd, gamma, beta, ld_p, R,
-      D, eps);
+      D, eps));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -605,8 +629,8 @@ extern "C" int fb_ln_bwd(const void* dy, const void* dy2, const void* z, const f
   else if (NV == 3) FB_LN_BWD(3);
   else FB_LN_BWD(4);
 #undef FB_LN_BWD
-  ln_bwd_finish_kernel<<<dim3((2 * D + TF_THREADS - 1) / TF_THREADS, C), TF_THREADS, 0, (cudaStream_t)stream>>>(scratch, S, D, dgamma,
-                                                                                                            dbeta, ld_g);
+  FB_CHECK_CUDA(fb_launch_pdl(ln_bwd_finish_kernel, dim3(dim3((2 * D + TF_THREADS - 1) / TF_THREADS, C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, scratch, S, D, dgamma,
+                                                                                                            dbeta, ld_g));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -652,7 +676,7 @@ extern "C" int fb_attn_softmax_bwd(const float* dP, const void* P_bf16, void* dS
 extern "C" int fb_act_fwd(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
   FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(y),
              "fb_act_fwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
-  act_fwd_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8, mode);
+  FB_CHECK_CUDA(fb_launch_pdl(act_fwd_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8, mode));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -661,8 +685,8 @@ extern "C" int fb_act_bwd(const void* dy, const void* x, void* dx, int64_t n, in
   FB_REQUIRE(dy && x && dx && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(dy) &&
                  TF_ALIGNED16(dx),
              "fb_act_bwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
-  act_bwd_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
-                                                                       (__nv_bfloat16*)dx, n / 8, mode);
+  FB_CHECK_CUDA(fb_launch_pdl(act_bwd_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
+                                                                       (__nv_bfloat16*)dx, n / 8, mode));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -671,8 +695,8 @@ extern "C" int fb_dropout_bf16(const void* x, const void* x2, void* y, int64_t n
                                const uint32_t* step_dev, fb_stream_t stream) {
   FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && p >= 0.f && p < 1.f && TF_ALIGNED16(x) && TF_ALIGNED16(x2) && TF_ALIGNED16(y),
              "fb_dropout_bf16: n must be a multiple of 8, buffers 16-byte aligned, 0 <= p < 1");
-  dropout_kernel<<<ew_grid(n / 8), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)x2,
-                                                                       (__nv_bfloat16*)y, n / 8, p, seed, site, step_dev);
+  FB_CHECK_CUDA(fb_launch_pdl(dropout_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)x2,
+                                                                       (__nv_bfloat16*)y, n / 8, p, seed, site, step_dev));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -682,8 +706,8 @@ extern "C" int fb_colsum_bf16(const void* x, int32_t C, int64_t R, int32_t N, in
   FB_REQUIRE(x && out && C >= 1 && C <= 65535 && R >= 1 && N >= 8 && N % 8 == 0 && ldx % 8 == 0 && client_stride % 8 == 0 &&
                  TF_ALIGNED16(x),
              "fb_colsum_bf16: N, ldx and the client stride must be multiples of 8, x 16-byte aligned");
-  colsum_kernel<<<dim3((N + 63) / 64, C), TF_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, R, N, ldx, client_stride,
-                                                                              out, ld_o);
+  FB_CHECK_CUDA(fb_launch_pdl(colsum_kernel, dim3(dim3((N + 63) / 64, C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, R, N, ldx, client_stride,
+                                                                              out, ld_o));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
