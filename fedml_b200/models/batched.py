@@ -327,6 +327,10 @@ class NativeBackend(TorchBackend):
     def gemm_nn(self, a, b, out_dtype=None, b_t=None):
         # [C,M,N] x [C,N,K]: the tensor-core kernel wants K-major operands -> a x (b^T)^T with the b^T copy
         # the layer prepared together with the weights
+        # [C,M,N] x [C,N,K]: the NN operand form feeds b MN-major straight from the [out][in] weights, so no transposed
+        # staging copy is needed; a prepared b^T (K-major) is used when the NN form does not cover the layout
+        if self.use_tc_gemm and self._tf().mm_supported("nn", a, b):
+            return self._tf().mm("nn", a, b, out_dtype=out_dtype or a.dtype)
         if self.use_tc_gemm and b_t is not None and self.ops.grouped_gemm_supported(a, b_t):
             return self.ops.grouped_gemm(a, b_t, out_dtype or a.dtype)
         self._fb("gemm_nn")
@@ -485,8 +489,13 @@ class _Conv:
             wm = w.reshape(C, self.cout, self.cin).to(dtype)
         else:
             wm = w.permute(0, 1, 3, 4, 2).reshape(C, self.cout, self.k * self.k * self.cin).to(dtype)
-        wt = wm.transpose(1, 2).contiguous() if (transposed and self.need_dx) else None
+        wt = wm.transpose(1, 2).contiguous() if (transposed and self.wants_transposed()) else None
         return wm, wt
+
+    def wants_transposed(self):
+        """Only the implicit stride-1 3x3 data gradient reads the transposed copy [k*k*cin, cout]; every other data
+        gradient uses the NN GEMM form on the forward operand."""
+        return self.need_dx and self.k == 3 and self.stride == 1
 
     def _cols(self, be, x):
         C, B, H, W_, _ = x.shape
@@ -723,7 +732,7 @@ class BatchedResNet(BatchedModel):
                 n = c.cout * c.k * c.k * c.cin
                 dst = off; off = al(off + n)
                 dstT = -1
-                if c.need_dx:
+                if c.wants_transposed():
                     dstT = off; off = al(off + n)
                 rows.append([seg.offset, c.cout, c.cin_real, c.cin, c.k, dst, dstT, n])
                 plan[c.name] = (dst, dstT, c.cout, c.k * c.k * c.cin)
