@@ -344,6 +344,181 @@ extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, 
   return FB_OK;
 }
 
+// ---------------------------------------------------------------- fused optimizer step + re-staging (plain SGD)
+// One launch per local step does, for every trainable segment of every client,  w -= lr[c] * g  AND refreshes the bf16
+// GEMM operands of the next step, so the separate staging pass (read w again, write bf16) and the gradient un-staging
+// pass (GEMM layout -> parameter layout) disappear: k x k weight gradients are read straight from the GEMM-layout
+// scratch the weight-gradient kernels wrote.  Table (int64 x 10 per segment):
+//   w_off, cout, cin, cin_pad, k, dst (stage offset or -1: no bf16 copy), dstT (or -1), n = cout*k*k*cin_pad,
+//   g_off, g_kind (0: gradient in the arena at w_off, parameter layout; 1: in the scratch stack at g_off, GEMM layout)
+// Plain segments (BN affine, biases, fc) are listed as cout = numel, cin = k = 1, dst = -1.
+#define RS_MAX_SEGS 1024
+#define RS_VEC_TILE 4096      /* elements per tile of the vector path */
+#define RS_GEN_TILE 2048      /* elements per tile of the element-wise path */
+struct RsSeg {
+  int64_t src, dst, dstT, goff;
+  int cout, cin, cinp, k, n, gkind, path;   // path 0: vector, 1: 3x3 tiles, 2: element-wise
+};
+__device__ __forceinline__ RsSeg rs_load(const int64_t* t, int64_t ld, int64_t stage_ld) {
+  RsSeg s;
+  s.src = t[0]; s.cout = (int)t[1]; s.cin = (int)t[2]; s.cinp = (int)t[3]; s.k = (int)t[4];
+  s.dst = t[5]; s.dstT = t[6]; s.n = (int)t[7]; s.goff = t[8]; s.gkind = (int)t[9];
+  if (s.k == 1 && s.cin == s.cinp && s.dstT < 0 && s.gkind == 0 && (s.n & 7) == 0 && (s.src & 3) == 0 &&
+      (s.dst < 0 || (s.dst & 7) == 0) && (ld & 3) == 0 && (stage_ld & 7) == 0)
+    s.path = 0;
+  else if (s.k == 3 && s.gkind == 1 && s.dst >= 0)
+    s.path = 1;
+  else
+    s.path = 2;
+  return s;
+}
+__device__ __forceinline__ int rs_tiles(const RsSeg& s) {
+  if (s.path == 0) return (s.n + RS_VEC_TILE - 1) / RS_VEC_TILE;
+  if (s.path == 1) return ((s.cout + 31) / 32) * ((s.cinp + 31) / 32);
+  return (s.n + RS_GEN_TILE - 1) / RS_GEN_TILE;
+}
+
+// grid (X, C): the CTAs of a client walk ONE flat list of tiles over all segments (prefix of per-segment tile counts in
+// shared memory), so small segments cost a tile, not a grid slice of mostly empty CTAs
+__global__ void __launch_bounds__(256)
+sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, int64_t ld, const float* __restrict__ scratch,
+                   int64_t scratch_ld, __nv_bfloat16* __restrict__ stage, int64_t stage_ld, const int64_t* __restrict__ table,
+                   int n_layers, const float* __restrict__ lr_dev) {
+  __shared__ float tile[32 * 289];
+  __shared__ int tstart[RS_MAX_SEGS + 1];
+  for (int l = threadIdx.x; l < n_layers; l += blockDim.x) {          // the table is host-written: readable before the wait
+    const RsSeg sg = rs_load(table + (size_t)l * 10, ld, stage_ld);
+    tstart[l + 1] = rs_tiles(sg);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    tstart[0] = 0;
+    for (int l = 0; l < n_layers; ++l) tstart[l + 1] += tstart[l];
+  }
+  __syncthreads();
+  const int total = tstart[n_layers];
+  pdl_wait();
+  pdl_trigger();
+  const int c = blockIdx.y;
+  const float lr = lr_dev[c];
+  float* row = arena + (size_t)c * ld;
+  const float* grow = grads + (size_t)c * ld;
+  const float* srow = scratch ? scratch + (size_t)c * scratch_ld : nullptr;
+  __nv_bfloat16* out = stage ? stage + (size_t)c * stage_ld : nullptr;
+  for (int gt = blockIdx.x; gt < total; gt += gridDim.x) {
+    int lo = 0, hi = n_layers - 1;                                      // last segment with tstart <= gt
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tstart[mid] <= gt) lo = mid; else hi = mid - 1;
+    }
+    const RsSeg sg = rs_load(table + (size_t)lo * 10, ld, stage_ld);
+    const int tl = gt - tstart[lo];
+    const int64_t src = sg.src, dst = sg.dst, dstT = sg.dstT, goff = sg.goff;
+    const int cout = sg.cout, cin = sg.cin, cinp = sg.cinp, n = sg.n;
+    if (sg.path == 0) {
+      float4* w4 = reinterpret_cast<float4*>(row + src);
+      const float4* g4 = reinterpret_cast<const float4*>(grow + src);
+      uint4* d4 = dst >= 0 ? reinterpret_cast<uint4*>(out + dst) : nullptr;
+      const int v0 = tl * (RS_VEC_TILE / 8), v1 = min(n >> 3, v0 + RS_VEC_TILE / 8);
+      for (int v = v0 + threadIdx.x; v < v1; v += 256) {
+        float4 a = w4[2 * v], b = w4[2 * v + 1];
+        const float4 ga = __ldg(g4 + 2 * v), gb = __ldg(g4 + 2 * v + 1);
+        a.x -= lr * ga.x; a.y -= lr * ga.y; a.z -= lr * ga.z; a.w -= lr * ga.w;
+        b.x -= lr * gb.x; b.y -= lr * gb.y; b.z -= lr * gb.z; b.w -= lr * gb.w;
+        if (lr != 0.f) { w4[2 * v] = a; w4[2 * v + 1] = b; }
+        if (d4) {
+          uint4 o;
+          __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&o);
+          h2[0] = __floats2bfloat162_rn(a.x, a.y);
+          h2[1] = __floats2bfloat162_rn(a.z, a.w);
+          h2[2] = __floats2bfloat162_rn(b.x, b.y);
+          h2[3] = __floats2bfloat162_rn(b.z, b.w);
+          d4[v] = o;
+        }
+      }
+    } else if (sg.path == 1) {
+      constexpr int KK = 9, RUN = 32 * KK;
+      const int n_ib = (cinp + 31) / 32;
+      const int co0 = (tl / n_ib) * 32, ci0 = (tl % n_ib) * 32;
+      const int lane = threadIdx.x & 31;
+      __syncthreads();
+#pragma unroll 12
+      for (int i = threadIdx.x; i < 32 * RUN; i += 256) {                   // w tile, parameter layout runs
+        const int co = i / RUN, r = i - co * RUN;
+        const int ci = r / KK;
+        float v = 0.f;
+        if (co0 + co < cout && ci0 + ci < cin) v = row[src + ((size_t)(co0 + co) * cin + ci0) * KK + r];
+        tile[co * 289 + r] = v;
+      }
+      __syncthreads();
+#pragma unroll 12
+      for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {                 // GEMM-layout pass: gradient, update, Wm
+        const int co = q / KK, tap = q - co * KK;
+        if (co0 + co < cout && ci0 + lane < cinp) {
+          const size_t gi = ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + lane;
+          float w = tile[co * 289 + lane * 9 + tap];
+          if (ci0 + lane < cin) {
+            w -= lr * __ldg(srow + goff + gi);
+            tile[co * 289 + lane * 9 + tap] = w;
+          }
+          out[dst + gi] = __float2bfloat16_rn(w);
+        }
+      }
+      __syncthreads();
+      if (dstT >= 0) {
+#pragma unroll 12
+        for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {               // WmT: a warp writes 32 output channels
+          const int tap = q >> 5, ci = q & 31;
+          if (co0 + lane < cout && ci0 + ci < cinp)
+            out[dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane] = __float2bfloat16_rn(tile[lane * 289 + ci * 9 + tap]);
+        }
+      }
+      if (lr != 0.f) {
+#pragma unroll 12
+        for (int i = threadIdx.x; i < 32 * RUN; i += 256) {                 // updated weights back, parameter layout runs
+          const int co = i / RUN, r = i - co * RUN;
+          const int ci = r / KK;
+          if (co0 + co < cout && ci0 + ci < cin) row[src + ((size_t)(co0 + co) * cin + ci0) * KK + r] = tile[co * 289 + r];
+        }
+      }
+    } else {
+      // element-wise form (tiny or odd-sized segments, channel-padded 1x1, k x k without scratch gradients)
+      const int kk = sg.k * sg.k, kdim = kk * cinp;
+      const int e0 = tl * RS_GEN_TILE, e1 = min(n, e0 + RS_GEN_TILE);
+      for (int e = e0 + threadIdx.x; e < e1; e += 256) {
+        const int co = e / kdim, r = e - co * kdim;
+        const int tap = r / cinp, ci = r - tap * cinp;
+        float w = 0.f;
+        if (ci < cin) {
+          const size_t wi = src + ((size_t)co * cin + ci) * kk + tap;
+          w = row[wi] - lr * (sg.gkind ? srow[goff + e] : grow[wi]);
+          if (lr != 0.f) row[wi] = w;
+        }
+        if (dst >= 0) {
+          const __nv_bfloat16 h = __float2bfloat16_rn(w);
+          out[dst + e] = h;
+          if (dstT >= 0) out[dstT + (size_t)r * cout + co] = h;
+        }
+      }
+    }
+  }
+}
+extern "C" int fb_sgd_restage(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                              void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                              const float* lr_dev, fb_stream_t stream) {
+  FB_REQUIRE(arena && grads && table_dev && lr_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_sgd_restage: bad arguments");
+  FB_REQUIRE(n_layers <= RS_MAX_SEGS, "fb_sgd_restage: at most %d segments", RS_MAX_SEGS);
+  // CTAs per client: enough to put ~16 CTAs on every SM overall, at least one per ~8K elements, at most 256
+  int gx = (16 * fb_num_sms() + C - 1) / C;
+  const int by_work = total_elems / 8192 + 1;
+  if (gx > by_work) gx = by_work;
+  if (gx > 256) gx = 256;
+  if (gx < 1) gx = 1;
+  FB_CHECK_CUDA(fb_launch_pdl(sgd_restage_kernel, dim3(gx, C), dim3(256), (size_t)0, (cudaStream_t)stream, arena, grads, ld, scratch,
+                              scratch_ld, (__nv_bfloat16*)stage, stage_ld, table_dev, n_layers, lr_dev));
+  return FB_OK;
+}
+
 // ---------------------------------------------------------------- weight-gradient un-staging (one launch per step)
 // The k x k weight-gradient GEMMs produce dW in the GEMM layout fp32 [cout][(kh,kw,cin_pad)] (scratch rows); the
 // gradient arena wants the parameter layout [cout][cin][kh][kw].  Table (int64 x 8 per layer): src_off (scratch),

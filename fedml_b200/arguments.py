@@ -128,6 +128,7 @@ SCHEMA: Dict[str, tuple] = {
     "compute_dtype": (str, "bf16"),
     "use_multicast": (bool, True),
     "use_cuda_graphs": (bool, True),
+    "fused_sgd_restage": (bool, True),      # plain SGD: optimizer step fused with re-staging the bf16 operands
     "client_groups": (int, 0),              # 0 = auto: clients of a GPU advance in this many concurrent stream groups
     "sparse_embedding_sgd": (bool, True),   # plain SGD: update only the word-embedding rows of tokens that occur
     "dp_clip": (float, 0.0),

@@ -750,8 +750,61 @@ class BatchedResNet(BatchedModel):
                 views[name] = wm if name == "fc" else (wm, wt)
             st = self._stage = {"key": key, "stage": stage, "table": table, "views": views, "n": len(rows),
                                 "max_n": max(r[7] for r in rows)}
-        self.be.ops.stage_conv_weights(arena, st["stage"], st["table"], st["n"], st["max_n"])
+        if not (getattr(self, "_stage_fresh", False) and st.get("fresh_key") == key):
+            self.be.ops.stage_conv_weights(arena, st["stage"], st["table"], st["n"], st["max_n"])
         return st["views"]
+
+    # ---- fused optimizer step + re-staging (plain SGD): see fb_sgd_restage ---------------------------------------
+    supports_fused_sgd = True
+    fused_lr = None
+
+    def set_fused_sgd(self, lr_dev):
+        """``lr_dev`` [C] (device; 0 freezes a client): the training step ends with ONE launch that applies
+        w -= lr * g to every trainable segment and refreshes the bf16 GEMM operands, so the next step needs no staging
+        pass and the k x k weight gradients need no un-staging pass.  None restores the separate optimizer step."""
+        self.fused_lr = lr_dev
+
+    def restage(self, W):
+        """Stage the current weights now (round start, after the global model was written into the arena) and mark
+        the staged copy as current; it stays current while only the fused step modifies the weights."""
+        self._stage_fresh = False
+        if isinstance(self.be, NativeBackend) and self.be.dtype == torch.bfloat16 and getattr(W, "arena", None) is not None:
+            self._prepare_staged(W)
+            self._stage["fresh_key"] = self._stage["key"]
+            self._stage_fresh = True
+
+    def invalidate_stage(self):
+        self._stage_fresh = False
+
+    def _fused_plan(self, W, G):
+        """Segment table of the fused step: staged conv / fc weights (gradients in the arena or, for k x k, in the
+        GEMM-layout scratch) plus every other trainable segment as a plain row."""
+        st = getattr(self, "_stage", None)
+        big = getattr(self, "_dw_big", None)
+        if st is None or G.arena is None:
+            return None
+        key = (st["key"], None if big is None else big.data_ptr())
+        fp = getattr(self, "_fused", None)
+        if fp is not None and fp["key"] == key:
+            return fp
+        layout = W.layout
+        srow = {r[5]: r for r in getattr(self, "_unstage_rows", [])}      # arena offset -> un-staging row
+        rows, staged_offsets = [], set()
+        for r in st["table"].cpu().tolist():
+            w_off, cout, cin, cinp, k, dst, dstT, n = r
+            staged_offsets.add(w_off)
+            if w_off in srow:
+                rows.append([w_off, cout, cin, cinp, k, dst, dstT, n, srow[w_off][0], 1])
+            elif k == 1 and cin == cinp:
+                rows.append([w_off, cout, cin, cinp, k, dst, dstT, n, 0, 0])
+            else:
+                return None                                               # gradient layout not covered: keep the split path
+        for sg in layout.segments:
+            if sg.kind == "param" and sg.offset not in staged_offsets:
+                rows.append([sg.offset, sg.numel, 1, 1, 1, -1, -1, sg.numel, 0, 0])
+        fp = self._fused = {"key": key, "table": torch.tensor(rows, dtype=torch.int64).to(W.arena.device), "n": len(rows),
+                            "max_n": min(sum(r[7] for r in rows), 2 ** 31 - 1)}
+        return fp
 
     def _input(self, x):
         if x.dtype == torch.uint8:
@@ -803,6 +856,7 @@ class BatchedResNet(BatchedModel):
                 c._defer_scatter = c.k * c.k <= 9
                 off += n
             self._unstage = None
+            self._unstage_rows = rows
             if rows and all(c._defer_scatter for c in need):
                 self._unstage = (torch.tensor(rows, dtype=torch.int64).to(arena.device), len(rows),
                                  max(((r[1] + 31) // 32) * ((r[2] + 31) // 32) for r in rows))
@@ -841,8 +895,18 @@ class BatchedResNet(BatchedModel):
         x0, a, hstem, m, r = tape[0]
         da, _ = self.stem_bn.bwd(be, d, a, hstem, W, G, m, r, relu=True, want_dres=False)
         self.stem_conv.bwd(be, da, x0, Wm["conv1"], G["conv1.weight"])
-        self._scatter_grads(G)
-        be.join()
+        fp = self._fused_plan(W, G) if (self.fused_lr is not None and getattr(self, "_unstage", None) is not None) else None
+        if fp is not None:
+            be.join()                                                 # weight gradients complete
+            be.ops.sgd_restage(W.arena, G.arena, self._dw_big, self._stage["stage"], fp["table"], fp["n"], fp["max_n"],
+                               self.fused_lr)
+            self._stage["fresh_key"] = self._stage["key"]
+            self._stage_fresh = True
+            self.fused_applied = True
+        else:
+            self._scatter_grads(G)
+            be.join()
+            self.fused_applied = False
         return loss
 
     def logits(self, x, W):

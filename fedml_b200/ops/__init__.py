@@ -495,6 +495,16 @@ def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Te
     count_launch()
 
 
+def sgd_restage(arena: torch.Tensor, grads: torch.Tensor, scratch: Optional[torch.Tensor], stage: Optional[torch.Tensor],
+                table: torch.Tensor, n_layers: int, max_n: int, lr: torch.Tensor):
+    """Plain-SGD step on every listed segment fused with re-staging the bf16 GEMM operands (csrc/train.cu)."""
+    check(lib().fb_sgd_restage(vp(ptr(arena)), vp(ptr(grads)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(scratch)),
+                               i64(scratch.stride(0) if scratch is not None else 0), vp(ptr(stage)),
+                               i64(stage.stride(0) if stage is not None else 0), vp(ptr(table)), i32(n_layers), i32(max_n),
+                               vp(ptr(lr)), vp(stream_ptr(arena.device))), "sgd_restage")
+    count_launch()
+
+
 def unstage_conv_grads(scratch: torch.Tensor, grads: torch.Tensor, table: torch.Tensor, n_layers: int, max_tiles: int):
     """GEMM-layout weight gradients (rows of ``scratch`` fp32 [C, *]) -> parameter layout inside the gradient arena."""
     check(lib().fb_unstage_conv_grads(vp(ptr(scratch)), i64(scratch.stride(0)), vp(ptr(grads)), i64(grads.stride(0)),

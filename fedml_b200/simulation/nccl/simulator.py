@@ -429,9 +429,24 @@ class NCCLSimulator:
             return
         if sparse:
             self.batched.set_sparse_sgd(st["lr"])
+        fused = self._fused_sgd()
+        if fused:
+            self.batched.set_fused_sgd(st["lr"])
         loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
-        self._sgd(self.C_max, st["lr"], False)
+        if not (fused and getattr(self.batched, "fused_applied", False)):
+            self._sgd(self.C_max, st["lr"], False)
         st["loss"].copy_(loss)
+
+    def _fused_sgd(self):
+        """Plain SGD on the native back-end: the executor applies the optimizer step itself, fused with re-staging the
+        next step's bf16 operands (``fb_sgd_restage``)."""
+        if not hasattr(self, "_fused_ok"):
+            plain = not (self.momentum or self.wd or self.mu)
+            self._fused_ok = bool(self.cuda and plain and getattr(self.batched, "supports_fused_sgd", False)
+                                  and isinstance(getattr(self.batched, "be", None), NativeBackend)
+                                  and bool(getattr(self.args, "fused_sgd_restage", True))
+                                  and os.environ.get("FB_FUSED_SGD", "1") != "0")
+        return self._fused_ok
 
     def _train_batched(self, staged, n_local):
         Xd, Yd, steps_dev, inv_valid, S, ev = staged
@@ -449,6 +464,8 @@ class NCCLSimulator:
             self.graph = None
         st = self._static
         first = True
+        if self._fused_sgd():
+            self.batched.restage(self.W)                     # the arena holds the fresh global model: stage it once
         for _ in range(epochs):
             for s in range(S):
                 act = (steps_dev > s).to(torch.float32)
@@ -466,6 +483,8 @@ class NCCLSimulator:
                 else:
                     self._step_body(st)
                 first = False
+        if self._fused_sgd():
+            self.batched.invalidate_stage()                  # aggregation rewrites the arena behind the executor's back
         return st["loss"]
 
     def _capture(self, st):
@@ -479,6 +498,8 @@ class NCCLSimulator:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.stack.copy_(backup)          # warm-up steps must not advance the models
+        if self._fused_sgd():
+            self.batched.restage(self.W)
         self.graph = torch.cuda.CUDAGraph()
         before = _native.LAUNCHES[0]
         with torch.cuda.graph(self.graph):
@@ -486,6 +507,8 @@ class NCCLSimulator:
         self._graph_launches = _native.LAUNCHES[0] - before
         _native.LAUNCHES[0] = before
         self.stack.copy_(backup)          # capture does not execute, but keep the invariant explicit
+        if self._fused_sgd():
+            self.batched.restage(self.W)
 
     def _train_sequential(self, my_clients, round_idx):
         """Per-client eager training on arena-bound parameters (custom trainers / unbatched families)."""

@@ -232,6 +232,15 @@ int fb_softmax_xent(const float* logits, const int64_t* labels, int64_t R, int32
  * cast/permute kernels per layer per step. */
 int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage_bf16, int64_t stage_ld,
                           const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream);
+/* Plain-SGD optimizer step fused with the re-staging of the next step's GEMM operands: for every listed segment of every
+ * client  w -= lr[c] * g, then the updated weights are written back AND cast / re-laid-out into the bf16 staging stack in
+ * the same pass; k x k weight gradients are read in the GEMM layout from the scratch stack of the weight-gradient
+ * kernels (no un-staging pass).  table_dev: int64 [n_layers][10] = {w_off, cout, cin, cin_pad, k, dst | -1, dstT | -1,
+ * n, g_off, g_kind (0 arena / 1 scratch)}.  Replaces torch.optim.SGD.step() of every client
+ * (my_model_trainer_classification.py:26-37) plus this library's own staging and un-staging launches. */
+int fb_sgd_restage(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                   void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                   const float* lr_dev, fb_stream_t stream);
 /* The inverse direction for k x k weight gradients: GEMM-layout fp32 [cout][(kh,kw,cin_pad)] rows of a scratch stack
  * -> parameter layout [cout][cin][kh][kw] inside the gradient arena, all listed layers of all clients in one launch.
  * table_dev: int64 [n_layers][8] = {src_off, cout, cin, cin_pad, k, dst_off, 0, 0}; max_tiles = largest

@@ -573,3 +573,43 @@ def test_implicit_conv3x3_wgrad(C, B, H, cin, cout, stride):
         ref = w.grad.permute(0, 2, 3, 1).reshape(cout, 9 * cin)
         torch.testing.assert_close(dw[c], ref, rtol=2e-2, atol=2e-2 * float(ref.abs().max()))
     assert float(arena[:, :32].abs().sum()) == 0 and float(arena[:, 32 + cout * 9 * cin:].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("block", ["bottleneck", "basic"])
+def test_fused_sgd_restage_matches_separate_optimizer_step(block):
+    """train_step ending in fb_sgd_restage (optimizer + bf16 re-staging in one launch, k x k gradients read from the
+    GEMM-layout scratch) == train_step + un-staging + fused SGD kernel + staging, over three steps."""
+    from fedml_b200 import ops
+    from fedml_b200.models.batched import NativeBackend, make_batched
+    from fedml_b200.models.cv import BasicBlock, Bottleneck, ResNet
+    from fedml_b200.parallel.arena import ArenaLayout
+    torch.manual_seed(0)
+    C, B = 3, 8
+    blk = Bottleneck if block == "bottleneck" else BasicBlock
+    model = ResNet(blk, [1, 1, 1], num_classes=10)
+    layout = ArenaLayout(model)
+    base = torch.stack([layout.flatten(model.state_dict()) for _ in range(C)]).to(DEV)
+    base += 0.01 * torch.randn_like(base)
+    x = torch.randint(0, 256, (C, B, 32, 32, 3), dtype=torch.uint8, device=DEV)
+    y = torch.randint(0, 10, (C, B), device=DEV)
+    active = torch.ones(C, device=DEV)
+    lr = torch.tensor([0.05, 0.0, 0.02], device=DEV)          # client 1 frozen
+    results = []
+    for fused in (False, True):
+        st, gst = base.clone(), torch.zeros_like(base)
+        W, G = layout.stacked_views(st), layout.stacked_views(gst)
+        ex = make_batched(model, NativeBackend(torch.bfloat16))
+        if fused:
+            ex.set_fused_sgd(lr)
+            ex.restage(W)
+        for _ in range(3):
+            ex.train_step(x, y, W, G, active)
+            if fused:
+                assert ex.fused_applied
+            else:
+                ops.sgd_step_stacked(st, gst, layout.P_train, lr)
+        results.append(st.clone())
+    a, b = results
+    assert torch.equal(a[1, :layout.P_train], base[1, :layout.P_train]) and torch.equal(b[1, :layout.P_train], base[1, :layout.P_train])
+    torch.testing.assert_close(b, a, rtol=1e-4, atol=1e-5)
+    assert not torch.equal(a[0], base[0])
