@@ -109,6 +109,57 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
       : "r"(taddr)
       : "memory");
 }
+// ---- CTA-pair (cta_group::2) forms: two CTAs of a cluster share one 256-row MMA tile
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose completion is signalled on the LEADER CTA's mbarrier (cluster address), data lands in this CTA
+__device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* map, void* smem_dst, uint32_t leader_bar, int c0, int c1,
+                                                 int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// arrive on the barrier at this smem offset in BOTH CTAs of the pair once the MMAs issued so far have completed
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  const uint16_t mask = 3;
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version field = 1
@@ -125,7 +176,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   return d;
 }
 // instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128, N = bn; majors: 0 = K, 1 = MN
-__device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn) {
+__device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn, int m = GEMM_BM) {
   uint32_t d = 0;
   d |= 1u << 4;                       // c_format = F32
   d |= 1u << 7;                       // a_format = BF16
@@ -133,7 +184,7 @@ __device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn) {
   d |= (uint32_t)(a_mn & 1) << 15;
   d |= (uint32_t)(b_mn & 1) << 16;
   d |= (uint32_t)(bn >> 3) << 17;     // N / 8
-  d |= (uint32_t)(GEMM_BM >> 4) << 24;  // M / 16
+  d |= (uint32_t)(m >> 4) << 24;        // M / 16
   return d;
 }
 
@@ -165,15 +216,21 @@ struct GemmArgs {
 };
 
 // MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory); MODE 4: implicit 3x3 conv
-template <int MODE>
+// PAIR: the kernel runs as clusters of two CTAs (one TPC) that share 256 x BN tiles through tcgen05 cta_group::2: each CTA
+// stages its 128 rows of A and its half of B, the leader CTA issues M = 256 MMAs that read both CTAs' shared memory, each
+// CTA drains its own 128 accumulator rows.  Per output tile the pair moves half the B bytes from L2 that two
+// independent CTAs would.
+template <int MODE, bool PAIR = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128B swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const uint32_t b_bytes = (uint32_t)a.BNpad * 128u;
+  const uint32_t b_bytes = (uint32_t)(PAIR ? a.BNpad / 2 : a.BNpad) * 128u;   // a pair CTA stages half of B
   const uint32_t stage_bytes = GEMM_A_BYTES + b_bytes;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  constexpr int TILE_M = PAIR ? 2 * GEMM_BM : GEMM_BM;
   const int STAGES = a.stages;
   uint8_t* staging = smem + (size_t)STAGES * stage_bytes;            // 1024-aligned: stage_bytes is a multiple of 2048
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + GEMM_STAGING_BYTES);
@@ -197,11 +254,15 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tmem_full + i, 1);
-      mbar_init(tmem_empty + i, 4);   // one arrive per epilogue warp
+      mbar_init(tmem_empty + i, PAIR ? 8 : 4);   // one arrive per epilogue warp (of both CTAs of a pair)
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, (uint32_t)a.tmem_cols);
+  if (PAIR) cluster_sync_all();        // the peer's barriers exist before anything is signalled across CTAs
+  if (warp == 1) {
+    if (PAIR) tmem_alloc_pair(tmem_slot, (uint32_t)a.tmem_cols);
+    else tmem_alloc(tmem_slot, (uint32_t)a.tmem_cols);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -216,7 +277,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
         const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
         if (CONV) {
           // 128 consecutive output pixels of group g: image n0 (a tile spans 128 / (Ho*Wo) images when the plane is
@@ -268,6 +329,26 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
             continue;
           }
+          if constexpr (PAIR) {
+            // this CTA's 128 rows of A and its half of B; every byte of both CTAs is counted on the leader's barrier
+            const uint32_t lbar = mapa_u32(smem_u32(full_bar + stage), 0);
+            if (rank == 0) mbar_expect_tx(full_bar + stage, 2 * stage_bytes);
+            const int m0 = mt * TILE_M + (int)rank * GEMM_BM, nh = a.BN / 2, n0 = nt * a.BN + (int)rank * nh;
+            if (!A_MN) {
+              tma_load_4d_pair(&tmA, sa, lbar, kb * GEMM_BK, m0, g0, g1);
+            } else {
+              for (int i = 0; i < GEMM_BM / 64; ++i)
+                tma_load_4d_pair(&tmA, sa + (size_t)i * GEMM_BK * 128, lbar, m0 + i * 64, kb * GEMM_BK, g0, g1);
+            }
+            if (!B_MN) {
+              tma_load_4d_pair(&tmB, sb, lbar, kb * GEMM_BK, n0, g0, g1);
+            } else {
+              for (int i = 0; i < nh / 64; ++i)
+                tma_load_4d_pair(&tmB, sb + (size_t)i * GEMM_BK * 128, lbar, n0 + i * 64, kb * GEMM_BK, g0, g1);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            continue;
+          }
           mbar_expect_tx(full_bar + stage, stage_bytes);
           if (!A_MN) {
             tma_load_4d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g0, g1);
@@ -287,11 +368,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp == 1) {
     // ===================================================== MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN);
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN, TILE_M);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
         mbar_wait(tmem_empty + acc, acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(acc * a.BN);
@@ -315,12 +396,16 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
               bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
             }
-            umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            if constexpr (PAIR) umma_bf16_pair(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            else umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
           }
-          umma_commit(empty_bar + stage);   // smem slot reusable once these MMAs have read it
+          // smem slot reusable once these MMAs have read it (in a pair: the slot of both CTAs)
+          if constexpr (PAIR) umma_commit_pair(empty_bar + stage);
+          else umma_commit(empty_bar + stage);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tmem_full + acc);       // accumulator complete -> epilogue
+        if constexpr (PAIR) umma_commit_pair(tmem_full + acc);   // accumulator complete -> epilogue (of both CTAs)
+        else umma_commit(tmem_full + acc);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -331,11 +416,12 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t acc_phase = 0;
     uint8_t* my_stage = staging + (size_t)q * 2 * 4096;
     int sbuf = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
       const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
       mbar_wait(tmem_full + acc, acc_phase);
       tc_fence_after();
-      const int row = mt * GEMM_BM + q * 32 + lane;
+      const int row0 = mt * TILE_M + (int)rank * GEMM_BM + q * 32;   // first output row of this warp's TMEM lane quarter
+      const int row = row0 + lane;
       const bool row_ok = row < a.M;
       const uint32_t taddr = tmem_base + (uint32_t)(acc * a.BN) + ((uint32_t)(q * 32) << 16);
       const float* bias = a.bias ? a.bias + (size_t)g * a.bias_gs : nullptr;
@@ -398,11 +484,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (lane == 0) {
             if (a.reduce_add) {
               asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-                           ::"l"(&tmD), "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(og0), "r"(og1)
+                           ::"l"(&tmD), "r"(smem_u32(buf)), "r"(col0), "r"(row0), "r"(og0), "r"(og1)
                            : "memory");
             } else {
               asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(&tmD),
-                           "r"(smem_u32(buf)), "r"(col0), "r"(mt * GEMM_BM + q * 32), "r"(og0), "r"(og1)
+                           "r"(smem_u32(buf)), "r"(col0), "r"(row0), "r"(og0), "r"(og1)
                            : "memory");
             }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -440,16 +526,21 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tmem_empty + acc);
+      if (lane == 0) {
+        if constexpr (PAIR) mbar_arrive_cluster(mapa_u32(smem_u32(tmem_empty + acc), 0));   // the leader issues the next MMAs
+        else mbar_arrive(tmem_empty + acc);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (a.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores complete before exit
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();        // neither CTA frees TMEM / exits while the peer may still signal or read it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+    if (PAIR) tmem_dealloc_pair(tmem_base, (uint32_t)a.tmem_cols);
+    else tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
   }
 }
 
@@ -543,6 +634,18 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
     }
     bn = (cost[1] * 108 < cost[0] * 100) ? cand[1] : cand[0];
   }
+  // CTA pairs (cta_group::2, 256 x bn tiles over two SMs): large problems only; n-tiles are multiples of 128 so that each
+  // CTA's half of B is whole 64-column chunks
+  static int pair_env = -1;
+  if (pair_env < 0) {
+    const char* e = getenv("FB_GEMM_PAIR");
+    pair_env = e ? atoi(e) : 1;
+  }
+  const bool pair = pair_env != 0 && p->M >= 512 && p->N >= 128 && p->K >= 128 && group_div == 1;
+  if (pair) {
+    const int nt = (p->N + 255) / 256;
+    bn = ((p->N + nt - 1) / nt + 127) / 128 * 128;
+  }
   a.BN = bn;
   const uint64_t es = p->d_fp32 ? 4 : 2;
   a.gi = gi;
@@ -557,7 +660,7 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   FB_REQUIRE(!a.reduce_add || a.tma_store, "fb_grouped_gemm: accumulate needs a 16-byte aligned output (TMA reduce-store)");
   a.BNpad = b_mn ? (bn + 63) / 64 * 64 : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
-  a.m_tiles = (p->M + GEMM_BM - 1) / GEMM_BM;
+  a.m_tiles = pair ? (p->M + 2 * GEMM_BM - 1) / (2 * GEMM_BM) : (p->M + GEMM_BM - 1) / GEMM_BM;
   a.k_blocks = (p->K + GEMM_BK - 1) / GEMM_BK;
   int cols = 32;
   while (cols < 2 * bn) cols <<= 1;
@@ -574,12 +677,12 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   if (rc) return rc;
   if (!b_mn)
     rc = make_map(&tmB, p->b, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
-                  (uint64_t)p->b_gs2, (uint32_t)a.BN);
+                  (uint64_t)p->b_gs2, (uint32_t)(pair ? a.BN / 2 : a.BN));
   else
     rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
                   (uint64_t)p->b_gs2, GEMM_BK);
   if (rc) return rc;
-  const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
+  const size_t stage_bytes = GEMM_A_BYTES + (size_t)(pair ? a.BNpad / 2 : a.BNpad) * 128;
   const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/;
   // two co-resident CTAs per SM hide each other's per-tile latencies (TMEM allows it while 2 x tmem_cols <= 512)
   static int force_ctas = -1;
@@ -589,6 +692,7 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   }
   int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
   if (force_ctas == 1 || force_ctas == 2) ctas_per_sm = (force_ctas == 2 && a.tmem_cols <= 256) ? 2 : 1;
+  if (pair) ctas_per_sm = 1;
   int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
   if (stages < 3 && ctas_per_sm == 2) {
     ctas_per_sm = 1;
@@ -607,6 +711,21 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   }
   const int total = a.G * a.m_tiles * a.n_tiles;
   int grid = fb_num_sms() * ctas_per_sm;
+  if (pair) {
+    grid &= ~1;
+    if (grid > 2 * total) grid = 2 * total;
+#define FB_LAUNCH_PAIR(MODE_)                                                                                             \
+  do {                                                                                                                      \
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<MODE_, true>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,    \
+                                        (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));                                      \
+  } while (0)
+    if (mode == 3) FB_LAUNCH_PAIR(3);
+    else if (mode == 2) FB_LAUNCH_PAIR(2);
+    else FB_LAUNCH_PAIR(0);
+#undef FB_LAUNCH_PAIR
+    return FB_OK;
+  }
   if (grid > total) grid = total;
   if (mode == 3) {
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

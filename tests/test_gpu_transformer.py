@@ -223,3 +223,25 @@ def test_native_batched_distilbert_step(dropout):
         rel = (gn - gt).norm(dim=1) / gt.norm(dim=1)
         assert float(rel.max()) < 0.2, rel
     torch.testing.assert_close(outs["native"][3], outs["torch"][3], rtol=5e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("mode,G,M,N,K", [("nt", 3, 1024, 768, 320), ("nt", 2, 640, 384, 200), ("nn", 2, 1000, 256, 136),
+                                          ("tn", 2, 512, 3072, 328), ("nt", 1, 2048, 130 * 8, 512)])
+def test_mm_cta_pair_tiles(mode, G, M, N, K):
+    """Shapes large enough for the cta_group::2 path (256 x bn tiles shared by two CTAs of a cluster), incl. ragged edges."""
+    from fedml_b200.ops import transformer as tf
+    torch.manual_seed(0)
+    if mode == "nt":
+        a, b = _bf(G, M, K), _bf(G, N, K)
+        ref = a.float() @ b.float().transpose(1, 2)
+    elif mode == "nn":
+        a, b = _bf(G, M, K), _bf(G, K, N)
+        ref = a.float() @ b.float()
+    else:
+        a, b = _bf(G, K, M), _bf(G, K, N)
+        ref = a.float().transpose(1, 2) @ b.float()
+    bias = torch.randn(G, N, device=DEV)
+    out = tf.mm(mode, a, b, out_dtype=torch.float32, bias=bias)
+    torch.testing.assert_close(out, ref + bias[:, None, :], rtol=1e-3, atol=5e-2)
+    out16 = tf.mm(mode, a, b, relu=True)
+    torch.testing.assert_close(out16.float(), torch.relu(ref), rtol=2e-2, atol=2e-1)
