@@ -245,3 +245,43 @@ def test_mm_cta_pair_tiles(mode, G, M, N, K):
     torch.testing.assert_close(out, ref + bias[:, None, :], rtol=1e-3, atol=5e-2)
     out16 = tf.mm(mode, a, b, relu=True)
     torch.testing.assert_close(out16.float(), torch.relu(ref), rtol=2e-2, atol=2e-1)
+
+
+def test_distilbert_fused_sgd_restage_matches_separate_step():
+    """DistilBERT executor: optimizer step + bf16 re-staging in one launch (plus the sparse embedding update) == the
+    separate fused-SGD kernel over the dense gradient arena, over two steps."""
+    from fedml_b200 import ops
+    from fedml_b200.models.batched import NativeBackend, make_batched
+    from fedml_b200.models.nlp import DistilBertForSequenceClassification
+    from fedml_b200.parallel.arena import ArenaLayout
+    torch.manual_seed(0)
+    C, B, S = 3, 4, 32
+    model = DistilBertForSequenceClassification(num_labels=20, seq_classif_dropout=0.0, vocab_size=512, dim=128, n_layers=2,
+                                                n_heads=4, hidden_dim=256, max_pos=64, dropout=0.0, attention_dropout=0.0)
+    layout = ArenaLayout(model)
+    base = torch.stack([layout.flatten(model.state_dict()) for _ in range(C)]).to(DEV)
+    base += 0.02 * torch.randn_like(base)
+    ids = torch.randint(1, 512, (C, B, S), device=DEV)
+    y = torch.randint(0, 20, (C, B), device=DEV)
+    active = torch.ones(C, device=DEV)
+    lr = torch.tensor([0.05, 0.0, 0.02], device=DEV)
+    results = []
+    for fused in (False, True):
+        st, gst = base.clone(), torch.zeros_like(base)
+        W, G = layout.stacked_views(st), layout.stacked_views(gst)
+        ex = make_batched(model, NativeBackend(torch.bfloat16))
+        if fused:
+            ex.set_sparse_sgd(lr)
+            ex.set_fused_sgd(lr)
+            ex.restage(W)
+        for _ in range(2):
+            ex.train_step(ids, y, W, G, active)
+            if fused:
+                assert ex.fused_applied
+            else:
+                ops.sgd_step_stacked(st, gst, layout.P_train, lr)
+        results.append(st.clone())
+    a, b = results
+    assert torch.equal(b[1], base[1])
+    torch.testing.assert_close(b, a, rtol=1e-3, atol=2e-5)
+    assert not torch.equal(a[0], base[0])
