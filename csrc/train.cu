@@ -290,9 +290,45 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
       __shared__ float tile[32 * 289];   // [cout 32][cin 32][tap 9] + 1 pad per row: every access pattern below is conflict-free
       constexpr int KK = 9, RUN = 32 * KK;
       const int n_cb = (cout + 31) / 32, n_ib = (cinp + 31) / 32;
+      const bool full = cin == cinp && (cin & 31) == 0 && (cout & 31) == 0 && (src & 3) == 0 && (dst & 3) == 0 &&
+                        (dstT < 0 || (dstT & 3) == 0) && (ld & 3) == 0 && (stage_ld & 3) == 0;
       for (int t = blockIdx.x; t < n_cb * n_ib; t += gridDim.x) {
         const int co0 = (t / n_ib) * 32, ci0 = (t % n_ib) * 32;
         __syncthreads();
+        if (full) {                                                    // vectorised whole tile, as in sgd_restage_kernel
+          const float* wbase = row + src + ((size_t)co0 * cin + ci0) * KK;
+#pragma unroll 3
+          for (int i = threadIdx.x; i < 32 * (RUN / 4); i += 256) {
+            const int co = i / (RUN / 4), v4 = i - co * (RUN / 4);
+            const float4 v = __ldg(reinterpret_cast<const float4*>(wbase + (size_t)co * cin * KK + v4 * 4));
+            float* tt = tile + co * 289 + v4 * 4;
+            tt[0] = v.x; tt[1] = v.y; tt[2] = v.z; tt[3] = v.w;
+          }
+          __syncthreads();
+#pragma unroll 3
+          for (int i = threadIdx.x; i < 32 * KK * 8; i += 256) {
+            const int ci4 = i & 7, q = i >> 3;
+            const int co = q / KK, tap = q - co * KK;
+            const float* tt = tile + co * 289 + ci4 * 36 + tap;
+            uint2 o;
+            *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(tt[0], tt[9]);
+            *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(tt[18], tt[27]);
+            *reinterpret_cast<uint2*>(out + dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + ci4 * 4) = o;
+          }
+          if (dstT >= 0) {
+#pragma unroll 3
+            for (int i = threadIdx.x; i < KK * 32 * 8; i += 256) {
+              const int co4 = i & 7, q = i >> 3;
+              const int ci = q & 31, tap = q >> 5;
+              const float* tt = tile + co4 * 4 * 289 + ci * 9 + tap;
+              uint2 o;
+              *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(tt[0], tt[289]);
+              *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(tt[578], tt[867]);
+              *reinterpret_cast<uint2*>(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + co4 * 4) = o;
+            }
+          }
+          continue;
+        }
 #pragma unroll 12
         for (int i = threadIdx.x; i < 32 * RUN; i += 256) {            // 36 independent loads per thread: keep them in flight
           const int co = i / RUN, r = i - co * RUN;
