@@ -6,6 +6,7 @@
 // (radix-2, MSB first) selection for the wanted order statistics: 32 passes of K/4 compares per
 // lane + 2 shuffles.  No sort, no global scratch, every HBM/NVLink byte is read exactly once.
 #include "common.cuh"
+#include <stdlib.h>
 #include "../include/fedml_b200.h"
 
 #define SEL_THREADS 256
@@ -103,6 +104,66 @@ __global__ void __launch_bounds__(SEL_THREADS) robust_select_kernel(const float*
   }
 }
 
+// Register sorting network: for up to 128 clients every thread owns one coordinate, holds the K values in registers
+// (padded with +inf to a power of two) and runs a fully unrolled bitonic network of min / max pairs: K log^2 K / 4
+// compare-exchanges instead of 32 counting passes over shared memory (7.8 -> ~1 ms for 64 x 11.2 M).
+#define SORT_THREADS 128
+template <int KP>
+__global__ void __launch_bounds__(SORT_THREADS) robust_sort_kernel(const float* const* __restrict__ rows, int K, int64_t j0,
+                                                                   int64_t j1, int mode, int trim,
+                                                                   float* const* __restrict__ outs, int n_out) {
+  for (int64_t j = j0 + (int64_t)blockIdx.x * SORT_THREADS + threadIdx.x; j < j1; j += (int64_t)gridDim.x * SORT_THREADS) {
+    float v[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+      v[k] = INFINITY;
+      if (k < K) {
+        const float* src = rows[k] + j;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v[k]) : "l"(src) : "memory");
+      }
+    }
+#pragma unroll
+    for (int size = 2; size <= KP; size <<= 1) {
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+        for (int i = 0; i < KP; ++i) {
+          const int l = i ^ stride;
+          if (l > i) {
+            const float lo = fminf(v[i], v[l]), hi = fmaxf(v[i], v[l]);
+            const bool up = (i & size) == 0;
+            v[i] = up ? lo : hi;
+            v[l] = up ? hi : lo;
+          }
+        }
+      }
+    }
+    float result = 0.f;
+    if (mode == 0) {
+      const int idx = (K - 1) / 2;                       // lower median, as torch.median
+#pragma unroll
+      for (int k = 0; k < KP; ++k)
+        if (k == idx) result = v[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < KP; ++k)
+        if (k >= trim && k < K - trim) result += v[k];
+      result /= (float)(K - 2 * trim);
+    }
+    for (int o = 0; o < n_out; ++o) outs[o][j] = result;
+  }
+}
+template <int KP>
+static int launch_robust_sort(const float* const* rows_dev, int K, int64_t j0, int64_t j1, int mode, int trim,
+                              float* const* outs_dev, int n_out, cudaStream_t stream) {
+  const int64_t nt = (j1 - j0 + SORT_THREADS - 1) / SORT_THREADS;
+  int64_t grid = (int64_t)fb_num_sms() * 8;
+  if (grid > nt) grid = nt;
+  robust_sort_kernel<KP><<<(int)grid, SORT_THREADS, 0, stream>>>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
 extern "C" int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t j0, int64_t j1, int32_t mode,
                                 int32_t trim, float* const* outs_dev, int32_t n_out, fb_stream_t stream) {
   FB_REQUIRE(rows_dev && outs_dev && K >= 1 && j1 >= j0 && n_out >= 1, "fb_robust_select: bad arguments");
@@ -114,6 +175,19 @@ extern "C" int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t
     return FB_ERR_LIMIT;
   }
   if (j1 == j0) return FB_OK;
+  static int use_sort = -1;
+  if (use_sort < 0) {
+    const char* e = getenv("FB_ROBUST_SORT");
+    use_sort = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  if (use_sort && K <= 128) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (K <= 8) return launch_robust_sort<8>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out, st);
+    if (K <= 16) return launch_robust_sort<16>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out, st);
+    if (K <= 32) return launch_robust_sort<32>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out, st);
+    if (K <= 64) return launch_robust_sort<64>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out, st);
+    return launch_robust_sort<128>(rows_dev, K, j0, j1, mode, trim, outs_dev, n_out, st);
+  }
   FB_CHECK_CUDA(cudaFuncSetAttribute(robust_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 1;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, robust_select_kernel, SEL_THREADS, smem);
