@@ -167,10 +167,26 @@ bn_apply_body(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
   }
 }
 
+static int bn_forced_slices(int bwd) {
+  static int f[2] = {-1, -1};
+  if (f[bwd] < 0) {
+    const char* e = getenv(bwd ? "FB_BN_S_BWD" : "FB_BN_S_FWD");
+    f[bwd] = e ? atoi(e) : 0;
+  }
+  return f[bwd];
+}
 static int bn_slices(int C, int64_t M, int ch) {
-  // ~6 CTAs per SM in flight (these kernels are pure streaming: occupancy = bytes in flight), but at least
-  // four sweeps of 2048 elements per CTA so the per-CTA prologue stays amortised
-  int64_t want = (6 * (int64_t)fb_num_sms() + C - 1) / C;
+  // slices per client; at least four sweeps of 2048 elements per CTA so the per-CTA prologue stays amortised.
+  // total CTAs ~ 3.4 per SM: measured on the 100-client bench (ms / round by slices per client, forward x backward):
+  // 5x5 69.0, 5x8 69.7, 8x5 69.8, 8x8 70.6, 9x9 73.7, 11x8 72.2, 18x18 77.8 - more slices pay the S x ch partial-sum
+  // prologue in every CTA, and 6 or 9 slices x 100 clients leave a nearly empty last wave
+  static int milli_per_sm = 0;
+  if (!milli_per_sm) {
+    const char* e = getenv("FB_BN_CTAS_PER_SM");
+    milli_per_sm = e ? (int)(atof(e) * 1000) : 3400;
+    if (milli_per_sm < 100) milli_per_sm = 100;
+  }
+  int64_t want = ((int64_t)milli_per_sm * fb_num_sms() / 1000 + C / 2) / C;
   int64_t max_s = (M * ch + 8191) / 8192;
   if (want > max_s) want = max_s;
   if (want < 1) want = 1;
@@ -263,7 +279,8 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_fwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   FB_REQUIRE(running_mean && running_var, "fb_bn_fwd_stacked: running statistics missing");
   FB_REQUIRE(!training || scratch, "fb_bn_fwd_stacked: training needs the partial-sum scratch");
-  const int S = bn_slices(C, M, ch);
+  int S = bn_slices(C, M, ch);
+  if (bn_forced_slices(0) > 0) S = bn_forced_slices(0);
   if (training && bn_fused_enabled((int64_t)C * M * ch * 2)) {
     FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
@@ -486,7 +503,8 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x,
              "fb_bn_bwd_stacked: bad arguments");
   FB_REQUIRE(!relu || y || beta, "fb_bn_bwd_stacked: the ReLU mask needs the forward output or beta to recompute it");
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
-  const int S = bn_slices(C, M, ch);
+  int S = bn_slices(C, M, ch);
+  if (bn_forced_slices(1) > 0) S = bn_forced_slices(1);
   if (bn_fused_enabled((int64_t)C * M * ch * 2)) {
     FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
