@@ -329,6 +329,9 @@ class NativeBackend(TorchBackend):
         # the layer prepared together with the weights
         # [C,M,N] x [C,N,K]: the NN operand form feeds b MN-major straight from the [out][in] weights, so no transposed
         # staging copy is needed; a prepared b^T (K-major) is used when the NN form does not cover the layout
+        if self.use_tc_gemm and b_t is not None and os.environ.get("FB_DGRAD_NN", "1") == "0" \
+                and self.ops.grouped_gemm_supported(a, b_t):
+            return self.ops.grouped_gemm(a, b_t, out_dtype or a.dtype)
         if self.use_tc_gemm and self._tf().mm_supported("nn", a, b):
             return self._tf().mm("nn", a, b, out_dtype=out_dtype or a.dtype)
         if self.use_tc_gemm and b_t is not None and self.ops.grouped_gemm_supported(a, b_t):
@@ -495,6 +498,8 @@ class _Conv:
     def wants_transposed(self):
         """Only the implicit stride-1 3x3 data gradient reads the transposed copy [k*k*cin, cout]; every other data
         gradient uses the NN GEMM form on the forward operand."""
+        if os.environ.get("FB_DGRAD_NN", "1") == "0":          # A/B switch: K-major transposed copies for every data gradient
+            return self.need_dx
         return self.need_dx and self.k == 3 and self.stride == 1
 
     def _cols(self, be, x):
