@@ -178,6 +178,10 @@ class NCCLSimulator:
     def _build_executor(self):
         args = self.args
         self.batched = None
+        if int(getattr(args, "client_groups", 0) or os.environ.get("FB_CLIENT_GROUPS", "0") or 0) > 1:
+            # concurrent client groups launch BatchNorm kernels on several streams at once; the single-launch form shares
+            # one in-library barrier per client index, so keep the two-pass form (read once, before the first BN call)
+            os.environ.setdefault("FB_BN_FUSED", "0")
         if self.custom_trainer is None and bool(getattr(args, "batched_clients", True)):
             if self.cuda:
                 dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "fp16": torch.float16}[
