@@ -209,6 +209,47 @@ __global__ void __launch_bounds__(256) krum_pack_kernel(const float* const* __re
                                                         int64_t ld) {
   const int k = blockIdx.y;
   const float* row = rows[k];
+  if ((((uintptr_t)(row + j0)) & 15) == 0 && (ref == nullptr || (((uintptr_t)(ref + j0)) & 15) == 0) && (ld & 3) == 0 &&
+      (((uintptr_t)hi) & 7) == 0 && (lo == nullptr || (((uintptr_t)lo) & 7) == 0)) {
+    // four coordinates per thread: 16-byte peer loads, 8-byte bf16 stores
+    const int64_t nv = ld >> 2;
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += (int64_t)gridDim.x * blockDim.x) {
+      const int64_t i = v << 2;
+      float x[4] = {0.f, 0.f, 0.f, 0.f};
+      if (i + 3 < n) {
+        asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(x[0]), "=f"(x[1]), "=f"(x[2]), "=f"(x[3])
+                     : "l"(row + j0 + i)
+                     : "memory");
+        if (ref) {
+          const float4 r = __ldg(reinterpret_cast<const float4*>(ref + j0 + i));
+          x[0] -= r.x; x[1] -= r.y; x[2] -= r.z; x[3] -= r.w;
+        }
+      } else {
+        for (int e = 0; e < 4; ++e)
+          if (i + e < n) {
+            asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(x[e]) : "l"(row + j0 + i + e) : "memory");
+            if (ref) x[e] -= __ldg(ref + j0 + i + e);
+          }
+      }
+      __nv_bfloat16 h[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) h[e] = __float2bfloat16_rn(x[e]);
+      uint2 o;
+      o.x = (uint32_t)__bfloat16_as_ushort(h[0]) | ((uint32_t)__bfloat16_as_ushort(h[1]) << 16);
+      o.y = (uint32_t)__bfloat16_as_ushort(h[2]) | ((uint32_t)__bfloat16_as_ushort(h[3]) << 16);
+      *reinterpret_cast<uint2*>(hi + (size_t)k * ld + i) = o;
+      if (lo) {
+        __nv_bfloat16 l[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) l[e] = __float2bfloat16_rn(x[e] - __bfloat162float(h[e]));
+        o.x = (uint32_t)__bfloat16_as_ushort(l[0]) | ((uint32_t)__bfloat16_as_ushort(l[1]) << 16);
+        o.y = (uint32_t)__bfloat16_as_ushort(l[2]) | ((uint32_t)__bfloat16_as_ushort(l[3]) << 16);
+        *reinterpret_cast<uint2*>(lo + (size_t)k * ld + i) = o;
+      }
+    }
+    return;
+  }
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < ld; i += (int64_t)gridDim.x * blockDim.x) {
     float x = 0.f;
     if (i < n) {
