@@ -831,6 +831,14 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
   const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
   int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  {
+    static int conv_ctas = -1;
+    if (conv_ctas < 0) {
+      const char* e = getenv("FB_CONV_CTAS_PER_SM");
+      conv_ctas = e ? atoi(e) : 0;
+    }
+    if (conv_ctas == 1) ctas_per_sm = 1;
+  }
   int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
   if (stages < 3 && ctas_per_sm == 2) {
     ctas_per_sm = 1;
@@ -924,6 +932,14 @@ extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
   const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
   int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  {
+    static int conv_ctas = -1;
+    if (conv_ctas < 0) {
+      const char* e = getenv("FB_CONV_CTAS_PER_SM");
+      conv_ctas = e ? atoi(e) : 0;
+    }
+    if (conv_ctas == 1) ctas_per_sm = 1;
+  }
   int stages = (int)((227 * 1024 / ctas_per_sm - fixed) / stage_bytes);
   if (stages < 3 && ctas_per_sm == 2) {
     ctas_per_sm = 1;
