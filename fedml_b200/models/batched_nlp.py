@@ -255,17 +255,20 @@ class BatchedDistilBert(BatchedModel):
             dz2 = be.ln_bwd(d, d2, z2, m2, r2, W[p + "output_layer_norm.weight"], G[p + "output_layer_norm.weight"],
                             G[p + "output_layer_norm.bias"])
             df = self._drop(dz2, self.p_hidden, 16 * (i + 1) + 2, True)
-            be.mm("tn", df, a, out=G[p + "ffn.lin2.weight"])
-            be.colsum(df, G[p + "ffn.lin2.bias"])
+            with be.side(df):                      # parameter gradients: off the data-gradient chain (parallel graph branch)
+                be.mm("tn", df, a, out=G[p + "ffn.lin2.weight"])
+                be.colsum(df, G[p + "ffn.lin2.bias"])
             da = be.mm("nn", df, Wm[f"f2{i}"])
             du = be.act_bwd(da, u, "gelu")
-            be.mm("tn", du, h1, out=G[p + "ffn.lin1.weight"])
-            be.colsum(du, G[p + "ffn.lin1.bias"])
+            with be.side(du):
+                be.mm("tn", du, h1, out=G[p + "ffn.lin1.weight"])
+                be.colsum(du, G[p + "ffn.lin1.bias"])
             dh1 = be.mm("nn", du, Wm[f"f1{i}"])
             dz1 = be.ln_bwd(dh1, dz2, z1, m1, r1, W[p + "sa_layer_norm.weight"], G[p + "sa_layer_norm.weight"],
                             G[p + "sa_layer_norm.bias"])
-            be.mm("tn", dz1, ctx, out=G[p + "attention.out_lin.weight"])
-            be.colsum(dz1, G[p + "attention.out_lin.bias"])
+            with be.side(dz1):
+                be.mm("tn", dz1, ctx, out=G[p + "attention.out_lin.weight"])
+                be.colsum(dz1, G[p + "attention.out_lin.bias"])
             dctx = be.mm("nn", dz1, Wm[f"o{i}"])
             dctx_h = self._heads(dctx, C, B, S)
             dqkv = torch.empty_like(qkv)
@@ -276,10 +279,11 @@ class BatchedDistilBert(BatchedModel):
             del dP
             be.mm("nn", dS, k, out=dq)                                                       # dQ = dS K
             be.mm("tn", dS, q, out=dk)                                                       # dK = dS^T Q
-            for j, nm in enumerate(("q_lin", "k_lin", "v_lin")):
-                blk = dqkv[:, :, j * D:(j + 1) * D]
-                be.mm("tn", blk, h, out=G[p + f"attention.{nm}.weight"])
-                be.colsum(blk, G[p + f"attention.{nm}.bias"])
+            with be.side(dqkv):
+                for j, nm in enumerate(("q_lin", "k_lin", "v_lin")):
+                    blk = dqkv[:, :, j * D:(j + 1) * D]
+                    be.mm("tn", blk, h, out=G[p + f"attention.{nm}.weight"])
+                    be.colsum(blk, G[p + f"attention.{nm}.bias"])
             d = be.mm("nn", dqkv, Wm[f"qkv{i}"])
             d2 = dz1
         # ---- embeddings
@@ -297,6 +301,7 @@ class BatchedDistilBert(BatchedModel):
         else:
             G[wname].zero_()
             be.embed_bwd(ids2, de, G[wname], G["distilbert.embeddings.position_embeddings.weight"], S)
+        be.join()                                  # parameter-gradient branch complete
         self.fused_applied = False
         if self.fused_lr is not None and isinstance(be, NativeBackend) and getattr(W, "arena", None) is not None:
             fp = self._fused_plan(W)
