@@ -299,18 +299,23 @@ class NativeBackend(TorchBackend):
         import contextlib
         if not (self.use_side_stream and torch.cuda.is_available()):
             return contextlib.nullcontext()
-        if getattr(self, "_side", None) is None:
-            self._side, self._keep, self._forked = torch.cuda.Stream(), [], False
-        self._side.wait_stream(torch.cuda.current_stream())
+        if getattr(self, "_sides", None) is None:
+            n = max(1, int(os.environ.get("FB_SIDE_STREAMS", "1")))
+            self._sides, self._keep, self._forked, self._side_rr = [torch.cuda.Stream() for _ in range(n)], [], False, 0
+        side = self._sides[self._side_rr % len(self._sides)]      # round-robin over the branch streams
+        self._side_rr += 1
+        side.wait_stream(torch.cuda.current_stream())
         self._keep.extend(keep)          # main-stream tensors the branch reads stay allocated until join()
         self._forked = True
-        return torch.cuda.stream(self._side)
+        return torch.cuda.stream(side)
 
     def join(self):
         if getattr(self, "_forked", False):
-            torch.cuda.current_stream().wait_stream(self._side)
+            for side in self._sides:
+                torch.cuda.current_stream().wait_stream(side)
             self._keep.clear()
             self._forked = False
+            self._side_rr = 0
 
     @staticmethod
     def _bn_ok(ch):
@@ -879,8 +884,8 @@ class BatchedResNet(BatchedModel):
         """GEMM-layout weight gradients -> parameter layout in the arena (one launch; on the weight-gradient branch)."""
         un = getattr(self, "_unstage", None)
         if un is not None:
-            with self.be.side():
-                self.be.ops.unstage_conv_grads(self._dw_big, G.arena, un[0], un[1], un[2])
+            self.be.join()               # every weight-gradient GEMM of the branch streams has finished
+            self.be.ops.unstage_conv_grads(self._dw_big, G.arena, un[0], un[1], un[2])
 
     def train_step(self, x, y, W, G, active, row_scale=None):
         be = self.be
