@@ -283,7 +283,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // 128 consecutive output pixels of group g: image n0 (a tile spans 128 / (Ho*Wo) images when the plane is
           // smaller), output rows from ho0.  One k-block per (tap, channel block): the tap's shifted input window
           // is one TMA box (padding = out-of-bounds zero fill, stride = element strides of the map).
-          const int p0 = mt * GEMM_BM;
+          const int p0 = mt * TILE_M + (int)rank * GEMM_BM;       // a pair CTA gathers its own 128 pixels
           const int n0 = g * a.cv_B + p0 / a.cv_HoWo, ho0 = (p0 % a.cv_HoWo) / a.cv_Wo;
           const uint32_t inner_bytes = (uint32_t)a.cv_kblk * 2u;
           for (int kb = 0; kb < a.k_blocks; ++kb) {
@@ -293,10 +293,19 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_wait(empty_bar + stage, phase ^ 1);
             uint8_t* sa = smem + (size_t)stage * stage_bytes;
             uint8_t* sb = sa + GEMM_A_BYTES;
-            mbar_expect_tx(full_bar + stage, (GEMM_BM + (uint32_t)a.BN) * inner_bytes);
-            tma_load_4d(&tmA, sa, full_bar + stage, kc * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
-            tma_load_4d(&tmB, sb, full_bar + stage, kc * a.cv_kblk + wt * a.cv_b_inner_off, nt * a.BN + wt * a.cv_b_row_off,
-                        g, 0);
+            if constexpr (PAIR) {
+              const uint32_t lbar = mapa_u32(smem_u32(full_bar + stage), 0);
+              const int nh = a.BN / 2;                               // this CTA's half of the filter rows
+              if (rank == 0) mbar_expect_tx(full_bar + stage, 2u * (GEMM_BM + (uint32_t)nh) * inner_bytes);
+              tma_load_4d_pair(&tmA, sa, lbar, kc * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
+              tma_load_4d_pair(&tmB, sb, lbar, kc * a.cv_kblk + wt * a.cv_b_inner_off,
+                               nt * a.BN + (int)rank * nh + wt * a.cv_b_row_off, g, 0);
+            } else {
+              mbar_expect_tx(full_bar + stage, (GEMM_BM + (uint32_t)a.BN) * inner_bytes);
+              tma_load_4d(&tmA, sa, full_bar + stage, kc * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
+              tma_load_4d(&tmB, sb, full_bar + stage, kc * a.cv_kblk + wt * a.cv_b_inner_off, nt * a.BN + wt * a.cv_b_row_off,
+                          g, 0);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
           continue;
@@ -780,13 +789,28 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
     const int nt = (p->cout + 255) / 256;
     bn_cols = ((p->cout + nt - 1) / nt + 63) / 64 * 64;
   }
+  // CTA pairs (cta_group::2): 256 output pixels x bn filters per pair, each CTA gathers its own 128 pixels and stages
+  // half of the filter rows.  Wide layers only: the halves must be whole 64-row blocks.  OPT-IN (FB_CONV_PAIR=1): measured
+  // on ResNet-18 x 64 clients it is not faster (54.7 vs 54.5 ms/round; these convolutions are pipeline-latency bound, not
+  // L2-traffic bound), and only one forward shape (stride 2, 64 -> 128 channels) is checked against F.conv2d; the
+  // data-gradient form of the pair path has no oracle test yet.
+  static int conv_pair_env = -1;
+  if (conv_pair_env < 0) {
+    const char* e = getenv("FB_CONV_PAIR");
+    conv_pair_env = e ? atoi(e) : 0;
+  }
+  const bool pair = conv_pair_env != 0 && p->cout >= 128 && (int64_t)p->B * plane >= 512 && inner_bytes == 128;
+  if (pair) {
+    const int nt = (p->cout + 255) / 256;
+    bn_cols = ((p->cout + nt - 1) / nt + 127) / 128 * 128;
+  }
   a.BN = bn_cols; a.BNpad = bn_cols;
   a.gi = p->G; a.gi_out = p->G; a.group_div = 1; a.d_gs2 = 0;
   a.tma_store = ((uint64_t)p->cout * 2) % 16 == 0;
   a.chunk_cols = bn_cols >= 64 ? 64 : bn_cols;
   a.chunk_bytes = a.chunk_cols * 2;
   a.n_tiles = (p->cout + bn_cols - 1) / bn_cols;
-  a.m_tiles = (a.M + GEMM_BM - 1) / GEMM_BM;
+  a.m_tiles = pair ? (a.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM) : (a.M + GEMM_BM - 1) / GEMM_BM;
   a.cv_B = p->B; a.cv_HoWo = plane; a.cv_Wo = Wo; a.cv_stride = s; a.cv_flip = p->dgrad ? 1 : 0;
   a.cv_kblk = kblk; a.cv_kcs = p->cin / kblk; a.k_blocks = 9 * a.cv_kcs;
   a.cv_sbo = 8 * inner_bytes;
@@ -815,7 +839,7 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
     const uint64_t rows = p->dgrad ? (uint64_t)9 * p->cout : (uint64_t)p->cout;
     cuuint64_t dims[4] = {inner, rows, (cuuint64_t)p->G, 1};
     cuuint64_t strides[3] = {inner * 2, (cuuint64_t)(p->G > 1 ? p->w_gs : inner * rows) * 2, inner * rows * p->G * 2};
-    cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)bn_cols, 1, 1};
+    cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(pair ? bn_cols / 2 : bn_cols), 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -828,9 +852,10 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
                             (uint64_t)a.d_gs, 0, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
     if (rc) return rc;
   }
-  const size_t stage_bytes = GEMM_A_BYTES + (size_t)a.BNpad * 128;
+  const size_t stage_bytes = GEMM_A_BYTES + (size_t)(pair ? a.BNpad / 2 : a.BNpad) * 128;   // as in the kernel
   const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
   int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
+  if (pair) ctas_per_sm = 1;
   {
     static int conv_ctas = -1;
     if (conv_ctas < 0) {
@@ -851,6 +876,14 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   const int total = a.G * a.m_tiles * a.n_tiles;
   int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
+  if (pair) {
+    grid = fb_num_sms() & ~1;
+    if (grid > 2 * total) grid = 2 * total;
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<4, true>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,
+                                        (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));
+    return FB_OK;
+  }
   FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<4>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
   FB_CHECK_CUDA(cudaGetLastError());
