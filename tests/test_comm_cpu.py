@@ -89,6 +89,9 @@ def test_broker_last_will_and_status_manager(broker):
     sm.stop()
 
 
+_INIT_LOCK = threading.Lock()
+
+
 def _run_cross_silo(backend, broker, tmp_path, **kw):
     base = dict(training_type="cross_silo", dataset="mnist", model="lr", client_num_in_total=2, client_num_per_round=2, client_id_list="[1, 2]",
                 comm_round=2, batch_size=10, learning_rate=0.03, frequency_of_the_test=1, synthetic_train_size=1200, mnist_client_num=2,
@@ -101,10 +104,16 @@ def _run_cross_silo(backend, broker, tmp_path, **kw):
 
     def role(rank):
         try:
-            a = fedml.init(Arguments.from_dict(dict(base, rank=rank)))
-            ds, out = fedml.data.load_cross_silo(a)
-            torch.manual_seed(0)
-            model = fedml.model.create(a, out)
+            # The three roles are threads of ONE process here, so they share torch's global RNG (in a deployment each is
+            # its own process).  fedml.init() seeds it and model construction draws from it: without the lock another
+            # role's seeding / drawing can land between this role's manual_seed(0) and its weight init, and the initial
+            # global model - hence the final one - then depends on the thread schedule (the two runs compared by
+            # test_cross_silo_backends_agree differed by ~4e-4 in about half of the runs).
+            with _INIT_LOCK:
+                a = fedml.init(Arguments.from_dict(dict(base, rank=rank)))
+                ds, out = fedml.data.load_cross_silo(a)
+                torch.manual_seed(0)
+                model = fedml.model.create(a, out)
             res[rank] = (fedml.cross_silo.Server if rank == 0 else fedml.cross_silo.Client)(a, torch.device("cpu"), ds, model).run()
         except BaseException as exc:  # noqa: BLE001
             errs.append(exc); raise
