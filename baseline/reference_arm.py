@@ -53,8 +53,10 @@ class _StubFinder(importlib.abc.MetaPathFinder):
 
 
 def import_reference():
-    if not os.path.isdir(os.path.join(REF, "fedml")):
-        raise ImportError("baseline/_ref/fedml missing: run the offline pip install recorded in DESIGN.md")
+    if HERE not in sys.path:
+        sys.path.insert(0, HERE)
+    from install_reference import ensure_reference
+    ensure_reference()          # installs from /root/reference/python when baseline/_ref is not there yet
     # the reference ships protoc<3.19 generated gRPC stubs; the pure-python protobuf runtime still accepts
     # them (must be set before google.protobuf is first imported)
     os.environ.setdefault("PROTOCOL_BUFFERS_PYTHON_IMPLEMENTATION", "python")

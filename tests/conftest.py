@@ -35,3 +35,9 @@ def native_lib():
     build()
     from fedml_b200.ops import native
     return native.lib()
+
+
+@pytest.fixture(autouse=True)
+def _run_in_tmp_cwd(tmp_path, monkeypatch):
+    """The reference-compatible defaults write ./log and ./model_file_cache: keep them out of the source tree."""
+    monkeypatch.chdir(tmp_path)
