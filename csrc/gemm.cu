@@ -101,6 +101,27 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// same with kind::tf32: fp32 operands in shared memory (the tensor core reads sign, exponent and the top 10 mantissa bits)
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -176,11 +197,11 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   return d;
 }
 // instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128, N = bn; majors: 0 = K, 1 = MN
-__device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn, int m = GEMM_BM) {
+__device__ __forceinline__ uint32_t make_idesc(int bn, int a_mn, int b_mn, int m = GEMM_BM, bool tf32 = false) {
   uint32_t d = 0;
   d |= 1u << 4;                       // c_format = F32
-  d |= 1u << 7;                       // a_format = BF16
-  d |= 1u << 10;                      // b_format = BF16
+  d |= (tf32 ? 2u : 1u) << 7;         // a_format: 1 = BF16, 2 = TF32
+  d |= (tf32 ? 2u : 1u) << 10;        // b_format
   d |= (uint32_t)(a_mn & 1) << 15;
   d |= (uint32_t)(b_mn & 1) << 16;
   d |= (uint32_t)(bn >> 3) << 17;     // N / 8
@@ -220,7 +241,11 @@ struct GemmArgs {
 // stages its 128 rows of A and its half of B, the leader CTA issues M = 256 MMAs that read both CTAs' shared memory, each
 // CTA drains its own 128 accumulator rows.  Per output tile the pair moves half the B bytes from L2 that two
 // independent CTAs would.
-template <int MODE, bool PAIR = false>
+// TF32: operands are fp32 in memory and in shared memory, multiplied by tcgen05.mma kind::tf32 (the precision of the
+// reference's cuDNN convolutions).  A 128-byte swizzle row then holds 32 elements instead of 64, so a k-block is 32
+// elements (K-major) / 32 rows of 32-element chunks (MN-major) and one MMA covers K = 8; byte geometry of the stages,
+// descriptors' 32-byte K-major advance and the epilogue are unchanged.
+template <int MODE, bool PAIR = false, bool TF32 = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmArgs a) {
@@ -231,6 +256,13 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t stage_bytes = GEMM_A_BYTES + b_bytes;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   constexpr int TILE_M = PAIR ? 2 * GEMM_BM : GEMM_BM;
+  constexpr uint32_t ES = TF32 ? 4u : 2u;      // operand element size
+  constexpr int BK = 128 / (int)ES;            // elements per k-block (one 128-byte swizzle row); also the MN chunk width
+  constexpr int UK = 32 / (int)ES;             // K elements per MMA instruction
+  // MN-major operands: 16-bit types use the 128-byte swizzle (pattern period 8 k-rows); 32-bit types only exist in the
+  // "128-byte swizzle, 32-byte atom" layout (TMA SWIZZLE_128B_ATOM_32B, descriptor layout type 1), whose pattern repeats
+  // every 4 k-rows of 128 bytes
+  constexpr uint32_t MN_SBO = TF32 ? 512u : 1024u, MN_SWZ = TF32 ? 1u : 2u;
   const int STAGES = a.stages;
   uint8_t* staging = smem + (size_t)STAGES * stage_bytes;            // 1024-aligned: stage_bytes is a multiple of 2048
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + GEMM_STAGING_BYTES);
@@ -285,7 +317,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // is one TMA box (padding = out-of-bounds zero fill, stride = element strides of the map).
           const int p0 = mt * TILE_M + (int)rank * GEMM_BM;       // a pair CTA gathers its own 128 pixels
           const int n0 = g * a.cv_B + p0 / a.cv_HoWo, ho0 = (p0 % a.cv_HoWo) / a.cv_Wo;
-          const uint32_t inner_bytes = (uint32_t)a.cv_kblk * 2u;
+          const uint32_t inner_bytes = (uint32_t)a.cv_kblk * ES;
           for (int kb = 0; kb < a.k_blocks; ++kb) {
             const int tap = kb / a.cv_kcs, kc = kb - tap * a.cv_kcs;
             const int kh = tap / 3, kw = tap - kh * 3;
@@ -318,21 +350,21 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (WGRAD) {
             // weight gradient of a 3x3 convolution: k-block = 64 consecutive output pixels of this (client, K-slice)
             // group; n-tile = (tap, channel chunk); B = the tap's shifted input window, gathered MN-major by TMA
-            const uint32_t row_bytes = (uint32_t)a.cv_kblk * 2u;
-            const int subs = a.BN / a.cv_kblk;                       // 64-row B chunks per k-block (taps x channel blocks)
+            const uint32_t row_bytes = (uint32_t)a.cv_kblk * ES;
+            const int subs = a.BN / a.cv_kblk;                       // BK-row B chunks per k-block (taps x channel blocks)
             const int per_tap = subs / a.cv_tpt;
-            const int a_chunks = min(GEMM_BM / 64, (a.M - mt * GEMM_BM + 63) / 64);   // rows of D beyond cout are never stored
-            mbar_expect_tx(full_bar + stage, (uint32_t)a_chunks * GEMM_BK * 128u + (uint32_t)subs * GEMM_BK * row_bytes);
+            const int a_chunks = min(GEMM_BM / BK, (a.M - mt * GEMM_BM + BK - 1) / BK);   // rows of D beyond cout are never stored
+            mbar_expect_tx(full_bar + stage, (uint32_t)a_chunks * BK * 128u + (uint32_t)subs * BK * row_bytes);
             for (int i = 0; i < a_chunks; ++i)
-              tma_load_4d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g0, g1);
+              tma_load_4d(&tmA, sa + (size_t)i * BK * 128, full_bar + stage, mt * GEMM_BM + i * BK, kb * BK, g0, g1);
             const int tap0 = a.cv_tpt > 1 ? nt * a.cv_tpt : nt / a.cv_kcs;
             const int cc = a.cv_tpt > 1 ? 0 : nt - tap0 * a.cv_kcs;
-            const int p0 = (g % a.group_div) * a.K + kb * GEMM_BK;
+            const int p0 = (g % a.group_div) * a.K + kb * BK;
             const int n0 = (g / a.group_div) * a.cv_B + p0 / a.cv_HoWo, ho0 = (p0 % a.cv_HoWo) / a.cv_Wo;
             for (int i = 0; i < subs; ++i) {
               const int tap = tap0 + i / per_tap, sub = i - (i / per_tap) * per_tap;
               const int kh = tap / 3, kw = tap - kh * 3;
-              tma_load_4d(&tmB, sb + (size_t)i * GEMM_BK * row_bytes, full_bar + stage,
+              tma_load_4d(&tmB, sb + (size_t)i * BK * row_bytes, full_bar + stage,
                           cc * (a.BN / a.cv_tpt) + sub * a.cv_kblk, kw - 1, ho0 * a.cv_stride + kh - 1, n0);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -344,32 +376,32 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (rank == 0) mbar_expect_tx(full_bar + stage, 2 * stage_bytes);
             const int m0 = mt * TILE_M + (int)rank * GEMM_BM, nh = a.BN / 2, n0 = nt * a.BN + (int)rank * nh;
             if (!A_MN) {
-              tma_load_4d_pair(&tmA, sa, lbar, kb * GEMM_BK, m0, g0, g1);
+              tma_load_4d_pair(&tmA, sa, lbar, kb * BK, m0, g0, g1);
             } else {
-              for (int i = 0; i < GEMM_BM / 64; ++i)
-                tma_load_4d_pair(&tmA, sa + (size_t)i * GEMM_BK * 128, lbar, m0 + i * 64, kb * GEMM_BK, g0, g1);
+              for (int i = 0; i < GEMM_BM / BK; ++i)
+                tma_load_4d_pair(&tmA, sa + (size_t)i * BK * 128, lbar, m0 + i * BK, kb * BK, g0, g1);
             }
             if (!B_MN) {
-              tma_load_4d_pair(&tmB, sb, lbar, kb * GEMM_BK, n0, g0, g1);
+              tma_load_4d_pair(&tmB, sb, lbar, kb * BK, n0, g0, g1);
             } else {
-              for (int i = 0; i < nh / 64; ++i)
-                tma_load_4d_pair(&tmB, sb + (size_t)i * GEMM_BK * 128, lbar, n0 + i * 64, kb * GEMM_BK, g0, g1);
+              for (int i = 0; i < nh / BK; ++i)
+                tma_load_4d_pair(&tmB, sb + (size_t)i * BK * 128, lbar, n0 + i * BK, kb * BK, g0, g1);
             }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
             continue;
           }
           mbar_expect_tx(full_bar + stage, stage_bytes);
           if (!A_MN) {
-            tma_load_4d(&tmA, sa, full_bar + stage, kb * GEMM_BK, mt * GEMM_BM, g0, g1);
+            tma_load_4d(&tmA, sa, full_bar + stage, kb * BK, mt * GEMM_BM, g0, g1);
           } else {
-            for (int i = 0; i < GEMM_BM / 64; ++i)
-              tma_load_4d(&tmA, sa + (size_t)i * GEMM_BK * 128, full_bar + stage, mt * GEMM_BM + i * 64, kb * GEMM_BK, g0, g1);
+            for (int i = 0; i < GEMM_BM / BK; ++i)
+              tma_load_4d(&tmA, sa + (size_t)i * BK * 128, full_bar + stage, mt * GEMM_BM + i * BK, kb * BK, g0, g1);
           }
           if (!B_MN) {
-            tma_load_4d(&tmB, sb, full_bar + stage, kb * GEMM_BK, nt * a.BN, g0, g1);
+            tma_load_4d(&tmB, sb, full_bar + stage, kb * BK, nt * a.BN, g0, g1);
           } else {
-            for (int i = 0; i < a.BNpad / 64; ++i)
-              tma_load_4d(&tmB, sb + (size_t)i * GEMM_BK * 128, full_bar + stage, nt * a.BN + i * 64, kb * GEMM_BK, g0, g1);
+            for (int i = 0; i < a.BNpad / BK; ++i)
+              tma_load_4d(&tmB, sb + (size_t)i * BK * 128, full_bar + stage, nt * a.BN + i * BK, kb * BK, g0, g1);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -378,7 +410,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0 && rank == 0) {
-      const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN, TILE_M);
+      const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN, TILE_M, TF32);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
@@ -390,23 +422,29 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
           const uint32_t sb = sa + GEMM_A_BYTES;
-          const int k_rem = a.K - kb * GEMM_BK;
-          const int k_steps = CONV ? a.cv_kblk / 16 : (k_rem >= GEMM_BK ? GEMM_BK / 16 : (k_rem + 15) / 16);
+          const int k_rem = a.K - kb * BK;
+          const int k_steps = CONV ? a.cv_kblk / UK : (k_rem >= BK ? BK / UK : (k_rem + UK - 1) / UK);
           for (int k = 0; k < k_steps; ++k) {
             uint64_t ad, bd;
             if (CONV) {
               ad = make_smem_desc(sa + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
               bd = make_smem_desc(sb + k * 32, 16, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
             } else if (WGRAD) {
-              const uint32_t row_bytes = (uint32_t)a.cv_kblk * 2u;
-              ad = make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024);
-              bd = make_smem_desc(sb + k * 16 * row_bytes, GEMM_BK * row_bytes, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
+              const uint32_t row_bytes = (uint32_t)a.cv_kblk * ES;
+              ad = make_smem_desc(sa + k * UK * 128, BK * 128, MN_SBO, MN_SWZ);
+              bd = make_smem_desc(sb + k * UK * row_bytes, BK * row_bytes, (uint32_t)a.cv_sbo, (uint32_t)a.cv_swz);
             } else {
-              ad = A_MN ? make_smem_desc(sa + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-              bd = B_MN ? make_smem_desc(sb + k * 2048, GEMM_BK * 128, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+              // MN-major: UK k-rows of 128 bytes per MMA; the next MN chunk (BK elements) starts BK rows further
+              ad = A_MN ? make_smem_desc(sa + k * UK * 128, BK * 128, MN_SBO, MN_SWZ) : make_smem_desc(sa + k * 32, 16, 1024);
+              bd = B_MN ? make_smem_desc(sb + k * UK * 128, BK * 128, MN_SBO, MN_SWZ) : make_smem_desc(sb + k * 32, 16, 1024);
             }
-            if constexpr (PAIR) umma_bf16_pair(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
-            else umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            if constexpr (TF32) {
+              if constexpr (PAIR) umma_tf32_pair(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+              else umma_tf32(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            } else {
+              if constexpr (PAIR) umma_bf16_pair(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+              else umma_bf16(tmem_d, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            }
           }
           // smem slot reusable once these MMAs have read it (in a pair: the slot of both CTAs)
           if constexpr (PAIR) umma_commit_pair(empty_bar + stage);
@@ -572,19 +610,22 @@ static PFN_encodeTiled get_encode() {
 // 4-D bf16 tensor map: dims (inner, rows, inner groups, outer groups), box (64, box_rows, 1, 1), 128B swizzle,
 // zero OOB fill.  A dimension of extent 1 gets a harmless dense stride.
 static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint64_t gi, uint64_t go,
-                    uint64_t row_stride_elems, uint64_t gs_elems, uint64_t gs2_elems, uint32_t box_rows) {
+                    uint64_t row_stride_elems, uint64_t gs_elems, uint64_t gs2_elems, uint32_t box_rows, bool tf32 = false,
+                    bool mn_major = false) {
   PFN_encodeTiled enc = get_encode();
   FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  const uint64_t es = tf32 ? 4 : 2;
   cuuint64_t dims[4] = {inner, rows, gi, go};
   const uint64_t dense = row_stride_elems * rows;
-  cuuint64_t strides[3] = {row_stride_elems * 2, (gi > 1 ? gs_elems : dense) * 2, (go > 1 ? gs2_elems : dense * gi) * 2};
-  cuuint32_t box[4] = {64, box_rows, 1, 1};
+  cuuint64_t strides[3] = {row_stride_elems * es, (gi > 1 ? gs_elems : dense) * es, (go > 1 ? gs2_elems : dense * gi) * es};
+  cuuint32_t box[4] = {(cuuint32_t)(128 / es), box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   FB_REQUIRE((strides[0] % 16) == 0 && (strides[1] % 16) == 0 && (strides[2] % 16) == 0 && ((uintptr_t)base % 16) == 0,
              "grouped GEMM operands need 16-byte aligned base pointers and strides");
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code %d", (int)r);
   return FB_OK;
 }
@@ -608,8 +649,9 @@ static int make_store_map(CUtensorMap* m, void* base, int fp32, uint64_t N, uint
   return FB_OK;
 }
 
-static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
+static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, bool tf32 = false) {
   const bool a_mn = (mode & 1) != 0, b_mn = (mode & 2) != 0;
+  const int BK = tf32 ? 32 : 64;      // elements per k-block and per MN-major chunk (one 128-byte row)
   FB_REQUIRE(p && p->a && p->b && p->d, "fb_grouped_gemm: null operand");
   FB_REQUIRE(p->G >= 1 && p->M >= 1 && p->N >= 1 && p->K >= 1, "fb_grouped_gemm: empty problem");
   const int group_div = p->out_group_div > 0 ? p->out_group_div : 1;
@@ -667,29 +709,29 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   a.reduce_add = p->accumulate ? 1 : 0;
   a.group_div = group_div;
   FB_REQUIRE(!a.reduce_add || a.tma_store, "fb_grouped_gemm: accumulate needs a 16-byte aligned output (TMA reduce-store)");
-  a.BNpad = b_mn ? (bn + 63) / 64 * 64 : bn;
+  a.BNpad = b_mn ? (bn + BK - 1) / BK * BK : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
   a.m_tiles = pair ? (p->M + 2 * GEMM_BM - 1) / (2 * GEMM_BM) : (p->M + GEMM_BM - 1) / GEMM_BM;
-  a.k_blocks = (p->K + GEMM_BK - 1) / GEMM_BK;
+  a.k_blocks = (p->K + BK - 1) / BK;
   int cols = 32;
   while (cols < 2 * bn) cols <<= 1;
   a.tmem_cols = cols;
   CUtensorMap tmA, tmB;
   int rc;
-  FB_REQUIRE(p->lda % 8 == 0 && p->ldb % 8 == 0, "fb_grouped_gemm: lda/ldb must be multiples of 8 elements");
+  FB_REQUIRE(p->lda % (tf32 ? 4 : 8) == 0 && p->ldb % (tf32 ? 4 : 8) == 0, "fb_grouped_gemm: lda/ldb must be multiples of 16 bytes");
   if (!a_mn)
     rc = make_map(&tmA, p->a, (uint64_t)p->K, (uint64_t)p->M, (uint64_t)gi, (uint64_t)go, (uint64_t)p->lda, (uint64_t)p->a_gs,
-                  (uint64_t)p->a_gs2, GEMM_BM);
+                  (uint64_t)p->a_gs2, GEMM_BM, tf32);
   else
     rc = make_map(&tmA, p->a, (uint64_t)p->M, (uint64_t)p->K, (uint64_t)gi, (uint64_t)go, (uint64_t)p->lda, (uint64_t)p->a_gs,
-                  (uint64_t)p->a_gs2, GEMM_BK);
+                  (uint64_t)p->a_gs2, (uint32_t)BK, tf32, true);
   if (rc) return rc;
   if (!b_mn)
     rc = make_map(&tmB, p->b, (uint64_t)p->K, (uint64_t)p->N, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
-                  (uint64_t)p->b_gs2, (uint32_t)(pair ? a.BN / 2 : a.BN));
+                  (uint64_t)p->b_gs2, (uint32_t)(pair ? a.BN / 2 : a.BN), tf32);
   else
     rc = make_map(&tmB, p->b, (uint64_t)p->N, (uint64_t)p->K, (uint64_t)gi, (uint64_t)go, (uint64_t)p->ldb, (uint64_t)p->b_gs,
-                  (uint64_t)p->b_gs2, GEMM_BK);
+                  (uint64_t)p->b_gs2, (uint32_t)BK, tf32, true);
   if (rc) return rc;
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)(pair ? a.BNpad / 2 : a.BNpad) * 128;
   const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/;
@@ -720,31 +762,41 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream) {
   }
   const int total = a.G * a.m_tiles * a.n_tiles;
   int grid = fb_num_sms() * ctas_per_sm;
+#define FB_LAUNCH_PAIR(MODE_, TF_)                                                                                              \
+  do {                                                                                                                            \
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, true, TF_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<MODE_, true, TF_>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,    \
+                                        (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));                                            \
+  } while (0)
+#define FB_LAUNCH_ONE(MODE_, TF_)                                                                                               \
+  do {                                                                                                                            \
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, false, TF_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<MODE_, false, TF_>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,           \
+                                (cudaStream_t)stream, tmA, tmB, tmD, a));                                                        \
+  } while (0)
   if (pair) {
     grid &= ~1;
     if (grid > 2 * total) grid = 2 * total;
-#define FB_LAUNCH_PAIR(MODE_)                                                                                             \
-  do {                                                                                                                      \
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<MODE_, true>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,    \
-                                        (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));                                      \
-  } while (0)
-    if (mode == 3) FB_LAUNCH_PAIR(3);
-    else if (mode == 2) FB_LAUNCH_PAIR(2);
-    else FB_LAUNCH_PAIR(0);
-#undef FB_LAUNCH_PAIR
+    if (tf32) {
+      if (mode == 3) FB_LAUNCH_PAIR(3, true);
+      else if (mode == 2) FB_LAUNCH_PAIR(2, true);
+      else FB_LAUNCH_PAIR(0, true);
+    } else {
+      if (mode == 3) FB_LAUNCH_PAIR(3, false);
+      else if (mode == 2) FB_LAUNCH_PAIR(2, false);
+      else FB_LAUNCH_PAIR(0, false);
+    }
     return FB_OK;
   }
   if (grid > total) grid = total;
-  if (mode == 3) {
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<3>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
-  } else if (mode == 2) {
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<2>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
+  if (tf32) {
+    if (mode == 3) FB_LAUNCH_ONE(3, true);
+    else if (mode == 2) FB_LAUNCH_ONE(2, true);
+    else FB_LAUNCH_ONE(0, true);
   } else {
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<0>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
+    if (mode == 3) FB_LAUNCH_ONE(3, false);
+    else if (mode == 2) FB_LAUNCH_ONE(2, false);
+    else FB_LAUNCH_ONE(0, false);
   }
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
@@ -755,34 +807,35 @@ static CUtensorMapSwizzle swizzle_for(int inner_bytes) {
   return inner_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
 }
 
-extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
-  FB_REQUIRE(p && p->x && p->w && p->y, "fb_conv3x3_bf16: null operand");
-  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_bf16: empty problem");
-  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_bf16: stride must be 1 or 2");
-  FB_REQUIRE(!(p->dgrad && p->stride != 1), "fb_conv3x3_bf16: the data-gradient form needs stride 1");
-  FB_REQUIRE(p->cin >= 16 && p->cin % 16 == 0 && (p->cin <= 64 ? (p->cin & (p->cin - 1)) == 0 : p->cin % 64 == 0),
-             "fb_conv3x3_bf16: input channels must be 16, 32 or a multiple of 64 (got %d)", p->cin);
-  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_bf16: output channels must be a multiple of 8");
+static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32) {
+  const int es = tf32 ? 4 : 2, BK = 128 / es;
+  FB_REQUIRE(p && p->x && p->w && p->y, "fb_conv3x3: null operand");
+  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3: empty problem");
+  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3: stride must be 1 or 2");
+  FB_REQUIRE(!(p->dgrad && p->stride != 1), "fb_conv3x3: the data-gradient form needs stride 1");
+  FB_REQUIRE(p->cin * es >= 32 && (p->cin <= BK ? (p->cin & (p->cin - 1)) == 0 : p->cin % BK == 0),
+             "fb_conv3x3: input channels must fill 32 or 64 bytes or a multiple of 128 bytes (got %d)", p->cin);
+  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3: output channels must be a multiple of 8");
   const int s = p->stride;
   const int Ho = (p->H - 1) / s + 1, Wo = (p->W - 1) / s + 1;
   FB_REQUIRE(Wo <= 128 && (Wo & (Wo - 1)) == 0 && (Ho & (Ho - 1)) == 0 && Wo * s <= 256,
-             "fb_conv3x3_bf16: output plane must be a power of two per side, at most 128 wide (got %d x %d)", Ho, Wo);
+             "fb_conv3x3: output plane must be a power of two per side, at most 128 wide (got %d x %d)", Ho, Wo);
   const int plane = Ho * Wo;
   const int bh = plane >= GEMM_BM ? GEMM_BM / Wo : Ho;          // output rows per tile
   const int bn = plane >= GEMM_BM ? 1 : GEMM_BM / plane;        // images per tile
-  FB_REQUIRE(bh >= 1 && bh * s <= 256 && bn <= 256, "fb_conv3x3_bf16: unsupported plane shape");
+  FB_REQUIRE(bh >= 1 && bh * s <= 256 && bn <= 256, "fb_conv3x3: unsupported plane shape");
   PFN_encodeTiled enc = get_encode();
   FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-  FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->w % 16) == 0 && ((uintptr_t)p->y % 16) == 0 && p->w_gs % 8 == 0,
-             "fb_conv3x3_bf16: operands must be 16-byte aligned");
+  FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->w % 16) == 0 && ((uintptr_t)p->y % 16) == 0 && (p->w_gs * es) % 16 == 0,
+             "fb_conv3x3: operands must be 16-byte aligned");
 
-  const int kblk = p->cin < 64 ? p->cin : 64;
-  const int inner_bytes = kblk * 2;
+  const int kblk = p->cin < BK ? p->cin : BK;
+  const int inner_bytes = kblk * es;
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.d = p->y; a.bias = nullptr;
   a.G = p->G; a.M = p->B * plane; a.N = p->cout; a.K = 9 * p->cin;
-  a.ldd = p->cout; a.d_fp32 = 0; a.relu = 0;
+  a.ldd = p->cout; a.d_fp32 = tf32 ? 1 : 0; a.relu = 0;
   a.d_gs = (int64_t)a.M * a.N;
   int bn_cols = (p->cout + 15) / 16 * 16;
   if (bn_cols > 64) {
@@ -806,9 +859,9 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   }
   a.BN = bn_cols; a.BNpad = bn_cols;
   a.gi = p->G; a.gi_out = p->G; a.group_div = 1; a.d_gs2 = 0;
-  a.tma_store = ((uint64_t)p->cout * 2) % 16 == 0;
-  a.chunk_cols = bn_cols >= 64 ? 64 : bn_cols;
-  a.chunk_bytes = a.chunk_cols * 2;
+  a.tma_store = ((uint64_t)p->cout * es) % 16 == 0;
+  a.chunk_cols = tf32 ? (bn_cols >= 32 ? 32 : 16) : (bn_cols >= 64 ? 64 : bn_cols);
+  a.chunk_bytes = a.chunk_cols * es;
   a.n_tiles = (p->cout + bn_cols - 1) / bn_cols;
   a.m_tiles = pair ? (a.M + 2 * GEMM_BM - 1) / (2 * GEMM_BM) : (a.M + GEMM_BM - 1) / GEMM_BM;
   a.cv_B = p->B; a.cv_HoWo = plane; a.cv_Wo = Wo; a.cv_stride = s; a.cv_flip = p->dgrad ? 1 : 0;
@@ -826,10 +879,10 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   CUtensorMap tmA, tmB, tmD;
   {
     cuuint64_t dims[4] = {(cuuint64_t)p->cin, (cuuint64_t)p->W, (cuuint64_t)p->H, (cuuint64_t)p->G * p->B};
-    cuuint64_t strides[3] = {(cuuint64_t)p->cin * 2, (cuuint64_t)p->cin * p->W * 2, (cuuint64_t)p->cin * p->W * p->H * 2};
+    cuuint64_t strides[3] = {(cuuint64_t)p->cin * es, (cuuint64_t)p->cin * p->W * es, (cuuint64_t)p->cin * p->W * p->H * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
     cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
-    CUresult r = enc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+    CUresult r = enc(&tmA, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv input) failed with code %d", (int)r);
@@ -838,17 +891,17 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
     const uint64_t inner = p->dgrad ? (uint64_t)p->cin : (uint64_t)9 * p->cin;
     const uint64_t rows = p->dgrad ? (uint64_t)9 * p->cout : (uint64_t)p->cout;
     cuuint64_t dims[4] = {inner, rows, (cuuint64_t)p->G, 1};
-    cuuint64_t strides[3] = {inner * 2, (cuuint64_t)(p->G > 1 ? p->w_gs : inner * rows) * 2, inner * rows * p->G * 2};
+    cuuint64_t strides[3] = {inner * es, (cuuint64_t)(p->G > 1 ? p->w_gs : inner * rows) * es, inner * rows * p->G * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(pair ? bn_cols / 2 : bn_cols), 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
+    CUresult r = enc(&tmB, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv weights) failed with code %d", (int)r);
   }
   memset(&tmD, 0, sizeof(tmD));
   if (a.tma_store) {
-    int rc = make_store_map(&tmD, p->y, 0, (uint64_t)p->cout, (uint64_t)a.M, (uint64_t)p->G, 1, (uint64_t)p->cout,
+    int rc = make_store_map(&tmD, p->y, tf32 ? 1 : 0, (uint64_t)p->cout, (uint64_t)a.M, (uint64_t)p->G, 1, (uint64_t)p->cout,
                             (uint64_t)a.d_gs, 0, (uint32_t)a.chunk_cols, a.chunk_bytes == 128);
     if (rc) return rc;
   }
@@ -870,7 +923,7 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
     stages = (int)((227 * 1024 - fixed) / stage_bytes);
   }
   if (stages > GEMM_MAX_STAGES) stages = GEMM_MAX_STAGES;
-  FB_REQUIRE(stages >= 2, "fb_conv3x3_bf16: tile does not fit shared memory");
+  FB_REQUIRE(stages >= 2, "fb_conv3x3: tile does not fit shared memory");
   a.stages = stages;
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const int total = a.G * a.m_tiles * a.n_tiles;
@@ -879,43 +932,48 @@ extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) {
   if (pair) {
     grid = fb_num_sms() & ~1;
     if (grid > 2 * total) grid = 2 * total;
-    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<4, true>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,
-                                        (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));
+    if (tf32) FB_LAUNCH_PAIR(4, true);
+    else FB_LAUNCH_PAIR(4, false);
     return FB_OK;
   }
-  FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<4>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
+  if (tf32) FB_LAUNCH_ONE(4, true);
+  else FB_LAUNCH_ONE(4, false);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+extern "C" int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream) { return conv3x3_impl(p, stream, false); }
+extern "C" int fb_conv3x3_tf32(const FbConv3x3* p, fb_stream_t stream) { return conv3x3_impl(p, stream, true); }
 
-extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream) {
-  FB_REQUIRE(p && p->x && p->dy && p->dw, "fb_conv3x3_wgrad_bf16: null operand");
-  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_wgrad_bf16: empty problem");
-  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_wgrad_bf16: stride must be 1 or 2");
-  FB_REQUIRE(p->cin >= 16 && p->cin % 16 == 0 && (p->cin <= 64 ? (p->cin & (p->cin - 1)) == 0 : (p->cin % 64 == 0)) &&
+
+static int conv3x3_wgrad_impl(const FbConv3x3Wgrad* p, fb_stream_t stream, const bool tf32) {
+  const int es = tf32 ? 4 : 2, BK = 128 / es;
+  FB_REQUIRE(p && p->x && p->dy && p->dw, "fb_conv3x3_wgrad: null operand");
+  FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_wgrad: empty problem");
+  FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_wgrad: stride must be 1 or 2");
+  // fp32 operands fed MN-major exist only in the 128-byte-row layout (see the kernel): whole 32-channel blocks
+  FB_REQUIRE(p->cin % 16 == 0 && (p->cin <= BK ? (!tf32 && (p->cin & (p->cin - 1)) == 0) || p->cin == BK : (p->cin % BK == 0)) &&
                  (p->cin <= 256 || p->cin % 256 == 0),
-             "fb_conv3x3_wgrad_bf16: input channels must be 16, 32, 64, 128, 192, 256 or a multiple of 256 (got %d)", p->cin);
-  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_wgrad_bf16: output channels must be a multiple of 8");
+             "fb_conv3x3_wgrad: input channels must fill 32 or 64 bytes, a multiple of 128 bytes up to 256 channels, or a "
+             "multiple of 256 channels (got %d)", p->cin);
+  FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_wgrad: output channels must be a multiple of 8");
   const int s = p->stride;
   const int Ho = (p->H - 1) / s + 1, Wo = (p->W - 1) / s + 1;
   FB_REQUIRE(Wo <= 64 && (Wo & (Wo - 1)) == 0 && (Ho & (Ho - 1)) == 0,
-             "fb_conv3x3_wgrad_bf16: output plane must be a power of two per side, at most 64 wide (got %d x %d)", Ho, Wo);
+             "fb_conv3x3_wgrad: output plane must be a power of two per side, at most 64 wide (got %d x %d)", Ho, Wo);
   const int plane = Ho * Wo;
   const int S = p->split > 0 ? p->split : 1;
   const int64_t Ktot = (int64_t)p->B * plane;
-  FB_REQUIRE(Ktot % ((int64_t)S * GEMM_BK) == 0, "fb_conv3x3_wgrad_bf16: B*Ho*Wo must be a multiple of 64 x split");
+  FB_REQUIRE(Ktot % ((int64_t)S * BK) == 0, "fb_conv3x3_wgrad: B*Ho*Wo must be a multiple of %d x split", BK);
   const int Ks = (int)(Ktot / S);
-  const int bh = plane >= GEMM_BK ? GEMM_BK / Wo : Ho;
-  const int bn = plane >= GEMM_BK ? 1 : GEMM_BK / plane;
+  const int bh = plane >= BK ? BK / Wo : Ho;
+  const int bn = plane >= BK ? 1 : BK / plane;
   PFN_encodeTiled enc = get_encode();
   FB_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->dy % 16) == 0 && ((uintptr_t)p->dw % 16) == 0 &&
                  (p->G == 1 || p->dw_gs % 4 == 0),
-             "fb_conv3x3_wgrad_bf16: operands must be 16-byte aligned");
-  const int kblk = p->cin < 64 ? p->cin : 64;
-  const int row_bytes = kblk * 2;
+             "fb_conv3x3_wgrad: operands must be 16-byte aligned");
+  const int kblk = p->cin < BK ? p->cin : BK;
+  const int row_bytes = kblk * es;
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.d = p->dw; a.bias = nullptr;
@@ -928,7 +986,7 @@ extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream
   const int bn_tap = p->cin < 256 ? p->cin : 256;
   a.cv_tpt = tpt;
   a.BN = tpt * bn_tap;
-  a.BNpad = (a.BN + 63) / 64 * 64;
+  a.BNpad = (a.BN + BK - 1) / BK * BK;
   a.gi = a.G; a.group_div = S; a.gi_out = p->G;
   a.tma_store = 1;
   a.reduce_add = (S > 1 || p->accumulate) ? 1 : 0;
@@ -937,25 +995,25 @@ extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream
   a.cv_kcs = p->cin / bn_tap;
   a.n_tiles = (9 / tpt) * a.cv_kcs;
   a.m_tiles = (p->cout + GEMM_BM - 1) / GEMM_BM;
-  a.k_blocks = Ks / GEMM_BK;
+  a.k_blocks = Ks / BK;
   a.cv_B = p->B; a.cv_HoWo = plane; a.cv_Wo = Wo; a.cv_stride = s;
   a.cv_kblk = kblk;
-  a.cv_sbo = 8 * row_bytes;
-  a.cv_swz = row_bytes == 32 ? 6 : row_bytes == 64 ? 4 : 2;
+  a.cv_sbo = tf32 ? 512 : 8 * row_bytes;
+  a.cv_swz = tf32 ? 1 : (row_bytes == 32 ? 6 : row_bytes == 64 ? 4 : 2);
   int cols = 32;
   while (cols < 2 * a.BN) cols <<= 1;
   a.tmem_cols = cols;
   CUtensorMap tmA, tmB, tmD;
   int rc = make_map(&tmA, p->dy, (uint64_t)p->cout, (uint64_t)Ks, (uint64_t)a.G, 1, (uint64_t)p->cout, (uint64_t)Ks * p->cout, 0,
-                    GEMM_BK);
+                    (uint32_t)BK, tf32, true);
   if (rc) return rc;
   {
     cuuint64_t dims[4] = {(cuuint64_t)p->cin, (cuuint64_t)p->W, (cuuint64_t)p->H, (cuuint64_t)p->G * p->B};
-    cuuint64_t strides[3] = {(cuuint64_t)p->cin * 2, (cuuint64_t)p->cin * p->W * 2, (cuuint64_t)p->cin * p->W * p->H * 2};
+    cuuint64_t strides[3] = {(cuuint64_t)p->cin * es, (cuuint64_t)p->cin * p->W * es, (cuuint64_t)p->cin * p->W * p->H * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
     cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
-    CUresult r = enc(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(row_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+    CUresult r = enc(&tmB, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, tf32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : swizzle_for(row_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (wgrad input) failed with code %d", (int)r);
   }
@@ -979,18 +1037,25 @@ extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream
     stages = (int)((227 * 1024 - fixed) / stage_bytes);
   }
   if (stages > GEMM_MAX_STAGES) stages = GEMM_MAX_STAGES;
-  FB_REQUIRE(stages >= 2, "fb_conv3x3_wgrad_bf16: tile does not fit shared memory");
+  FB_REQUIRE(stages >= 2, "fb_conv3x3_wgrad: tile does not fit shared memory");
   a.stages = stages;
   const size_t smem = (size_t)stages * stage_bytes + fixed;
   const int total = a.G * a.m_tiles * a.n_tiles;
   int grid = fb_num_sms() * ctas_per_sm;
   if (grid > total) grid = total;
-  FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<5>, dim3(grid), dim3(GEMM_THREADS), (size_t)(smem), (cudaStream_t)stream, tmA, tmB, tmD, a));
+  if (tf32) FB_LAUNCH_ONE(5, true);
+  else FB_LAUNCH_ONE(5, false);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+extern "C" int fb_conv3x3_wgrad_bf16(const FbConv3x3Wgrad* p, fb_stream_t stream) { return conv3x3_wgrad_impl(p, stream, false); }
+extern "C" int fb_conv3x3_wgrad_tf32(const FbConv3x3Wgrad* p, fb_stream_t stream) { return conv3x3_wgrad_impl(p, stream, true); }
+
 
 extern "C" int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 0, stream); }
 extern "C" int fb_grouped_gemm_tn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 3, stream); }
 extern "C" int fb_grouped_gemm_nn_bf16(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 2, stream); }
+/* fp32 operands, tcgen05 kind::tf32 (see the kernel template): same structs, strides in fp32 elements */
+extern "C" int fb_grouped_gemm_tf32(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 0, stream, true); }
+extern "C" int fb_grouped_gemm_tn_tf32(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 3, stream, true); }
+extern "C" int fb_grouped_gemm_nn_tf32(const FbGroupedGemm* p, fb_stream_t stream) { return launch_gemm(p, 2, stream, true); }

@@ -358,21 +358,26 @@ def col2im3x3(dcols, B, H, W, ch, stride):
 from .native import FbGroupedGemm  # noqa: E402
 
 
+def _al(t):
+    """elements per 16 bytes"""
+    return 16 // t.element_size()
+
+
 def _gemm_operand_ok(t):
-    return (t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 3 and t.stride(2) == 1 and t.stride(1) % 8 == 0
-            and (t.shape[0] == 1 or t.stride(0) % 8 == 0) and t.data_ptr() % 16 == 0)
+    return (t.is_cuda and t.dtype in (torch.bfloat16, torch.float32) and t.dim() == 3 and t.stride(2) == 1
+            and t.stride(1) % _al(t) == 0 and (t.shape[0] == 1 or t.stride(0) % _al(t) == 0) and t.data_ptr() % 16 == 0)
 
 
 def grouped_gemm_supported(a, b) -> bool:
-    """NT form: a [G,M,K], b [G,N,K] bf16, K-contiguous, 16-byte aligned rows."""
-    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.shape[2] == b.shape[2] and a.shape[2] % 8 == 0 \
-        and a.shape[0] == b.shape[0]
+    """NT form: a [G,M,K], b [G,N,K] bf16 (or fp32 -> TF32 tensor cores), K-contiguous, 16-byte aligned rows."""
+    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.dtype == b.dtype and a.shape[2] == b.shape[2] \
+        and a.shape[2] % _al(a) == 0 and a.shape[0] == b.shape[0]
 
 
 def grouped_gemm_tn_supported(a, b) -> bool:
-    """TN form: a [G,K,M], b [G,K,N] bf16, M/N-contiguous with M % 8 == 0 == N % 8."""
-    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.shape[1] == b.shape[1] and a.shape[0] == b.shape[0] \
-        and a.shape[2] % 8 == 0 and b.shape[2] % 8 == 0
+    """TN form: a [G,K,M], b [G,K,N] bf16 / fp32, M/N-contiguous, 16-byte multiples."""
+    return _gemm_operand_ok(a) and _gemm_operand_ok(b) and a.dtype == b.dtype and a.shape[1] == b.shape[1] \
+        and a.shape[0] == b.shape[0] and a.shape[2] % _al(a) == 0 and b.shape[2] % _al(a) == 0
 
 
 def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, accumulate=False, group_div=1):
@@ -391,11 +396,13 @@ def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, ac
 
 
 def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
-    """d[g] = a[g] @ b[g]^T   (a [G,M,K], b [G,N,K]) on the tcgen05 tensor cores."""
+    """d[g] = a[g] @ b[g]^T   (a [G,M,K], b [G,N,K]) on the tcgen05 tensor cores (fp32 operands: kind::tf32, fp32 out)."""
     if not grouped_gemm_supported(a, b):
         raise NativeError("grouped_gemm: unsupported operand layout")
     G, M, K = a.shape
-    return _launch_gemm(lib().fb_grouped_gemm_bf16, a, b, G, M, b.shape[1], K, out_dtype, relu, bias, "grouped_gemm")
+    tf32 = a.dtype == torch.float32
+    fn = lib().fb_grouped_gemm_tf32 if tf32 else lib().fb_grouped_gemm_bf16
+    return _launch_gemm(fn, a, b, G, M, b.shape[1], K, torch.float32 if tf32 else out_dtype, relu, bias, "grouped_gemm")
 
 
 def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
@@ -408,8 +415,11 @@ def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False
     N = b.shape[2]
     tiles = G * ((M + 127) // 128) * ((N + 255) // 256)
     S = 1
-    if tiles < 296 and a.is_contiguous() and b.is_contiguous() and K % 64 == 0:
-        kb = K // 64
+    tf32 = a.dtype == torch.float32
+    BK = 32 if tf32 else 64
+    fn_tn = lib().fb_grouped_gemm_tn_tf32 if tf32 else lib().fb_grouped_gemm_tn_bf16
+    if tiles < 296 and a.is_contiguous() and b.is_contiguous() and K % BK == 0:
+        kb = K // BK
         for cand in (16, 10, 8, 5, 4, 2):
             if kb % cand == 0 and kb // cand >= 4 and tiles * cand <= 1184:
                 S = cand
@@ -419,13 +429,13 @@ def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False
                                 and out.data_ptr() % 16 == 0 and (G == 1 or out.stride(0) % 4 == 0)):
         out = None
     if S == 1:
-        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn",
+        return _launch_gemm(fn_tn, a, b, G, M, N, K, out_dtype, False, None, "grouped_gemm_tn",
                             out=out if out_dtype == torch.float32 else None)
     if out is not None and out_is_zeroed:
         # split-K slices reduce-add straight into the (pre-zeroed) output with TMA reduce-stores: no partial buffer
-        return _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
+        return _launch_gemm(fn_tn, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
                             K // S, torch.float32, False, None, "grouped_gemm_tn", out=out, accumulate=True, group_div=S)
-    part = _launch_gemm(lib().fb_grouped_gemm_tn_bf16, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
+    part = _launch_gemm(fn_tn, a.view(G * S, K // S, M), b.view(G * S, K // S, N), G * S, M, N,
                         K // S, torch.float32, False, None, "grouped_gemm_tn")
     if out is not None:
         return torch.sum(part.view(G, S, M, N), dim=1, out=out)
@@ -540,13 +550,15 @@ def amp_normalize(x: torch.Tensor, amp_running: Optional[torch.Tensor] = None, m
 
 # --------------------------------------------------------------------------- implicit 3x3 convolution (tcgen05, TMA-gathered taps)
 def conv3x3_supported(x: torch.Tensor, cout: int, stride: int) -> bool:
-    """x [C, B, H, W, cin] bf16 NHWC."""
-    if not (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 5 and x.is_contiguous() and stride in (1, 2)):
+    """x [C, B, H, W, cin] bf16 (or fp32: TF32 tensor cores) NHWC."""
+    if not (x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and x.dim() == 5 and x.is_contiguous()
+            and stride in (1, 2)):
         return False
     _, _, H, W, cin = x.shape
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     pow2 = lambda v: v >= 1 and (v & (v - 1)) == 0   # noqa: E731
-    ok_c = cin in (16, 32) or (cin >= 64 and cin % 64 == 0)
+    row = 128 // x.element_size()                     # channels per 128-byte k-block
+    ok_c = (cin * x.element_size() in (32, 64)) or (cin >= row and cin % row == 0)
     return ok_c and cout % 8 == 0 and cout >= 8 and pow2(Ho) and pow2(Wo) and Wo <= 128 and Wo * stride <= 256
 
 
@@ -554,12 +566,13 @@ def _conv3x3(x, w, cout, stride, dgrad):
     from .native import FbConv3x3
     Cn, B, H, W, cin = x.shape
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
-    y = torch.empty((Cn, B, Ho, Wo, cout), dtype=torch.bfloat16, device=x.device)
+    y = torch.empty((Cn, B, Ho, Wo, cout), dtype=x.dtype, device=x.device)
     p = FbConv3x3()
     p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
     p.w_gs = w.stride(0)
     p.G, p.B, p.H, p.W, p.cin, p.cout, p.stride, p.dgrad = Cn, B, H, W, cin, cout, stride, int(dgrad)
-    check(lib().fb_conv3x3_bf16(C.byref(p), vp(stream_ptr(x.device))), "conv3x3")
+    fn = lib().fb_conv3x3_tf32 if x.dtype == torch.float32 else lib().fb_conv3x3_bf16
+    check(fn(C.byref(p), vp(stream_ptr(x.device))), "conv3x3")
     count_launch()
     return y
 
@@ -568,7 +581,7 @@ def conv3x3(x: torch.Tensor, wm: torch.Tensor, stride: int = 1) -> torch.Tensor:
     """Implicit-GEMM 3x3 convolution, pad 1: x [C,B,H,W,cin] bf16, wm [C, cout, 9*cin] ((kh,kw,cin) columns)."""
     cout = wm.shape[1]
     if not conv3x3_supported(x, cout, stride) or wm.shape[2] != 9 * x.shape[-1] or wm.stride(2) != 1 \
-            or wm.stride(1) != wm.shape[2]:
+            or wm.stride(1) != wm.shape[2] or wm.dtype != x.dtype:
         raise NativeError("conv3x3: unsupported operand layout")
     return _conv3x3(x, wm, cout, stride, False)
 
@@ -576,21 +589,24 @@ def conv3x3(x: torch.Tensor, wm: torch.Tensor, stride: int = 1) -> torch.Tensor:
 def conv3x3_dgrad(dy: torch.Tensor, wt: torch.Tensor) -> torch.Tensor:
     """Input gradient of a stride-1 3x3 convolution: dy [C,B,H,W,cout], wt [C, 9*cin, cout] (transposed staging copy)."""
     cin = wt.shape[1] // 9
-    if not conv3x3_supported(dy, cin, 1) or wt.shape[2] != dy.shape[-1] or wt.stride(2) != 1 or wt.stride(1) != wt.shape[2]:
+    if not conv3x3_supported(dy, cin, 1) or wt.shape[2] != dy.shape[-1] or wt.stride(2) != 1 or wt.stride(1) != wt.shape[2] \
+            or wt.dtype != dy.dtype:
         raise NativeError("conv3x3_dgrad: unsupported operand layout")
     return _conv3x3(dy, wt, cin, 1, True)
 
 
 def conv3x3_wgrad_supported(x: torch.Tensor, dy: torch.Tensor, stride: int) -> bool:
-    if not (x.is_cuda and x.dtype == torch.bfloat16 and dy.dtype == torch.bfloat16 and x.dim() == 5 and x.is_contiguous()
-            and dy.is_contiguous() and stride in (1, 2)):
+    if not (x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and dy.dtype == x.dtype and x.dim() == 5
+            and x.is_contiguous() and dy.is_contiguous() and stride in (1, 2)):
         return False
     _, B, H, W, cin = x.shape
     cout = dy.shape[-1]
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     pow2 = lambda v: v >= 1 and (v & (v - 1)) == 0   # noqa: E731
-    ok_c = cin in (16, 32, 64, 128, 192, 256) or (cin > 256 and cin % 256 == 0)
-    return ok_c and cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 64 and (B * Ho * Wo) % 64 == 0 \
+    row = 128 // x.element_size()
+    ok_c = (cin * x.element_size() in (32, 64) and x.dtype == torch.bfloat16) or (row <= cin <= 256 and cin % row == 0) \
+        or (cin > 256 and cin % 256 == 0)       # fp32 operands fed MN-major need whole 128-byte channel blocks
+    return ok_c and cin % 16 == 0 and cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 64 and (B * Ho * Wo) % row == 0 \
         and tuple(dy.shape[:4]) == (x.shape[0], B, Ho, Wo)
 
 
@@ -607,7 +623,7 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, stride: int = 1, out: Optio
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     tpt = 9 if 9 * cin <= 256 else (3 if 3 * cin <= 256 else 1)     # taps per tile, as in the kernel launcher
     tiles = Cn * ((cout + 127) // 128) * (9 // tpt) * (cin // min(cin, 256))
-    kb = B * Ho * Wo // 64
+    kb = B * Ho * Wo // (128 // x.element_size())
     S = 1
     if tiles < 296:
         for cand in (16, 10, 8, 5, 4, 2):
@@ -626,6 +642,7 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, stride: int = 1, out: Optio
     p.x, p.dy, p.dw = x.data_ptr(), dy.data_ptr(), out.data_ptr()
     p.dw_gs = out.stride(0) if Cn > 1 else cout * 9 * cin
     p.G, p.B, p.H, p.W, p.cin, p.cout, p.stride, p.split, p.accumulate = Cn, B, H, W, cin, cout, stride, S, 0
-    check(lib().fb_conv3x3_wgrad_bf16(C.byref(p), vp(stream_ptr(x.device))), "conv3x3_wgrad")
+    fn = lib().fb_conv3x3_wgrad_tf32 if x.dtype == torch.float32 else lib().fb_conv3x3_wgrad_bf16
+    check(fn(C.byref(p), vp(stream_ptr(x.device))), "conv3x3_wgrad")
     count_launch()
     return out

@@ -17,6 +17,8 @@ f32, i64, i32, u32, u64 = C.c_float, C.c_int64, C.c_int32, C.c_uint32, C.c_uint6
 vp = C.c_void_p
 
 _MODES = {"nt": "fb_grouped_gemm_bf16", "tn": "fb_grouped_gemm_tn_bf16", "nn": "fb_grouped_gemm_nn_bf16"}
+# fp32 operands run on the same kernel with tcgen05 kind::tf32 (the reference's cuDNN convolution precision)
+_MODES_TF32 = {"nt": "fb_grouped_gemm_tf32", "tn": "fb_grouped_gemm_tn_tf32", "nn": "fb_grouped_gemm_nn_tf32"}
 _SCRATCH = {}
 
 
@@ -53,9 +55,10 @@ def mm_supported(mode: str, a: torch.Tensor, b: torch.Tensor, out: Optional[torc
         a, b = _as4(a), _as4(b)
     except NativeError:
         return False
-    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or a.shape[:2] != b.shape[:2]:
+    if a.dtype != b.dtype or a.dtype not in (torch.bfloat16, torch.float32) or a.shape[:2] != b.shape[:2]:
         return False
-    if not (_operand_ok(a, 2) and _operand_ok(b, 2)):
+    es = a.element_size()
+    if not (_operand_ok(a, es) and _operand_ok(b, es)):
         return False
     K = a.shape[3] if mode != "tn" else a.shape[2]
     Kb = b.shape[3] if mode == "nt" else b.shape[2]
@@ -64,6 +67,8 @@ def mm_supported(mode: str, a: torch.Tensor, b: torch.Tensor, out: Optional[torc
     if out is not None:
         o = _as4(out)
         if o.dtype not in (torch.bfloat16, torch.float32) or not _operand_ok(o, o.element_size()):
+            return False
+        if es == 4 and o.dtype != torch.float32:
             return False
     return True
 
@@ -91,7 +96,7 @@ def mm(mode: str, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] 
         K, M, N = a4.shape[2], a4.shape[3], b4.shape[3]
     if out is None:
         shape = tuple(a.shape[:-2]) + (M, N)
-        out = torch.empty(shape, dtype=out_dtype, device=a.device)
+        out = torch.empty(shape, dtype=torch.float32 if a.dtype == torch.float32 else out_dtype, device=a.device)
     o4 = _as4(out)
     if tuple(o4.shape) != (go, gi, M, N):
         raise NativeError(f"mm[{mode}]: output shape {tuple(o4.shape)} != {(go, gi, M, N)}")
@@ -107,7 +112,8 @@ def mm(mode: str, a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] 
             raise NativeError("mm: bias must be fp32 [G, N] with one-level groups")
         p.bias, p.bias_gs = bias.data_ptr(), bias.stride(0)
     p.d_fp32, p.relu = int(out.dtype == torch.float32), int(relu)
-    check(getattr(lib(), _MODES[mode])(C.byref(p), vp(stream_ptr(a.device))), f"mm[{mode}]")
+    table = _MODES_TF32 if a.dtype == torch.float32 else _MODES
+    check(getattr(lib(), table[mode])(C.byref(p), vp(stream_ptr(a.device))), f"mm[{mode}]")
     count_launch()
     return out
 
