@@ -12,11 +12,36 @@
 #define BN_THREADS 256
 #define BN_VEC 8
 
-struct bf16x8 {
-  uint4 raw;
-};
-__device__ __forceinline__ void unpack8(const uint4& r, float* f) {
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+// Eight consecutive channels of one pixel: 16 bytes of bf16 or 32 bytes of fp32 (two 16-byte accesses).  Kernels are
+// templated on the activation element type T; all arithmetic is fp32 either way.
+template <typename T> struct Raw8;
+template <> struct Raw8<__nv_bfloat16> { uint4 v; };
+template <> struct Raw8<float> { float4 a, b; };
+__device__ __forceinline__ Raw8<__nv_bfloat16> ldraw(const __nv_bfloat16* p) {
+  Raw8<__nv_bfloat16> r;
+  r.v = __ldg(reinterpret_cast<const uint4*>(p));
+  return r;
+}
+__device__ __forceinline__ Raw8<float> ldraw(const float* p) {
+  Raw8<float> r;
+  r.a = __ldg(reinterpret_cast<const float4*>(p));
+  r.b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  return r;
+}
+template <typename T> __device__ __forceinline__ Raw8<T> zero_raw();
+template <> __device__ __forceinline__ Raw8<__nv_bfloat16> zero_raw<__nv_bfloat16>() {
+  Raw8<__nv_bfloat16> r;
+  r.v = make_uint4(0, 0, 0, 0);
+  return r;
+}
+template <> __device__ __forceinline__ Raw8<float> zero_raw<float>() {
+  Raw8<float> r;
+  r.a = make_float4(0.f, 0.f, 0.f, 0.f);
+  r.b = r.a;
+  return r;
+}
+__device__ __forceinline__ void unpack8(const Raw8<__nv_bfloat16>& r, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r.v);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     float2 t = __bfloat1622float2(h[i]);
@@ -24,14 +49,26 @@ __device__ __forceinline__ void unpack8(const uint4& r, float* f) {
     f[2 * i + 1] = t.y;
   }
 }
-__device__ __forceinline__ uint4 pack8(const float* f) {
+__device__ __forceinline__ void unpack8(const Raw8<float>& r, float* f) {
+  f[0] = r.a.x; f[1] = r.a.y; f[2] = r.a.z; f[3] = r.a.w;
+  f[4] = r.b.x; f[5] = r.b.y; f[6] = r.b.z; f[7] = r.b.w;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* f) {
   uint4 r;
   __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
 #pragma unroll
   for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-  return r;
+  *reinterpret_cast<uint4*>(p) = r;
 }
-__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void store8(float* p, const float* f) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
+__device__ __forceinline__ void store_raw(__nv_bfloat16* p, const Raw8<__nv_bfloat16>& r) { *reinterpret_cast<uint4*>(p) = r.v; }
+__device__ __forceinline__ void store_raw(float* p, const Raw8<float>& r) {
+  reinterpret_cast<float4*>(p)[0] = r.a;
+  reinterpret_cast<float4*>(p)[1] = r.b;
+}
 
 // reduce the 16 per-thread accumulators (8 channels x 2 quantities) over the threads that share a channel
 // group and write [2][ch] to `out`.  smem: BN_THREADS*16 floats.
@@ -56,19 +93,20 @@ __device__ __forceinline__ void reduce_channel_pairs(const float* a, const float
 
 // ---------------------------------------------------------------- BN forward
 // stage 1: partial[c][s][2][ch] = (sum x, sum x^2) over the rows of slice s
+template <typename T>
 __device__ __forceinline__ void
-bn_stats_body(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial, float* smem) {
+bn_stats_body(const T* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial, float* smem) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
-  const __nv_bfloat16* base = x + (size_t)c * M * ch;
+  const T* base = x + (size_t)c * M * ch;
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const int64_t v0 = r0 * ch / BN_VEC, v1 = r1 * ch / BN_VEC;
   for (int64_t v = v0 + tid; v < v1; v += 4 * BN_THREADS) {   // 4 independent 16-byte loads in flight per thread
-    uint4 r[4];
+    Raw8<T> r[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u)
-      r[u] = (v + u * BN_THREADS < v1) ? ldg16(base + (v + u * BN_THREADS) * BN_VEC) : make_uint4(0, 0, 0, 0);
+      r[u] = (v + u * BN_THREADS < v1) ? ldraw(base + (v + u * BN_THREADS) * BN_VEC) : zero_raw<T>();
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       float f[8];
@@ -84,8 +122,9 @@ bn_stats_body(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, flo
 }
 
 // stage 2: finish the statistics (every CTA redundantly, S is small), update running stats, apply
+template <typename T>
 __device__ __forceinline__ void
-bn_apply_body(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
                 int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                 const float* __restrict__ active, float momentum, float eps, int relu, int training,
@@ -144,12 +183,12 @@ bn_apply_body(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
   for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {    // two vectors (x and res each) in flight per thread
     const int64_t vb = v + BN_THREADS;
     const bool two = vb < v1;
-    const uint4 xa = ldg16(x + cbase + v * BN_VEC);
-    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
-    uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
+    const Raw8<T> xa = ldraw(x + cbase + v * BN_VEC);
+    const Raw8<T> xb = two ? ldraw(x + cbase + vb * BN_VEC) : zero_raw<T>();
+    Raw8<T> ra = zero_raw<T>(), rb = ra;
     if (res) {
-      ra = ldg16(res + cbase + v * BN_VEC);
-      if (two) rb = ldg16(res + cbase + vb * BN_VEC);
+      ra = ldraw(res + cbase + v * BN_VEC);
+      if (two) rb = ldraw(res + cbase + vb * BN_VEC);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -162,7 +201,7 @@ bn_apply_body(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
         f[i] = f[i] * sc[i] + sh[i] + r[i];
         if (relu) f[i] = fmaxf(f[i], 0.f);
       }
-      *reinterpret_cast<uint4*>(y + cbase + (u ? vb : v) * BN_VEC) = pack8(f);
+      store8(y + cbase + (u ? vb : v) * BN_VEC, f);
     }
   }
 }
@@ -195,15 +234,17 @@ static int bn_slices(int C, int64_t M, int ch) {
 }
 
 // ---------------------------------------------------------------- kernels: two-pass and fused single-launch forms
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial) {
+bn_stats_kernel(const T* __restrict__ x, int64_t M, int ch, int S, float* __restrict__ partial) {
   __shared__ float smem[BN_THREADS * 16];
   pdl_wait();
   pdl_trigger();
   bn_stats_body(x, M, ch, S, partial, smem);
 }
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
                 int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                 int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                 float momentum, float eps, int relu, int training, float* __restrict__ save_mean,
@@ -240,8 +281,9 @@ __device__ __forceinline__ void client_barrier(int S) {
 
 // stats -> per-client barrier -> apply in ONE launch: the second read of x comes from L2 (a client's slice was just
 // streamed by its sibling CTAs) and a BN layer costs one kernel instead of two
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_fwd_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, __nv_bfloat16* __restrict__ y,
+bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y,
                     int64_t M, int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                     float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
@@ -270,7 +312,8 @@ static bool bn_fused_enabled(int64_t act_bytes) {
 
 extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * 64 * 2 * ch; }
 
-extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch,
+template <typename T>
+static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch,
                                  const float* gamma, const float* beta, int64_t ld_p, float* running_mean,
                                  float* running_var, int64_t ld_r, const float* active, float momentum, float eps,
                                  int32_t relu, int32_t training, float* save_mean, float* save_rstd, float* scratch,
@@ -281,19 +324,19 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
   FB_REQUIRE(!training || scratch, "fb_bn_fwd_stacked: training needs the partial-sum scratch");
   int S = bn_slices(C, M, ch);
   if (bn_forced_slices(0) > 0) S = bn_forced_slices(0);
-  if (training && bn_fused_enabled((int64_t)C * M * ch * 2)) {
-    FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
+  if (training && bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
+        (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
         running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
   if (training) {
-    FB_CHECK_CUDA(fb_launch_pdl(bn_stats_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, M, ch, S, scratch));
+    FB_CHECK_CUDA(fb_launch_pdl(bn_stats_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)x, M, ch, S, scratch));
     FB_CHECK_CUDA(cudaGetLastError());
   }
-  FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
-      (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, (__nv_bfloat16*)y, M, ch, S, scratch, gamma, beta, ld_p,
+  FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
+      (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p,
       running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd, num_batches_tracked, ld_n));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
@@ -301,10 +344,11 @@ extern "C" int fb_bn_fwd_stacked(const void* x, const void* res, void* y, int32_
 
 // ---------------------------------------------------------------- BN backward
 // stage 1: partial[c][s][2][ch] = (sum dy', sum dy' * xhat), dy' = dy masked by the ReLU of the forward output
+template <typename T>
 __device__ __forceinline__ void
-bn_bwd_stats_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
-                    const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
+bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
+                    const T* __restrict__ x,
+                    const T* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, int relu, float* __restrict__ partial, float* smem) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
@@ -326,13 +370,13 @@ bn_bwd_stats_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
   for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {
     const int64_t vb = v + BN_THREADS;
     const bool two = vb < v1;
-    const uint4 da = ldg16(dy + cbase + v * BN_VEC), xa = ldg16(x + cbase + v * BN_VEC);
-    const uint4 db_ = two ? ldg16(dy + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
-    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
-    uint4 ya = make_uint4(0, 0, 0, 0), yb = ya;
+    const Raw8<T> da = ldraw(dy + cbase + v * BN_VEC), xa = ldraw(x + cbase + v * BN_VEC);
+    const Raw8<T> db_ = two ? ldraw(dy + cbase + vb * BN_VEC) : zero_raw<T>();
+    const Raw8<T> xb = two ? ldraw(x + cbase + vb * BN_VEC) : zero_raw<T>();
+    Raw8<T> ya = zero_raw<T>(), yb = ya;
     if (relu && y) {
-      ya = ldg16(y + cbase + v * BN_VEC);
-      if (two) yb = ldg16(y + cbase + vb * BN_VEC);
+      ya = ldraw(y + cbase + v * BN_VEC);
+      if (two) yb = ldraw(y + cbase + vb * BN_VEC);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -342,7 +386,7 @@ bn_bwd_stats_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
       unpack8(u ? xb : xa, xv);
       if (dy2) {   // gradient arriving over a second path (residual branch): summed on load instead of by a separate kernel
         float e[8];
-        unpack8(ldg16(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
+        unpack8(ldraw(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
 #pragma unroll
         for (int i = 0; i < 8; ++i) d[i] += e[i];
       }
@@ -367,10 +411,11 @@ bn_bwd_stats_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
 }
 
+template <typename T>
 __device__ __forceinline__ void
-bn_bwd_apply_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
-                    const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
+bn_bwd_apply_body(const T* __restrict__ dy, const T* __restrict__ dy2,
+                    const T* __restrict__ x,
+                    const T* __restrict__ y, T* __restrict__ dx, T* __restrict__ dres,
                     int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma,
                     const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
                     const float* __restrict__ rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -417,13 +462,13 @@ bn_bwd_apply_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
   for (int64_t v = v0 + tid; v < v1; v += 2 * BN_THREADS) {
     const int64_t vb = v + BN_THREADS;
     const bool two = vb < v1;
-    const uint4 da = ldg16(dy + cbase + v * BN_VEC), xa = ldg16(x + cbase + v * BN_VEC);
-    const uint4 db_ = two ? ldg16(dy + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
-    const uint4 xb = two ? ldg16(x + cbase + vb * BN_VEC) : make_uint4(0, 0, 0, 0);
-    uint4 ya = make_uint4(0, 0, 0, 0), yb = ya;
+    const Raw8<T> da = ldraw(dy + cbase + v * BN_VEC), xa = ldraw(x + cbase + v * BN_VEC);
+    const Raw8<T> db_ = two ? ldraw(dy + cbase + vb * BN_VEC) : zero_raw<T>();
+    const Raw8<T> xb = two ? ldraw(x + cbase + vb * BN_VEC) : zero_raw<T>();
+    Raw8<T> ya = zero_raw<T>(), yb = ya;
     if (relu && y) {
-      ya = ldg16(y + cbase + v * BN_VEC);
-      if (two) yb = ldg16(y + cbase + vb * BN_VEC);
+      ya = ldraw(y + cbase + v * BN_VEC);
+      if (two) yb = ldraw(y + cbase + vb * BN_VEC);
     }
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -434,7 +479,7 @@ bn_bwd_apply_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
       unpack8(u ? xb : xa, xv);
       if (dy2) {   // gradient arriving over a second path (residual branch): summed on load instead of by a separate kernel
         float e[8];
-        unpack8(ldg16(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
+        unpack8(ldraw(dy2 + cbase + (u ? vb : v) * BN_VEC), e);
 #pragma unroll
         for (int i = 0; i < 8; ++i) d[i] += e[i];
       }
@@ -449,18 +494,19 @@ bn_bwd_apply_body(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
           for (int i = 0; i < 8; ++i) d[i] = (xv[i] * A[i] + K[i]) > 0.f ? d[i] : 0.f;
         }
       }
-      if (dres) *reinterpret_cast<uint4*>(dres + cbase + vv * BN_VEC) = pack8(d);
+      if (dres) store8(dres + cbase + vv * BN_VEC, d);
       float o[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) o[i] = d[i] * A[i] + xv[i] * B[i] + Cc[i];   // = g*(d - dbeta/M - xhat*dgamma/M)
-      *reinterpret_cast<uint4*>(dx + cbase + vv * BN_VEC) = pack8(o);
+      store8(dx + cbase + vv * BN_VEC, o);
     }
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
+bn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x,
+                    const T* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                     int relu, float* __restrict__ partial) {
   __shared__ float smem[BN_THREADS * 16];
@@ -468,9 +514,10 @@ bn_bwd_stats_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   pdl_trigger();
   bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
 }
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int64_t M,
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x,
+                    const T* __restrict__ y, T* __restrict__ dx, T* __restrict__ dres, int64_t M,
                     int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g) {
@@ -479,9 +526,10 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   pdl_trigger();
   bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
 }
+template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, int64_t M,
+bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x,
+                    const T* __restrict__ y, T* __restrict__ dx, T* __restrict__ dres, int64_t M,
                     int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                     const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
                     float* __restrict__ dbeta, int64_t ld_g) {
@@ -494,7 +542,8 @@ bn_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
 }
 
-extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t C,
+template <typename T>
+static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t C,
                                  int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
                                  const float* save_mean,
                                  const float* save_rstd, int32_t relu, float* dgamma, float* dbeta, int64_t ld_g,
@@ -505,28 +554,29 @@ extern "C" int fb_bn_bwd_stacked(const void* dy, const void* dy2, const void* x,
   FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_bn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
   int S = bn_slices(C, M, ch);
   if (bn_forced_slices(1) > 0) S = bn_forced_slices(1);
-  if (bn_fused_enabled((int64_t)C * M * ch * 2)) {
-    FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
-        (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+  if (bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
+        (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx,
+        (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
-  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_stats_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, 
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, M, ch, S, save_mean, save_rstd, gamma,
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_stats_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, 
+      (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, M, ch, S, save_mean, save_rstd, gamma,
       beta, ld_p, relu, scratch));
   FB_CHECK_CUDA(cudaGetLastError());
-  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_apply_kernel, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)dy2, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)dx,
-      (__nv_bfloat16*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_apply_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
+      (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx,
+      (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
 
 // ---------------------------------------------------------------- im2col / col2im (3x3, pad 1, NHWC, bf16)
 // cols[n][ho][wo][kh][kw][ch]; one thread moves one 16-byte vector (8 channels)
+template <typename T>
 __global__ void __launch_bounds__(256)
-im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ cols, int64_t total_vec, int H, int W,
+im2col3x3_kernel(const T* __restrict__ x, T* __restrict__ cols, int64_t total_vec, int H, int W,
                  int Ho, int Wo, int ch, int stride) {
   // all index arithmetic in 32 bits (64-bit div/mod per vector made this kernel ALU-bound); the host
   // guarantees total_vec < 2^32
@@ -541,28 +591,30 @@ im2col3x3_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict_
     const uint32_t tap = r2 / cv, c8 = r2 - tap * cv;
     const int kh = (int)(tap / 3u), kw = (int)(tap - (tap / 3u) * 3u);
     const int h = (int)ho * stride + kh - 1, w = (int)wo * stride + kw - 1;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (h >= 0 && h < H && w >= 0 && w < W) v = ldg16(x + (((size_t)n * H + h) * W + w) * ch + (size_t)c8 * 8);
-    *reinterpret_cast<uint4*>(cols + (size_t)i * 8) = v;
+    Raw8<T> v = zero_raw<T>();
+    if (h >= 0 && h < H && w >= 0 && w < W) v = ldraw(x + (((size_t)n * H + h) * W + w) * ch + (size_t)c8 * 8);
+    store_raw(cols + (size_t)i * 8, v);
   }
 }
-extern "C" int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+template <typename T>
+static int im2col_impl(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch,
                                       int32_t stride, fb_stream_t stream) {
   FB_REQUIRE(x && cols && n_img >= 1 && H >= 1 && W >= 1 && ch >= 8 && ch % 8 == 0 && (stride == 1 || stride == 2),
-             "fb_im2col3x3_nhwc_bf16: bad arguments (ch must be a multiple of 8)");
+             "fb_im2col3x3_nhwc: bad arguments (ch must be a multiple of 8)");
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   const int64_t total = (int64_t)n_img * Ho * Wo * 9 * (ch / 8);
-  FB_REQUIRE(total < 4294967296LL, "fb_im2col3x3_nhwc_bf16: tensor too large for 32-bit indexing");
+  FB_REQUIRE(total < 4294967296LL, "fb_im2col3x3_nhwc: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
-  FB_CHECK_CUDA(fb_launch_pdl(im2col3x3_kernel, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)cols, total, H, W, Ho, Wo, ch, stride));
+  FB_CHECK_CUDA(fb_launch_pdl(im2col3x3_kernel<T>, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      (const T*)x, (T*)cols, total, H, W, Ho, Wo, ch, stride));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
 
 // dx[n][h][w][c] = sum over taps of dcols[n][ho][wo][kh][kw][c] with h = ho*stride + kh - 1 (gather: no atomics)
+template <typename T>
 __global__ void __launch_bounds__(256)
-col2im3x3_kernel(const __nv_bfloat16* __restrict__ cols, __nv_bfloat16* __restrict__ dx, int64_t total_vec, int H, int W,
+col2im3x3_kernel(const T* __restrict__ cols, T* __restrict__ dx, int64_t total_vec, int H, int W,
                  int Ho, int Wo, int ch, int stride) {
   const uint32_t cv = ch / 8, per_row = cv * (uint32_t)W, per_img = per_row * (uint32_t)H;
   const uint32_t total = (uint32_t)total_vec;
@@ -588,25 +640,61 @@ col2im3x3_kernel(const __nv_bfloat16* __restrict__ cols, __nv_bfloat16* __restri
         const int wo = ww / stride;
         if (wo >= Wo) continue;
         float f[8];
-        unpack8(ldg16(cols + (((((size_t)n * Ho + ho) * Wo + wo) * 3 + kh) * 3 + kw) * ch + (size_t)c8 * 8), f);
+        unpack8(ldraw(cols + (((((size_t)n * Ho + ho) * Wo + wo) * 3 + kh) * 3 + kw) * ch + (size_t)c8 * 8), f);
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[e] += f[e];
       }
     }
-    *reinterpret_cast<uint4*>(dx + (size_t)i * 8) = pack8(acc);
+    store8(dx + (size_t)i * 8, acc);
   }
 }
-extern "C" int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+template <typename T>
+static int col2im_impl(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch,
                                       int32_t stride, fb_stream_t stream) {
   FB_REQUIRE(cols && dx && n_img >= 1 && H >= 1 && W >= 1 && ch >= 8 && ch % 8 == 0 && (stride == 1 || stride == 2),
-             "fb_col2im3x3_nhwc_bf16: bad arguments (ch must be a multiple of 8)");
+             "fb_col2im3x3_nhwc: bad arguments (ch must be a multiple of 8)");
   const int Ho = (H - 1) / stride + 1, Wo = (W - 1) / stride + 1;
   const int64_t total = (int64_t)n_img * H * W * (ch / 8);
   FB_REQUIRE(total < 4294967296LL && (int64_t)n_img * Ho * Wo * 9 * (ch / 8) < 4294967296LL,
-             "fb_col2im3x3_nhwc_bf16: tensor too large for 32-bit indexing");
+             "fb_col2im3x3_nhwc: tensor too large for 32-bit indexing");
   int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
-  FB_CHECK_CUDA(fb_launch_pdl(col2im3x3_kernel, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
-      (const __nv_bfloat16*)cols, (__nv_bfloat16*)dx, total, H, W, Ho, Wo, ch, stride));
+  FB_CHECK_CUDA(fb_launch_pdl(col2im3x3_kernel<T>, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)(0), (cudaStream_t)stream, 
+      (const T*)cols, (T*)dx, total, H, W, Ho, Wo, ch, stride));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
+}
+
+// ---------------------------------------------------------------- C ABI: bf16 and fp32 activation variants
+#define FB_BN_FWD_ARGS                                                                                                      \
+  const void *x, const void *res, void *y, int32_t C, int64_t M, int32_t ch, const float *gamma, const float *beta,        \
+      int64_t ld_p, float *running_mean, float *running_var, int64_t ld_r, const float *active, float momentum, float eps, \
+      int32_t relu, int32_t training, float *save_mean, float *save_rstd, float *scratch, float *num_batches_tracked,      \
+      int64_t ld_n, fb_stream_t stream
+#define FB_BN_FWD_PASS                                                                                                      \
+  x, res, y, C, M, ch, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu, training,          \
+      save_mean, save_rstd, scratch, num_batches_tracked, ld_n, stream
+extern "C" int fb_bn_fwd_stacked(FB_BN_FWD_ARGS) { return bn_fwd_impl<__nv_bfloat16>(FB_BN_FWD_PASS); }
+extern "C" int fb_bn_fwd_stacked_f32(FB_BN_FWD_ARGS) { return bn_fwd_impl<float>(FB_BN_FWD_PASS); }
+#define FB_BN_BWD_ARGS                                                                                                      \
+  const void *dy, const void *dy2, const void *x, const void *y, void *dx, void *dres, int32_t C, int64_t M, int32_t ch,   \
+      const float *gamma, const float *beta, int64_t ld_p, const float *save_mean, const float *save_rstd, int32_t relu,   \
+      float *dgamma, float *dbeta, int64_t ld_g, float *scratch, fb_stream_t stream
+#define FB_BN_BWD_PASS dy, dy2, x, y, dx, dres, C, M, ch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g, scratch, stream
+extern "C" int fb_bn_bwd_stacked(FB_BN_BWD_ARGS) { return bn_bwd_impl<__nv_bfloat16>(FB_BN_BWD_PASS); }
+extern "C" int fb_bn_bwd_stacked_f32(FB_BN_BWD_ARGS) { return bn_bwd_impl<float>(FB_BN_BWD_PASS); }
+extern "C" int fb_im2col3x3_nhwc_bf16(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                                      fb_stream_t stream) {
+  return im2col_impl<__nv_bfloat16>(x, cols, n_img, H, W, ch, stride, stream);
+}
+extern "C" int fb_im2col3x3_nhwc_f32(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                                     fb_stream_t stream) {
+  return im2col_impl<float>(x, cols, n_img, H, W, ch, stride, stream);
+}
+extern "C" int fb_col2im3x3_nhwc_bf16(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                                      fb_stream_t stream) {
+  return col2im_impl<__nv_bfloat16>(cols, dx, n_img, H, W, ch, stride, stream);
+}
+extern "C" int fb_col2im3x3_nhwc_f32(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                                     fb_stream_t stream) {
+  return col2im_impl<float>(cols, dx, n_img, H, W, ch, stride, stream);
 }

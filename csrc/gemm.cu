@@ -592,6 +592,9 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---------------------------------------------------------------- host side
+// fp32 operands travel as plain FLOAT32 tensor maps; the tensor core reads sign, exponent and the top 10 mantissa bits
+// (measured: results match the truncated-operand product to fp32 accumulation order; TFLOAT32 maps gave no accuracy gain)
+#define FB_TF32_LOAD_TYPE CU_TENSOR_MAP_DATA_TYPE_FLOAT32
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -622,7 +625,7 @@ static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t r
   cuuint32_t estr[4] = {1, 1, 1, 1};
   FB_REQUIRE((strides[0] % 16) == 0 && (strides[1] % 16) == 0 && (strides[2] % 16) == 0 && ((uintptr_t)base % 16) == 0,
              "grouped GEMM operands need 16-byte aligned base pointers and strides");
-  CUresult r = enc(m, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims,
+  CUresult r = enc(m, tf32 ? FB_TF32_LOAD_TYPE : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    (tf32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -882,7 +885,7 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
     cuuint64_t strides[3] = {(cuuint64_t)p->cin * es, (cuuint64_t)p->cin * p->W * es, (cuuint64_t)p->cin * p->W * p->H * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
     cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
-    CUresult r = enc(&tmA, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+    CUresult r = enc(&tmA, tf32 ? FB_TF32_LOAD_TYPE : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv input) failed with code %d", (int)r);
@@ -894,7 +897,7 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
     cuuint64_t strides[3] = {inner * es, (cuuint64_t)(p->G > 1 ? p->w_gs : inner * rows) * es, inner * rows * p->G * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(pair ? bn_cols / 2 : bn_cols), 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(&tmB, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
+    CUresult r = enc(&tmB, tf32 ? FB_TF32_LOAD_TYPE : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->w), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (conv weights) failed with code %d", (int)r);
@@ -1012,7 +1015,7 @@ static int conv3x3_wgrad_impl(const FbConv3x3Wgrad* p, fb_stream_t stream, const
     cuuint64_t strides[3] = {(cuuint64_t)p->cin * es, (cuuint64_t)p->cin * p->W * es, (cuuint64_t)p->cin * p->W * p->H * es};
     cuuint32_t box[4] = {(cuuint32_t)kblk, (cuuint32_t)(Wo * s), (cuuint32_t)(bh * s), (cuuint32_t)bn};
     cuuint32_t estr[4] = {1, (cuuint32_t)s, (cuuint32_t)s, 1};
-    CUresult r = enc(&tmB, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
+    CUresult r = enc(&tmB, tf32 ? FB_TF32_LOAD_TYPE : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(p->x), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, tf32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : swizzle_for(row_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (wgrad input) failed with code %d", (int)r);

@@ -252,14 +252,41 @@ extern "C" int fb_eval_counts(const float* logits, const int64_t* labels, int64_
 //   Wm  bf16 [cout][k*k*cin_pad]   ((kh,kw,cin) order = the im2col column order, zero-padded input channels)
 //   WmT bf16 [k*k*cin_pad][cout]   (K-major operand for the dgrad GEMM), optional
 // Segment table (int64 x 8 per layer): src_off, cout, cin, cin_pad, k, dst_off, dstT_off (-1: none), n = cout*k*k*cin_pad
+// staged GEMM operands are bf16 (kind::f16 path) or fp32 (kind::tf32 path): ST is the staged element type
+__device__ __forceinline__ void stage_st1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+__device__ __forceinline__ void stage_st1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void stage_st4(__nv_bfloat16* p, float a, float b, float c, float d) {
+  uint2 o;
+  *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(a, b);
+  *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(c, d);
+  *reinterpret_cast<uint2*>(p) = o;
+}
+__device__ __forceinline__ void stage_st4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void stage_st8(__nv_bfloat16* p, const float4& a, const float4& b) {
+  uint4 o;
+  __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&o);
+  h2[0] = __floats2bfloat162_rn(a.x, a.y);
+  h2[1] = __floats2bfloat162_rn(a.z, a.w);
+  h2[2] = __floats2bfloat162_rn(b.x, b.y);
+  h2[3] = __floats2bfloat162_rn(b.z, b.w);
+  *reinterpret_cast<uint4*>(p) = o;
+}
+__device__ __forceinline__ void stage_st8(float* p, const float4& a, const float4& b) {
+  reinterpret_cast<float4*>(p)[0] = a;
+  reinterpret_cast<float4*>(p)[1] = b;
+}
+
+template <typename ST>
 __global__ void __launch_bounds__(256)
-stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16* __restrict__ stage, int64_t stage_ld,
+stage_weights_kernel(const float* __restrict__ arena, int64_t ld, ST* __restrict__ stage, int64_t stage_ld,
                      const int64_t* __restrict__ table, int n_layers) {
   pdl_wait();      // programmatic dependent launch: see common.cuh
   pdl_trigger();
   const int c = blockIdx.y;
   const float* row = arena + (size_t)c * ld;
-  __nv_bfloat16* out = stage + (size_t)c * stage_ld;
+  ST* out = stage + (size_t)c * stage_ld;
   for (int l = blockIdx.z; l < n_layers; l += gridDim.z) {
     const int64_t* t = table + (size_t)l * 8;
     const int64_t src = t[0], dst = t[5], dstT = t[6];
@@ -269,16 +296,9 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
         (stage_ld & 7) == 0) {
       // plain fp32 -> bf16 cast of a linear layer / 1x1 conv: 32-byte loads, 16-byte stores
       const float4* s4 = reinterpret_cast<const float4*>(row + src);
-      uint4* d4 = reinterpret_cast<uint4*>(out + dst);
       for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < (n >> 3); v += gridDim.x * blockDim.x) {
         const float4 a = __ldg(s4 + 2 * v), b = __ldg(s4 + 2 * v + 1);
-        uint4 o;
-        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&o);
-        h2[0] = __floats2bfloat162_rn(a.x, a.y);
-        h2[1] = __floats2bfloat162_rn(a.z, a.w);
-        h2[2] = __floats2bfloat162_rn(b.x, b.y);
-        h2[3] = __floats2bfloat162_rn(b.z, b.w);
-        d4[v] = o;
+        stage_st8(out + dst + (size_t)v * 8, a, b);
       }
       continue;
     }
@@ -310,10 +330,7 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
             const int ci4 = i & 7, q = i >> 3;
             const int co = q / KK, tap = q - co * KK;
             const float* tt = tile + co * 289 + ci4 * 36 + tap;
-            uint2 o;
-            *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(tt[0], tt[9]);
-            *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(tt[18], tt[27]);
-            *reinterpret_cast<uint2*>(out + dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + ci4 * 4) = o;
+            stage_st4(out + dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + ci4 * 4, tt[0], tt[9], tt[18], tt[27]);
           }
           if (dstT >= 0) {
 #pragma unroll 3
@@ -321,10 +338,7 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
               const int co4 = i & 7, q = i >> 3;
               const int ci = q & 31, tap = q >> 5;
               const float* tt = tile + co4 * 4 * 289 + ci * 9 + tap;
-              uint2 o;
-              *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(tt[0], tt[289]);
-              *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(tt[578], tt[867]);
-              *reinterpret_cast<uint2*>(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + co4 * 4) = o;
+              stage_st4(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + co4 * 4, tt[0], tt[289], tt[578], tt[867]);
             }
           }
           continue;
@@ -343,14 +357,14 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
         for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {                 // Wm: a warp writes 32 input channels
           const int co = q / KK, tap = q - co * KK;
           if (co0 + co < cout && ci0 + lane < cinp)
-            out[dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + lane] = __float2bfloat16_rn(tile[co * 289 + lane * 9 + tap]);
+            stage_st1(out + dst + ((size_t)(co0 + co) * KK + tap) * cinp + ci0 + lane, tile[co * 289 + lane * 9 + tap]);
         }
         if (dstT >= 0) {
 #pragma unroll 12
           for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {               // WmT: a warp writes 32 output channels
             const int tap = q >> 5, ci = q & 31;
             if (co0 + lane < cout && ci0 + ci < cinp)
-              out[dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane] = __float2bfloat16_rn(tile[lane * 289 + ci * 9 + tap]);
+              stage_st1(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane, tile[lane * 289 + ci * 9 + tap]);
           }
         }
       }
@@ -360,24 +374,32 @@ stage_weights_kernel(const float* __restrict__ arena, int64_t ld, __nv_bfloat16*
       const int co = e / kdim, r = e - co * kdim;
       const int tap = r / cinp, ci = r - tap * cinp;
       const float v = ci < cin ? row[src + ((size_t)co * cin + ci) * kk + tap] : 0.f;
-      const __nv_bfloat16 h = __float2bfloat16_rn(v);
-      out[dst + e] = h;
-      if (dstT >= 0) out[dstT + (size_t)r * cout + co] = h;
+      stage_st1(out + dst + e, v);
+      if (dstT >= 0) stage_st1(out + dstT + (size_t)r * cout + co, v);
     }
   }
 }
-extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage, int64_t stage_ld,
-                                     const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
+template <typename ST>
+static int stage_conv_weights_impl(const float* arena, int64_t ld, int32_t C, void* stage, int64_t stage_ld,
+                                   const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
   FB_REQUIRE(arena && stage && table_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_stage_conv_weights: bad arguments");
   int gx = (max_n + 255) / 256;
   const int gx_cap = max_n >= (1 << 18) ? 64 : 16;   // big linear layers: more CTAs per (client, layer) slice
   if (gx > gx_cap) gx = gx_cap;
   if (gx < 1) gx = 1;
   int gz = n_layers < 64 ? n_layers : 64;
-  FB_CHECK_CUDA(fb_launch_pdl(stage_weights_kernel, dim3(dim3(gx, C, gz)), dim3(256), (size_t)(0), (cudaStream_t)stream, arena, ld, (__nv_bfloat16*)stage, stage_ld,
+  FB_CHECK_CUDA(fb_launch_pdl(stage_weights_kernel<ST>, dim3(dim3(gx, C, gz)), dim3(256), (size_t)(0), (cudaStream_t)stream, arena, ld, (ST*)stage, stage_ld,
                                                                          table_dev, n_layers));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
+}
+extern "C" int fb_stage_conv_weights(const float* arena, int64_t ld, int32_t C, void* stage, int64_t stage_ld,
+                                     const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
+  return stage_conv_weights_impl<__nv_bfloat16>(arena, ld, C, stage, stage_ld, table_dev, n_layers, max_n, stream);
+}
+extern "C" int fb_stage_conv_weights_f32(const float* arena, int64_t ld, int32_t C, void* stage, int64_t stage_ld,
+                                         const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream) {
+  return stage_conv_weights_impl<float>(arena, ld, C, stage, stage_ld, table_dev, n_layers, max_n, stream);
 }
 
 // ---------------------------------------------------------------- fused optimizer step + re-staging (plain SGD)
@@ -416,9 +438,10 @@ __device__ __forceinline__ int rs_tiles(const RsSeg& s) {
 
 // grid (X, C): the CTAs of a client walk ONE flat list of tiles over all segments (prefix of per-segment tile counts in
 // shared memory), so small segments cost a tile, not a grid slice of mostly empty CTAs
+template <typename ST>
 __global__ void __launch_bounds__(256)
 sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, int64_t ld, const float* __restrict__ scratch,
-                   int64_t scratch_ld, __nv_bfloat16* __restrict__ stage, int64_t stage_ld, const int64_t* __restrict__ table,
+                   int64_t scratch_ld, ST* __restrict__ stage, int64_t stage_ld, const int64_t* __restrict__ table,
                    int n_layers, const float* __restrict__ lr_dev) {
   __shared__ float tile[32 * 289];
   __shared__ int tstart[RS_MAX_SEGS + 1];
@@ -440,7 +463,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
   float* row = arena + (size_t)c * ld;
   const float* grow = grads + (size_t)c * ld;
   const float* srow = scratch ? scratch + (size_t)c * scratch_ld : nullptr;
-  __nv_bfloat16* out = stage ? stage + (size_t)c * stage_ld : nullptr;
+  ST* out = stage ? stage + (size_t)c * stage_ld : nullptr;
   for (int gt = blockIdx.x; gt < total; gt += gridDim.x) {
     int lo = 0, hi = n_layers - 1;                                      // last segment with tstart <= gt
     while (lo < hi) {
@@ -454,7 +477,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
     if (sg.path == 0) {
       float4* w4 = reinterpret_cast<float4*>(row + src);
       const float4* g4 = reinterpret_cast<const float4*>(grow + src);
-      uint4* d4 = dst >= 0 ? reinterpret_cast<uint4*>(out + dst) : nullptr;
+      ST* d8 = dst >= 0 ? out + dst : nullptr;
       const int v0 = tl * (RS_VEC_TILE / 8), v1 = min(n >> 3, v0 + RS_VEC_TILE / 8);
       for (int v = v0 + threadIdx.x; v < v1; v += 256) {
         float4 a = w4[2 * v], b = w4[2 * v + 1];
@@ -462,15 +485,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
         a.x -= lr * ga.x; a.y -= lr * ga.y; a.z -= lr * ga.z; a.w -= lr * ga.w;
         b.x -= lr * gb.x; b.y -= lr * gb.y; b.z -= lr * gb.z; b.w -= lr * gb.w;
         if (lr != 0.f) { w4[2 * v] = a; w4[2 * v + 1] = b; }
-        if (d4) {
-          uint4 o;
-          __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&o);
-          h2[0] = __floats2bfloat162_rn(a.x, a.y);
-          h2[1] = __floats2bfloat162_rn(a.z, a.w);
-          h2[2] = __floats2bfloat162_rn(b.x, b.y);
-          h2[3] = __floats2bfloat162_rn(b.z, b.w);
-          d4[v] = o;
-        }
+        if (d8) stage_st8(d8 + (size_t)v * 8, a, b);
       }
     } else if (sg.path == 1) {
       constexpr int KK = 9, RUN = 32 * KK;
@@ -502,10 +517,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
           float* t = tile + co * 289 + ci4 * 36 + tap;
           const float w0 = t[0] - lr * g.x, w1 = t[9] - lr * g.y, w2 = t[18] - lr * g.z, w3 = t[27] - lr * g.w;
           t[0] = w0; t[9] = w1; t[18] = w2; t[27] = w3;
-          uint2 o;
-          *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(w0, w1);
-          *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(w2, w3);
-          *reinterpret_cast<uint2*>(out + dst + gi) = o;
+          stage_st4(out + dst + gi, w0, w1, w2, w3);
         }
         __syncthreads();
         if (dstT >= 0) {
@@ -514,10 +526,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
             const int co4 = i & 7, q = i >> 3;
             const int ci = q & 31, tap = q >> 5;
             const float* t = tile + co4 * 4 * 289 + ci * 9 + tap;
-            uint2 o;
-            *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(t[0], t[289]);
-            *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(t[578], t[867]);
-            *reinterpret_cast<uint2*>(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + co4 * 4) = o;
+            stage_st4(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + co4 * 4, t[0], t[289], t[578], t[867]);
           }
         }
         if (lr != 0.f) {
@@ -549,7 +558,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
             w -= lr * __ldg(srow + goff + gi);
             tile[co * 289 + lane * 9 + tap] = w;
           }
-          out[dst + gi] = __float2bfloat16_rn(w);
+          stage_st1(out + dst + gi, w);
         }
       }
       __syncthreads();
@@ -558,7 +567,7 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
         for (int q = threadIdx.x >> 5; q < 32 * KK; q += 8) {               // WmT: a warp writes 32 output channels
           const int tap = q >> 5, ci = q & 31;
           if (co0 + lane < cout && ci0 + ci < cinp)
-            out[dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane] = __float2bfloat16_rn(tile[lane * 289 + ci * 9 + tap]);
+            stage_st1(out + dstT + ((size_t)tap * cinp + ci0 + ci) * cout + co0 + lane, tile[lane * 289 + ci * 9 + tap]);
         }
       }
       if (lr != 0.f) {
@@ -583,17 +592,17 @@ sgd_restage_kernel(float* __restrict__ arena, const float* __restrict__ grads, i
           if (lr != 0.f) row[wi] = w;
         }
         if (dst >= 0) {
-          const __nv_bfloat16 h = __float2bfloat16_rn(w);
-          out[dst + e] = h;
-          if (dstT >= 0) out[dstT + (size_t)r * cout + co] = h;
+          stage_st1(out + dst + e, w);
+          if (dstT >= 0) stage_st1(out + dstT + (size_t)r * cout + co, w);
         }
       }
     }
   }
 }
-extern "C" int fb_sgd_restage(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
-                              void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
-                              const float* lr_dev, fb_stream_t stream) {
+template <typename ST>
+static int sgd_restage_impl(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                            void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                            const float* lr_dev, fb_stream_t stream) {
   FB_REQUIRE(arena && grads && table_dev && lr_dev && C >= 1 && C <= 65535 && n_layers >= 1, "fb_sgd_restage: bad arguments");
   FB_REQUIRE(n_layers <= RS_MAX_SEGS, "fb_sgd_restage: at most %d segments", RS_MAX_SEGS);
   // CTAs per client: enough to put ~16 CTAs on every SM overall, at least one per ~8K elements, at most 256
@@ -602,9 +611,21 @@ extern "C" int fb_sgd_restage(float* arena, const float* grads, int64_t ld, int3
   if (gx > by_work) gx = by_work;
   if (gx > 256) gx = 256;
   if (gx < 1) gx = 1;
-  FB_CHECK_CUDA(fb_launch_pdl(sgd_restage_kernel, dim3(gx, C), dim3(256), (size_t)0, (cudaStream_t)stream, arena, grads, ld, scratch,
-                              scratch_ld, (__nv_bfloat16*)stage, stage_ld, table_dev, n_layers, lr_dev));
+  FB_CHECK_CUDA(fb_launch_pdl(sgd_restage_kernel<ST>, dim3(gx, C), dim3(256), (size_t)0, (cudaStream_t)stream, arena, grads, ld, scratch,
+                              scratch_ld, (ST*)stage, stage_ld, table_dev, n_layers, lr_dev));
   return FB_OK;
+}
+extern "C" int fb_sgd_restage(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                              void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                              const float* lr_dev, fb_stream_t stream) {
+  return sgd_restage_impl<__nv_bfloat16>(arena, grads, ld, C, scratch, scratch_ld, stage, stage_ld, table_dev, n_layers, total_elems,
+                                         lr_dev, stream);
+}
+extern "C" int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                                  void* stage, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                                  const float* lr_dev, fb_stream_t stream) {
+  return sgd_restage_impl<float>(arena, grads, ld, C, scratch, scratch_ld, stage, stage_ld, table_dev, n_layers, total_elems, lr_dev,
+                                 stream);
 }
 
 // ---------------------------------------------------------------- weight-gradient un-staging (one launch per step)

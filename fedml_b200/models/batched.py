@@ -358,27 +358,29 @@ class NativeBackend(TorchBackend):
     # fp32 partial buffers + a separate sum, for A/B timing)
     grads_prezeroed = os.environ.get("FB_PREZERO_GRADS", "1") != "0"
 
+    _ACT = (torch.bfloat16, torch.float32)      # activation dtypes the native kernels are instantiated for
+
     def im2col3x3(self, x, stride):
-        if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
+        if x.dtype in self._ACT and x.shape[-1] % 8 == 0:
             return self.ops.im2col3x3(x, stride)
         self._fb("im2col")
         return super().im2col3x3(x, stride)
 
     def col2im3x3(self, dcols, B, H, W, ch, stride):
-        if dcols.dtype == torch.bfloat16 and ch % 8 == 0:
+        if dcols.dtype in self._ACT and ch % 8 == 0:
             return self.ops.col2im3x3(dcols, B, H, W, ch, stride)
         self._fb("col2im")
         return super().col2im3x3(dcols, B, H, W, ch, stride)
 
     def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
-        if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
+        if x.dtype in self._ACT and self._bn_ok(x.shape[-1]):
             return self.ops.bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
         self._fb("bn_fwd")
         return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
 
     def bn_bwd(self, dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, had_res=True, dgamma_out=None,
                dbeta_out=None):
-        if x.dtype == torch.bfloat16 and self._bn_ok(x.shape[-1]):
+        if x.dtype in self._ACT and self._bn_ok(x.shape[-1]):
             skip_y = relu and not had_res and beta is not None   # mask recomputed from x: one stream less
             d1, d2 = dy if isinstance(dy, tuple) else (dy, None)
             return self.ops.bn_bwd_stacked(d1, x, None if skip_y else y, gamma, mean, rstd, relu, want_dres, beta=beta,
@@ -722,14 +724,16 @@ class BatchedResNet(BatchedModel):
     def prepare(self, W):
         dt = self.be.dtype
         tr = self.be.want_transposed_weights
-        if isinstance(self.be, NativeBackend) and dt == torch.bfloat16 and getattr(W, "arena", None) is not None:
+        if isinstance(self.be, NativeBackend) and dt in NativeBackend._ACT and getattr(W, "arena", None) is not None:
             return self._prepare_staged(W)
         Wm = {c.name: c.prep(W, dt, tr) for c in self.convs}
         Wm["fc"] = W["fc.weight"].to(dt)
         return Wm
 
     def _prepare_staged(self, W):
-        """All conv / fc weights of all clients -> bf16 GEMM operands with ONE kernel launch."""
+        """All conv / fc weights of all clients -> GEMM operands in the compute dtype with ONE kernel launch.
+        With fp32 (TF32) compute the 1x1-convolution and fc weights already ARE the GEMM operands ([cout][cin] rows of
+        the arena, 16-byte aligned segments): they are used in place and only k x k / channel-padded layers are staged."""
         arena, layout = W.arena, W.layout
         C = arena.shape[0]
         key = (arena.data_ptr(), C)
@@ -737,8 +741,13 @@ class BatchedResNet(BatchedModel):
         if st is None or st["key"] != key:
             rows, off, plan = [], 0, {}
             al = lambda v: (v + 7) // 8 * 8   # noqa: E731  16-byte aligned segments for TMA
+            fp32 = self.be.dtype == torch.float32
+            in_place = {}
             for c in self.convs:
                 seg = layout.by_name[c.wname]
+                if fp32 and c.k == 1 and c.cin == c.cin_real and arena.stride(0) % 4 == 0:
+                    in_place[c.name] = (W[c.wname].view(C, c.cout, c.cin), None)
+                    continue
                 n = c.cout * c.k * c.k * c.cin
                 dst = off; off = al(off + n)
                 dstT = -1
@@ -748,16 +757,20 @@ class BatchedResNet(BatchedModel):
                 plan[c.name] = (dst, dstT, c.cout, c.k * c.k * c.cin)
             seg = layout.by_name["fc.weight"]
             n = self.ncls * self.feat_dim
-            rows.append([seg.offset, self.ncls, self.feat_dim, self.feat_dim, 1, off, -1, n])
-            plan["fc"] = (off, -1, self.ncls, self.feat_dim)
-            off = al(off + n)
-            stage = torch.zeros((C, off), dtype=torch.bfloat16, device=arena.device)
+            if fp32 and arena.stride(0) % 4 == 0:
+                in_place["fc"] = W["fc.weight"]
+            else:
+                rows.append([seg.offset, self.ncls, self.feat_dim, self.feat_dim, 1, off, -1, n])
+                plan["fc"] = (off, -1, self.ncls, self.feat_dim)
+                off = al(off + n)
+            stage = torch.zeros((C, off), dtype=self.be.dtype, device=arena.device)
             table = torch.tensor(rows, dtype=torch.int64).to(arena.device)
             views = {}
             for name, (dst, dstT, cout, kdim) in plan.items():
                 wm = stage[:, dst:dst + cout * kdim].view(C, cout, kdim)
                 wt = stage[:, dstT:dstT + cout * kdim].view(C, kdim, cout) if dstT >= 0 else None
                 views[name] = wm if name == "fc" else (wm, wt)
+            views.update(in_place)
             st = self._stage = {"key": key, "stage": stage, "table": table, "views": views, "n": len(rows),
                                 "max_n": max(r[7] for r in rows)}
         if not (getattr(self, "_stage_fresh", False) and st.get("fresh_key") == key):
@@ -778,7 +791,7 @@ class BatchedResNet(BatchedModel):
         """Stage the current weights now (round start, after the global model was written into the arena) and mark
         the staged copy as current; it stays current while only the fused step modifies the weights."""
         self._stage_fresh = False
-        if isinstance(self.be, NativeBackend) and self.be.dtype == torch.bfloat16 and getattr(W, "arena", None) is not None:
+        if isinstance(self.be, NativeBackend) and self.be.dtype in NativeBackend._ACT and getattr(W, "arena", None) is not None:
             self._prepare_staged(W)
             self._stage["fresh_key"] = self._stage["key"]
             self._stage_fresh = True

@@ -276,7 +276,7 @@ def _bn_fused(x) -> bool:
     """Mirror of bn_fused_enabled() in csrc/conv.cu (stats + apply in one launch for large layers)."""
     if _BN_FUSED_ENV is not None:
         return _BN_FUSED_ENV != "0"
-    return x.numel() * 2 >= 48 << 20
+    return x.numel() * x.element_size() >= 48 << 20
 
 
 def _scratch_for(device, n_floats):
@@ -298,7 +298,8 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
     mean = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     rstd = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
-    check(lib().fb_bn_fwd_stacked(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)), i32(Cn),
+    fn = lib().fb_bn_fwd_stacked_f32 if x.dtype == torch.float32 else lib().fb_bn_fwd_stacked
+    check(fn(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)), i32(Cn),
                                   i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(rm)),
                                   vp(ptr(rv)), i64(rm.stride(0)), vp(ptr(active)), f32(momentum), f32(eps),
                                   i32(int(relu)), i32(int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
@@ -322,7 +323,8 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgam
     dbeta = dbeta_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     ld_g = dgamma.stride(0) if Cn > 1 else max(dgamma.stride(0), ch)
     scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
-    check(lib().fb_bn_bwd_stacked(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
+    fn = lib().fb_bn_bwd_stacked_f32 if x.dtype == torch.float32 else lib().fb_bn_bwd_stacked
+    check(fn(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
                                   i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
                                   vp(ptr(rstd)), i32(int(relu)), vp(ptr(dgamma)), vp(ptr(dbeta)), i64(ld_g), vp(ptr(scratch)),
                                   vp(stream_ptr(x.device))), "bn_bwd_stacked")
@@ -338,7 +340,8 @@ def im2col3x3(x, stride):
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     x = x.contiguous()
     cols = torch.empty((Cn, B * Ho * Wo, 9 * ch), dtype=x.dtype, device=x.device)
-    check(lib().fb_im2col3x3_nhwc_bf16(vp(ptr(x)), vp(ptr(cols)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
+    fn = lib().fb_im2col3x3_nhwc_f32 if x.dtype == torch.float32 else lib().fb_im2col3x3_nhwc_bf16
+    check(fn(vp(ptr(x)), vp(ptr(cols)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
                                        vp(stream_ptr(x.device))), "im2col3x3")
     count_launch()
     return cols
@@ -348,7 +351,8 @@ def col2im3x3(dcols, B, H, W, ch, stride):
     Cn = dcols.shape[0]
     dcols = dcols.contiguous()
     dx = torch.empty((Cn, B, H, W, ch), dtype=dcols.dtype, device=dcols.device)
-    check(lib().fb_col2im3x3_nhwc_bf16(vp(ptr(dcols)), vp(ptr(dx)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
+    fn = lib().fb_col2im3x3_nhwc_f32 if dcols.dtype == torch.float32 else lib().fb_col2im3x3_nhwc_bf16
+    check(fn(vp(ptr(dcols)), vp(ptr(dx)), i32(Cn * B), i32(H), i32(W), i32(ch), i32(stride),
                                        vp(stream_ptr(dcols.device))), "col2im3x3")
     count_launch()
     return dx
@@ -499,7 +503,8 @@ def gram_bf16(hi: torch.Tensor, lo: Optional[torch.Tensor] = None, split: int = 
 
 def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Tensor, n_layers: int, max_n: int):
     """arena fp32 [C, ld] -> stage bf16 [C, stage_ld] following the int64 [n_layers, 8] device table."""
-    check(lib().fb_stage_conv_weights(vp(ptr(arena)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(stage)),
+    fn = lib().fb_stage_conv_weights_f32 if stage.dtype == torch.float32 else lib().fb_stage_conv_weights
+    check(fn(vp(ptr(arena)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(stage)),
                                       i64(stage.stride(0)), vp(ptr(table)), i32(n_layers), i32(max_n),
                                       vp(stream_ptr(arena.device))), "stage_conv_weights")
     count_launch()
@@ -508,7 +513,8 @@ def stage_conv_weights(arena: torch.Tensor, stage: torch.Tensor, table: torch.Te
 def sgd_restage(arena: torch.Tensor, grads: torch.Tensor, scratch: Optional[torch.Tensor], stage: Optional[torch.Tensor],
                 table: torch.Tensor, n_layers: int, max_n: int, lr: torch.Tensor):
     """Plain-SGD step on every listed segment fused with re-staging the bf16 GEMM operands (csrc/train.cu)."""
-    check(lib().fb_sgd_restage(vp(ptr(arena)), vp(ptr(grads)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(scratch)),
+    fn = lib().fb_sgd_restage_f32 if (stage is not None and stage.dtype == torch.float32) else lib().fb_sgd_restage
+    check(fn(vp(ptr(arena)), vp(ptr(grads)), i64(arena.stride(0)), i32(arena.shape[0]), vp(ptr(scratch)),
                                i64(scratch.stride(0) if scratch is not None else 0), vp(ptr(stage)),
                                i64(stage.stride(0) if stage is not None else 0), vp(ptr(table)), i32(n_layers), i32(max_n),
                                vp(ptr(lr)), vp(stream_ptr(arena.device))), "sgd_restage")

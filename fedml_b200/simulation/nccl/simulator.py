@@ -184,7 +184,8 @@ class NCCLSimulator:
             os.environ.setdefault("FB_BN_FUSED", "0")
         if self.custom_trainer is None and bool(getattr(args, "batched_clients", True)):
             if self.cuda:
-                dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "fp16": torch.float16}[
+                # "tf32" / "fp32": fp32 activations and weights in HBM, TF32 tensor-core products (the reference's precision)
+                dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "tf32": torch.float32, "fp16": torch.float16}[
                     str(getattr(args, "compute_dtype", "bf16")).lower()]
                 backend = NativeBackend(dtype)
             else:
