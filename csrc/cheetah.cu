@@ -22,11 +22,11 @@ __device__ __forceinline__ void dp_signal_wait(uint32_t* const* peer_flags, int 
     __threadfence_system();
     st_release_sys(peer_flags[q] + ((size_t)phase * G + rank) * FB_ROUND_MAX_BLOCKS + block, epoch);
     const uint32_t* mine = peer_flags[rank] + ((size_t)phase * G + q) * FB_ROUND_MAX_BLOCKS + block;
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-    }
+    fb_spin_wait_ge<true>(mine, epoch, 1u + (uint32_t)phase, (uint32_t)q);     // bounded: see common.cuh
   }
   __syncthreads();
 }
+FB_DEFINE_SPIN_API(fb_dp)
 
 __device__ void dp_body(const FbDpStepParams& p, int block, int nblocks) {
   const int G = p.G, rank = p.rank;

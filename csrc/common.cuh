@@ -10,6 +10,7 @@
 #define FB_ERR_ARG -1
 #define FB_ERR_CUDA -2
 #define FB_ERR_LIMIT -3
+#define FB_ERR_TIMEOUT -4
 
 void fb_set_error(const char* fmt, ...);
 
@@ -165,6 +166,69 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+
+// ---------------------------------------------------------------- bounded spins on flags written by other ranks / blocks
+// Every wait on a flag that another GPU (or another block) writes is bounded by the global nanosecond timer: when the
+// writer never shows up (a crashed rank, a launch that was never made) the waiter records {code, who, target, block} in
+// a device-side error record, gives up and lets the kernel run to completion on whatever data it has, so the GPU is
+// released; every later wait of the same launch bails out at its next timer check.  The host reads (and clears) the
+// record after its next synchronisation point (fb_*_spin_status) and turns it into FB_ERR_TIMEOUT.  One record per
+// translation unit that spins (round.cu, cheetah.cu); FB_DEFINE_SPIN_API(prefix) emits its two host accessors.
+#ifdef __CUDACC__
+static __device__ unsigned g_fb_spin_err[4];                                   // code (0 = none), who, target, block
+static __device__ unsigned long long g_fb_spin_timeout_ns = 20000000000ull;   // 20 s unless the host sets it
+__device__ __forceinline__ unsigned long long fb_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ bool fb_spin_failed() { return *reinterpret_cast<volatile unsigned*>(&g_fb_spin_err[0]) != 0u; }
+// wait until *flag >= target (wrap-around safe); SYS: the flag lives in memory another GPU writes.  false on time-out.
+template <bool SYS>
+__device__ __forceinline__ bool fb_spin_wait_ge(const uint32_t* flag, uint32_t target, uint32_t code, uint32_t who) {
+  uint32_t polls = 0;
+  unsigned long long t0 = 0;
+  while ((int32_t)((SYS ? ld_acquire_sys(flag) : ld_acquire_gpu(flag)) - target) < 0) {
+    if ((++polls & 0xFFu) == 0u) {
+      const unsigned long long now = fb_globaltimer();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > g_fb_spin_timeout_ns || fb_spin_failed()) {
+        if (atomicCAS(&g_fb_spin_err[0], 0u, code) == 0u) {
+          g_fb_spin_err[1] = who;
+          g_fb_spin_err[2] = target;
+          g_fb_spin_err[3] = blockIdx.x;
+          __threadfence();
+        }
+        return false;
+      }
+    }
+  }
+  return true;
+}
+#define FB_DEFINE_SPIN_API(prefix)                                                                                          \
+  extern "C" int prefix##_set_spin_timeout_ms(int64_t ms) {                                                                 \
+    unsigned long long ns = (unsigned long long)(ms < 1 ? 1 : ms) * 1000000ull;                                            \
+    FB_CHECK_CUDA(cudaMemcpyToSymbol(g_fb_spin_timeout_ns, &ns, sizeof(ns)));                                              \
+    return FB_OK;                                                                                                           \
+  }                                                                                                                         \
+  /* out4 = {code, who, target, block}; synchronises with the device; clears the record when `clear`; returns             \
+     FB_ERR_TIMEOUT when a wait gave up since the last clear */                                                            \
+  extern "C" int prefix##_spin_status(uint32_t* out4, int32_t clear) {                                                      \
+    unsigned h[4] = {0, 0, 0, 0};                                                                                           \
+    FB_CHECK_CUDA(cudaMemcpyFromSymbol(h, g_fb_spin_err, sizeof(h)));                                                      \
+    if (out4) for (int i = 0; i < 4; ++i) out4[i] = h[i];                                                                   \
+    if (h[0] != 0 && clear) {                                                                                               \
+      unsigned z[4] = {0, 0, 0, 0};                                                                                         \
+      FB_CHECK_CUDA(cudaMemcpyToSymbol(g_fb_spin_err, z, sizeof(z)));                                                      \
+    }                                                                                                                       \
+    if (h[0] != 0) {                                                                                                        \
+      fb_set_error(#prefix ": a wait on a flag written by %s %u timed out (wait kind %u, expected value %u, block %u): "   \
+                   "a peer rank died or never launched its kernel", h[0] == 3 ? "block group" : "rank", h[1], h[0], h[2], h[3]); \
+      return FB_ERR_TIMEOUT;                                                                                                \
+    }                                                                                                                       \
+    return FB_OK;                                                                                                           \
+  }
+#endif
 
 // ---------------------------------------------------------------- Philox4x32-10 counter RNG
 struct Philox4 {

@@ -107,8 +107,7 @@ __device__ __forceinline__ void block_signal_and_wait(uint32_t* const* peer_flag
     uint32_t* remote = peer_flags[q] + ((size_t)phase * G + rank) * FB_ROUND_MAX_BLOCKS + block;
     st_release_sys(remote, epoch);
     const uint32_t* mine = peer_flags[rank] + ((size_t)phase * G + q) * FB_ROUND_MAX_BLOCKS + block;
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-    }
+    fb_spin_wait_ge<true>(mine, epoch, 1u + (uint32_t)phase, (uint32_t)q);     // bounded: see common.cuh
   }
   __syncthreads();
 }
@@ -119,8 +118,7 @@ __device__ __forceinline__ void rank_grid_barrier(uint32_t* counter, uint32_t ta
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(counter, 1u);
-    while ((int32_t)(ld_acquire_gpu(counter) - target) < 0) {
-    }
+    fb_spin_wait_ge<false>(counter, target, 3u, 0u);
   }
   __syncthreads();
 }
@@ -566,10 +564,10 @@ __global__ void peer_barrier_kernel(uint32_t* const* peer_flags, int rank, int G
     __threadfence_system();
     st_release_sys(peer_flags[q] + (size_t)slot * G + rank, epoch);
     const uint32_t* mine = peer_flags[rank] + (size_t)slot * G + q;
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-    }
+    fb_spin_wait_ge<true>(mine, epoch, 4u, (uint32_t)q);
   }
 }
+FB_DEFINE_SPIN_API(fb_round)
 extern "C" int64_t fb_peer_barrier_flag_bytes(int32_t G) { return (int64_t)8 * (G < 1 ? 1 : G) * sizeof(uint32_t); }
 extern "C" int fb_peer_barrier(uint32_t* const* peer_flags, int32_t rank, int32_t G, uint32_t epoch, int32_t slot,
                                fb_stream_t stream) {

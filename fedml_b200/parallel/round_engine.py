@@ -49,6 +49,26 @@ class DPConfig:
     aggregate_noise: bool = False   # one draw on the aggregate (same output distribution, no per-client RNG cost)
 
 
+def shard_bounds(P: int, P_train: int, G: int, rank: int):
+    """Element range of the server-optimizer state that ``rank`` owns in two-shot mode: shard ``rank`` of the float4
+    lanes of the flat model (csrc/round.cu: S4 = ceil(P/4 / G) lanes per shard), clipped to the trainable prefix."""
+    nvec = P // 4
+    s4 = (nvec + G - 1) // G
+    lo, hi = min(rank * s4 * 4, P_train), min((rank + 1) * s4 * 4, P_train)
+    return lo, hi
+
+
+def merge_sharded_moments(per_rank, P: int, P_train: int):
+    """Two-shot mode updates the moments of shard r on rank r only: assemble the complete tensor from every rank's own
+    shard (``per_rank``: list of [P_train] tensors, one per rank)."""
+    G = len(per_rank)
+    out = torch.zeros_like(per_rank[0])
+    for r, t in enumerate(per_rank):
+        lo, hi = shard_bounds(P, P_train, G, r)
+        out[lo:hi] = t[lo:hi]
+    return out
+
+
 class RoundEngine:
     TWO_SHOT_BYTES = 8 << 20    # above this the reduce is bandwidth-bound: shard it (SURVEY §5.8)
 
@@ -153,16 +173,55 @@ class RoundEngine:
         p.m = self.m.data_ptr() if self.m is not None else None
         p.v = self.v.data_ptr() if self.v is not None else None
         if self.dp.clip > 0:
-            self.clip_calls += 1
+            # the kernel runs its intra-rank grid barrier (one arrival per block) only when it has client rows to clip:
+            # count exactly those launches, or a round without clients leaves the target ahead of the counter and the
+            # next clipped round spins forever
+            if Cn > 0:
+                self.clip_calls += 1
             p.sqnorm_part, p.clip_scale_out = self.sqnorm_part.data_ptr(), self.clip_scale.data_ptr()
             p.grid_bar, p.grid_bar_target = self.grid_bar.data_ptr(), self.grid * self.clip_calls
         ops.round_launch(p, self.device)
         return self.global_model
 
+    # ------------------------------------------------------------------ failure detection
+    @staticmethod
+    def set_spin_timeout(ms: int):
+        """Upper bound on any in-kernel wait for another rank (default 20 s)."""
+        from ..ops.native import check, lib
+        check(lib().fb_round_set_spin_timeout_ms(C.c_int64(int(ms))), "fb_round_set_spin_timeout_ms")
+
+    @staticmethod
+    def check_spin_errors(clear: bool = True):
+        """Synchronises with the device and raises ``NativeError`` (FB_ERR_TIMEOUT) if a cross-rank wait of a round
+        kernel or barrier gave up since the last check: a peer died or never launched.  The global model produced by
+        that round is garbage and must be discarded (resume from the last checkpoint)."""
+        from ..ops.native import check, lib
+        out = (C.c_uint32 * 4)()
+        check(lib().fb_round_spin_status(out, C.c_int32(int(clear))), "round kernel")
+
     # ------------------------------------------------------------------ checkpoint helpers
+    def _full_moment(self, t: Optional[torch.Tensor]):
+        """Complete server-optimizer moment tensor.  In two-shot mode with several GPUs each rank only ever updates its
+        own shard (round.cu phase 3), so the other shards of its copy are stale: take every rank's own shard (masked
+        all-reduce over the bootstrap process group).  COLLECTIVE in that mode: call on every rank."""
+        if t is None:
+            return None
+        if not (self.G > 1 and self.two_shot):
+            return t.detach().cpu()
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            raise RuntimeError("RoundEngine.state_dict: two-shot mode on several GPUs needs torch.distributed to gather "
+                               "the sharded optimizer state")
+        lo, hi = shard_bounds(self.P, self.P_train, self.G, self.rank)
+        full = torch.zeros_like(t)
+        full[lo:hi] = t[lo:hi]
+        dist.all_reduce(full)
+        return full.cpu()
+
     def state_dict(self):
-        return {"global": self.global_model.detach().cpu(), "m": None if self.m is None else self.m.cpu(),
-                "v": None if self.v is None else self.v.cpu(), "opt_step": self.opt_step}
+        """Checkpoint state.  With G > 1 in two-shot mode this is a collective (see ``_full_moment``)."""
+        return {"global": self.global_model.detach().cpu(), "m": self._full_moment(self.m), "v": self._full_moment(self.v),
+                "opt_step": self.opt_step}
 
     def load_state_dict(self, sd):
         self.global_model.copy_(sd["global"])
@@ -176,7 +235,7 @@ class RoundEngine:
 def emulated_round(clients_per_rank, weights_per_rank, global_model: torch.Tensor, P_train: int, inv_total: float,
                    two_shot: bool, opt: ServerOptConfig = None, dp: DPConfig = None, m=None, v=None, opt_step=1,
                    round_idx=0, epoch=1, state=None, self_coef=0.0, grad_scale=1.0, weights_buf_per_rank=None,
-                   inv_total_buf=None):
+                   inv_total_buf=None, dead_rank=None):
     """Run G emulated ranks of the round kernel in ONE cooperative launch on one GPU.
 
     Returns the list of per-rank global models after the round.  Used by the GPU tests to exercise
@@ -195,12 +254,10 @@ def emulated_round(clients_per_rank, weights_per_rank, global_model: torch.Tenso
         st["v"] = [(v.clone() if v is not None else torch.zeros(P_train, device=dev))
                    if opt.name in ("adam", "yogi", "adagrad") else None for _ in range(G)]
         st["grid_bar"] = [torch.zeros(4, dtype=torch.int32, device=dev) for _ in range(G)]
-        st["clip_calls"] = 0
+        st["clip_calls"] = [0] * G        # per rank: a rank without clients skips the grid barrier (see RoundEngine.aggregate)
     grid = ops.round_grid(P, G, G)
     tab = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64).to(dev)
     t_partial, t_global, t_flags = tab(st["partials"]), tab(st["globals"]), tab(st["flags"])
-    if dp.clip > 0:
-        st["clip_calls"] += 1
     params, keep = [], []
     base = 0
     for r in range(G):
@@ -219,6 +276,8 @@ def emulated_round(clients_per_rank, weights_per_rank, global_model: torch.Tenso
         p.global_model, p.partial = st["globals"][r].data_ptr(), st["partials"][r].data_ptr()
         p.peer_partial, p.peer_global, p.peer_flags = t_partial.data_ptr(), t_global.data_ptr(), t_flags.data_ptr()
         p.rank, p.G, p.epoch, p.two_shot = r, G, epoch, int(two_shot and G > 1)
+        if dead_rank is not None and r == dead_rank:
+            p.epoch = epoch - 1       # fault injection: this rank never announces the current round (a crashed peer)
         p.clip_bound, p.noise_std, p.seed, p.round = dp.clip, dp.sigma, dp.seed, round_idx
         p.opt, p.nesterov, p.lr, p.momentum = FB_OPT[opt.name], int(opt.nesterov), opt.lr, opt.momentum
         p.beta1, p.beta2, p.eps = opt.beta1, opt.beta2, opt.eps
@@ -230,7 +289,9 @@ def emulated_round(clients_per_rank, weights_per_rank, global_model: torch.Tenso
             cs = torch.zeros(max(Cn, 1), dtype=torch.float32, device=dev)
             keep += [sq, cs]
             p.sqnorm_part, p.clip_scale_out = sq.data_ptr(), cs.data_ptr()
-            p.grid_bar, p.grid_bar_target = st["grid_bar"][r].data_ptr(), grid * st["clip_calls"]
+            if Cn > 0:
+                st["clip_calls"][r] += 1
+            p.grid_bar, p.grid_bar_target = st["grid_bar"][r].data_ptr(), grid * st["clip_calls"][r]
         params.append(p)
     ops.round_launch_emulated(params, P, dev)
     st["_keep"] = keep

@@ -764,8 +764,8 @@ class NCCLSimulator:
             if freq > 0 and (round_idx == int(args.comm_round) - 1 or round_idx % freq == 0):
                 self.evaluate(round_idx)
             every = int(getattr(args, "checkpoint_every", 0) or 0)
-            if every and getattr(args, "checkpoint_dir", None) and (round_idx + 1) % every == 0 and self.rank == 0:
-                self.save(args.checkpoint_dir)
+            if every and getattr(args, "checkpoint_dir", None) and (round_idx + 1) % every == 0:
+                self.save(args.checkpoint_dir)          # collective: sharded optimizer state is gathered from every rank
         return self.global_state_dict()
 
     def global_state_dict(self):
@@ -775,7 +775,8 @@ class NCCLSimulator:
         from ...utils.checkpoint import save_run_state
         extra = {"engine": self.engine.state_dict()} if self.engine is not None else \
             {"server_opt": self.server_opt.state_dict() if self.server_opt is not None else None}
-        save_run_state(cdir, self.round_idx, self.global_state_dict(), extra)
+        if self.rank == 0:
+            save_run_state(cdir, self.round_idx, self.global_state_dict(), extra)
 
     def resume(self, cdir) -> int:
         from ...utils.checkpoint import load_run_state

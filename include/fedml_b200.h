@@ -421,6 +421,57 @@ int fb_amp_normalize(const float* x, float* y, int32_t n_img, int32_t ch, int32_
                      void* workspace, fb_stream_t stream);
 int64_t fb_amp_normalize_workspace_bytes(int32_t n_img, int32_t ch, int32_t H, int32_t W);
 
+/* ---------------------------------------------------------------------------------------------
+ * fp32-activation / TF32 tensor-core variants (the precision the reference trains at: stock nn.Conv2d under
+ * cuDNN's TF32 default, fp32 activations; simulation/single_process/fedavg/my_model_trainer_classification.py:18-91,
+ * model/cv/resnet.py:116-136).  Same structs and conventions as the bf16 entry points; operands and outputs are fp32,
+ * leading dimensions / group strides are in fp32 elements (multiples of 4), products run on tcgen05 kind::tf32.
+ *   - grouped GEMMs: k-blocks of 32 elements; MN-major operands use the 128-byte-swizzle / 32-byte-atom layout, the
+ *     only shared-memory layout tcgen05 accepts for 32-bit MN-major operands;
+ *   - fb_conv3x3_tf32: cin in {8, 16} or a multiple of 32; fb_conv3x3_wgrad_tf32: cin a multiple of 32
+ *     (<= 256, or a multiple of 256), B*Ho*Wo % (32*split) == 0;
+ *   - BatchNorm / im2col / col2im / staging kernels: the same kernels instantiated for fp32 activations; the staged
+ *     GEMM operands of fb_stage_conv_weights_f32 / fb_sgd_restage_f32 are fp32 (1x1-convolution and fc weights need
+ *     no staging in this mode: the [cout][cin] rows of the arena are the GEMM operand).
+ * ------------------------------------------------------------------------------------------- */
+int fb_grouped_gemm_tf32(const FbGroupedGemm* p, fb_stream_t stream);
+int fb_grouped_gemm_tn_tf32(const FbGroupedGemm* p, fb_stream_t stream);
+int fb_grouped_gemm_nn_tf32(const FbGroupedGemm* p, fb_stream_t stream);
+int fb_conv3x3_tf32(const FbConv3x3* p, fb_stream_t stream);
+int fb_conv3x3_wgrad_tf32(const FbConv3x3Wgrad* p, fb_stream_t stream);
+int fb_bn_fwd_stacked_f32(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch, const float* gamma,
+                          const float* beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
+                          const float* active, float momentum, float eps, int32_t relu, int32_t training, float* save_mean,
+                          float* save_rstd, float* scratch, float* num_batches_tracked, int64_t ld_n, fb_stream_t stream);
+int fb_bn_bwd_stacked_f32(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t C,
+                          int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p, const float* save_mean,
+                          const float* save_rstd, int32_t relu, float* dgamma, float* dbeta, int64_t ld_g, float* scratch,
+                          fb_stream_t stream);
+int fb_im2col3x3_nhwc_f32(const void* x, void* cols, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                          fb_stream_t stream);
+int fb_col2im3x3_nhwc_f32(const void* cols, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch, int32_t stride,
+                          fb_stream_t stream);
+int fb_stage_conv_weights_f32(const float* arena, int64_t ld, int32_t C, void* stage_f32, int64_t stage_ld,
+                              const int64_t* table_dev, int32_t n_layers, int32_t max_n, fb_stream_t stream);
+int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
+                       void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
+                       const float* lr_dev, fb_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Bounded cross-rank waits (failure detection; the reference has none on this path: a dead MPI worker hangs
+ * FedAVGAggregator.check_whether_all_receive forever, simulation/mpi_p2p_mp/fedavg/FedAVGAggregator.py:58-66).
+ * Every wait on a flag another rank or block writes (fb_round_launch, fb_peer_barrier, fb_dp_allreduce_step and
+ * their emulated forms) gives up after the time-out (default 20 s), records who it was waiting for and lets the
+ * kernel retire.  *_spin_status synchronises with the device, copies {wait kind, rank waited for, expected flag
+ * value, block} to out4 (may be NULL), clears the record when `clear` != 0 and returns FB_ERR_TIMEOUT if a wait
+ * gave up since the last clear — the data produced by that launch must then be discarded.
+ * ------------------------------------------------------------------------------------------- */
+#define FB_ERR_TIMEOUT (-4)
+int fb_round_set_spin_timeout_ms(int64_t ms);
+int fb_round_spin_status(uint32_t* out4, int32_t clear);
+int fb_dp_set_spin_timeout_ms(int64_t ms);
+int fb_dp_spin_status(uint32_t* out4, int32_t clear);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,122 @@
+"""Failure detection and state handling of the fused round kernel (csrc/round.cu), on emulated ranks (all ranks of
+the protocol in ONE cooperative launch on one GPU)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _lib(native_lib):
+    return native_lib
+
+
+def _mk(G, counts, P, seed):
+    torch.manual_seed(seed)
+    g = torch.randn(P, device=DEV)
+    clients = [(g + 0.1 * torch.randn(c, P, device=DEV)) if c else None for c in counts]
+    weights = [(torch.randint(10, 100, (c,), device=DEV).float()) if c else None for c in counts]
+    total = sum(float(w.sum()) for w in weights if w is not None)
+    return g, clients, weights, total
+
+
+def test_clipped_round_after_a_round_where_one_rank_had_no_clients():
+    """A rank that drew no client skips the intra-rank grid barrier of the clip phase; its barrier target must not run
+    ahead of its counter (the next clipped round with clients would wait forever)."""
+    from fedml_b200.parallel.round_engine import DPConfig, RoundEngine, emulated_round
+    from test_gpu_kernels import _oracle_round
+    RoundEngine.set_spin_timeout(5000)
+    P, P_train = 4 * 3001, 4 * 2800
+    dpc = DPConfig(clip=1.5, sigma=0.0, seed=5)
+    state = None
+    g_cur = None
+    for rnd, counts in enumerate([(3, 0), (2, 4), (0, 3), (5, 1)]):
+        g, clients, weights, total = _mk(2, counts, P, 20 + rnd)
+        if g_cur is None:
+            g_cur = g
+        else:                                       # continue from the model the previous round left on the ranks
+            clients = [None if c is None else c - g + g_cur for c in clients]
+        outs, state = emulated_round(clients, weights, g_cur, P_train, 1.0 / total, False, dp=dpc, round_idx=rnd,
+                                     epoch=rnd + 1, state=state)
+        RoundEngine.check_spin_errors()
+        ref = _oracle_round(clients, weights, g_cur, P_train, dpc.clip, 0.0, dpc.seed, rnd, None, None, None, 1, 1.0 / total)
+        torch.testing.assert_close(outs[0].double(), ref, rtol=1e-5, atol=2e-5)
+        assert torch.equal(outs[0], outs[1])
+        g_cur = outs[0].clone()
+    RoundEngine.set_spin_timeout(20000)
+
+
+@pytest.mark.parametrize("opt_name,momentum", [("adam", 0.0), ("sgd", 0.9)])
+def test_two_shot_sharded_optimizer_state_resume(opt_name, momentum):
+    """Two-shot mode keeps valid moments for shard r on rank r only.  A checkpoint assembled from every rank's own shard,
+    loaded on all ranks, continues exactly like the uninterrupted run."""
+    from fedml_b200.parallel.round_engine import ServerOptConfig, emulated_round, merge_sharded_moments
+    G, P, P_train, K = 2, 4 * 2048, 4 * 2000, 8
+    opt = ServerOptConfig(opt_name, lr=0.05, momentum=momentum, beta1=0.9, beta2=0.99, eps=1e-3)
+    torch.manual_seed(3)
+    g0 = torch.randn(P, device=DEV)
+
+    def round_inputs(rnd, g):
+        torch.manual_seed(100 + rnd)
+        X = g + 0.05 * torch.randn(K, P, device=DEV)
+        w = torch.arange(1, K + 1, device=DEV).float()
+        per = K // G
+        return [X[r * per:(r + 1) * per] for r in range(G)], [w[r * per:(r + 1) * per].contiguous() for r in range(G)], float(w.sum())
+
+    def run(state, g, rnd):
+        cl, wt, tot = round_inputs(rnd, g)
+        outs, state = emulated_round(cl, wt, g, P_train, 1.0 / tot, True, opt=opt, opt_step=rnd + 1, epoch=rnd + 1, state=state)
+        return outs[0].clone(), state
+
+    # uninterrupted: three rounds
+    g, st = g0.clone(), None
+    for rnd in range(3):
+        g, st = run(st, g, rnd)
+    full = g
+    # interrupted after two rounds: checkpoint = global + moments merged from each rank's own shard
+    g, st = g0.clone(), None
+    for rnd in range(2):
+        g, st = run(st, g, rnd)
+    m = merge_sharded_moments(st["m"], P, P_train) if st["m"][0] is not None else None
+    v = merge_sharded_moments(st["v"], P, P_train) if st["v"][0] is not None else None
+    # the shards a rank does not own really are stale (otherwise this test checks nothing)
+    if m is not None:
+        assert not torch.equal(st["m"][0], st["m"][1])
+    cl, wt, tot = round_inputs(2, g)
+    outs, _ = emulated_round(cl, wt, g, P_train, 1.0 / tot, True, opt=opt, m=m, v=v, opt_step=3, epoch=1, state=None)
+    assert torch.equal(outs[0], full) and torch.equal(outs[1], full)
+    # resuming from rank 0's copy alone (the old behaviour) does NOT reproduce the run
+    m0 = st["m"][0] if m is not None else None
+    v0 = st["v"][0] if v is not None else None
+    outs_bad, _ = emulated_round(cl, wt, g, P_train, 1.0 / tot, True, opt=opt, m=m0, v=v0, opt_step=3, epoch=1, state=None)
+    assert not torch.equal(outs_bad[1], full)
+
+
+def test_dead_rank_is_reported_not_waited_for_forever():
+    """Fault injection: one emulated rank never announces the round.  The other ranks' waits give up after the
+    time-out, the kernel retires, the host gets FB_ERR_TIMEOUT naming the rank, and the next round works."""
+    import time
+    from fedml_b200.ops.native import NativeError
+    from fedml_b200.parallel.round_engine import RoundEngine, emulated_round
+    P, P_train = 4 * 3001, 4 * 2800
+    g, clients, weights, total = _mk(3, (2, 3, 1), P, 1)
+    RoundEngine.set_spin_timeout(300)
+    try:
+        t0 = time.time()
+        outs, state = emulated_round(clients, weights, g, P_train, 1.0 / total, False, epoch=1, dead_rank=1)
+        torch.cuda.synchronize()
+        assert time.time() - t0 < 30.0
+        with pytest.raises(NativeError, match="timed out"):
+            RoundEngine.check_spin_errors()
+        RoundEngine.check_spin_errors()                      # record was cleared
+        # healthy round afterwards, same flag buffers (epoch moves on)
+        for r in range(3):
+            state["globals"][r].copy_(g)
+        outs, state = emulated_round(clients, weights, g, P_train, 1.0 / total, False, epoch=2, state=state)
+        RoundEngine.check_spin_errors()
+        ref = sum((w[:, None] * c).sum(0) for w, c in zip(weights, clients)) / total
+        torch.testing.assert_close(outs[0], ref, rtol=1e-5, atol=2e-5)
+    finally:
+        RoundEngine.set_spin_timeout(20000)

@@ -9,7 +9,8 @@ build()
 K = int(os.environ.get("K", "13"))
 args = Arguments.from_dict(dict(training_type="simulation", backend="NCCL", federated_optimizer="FedAvg", dataset="cifar10", model="resnet56",
     client_num_in_total=1000, client_num_per_round=K, comm_round=12, epochs=1, batch_size=10, learning_rate=0.03, partition_method="homo",
-    using_gpu=True, frequency_of_the_test=0, log_level="WARNING", synthetic_train_size=50000))
+    using_gpu=True, frequency_of_the_test=0, log_level="WARNING", synthetic_train_size=50000,
+    compute_dtype=os.environ.get("DTYPE", "tf32")))
 args = fedml.init(args); dev = torch.device("cuda:0")
 ds, ncls = fedml.data.load(args); args._federated_dataset.pin(); model = fedml.models.create(args, ncls)
 from fedml_b200.simulation import SimulatorNCCL
@@ -23,4 +24,4 @@ ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUD
 tot = sum(e.device_time if hasattr(e, "device_time") else e.cuda_time for e in ev)
 t0 = min(e.time_range.start for e in ev); t1 = max(e.time_range.end for e in ev)
 print(f"K={K}: {len(ev)} device activities, kernel time sum {tot/1e3:.2f} ms, span {(t1-t0)/1e3:.2f} ms")
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=18, max_name_column_width=60))
+print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=60))
