@@ -75,6 +75,23 @@ def import_reference():
     return fedml
 
 
+def make_dataset_flat(torch, np, n_clients, per_client, batch_size, dim=784, seed=0):
+    """MNIST-shaped clients (flattened 28x28 floats in [0, 1]) for the logistic-regression config."""
+    g = np.random.default_rng(seed)
+    from torch.utils.data import DataLoader, TensorDataset
+    train_local, test_local, nums = {}, {}, {}
+    xt = torch.from_numpy(g.random((batch_size, dim), dtype=np.float32))
+    yt = torch.from_numpy(g.integers(0, 10, batch_size).astype(np.int64))
+    test_loader = DataLoader(TensorDataset(xt, yt), batch_size=batch_size)
+    for c in range(n_clients):
+        x = torch.from_numpy(g.random((per_client, dim), dtype=np.float32))
+        y = torch.from_numpy(g.integers(0, 10, per_client).astype(np.int64))
+        train_local[c] = DataLoader(TensorDataset(x, y), batch_size=batch_size, shuffle=True, drop_last=False)
+        test_local[c] = test_loader
+        nums[c] = per_client
+    return [n_clients * per_client, batch_size, test_loader, test_loader, nums, train_local, test_local, 10, None]
+
+
 def make_dataset(torch, np, n_clients, per_client, batch_size, seed=0):
     g = np.random.default_rng(seed)
     mean = np.array([0.4914, 0.4822, 0.4465], dtype=np.float32).reshape(1, 3, 1, 1)
@@ -104,15 +121,20 @@ def run(cfg, steps, warmup, n_gpus):
     import logging
     logging.disable(logging.INFO)
     args = types.SimpleNamespace(
-        training_type="simulation", backend="single_process", dataset="cifar10", model=cfg["model"],
+        training_type="simulation", backend="single_process", dataset=cfg.get("dataset", "cifar10"), model=cfg["model"],
         federated_optimizer="FedAvg", client_num_in_total=cfg["client_num_in_total"],
         client_num_per_round=cfg["client_num_per_round"], comm_round=warmup + steps, epochs=cfg["epochs"],
         batch_size=cfg["batch_size"], client_optimizer="sgd", learning_rate=cfg["learning_rate"], weight_decay=0.001,
         frequency_of_the_test=10 ** 9, using_gpu=True, gpu_id=0, random_seed=0, enable_wandb=False, rank=0, run_id="0",
         using_mlops=False)
     torch.manual_seed(0); np.random.seed(0)
-    device = torch.device("cuda:0" if torch.cuda.is_available() else "cpu")
-    dataset = make_dataset(torch, np, cfg["client_num_in_total"], cfg["samples_per_client"], cfg["batch_size"])
+    on_cpu = bool(cfg.get("cpu"))
+    device = torch.device("cuda:0" if (torch.cuda.is_available() and not on_cpu) else "cpu")
+    if on_cpu:
+        args.using_gpu = False
+        dataset = make_dataset_flat(torch, np, cfg["client_num_in_total"], cfg["samples_per_client"], cfg["batch_size"])
+    else:
+        dataset = make_dataset(torch, np, cfg["client_num_in_total"], cfg["samples_per_client"], cfg["batch_size"])
     model = fedml.model.create(args, 10)
     from fedml.simulation import SimulatorSingleProcess
     sim = SimulatorSingleProcess(args, device, dataset, model)

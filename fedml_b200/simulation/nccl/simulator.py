@@ -68,8 +68,19 @@ class PhaseTimer:
         self.pending: Dict[str, list] = {}
         self.totals: Dict[str, float] = {}
 
+    # NVTX ranges carry the reference's MLOps event names so a timeline reads like its log
+    # (core/mlops/mlops_profiler_event.py: "train", "aggregate", "comm_c2s", "server.wait")
+    NVTX = os.environ.get("FB_NVTX", "1") != "0"
+
+    def reset(self):
+        """Drop everything measured so far (e.g. warm-up rounds that include CUDA-graph capture)."""
+        self.collect()
+        self.totals = {}
+
     def start(self, name):
         if self.cuda:
+            if self.NVTX:
+                torch.cuda.nvtx.range_push(name)
             ev = torch.cuda.Event(enable_timing=True); ev.record()
         else:
             ev = time.perf_counter()
@@ -78,6 +89,8 @@ class PhaseTimer:
     def stop(self, name):
         if self.cuda:
             ev = torch.cuda.Event(enable_timing=True); ev.record()
+            if self.NVTX:
+                torch.cuda.nvtx.range_pop()
         else:
             ev = time.perf_counter()
         self.pending[name][-1][1] = ev
