@@ -129,7 +129,7 @@ bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict_
                 const float* __restrict__ beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                 const float* __restrict__ active, float momentum, float eps, int relu, int training,
                 float* __restrict__ save_mean, float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n,
-                float* sm /* scale[ch], shift[ch] */) {
+                float* sm /* scale[ch], shift[ch] */, int SP /* slices of `partial` per client (1: complete sums) */) {
   float* scale = sm;
   float* shift = sm + ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
@@ -139,9 +139,9 @@ bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict_
     float mean, var;
     if (training) {
       float su = 0.f, sq = 0.f;
-      for (int j = 0; j < S; ++j) {
-        su += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);        // L2: written by sibling CTAs in the fused kernel
-        sq += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
+      for (int j = 0; j < SP; ++j) {
+        su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);       // L2: written by sibling CTAs in the fused kernel
+        sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
       }
       mean = su / (float)M;
       var = fmaxf(sq / (float)M - mean * mean, 0.f);
@@ -248,12 +248,12 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
                 int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                 int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                 float momentum, float eps, int relu, int training, float* __restrict__ save_mean,
-                float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n) {
+                float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n, int SP) {
   extern __shared__ float sm[];
   pdl_wait();
   pdl_trigger();
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu,
-                training, save_mean, save_rstd, num_batches_tracked, ld_n, sm);
+                training, save_mean, save_rstd, num_batches_tracked, ld_n, sm, SP);
 }
 
 // Barrier among the S CTAs of one client (blockIdx.y): {arrival count, generation} per client, self-resetting, so
@@ -295,7 +295,7 @@ bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __res
   bn_stats_body(x, M, ch, S, partial, smem);
   client_barrier(S);
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu, 1,
-                save_mean, save_rstd, num_batches_tracked, ld_n, sm);
+                save_mean, save_rstd, num_batches_tracked, ld_n, sm, S);
 }
 
 // The fused form wins when the layer is large (second pass served by L2, 1-2 % on the 100-client bench) and loses when
@@ -324,20 +324,24 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
   FB_REQUIRE(!training || scratch, "fb_bn_fwd_stacked: training needs the partial-sum scratch");
   int S = bn_slices(C, M, ch);
   if (bn_forced_slices(0) > 0) S = bn_forced_slices(0);
-  if (training && bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+  // training == 2: `scratch` already holds the complete per-client sums [C][2][ch] (sum x, sum x^2), produced by the
+  // epilogue of the convolution that wrote x (FbGroupedGemm.stats): one pass over x instead of two
+  const bool have_stats = training == 2;
+  if (training == 1 && bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
     FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
         running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
-  if (training) {
+  if (training == 1) {
     FB_CHECK_CUDA(fb_launch_pdl(bn_stats_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)x, M, ch, S, scratch));
     FB_CHECK_CUDA(cudaGetLastError());
   }
   FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
       (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p,
-      running_mean, running_var, ld_r, active, momentum, eps, relu, training, save_mean, save_rstd, num_batches_tracked, ld_n));
+      running_mean, running_var, ld_r, active, momentum, eps, relu, training ? 1 : 0, save_mean, save_rstd, num_batches_tracked, ld_n,
+      have_stats ? 1 : S));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

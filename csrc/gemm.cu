@@ -234,7 +234,12 @@ struct GemmArgs {
   int cv_b_inner_off, cv_b_row_off;               // per-tap coordinate offsets into the weight map
   int cv_sbo, cv_swz;                             // 8-row group stride (bytes) and descriptor swizzle code
   int cv_tpt;                                     // MODE 5: taps per n-tile (9, 3 or 1)
+  // per-column statistics of the output (BatchNorm batch statistics produced by the convolution that feeds it):
+  // stats[g][0][n] += sum over rows of D[g][:, n], stats[g][1][n] += sum of squares; group stride stats_gs floats
+  float* stats;
+  int64_t stats_gs;
 };
+#define GEMM_STATS_BYTES (4 * 2 * 256 * 4)   /* per epilogue warp: sum and sum of squares for up to 256 tile columns */
 
 // MODE bit 0: A is MN-major ([K][M] in memory), bit 1: B is MN-major ([K][N] in memory); MODE 4: implicit 3x3 conv
 // PAIR: the kernel runs as clusters of two CTAs (one TPC) that share 256 x BN tiles through tcgen05 cta_group::2: each CTA
@@ -270,6 +275,17 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tmem_full = empty_bar + GEMM_MAX_STAGES;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* stats_acc = reinterpret_cast<float*>(staging + GEMM_STAGING_BYTES + 256);   // only carved when a.stats != nullptr
+  // Tile walk.  Default: grid-stride over (group, m-tile, n-tile) with the n-tile fastest.  With output statistics a CTA
+  // takes a CONTIGUOUS range of tiles, m-tile fastest, so that consecutive tiles share (group, n-tile) and the column
+  // sums stay in shared memory across them: one round of global atomics per CTA and group instead of one per tile.
+  const bool STATS = a.stats != nullptr;
+  const int n_ctas = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x, cta = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tiles_all = a.G * a.m_tiles * a.n_tiles;
+  const int per_cta = (tiles_all + n_ctas - 1) / n_ctas;
+  const int t_first = STATS ? cta * per_cta : cta;
+  const int t_last = STATS ? min(tiles_all, t_first + per_cta) : tiles_all;
+  const int t_step = STATS ? 1 : n_ctas;
 
   constexpr bool CONV = MODE == 4, WGRAD = MODE == 5;   // 5: TN form whose B operand is gathered from the NHWC activation
   constexpr bool A_MN = (MODE & 1) != 0, B_MN = (MODE & 2) != 0 || WGRAD;
@@ -309,8 +325,9 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
-        const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
+      for (int t = t_first; t < t_last; t += t_step) {
+        const int nt = STATS ? (t / a.m_tiles) % a.n_tiles : t % a.n_tiles;
+      const int mt = STATS ? t % a.m_tiles : (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
         if (CONV) {
           // 128 consecutive output pixels of group g: image n0 (a tile spans 128 / (Ho*Wo) images when the plane is
           // smaller), output rows from ho0.  One k-block per (tap, channel block): the tap's shifted input window
@@ -413,7 +430,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t idesc = make_idesc(a.BN, A_MN, B_MN, TILE_M, TF32);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
+      for (int t = t_first; t < t_last; t += t_step) {
         mbar_wait(tmem_empty + acc, acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(acc * a.BN);
@@ -463,10 +480,31 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t acc_phase = 0;
     uint8_t* my_stage = staging + (size_t)q * 2 * 4096;
     int sbuf = 0;
-    for (int t = PAIR ? blockIdx.x >> 1 : blockIdx.x; t < total_tiles; t += PAIR ? gridDim.x >> 1 : gridDim.x) {
-      const int nt = t % a.n_tiles, mt = (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
+    float* my_acc = stats_acc + q * 512;          // [2][256] of this warp
+    int acc_key = -1;                             // (group, n-tile) the accumulators belong to
+    if (STATS)
+      for (int i = lane; i < 512; i += 32) my_acc[i] = 0.f;
+    for (int t = t_first; t < t_last; t += t_step) {
+      const int nt = STATS ? (t / a.m_tiles) % a.n_tiles : t % a.n_tiles;
+      const int mt = STATS ? t % a.m_tiles : (t / a.n_tiles) % a.m_tiles, g = t / (a.n_tiles * a.m_tiles);
       mbar_wait(tmem_full + acc, acc_phase);
       tc_fence_after();
+      if (STATS && acc_key != g * a.n_tiles + nt) {
+        if (acc_key >= 0) {
+          const int pg = acc_key / a.n_tiles, pn = acc_key - pg * a.n_tiles;
+          float* dst = a.stats + (size_t)pg * a.stats_gs + pn * a.BN;
+          for (int c = lane; c < a.BN; c += 32) {
+            if (pn * a.BN + c < a.N) {
+              atomicAdd(dst + c, my_acc[c]);
+              atomicAdd(dst + a.N + c, my_acc[256 + c]);
+            }
+            my_acc[c] = 0.f;
+            my_acc[256 + c] = 0.f;
+          }
+          __syncwarp();
+        }
+        acc_key = g * a.n_tiles + nt;
+      }
       const int row0 = mt * TILE_M + (int)rank * GEMM_BM + q * 32;   // first output row of this warp's TMEM lane quarter
       const int row = row0 + lane;
       const bool row_ok = row < a.M;
@@ -528,6 +566,40 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           fence_async_proxy();   // generic-proxy smem writes -> visible to the TMA (async proxy)
           __syncwarp();
+          if (STATS) {
+            // column sums of the staged 32 x CW box (the values exactly as stored): lane c walks column c down the rows;
+            // at a fixed row the 32 lanes read one (swizzle-permuted) row segment, so the reads are conflict-free
+            const int rows_valid = min(32, a.M - row0);
+            if (a.d_fp32) {
+              if (lane < CW && col0 + lane < a.N) {
+                float s1 = 0.f, s2 = 0.f;
+                for (int r = 0; r < rows_valid; ++r) {
+                  int slot = lane >> 2;
+                  if (RB == 128) slot ^= (r & 7);
+                  const float v = *reinterpret_cast<const float*>(buf + r * RB + slot * 16 + (lane & 3) * 4);
+                  s1 += v;
+                  s2 += v * v;
+                }
+                my_acc[c0 + lane] += s1;
+                my_acc[256 + c0 + lane] += s2;
+              }
+            } else {
+              if (2 * lane < CW && col0 + 2 * lane < a.N) {
+                float s1a = 0.f, s2a = 0.f, s1b = 0.f, s2b = 0.f;
+                for (int r = 0; r < rows_valid; ++r) {
+                  int slot = lane >> 2;
+                  if (RB == 128) slot ^= (r & 7);
+                  const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(buf + r * RB + slot * 16 + (lane & 3) * 4));
+                  s1a += v.x; s2a += v.x * v.x;
+                  s1b += v.y; s2b += v.y * v.y;
+                }
+                my_acc[c0 + 2 * lane] += s1a;
+                my_acc[256 + c0 + 2 * lane] += s2a;
+                my_acc[c0 + 2 * lane + 1] += s1b;
+                my_acc[256 + c0 + 2 * lane + 1] += s2b;
+              }
+            }
+          }
           if (lane == 0) {
             if (a.reduce_add) {
               asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
@@ -578,6 +650,16 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         else mbar_arrive(tmem_empty + acc);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (STATS && acc_key >= 0) {
+      const int pg = acc_key / a.n_tiles, pn = acc_key - pg * a.n_tiles;
+      float* dst = a.stats + (size_t)pg * a.stats_gs + pn * a.BN;
+      for (int c = lane; c < a.BN; c += 32) {
+        if (pn * a.BN + c < a.N) {
+          atomicAdd(dst + c, my_acc[c]);
+          atomicAdd(dst + a.N + c, my_acc[256 + c]);
+        }
+      }
     }
     if (a.tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores complete before exit
   }
@@ -712,6 +794,10 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, boo
   a.reduce_add = p->accumulate ? 1 : 0;
   a.group_div = group_div;
   FB_REQUIRE(!a.reduce_add || a.tma_store, "fb_grouped_gemm: accumulate needs a 16-byte aligned output (TMA reduce-store)");
+  a.stats = p->stats;
+  a.stats_gs = p->stats_gs;
+  FB_REQUIRE(!a.stats || (a.tma_store && group_div == 1 && go == 1),
+             "fb_grouped_gemm: output statistics need a 16-byte aligned output and one-level groups without split-K");
   a.BNpad = b_mn ? (bn + BK - 1) / BK * BK : bn;
   a.n_tiles = (p->N + bn - 1) / bn;
   a.m_tiles = pair ? (p->M + 2 * GEMM_BM - 1) / (2 * GEMM_BM) : (p->M + GEMM_BM - 1) / GEMM_BM;
@@ -737,7 +823,7 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, boo
                   (uint64_t)p->b_gs2, (uint32_t)BK, tf32, true);
   if (rc) return rc;
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)(pair ? a.BNpad / 2 : a.BNpad) * 128;
-  const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/;
+  const size_t fixed = 1024 /*align slack*/ + GEMM_STAGING_BYTES + 256 /*barriers*/ + (a.stats ? GEMM_STATS_BYTES : 0);
   // two co-resident CTAs per SM hide each other's per-tile latencies (TMEM allows it while 2 x tmem_cols <= 512)
   static int force_ctas = -1;
   if (force_ctas < 0) {
@@ -878,6 +964,9 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
   int cols = 32;
   while (cols < 2 * bn_cols) cols <<= 1;
   a.tmem_cols = cols;
+  a.stats = p->stats;
+  a.stats_gs = p->stats_gs;
+  FB_REQUIRE(!a.stats || a.tma_store, "fb_conv3x3: output statistics need cout * element size to be a multiple of 16 bytes");
 
   CUtensorMap tmA, tmB, tmD;
   {
@@ -909,7 +998,7 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
     if (rc) return rc;
   }
   const size_t stage_bytes = GEMM_A_BYTES + (size_t)(pair ? a.BNpad / 2 : a.BNpad) * 128;   // as in the kernel
-  const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256;
+  const size_t fixed = 1024 + GEMM_STAGING_BYTES + 256 + (a.stats ? GEMM_STATS_BYTES : 0);
   int ctas_per_sm = (a.tmem_cols <= 256) ? 2 : 1;
   if (pair) ctas_per_sm = 1;
   {

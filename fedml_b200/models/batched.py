@@ -37,8 +37,10 @@ class TorchBackend:
         self.dtype = dtype
 
     # ---- GEMMs (client-batched) -------------------------------------------------
-    def gemm_nt(self, a, b, out_dtype=None, relu=False):
-        """a [C,M,K] x b [C,N,K]^T -> [C,M,N]"""
+    def gemm_nt(self, a, b, out_dtype=None, relu=False, stats=None):
+        """a [C,M,K] x b [C,N,K]^T -> [C,M,N].  ``stats`` (fp32 [C,2,N], zeroed): back-ends that can, add the column sums
+        and sums of squares of the result into it and set ``self.stats_done``; this one leaves it alone."""
+        self.stats_done = False
         y = torch.bmm(a, b.transpose(1, 2))
         if relu:
             y = torch.relu_(y)
@@ -97,7 +99,7 @@ class TorchBackend:
         return dxp[:, :, 1:H + 1, 1:W + 1, :].contiguous()
 
     # ---- BatchNorm (+residual, +ReLU) ---------------------------------------------
-    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
+    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training, stats=None):
         """x [C,B,H,W,ch]; gamma/beta/rm/rv [C,ch] fp32 (views, rm/rv updated in place); nbt [C] fp32."""
         C = x.shape[0]
         ch = x.shape[-1]
@@ -273,8 +275,9 @@ class NativeBackend(TorchBackend):
     def conv3x3_ok(self, x, cout, stride):
         return self.use_tc_gemm and self.use_implicit_conv and self.ops.conv3x3_supported(x, cout, stride)
 
-    def conv3x3(self, x, wm, stride):
-        return self.ops.conv3x3(x, wm, stride)
+    def conv3x3(self, x, wm, stride, stats=None):
+        self.stats_done = stats is not None
+        return self.ops.conv3x3(x, wm, stride, stats=stats)
 
     # implicit weight gradients pay off when a pixel's channel vector fills a 128-byte line (cin >= 64); for narrower
     # layers the 32/64-byte TMA gathers cost more than the im2col buffer they avoid (measured, profiles/README.md)
@@ -321,9 +324,19 @@ class NativeBackend(TorchBackend):
     def _bn_ok(ch):
         return 8 <= ch <= 2048 and 2048 % ch == 0
 
-    def gemm_nt(self, a, b, out_dtype=None, relu=False):
+    # BatchNorm batch statistics produced by the epilogue of the convolution GEMM instead of a statistics pass over the
+    # activation.  OPT-IN (FB_EPILOGUE_STATS=1): correct (tests/test_gpu_tf32.py) but measured SLOWER on the headline bench
+    # (tf32 112.6 -> 119.6 ms/round, bf16 68.9 -> 82.8): these skinny GEMMs (N = 16..64, K = 16..256) are bound by their
+    # four epilogue warps, so 32 shared-memory reads + 64 FMAs per 32 x 32 output box cost more there than the saved
+    # read of the activation costs in the BatchNorm kernel.  The atomic column sums also make runs non-reproducible.
+    epilogue_stats = os.environ.get("FB_EPILOGUE_STATS", "0") == "1"
+
+    def gemm_nt(self, a, b, out_dtype=None, relu=False, stats=None):
         if self.use_tc_gemm and self.ops.grouped_gemm_supported(a, b):
-            return self.ops.grouped_gemm(a, b, out_dtype or a.dtype, relu=relu)
+            n = b.shape[1]
+            ok = stats is not None and self.epilogue_stats and (n * (4 if a.dtype == torch.float32 else (out_dtype or a.dtype).itemsize)) % 16 == 0
+            self.stats_done = ok
+            return self.ops.grouped_gemm(a, b, out_dtype or a.dtype, relu=relu, stats=stats if ok else None)
         self._fb("gemm_nt")
         return super().gemm_nt(a, b, out_dtype, relu)
 
@@ -372,9 +385,9 @@ class NativeBackend(TorchBackend):
         self._fb("col2im")
         return super().col2im3x3(dcols, B, H, W, ch, stride)
 
-    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
+    def bn_fwd(self, x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training, stats=None):
         if x.dtype in self._ACT and self._bn_ok(x.shape[-1]):
-            return self.ops.bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
+            return self.ops.bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training, stats=stats)
         self._fb("bn_fwd")
         return super().bn_fwd(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training)
 
@@ -519,11 +532,18 @@ class _Conv:
         Ho, Wo = (H - 1) // s + 1, (W_ - 1) // s + 1
         return be.im2col3x3(x, s), Ho, Wo
 
-    def fwd(self, be, x, Wm):
+    def fwd(self, be, x, Wm, stats=None):
+        """``stats``: zeroed fp32 [C,2,cout]; a back-end that can fills it with the output's column sums / sums of squares
+        (``be.stats_done`` says whether it did), which spares the BatchNorm that follows its statistics pass."""
         C, B = x.shape[0], x.shape[1]
+        be.stats_done = False
         if self.k == 3 and be.conv3x3_ok(x, self.cout, self.stride):
+            if stats is not None and getattr(be, "epilogue_stats", False):
+                return be.conv3x3(x, Wm[0], self.stride, stats=stats)
             return be.conv3x3(x, Wm[0], self.stride)                  # implicit GEMM: no im2col buffer
         cols, Ho, Wo = self._cols(be, x)
+        if stats is not None:
+            return be.gemm_nt(cols, Wm[0], stats=stats).view(C, B, Ho, Wo, self.cout)
         return be.gemm_nt(cols, Wm[0]).view(C, B, Ho, Wo, self.cout)
 
     def _wgrad(self, be, dy2, x, gW, dy=None):
@@ -579,8 +599,11 @@ class _BN:
     def __init__(self, name, ch, momentum=0.1, eps=1e-5):
         self.name, self.ch, self.momentum, self.eps = name, ch, momentum, eps
 
-    def fwd(self, be, x, W, active, relu, res=None, training=True):
+    def fwd(self, be, x, W, active, relu, res=None, training=True, stats=None):
         n = self.name
+        if stats is not None:
+            return be.bn_fwd(x, res, W[n + ".weight"], W[n + ".bias"], W[n + ".running_mean"], W[n + ".running_var"],
+                             W[n + ".num_batches_tracked"], active, self.momentum, self.eps, relu, training, stats=stats)
         return be.bn_fwd(x, res, W[n + ".weight"], W[n + ".bias"], W[n + ".running_mean"], W[n + ".running_var"],
                          W[n + ".num_batches_tracked"], active, self.momentum, self.eps, relu, training)
 
@@ -617,17 +640,21 @@ class _Block:
         saved = {"x": x}
         h = x
         n = len(self.convs)
+        st = getattr(self, "_stats", None) if training else None      # {bn name: zeroed [C,2,ch] slot}, set per step
         if self.ds is not None:
             dconv, dbn = self.ds
-            a = dconv.fwd(be, x, Wm[dconv.name])
-            idt, m, r = dbn.fwd(be, a, W, active, relu=False, training=training)
+            slot = st.get(dbn.name) if st else None
+            a = dconv.fwd(be, x, Wm[dconv.name], stats=slot)
+            idt, m, r = dbn.fwd(be, a, W, active, relu=False, training=training, stats=slot if be.stats_done else None)
             saved["ds"] = (a, idt, m, r)
         else:
             idt = x
         for i, (conv, bn) in enumerate(zip(self.convs, self.bns)):
-            a = conv.fwd(be, h, Wm[conv.name])
+            slot = st.get(bn.name) if st else None
+            a = conv.fwd(be, h, Wm[conv.name], stats=slot)
             last = i == n - 1
-            y, m, r = bn.fwd(be, a, W, active, relu=True, res=idt if last else None, training=training)
+            y, m, r = bn.fwd(be, a, W, active, relu=True, res=idt if last else None, training=training,
+                             stats=slot if be.stats_done else None)
             saved[i] = (h, a, y, m, r)
             h = y
         if tape is not None:
@@ -843,8 +870,12 @@ class BatchedResNet(BatchedModel):
     def _forward(self, x, W, Wm, active, training, tape):
         be = self.be
         x = self._input(x)
-        a = self.stem_conv.fwd(be, x, Wm["conv1"])
-        h, m, r = self.stem_bn.fwd(be, a, W, active, relu=True, training=training)
+        st = self._bn_stat_slots(x.shape[0], x.device) if (training and getattr(be, "epilogue_stats", False)) else None
+        for blk in self.blocks:
+            blk._stats = st
+        slot = st.get(self.stem_bn.name) if st else None
+        a = self.stem_conv.fwd(be, x, Wm["conv1"], stats=slot)
+        h, m, r = self.stem_bn.fwd(be, a, W, active, relu=True, training=training, stats=slot if be.stats_done else None)
         if tape is not None:
             tape.append((x, a, h, m, r))
         for blk in self.blocks:
@@ -853,6 +884,22 @@ class BatchedResNet(BatchedModel):
         feat = h.float().mean(dim=(2, 3)).to(be.dtype)                 # [C,B,feat]
         logits = be.gemm_nt(feat, Wm["fc"], out_dtype=torch.float32) + W["fc.bias"][:, None, :]
         return logits, feat, h
+
+    def _bn_stat_slots(self, C, device):
+        """One zeroed fp32 buffer per step holding a [C, 2, ch] slot for every BatchNorm layer: the convolution that feeds
+        the layer adds its output's per-channel sums / sums of squares in its epilogue (one memset per step)."""
+        cache = getattr(self, "_bn_stats", None)
+        if cache is None or cache[0].shape[0] != C or cache[0].device != device:
+            bns = [self.stem_bn] + [b for blk in self.blocks for b in (blk.bns + ([blk.ds[1]] if blk.ds else []))]
+            total = sum(2 * b.ch for b in bns)
+            buf = torch.zeros((len(bns) and 1, C * total), dtype=torch.float32, device=device)
+            slots, off = {}, 0
+            for b in bns:
+                slots[b.name] = buf[0, off:off + C * 2 * b.ch].view(C, 2, b.ch)
+                off += C * 2 * b.ch
+            cache = self._bn_stats = (buf, slots)
+        cache[0].zero_()
+        return cache[1]
 
     def _zero_grads(self, G):
         """Per-step gradient bookkeeping of the native back-end.  Weight-gradient GEMMs of k x k (and channel-padded)

@@ -289,23 +289,28 @@ def _scratch_for(device, n_floats):
     return buf
 
 
-def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training):
-    """x [C,B,H,W,ch] bf16 contiguous -> (y, save_mean [C,ch], save_rstd [C,ch]); running stats updated in place."""
+def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu, training, stats=None):
+    """x [C,B,H,W,ch] bf16 / fp32 contiguous -> (y, save_mean [C,ch], save_rstd [C,ch]); running stats updated in place.
+    ``stats`` fp32 [C, 2, ch] contiguous: per-client sums of x and x^2 already produced by the epilogue of the convolution
+    that wrote x (``grouped_gemm(..., stats=)`` / ``conv3x3(..., stats=)``): the statistics pass over x is skipped."""
     Cn, ch = x.shape[0], x.shape[-1]
     M = x.numel() // (Cn * ch)
     x = x.contiguous()
     y = torch.empty_like(x)
     mean = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     rstd = torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
-    scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
+    use_stats = training and stats is not None
+    if use_stats and not (stats.dtype == torch.float32 and stats.is_contiguous() and stats.numel() == Cn * 2 * ch):
+        raise NativeError("bn_fwd_stacked: stats must be contiguous fp32 [C, 2, ch]")
+    scratch = stats if use_stats else _scratch_for(x.device, Cn * 64 * 2 * ch)
     fn = lib().fb_bn_fwd_stacked_f32 if x.dtype == torch.float32 else lib().fb_bn_fwd_stacked
     check(fn(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)), i32(Cn),
                                   i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(rm)),
                                   vp(ptr(rv)), i64(rm.stride(0)), vp(ptr(active)), f32(momentum), f32(eps),
-                                  i32(int(relu)), i32(int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
+                                  i32(int(relu)), i32(2 if use_stats else int(training)), vp(ptr(mean)), vp(ptr(rstd)), vp(ptr(scratch)),
                                   vp(ptr(nbt)), i64(nbt.stride(0) if nbt is not None and nbt.dim() else 1),
                                   vp(stream_ptr(x.device))), "bn_fwd_stacked")
-    count_launch(1 if (not training or _bn_fused(x)) else 2)
+    count_launch(1 if (not training or use_stats or _bn_fused(x)) else 2)
     return y, mean, rstd
 
 
@@ -384,7 +389,7 @@ def grouped_gemm_tn_supported(a, b) -> bool:
         and a.shape[0] == b.shape[0] and a.shape[2] % _al(a) == 0 and b.shape[2] % _al(a) == 0
 
 
-def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, accumulate=False, group_div=1):
+def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, accumulate=False, group_div=1, stats=None):
     d = torch.empty((G, M, N), dtype=out_dtype, device=a.device) if out is None else out
     p = FbGroupedGemm()
     p.a, p.b, p.d = a.data_ptr(), b.data_ptr(), d.data_ptr()
@@ -394,19 +399,24 @@ def _launch_gemm(fn, a, b, G, M, N, K, out_dtype, relu, bias, name, out=None, ac
     p.G, p.M, p.N, p.K = G, M, N, K
     p.lda, p.ldb, p.ldd = a.stride(1), b.stride(1), N
     p.d_fp32, p.relu, p.accumulate, p.out_group_div = int(out_dtype == torch.float32), int(relu), int(accumulate), group_div
+    if stats is not None:               # fp32 [G, 2, N] (zeroed by the caller): column sums / sums of squares of d
+        if stats.dtype != torch.float32 or stats.shape != (G, 2, N) or stats.stride(2) != 1 or stats.stride(1) != N:
+            raise NativeError(f"{name}: stats must be fp32 [G, 2, N] with contiguous [2, N] blocks")
+        p.stats, p.stats_gs = stats.data_ptr(), stats.stride(0)
     check(fn(C.byref(p), vp(stream_ptr(a.device))), name)
     count_launch()
     return d
 
 
-def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None):
+def grouped_gemm(a, b, out_dtype=torch.bfloat16, relu=False, bias=None, stats=None):
     """d[g] = a[g] @ b[g]^T   (a [G,M,K], b [G,N,K]) on the tcgen05 tensor cores (fp32 operands: kind::tf32, fp32 out)."""
     if not grouped_gemm_supported(a, b):
         raise NativeError("grouped_gemm: unsupported operand layout")
     G, M, K = a.shape
     tf32 = a.dtype == torch.float32
     fn = lib().fb_grouped_gemm_tf32 if tf32 else lib().fb_grouped_gemm_bf16
-    return _launch_gemm(fn, a, b, G, M, b.shape[1], K, torch.float32 if tf32 else out_dtype, relu, bias, "grouped_gemm")
+    return _launch_gemm(fn, a, b, G, M, b.shape[1], K, torch.float32 if tf32 else out_dtype, relu, bias, "grouped_gemm",
+                        stats=stats)
 
 
 def grouped_gemm_tn(a, b, out_dtype=torch.float32, out=None, out_is_zeroed=False):
@@ -568,7 +578,7 @@ def conv3x3_supported(x: torch.Tensor, cout: int, stride: int) -> bool:
     return ok_c and cout % 8 == 0 and cout >= 8 and pow2(Ho) and pow2(Wo) and Wo <= 128 and Wo * stride <= 256
 
 
-def _conv3x3(x, w, cout, stride, dgrad):
+def _conv3x3(x, w, cout, stride, dgrad, stats=None):
     from .native import FbConv3x3
     Cn, B, H, W, cin = x.shape
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
@@ -577,19 +587,23 @@ def _conv3x3(x, w, cout, stride, dgrad):
     p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
     p.w_gs = w.stride(0)
     p.G, p.B, p.H, p.W, p.cin, p.cout, p.stride, p.dgrad = Cn, B, H, W, cin, cout, stride, int(dgrad)
+    if stats is not None:
+        if stats.dtype != torch.float32 or stats.shape != (Cn, 2, cout) or stats.stride(2) != 1 or stats.stride(1) != cout:
+            raise NativeError("conv3x3: stats must be fp32 [C, 2, cout] with contiguous [2, cout] blocks")
+        p.stats, p.stats_gs = stats.data_ptr(), stats.stride(0)
     fn = lib().fb_conv3x3_tf32 if x.dtype == torch.float32 else lib().fb_conv3x3_bf16
     check(fn(C.byref(p), vp(stream_ptr(x.device))), "conv3x3")
     count_launch()
     return y
 
 
-def conv3x3(x: torch.Tensor, wm: torch.Tensor, stride: int = 1) -> torch.Tensor:
+def conv3x3(x: torch.Tensor, wm: torch.Tensor, stride: int = 1, stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Implicit-GEMM 3x3 convolution, pad 1: x [C,B,H,W,cin] bf16, wm [C, cout, 9*cin] ((kh,kw,cin) columns)."""
     cout = wm.shape[1]
     if not conv3x3_supported(x, cout, stride) or wm.shape[2] != 9 * x.shape[-1] or wm.stride(2) != 1 \
             or wm.stride(1) != wm.shape[2] or wm.dtype != x.dtype:
         raise NativeError("conv3x3: unsupported operand layout")
-    return _conv3x3(x, wm, cout, stride, False)
+    return _conv3x3(x, wm, cout, stride, False, stats)
 
 
 def conv3x3_dgrad(dy: torch.Tensor, wt: torch.Tensor) -> torch.Tensor:

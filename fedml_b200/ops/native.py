@@ -49,6 +49,7 @@ class FbGroupedGemm(C.Structure):
         ("lda", C.c_int32), ("ldb", C.c_int32), ("ldd", C.c_int32),
         ("d_fp32", C.c_int32), ("relu", C.c_int32), ("accumulate", C.c_int32), ("out_group_div", C.c_int32),
         ("group_inner", C.c_int32), ("a_gs2", C.c_int64), ("b_gs2", C.c_int64), ("d_gs2", C.c_int64),
+        ("stats", C.c_void_p), ("stats_gs", C.c_int64),
     ]
 
 
@@ -56,7 +57,7 @@ class FbConv3x3(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p), ("w_gs", C.c_int64),
         ("G", C.c_int32), ("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("cin", C.c_int32), ("cout", C.c_int32),
-        ("stride", C.c_int32), ("dgrad", C.c_int32),
+        ("stride", C.c_int32), ("dgrad", C.c_int32), ("stats", C.c_void_p), ("stats_gs", C.c_int64),
     ]
 
 

@@ -274,6 +274,13 @@ typedef struct {
                           * inner * x_gs.  Lets attention heads be addressed in place inside [batch][seq][heads*dh]
                           * buffers (4-D tensor maps) without split/merge-heads copies.  0: one level (x_gs only). */
   int64_t a_gs2, b_gs2, d_gs2;
+  /* optional per-column statistics of the output, accumulated (atomic adds; zero it first) by the epilogue:
+   * stats[g][0][n] += sum_m D_g[m][n], stats[g][1][n] += sum_m D_g[m][n]^2 over the values as stored; group stride stats_gs
+   * floats (>= 2*N).  These are the BatchNorm batch statistics of a convolution's output, so the normalisation
+   * that follows needs no statistics pass of its own (reference op: nn.BatchNorm2d after every conv,
+   * model/cv/resnet.py:116-136).  Needs a 16-byte aligned output, one-level groups, no split-K.  NULL: off. */
+  float* stats;
+  int64_t stats_gs;
 } FbGroupedGemm;
 int fb_grouped_gemm_bf16(const FbGroupedGemm* p, fb_stream_t stream);
 /* Weight-gradient form: D_g[M][N] = A_g^T * B_g with A_g stored [K][M] and B_g stored [K][N] (M resp. N contiguous,
@@ -294,6 +301,8 @@ typedef struct {
   void* y;           /* bf16 [G*B][Ho][Wo][cout] */
   int64_t w_gs;
   int32_t G, B, H, W, cin, cout, stride, dgrad;
+  float* stats;      /* optional [G][2][cout] output statistics, as in FbGroupedGemm; NULL: off */
+  int64_t stats_gs;
 } FbConv3x3;
 int fb_conv3x3_bf16(const FbConv3x3* p, fb_stream_t stream);
 /* Weight gradient of the same convolution, also without an im2col buffer:

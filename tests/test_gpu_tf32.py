@@ -265,3 +265,52 @@ def test_tf32_fused_sgd_restage_matches_separate_optimizer_step():
     # at TF32 resolution, not at fp32 resolution
     torch.testing.assert_close(b[2], a[2], rtol=1e-2, atol=2e-3)
     assert not torch.equal(a[2][0], base[0])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("G,M,N,K", [(5, 10240, 16, 64), (3, 200, 96, 136), (100, 640, 64, 256), (2, 640, 512, 256),
+                                     (7, 1000, 24, 72), (300, 130, 32, 32)])
+def test_gemm_epilogue_column_statistics(dtype, G, M, N, K):
+    """Column sums / sums of squares of the GEMM output accumulated by the epilogue (BatchNorm batch statistics of a
+    1x1 convolution's output) vs torch on the stored output."""
+    from fedml_b200 import ops
+    torch.manual_seed(G + M + N)
+    a = torch.randn(G, M, K, device=DEV).to(dtype)
+    b = (torch.randn(G, N, K, device=DEV) * 0.2).to(dtype)
+    stats = torch.zeros(G, 2, N, device=DEV)
+    d = ops.grouped_gemm(a, b, dtype, stats=stats)
+    d0 = ops.grouped_gemm(a, b, dtype)
+    assert torch.equal(d, d0)                                      # the tile walk differs, the result must not
+    df = d.double()
+    torch.testing.assert_close(stats[:, 0].double(), df.sum(dim=1), rtol=1e-4, atol=1e-3 * M ** 0.5)
+    torch.testing.assert_close(stats[:, 1].double(), (df * df).sum(dim=1), rtol=1e-4, atol=1e-3 * M ** 0.5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("C,B,H,cin,cout,stride", [(4, 10, 32, 16, 16, 1), (6, 4, 16, 32, 64, 2), (3, 6, 8, 64, 64, 1)])
+def test_conv3x3_epilogue_statistics_feed_batchnorm(dtype, C, B, H, cin, cout, stride):
+    """conv3x3(..., stats=) then BatchNorm from those statistics == conv3x3 then BatchNorm with its own statistics pass."""
+    from fedml_b200 import ops
+    torch.manual_seed(1)
+    x = torch.randn(C, B, H, H, cin, device=DEV).to(dtype)
+    wm = (torch.randn(C, cout, 9 * cin, device=DEV) * 0.1).to(dtype)
+    stats = torch.zeros(C, 2, cout, device=DEV)
+    y = ops.conv3x3(x, wm, stride, stats=stats)
+    assert torch.equal(y, ops.conv3x3(x, wm, stride))
+    yd = y.double().reshape(C, -1, cout)
+    torch.testing.assert_close(stats[:, 0].double(), yd.sum(dim=1), rtol=1e-4, atol=1e-2)
+    torch.testing.assert_close(stats[:, 1].double(), (yd * yd).sum(dim=1), rtol=1e-4, atol=1e-2)
+    arena = torch.randn(C, 4 * cout, device=DEV)
+    gamma, beta = arena[:, :cout], arena[:, cout:2 * cout]
+    active = torch.ones(C, device=DEV)
+    outs = []
+    for st in (None, stats):
+        rm, rv, nbt = torch.zeros(C, cout, device=DEV), torch.ones(C, cout, device=DEV), torch.zeros(C, device=DEV)
+        o = ops.bn_fwd_stacked(y, None, gamma, beta, rm, rv, nbt, active, 0.1, 1e-5, True, True, stats=st)
+        outs.append((o, rm, rv, nbt))
+    (ya, ma, ra), (yb, mb, rb) = outs[0][0], outs[1][0]
+    torch.testing.assert_close(mb, ma, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(rb, ra, rtol=1e-3, atol=1e-5)
+    torch.testing.assert_close(yb.float(), ya.float(), rtol=1e-2 if dtype == torch.bfloat16 else 1e-3, atol=2e-2 if dtype == torch.bfloat16 else 1e-3)
+    for i in (1, 2, 3):
+        torch.testing.assert_close(outs[1][i], outs[0][i], rtol=1e-3, atol=1e-5)
