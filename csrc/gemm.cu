@@ -250,8 +250,8 @@ struct GemmArgs {
 // reference's cuDNN convolutions).  A 128-byte swizzle row then holds 32 elements instead of 64, so a k-block is 32
 // elements (K-major) / 32 rows of 32-element chunks (MN-major) and one MMA covers K = 8; byte geometry of the stages,
 // descriptors' 32-byte K-major advance and the epilogue are unchanged.
-template <int MODE, bool PAIR = false, bool TF32 = false>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int MODE, bool PAIR = false, bool TF32 = false, bool STATS = false>
+__global__ void __launch_bounds__(GEMM_THREADS, STATS ? 2 : 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -279,7 +279,6 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // Tile walk.  Default: grid-stride over (group, m-tile, n-tile) with the n-tile fastest.  With output statistics a CTA
   // takes a CONTIGUOUS range of tiles, m-tile fastest, so that consecutive tiles share (group, n-tile) and the column
   // sums stay in shared memory across them: one round of global atomics per CTA and group instead of one per tile.
-  const bool STATS = a.stats != nullptr;
   const int n_ctas = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x, cta = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int tiles_all = a.G * a.m_tiles * a.n_tiles;
   const int per_cta = (tiles_all + n_ctas - 1) / n_ctas;
@@ -777,7 +776,7 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, boo
     const char* e = getenv("FB_GEMM_PAIR");
     pair_env = e ? atoi(e) : 1;
   }
-  const bool pair = pair_env != 0 && p->M >= 512 && p->N >= 128 && p->K >= 128 && group_div == 1;
+  const bool pair = pair_env != 0 && p->M >= 512 && p->N >= 128 && p->K >= 128 && group_div == 1 && !p->stats;
   if (pair) {
     const int nt = (p->N + 255) / 256;
     bn = ((p->N + nt - 1) / nt + 127) / 128 * 128;
@@ -857,6 +856,12 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, boo
     FB_CHECK_CUDA(fb_launch_pdl_cluster(grouped_gemm_kernel<MODE_, true, TF_>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,    \
                                         (cudaStream_t)stream, 2u, tmA, tmB, tmD, a));                                            \
   } while (0)
+#define FB_LAUNCH_ONE_ST(MODE_, TF_)                                                                                            \
+  do {                                                                                                                            \
+    FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, false, TF_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    FB_CHECK_CUDA(fb_launch_pdl(grouped_gemm_kernel<MODE_, false, TF_, true>, dim3(grid), dim3(GEMM_THREADS), (size_t)smem,     \
+                                (cudaStream_t)stream, tmA, tmB, tmD, a));                                                        \
+  } while (0)
 #define FB_LAUNCH_ONE(MODE_, TF_)                                                                                               \
   do {                                                                                                                            \
     FB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<MODE_, false, TF_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
@@ -881,10 +886,12 @@ static int launch_gemm(const FbGroupedGemm* p, int mode, fb_stream_t stream, boo
   if (tf32) {
     if (mode == 3) FB_LAUNCH_ONE(3, true);
     else if (mode == 2) FB_LAUNCH_ONE(2, true);
+    else if (a.stats) FB_LAUNCH_ONE_ST(0, true);
     else FB_LAUNCH_ONE(0, true);
   } else {
     if (mode == 3) FB_LAUNCH_ONE(3, false);
     else if (mode == 2) FB_LAUNCH_ONE(2, false);
+    else if (a.stats) FB_LAUNCH_ONE_ST(0, false);
     else FB_LAUNCH_ONE(0, false);
   }
   FB_CHECK_CUDA(cudaGetLastError());
@@ -941,7 +948,7 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
     const char* e = getenv("FB_CONV_PAIR");
     conv_pair_env = e ? atoi(e) : 0;
   }
-  const bool pair = conv_pair_env != 0 && p->cout >= 128 && (int64_t)p->B * plane >= 512 && inner_bytes == 128;
+  const bool pair = conv_pair_env != 0 && p->cout >= 128 && (int64_t)p->B * plane >= 512 && inner_bytes == 128 && !p->stats;
   if (pair) {
     const int nt = (p->cout + 255) / 256;
     bn_cols = ((p->cout + nt - 1) / nt + 127) / 128 * 128;
@@ -1028,7 +1035,10 @@ static int conv3x3_impl(const FbConv3x3* p, fb_stream_t stream, const bool tf32)
     else FB_LAUNCH_PAIR(4, false);
     return FB_OK;
   }
-  if (tf32) FB_LAUNCH_ONE(4, true);
+  if (a.stats) {
+    if (tf32) FB_LAUNCH_ONE_ST(4, true);
+    else FB_LAUNCH_ONE_ST(4, false);
+  } else if (tf32) FB_LAUNCH_ONE(4, true);
   else FB_LAUNCH_ONE(4, false);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;

@@ -691,3 +691,142 @@ extern "C" int fb_unstage_conv_grads(const float* scratch, int64_t scratch_ld, f
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+
+// ---------------------------------------------------------------- fused classifier head: pool -> fc -> loss -> backward
+// One launch replaces the tail of the forward pass and the head of the backward pass of a client-stacked ResNet:
+// global average pool, fc (+bias), softmax cross-entropy, d(logits), fc weight / bias gradients, d(features) and its
+// broadcast back over the H x W positions.  One CTA per client; everything between the two big tensors (h in, dh out)
+// lives in shared memory, the fc weights are read in place from the parameter arena (fp32) and all arithmetic is fp32.
+// This also takes the 10-column fc products off the library GEMM path (their K / N are not multiples of 16 bytes).
+//   h  [C][B][HW][ch] (T)      W [C][ncls][ch] fp32, client stride ld_w      bias [C][ncls], stride ld_b
+//   labels int64 [C][B] (negative or >= ncls: padding row)       row_scale [C] (NULL: 1 / B)
+//   loss [C] = row_scale * sum_b CE_b      dh [C][B][HW][ch] (T) = d loss / d h
+//   gW [C][ncls][ch] (stride ld_gw), gb [C][ncls] (stride ld_gb): gradients, overwritten
+#define HEAD_THREADS 512
+template <typename T> __device__ __forceinline__ float head_ld(const T* p);
+template <> __device__ __forceinline__ float head_ld<float>(const float* p) { return __ldg(p); }
+template <> __device__ __forceinline__ float head_ld<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ void head_st4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void head_st4(__nv_bfloat16* p, float a, float b, float c, float d) { stage_st4(p, a, b, c, d); }
+
+template <typename T>
+__global__ void __launch_bounds__(HEAD_THREADS)
+head_fwd_bwd_kernel(const T* __restrict__ h, int B, int HW, int ch, const float* __restrict__ W, int64_t ld_w,
+                    const float* __restrict__ bias, int64_t ld_b, int ncls, const int64_t* __restrict__ labels,
+                    const float* __restrict__ row_scale, float* __restrict__ loss, T* __restrict__ dh, float* __restrict__ gW,
+                    int64_t ld_gw, float* __restrict__ gb, int64_t ld_gb) {
+  extern __shared__ float sm[];
+  float* feat = sm;                        // [B][ch]  pooled features, later d(features) / HW
+  float* dlog = sm + (size_t)B * ch;       // [B][ncls] logits, then d(logits)
+  float* lrow = dlog + (size_t)B * ncls;   // [B] per-row loss
+  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = HEAD_THREADS / 32;
+  pdl_wait();
+  pdl_trigger();
+  const T* hc = h + (size_t)c * B * HW * ch;
+  const float* Wc = W + (size_t)c * ld_w;
+  const float inv_hw = 1.f / (float)HW;
+  // ---- average pool: thread <-> (image, channel); consecutive threads read consecutive channels
+  for (int idx = tid; idx < B * ch; idx += HEAD_THREADS) {
+    const int b = idx / ch, k = idx - b * ch;
+    const T* src = hc + (size_t)b * HW * ch + k;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int p = 0;
+    for (; p + 4 <= HW; p += 4) {
+      s0 += head_ld<T>(src + (size_t)p * ch);
+      s1 += head_ld<T>(src + (size_t)(p + 1) * ch);
+      s2 += head_ld<T>(src + (size_t)(p + 2) * ch);
+      s3 += head_ld<T>(src + (size_t)(p + 3) * ch);
+    }
+    for (; p < HW; ++p) s0 += head_ld<T>(src + (size_t)p * ch);
+    feat[idx] = (s0 + s1 + s2 + s3) * inv_hw;
+  }
+  __syncthreads();
+  // ---- logits: one warp per (image, class)
+  for (int pr = warp; pr < B * ncls; pr += nwarps) {
+    const int b = pr / ncls, k = pr - b * ncls;
+    const float* w = Wc + (size_t)k * ch;
+    const float* f = feat + (size_t)b * ch;
+    float s = 0.f;
+    for (int j = lane; j < ch; j += 32) s += f[j] * __ldg(w + j);
+    s = warp_sum(s);
+    if (lane == 0) dlog[pr] = s + __ldg(bias + (size_t)c * ld_b + k);
+  }
+  __syncthreads();
+  // ---- softmax cross-entropy and d(logits): one thread per image
+  const float scale = row_scale ? __ldg(row_scale + c) : 1.f / (float)B;
+  if (tid < B) {
+    float* z = dlog + (size_t)tid * ncls;
+    const int64_t y = labels[(size_t)c * B + tid];
+    const bool ignored = y < 0 || y >= ncls;
+    float mx = -INFINITY;
+    for (int k = 0; k < ncls; ++k) mx = fmaxf(mx, z[k]);
+    float se = 0.f;
+    for (int k = 0; k < ncls; ++k) se += __expf(z[k] - mx);
+    const float lse = mx + __logf(se);
+    lrow[tid] = ignored ? 0.f : lse - z[y];
+    const float sc = ignored ? 0.f : scale;
+    for (int k = 0; k < ncls; ++k) z[k] = (__expf(z[k] - lse) - (k == (int)y ? 1.f : 0.f)) * sc;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+    for (int b = 0; b < B; ++b) t += lrow[b];
+    loss[c] = t * scale;
+  }
+  // ---- fc gradients: gW[k][j] = sum_b dlog[b][k] * feat[b][j], gb[k] = sum_b dlog[b][k]
+  for (int idx = tid; idx < ncls * ch; idx += HEAD_THREADS) {
+    const int k = idx / ch, j = idx - k * ch;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dlog[b * ncls + k] * feat[(size_t)b * ch + j];
+    gW[(size_t)c * ld_gw + idx] = s;
+  }
+  if (tid < ncls) {
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dlog[b * ncls + tid];
+    gb[(size_t)c * ld_gb + tid] = s;
+  }
+  __syncthreads();
+  // ---- d(features) / HW, in place over feat
+  for (int idx = tid; idx < B * ch; idx += HEAD_THREADS) {
+    const int b = idx / ch, j = idx - b * ch;
+    float s = 0.f;
+    for (int k = 0; k < ncls; ++k) s += dlog[b * ncls + k] * __ldg(Wc + (size_t)k * ch + j);
+    feat[idx] = s * inv_hw;
+  }
+  __syncthreads();
+  // ---- broadcast over the H x W positions: dh[b][p][:] = dfeat[b][:]   (ch % 4 == 0: four channels per store)
+  T* dc = dh + (size_t)c * B * HW * ch;
+  const int ch4 = ch >> 2;
+  const int64_t total4 = (int64_t)B * HW * ch4;
+  for (int64_t i = tid; i < total4; i += HEAD_THREADS) {
+    const int j4 = (int)(i % ch4);
+    const int b = (int)(i / ((int64_t)HW * ch4));
+    const float* f = feat + (size_t)b * ch + j4 * 4;
+    head_st4(dc + i * 4, f[0], f[1], f[2], f[3]);
+  }
+}
+
+template <typename T>
+static int head_impl(const void* h, int32_t C, int32_t B, int32_t HW, int32_t ch, const float* W, int64_t ld_w, const float* bias,
+                     int64_t ld_b, int32_t ncls, const int64_t* labels, const float* row_scale, float* loss, void* dh, float* gW,
+                     int64_t ld_gw, float* gb, int64_t ld_gb, fb_stream_t stream) {
+  FB_REQUIRE(h && W && bias && labels && loss && dh && gW && gb, "fb_head_fwd_bwd: null argument");
+  FB_REQUIRE(C >= 1 && B >= 1 && B <= HEAD_THREADS && HW >= 1 && ch >= 4 && ch % 4 == 0 && ncls >= 1 && ncls <= HEAD_THREADS,
+             "fb_head_fwd_bwd: bad shape (B, ncls <= %d, ch a multiple of 4)", HEAD_THREADS);
+  const size_t smem = ((size_t)B * ch + (size_t)B * ncls + B) * sizeof(float);
+  FB_REQUIRE(smem <= 200 * 1024, "fb_head_fwd_bwd: B x (ch + ncls) = %d x (%d + %d) floats exceed shared memory", B, ch, ncls);
+  FB_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FB_CHECK_CUDA(fb_launch_pdl(head_fwd_bwd_kernel<T>, dim3(C), dim3(HEAD_THREADS), smem, (cudaStream_t)stream, (const T*)h, B, HW, ch, W,
+                              ld_w, bias, ld_b, ncls, labels, row_scale, loss, (T*)dh, gW, ld_gw, gb, ld_gb));
+  return FB_OK;
+}
+extern "C" int fb_head_fwd_bwd(const void* h, int32_t act_fp32, int32_t C, int32_t B, int32_t HW, int32_t ch, const float* W,
+                               int64_t ld_w, const float* bias, int64_t ld_b, int32_t ncls, const int64_t* labels,
+                               const float* row_scale, float* loss, void* dh, float* gW, int64_t ld_gw, float* gb, int64_t ld_gb,
+                               fb_stream_t stream) {
+  if (act_fp32)
+    return head_impl<float>(h, C, B, HW, ch, W, ld_w, bias, ld_b, ncls, labels, row_scale, loss, dh, gW, ld_gw, gb, ld_gb, stream);
+  return head_impl<__nv_bfloat16>(h, C, B, HW, ch, W, ld_w, bias, ld_b, ncls, labels, row_scale, loss, dh, gW, ld_gw, gb, ld_gb, stream);
+}

@@ -155,6 +155,18 @@ class TorchBackend:
         loss.sum().backward()
         return loss.detach(), lg.grad
 
+    def head_fwd_bwd(self, h, fc_w, fc_b, labels, row_scale, g_w, g_b):
+        """Classifier head, forward and backward: average pool -> fc -> cross-entropy; writes the fc gradients into
+        ``g_w`` / ``g_b`` and returns (loss per client [C], d loss / d h).  Reference composition of the primitives."""
+        C, B, H, W_, ch = h.shape
+        feat = h.float().mean(dim=(2, 3))
+        logits = torch.bmm(feat, fc_w.transpose(1, 2)) + fc_b[:, None, :]
+        loss, dlog = TorchBackend.xent(self, logits, labels, row_scale=row_scale)
+        g_w.copy_(torch.bmm(dlog.transpose(1, 2), feat))
+        g_b.copy_(dlog.sum(dim=1))
+        dfeat = torch.bmm(dlog, fc_w) / (H * W_)
+        return loss, dfeat.to(h.dtype)[:, :, None, None, :].expand(C, B, H, W_, ch).contiguous()
+
     def normalize_images(self, x_u8, mean, std):
         """uint8 [C,B,H,W,3] -> normalised activations in the compute dtype."""
         return ((x_u8.float() / 255.0 - mean) / std).to(self.dtype)
@@ -400,6 +412,17 @@ class NativeBackend(TorchBackend):
                                            dgamma_out=dgamma_out, dbeta_out=dbeta_out, dy2=d2)   # grads land in the arena
         self._fb("bn_bwd")
         return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres, dgamma_out=dgamma_out, dbeta_out=dbeta_out)
+
+    fused_head = os.environ.get("FB_FUSED_HEAD", "1") != "0"
+
+    def head_fwd_bwd(self, h, fc_w, fc_b, labels, row_scale, g_w, g_b):
+        C, B = h.shape[0], h.shape[1]
+        ch, ncls = h.shape[-1], fc_w.shape[1]
+        if self.fused_head and h.dtype in self._ACT and h.is_contiguous() and ch % 4 == 0 and B <= 512 and ncls <= 512 \
+                and (B * (ch + ncls + 1)) * 4 <= 200 * 1024 and fc_w.stride(1) == ch and g_w.stride(1) == ch:
+            return self.ops.head_fwd_bwd(h, fc_w, fc_b, labels, row_scale, g_w, g_b)
+        self._fb("head")
+        return super().head_fwd_bwd(h, fc_w, fc_b, labels, row_scale, g_w, g_b)
 
     def xent(self, logits, labels, pre_sigmoid=False, row_scale=None):
         C, B, ncls = logits.shape
@@ -867,7 +890,7 @@ class BatchedResNet(BatchedModel):
             x = F.pad(x, (0, self.stem_conv.cin - x.shape[-1]))       # zero channels so that K = 9*8 feeds TMA
         return x
 
-    def _forward(self, x, W, Wm, active, training, tape):
+    def _forward(self, x, W, Wm, active, training, tape, want_logits=True):
         be = self.be
         x = self._input(x)
         st = self._bn_stat_slots(x.shape[0], x.device) if (training and getattr(be, "epilogue_stats", False)) else None
@@ -880,6 +903,8 @@ class BatchedResNet(BatchedModel):
             tape.append((x, a, h, m, r))
         for blk in self.blocks:
             h = blk.fwd(be, h, W, Wm, active, training, tape)
+        if not want_logits:
+            return None, None, h
         C, B = h.shape[0], h.shape[1]
         feat = h.float().mean(dim=(2, 3)).to(be.dtype)                 # [C,B,feat]
         logits = be.gemm_nt(feat, Wm["fc"], out_dtype=torch.float32) + W["fc.bias"][:, None, :]
@@ -952,14 +977,9 @@ class BatchedResNet(BatchedModel):
         Wm = self.prepare(W)
         self._zero_grads(G)
         tape: list = []
-        logits, feat, h_last = self._forward(x, W, Wm, active, True, tape)
-        loss, dlog = be.xent(logits, y, row_scale=row_scale)
-        dlog_c = dlog.to(be.dtype)
-        G["fc.weight"].copy_(be.gemm_tn(dlog_c, feat))
-        G["fc.bias"].copy_(dlog.sum(dim=1))
-        dfeat = be.gemm_nn(dlog_c, Wm["fc"])                           # [C,B,feat]
-        C, B, H, W_, ch = h_last.shape
-        d = (dfeat.float() / (H * W_)).to(be.dtype)[:, :, None, None, :].expand(C, B, H, W_, ch).contiguous()
+        _, _, h_last = self._forward(x, W, Wm, active, True, tape, want_logits=False)
+        # pool -> fc -> loss -> fc gradients -> d(h_last): one launch on the native back-end
+        loss, d = be.head_fwd_bwd(h_last.contiguous(), W["fc.weight"], W["fc.bias"], y, row_scale, G["fc.weight"], G["fc.bias"])
         for blk, saved in zip(reversed(self.blocks), reversed(tape[1:])):
             d = blk.bwd(be, d, W, Wm, G, saved)
         x0, a, hstem, m, r = tape[0]

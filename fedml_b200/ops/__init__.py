@@ -253,6 +253,35 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, ignore_index=-100, 
     return loss, grad
 
 
+def head_fwd_bwd(h, fc_w, fc_b, labels, row_scale, g_w, g_b):
+    """Fused classifier head (csrc/train.cu head_fwd_bwd_kernel).  h [C,B,H,W,ch] bf16/fp32 contiguous; fc_w [C,ncls,ch],
+    fc_b [C,ncls], g_w, g_b: fp32 views into the stacked arenas; labels int64 [C,B] (-1 = padding); row_scale fp32 [C] or
+    None.  Returns (loss [C], dh like h)."""
+    Cn, B = h.shape[0], h.shape[1]
+    ch = h.shape[-1]
+    HW = h.numel() // (Cn * B * ch)
+    ncls = fc_w.shape[1]
+    for t, nm in ((fc_w, "fc_w"), (g_w, "g_w")):
+        if t.dtype != torch.float32 or t.stride(2) != 1 or t.stride(1) != ch:
+            raise NativeError(f"head_fwd_bwd: {nm} must be fp32 [C, ncls, ch] with contiguous [ncls, ch] blocks")
+    for t, nm in ((fc_b, "fc_b"), (g_b, "g_b")):
+        if t.dtype != torch.float32 or t.stride(1) != 1:
+            raise NativeError(f"head_fwd_bwd: {nm} must be fp32 [C, ncls] with unit inner stride")
+    if h.dtype not in (torch.float32, torch.bfloat16) or not h.is_contiguous():
+        raise NativeError("head_fwd_bwd: h must be contiguous bf16 / fp32")
+    _req(labels, torch.int64, "labels")
+    labels = labels.contiguous()
+    loss = torch.empty(Cn, dtype=torch.float32, device=h.device)
+    dh = torch.empty_like(h)
+    ld = lambda t: t.stride(0) if Cn > 1 else max(t.stride(0), t[0].numel())   # noqa: E731
+    check(lib().fb_head_fwd_bwd(vp(ptr(h)), i32(int(h.dtype == torch.float32)), i32(Cn), i32(B), i32(HW), i32(ch), vp(ptr(fc_w)),
+                                i64(ld(fc_w)), vp(ptr(fc_b)), i64(ld(fc_b)), i32(ncls), vp(ptr(labels)), vp(ptr(row_scale)),
+                                vp(ptr(loss)), vp(ptr(dh)), vp(ptr(g_w)), i64(ld(g_w)), vp(ptr(g_b)), i64(ld(g_b)),
+                                vp(stream_ptr(h.device))), "head_fwd_bwd")
+    count_launch()
+    return loss, dh
+
+
 def eval_counts(logits: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor, loss_sum: torch.Tensor,
                 pre_sigmoid=False):
     """Accumulates [correct, total, tp.., fp.., fn..] (int32 view of uint32) and the loss sum."""

@@ -466,6 +466,17 @@ int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, 
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
 
+/* Fused classifier head of a client-stacked conv net, forward AND backward in one launch (one CTA per client):
+ * global average pool -> fc (+bias) -> softmax cross-entropy -> d(logits) -> fc weight / bias gradients -> d(features)
+ * broadcast back over the H x W positions.  h / dh: [C][B][HW][ch] in bf16 (act_fp32 = 0) or fp32 (1); W, bias, gW, gb:
+ * fp32 rows of the parameter / gradient arenas (client strides ld_*); labels int64 [C][B], rows with a label outside
+ * [0, ncls) are padding; row_scale [C] (NULL: 1/B); loss [C] = row_scale * sum of the rows' cross-entropy.
+ * Replaces avgpool + fc + F.cross_entropy + their autograd nodes (model/cv/resnet.py:226-232,
+ * my_model_trainer_classification.py:44-52) and keeps the 10-column fc products off the library GEMM. */
+int fb_head_fwd_bwd(const void* h, int32_t act_fp32, int32_t C, int32_t B, int32_t HW, int32_t ch, const float* W, int64_t ld_w,
+                    const float* bias, int64_t ld_b, int32_t ncls, const int64_t* labels, const float* row_scale, float* loss,
+                    void* dh, float* gW, int64_t ld_gw, float* gb, int64_t ld_gb, fb_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Bounded cross-rank waits (failure detection; the reference has none on this path: a dead MPI worker hangs
  * FedAVGAggregator.check_whether_all_receive forever, simulation/mpi_p2p_mp/fedavg/FedAVGAggregator.py:58-66).

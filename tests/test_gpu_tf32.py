@@ -314,3 +314,31 @@ def test_conv3x3_epilogue_statistics_feed_batchnorm(dtype, C, B, H, cin, cout, s
     torch.testing.assert_close(yb.float(), ya.float(), rtol=1e-2 if dtype == torch.bfloat16 else 1e-3, atol=2e-2 if dtype == torch.bfloat16 else 1e-3)
     for i in (1, 2, 3):
         torch.testing.assert_close(outs[1][i], outs[0][i], rtol=1e-3, atol=1e-5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("C,B,H,ch,ncls", [(5, 10, 8, 256, 10), (3, 7, 4, 512, 100), (2, 16, 2, 64, 3)])
+def test_fused_classifier_head_matches_oracle(dtype, C, B, H, ch, ncls):
+    """pool -> fc -> cross-entropy -> fc gradients -> d(h) in one launch vs the composition of PyTorch ops (fp32)."""
+    from fedml_b200.models.batched import NativeBackend, TorchBackend
+    torch.manual_seed(C * 100 + ncls)
+    h = torch.randn(C, B, H, H, ch, device=DEV).to(dtype)
+    arena = torch.randn(C, ncls * ch + ncls + 8, device=DEV) * 0.1
+    garena = torch.zeros(2, C, ncls * ch + ncls + 8, device=DEV)
+    fc_w, fc_b = arena[:, :ncls * ch].view(C, ncls, ch), arena[:, ncls * ch:ncls * ch + ncls]
+    y = torch.randint(0, ncls, (C, B), device=DEV)
+    y[0, -2:] = -1                                            # padding rows
+    scale = 1.0 / (y >= 0).sum(dim=1).clamp_min(1).float()
+    res = []
+    for i, be in enumerate((TorchBackend(torch.float32), NativeBackend(dtype))):
+        g_w, g_b = garena[i][:, :ncls * ch].view(C, ncls, ch), garena[i][:, ncls * ch:ncls * ch + ncls]
+        loss, dh = be.head_fwd_bwd(h if i else h.float(), fc_w, fc_b, y, scale, g_w, g_b)
+        res.append((loss, dh, g_w, g_b))
+        assert not getattr(be, "fallbacks", {})
+    (l0, d0, w0, b0), (l1, d1, w1, b1) = res
+    torch.testing.assert_close(l1, l0, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(w1, w0, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(b1, b0, rtol=1e-4, atol=1e-6)
+    tol = dict(rtol=1e-4, atol=1e-7) if dtype == torch.float32 else dict(rtol=1e-2, atol=1e-5)
+    torch.testing.assert_close(d1.float(), d0, **tol)
+    assert float(garena[:, :, ncls * ch + ncls:].abs().sum()) == 0
