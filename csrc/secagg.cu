@@ -80,17 +80,19 @@ extern "C" int fb_ff_matmul(const uint32_t* U, int32_t n_out, int32_t n_in, cons
   return FB_OK;
 }
 
-// y = x + sum_s sign_s * PRG(seed_s) mod p.  PRG word i of seed s = Philox(counter=i/4, key=seed)[i%4] mod p.
+// y = x + sum_s sign_s * PRG(seed_s, nonce) mod p.  PRG word i of seed s = Philox(counter=(i/4, stream tag, nonce),
+// key=seed)[i%4] mod p.  The nonce (the FL round) makes every round's masks different: with a fixed mask the difference
+// of two uploads of one client would reveal the difference of its two quantised updates.
 __global__ void __launch_bounds__(256) ff_mask_kernel(const uint32_t* __restrict__ x, int64_t n,
                                                       const uint64_t* __restrict__ seeds,
                                                       const int32_t* __restrict__ signs, int n_seeds, uint32_t p,
-                                                      uint32_t* __restrict__ y) {
+                                                      uint32_t nonce, uint32_t* __restrict__ y) {
   const int64_t nvec = (n + 3) / 4;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * blockDim.x) {
     long long acc[4] = {0, 0, 0, 0};
     for (int s = 0; s < n_seeds; ++s) {
       const uint64_t seed = seeds[s];
-      const Philox4 r = philox4x32_10((uint32_t)v, (uint32_t)(v >> 32), 0x5ec0a66u, 0u, (uint32_t)seed,
+      const Philox4 r = philox4x32_10((uint32_t)v, (uint32_t)(v >> 32), 0x5ec0a66u, nonce, (uint32_t)seed,
                                       (uint32_t)(seed >> 32));
       const long long sg = signs[s];
       acc[0] += sg * (long long)(r.x % p);
@@ -110,10 +112,10 @@ __global__ void __launch_bounds__(256) ff_mask_kernel(const uint32_t* __restrict
   }
 }
 extern "C" int fb_ff_mask(const uint32_t* x, int64_t n, const uint64_t* seeds_dev, const int32_t* signs_dev,
-                          int32_t n_seeds, uint32_t p, uint32_t* y, fb_stream_t stream) {
+                          int32_t n_seeds, uint32_t p, uint32_t nonce, uint32_t* y, fb_stream_t stream) {
   FB_REQUIRE(x && y && n > 0 && n_seeds >= 0 && (n_seeds == 0 || (seeds_dev && signs_dev)), "fb_ff_mask: bad arguments");
   FB_REQUIRE(p > 1 && p < 0x80000000u, "fb_ff_mask: p must be below 2^31");
-  ff_mask_kernel<<<ff_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(x, n, seeds_dev, signs_dev, n_seeds, p, y);
+  ff_mask_kernel<<<ff_grid((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(x, n, seeds_dev, signs_dev, n_seeds, p, nonce, y);
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }

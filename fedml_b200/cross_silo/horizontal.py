@@ -106,9 +106,13 @@ class FedMLServerManager(ServerManager):
         self._timer.start()
 
     def _deadline(self, rnd):
-        if rnd == self.round_idx and self.aggregator.received_indices():
+        if rnd != self.round_idx:
+            return
+        if self.aggregator.received_indices():
             logging.warning("round %d deadline hit: partial aggregation", rnd)
             self._finish_round(self.aggregator.received_indices())
+        else:
+            self._arm_deadline()        # nothing in yet (slow first result): keep waiting in deadline-sized steps
 
     def handle_message_receive_model_from_client(self, msg_params):
         sender = int(msg_params.get(MyMessage.MSG_ARG_KEY_SENDER))

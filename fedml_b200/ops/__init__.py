@@ -202,12 +202,12 @@ def ff_matmul(U: torch.Tensor, X: torch.Tensor, p: int) -> torch.Tensor:
     return out
 
 
-def ff_mask(x: torch.Tensor, seeds: Sequence[int], signs: Sequence[int], p: int) -> torch.Tensor:
+def ff_mask(x: torch.Tensor, seeds: Sequence[int], signs: Sequence[int], p: int, nonce: int = 0) -> torch.Tensor:
     dev = x.device
     y = torch.empty_like(x)
     s = torch.tensor([int(v) - (1 << 64) if int(v) >= (1 << 63) else int(v) for v in seeds], dtype=torch.int64).to(dev)
     g = torch.tensor(list(signs), dtype=torch.int32).to(dev)
-    check(lib().fb_ff_mask(vp(ptr(x)), i64(x.numel()), vp(ptr(s)), vp(ptr(g)), i32(len(seeds)), u32(p), vp(ptr(y)),
+    check(lib().fb_ff_mask(vp(ptr(x)), i64(x.numel()), vp(ptr(s)), vp(ptr(g)), i32(len(seeds)), u32(p), u32(int(nonce) & 0xFFFFFFFF), vp(ptr(y)),
                            vp(stream_ptr(dev))), "ff_mask")
     count_launch()
     return y

@@ -231,6 +231,8 @@ class FedAVGServerManager(ServerManager):
         if got:
             logging.warning("round %d deadline: aggregating %d of %d results", rnd, len(got), self.aggregator.worker_num)
             self._finish_round(got)
+        else:
+            self._arm_deadline()        # nothing in yet: keep waiting in deadline-sized steps
 
     def handle_message_receive_model_from_client(self, msg_params):
         sender = msg_params.get(MyMessage.MSG_ARG_KEY_SENDER)

@@ -200,9 +200,10 @@ int fb_ff_dequantize(const uint32_t* q, int64_t n, float inv_scale, uint32_t p, 
 /* out[i][d] = sum_j U[i][j] * X[j][d] mod p  — LCC/BGW encode and decode (mpc_function.py:62-75,111-136,201-217). */
 int fb_ff_matmul(const uint32_t* U, int32_t n_out, int32_t n_in, const uint32_t* X, int64_t d, int64_t ldx,
                  uint32_t p, uint32_t* out, int64_t ldo, fb_stream_t stream);
-/* y = x + sum_{s} sign[s] * PRG(seed[s]) mod p — pairwise additive masks expanded in registers. */
+/* y = x + sum_{s} sign[s] * PRG(seed[s], nonce) mod p — additive masks expanded in registers; `nonce` (the round index)
+ * enters the Philox counter so no mask is ever used twice. */
 int fb_ff_mask(const uint32_t* x, int64_t n, const uint64_t* seeds_dev, const int32_t* signs_dev, int32_t n_seeds,
-               uint32_t p, uint32_t* y, fb_stream_t stream);
+               uint32_t p, uint32_t nonce, uint32_t* y, fb_stream_t stream);
 /* acc = (acc + x) mod p */
 int fb_ff_add(uint32_t* acc, const uint32_t* x, int64_t n, uint32_t p, fb_stream_t stream);
 

@@ -273,3 +273,50 @@ def test_hs_fft_matches_numpy_oracle():
     a, b, c = amplitude_normalize(x, run)
     a2, b2, c2 = amplitude_normalize_numpy(x.numpy(), run.numpy())
     assert np.abs(a.numpy() - a2).max() < 1e-4 and np.abs(b.numpy() - b2).max() < 1e-4
+
+
+def test_secagg_keys_are_secret_masks_are_per_round_and_double_masking_recovers_dropouts():
+    """private keys must not be derivable from client ids, masks must differ between rounds, and a
+    server must not be able to unmask a client it (falsely) declares dropped."""
+    import numpy as np
+    import torch
+    from fedml_b200.core.security.mpc_function import DEFAULT_PRIME as p
+    from fedml_b200.core.security.secagg import (SecAggClient, SecAggServer, prg_mask, secure_weighted_mean, shamir_reconstruct,
+                                                 shamir_share)
+    # keys: two clients with the same id get different private keys (OS entropy), ids do not determine them
+    assert SecAggClient(3).sk != SecAggClient(3).sk
+    a, b = SecAggClient(0), SecAggClient(1)
+    a.agree({1: b.pk}); b.agree({0: a.pk})
+    assert a.seeds[1] == b.seeds[0]                                  # Diffie-Hellman from public keys alone
+    # the PRG takes the round: same seed, different round -> different mask; uploads of two rounds do not share a mask
+    assert not np.array_equal(prg_mask(99, 64, p, 0), prg_mask(99, 64, p, 1))
+    x = torch.randn(257)
+    y0 = a.mask(x, 1.0, 2 ** 16, [0, 1], round_idx=0).numpy()
+    y1 = a.mask(x, 1.0, 2 ** 16, [0, 1], round_idx=1).numpy()
+    assert not np.array_equal(y0, y1)                                # same update, different rounds: difference is not q(x)-q(x)=0
+    # Shamir: t shares reconstruct, the secret is not among fewer
+    sh = shamir_share(123456, list(range(5)), 3, p)
+    assert shamir_reconstruct({i: sh[i] for i in (0, 2, 4)}, p) == 123456
+    assert shamir_reconstruct({i: sh[i] for i in (1, 3)}, p) != 123456
+    # a participant refuses to reveal both kinds of share for one client
+    c = SecAggClient(2)
+    c.receive_shares(1, {"b": 5, "sk": 6})
+    with pytest.raises(ValueError):
+        c.reveal_shares([0, 1], [1])
+    # end to end with double masking, with and without a dropout, at a non-zero round
+    ups = [torch.randn(501) for _ in range(5)]
+    w = [3.0, 1.0, 2.0, 5.0, 4.0]
+    ref = sum(wi * u for wi, u in zip(w, ups)) / sum(w)
+    assert float((secure_weighted_mean(ups, w, round_idx=4) - ref).abs().max()) < 1e-3
+    alive = [0, 1, 3, 4]
+    ref2 = sum(w[i] * ups[i] for i in alive) / sum(w[i] for i in alive)
+    assert float((secure_weighted_mean(ups, w, dropped=[2], round_idx=9) - ref2).abs().max()) < 1e-3
+    # the server alone (no revealed shares) cannot unmask: a sum without the self masks removed is garbage
+    cl = [SecAggClient(i) for i in range(3)]
+    pks = {c_.cid: c_.pk for c_ in cl}
+    for c_ in cl:
+        c_.agree(pks)
+        c_.new_round_secrets([0, 1, 2])
+    masked = {i: cl[i].mask(ups[i], 1 / 3, 2 ** 16, [0, 1, 2], 0, self_mask=True) for i in range(3)}
+    garbage = SecAggServer(p).aggregate(masked, 2 ** 16, [0, 1, 2])
+    assert float((garbage - sum(ups[:3]) / 3).abs().max()) > 1.0
