@@ -259,19 +259,64 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
   const float* pp[8];
 #pragma unroll
   for (int q = 0; q < 8; ++q) pp[q] = (G > 1 && q < G) ? p.peer_partial[q] : nullptr;
+  // averaged sum -> (aggregate noise) -> server optimizer -> value to store, for the float4 lane v
+  auto finish = [&](const int64_t v, const float4 tot) -> float4 {
+    const int64_t j = v * 4;
+    const bool train = j < Pt;
+    const float inv = train ? p.inv_total : p.inv_total_buf;
+    float4 avg = make_float4(tot.x * inv, tot.y * inv, tot.z * inv, tot.w * inv);
+    if (train && p.agg_noise_std > 0.f) {
+      // one Gaussian draw on the aggregate: identical in distribution to summing the per-client draws
+      const float4 z = philox_normal4(p.seed, p.round, 0x00A66E6u, (uint64_t)v);
+      avg.x += p.agg_noise_std * z.x; avg.y += p.agg_noise_std * z.y; avg.z += p.agg_noise_std * z.z; avg.w += p.agg_noise_std * z.w;
+    }
+    float4 out = avg;
+    if (train && (p.opt != FB_OPT_NONE || p.self_coef != 0.f)) {
+      const float4 w = *reinterpret_cast<const float4*>(p.global_model + j);
+      if (p.self_coef != 0.f) {
+        avg.x += p.self_coef * w.x; avg.y += p.self_coef * w.y; avg.z += p.self_coef * w.z; avg.w += p.self_coef * w.w;
+      }
+      out = opt_apply4(o, w, avg, mom, sec, j);
+    }
+    return out;
+  };
   for (int s = s_begin; s < s_end; ++s) {
     const int64_t lo = (int64_t)s * S4, hi = min(lo + S4, nvec);
+    if (use_mc) {
+      // NVLS: the switch reduces the G replicas of a 16-byte word and returns the sum (one load instead of G) and
+      // multimem.st writes the result into all G replicas.  Four independent reductions are in flight per thread before
+      // the first epilogue: a reduction is a full NVLink round trip (~ 3-4 us), so bytes in flight, not issue rate, set
+      // the bandwidth (2 CTAs x 256 threads x 4 x 16 B = 32 KiB per SM).
+      constexpr int U = 4;
+      for (int64_t v0 = lo + (int64_t)block * T + tid; v0 < hi; v0 += (int64_t)U * stride) {
+        float4 t[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t v = v0 + (int64_t)u * stride;
+          if (v < hi)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(t[u].x), "=f"(t[u].y), "=f"(t[u].z), "=f"(t[u].w)
+                         : "l"(p.mc_partial + v * 4)
+                         : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t v = v0 + (int64_t)u * stride;
+          if (v < hi) {
+            const float4 out = finish(v, t[u]);
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.mc_global + v * 4), "f"(out.x),
+                         "f"(out.y), "f"(out.z), "f"(out.w)
+                         : "memory");
+          }
+        }
+      }
+      continue;
+    }
     for (int64_t v = lo + (int64_t)block * T + tid; v < hi; v += stride) {
       const int64_t j = v * 4;
       float4 tot = make_float4(0, 0, 0, 0);
       if (G == 1) {
         tot = local_accumulate(p, j, v, dp, clip, noise, wts, wts_b, s_scale);
-      } else if (use_mc) {
-        // NVLS: the switch reduces the G replicas of this 16-byte word and returns the sum (one load instead of G)
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(tot.x), "=f"(tot.y), "=f"(tot.z), "=f"(tot.w)
-                     : "l"(p.mc_partial + j)
-                     : "memory");
       } else if (G <= 8) {
         // all peer loads are issued before the first add so that G NVLink round trips overlap
         float4 xs[8];
@@ -290,27 +335,8 @@ __device__ void round_body(const FbRoundParams& p, const int block, const int nb
           tot.x += x.x; tot.y += x.y; tot.z += x.z; tot.w += x.w;
         }
       }
-      const bool train = j < Pt;
-      const float inv = train ? p.inv_total : p.inv_total_buf;
-      float4 avg = make_float4(tot.x * inv, tot.y * inv, tot.z * inv, tot.w * inv);
-      if (train && p.agg_noise_std > 0.f) {
-        // one Gaussian draw on the aggregate: identical in distribution to summing the per-client draws
-        const float4 z = philox_normal4(p.seed, p.round, 0x00A66E6u, (uint64_t)v);
-        avg.x += p.agg_noise_std * z.x; avg.y += p.agg_noise_std * z.y; avg.z += p.agg_noise_std * z.z; avg.w += p.agg_noise_std * z.w;
-      }
-      float4 out = avg;
-      if (train && (p.opt != FB_OPT_NONE || p.self_coef != 0.f)) {
-        const float4 w = *reinterpret_cast<const float4*>(p.global_model + j);
-        if (p.self_coef != 0.f) {
-          avg.x += p.self_coef * w.x; avg.y += p.self_coef * w.y; avg.z += p.self_coef * w.z; avg.w += p.self_coef * w.w;
-        }
-        out = opt_apply4(o, w, avg, mom, sec, j);
-      }
-      if (use_mc) {
-        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p.mc_global + j), "f"(out.x),
-                     "f"(out.y), "f"(out.z), "f"(out.w)
-                     : "memory");
-      } else if (p.two_shot && G > 1) {
+      const float4 out = finish(v, tot);
+      if (p.two_shot && G > 1) {
         for (int q = 0; q < G; ++q) st4((q == rank ? p.global_model : p.peer_global[q]) + j, out);
       } else {
         st4(p.global_model + j, out);

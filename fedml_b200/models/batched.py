@@ -159,7 +159,7 @@ class TorchBackend:
         """Classifier head, forward and backward: average pool -> fc -> cross-entropy; writes the fc gradients into
         ``g_w`` / ``g_b`` and returns (loss per client [C], d loss / d h).  Reference composition of the primitives."""
         C, B, H, W_, ch = h.shape
-        feat = h.float().mean(dim=(2, 3))
+        feat = h.to(fc_w.dtype).mean(dim=(2, 3))
         logits = torch.bmm(feat, fc_w.transpose(1, 2)) + fc_b[:, None, :]
         loss, dlog = TorchBackend.xent(self, logits, labels, row_scale=row_scale)
         g_w.copy_(torch.bmm(dlog.transpose(1, 2), feat))
@@ -338,7 +338,7 @@ class NativeBackend(TorchBackend):
 
     # BatchNorm batch statistics produced by the epilogue of the convolution GEMM instead of a statistics pass over the
     # activation.  OPT-IN (FB_EPILOGUE_STATS=1): correct (tests/test_gpu_tf32.py) but measured SLOWER on the headline bench
-    # (tf32 112.6 -> 119.6 ms/round, bf16 68.9 -> 82.8): these skinny GEMMs (N = 16..64, K = 16..256) are bound by their
+    # (tf32 113.9 -> 115.4 ms/round, bf16 69.3 -> 73.4 with the statistics variant held to 2 CTAs per SM): these skinny GEMMs (N = 16..64, K = 16..256) are bound by their
     # four epilogue warps, so 32 shared-memory reads + 64 FMAs per 32 x 32 output box cost more there than the saved
     # read of the activation costs in the BatchNorm kernel.  The atomic column sums also make runs non-reproducible.
     epilogue_stats = os.environ.get("FB_EPILOGUE_STATS", "0") == "1"

@@ -200,7 +200,10 @@ class NCCLSimulator:
                 # "tf32" / "fp32": fp32 activations and weights in HBM, TF32 tensor-core products (the reference's precision)
                 dtype = {"bf16": torch.bfloat16, "fp32": torch.float32, "tf32": torch.float32, "fp16": torch.float16}[
                     str(getattr(args, "compute_dtype", "bf16")).lower()]
-                backend = NativeBackend(dtype)
+                # batched_backend "torch": the same client-batched control flow on plain PyTorch fp32 ops (the oracle the
+                # multi-GPU tests compare the native path against)
+                backend = TorchBackend(torch.float32) if str(getattr(args, "batched_backend", "native")) == "torch" \
+                    else NativeBackend(dtype)
             else:
                 backend = TorchBackend(torch.float32)
             self.batched = make_batched(self.model, backend)

@@ -94,6 +94,68 @@ def main():
         dist.all_gather(gathered, flat)
         out[f"sim_{tag}"] = {"identical": all(torch.equal(gathered[0], g_) for g_ in gathered), "finite": bool(torch.isfinite(flat).all()),
                              "norm": float(flat.norm())}
+    # ---- ResNets on the tf32 native path (CUDA graphs on) over the ranks: the global model after ONE round (two local steps)
+    # is written to a file; the test compares it element-wise with one-process runs on the native path and on the plain
+    # PyTorch fp32 back-end (FB_SIM_BACKEND=torch).  One round only: at random init with batch 10 these nets amplify a
+    # last-bit difference by orders of magnitude per step (profiles/precision_sensitivity.md), so longer trajectories of
+    # two correct implementations are not comparable element-wise.
+    dump = os.environ.get("FB_DUMP_DIR")
+    if dump:
+        be = os.environ.get("FB_SIM_BACKEND", "native")
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        for mname in ("resnet18", "resnet56"):
+            base = dict(training_type="simulation", backend="NCCL", dataset="cifar10", model=mname, client_num_in_total=16,
+                        client_num_per_round=8, comm_round=2, epochs=1, batch_size=10, learning_rate=0.03, partition_method="homo",
+                        frequency_of_the_test=0, synthetic_train_size=16 * 20, log_level="WARNING", using_gpu=True,
+                        compute_dtype="tf32", batched_backend=be, use_cuda_graphs=(be == "native"), random_seed=0)
+            a = fedml.init(Arguments.from_dict(base))
+            ds, ncls = fedml.data.load(a)
+            torch.manual_seed(0)
+            model = fedml.models.create(a, ncls)
+            sim = SimulatorNCCL(a, dev, ds, model).simulator
+            init = sim.global_flat.clone()
+            sim.train_one_round(0)
+            torch.cuda.synchronize()
+            if sim.engine is not None:
+                sim.engine.check_spin_errors()
+            flat = sim.global_flat.clone()
+            gathered = [torch.zeros_like(flat) for _ in range(world)]
+            dist.all_gather(gathered, flat)
+            out[f"sim_{mname}"] = {"identical": all(torch.equal(gathered[0], g_) for g_ in gathered),
+                                   "finite": bool(torch.isfinite(flat).all()), "norm": float(flat.norm())}
+            if rank == 0:
+                torch.save({"init": init.cpu(), "flat": flat.cpu(), "P_train": sim.P_train},
+                           os.path.join(dump, f"{mname}_{be}_{world}.pt"))
+            del sim
+            torch.cuda.empty_cache()
+        # checkpoint with several ranks is a collective (two-shot FedAdam: the sharded moments are gathered), then resume
+        base = dict(training_type="simulation", backend="NCCL", dataset="mnist", model="lr", client_num_per_round=8, comm_round=4,
+                    batch_size=10, learning_rate=0.03, frequency_of_the_test=0, synthetic_train_size=2000, mnist_client_num=16,
+                    log_level="WARNING", using_gpu=True, compute_dtype="fp32", use_cuda_graphs=False, federated_optimizer="FedOpt",
+                    server_optimizer="adam", server_lr=0.01, two_shot=True)
+        a = fedml.init(Arguments.from_dict(base))
+        ds, ncls = fedml.data.load(a)
+        torch.manual_seed(0)
+        model = fedml.models.create(a, ncls)
+        sim = SimulatorNCCL(a, dev, ds, model).simulator
+        for r in range(2):
+            sim.train_one_round(r)
+        ck = os.path.join(dump, f"ckpt_lr_{be}_{world}")
+        sim.save(ck)
+        dist.barrier()
+        for r in range(2, 4):
+            sim.train_one_round(r)
+        torch.cuda.synchronize()
+        straight = sim.global_flat.clone()
+        torch.manual_seed(0)
+        sim2 = SimulatorNCCL(a, dev, ds, fedml.models.create(a, ncls)).simulator
+        assert sim2.resume(ck) == 2
+        for r in range(2, 4):
+            sim2.train_one_round(r)
+        torch.cuda.synchronize()
+        out["resume_fedadam_two_shot"] = {"max_diff": float((sim2.global_flat - straight).abs().max()),
+                                          "two_shot": bool(sim.engine.two_shot) if sim.engine is not None else None}
     if rank == 0:
         print("MULTIGPU_RESULT " + json.dumps(out), flush=True)
     dist.barrier()
