@@ -201,6 +201,186 @@ extern "C" int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t
   return FB_OK;
 }
 
+// ---------------------------------------------------------------- many clients (K > 128): sorted runs + merge-select
+// Step 1 (fb_robust_sort_runs): the rows are cut into runs of `run_len` <= 128 consecutive rows; for every coordinate
+// each run is sorted IN PLACE with the register network above (a run's rows live on one GPU, the GPU that trained
+// them, so this is local HBM traffic; median / trimmed mean do not care which client a value came from).
+// Step 2 (fb_robust_select_runs): the owner of a coordinate shard stages a tile of all K values in shared memory as
+// before and finds the wanted order statistic bit by bit, but a bit step now costs one binary search per run
+// (sum over runs of lower_bound(run, T) = number of keys < T) instead of a counting pass over all K keys:
+// 32 x R x log2(run_len) probes per coordinate instead of 32 x K (K = 512, runs of 64: 1536 instead of 16384).
+template <int KP>
+__global__ void __launch_bounds__(SORT_THREADS) robust_sort_runs_kernel(float* const* __restrict__ rows, int K, int run_len,
+                                                                        int64_t j0, int64_t j1) {
+  const int r0 = blockIdx.y * run_len;
+  const int len = min(run_len, K - r0);
+  for (int64_t j = j0 + (int64_t)blockIdx.x * SORT_THREADS + threadIdx.x; j < j1; j += (int64_t)gridDim.x * SORT_THREADS) {
+    float v[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+      v[k] = INFINITY;
+      if (k < len) v[k] = rows[r0 + k][j];
+    }
+#pragma unroll
+    for (int size = 2; size <= KP; size <<= 1) {
+#pragma unroll
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+        for (int i = 0; i < KP; ++i) {
+          const int l = i ^ stride;
+          if (l > i) {
+            const float lo = fminf(v[i], v[l]), hi = fmaxf(v[i], v[l]);
+            const bool up = (i & size) == 0;
+            v[i] = up ? lo : hi;
+            v[l] = up ? hi : lo;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KP; ++k)
+      if (k < len) rows[r0 + k][j] = v[k];
+  }
+}
+extern "C" int fb_robust_sort_runs(float* const* rows_dev, int32_t K, int32_t run_len, int64_t j0, int64_t j1,
+                                   fb_stream_t stream) {
+  FB_REQUIRE(rows_dev && K >= 1 && run_len >= 1 && run_len <= 128 && j1 >= j0, "fb_robust_sort_runs: run_len must be in [1, 128]");
+  if (j1 == j0) return FB_OK;
+  const int runs = (K + run_len - 1) / run_len;
+  const int64_t nt = (j1 - j0 + SORT_THREADS - 1) / SORT_THREADS;
+  int64_t gx = ((int64_t)fb_num_sms() * 8 + runs - 1) / runs;
+  if (gx > nt) gx = nt;
+  if (gx < 1) gx = 1;
+  const dim3 grid((unsigned)gx, (unsigned)runs);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (run_len <= 8) robust_sort_runs_kernel<8><<<grid, SORT_THREADS, 0, st>>>(rows_dev, K, run_len, j0, j1);
+  else if (run_len <= 16) robust_sort_runs_kernel<16><<<grid, SORT_THREADS, 0, st>>>(rows_dev, K, run_len, j0, j1);
+  else if (run_len <= 32) robust_sort_runs_kernel<32><<<grid, SORT_THREADS, 0, st>>>(rows_dev, K, run_len, j0, j1);
+  else if (run_len <= 64) robust_sort_runs_kernel<64><<<grid, SORT_THREADS, 0, st>>>(rows_dev, K, run_len, j0, j1);
+  else robust_sort_runs_kernel<128><<<grid, SORT_THREADS, 0, st>>>(rows_dev, K, run_len, j0, j1);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
+// rank-th smallest key of column `col` when rows [r*L, (r+1)*L) of `keys` are sorted ascending for every run r
+__device__ __forceinline__ uint32_t select_rank_runs(const uint32_t* keys, int K, int L, int col, int sub, int rank) {
+  const int R = (K + L - 1) / L;
+  uint32_t prefix = 0;
+  for (int bit = 31; bit >= 0; --bit) {
+    const uint32_t T = prefix | (1u << bit);
+    int cnt = 0;                                    // keys < T
+    for (int r = sub; r < R; r += SEL_SPLIT) {
+      const uint32_t* run = keys + (size_t)r * L * SEL_LD + col;
+      int lo = 0, hi = min(L, K - r * L);           // lower_bound over run[0 .. hi)
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (run[(size_t)mid * SEL_LD] < T) lo = mid + 1; else hi = mid;
+      }
+      cnt += lo;
+    }
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);
+    if (rank >= cnt) prefix = T;                    // at most `rank` keys lie below T: the answer is >= T
+  }
+  return prefix;
+}
+
+// K rows are staged; only the K_valid smallest values per coordinate are real (padding rows hold +inf and sort last)
+__global__ void __launch_bounds__(SEL_THREADS) robust_select_runs_kernel(const float* const* __restrict__ rows, int K, int K_valid, int L,
+                                                                         int64_t j0, int64_t j1, int mode, int trim,
+                                                                         float* const* __restrict__ outs, int n_out) {
+  extern __shared__ uint32_t keys[];  // [K][SEL_LD]
+  const int tid = threadIdx.x;
+  const int col = tid / SEL_SPLIT, sub = tid % SEL_SPLIT;
+  const int64_t ntiles = (j1 - j0 + SEL_TILE - 1) / SEL_TILE;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t base = j0 + tile * SEL_TILE;
+    const int width = (int)min((int64_t)SEL_TILE, j1 - base);
+    __syncthreads();
+    if (width == SEL_TILE && ((base & 3) == 0)) {
+      // 16-byte loads: a quarter-warp covers the 64 coordinates of one row
+      for (int idx = tid; idx < K * (SEL_TILE / 4); idx += SEL_THREADS) {
+        const int k = idx / (SEL_TILE / 4), t4 = idx % (SEL_TILE / 4);
+        float4 x;
+        const float* src = rows[k] + base + t4 * 4;
+        asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "l"(src) : "memory");
+        uint32_t* dst = keys + (size_t)k * SEL_LD + t4 * 4;
+        dst[0] = f2key(x.x); dst[1] = f2key(x.y); dst[2] = f2key(x.z); dst[3] = f2key(x.w);
+      }
+    } else {
+      for (int idx = tid; idx < K * SEL_TILE; idx += SEL_THREADS) {
+        const int k = idx / SEL_TILE, t = idx % SEL_TILE;
+        float x = 0.f;
+        if (t < width) {
+          const float* src = rows[k] + base + t;
+          asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(x) : "l"(src) : "memory");
+        }
+        keys[(size_t)k * SEL_LD + t] = f2key(x);
+      }
+    }
+    __syncthreads();
+    float result;
+    if (mode == 0) {
+      result = key2f(select_rank_runs(keys, K, L, col, sub, (K_valid - 1) / 2));
+    } else {
+      const uint32_t klo = select_rank_runs(keys, K, L, col, sub, trim);
+      const uint32_t khi = select_rank_runs(keys, K, L, col, sub, K_valid - trim - 1);
+      if (klo == khi) {
+        result = key2f(klo);
+      } else {
+        float sum = 0.f;
+        int lt_lo = 0, eq_lo = 0, lt_hi = 0;
+        for (int k = sub; k < K; k += SEL_SPLIT) {
+          const uint32_t x = keys[(size_t)k * SEL_LD + col];
+          lt_lo += x < klo;
+          eq_lo += x == klo;
+          lt_hi += x < khi;
+          if (x > klo && x < khi) sum += key2f(x);
+        }
+#pragma unroll
+        for (int o = 1; o < SEL_SPLIT; o <<= 1) {
+          sum += __shfl_xor_sync(0xffffffffu, sum, o);
+          lt_lo += __shfl_xor_sync(0xffffffffu, lt_lo, o);
+          eq_lo += __shfl_xor_sync(0xffffffffu, eq_lo, o);
+          lt_hi += __shfl_xor_sync(0xffffffffu, lt_hi, o);
+        }
+        const int n_lo = lt_lo + eq_lo - trim;
+        const int n_hi = (K_valid - trim) - lt_hi;
+        sum += (float)n_lo * key2f(klo) + (float)n_hi * key2f(khi);
+        result = sum / (float)(K_valid - 2 * trim);
+      }
+    }
+    if (sub == 0 && col < width) {
+      for (int o = 0; o < n_out; ++o) outs[o][base + col] = result;
+    }
+  }
+}
+extern "C" int fb_robust_select_runs(const float* const* rows_dev, int32_t K, int32_t K_valid, int32_t run_len, int64_t j0,
+                                     int64_t j1, int32_t mode, int32_t trim, float* const* outs_dev, int32_t n_out,
+                                     fb_stream_t stream) {
+  FB_REQUIRE(rows_dev && outs_dev && K >= 1 && K_valid >= 1 && K_valid <= K && run_len >= 1 && j1 >= j0 && n_out >= 1,
+             "fb_robust_select_runs: bad arguments");
+  FB_REQUIRE(mode == 0 || (trim >= 0 && 2 * trim < K_valid), "fb_robust_select_runs: trim removes every client");
+  const size_t smem = (size_t)K * SEL_LD * sizeof(uint32_t);
+  if (smem > 220 * 1024) {
+    fb_set_error("fb_robust_select_runs: K=%d exceeds the %d clients that fit one shared-memory tile", K,
+                 (int)(220 * 1024 / (SEL_LD * sizeof(uint32_t))));
+    return FB_ERR_LIMIT;
+  }
+  if (j1 == j0) return FB_OK;
+  FB_CHECK_CUDA(cudaFuncSetAttribute(robust_select_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, robust_select_runs_kernel, SEL_THREADS, smem);
+  if (per_sm < 1) per_sm = 1;
+  const int64_t ntiles = (j1 - j0 + SEL_TILE - 1) / SEL_TILE;
+  int64_t grid = (int64_t)per_sm * fb_num_sms();
+  if (grid > ntiles) grid = ntiles;
+  robust_select_runs_kernel<<<(int)grid, SEL_THREADS, smem, (cudaStream_t)stream>>>(rows_dev, K, K_valid, run_len, j0, j1, mode,
+                                                                                     trim, outs_dev, n_out);
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+
 // ---------------------------------------------------------------- K7: pack for the Gram GEMM
 // dst_hi[k][j-j0] = bf16(x), dst_lo = bf16(x - float(hi)) with x = rows[k][j] - ref[j].
 __global__ void __launch_bounds__(256) krum_pack_kernel(const float* const* __restrict__ rows,

@@ -134,21 +134,52 @@ def robust_select(rows_table: torch.Tensor, K: int, j0: int, j1: int, mode: str,
     count_launch()
 
 
-def coordinate_median(stack: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Lower median over dim 0 of a [K, P] fp32 stack (rows may be strided)."""
-    return _select_local(stack, "median", 0, out)
+def robust_sort_runs(rows_table: torch.Tensor, K: int, run_len: int, j0: int, j1: int):
+    """Sort every run of ``run_len`` consecutive rows in place, per coordinate (step 1 of the many-client path)."""
+    check(lib().fb_robust_sort_runs(vp(ptr(rows_table)), i32(K), i32(run_len), i64(j0), i64(j1),
+                                    vp(stream_ptr(rows_table.device))), "robust_sort_runs")
+    count_launch()
 
 
-def trimmed_mean(stack: torch.Tensor, trim: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    return _select_local(stack, "trimmed_mean", trim, out)
+def robust_select_runs(rows_table: torch.Tensor, K: int, K_valid: int, run_len: int, j0: int, j1: int, mode: str, trim: int,
+                       outs_table: torch.Tensor, n_out: int):
+    m = {"median": 0, "trimmed_mean": 1}[mode]
+    check(lib().fb_robust_select_runs(vp(ptr(rows_table)), i32(K), i32(K_valid), i32(run_len), i64(j0), i64(j1), i32(m), i32(trim),
+                                      vp(ptr(outs_table)), i32(n_out), vp(stream_ptr(rows_table.device))), "robust_select_runs")
+    count_launch()
 
 
-def _select_local(stack, mode, trim, out):
+def run_length_for(rows_per_rank: int) -> int:
+    """Largest run length <= 128 that divides the rows a rank holds (runs must not straddle ranks); 0: use the plain path."""
+    for L in range(min(128, rows_per_rank), 15, -1):
+        if rows_per_rank % L == 0:
+            return L
+    return 0
+
+
+def coordinate_median(stack: torch.Tensor, out: Optional[torch.Tensor] = None, inplace: bool = False) -> torch.Tensor:
+    """Lower median over dim 0 of a [K, P] fp32 stack (rows may be strided).  K > 128 takes the sorted-run path, which
+    permutes the values inside each run of rows: on a copy unless ``inplace``."""
+    return _select_local(stack, "median", 0, out, inplace)
+
+
+def trimmed_mean(stack: torch.Tensor, trim: int, out: Optional[torch.Tensor] = None, inplace: bool = False) -> torch.Tensor:
+    return _select_local(stack, "trimmed_mean", trim, out, inplace)
+
+
+def _select_local(stack, mode, trim, out, inplace=False):
     _req(stack, torch.float32, "stack")
     K, P = stack.shape
     out = torch.empty(P, dtype=torch.float32, device=stack.device) if out is None else out
-    rows = ptr_table([stack.data_ptr() + k * stack.stride(0) * 4 for k in range(K)], stack.device)
     outs = ptr_table([out.data_ptr()], stack.device)
+    L = run_length_for(K) if K > 128 else 0
+    if L:
+        work = stack if inplace else stack.clone()        # the sorted-run path reorders values inside each run
+        rows = ptr_table([work.data_ptr() + k * work.stride(0) * 4 for k in range(K)], stack.device)
+        robust_sort_runs(rows, K, L, 0, P)
+        robust_select_runs(rows, K, K, L, 0, P, mode, trim, outs, 1)
+        return out
+    rows = ptr_table([stack.data_ptr() + k * stack.stride(0) * 4 for k in range(K)], stack.device)
     robust_select(rows, K, 0, P, mode, trim, outs, 1)
     return out
 

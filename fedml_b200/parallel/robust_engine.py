@@ -44,7 +44,24 @@ def aggregate(sim, kind, K, trim, f, m, my_pos, sizes, round_idx):
     j0, j1 = min(rank * shard, P), min((rank + 1) * shard, P)
     if kind in ("median", "trimmed_mean"):
         outs = eng._peer_global if G > 1 else ops.ptr_table([eng.global_model.data_ptr()], sim.device)
-        ops.robust_select(rows, K, j0, j1, kind, trim, outs, G)
+        L = ops.run_length_for(sim.C_max) if K > 128 else 0
+        if L:
+            # many clients: every rank sorts runs of its OWN rows in place (local HBM), then the shard owners merge-select
+            # over all G * C_max rows.  Rows of a rank that drew fewer than C_max clients are filled with +inf: they sort
+            # to the end of their run and K_valid = K keeps them out of the order statistics.
+            n_mine = len(my_pos)
+            if n_mine < sim.C_max:
+                sim.stack[n_mine:].fill_(float("inf"))
+            own = ops.ptr_table([sim.stack.data_ptr() + i * sim.P * 4 for i in range(sim.C_max)], sim.device)
+            ops.robust_sort_runs(own, sim.C_max, L, 0, P)
+            eng.device_barrier(2)                           # every rank's runs are sorted
+            allrows = []
+            for q in range(G):
+                base = sim.stack.data_ptr() if sim.stack_region is None else sim.stack_region.peer_ptr("stack", q)
+                allrows += [base + i * sim.P * 4 for i in range(sim.C_max)]
+            ops.robust_select_runs(ops.ptr_table(allrows, sim.device), G * sim.C_max, K, L, j0, j1, kind, trim, outs, G)
+        else:
+            ops.robust_select(rows, K, j0, j1, kind, trim, outs, G)
         eng.device_barrier(1)                               # all shards have landed everywhere
         return
     # ---- Krum

@@ -337,4 +337,8 @@ def FedML_FedAvg_distributed(args, process_id, worker_number, comm, device, data
 
 FedML_FedOpt_distributed = FedML_FedAvg_distributed          # noqa: N816  server optimizer chosen by args
 FedML_FedProx_distributed = FedML_FedAvg_distributed         # noqa: N816  proximal term lives in the trainer
-FedML_FedAvgRobust_distributed = FedML_FedAvg_distributed    # noqa: N816  defence chosen by args.defense_type
+
+
+def FedML_FedAvgRobust_distributed(*a, **kw):                # noqa: N802  backdoor protocol: see fedavg_robust.py
+    from .fedavg_robust import FedML_FedAvgRobust_distributed as impl
+    return impl(*a, **kw)

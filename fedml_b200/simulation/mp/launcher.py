@@ -11,7 +11,10 @@ from ...constants import canonical_optimizer_name
 
 def _entry(name):
     from . import fedavg as F
-    if name in ("FedAvg", "FedOpt", "FedProx", "FedAvg_robust"):
+    if name == "FedAvg_robust":
+        from .fedavg_robust import FedML_FedAvgRobust_distributed
+        return FedML_FedAvgRobust_distributed
+    if name in ("FedAvg", "FedOpt", "FedProx"):
         return F.FedML_FedAvg_distributed
     if name == "base_framework":
         from .templates import FedML_Base_distributed

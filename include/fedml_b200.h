@@ -175,6 +175,15 @@ int64_t fb_peer_barrier_flag_bytes(int32_t G);
  * ------------------------------------------------------------------------------------------- */
 int fb_robust_select(const float* const* rows_dev, int32_t K, int64_t j0, int64_t j1, int32_t mode, int32_t trim,
                      float* const* outs_dev, int32_t n_out, fb_stream_t stream);
+/* Many clients (K > 128: BASELINE config "512 clients per round"): sorted runs + merge-select.
+ * fb_robust_sort_runs sorts, for every coordinate in [j0, j1), each run of `run_len` (<= 128) consecutive rows of the
+ * table IN PLACE (register sorting network; the rows must be writable from this GPU — a rank sorts the rows it trained).
+ * fb_robust_select_runs then finds the lower median (mode 0) or the trimmed mean (mode 1) with one binary search per run
+ * and bit instead of a pass over all K keys.  K rows are read; only the K_valid smallest values per coordinate count
+ * (padding rows must hold +inf).  Semantics as fb_robust_select (robust_aggregation.py:65-99, lower median). */
+int fb_robust_sort_runs(float* const* rows_dev, int32_t K, int32_t run_len, int64_t j0, int64_t j1, fb_stream_t stream);
+int fb_robust_select_runs(const float* const* rows_dev, int32_t K, int32_t K_valid, int32_t run_len, int64_t j0, int64_t j1,
+                          int32_t mode, int32_t trim, float* const* outs_dev, int32_t n_out, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K7  Krum: pack (centre + bf16 hi/lo split) and Gram matrix on tcgen05 tensor cores, then scores.

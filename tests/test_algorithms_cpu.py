@@ -276,3 +276,32 @@ def test_custom_client_trainer_and_server_aggregator_hooks():
     ds, model = build(a)
     fedml.FedMLRunner(a, CPU, ds, model, client_trainer=T(model, a), server_aggregator=S(model, a)).run()
     assert calls["train"] == 8 and calls["agg"] == 2
+
+
+def test_fedavg_robust_backdoor_protocol():
+    """Backdoor robust FedAvg (reference mpi_p2p_mp/fedavg_robust): the attacker (client 1) trains on the poisoned
+    loader and is force-sampled every attack_freq rounds; the server defends (norm-diff clipping) and evaluates the raw
+    task and the targeted task."""
+    from fedml_b200.simulation.mp.fedavg_robust import ATTACKER_CLIENT_INDEX, FedAvgRobustAggregator, FedAvgRobustTrainer
+    a = mk(federated_optimizer="FedAvg_robust", backend="MPI", worker_num=3, client_num_per_round=3, comm_round=4, attack_freq=2,
+           defense_type="norm_diff_clipping", norm_bound=5.0, frequency_of_the_test=1, run_id="robust-bd", ci=1, target_label=7)
+    ds, model = build(a)
+    agg = SimulatorMPI(a, CPU, ds, model).run()
+    assert isinstance(agg, FedAvgRobustAggregator)
+    assert agg.adversary_fl_rounds == [1, 3]
+    for r in range(4):
+        picked = list(agg.client_sampling(r, int(a.client_num_in_total), 3))
+        assert (picked[0] == ATTACKER_CLIENT_INDEX and len(picked) == 4) == (r in (1, 3))
+    # dual evaluation every round: raw-task accuracy in history, targeted-task accuracy next to it
+    assert len(agg.history) == 4 and all("targeted_acc" in h and "test_acc" in h for h in agg.history)
+    assert [h["attacker_round"] for h in agg.attack_history] == [False, True, False, True]
+    # the attacker's trainer swaps in the poisoned loader and its sample count
+    from fedml_b200.data import load_poisoned_dataset_from_edge_case_examples
+    ptrain, _, ttest, n_poison = load_poisoned_dataset_from_edge_case_examples(a)
+    tr = FedAvgRobustTrainer(0, ds[5], ds[4], ds[6], ds[0], CPU, a, agg.trainer, poisoned_train_loader=ptrain,
+                             num_dps_poisoned_dataset=n_poison)
+    tr.update_dataset(ATTACKER_CLIENT_INDEX)
+    assert tr.train_local is ptrain and tr.local_sample_number == n_poison
+    tr.update_dataset(0)
+    assert tr.train_local is ds[5][0]
+    assert all(int(y.unique()[0]) == 7 and y.unique().numel() == 1 for _, y in ttest)

@@ -120,3 +120,37 @@ def test_dead_rank_is_reported_not_waited_for_forever():
         torch.testing.assert_close(outs[0], ref, rtol=1e-5, atol=2e-5)
     finally:
         RoundEngine.set_spin_timeout(20000)
+
+
+@pytest.mark.parametrize("K,P", [(512, 4 * 5003), (300, 4 * 1001), (192, 2048)])
+def test_many_client_median_and_trimmed_mean_sorted_runs(K, P):
+    """K > 128 rows: in-place sorted runs + merge-select (fb_robust_sort_runs / fb_robust_select_runs) == torch (lower
+    median, trimmed mean), incl. +inf padding rows that must not count."""
+    from fedml_b200 import ops
+    torch.manual_seed(K)
+    x = torch.randn(K, P, device=DEV)
+    x[:, :64] = torch.randint(-2, 3, (K, 64), device=DEV).float()        # heavy ties
+    med = ops.coordinate_median(x)
+    assert torch.equal(med, torch.median(x, dim=0).values)
+    trim = K // 10
+    tm = ops.trimmed_mean(x, trim)
+    ref = torch.sort(x, dim=0).values[trim:K - trim].double().mean(dim=0)
+    torch.testing.assert_close(tm.double(), ref, rtol=1e-5, atol=1e-6)
+    # padded layout as the multi-GPU engine uses it: G blocks of C_max rows, the tail of each block is +inf
+    G, C_max = 4, (K + 3) // 4 + 3
+    L = ops.run_length_for(C_max)
+    if L:
+        pad = torch.full((G * C_max, P), float("inf"), device=DEV)
+        counts = [(K + G - 1 - g) // G for g in range(G)]
+        o = 0
+        for g, n in enumerate(counts):
+            pad[g * C_max:g * C_max + n] = x[o:o + n]
+            o += n
+        rows = ops.ptr_table([pad.data_ptr() + k * P * 4 for k in range(G * C_max)], DEV)
+        ops.robust_sort_runs(rows, G * C_max, L, 0, P)
+        out = torch.empty(P, device=DEV)
+        outs = ops.ptr_table([out.data_ptr()], DEV)
+        ops.robust_select_runs(rows, G * C_max, K, L, 0, P, "median", 0, outs, 1)
+        assert torch.equal(out, torch.median(x, dim=0).values)
+        ops.robust_select_runs(rows, G * C_max, K, L, 0, P, "trimmed_mean", trim, outs, 1)
+        torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-6)
