@@ -145,7 +145,8 @@ def load(args):
     ds = load_federated(args)
     bs = int(args.batch_size)
     image_like = ds.transform is not None           # CIFAR-style loaders use drop_last=True (cifar10/data_loader.py:209-214)
-    dataset8 = ds.as_tuple(bs, drop_last=image_like and bs > 0)
+    dl = getattr(args, "drop_last", None)             # explicit override; default follows the reference's loaders
+    dataset8 = ds.as_tuple(bs, drop_last=(image_like if dl is None else bool(dl)) and bs > 0)
     if centralized:
         dataset8 = merge_to_single_client(dataset8)
         args.client_num_in_total = 1

@@ -752,6 +752,7 @@ class BatchedLogisticRegression(BatchedModel):
 class BatchedResNet(BatchedModel):
     """CIFAR-stem / 3x3-stem ResNets (ResNet-56 Bottleneck, ResNet-18 BasicBlock) over C clients."""
     input_kind = "image_u8_nhwc"
+    uses_batch_statistics = True      # BatchNorm: padding rows of a ragged batch would enter the statistics
 
     def __init__(self, module: ResNet, backend: TorchBackend, mean=None, std=None):
         self.be = backend

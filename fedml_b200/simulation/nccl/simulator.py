@@ -208,10 +208,7 @@ class NCCLSimulator:
                 backend = TorchBackend(torch.float32)
             self.batched = make_batched(self.model, backend)
         if self.batched is None:
-            self.seq_model = self.model.to(self.device)
-            self.seq_flat = torch.zeros(self.P, dtype=torch.float32, device=self.device)
-            bind_module_to_flat(self.seq_model, self.layout, self.seq_flat)
-            self.seq_trainer = self.custom_trainer or create_model_trainer(self.seq_model, args)
+            self._ensure_sequential()
         self.lr = float(getattr(args, "learning_rate", getattr(args, "lr", 0.03)))
         self.momentum = float(getattr(args, "momentum", 0.0) or 0.0) if self.alg == "FedNova" or \
             str(getattr(args, "client_optimizer", "sgd")).lower() == "sgd_momentum" else 0.0
@@ -245,7 +242,8 @@ class NCCLSimulator:
         C = self.C_max
         if self.fed is None:
             return self._stage_round_inputs_generic(my_clients, round_idx)
-        drop_last = self.fed.transform is not None and bs > 0
+        dl = getattr(args, "drop_last", None)
+        drop_last = (self.fed.transform is not None if dl is None else bool(dl)) and bs > 0
         offs = self.fed.client_offsets
         plans = []
         for cid in my_clients:
@@ -292,6 +290,9 @@ class NCCLSimulator:
         torch.index_select(ys, 0, flat, out=Yp)
         Yp.view(C, S, B, *ys.shape[1:])[~valid] = -1
         inv_valid = 1.0 / valid.sum(dim=2).clamp_min(1).to(torch.float32)
+        # a step that is active for a client but not full: its padding slots would enter BatchNorm batch statistics
+        nvalid = valid.sum(dim=2)
+        self._ragged_round = bool(((nvalid > 0) & (nvalid < B)).any())
         if self.cuda:
             if getattr(self, "_copy_stream", None) is None:
                 self._copy_stream = torch.cuda.Stream(self.device)
@@ -402,6 +403,18 @@ class NCCLSimulator:
             if self.mu:
                 d = d + self.mu * (w - anchor[:n])
             w.sub_(lr_vec[:C, None] * d)
+
+    def _ensure_sequential(self):
+        """Per-client eager trainer on arena-bound parameters (families without a batched executor, custom trainers, and
+        rounds the batched executor must not take)."""
+        if getattr(self, "seq_trainer", None) is None:
+            import copy
+            # the fallback of a batched executor gets its own module; otherwise bind the caller's module (a custom trainer
+            # trains that very object)
+            self.seq_model = (copy.deepcopy(self.model) if getattr(self, "batched", None) is not None else self.model).to(self.device)
+            self.seq_flat = torch.zeros(self.P, dtype=torch.float32, device=self.device)
+            bind_module_to_flat(self.seq_model, self.layout, self.seq_flat)
+            self.seq_trainer = self.custom_trainer or create_model_trainer(self.seq_model, self.args)
 
     def _client_groups(self):
         """Optional (``client_groups`` > 1): split the clients of this GPU into groups that advance on separate
@@ -566,7 +579,19 @@ class NCCLSimulator:
             ops.broadcast_rows(self.global_flat, self.stack)
         else:
             self.stack.copy_(self.global_flat[None, :].expand_as(self.stack))
-        if self.batched is not None:
+        use_batched = self.batched is not None
+        if use_batched and staged is not None and getattr(self, "_ragged_round", False) \
+                and getattr(self.batched, "uses_batch_statistics", False):
+            # BatchNorm normalises over the rows of a batch: the padded slots of a ragged last batch (n % batch_size != 0
+            # without drop_last) would change mean / variance and the gradients.  Such rounds train client by client,
+            # exactly as the reference does (my_model_trainer_classification.py:21-70).
+            if not getattr(self, "_warned_ragged", False):
+                logging.warning("ragged batches with a BatchNorm model: this round trains sequentially (set drop_last / a "
+                                "batch size dividing the client sizes to use the client-batched kernels)")
+                self._warned_ragged = True
+            use_batched = False
+            self._ensure_sequential()
+        if use_batched:
             if staged is not None:
                 self._train_batched(staged, sizes)
         else:

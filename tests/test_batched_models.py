@@ -154,3 +154,41 @@ def test_batched_distilbert_dropout_masks_are_consistent():
     an = float((gstack.double() * direction.double()).sum())
     assert an > 0 and abs(fd - an) < 0.03 * an, (fd, an)
     assert l0.shape == (C,)
+
+
+def test_ragged_batches_with_batchnorm_train_sequentially():
+    """a BatchNorm model whose clients have n % batch_size != 0 (no drop_last) must not take the client-batched
+    path (padding rows would enter the batch statistics): the round trains client by client and equals the per-client
+    PyTorch loop."""
+    import copy
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.simulation import SimulatorNCCL
+    from fedml_b200.simulation.trainers import create_model_trainer
+    a = fedml.init(Arguments.from_dict(dict(
+        training_type="simulation", backend="NCCL", dataset="cifar10", model="resnet56", client_num_in_total=4,
+        client_num_per_round=2, comm_round=1, epochs=1, batch_size=8, learning_rate=0.05, partition_method="homo",
+        frequency_of_the_test=0, synthetic_train_size=4 * 13, log_level="ERROR", using_gpu=False, random_seed=0,
+        shuffle_clients=False, drop_last=False)))             # no drop_last: 13 samples = one full batch + 5 ragged
+    ds, ncls = fedml.data.load(a)
+    torch.manual_seed(0)
+    model = fedml.models.create(a, ncls)
+    sim = SimulatorNCCL(a, torch.device("cpu"), ds, copy.deepcopy(model)).simulator
+    assert sim.batched is not None and sim.batched.uses_batch_statistics
+    init = copy.deepcopy(model.state_dict())
+    sim.train_one_round(0)
+    assert sim._ragged_round and sim._warned_ragged
+    # oracle: the same two clients trained one after another with the stock trainer, sample-weighted average
+    from fedml_b200.simulation.sp.fedavg_api import client_sampling
+    picked = client_sampling(0, 4, 2)
+    acc, tot = None, 0
+    for cid in picked:
+        m = copy.deepcopy(model); m.load_state_dict(init)
+        tr = create_model_trainer(m, a); tr.set_id(cid)
+        tr.train(ds[5][cid], torch.device("cpu"), a)
+        n = ds[4][cid]; tot += n
+        sd = {k: v.double() * n for k, v in m.state_dict().items()}
+        acc = sd if acc is None else {k: acc[k] + sd[k] for k in acc}
+    got = sim.global_state_dict()
+    for k, v in acc.items():
+        torch.testing.assert_close(got[k].double(), v / tot, rtol=1e-4, atol=1e-5, msg=k)
