@@ -265,33 +265,18 @@ extern "C" int fb_robust_sort_runs(float* const* rows_dev, int32_t K, int32_t ru
 // rank-th smallest key of column `col` when rows [r*L, (r+1)*L) of `keys` are sorted ascending for every run r
 __device__ __forceinline__ uint32_t select_rank_runs(const uint32_t* keys, int K, int L, int col, int sub, int rank) {
   const int R = (K + L - 1) / L;
-  const int steps = 32 - __clz(L);                  // ceil(log2(L + 1)): iterations until every search has converged
   uint32_t prefix = 0;
   for (int bit = 31; bit >= 0; --bit) {
     const uint32_t T = prefix | (1u << bit);
     int cnt = 0;                                    // keys < T
-    // the lane's runs are searched in lock-step, eight at a time: the probes of different runs are independent loads,
-    // so their shared-memory latencies overlap (a single binary search is a chain of dependent loads)
-    for (int rb = sub; rb < R; rb += SEL_SPLIT * 8) {
-      int lo[8], hi[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int r = rb + i * SEL_SPLIT;
-        lo[i] = 0;
-        hi[i] = r < R ? min(L, K - r * L) : 0;
+    for (int r = sub; r < R; r += SEL_SPLIT) {
+      const uint32_t* run = keys + (size_t)r * L * SEL_LD + col;
+      int lo = 0, hi = min(L, K - r * L);           // lower_bound over run[0 .. hi)
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (run[(size_t)mid * SEL_LD] < T) lo = mid + 1; else hi = mid;
       }
-      for (int it = 0; it < steps; ++it) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (lo[i] < hi[i]) {
-            const int mid = (lo[i] + hi[i]) >> 1;
-            const uint32_t v = keys[((size_t)(rb + i * SEL_SPLIT) * L + mid) * SEL_LD + col];
-            if (v < T) lo[i] = mid + 1; else hi[i] = mid;
-          }
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) cnt += lo[i];
+      cnt += lo;
     }
     cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
     cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);

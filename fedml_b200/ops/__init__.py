@@ -151,7 +151,8 @@ def robust_select_runs(rows_table: torch.Tensor, K: int, K_valid: int, run_len: 
 
 def run_length_for(rows_per_rank: int) -> int:
     """Largest run length <= 128 that divides the rows a rank holds (runs must not straddle ranks); 0: use the plain path."""
-    for L in range(min(128, rows_per_rank), 15, -1):
+    # runs of at most 64 rows first: the 64-input sorting network stays in registers, the 128-input one spills
+    for L in list(range(min(64, rows_per_rank), 15, -1)) + list(range(min(128, rows_per_rank), 64, -1)):
         if rows_per_rank % L == 0:
             return L
     return 0

@@ -764,6 +764,12 @@ class NCCLSimulator:
         stats = {"round": round_idx}
         if self.fed is None:
             return stats
+        if self.cuda and self.batched is not None and bool(getattr(self.args, "native_eval", True)) \
+                and isinstance(getattr(self.batched, "be", None), NativeBackend):
+            try:
+                return self._evaluate_native(dict(stats), round_idx)
+            except (NotImplementedError, TypeError) as exc:      # executor without an eval forward for this input kind
+                logging.info("native evaluation not available for this model (%s): eager evaluation", exc)
         sd = self.layout.unflatten(self.global_flat)
         model = self.model.to(self.device)
         model.load_state_dict(sd)
@@ -787,6 +793,56 @@ class NCCLSimulator:
                 dist.all_reduce(vec)
             stats[f"{split}_acc"] = float(vec[0] / vec[2].clamp_min(1))
             stats[f"{split}_loss"] = float(vec[1] / vec[2].clamp_min(1))
+        self.history.append(stats)
+        if self.metrics is not None:
+            self.metrics.log({"Train/Acc": stats["train_acc"], "Train/Loss": stats["train_loss"],
+                              "Test/Acc": stats["test_acc"], "Test/Loss": stats["test_loss"], "round": round_idx})
+        return stats
+
+    def _evaluate_native(self, stats, round_idx):
+        """Evaluation on the native kernels: the client-batched executor's eval-mode forward over the packed arrays (one
+        "client" = the global model, read in place from the round engine's buffer) and the fused counter kernel
+        ``fb_eval_counts`` (K15: arg-max, correct / total, per-class TP / FP / FN and the summed loss in one pass over the
+        logits, no host sync per batch).  Replaces my_model_trainer_classification.py:95-154 (per-client eager test loop)."""
+        from ... import ops
+        from ...models.batched import make_batched
+        ex = getattr(self, "_eval_exec", None)
+        if ex is None:
+            ex = self._eval_exec = make_batched(self.model, NativeBackend(self.batched.be.dtype))
+            if ex is None:
+                raise NotImplementedError
+        g = self.global_flat.view(1, -1)
+        W1 = self.layout.stacked_views(g)
+        if hasattr(ex, "invalidate_stage"):
+            ex.invalidate_stage()
+        ncls = int(self.class_num)
+        pre_sig = bool(getattr(ex, "pre_sigmoid", False))
+        cap = int(getattr(self.args, "eval_sample_cap", 0) or 0)
+        bs = int(getattr(self.args, "eval_batch_size", 1024))
+        for split, (x, y) in (("train", (self.fed.x, self.fed.y)), ("test", (self.fed.x_test, self.fed.y_test))):
+            n = x.shape[0] if not cap else min(cap, x.shape[0])
+            lo, hi = (n * self.rank) // self.world, (n * (self.rank + 1)) // self.world
+            counts = torch.zeros(2 + 3 * ncls, dtype=torch.int32, device=self.device)
+            loss_sum = torch.zeros(1, dtype=torch.float32, device=self.device)
+            for i in range(lo, hi, bs):
+                xb = x[i:min(i + bs, hi)].to(self.device, non_blocking=True)
+                yb = y[i:min(i + bs, hi)].to(self.device, non_blocking=True).to(torch.int64)
+                if ex.input_kind != "image_u8_nhwc":
+                    xb = self.fed._prep(xb) if xb.dtype == torch.uint8 else xb
+                logits = ex.logits(xb.unsqueeze(0), W1)
+                ops.eval_counts(logits.reshape(-1, ncls).float().contiguous(), yb.reshape(-1).contiguous(), counts, loss_sum,
+                                pre_sigmoid=pre_sig)
+            vec = torch.cat([counts.to(torch.float64), loss_sum.to(torch.float64)])
+            if self.world > 1:
+                dist.all_reduce(vec)
+            vec = vec.cpu()
+            total = max(float(vec[1]), 1.0)
+            tp, fp, fn = vec[2:2 + ncls], vec[2 + ncls:2 + 2 * ncls], vec[2 + 2 * ncls:2 + 3 * ncls]
+            stats[f"{split}_acc"] = float(vec[0]) / total
+            stats[f"{split}_loss"] = float(vec[-1]) / total
+            stats[f"{split}_precision"] = float((tp / (tp + fp).clamp_min(1)).mean())
+            stats[f"{split}_recall"] = float((tp / (tp + fn).clamp_min(1)).mean())
+        stats["eval_path"] = "native"
         self.history.append(stats)
         if self.metrics is not None:
             self.metrics.log({"Train/Acc": stats["train_acc"], "Train/Loss": stats["train_loss"],

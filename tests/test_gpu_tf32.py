@@ -342,3 +342,33 @@ def test_fused_classifier_head_matches_oracle(dtype, C, B, H, ch, ncls):
     tol = dict(rtol=1e-4, atol=1e-7) if dtype == torch.float32 else dict(rtol=1e-2, atol=1e-5)
     torch.testing.assert_close(d1.float(), d0, **tol)
     assert float(garena[:, :, ncls * ch + ncls:].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("model,dataset,dtype", [("resnet56", "cifar10", "tf32"), ("resnet56", "cifar10", "bf16"), ("lr", "mnist", "fp32")])
+def test_simulator_native_evaluation_matches_eager(model, dataset, dtype):
+    """NCCLSimulator.evaluate on the native kernels (batched eval forward + fused fb_eval_counts) == the eager PyTorch
+    evaluation of the same global model."""
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.simulation import SimulatorNCCL
+    a = fedml.init(Arguments.from_dict(dict(
+        training_type="simulation", backend="NCCL", dataset=dataset, model=model, client_num_in_total=8, client_num_per_round=4,
+        comm_round=1, epochs=1, batch_size=10, learning_rate=0.03, partition_method="homo", frequency_of_the_test=0,
+        synthetic_train_size=8 * 40, log_level="ERROR", using_gpu=True, compute_dtype=dtype, random_seed=0, mnist_client_num=8)))
+    ds, ncls = fedml.data.load(a)
+    torch.manual_seed(0)
+    sim = SimulatorNCCL(a, torch.device(DEV), ds, fedml.models.create(a, ncls)).simulator
+    sim.train_one_round(0)
+    from fedml_b200.ops import native
+    before = native.LAUNCHES[0]
+    nat = sim.evaluate(0)
+    assert nat.get("eval_path") == "native" and native.LAUNCHES[0] > before
+    a.native_eval = False
+    eag = sim.evaluate(0)
+    assert eag.get("eval_path") is None
+    tol = 3e-2 if dtype == "bf16" else 5e-3
+    for k in ("train_acc", "test_acc"):
+        assert abs(nat[k] - eag[k]) <= tol + 1e-9, (k, nat[k], eag[k])
+    for k in ("train_loss", "test_loss"):
+        assert abs(nat[k] - eag[k]) <= tol * max(1.0, abs(eag[k])), (k, nat[k], eag[k])
+    assert 0.0 <= nat["test_precision"] <= 1.0 and 0.0 <= nat["test_recall"] <= 1.0
