@@ -139,12 +139,23 @@ def load_federated(args) -> FederatedDataset:
     return ds
 
 
+def _augment_enabled(args) -> bool:
+    """``augment: true`` (or "cifar"): the reference's CIFAR-family train transform, RandomCrop(32, 4) + flip + Cutout(16)
+    (data/cifar10/data_loader.py:58-103).  Off by default: the synthetic benchmarks measure training, not input noise."""
+    v = getattr(args, "augment", False)
+    return bool(v) and str(v).lower() not in ("0", "false", "none", "no")
+
+
 def load(args):
     logging.info("load_data. dataset_name = %s", args.dataset)
     centralized = int(args.client_num_in_total) == 1 and getattr(args, "training_type", "") != "cross_silo"
     ds = load_federated(args)
     bs = int(args.batch_size)
     image_like = ds.transform is not None           # CIFAR-style loaders use drop_last=True (cifar10/data_loader.py:209-214)
+    if image_like and _augment_enabled(args) and ds.x.dtype == torch.uint8 and ds.x.dim() == 4:
+        from .augment import TrainAugment
+        ds.train_augment = TrainAugment(int(getattr(args, "random_seed", 0)) + 7919, pad=int(getattr(args, "augment_pad", 4)),
+                                        cutout=int(getattr(args, "augment_cutout", 16)))
     dl = getattr(args, "drop_last", None)             # explicit override; default follows the reference's loaders
     dataset8 = ds.as_tuple(bs, drop_last=(image_like if dl is None else bool(dl)) and bs > 0)
     if centralized:

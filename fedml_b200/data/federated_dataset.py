@@ -28,6 +28,7 @@ class FederatedDataset:
         self.test_offsets = None if test_offsets is None else np.asarray(test_offsets, dtype=np.int64)
         self.class_num = int(class_num)
         self.transform = transform      # callable(x_raw_batch) -> float tensor, applied at batch time
+        self.train_augment = None       # callable(uint8 NHWC batch) -> uint8 NHWC batch, TRAIN batches only (data/augment.py)
         self.name, self.task = name, task
 
     # ------------------------------------------------------------------ basic facts
@@ -60,16 +61,18 @@ class FederatedDataset:
     def _prep(self, xb: torch.Tensor) -> torch.Tensor:
         return self.transform(xb) if self.transform is not None else xb
 
-    def batches(self, xs: torch.Tensor, ys: torch.Tensor, batch_size: int, drop_last: bool = False,
+    def batches(self, xs: torch.Tensor, ys: torch.Tensor, batch_size: int, drop_last: bool = False, train: bool = False,
                 ) -> List[Tuple[torch.Tensor, torch.Tensor]]:
+        aug = self.train_augment if (train and xs.dtype == torch.uint8) else None
+        prep = (lambda xb: self._prep(aug(xb))) if aug is not None else self._prep
         n = xs.shape[0]
         if batch_size <= 0 or batch_size >= n:
-            return [(self._prep(xs), ys)] if n else []
+            return [(prep(xs), ys)] if n else []
         out = []
         for i in range(0, n, batch_size):
             if drop_last and i + batch_size > n:
                 break
-            out.append((self._prep(xs[i:i + batch_size]), ys[i:i + batch_size]))
+            out.append((prep(xs[i:i + batch_size]), ys[i:i + batch_size]))
         return out
 
     def as_tuple(self, batch_size: int, drop_last: bool = False, test_batch_size: int = 0) -> list:
@@ -124,8 +127,9 @@ class _LazyClientBatches(dict):
         if not (0 <= int(cid) < self.ds.client_num):
             raise KeyError(cid)
         xs, ys = self.ds.client_slice(cid) if self.train else self.ds.client_test_slice(cid)
-        val = self.ds.batches(xs, ys, self.bs, self.drop_last)
-        self[cid] = val
+        val = self.ds.batches(xs, ys, self.bs, self.drop_last, train=self.train)
+        if not (self.train and self.ds.train_augment is not None):
+            self[cid] = val          # augmented train batches are NOT cached: every visit of a client is a fresh random pass
         return val
 
     def __contains__(self, cid):

@@ -285,6 +285,28 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, ignore_index=-100, 
     return loss, grad
 
 
+def augment_cifar(x: torch.Tensor, seed: int, nonce, pad: int = 4, cutout: int = 16, mean_u8=(125, 123, 114),
+                  first_index: int = 0) -> torch.Tensor:
+    """uint8 [N, H, W, C] -> randomly cropped / flipped / cut-out copy (csrc/augment.cu).  ``nonce``: int or a device
+    int64 tensor of one element (read by the kernel, so CUDA-graph replays differ)."""
+    _req(x, torch.uint8, "x")
+    if x.dim() != 4 or not x.is_contiguous() or x.shape[3] > 4:
+        raise NativeError("augment_cifar: expected contiguous uint8 [N, H, W, C<=4]")
+    N, H, W, Cc = x.shape
+    y = torch.empty_like(x)
+    fill = 0
+    for c in range(Cc):
+        fill |= (int(mean_u8[c]) & 0xFF if c < len(mean_u8) else 0) << (8 * c)
+    dev_nonce = nonce if torch.is_tensor(nonce) else None
+    if dev_nonce is not None and (dev_nonce.dtype != torch.int64 or not dev_nonce.is_cuda):
+        raise NativeError("augment_cifar: a tensor nonce must be a CUDA int64 tensor")
+    check(lib().fb_augment_cifar(vp(ptr(x)), vp(ptr(y)), i64(N), i32(H), i32(W), i32(Cc), u64(int(seed) & (2 ** 64 - 1)),
+                                 u32(0 if dev_nonce is not None else int(nonce) & 0xFFFFFFFF), vp(ptr(dev_nonce)), i32(pad),
+                                 i32(cutout), u32(fill), i64(first_index), vp(stream_ptr(x.device))), "augment_cifar")
+    count_launch()
+    return y
+
+
 def head_fwd_bwd(h, fc_w, fc_b, labels, row_scale, g_w, g_b):
     """Fused classifier head (csrc/train.cu head_fwd_bwd_kernel).  h [C,B,H,W,ch] bf16/fp32 contiguous; fc_w [C,ncls,ch],
     fc_b [C,ncls], g_w, g_b: fp32 views into the stacked arenas; labels int64 [C,B] (-1 = padding); row_scale fp32 [C] or

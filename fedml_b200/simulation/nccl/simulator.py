@@ -466,7 +466,14 @@ class NCCLSimulator:
         fused = self._fused_sgd()
         if fused:
             self.batched.set_fused_sgd(st["lr"])
-        loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
+        x_in = st["x"]
+        if st.get("aug_nonce") is not None and x_in.dtype == torch.uint8 and x_in.dim() == 5:
+            # train-time crop / flip / Cutout inside the step (and inside the captured graph): the nonce lives on the
+            # device and is bumped by the host copy before every step, so each replay draws new transforms
+            from ...data.augment import augment_cifar
+            aug = self.fed.train_augment
+            x_in = augment_cifar(x_in, aug.seed, st["aug_nonce"], aug.pad, aug.cutout, aug.mean_u8)
+        loss = self.batched.train_step(x_in, st["y"], self.W, self.G, st["active"], st["scale"])
         if not (fused and getattr(self.batched, "fused_applied", False)):
             self._sgd(self.C_max, st["lr"], False)
         st["loss"].copy_(loss)
@@ -495,6 +502,9 @@ class NCCLSimulator:
                             "lr": torch.zeros(C, dtype=torch.float32, device=dev),
                             "scale": torch.zeros(C, dtype=torch.float32, device=dev),
                             "loss": torch.zeros(C, dtype=torch.float32, device=dev)}
+            if self.fed is not None and getattr(self.fed, "train_augment", None) is not None and self.cuda:
+                self._static["aug_nonce"] = torch.zeros(1, dtype=torch.int64, device=dev)
+                self._aug_count = 0
             self.graph = None
         st = self._static
         first = True
@@ -505,6 +515,10 @@ class NCCLSimulator:
                 act = (steps_dev > s).to(torch.float32)
                 st["x"].copy_(Xd[:, s]); st["y"].copy_(Yd[:, s])
                 st["active"].copy_(act); st["lr"].copy_(act * self.lr); st["scale"].copy_(inv_valid[:, s])
+                if st.get("aug_nonce") is not None:
+                    self._aug_count += 1
+                    # rank-independent nonce; the sample index inside a step is the slot, which is fine for augmentation
+                    st["aug_nonce"].fill_(self._aug_count * 64 + self.rank)
                 if self.momentum and first:
                     loss = self.batched.train_step(st["x"], st["y"], self.W, self.G, st["active"], st["scale"])
                     self._sgd(C, st["lr"], True)

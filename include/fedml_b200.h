@@ -476,6 +476,16 @@ int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, 
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
 
+/* Train-time augmentation of uint8 NHWC image batches: RandomCrop(H, padding = pad, black border) + horizontal flip +
+ * Cutout(cutout x cutout, filled with fill_rgba = the per-channel dataset mean, byte c in bits [8c, 8c+8)).  Every
+ * random choice of sample i comes from Philox4x32-10(counter = (first_index + i, tag, nonce), key = seed); when
+ * nonce_dev is not NULL the nonce is read from that device int64 (a captured CUDA graph then augments differently at
+ * every replay).  Out of place.  Replaces the torchvision transform chain the reference runs per sample on the host
+ * (data/cifar10/data_loader.py:58-103). */
+int fb_augment_cifar(const uint8_t* x, uint8_t* y, int64_t n_img, int32_t H, int32_t W, int32_t C, uint64_t seed, uint32_t nonce,
+                     const int64_t* nonce_dev, int32_t pad, int32_t cutout, uint32_t fill_rgba, int64_t first_index,
+                     fb_stream_t stream);
+
 /* Fused classifier head of a client-stacked conv net, forward AND backward in one launch (one CTA per client):
  * global average pool -> fc (+bias) -> softmax cross-entropy -> d(logits) -> fc weight / bias gradients -> d(features)
  * broadcast back over the H x W positions.  h / dh: [C][B][HW][ch] in bf16 (act_fp32 = 0) or fp32 (1); W, bias, gW, gb:

@@ -248,3 +248,53 @@ def test_checkpoint_format_and_resume(tmp_path):
     w_res = res.run()
     for k in w_full:
         torch.testing.assert_close(w_res[k].float(), w_full[k].float(), rtol=1e-5, atol=1e-6)   # server-opt moments + round idx restored
+
+
+def test_train_time_augmentation_crop_flip_cutout():
+    """RandomCrop(32, 4) + HFlip + Cutout(16) as a pure function of (seed, nonce, sample) — reference
+    data/cifar10/data_loader.py:58-103 — and its hook into the train loaders."""
+    import torch
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.data.augment import CIFAR_MEAN_U8, augment_cifar_reference, augment_params
+    g = torch.Generator().manual_seed(0)
+    x = torch.randint(1, 255, (64, 32, 32, 3), dtype=torch.uint8, generator=g)
+    a = augment_cifar_reference(x, seed=11, nonce=3)
+    assert a.shape == x.shape and a.dtype == torch.uint8
+    assert torch.equal(a, augment_cifar_reference(x, 11, 3)) and not torch.equal(a, augment_cifar_reference(x, 11, 4))
+    dy, dx, flip, cy, cx = augment_params(64, 11, 3, 32, 32)
+    assert dy.min() >= 0 and dy.max() <= 8 and dx.min() >= 0 and dx.max() <= 8 and set(flip.tolist()) == {0, 1}
+    mean = torch.tensor(CIFAR_MEAN_U8, dtype=torch.uint8)
+    for i in range(64):
+        y1, y2, x1, x2 = max(0, cy[i] - 8), min(32, cy[i] + 8), max(0, cx[i] - 8), min(32, cx[i] + 8)
+        assert (a[i, y1:y2, x1:x2] == mean).all()                       # Cutout square = dataset mean (0 after Normalize)
+        # a pixel outside the square and inside the un-padded source area is the shifted (and mirrored) source pixel
+        for oy, ox in ((0, 0), (31, 31), (5, 20), (16, 16)):
+            if y1 <= oy < y2 and x1 <= ox < x2:
+                continue
+            sxo = 31 - ox if flip[i] else ox
+            sy, sx = oy + dy[i] - 4, sxo + dx[i] - 4
+            want = x[i, sy, sx] if (0 <= sy < 32 and 0 <= sx < 32) else torch.zeros(3, dtype=torch.uint8)
+            assert torch.equal(a[i, oy, ox], want)
+    # no augmentation parameters -> identity
+    assert torch.equal(augment_cifar_reference(x, 1, 1, pad=0, cutout=0)[flip_none(x, 1, 1)], x[flip_none(x, 1, 1)])
+    # loaders: train batches of a client differ between visits, test batches do not, default is off
+    args = fedml.init(Arguments.from_dict(dict(training_type="simulation", backend="sp", dataset="cifar10", model="resnet56",
+                                               client_num_in_total=4, client_num_per_round=2, comm_round=1, batch_size=8,
+                                               synthetic_train_size=64, augment=True, log_level="ERROR", using_gpu=False)))
+    ds, _ = fedml.data.load(args)
+    b1, b2 = ds[5][0][0][0], ds[5][0][0][0]
+    assert b1.shape == b2.shape and not torch.equal(b1, b2)
+    assert torch.equal(ds[6][0][0][0], ds[6][0][0][0])
+    args2 = fedml.init(Arguments.from_dict(dict(training_type="simulation", backend="sp", dataset="cifar10", model="resnet56",
+                                                client_num_in_total=4, client_num_per_round=2, comm_round=1, batch_size=8,
+                                                synthetic_train_size=64, log_level="ERROR", using_gpu=False)))
+    ds2, _ = fedml.data.load(args2)
+    assert torch.equal(ds2[5][0][0][0], ds2[5][0][0][0])
+
+
+def flip_none(x, seed, nonce):
+    """indices of the samples that are not mirrored for (seed, nonce)"""
+    import torch
+    from fedml_b200.data.augment import augment_params
+    return torch.from_numpy(augment_params(x.shape[0], seed, nonce, 32, 32, pad=0)[2] == 0)

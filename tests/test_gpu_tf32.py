@@ -372,3 +372,37 @@ def test_simulator_native_evaluation_matches_eager(model, dataset, dtype):
     for k in ("train_loss", "test_loss"):
         assert abs(nat[k] - eag[k]) <= tol * max(1.0, abs(eag[k])), (k, nat[k], eag[k])
     assert 0.0 <= nat["test_precision"] <= 1.0 and 0.0 <= nat["test_recall"] <= 1.0
+
+
+def test_augment_kernel_matches_oracle_and_runs_inside_the_training_graph():
+    """csrc/augment.cu == the CPU oracle byte for byte (crop / flip / Cutout from one Philox block per sample), with a
+    host nonce and with a device nonce; the simulator with ``augment: true`` trains with CUDA graphs on."""
+    from fedml_b200 import ops
+    from fedml_b200.data.augment import augment_cifar_reference
+    g = torch.Generator().manual_seed(0)
+    x = torch.randint(0, 256, (300, 32, 32, 3), dtype=torch.uint8, generator=g)
+    ref = augment_cifar_reference(x, seed=(5 << 33) | 77, nonce=9, first_index=1000)
+    got = ops.augment_cifar(x.to(DEV), (5 << 33) | 77, 9, first_index=1000)
+    assert torch.equal(got.cpu(), ref)
+    nonce = torch.tensor([9], dtype=torch.int64, device=DEV)
+    assert torch.equal(ops.augment_cifar(x.to(DEV), (5 << 33) | 77, nonce, first_index=1000).cpu(), ref)
+    nonce.fill_(10)
+    assert not torch.equal(ops.augment_cifar(x.to(DEV), (5 << 33) | 77, nonce, first_index=1000).cpu(), ref)
+    x1 = torch.randint(0, 256, (7, 16, 24, 1), dtype=torch.uint8, generator=g)          # other shapes / channel counts
+    assert torch.equal(ops.augment_cifar(x1.to(DEV), 3, 1, pad=2, cutout=6, mean_u8=(99,)).cpu(),
+                       augment_cifar_reference(x1, 3, 1, pad=2, cutout=6, mean_u8=(99,)))
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.simulation import SimulatorNCCL
+    a = fedml.init(Arguments.from_dict(dict(
+        training_type="simulation", backend="NCCL", dataset="cifar10", model="resnet56", client_num_in_total=8, client_num_per_round=4,
+        comm_round=2, epochs=1, batch_size=10, learning_rate=0.03, partition_method="homo", frequency_of_the_test=0,
+        synthetic_train_size=8 * 40, log_level="ERROR", using_gpu=True, compute_dtype="tf32", random_seed=0, augment=True)))
+    ds, ncls = fedml.data.load(a)
+    sim = SimulatorNCCL(a, torch.device(DEV), ds, fedml.models.create(a, ncls)).simulator
+    before = sim.global_flat.clone()
+    for r in range(2):
+        sim.train_one_round(r)
+    torch.cuda.synchronize()
+    assert sim.graph is not None and sim._static.get("aug_nonce") is not None and int(sim._static["aug_nonce"]) > 0
+    assert torch.isfinite(sim.global_flat).all() and not torch.equal(before, sim.global_flat)
