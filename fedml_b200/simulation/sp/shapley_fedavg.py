@@ -36,6 +36,29 @@ class SFedAvgAPI(FedAvgAPI):
         batches = list(itertools.islice(iter(self.test_global), 8))
         return batches
 
+    # ---- class-weighted client loss
+    def calc_class_weight(self, train_data):
+        """weight_c = n / (classes present on the client * samples of class c), 0 for absent classes
+        (s_fedavg/fedavg_api.py:112-136): every class a client holds contributes equally to its loss."""
+        ys = [b[1].reshape(-1) for b in train_data]
+        ncls = int(getattr(self, "class_num", 0) or getattr(self.args, "class_num", 0) or 0)
+        if not ys:
+            return torch.zeros(max(ncls, 1))
+        y = torch.cat(ys).to(torch.int64)
+        ncls = max(ncls, int(y.max()) + 1)
+        counts = torch.bincount(y, minlength=ncls).to(torch.float32)
+        present = int((counts > 0).sum())
+        w = torch.zeros(ncls)
+        w[counts > 0] = float(y.numel()) / (present * counts[counts > 0])
+        return w
+
+    def _train_one_client(self, client, w_global):
+        self.args.class_weight = self.calc_class_weight(client.local_training_data)
+        try:
+            return super()._train_one_client(client, w_global)
+        finally:
+            self.args.class_weight = None
+
     # ---- sampling biased by exp(phi)
     def _client_sampling(self, round_idx, n_total, n_round):
         if str(getattr(self.args, "sampling_filter", "exp")) != "exp" or round_idx == 0:

@@ -57,7 +57,9 @@ class ModelTrainerCLS(ClientTrainer):
     def train(self, train_data, device, args):
         model = self.model.to(device)
         model.train()
-        criterion = self.criterion_factory().to(device)
+        cw = getattr(args, "class_weight", None)           # per-client class weights (S-FedAvg: s_fedavg/fedavg_api.py:112-136)
+        criterion = (nn.CrossEntropyLoss(weight=torch.as_tensor(cw, dtype=torch.float32).to(device)) if cw is not None
+                     else self.criterion_factory()).to(device)
         trainable = [p for p in model.parameters() if p.requires_grad]
         optimizer = build_client_optimizer(trainable, args)
         mu = float(getattr(args, "fedprox_mu", 0.0) or 0.0)

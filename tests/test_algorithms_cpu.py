@@ -305,3 +305,32 @@ def test_fedavg_robust_backdoor_protocol():
     tr.update_dataset(0)
     assert tr.train_local is ds[5][0]
     assert all(int(y.unique()[0]) == 7 and y.unique().numel() == 1 for _, y in ttest)
+
+
+def test_s_fedavg_class_weighted_cross_entropy():
+    """S-FedAvg trains every client with class-weighted CE: weight_c = n / (#classes present * count_c)
+    (reference s_fedavg/fedavg_api.py:112-136)."""
+    import torch.nn as nn
+    from fedml_b200.simulation.sp.shapley_fedavg import SFedAvgAPI
+    a = mk(federated_optimizer="S_FedAvg", comm_round=1, client_num_per_round=2, shapley_mode="exact", frequency_of_the_test=100)
+    ds, model = build(a)
+    api = SFedAvgAPI(a, CPU, ds, model)
+    y = torch.tensor([0, 0, 0, 0, 0, 0, 3, 3, 7])
+    w = api.calc_class_weight([(torch.zeros(5, 4), y[:5]), (torch.zeros(4, 4), y[5:])])
+    assert w.shape[0] >= 8 and abs(float(w[0]) - 9 / (3 * 6)) < 1e-6 and abs(float(w[3]) - 9 / (3 * 2)) < 1e-6 \
+        and abs(float(w[7]) - 9 / (3 * 1)) < 1e-6 and float(w[1]) == 0.0
+    seen = []
+    orig = nn.CrossEntropyLoss.__init__
+
+    def spy(self, *args, weight=None, **kw):
+        seen.append(None if weight is None else weight.clone())
+        orig(self, *args, weight=weight, **kw)
+
+    nn.CrossEntropyLoss.__init__ = spy
+    try:
+        api.train()
+    finally:
+        nn.CrossEntropyLoss.__init__ = orig
+    weighted = [w_ for w_ in seen if w_ is not None]
+    assert len(weighted) >= 2 and all(float(w_.sum()) > 0 for w_ in weighted)     # one weighted criterion per trained client
+    assert getattr(a, "class_weight", None) is None                                # evaluation stays unweighted
