@@ -22,7 +22,9 @@ def create_comm_manager(args, rank, size, backend, announce_ready=False):
         from .grpc_backend import GRPCCommManager
         base = int(getattr(args, "grpc_base_port", 8888))
         return GRPCCommManager("0.0.0.0", base + rank, getattr(args, "grpc_ipconfig_path", None), client_id=rank,
-                               client_num=size - 1, base_port=base, announce_ready=announce_ready)
+                               client_num=size - 1, base_port=base, announce_ready=announce_ready,
+                               wire_format=getattr(args, "grpc_wire_format", "fedml_b200"),
+                               allow_pickle=bool(getattr(args, "grpc_allow_pickle", False)))
     if b == "TRPC":
         from .trpc_backend import TRPCCommManager
         return TRPCCommManager(getattr(args, "trpc_master_config_path", None), rank, size, args, announce_ready)

@@ -320,3 +320,63 @@ def test_secagg_keys_are_secret_masks_are_per_round_and_double_masking_recovers_
     masked = {i: cl[i].mask(ups[i], 1 / 3, 2 ** 16, [0, 1, 2], 0, self_mask=True) for i in range(3)}
     garbage = SecAggServer(p).aggregate(masked, 2 ** 16, [0, 1, 2])
     assert float((garbage - sum(ups[:3]) / 3).abs().max()) > 1.0
+
+
+def test_grpc_wire_compatibility_with_the_reference_service():
+    """A peer speaking the reference's protocol (service gRPCCommManager, CommRequest{client_id, message = pickle(Message)},
+    proto grpc_comm_manager.proto:3-16 / grpc_comm_manager.py:64-88) can send to our node, and a node configured with
+    grpc_wire_format=reference emits exactly that protocol."""
+    import pickle
+    import grpc
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+    from fedml_b200.core.distributed.communication.grpc_backend import (GRPCCommManager, decode_comm_request,
+                                                                         encode_comm_request, pickle_like_reference)
+    # the real protobuf runtime agrees with the hand-written CommRequest codec
+    fdp = descriptor_pb2.FileDescriptorProto(name="grpc_comm_manager_test.proto", syntax="proto3")
+    m = fdp.message_type.add(name="CommRequest")
+    m.field.add(name="client_id", number=1, type=descriptor_pb2.FieldDescriptorProto.TYPE_INT32, label=1)
+    m.field.add(name="message", number=2, type=descriptor_pb2.FieldDescriptorProto.TYPE_BYTES, label=1)
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(fdp)
+    CommRequest = message_factory.GetMessageClass(pool.FindMessageTypeByName("CommRequest"))
+    for cid, blob in ((7, b"hello" * 100), (0, b""), (300, bytes(range(256)))):
+        wire = CommRequest(client_id=cid, message=blob).SerializeToString()
+        assert wire == encode_comm_request(cid, blob) and decode_comm_request(wire) == (cid, blob)
+    # reference-format pickle names the reference's class and unpickles where that class exists (the fedml alias package)
+    msg = Message(3, 1, 0); msg.add_params("model_params", {"w": torch.arange(6.0).view(2, 3)}); msg.add_params("num_samples", 17)
+    blob = pickle_like_reference(msg)
+    assert b"fedml.core.distributed.communication.message\nMessage" in blob
+    import fedml  # noqa: F401  (alias of fedml_b200: provides fedml.core.distributed.communication.message)
+    back = pickle.loads(blob)
+    assert back.get_type() == 3 and back.get_sender_id() == 1 and torch.equal(back.get("model_params")["w"], torch.arange(6.0).view(2, 3))
+    # (1) reference-style client -> our server
+    p0, p1 = next_port(), None
+    got = []
+
+    class Obs:
+        def __init__(self): self.ev = threading.Event()
+        def receive_message(self, t, p): got.append((t, p)); self.ev.set()
+
+    server = GRPCCommManager("127.0.0.1", p0, client_id=0, client_num=1, base_port=p0, allow_pickle=True)
+    obs = Obs(); server.add_observer(obs)
+    th = threading.Thread(target=server.handle_receive_message, daemon=True); th.start()
+    ch = grpc.insecure_channel(f"127.0.0.1:{p0}")
+    stub = ch.unary_unary("/gRPCCommManager/sendMessage", request_serializer=None, response_deserializer=None)
+    resp = stub(CommRequest(client_id=1, message=blob).SerializeToString(), wait_for_ready=True, timeout=20)
+    assert decode_comm_request(resp) == (0, b"")
+    assert obs.ev.wait(20) and got[0][0] == 3 and got[0][1]["num_samples"] == 17
+    # without allow_pickle the reference service refuses pickles
+    strict = GRPCCommManager("127.0.0.1", p0 + 1, client_id=1, client_num=1, base_port=p0)
+    ch2 = grpc.insecure_channel(f"127.0.0.1:{p0 + 1}")
+    stub2 = ch2.unary_unary("/gRPCCommManager/sendMessage", request_serializer=None, response_deserializer=None)
+    with pytest.raises(grpc.RpcError):
+        stub2(CommRequest(client_id=1, message=blob).SerializeToString(), wait_for_ready=True, timeout=20)
+    # (2) our node in reference mode -> (our server standing in for) a reference server: same envelope on the wire
+    sender = GRPCCommManager("127.0.0.1", p0 + 2, client_id=2, client_num=2, base_port=p0, wire_format="reference")
+    obs.ev.clear()
+    out = Message(9, 2, 0); out.add_params("k", [1, 2, 3])
+    sender.send_message(out)
+    assert obs.ev.wait(20) and got[-1][0] == 9 and got[-1][1]["k"] == [1, 2, 3]
+    for mgr in (server, strict, sender):
+        mgr.stop_receive_message()
+    ch.close(); ch2.close()
