@@ -9,8 +9,9 @@ Topic scheme and behaviour follow the reference:
     type 0 ("connection ready") is emitted once subscriptions are in place; a last-will ``W/topic`` carries
     ``{ID, stat: "Online"}``;
   * MQTT_S3_MNN (mqtt_s3_mnn/mqtt_s3_comm_manager.py:197-235): the payload is a model *file* path.
-Broker: a real one through paho if available + configured, else :class:`LocalBroker` at
-``mqtt_host:mqtt_port`` (defaults 127.0.0.1:1883; ``args.mqtt_port``)."""
+Broker: any MQTT 3.1.1 broker at ``mqtt_host:mqtt_port`` (defaults 127.0.0.1:1883) — the bundled :class:`LocalBroker`
+or a production one; the client is the bundled protocol implementation (``broker.BrokerClient``) or paho
+(``args.mqtt_client: "paho"``), both speak the standard wire protocol."""
 import json
 import os
 import queue
@@ -20,7 +21,7 @@ from typing import List
 import yaml
 
 from .base_com_manager import BaseCommunicationManager
-from .broker import BrokerClient
+from .broker import BrokerClient, make_client
 from .message import Message, _jsonable
 from .observer import Observer
 from .remote_storage import create_store
@@ -51,7 +52,7 @@ class _MqttBase(BaseCommunicationManager):
         self.edge_id = 0 if self.rank == 0 else (self.client_real_ids[self.rank - 1]
                                                  if self.rank - 1 < len(self.client_real_ids) else self.rank)
         host, port = _broker_endpoint(args)
-        self._client = BrokerClient(host, port, client_id=f"{self.run_id}-{self.edge_id}", will_topic="W/topic",
+        self._client = make_client(host, port, kind=getattr(args, "mqtt_client", "auto"), client_id=f"{self.run_id}-{self.edge_id}", will_topic="W/topic",
                                     will_payload={"ID": self.edge_id, "stat": "Online"})
         self._client.on_message = self._on_message
         if self.rank == 0:
@@ -168,7 +169,8 @@ class MqttS3StatusManager:
 
     def __init__(self, args, topic="fedml_status"):
         host, port = _broker_endpoint(args)
-        self._client = BrokerClient(host, port, client_id=f"status-{getattr(args, 'run_id', 0)}-{uuid.uuid4().hex[:6]}")
+        self._client = make_client(host, port, kind=getattr(args, "mqtt_client", "auto"),
+                                   client_id=f"status-{getattr(args, 'run_id', 0)}-{uuid.uuid4().hex[:6]}")
         self._client.on_message = self._on_message
         self._observers = []
 

@@ -380,3 +380,46 @@ def test_grpc_wire_compatibility_with_the_reference_service():
     for mgr in (server, strict, sender):
         mgr.stop_receive_message()
     ch.close(); ch2.close()
+
+
+def test_mqtt_wire_protocol_interoperates_with_a_standard_peer(broker):
+    """The bundled broker / client speak MQTT 3.1.1 on the wire: a peer written against the spec with raw sockets (the bytes
+    a paho / mosquitto client emits) connects, subscribes with a wildcard, receives what BrokerClient publishes, publishes
+    at QoS 1 and gets its PUBACK; topic filters follow the spec."""
+    import socket
+    import struct
+    from fedml_b200.core.distributed.communication.broker import topic_matches
+    assert topic_matches("fedml_7_/+", "fedml_7_/3") and topic_matches("a/#", "a/b/c") and not topic_matches("a/+", "a/b/c") \
+        and topic_matches("W/topic", "W/topic") and not topic_matches("W/topic", "W/topic2")
+    s = socket.create_connection(("127.0.0.1", broker), timeout=10)
+    # CONNECT: protocol "MQTT" level 4, clean session, keep-alive 60, client id "rawpeer"
+    s.sendall(bytes.fromhex("10 13 00 04 4d 51 54 54 04 02 00 3c 00 07") + b"rawpeer")
+    assert s.recv(4) == bytes.fromhex("20 02 00 00")                        # CONNACK, accepted
+    # SUBSCRIBE packet id 1, filter "interop/+" QoS 0
+    s.sendall(bytes.fromhex("82 0e 00 01 00 09") + b"interop/+" + b"\x00")
+    assert s.recv(5) == bytes.fromhex("90 03 00 01 00")                     # SUBACK, granted QoS 0
+    ours = BrokerClient("127.0.0.1", broker, client_id="ours")
+    got = []
+    ours.on_message = lambda t, p: got.append((t, p))
+    ours.subscribe("interop/back")
+    ours.publish("interop/x", b"payload-\x00\x01")
+    hdr = s.recv(2)
+    assert hdr[0] == 0x30                                                   # PUBLISH QoS 0
+    body = s.recv(hdr[1])
+    (tl,) = struct.unpack(">H", body[:2])
+    assert body[2:2 + tl] == b"interop/x" and body[2 + tl:] == b"payload-\x00\x01"
+    # raw peer publishes at QoS 1 (packet id 9) -> broker acknowledges and forwards to our client
+    topic = b"interop/back"
+    pkt = struct.pack(">H", len(topic)) + topic + struct.pack(">H", 9) + b"from-raw"
+    s.sendall(bytes([0x32, len(pkt)]) + pkt)
+    assert s.recv(4) == bytes.fromhex("40 02 00 09")                        # PUBACK id 9
+    deadline = time.time() + 5
+    while not got and time.time() < deadline:
+        time.sleep(0.02)
+    assert got == [("interop/back", b"from-raw")]
+    echo = s.recv(2)                                                        # "interop/+" also matches its own publish
+    assert echo[0] == 0x30 and s.recv(echo[1])[2:14] == b"interop/back"
+    s.sendall(bytes.fromhex("c0 00"))
+    assert s.recv(2) == bytes.fromhex("d0 00")                              # PINGREQ -> PINGRESP
+    s.sendall(bytes.fromhex("e0 00"))                                       # DISCONNECT
+    s.close(); ours.disconnect()
