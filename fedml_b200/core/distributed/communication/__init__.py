@@ -5,7 +5,7 @@ from .observer import Observer
 BACKENDS = ("INPROC", "MPI", "TCP", "GRPC", "TRPC", "MQTT", "MQTT_S3", "MQTT_S3_MNN")
 
 
-def create_comm_manager(args, rank, size, backend, announce_ready=False):
+def create_comm_manager(args, rank, size, backend, announce_ready=False, comm=None):
     """Backend-by-name factory shared by ClientManager / ServerManager
     (reference: client_manager.py:27-94, server_manager.py:27-96)."""
     b = str(backend).upper()
@@ -13,8 +13,12 @@ def create_comm_manager(args, rank, size, backend, announce_ready=False):
     if b == "INPROC":
         from .inproc import InProcCommManager
         return InProcCommManager(run_id, rank, size, announce_ready)
+    if b == "MPI" and comm is not None and hasattr(comm, "Get_rank"):
+        # a real MPI communicator (mpi4py, job started by mpirun): the reference's transport
+        from .mpi_backend import MpiCommManager
+        return MpiCommManager(comm, rank, size, announce_ready=announce_ready)
     if b in ("MPI", "TCP"):
-        # mpi4py is not part of this build: the multi-process star topology runs over sockets
+        # no MPI communicator (mpi4py absent or not under mpirun): the same star topology over sockets
         from .tcp import TcpCommManager
         hosts = getattr(args, "host_table", None)
         return TcpCommManager(rank, size, hosts, int(getattr(args, "tcp_base_port", 50000)), announce_ready)

@@ -17,7 +17,7 @@ class _Manager(Observer):
         self.args, self.size, self.rank, self.backend = args, int(size), int(rank), backend
         self.comm = comm
         self.com_manager = comm if (comm is not None and hasattr(comm, "send_message")) else \
-            create_comm_manager(args, self.rank, self.size, backend, self.announce_ready)
+            create_comm_manager(args, self.rank, self.size, backend, self.announce_ready, comm=comm)
         self.com_manager.add_observer(self)
         self.message_handler_dict = {}
         self.com_manager_status = "INIT"
