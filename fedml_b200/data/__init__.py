@@ -83,29 +83,60 @@ def load_federated(args) -> FederatedDataset:
             nat = int(getattr(args, "mnist_client_num", 1000))
             ds = S.make_mnist_like(client_num=nat, total_train=small or 61664, seed=seed)
     elif name == "femnist":
-        ds = S.make_femnist_like(client_num=int(getattr(args, "femnist_client_num", 3400)), seed=seed,
-                                 total_train=small or 340000)
+        from . import readers as R
+        ds = R.load_leaf_images(cache, "femnist", 62, "femnist", shape=(28, 28)) \
+            or R.load_tff_h5(os.path.join(cache, "fed_emnist_train.h5"), os.path.join(cache, "fed_emnist_test.h5"),
+                             "pixels", "label", 62, "femnist")
+        if ds is None:
+            ds = S.make_femnist_like(client_num=int(getattr(args, "femnist_client_num", 3400)), seed=seed,
+                                     total_train=small or 340000)
     elif name in ("cifar10", "cifar100", "cinic10"):
         cnum = 100 if name == "cifar100" else 10
         mean, std = (S.CIFAR100_MEAN, S.CIFAR100_STD) if name == "cifar100" else (S.CIFAR10_MEAN, S.CIFAR10_STD)
         ntr = small or (90000 if name == "cinic10" else 50000)
         nte = max(100, ntr // 5)
         real = _try_real_cifar10(cache) if name == "cifar10" else None
+        if name == "cifar100":
+            from . import readers as R
+            real = R.load_cifar100_pickles(cache)
+        elif name == "cinic10":
+            from . import readers as R
+            folder = R.load_image_folder(os.path.join(cache, "cinic10"), 32, "train", "test")
+            real = folder[:4] if folder is not None else None
         if real is not None:
             from ..core.non_iid_partition import homo_partition, non_iid_partition_with_dirichlet_distribution
             xtr, ytr, xte, yte = real
             st = np.random.get_state(); np.random.seed(10)
             part = homo_partition(len(ytr), n_clients) if pm == "homo" else \
-                non_iid_partition_with_dirichlet_distribution(ytr.numpy(), n_clients, 10, pa)
+                non_iid_partition_with_dirichlet_distribution(ytr.numpy(), n_clients, cnum, pa)
             np.random.set_state(st)
             x, y, offs = S._pack_by_partition(xtr, ytr, part)
-            ds = FederatedDataset(x, y, offs, xte, yte, None, 10, S.ImageNormalize(mean, std), name)
+            ds = FederatedDataset(x, y, offs, xte, yte, None, cnum, S.ImageNormalize(mean, std), name)
         else:
             ds = S.make_cifar_like(n_clients, pm, pa, cnum, ntr, nte, 32, seed, name, mean, std)
+    elif name == "fed_cifar100" and os.path.isfile(os.path.join(cache, "fed_cifar100_train.h5")):
+        from . import readers as R
+        ds = R.load_tff_h5(os.path.join(cache, "fed_cifar100_train.h5"), os.path.join(cache, "fed_cifar100_test.h5"),
+                           "image", "label", 100, "fed_cifar100", S.ImageNormalize(S.CIFAR100_MEAN, S.CIFAR100_STD), to_uint8=True)
     elif name == "fed_cifar100":
         ds = S.make_cifar_like(int(getattr(args, "fed_cifar100_client_num", 500)), "hetero", 0.1, 100,
                                small or 50000, 10000 if not small else max(100, small // 5), 24, seed,
                                name, S.CIFAR100_MEAN, S.CIFAR100_STD)
+    elif name in ("ilsvrc2012", "imagenet") and os.path.isdir(os.path.join(cache, "train")):
+        from . import readers as R
+        from ..core.non_iid_partition import homo_partition, non_iid_partition_with_dirichlet_distribution
+        hw = int(getattr(args, "image_size", 224))
+        xtr, ytr, xva, yva, classes = R.load_image_folder(cache, hw, "train", "val", int(getattr(args, "max_images_per_class", 0)))
+        st = np.random.get_state(); np.random.seed(10)
+        part = homo_partition(len(ytr), n_clients) if pm == "homo" else \
+            non_iid_partition_with_dirichlet_distribution(ytr.numpy(), n_clients, len(classes), pa)
+        np.random.set_state(st)
+        x, y, offs = S._pack_by_partition(xtr, ytr, part)
+        ds = FederatedDataset(x, y, offs, xva, yva, None, len(classes), S.ImageNormalize(S.IMAGENET_MEAN, S.IMAGENET_STD), name)
+    elif name in ("gld23k", "gld160k") and os.path.isfile(os.path.join(cache, f"{name}_user_dict_train.csv")):
+        from . import readers as R
+        ds = R.load_landmarks_csv(os.path.join(cache, "images"), os.path.join(cache, f"{name}_user_dict_train.csv"),
+                                  os.path.join(cache, f"{name}_user_dict_test.csv"), int(getattr(args, "image_size", 224)))
     elif name in ("ilsvrc2012", "imagenet", "gld23k", "gld160k"):
         clients = {"gld23k": 233, "gld160k": 1262}.get(name, n_clients)
         classes = {"gld23k": 203, "gld160k": 2028}.get(name, 1000)
@@ -113,6 +144,14 @@ def load_federated(args) -> FederatedDataset:
         ntr = small or 2048
         ds = S.make_cifar_like(clients, "homo" if name.startswith("il") or name == "imagenet" else "hetero", pa,
                                classes, ntr, max(64, ntr // 8), hw, seed, name, S.IMAGENET_MEAN, S.IMAGENET_STD)
+    elif name == "shakespeare" and os.path.isdir(os.path.join(cache, "shakespeare", "train")):
+        from . import readers as R
+        ds = R.load_leaf_shakespeare(cache)
+    elif name in ("fed_shakespeare", "stackoverflow_nwp", "stackoverflow_lr") and any(
+            os.path.isfile(os.path.join(cache, f)) for f in ("shakespeare_train.h5", "stackoverflow_train.h5")):
+        from . import readers as R
+        R.need_h5py(os.path.join(cache, "shakespeare_train.h5" if name == "fed_shakespeare" else "stackoverflow_train.h5"))
+        raise NotImplementedError(f"{name}: TFF .h5 text exports need h5py plus the reference's tokeniser tables")
     elif name in ("shakespeare", "fed_shakespeare"):
         ds = S.make_char_lm(715 if not small else max(4, small // 64), 80, 90, 64, seed, name,
                             next_token_only=(name == "shakespeare"))
