@@ -143,3 +143,123 @@ class Network(nn.Module):
         concat = list(range(2 + self._steps - self._multiplier, self._steps + 2))
         return Genotype(parse(F.softmax(self.alphas_normal, -1).tolist()), concat,
                         parse(F.softmax(self.alphas_reduce, -1).tolist()), concat)
+
+
+class NetworkGDAS(Network):
+    """GDAS search space (reference: model/cv/darts/model_search_gdas.py): every edge samples ONE operation per forward
+    pass with the Gumbel-softmax straight-through estimator (temperature ``tau``, annealed by the trainer via
+    ``set_tau``), so a step costs one operation per edge instead of all eight, while the architecture parameters still get
+    gradients through the soft probabilities."""
+
+    def __init__(self, *a, tau: float = 10.0, **kw):
+        super().__init__(*a, **kw)
+        self.tau = float(tau)
+
+    def set_tau(self, tau: float):
+        self.tau = float(tau)
+
+    def get_tau(self) -> float:
+        return self.tau
+
+    def _edge_weights(self, alphas):
+        if not self.training:
+            idx = alphas.argmax(dim=-1, keepdim=True)
+            return torch.zeros_like(alphas).scatter_(-1, idx, 1.0)
+        return F.gumbel_softmax(alphas, tau=self.tau, hard=True, dim=-1)     # one-hot forward, soft backward
+
+    def forward(self, x):
+        s0 = s1 = self.stem(x)
+        wn, wr = self._edge_weights(self.alphas_normal), self._edge_weights(self.alphas_reduce)
+        for cell in self.cells:
+            s0, s1 = s1, _gdas_cell(cell, s0, s1, wr if cell.reduction else wn)
+        return self.classifier(F.adaptive_avg_pool2d(s1, 1).flatten(1))
+
+
+def _gdas_cell(cell: Cell, s0, s1, weights):
+    """Cell forward that evaluates only the sampled operation of every edge."""
+    states, off = [cell.pre0(s0), cell.pre1(s1)], 0
+    for _ in range(cell._steps):
+        acc = 0
+        for j, h in enumerate(states):
+            w = weights[off + j]
+            k = int(w.argmax())
+            acc = acc + w[k] * cell._ops[off + j]._ops[k](h)
+        off += len(states)
+        states.append(acc)
+    return torch.cat(states[-cell._multiplier:], dim=1)
+
+
+class Architect:
+    """Architecture step of DARTS (reference: model/cv/darts/architect.py).  ``step(..., unrolled=False)`` is the
+    first-order rule (gradient of the validation loss at the current weights); ``unrolled=True`` is the second-order rule:
+    with w' = w - eta * (momentum * buf + grad_w L_train(w, a) + wd * w),
+
+        d a = grad_a L_val(w', a) - eta * [grad_a L_train(w + e v, a) - grad_a L_train(w - e v, a)] / (2 e),
+        v = grad_w' L_val(w', a),  e = 0.01 / ||v||
+
+    (the finite-difference Hessian-vector product of the DARTS paper).  Implemented with ``torch.func.functional_call`` on
+    a parameter dict, so no second model instance is built."""
+
+    def __init__(self, model: Network, criterion=None, arch_learning_rate=3e-4, arch_weight_decay=1e-3, momentum=0.9,
+                 weight_decay=3e-4):
+        self.model, self.criterion = model, criterion or nn.CrossEntropyLoss()
+        self.momentum, self.weight_decay = float(momentum), float(weight_decay)
+        self.optimizer = torch.optim.Adam(model.arch_parameters(), lr=arch_learning_rate, betas=(0.5, 0.999),
+                                          weight_decay=arch_weight_decay)
+
+    # -- helpers -----------------------------------------------------------------------------------------------------
+    def _names(self):
+        arch_ids = {id(p) for p in self.model.arch_parameters()}
+        wn = [n for n, p in self.model.named_parameters() if id(p) not in arch_ids]
+        an = [n for n, p in self.model.named_parameters() if id(p) in arch_ids]
+        return wn, an
+
+    def _loss(self, params: dict, x, y):
+        from torch.func import functional_call
+        buffers = {n: b for n, b in self.model.named_buffers()}
+        return self.criterion(functional_call(self.model, {**params, **buffers}, (x,)), y)
+
+    def arch_gradient(self, x_train, y_train, x_valid, y_valid, eta: float, network_optimizer=None, unrolled: bool = True):
+        """-> list of gradients, one per architecture parameter."""
+        wn, an = self._names()
+        named = dict(self.model.named_parameters())
+        w = {n: named[n] for n in wn}
+        a = {n: named[n] for n in an}
+        if not unrolled:
+            gs = torch.autograd.grad(self._loss({**w, **a}, x_valid, y_valid), list(a.values()), allow_unused=True)
+            return [torch.zeros_like(p) if gi is None else gi for gi, p in zip(gs, a.values())]
+        # virtual step of the weights
+        g = torch.autograd.grad(self._loss({**w, **a}, x_train, y_train), list(w.values()), allow_unused=True)
+        w_prime = {}
+        for (n, p), gi in zip(w.items(), g):
+            gi = torch.zeros_like(p) if gi is None else gi
+            buf = None
+            if network_optimizer is not None:
+                buf = network_optimizer.state.get(p, {}).get("momentum_buffer")
+            mom = self.momentum * buf if buf is not None else 0.0
+            w_prime[n] = (p - eta * (mom + gi + self.weight_decay * p)).detach().requires_grad_(True)
+        a_leaf = {n: p.detach().requires_grad_(True) for n, p in a.items()}
+        grads = torch.autograd.grad(self._loss({**w_prime, **a_leaf}, x_valid, y_valid),
+                                    list(a_leaf.values()) + list(w_prime.values()), allow_unused=True)
+        da = [gi if gi is not None else torch.zeros_like(p) for gi, p in zip(grads[:len(a_leaf)], a_leaf.values())]
+        v = [gi if gi is not None else torch.zeros_like(p) for gi, p in zip(grads[len(a_leaf):], w_prime.values())]
+        vnorm = torch.sqrt(sum((vi * vi).sum() for vi in v))
+        eps = 0.01 / float(vnorm.clamp_min(1e-12))
+        hv = []
+        for sign in (1.0, -1.0):
+            w_shift = {n: (p + sign * eps * vi).detach() for (n, p), vi in zip(w.items(), v)}
+            a_req = {n: p.detach().requires_grad_(True) for n, p in a.items()}
+            hv.append(torch.autograd.grad(self._loss({**w_shift, **a_req}, x_train, y_train), list(a_req.values()), allow_unused=True))
+        out = []
+        for d, gp, gm, p in zip(da, hv[0], hv[1], a.values()):
+            gp = torch.zeros_like(p) if gp is None else gp
+            gm = torch.zeros_like(p) if gm is None else gm
+            out.append(d - eta * (gp - gm) / (2 * eps))
+        return out
+
+    def step(self, x_train, y_train, x_valid, y_valid, eta: float, network_optimizer=None, unrolled: bool = False):
+        grads = self.arch_gradient(x_train, y_train, x_valid, y_valid, eta, network_optimizer, unrolled)
+        self.optimizer.zero_grad(set_to_none=True)
+        for p, gi in zip(self.model.arch_parameters(), grads):
+            p.grad = gi.detach().clone()
+        self.optimizer.step()

@@ -25,16 +25,22 @@ class FedNASTrainer(ClientTrainer):
         crit = nn.CrossEntropyLoss()
         w_opt = torch.optim.SGD(m.weight_parameters(), lr=float(getattr(args, "learning_rate", 0.025)), momentum=0.9,
                                 weight_decay=float(getattr(args, "weight_decay", 3e-4)))
-        a_opt = torch.optim.Adam(m.arch_parameters(), lr=float(getattr(args, "arch_learning_rate", 3e-4)), betas=(0.5, 0.999),
-                                 weight_decay=float(getattr(args, "arch_weight_decay", 1e-3)))
+        from ...models.darts import Architect
+        lr = float(getattr(args, "learning_rate", 0.025))
+        architect = Architect(m, crit, float(getattr(args, "arch_learning_rate", 3e-4)), float(getattr(args, "arch_weight_decay", 1e-3)),
+                              momentum=0.9, weight_decay=float(getattr(args, "weight_decay", 3e-4)))
+        # arch_order 2 = the unrolled (second-order) architect step of the reference (architect.py), 1 = first order
+        unrolled = int(getattr(args, "arch_order", 1) or 1) == 2 or bool(getattr(args, "unrolled", False))
         search = str(getattr(args, "stage", "search")) == "search"
+        if hasattr(m, "set_tau"):                       # GDAS: temperature annealed linearly over the rounds
+            t_hi, t_lo = float(getattr(args, "tau_max", 10.0)), float(getattr(args, "tau_min", 1.0))
+            frac = float(getattr(args, "round_idx", 0) or 0) / max(1, int(getattr(args, "comm_round", 1)) - 1)
+            m.set_tau(t_hi - (t_hi - t_lo) * min(1.0, frac))
         for _ in range(int(getattr(args, "epochs", 1))):
             for i, (x, y) in enumerate(w_batches):
-                if search:   # first-order DARTS: alpha step on validation data, then weight step on training data
+                if search:   # alpha step on held-out data (first or second order), then weight step on training data
                     xa, ya = a_batches[i % len(a_batches)]
-                    a_opt.zero_grad(set_to_none=True)
-                    crit(m(xa.to(device)), ya.to(device)).backward()
-                    a_opt.step()
+                    architect.step(x.to(device), y.to(device), xa.to(device), ya.to(device), lr, w_opt, unrolled=unrolled)
                 w_opt.zero_grad(set_to_none=True)
                 crit(m(x.to(device)), y.to(device)).backward()
                 nn.utils.clip_grad_norm_(m.weight_parameters(), float(getattr(args, "grad_clip", 5.0)))
@@ -55,6 +61,9 @@ class FedNASTrainer(ClientTrainer):
 
 def FedML_FedNAS_distributed(args, process_id, worker_number, comm, device, dataset, model=None, model_trainer=None,  # noqa: N802
                              backend="INPROC", **kw):
+    if not isinstance(model, Network) and str(getattr(args, "nas_space", "darts")).lower() == "gdas":
+        from ...models.darts import NetworkGDAS
+        model = NetworkGDAS(C=int(getattr(args, "init_channels", 8)), num_classes=dataset[7], layers=int(getattr(args, "layers", 3)))
     if not isinstance(model, Network):
         model = Network(C=int(getattr(args, "init_channels", 8)), num_classes=dataset[7], layers=int(getattr(args, "layers", 3)))
     out = FedML_FedAvg_distributed(args, process_id, worker_number, comm, device, dataset, model,

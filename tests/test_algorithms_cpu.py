@@ -334,3 +334,53 @@ def test_s_fedavg_class_weighted_cross_entropy():
     weighted = [w_ for w_ in seen if w_ is not None]
     assert len(weighted) >= 2 and all(float(w_.sum()) > 0 for w_ in weighted)     # one weighted criterion per trained client
     assert getattr(a, "class_weight", None) is None                                # evaluation stays unweighted
+
+
+def test_darts_second_order_architect_and_gdas():
+    """DARTS unrolled (second-order) architecture gradient (reference model/cv/darts/architect.py) vs the exact
+    hyper-gradient obtained by differentiating through the virtual weight step; GDAS space samples one op per edge and
+    still trains its architecture parameters; FedNAS runs with both."""
+    from torch.func import functional_call
+    from fedml_b200.models.darts import Architect, Network, NetworkGDAS
+    torch.manual_seed(0)
+    net = Network(C=4, num_classes=4, layers=1, steps=2, multiplier=2).double()
+    xt, yt = torch.randn(6, 3, 8, 8, dtype=torch.float64), torch.randint(0, 4, (6,))
+    xv, yv = torch.randn(6, 3, 8, 8, dtype=torch.float64), torch.randint(0, 4, (6,))
+    arch = Architect(net, momentum=0.0, weight_decay=0.0)
+    eta = 0.05
+    approx = arch.arch_gradient(xt, yt, xv, yv, eta, None, unrolled=True)
+    first = arch.arch_gradient(xt, yt, xv, yv, eta, None, unrolled=False)
+    # exact: d/da L_val(w - eta * grad_w L_train(w, a), a)
+    wn, an = arch._names()
+    named = dict(net.named_parameters())
+    w = {n: named[n] for n in wn}; a = {n: named[n] for n in an}
+    bufs = dict(net.named_buffers())
+    crit = torch.nn.CrossEntropyLoss()
+    ltr = crit(functional_call(net, {**w, **a, **bufs}, (xt,)), yt)
+    gw = torch.autograd.grad(ltr, list(w.values()), create_graph=True, allow_unused=True)
+    w2 = {n: (p - eta * g) if g is not None else p for (n, p), g in zip(w.items(), gw)}
+    exact = torch.autograd.grad(crit(functional_call(net, {**w2, **a, **bufs}, (xv,)), yv), list(a.values()), allow_unused=True)
+    exact = [torch.zeros_like(p) if g_ is None else g_ for g_, p in zip(exact, a.values())]
+    fa, fe, ff = (torch.cat([g.reshape(-1) for g in gs]) for gs in (approx, exact, first))
+    cos = float(torch.dot(fa, fe) / (fa.norm() * fe.norm()))
+    assert cos > 0.98 and float((fa - fe).norm() / fe.norm()) < 0.2, cos
+    assert float((fa - fe).norm()) < float((ff - fe).norm()) + 1e-12     # closer to the exact hyper-gradient than first order
+    before = [p.clone() for p in net.arch_parameters()]
+    arch.step(xt, yt, xv, yv, eta, None, unrolled=True)
+    assert not torch.equal(before[0], net.arch_parameters()[0])
+    # GDAS: hard one-hot edge weights in the forward pass, gradients reach the alphas, tau is adjustable
+    g = NetworkGDAS(C=4, num_classes=4, layers=1, steps=2, multiplier=2, tau=5.0)
+    g.train()
+    wgt = g._edge_weights(g.alphas_normal)
+    assert torch.equal(wgt.sum(-1), torch.ones(wgt.shape[0])) and set(wgt.unique().tolist()) <= {0.0, 1.0}
+    torch.nn.functional.cross_entropy(g(xt.float()), yt).backward()
+    assert g.alphas_normal.grad is not None and float(g.alphas_normal.grad.abs().sum()) > 0
+    g.set_tau(1.0); assert g.get_tau() == 1.0
+    g.eval(); assert g(xt.float()).shape == (6, 4)
+    for kw in (dict(arch_order=2), dict(nas_space="gdas")):
+        a_ = mk(federated_optimizer="FedNAS", backend="MPI", worker_num=2, client_num_per_round=2, client_num_in_total=2, comm_round=1,
+                dataset="cifar10", layers=2, synthetic_train_size=32, batch_size=8, run_id="nas" + str(list(kw)[0]), ci=1,
+                frequency_of_the_test=1, **kw)
+        ds, model = build(a_)
+        r = SimulatorMPI(a_, CPU, ds, model).run()
+        assert len(r.history) >= 1 and r.genotype is not None
