@@ -139,11 +139,55 @@ class SysStats:
         return info
 
 
+def _post_json(url: str, obj: dict, timeout: float = 10.0) -> dict:
+    """POST a JSON document; ``file://path`` appends it as one line to a local file (offline sink)."""
+    import json
+    if url.startswith("file://"):
+        path = url[len("file://"):]
+        import os
+        os.makedirs(os.path.dirname(path) or ".", exist_ok=True)
+        with open(path, "a") as fh:
+            fh.write(json.dumps(obj) + "\n")
+        return {"code": "SUCCESS"}
+    import urllib.request
+    req = urllib.request.Request(url, data=json.dumps(obj).encode(), headers={"Content-Type": "application/json", "Connection": "close"})
+    with urllib.request.urlopen(req, timeout=timeout) as resp:
+        body = resp.read().decode() or "{}"
+        if resp.status != 200:
+            raise OSError(f"HTTP {resp.status}")
+    try:
+        return json.loads(body)
+    except ValueError:
+        return {}
+
+
 class MLOpsRuntimeLog:
+    """Run log + its background uploader (reference: core/mlops/mlops_runtime_log.py:29-200): the log file of the run is
+    tailed by a daemon thread that every ``log_upload_interval`` seconds (10 in the reference) posts the new lines as
+    ``{run_id, edge_id, logs, create_time, update_time, created_by, updated_by}`` to ``args.log_server_url``; a failed post
+    is retried with the same lines at the next tick."""
     _instance = None
 
     def __init__(self, args):
         self.args = args
+        self.run_id = getattr(args, "run_id", 0)
+        self.edge_id = self._edge_id(args)
+        self.log_server_url = getattr(args, "log_server_url", None)
+        self.log_line_index = 0
+        self._thread = None
+        self._stop = None
+        self.log_file_path = None
+
+    @staticmethod
+    def _edge_id(args):
+        rank = int(getattr(args, "rank", 0) or 0)
+        if rank == 0:
+            return 0
+        try:
+            ids = args.client_ids() if hasattr(args, "client_ids") else []
+            return ids[rank - 1] if rank - 1 < len(ids) else rank
+        except Exception:  # noqa: BLE001
+            return rank
 
     @classmethod
     def get_instance(cls, args):
@@ -153,7 +197,57 @@ class MLOpsRuntimeLog:
 
     def init_logs(self):
         from ...utils.logging import init_logs
-        init_logs(self.args)
+        self.log_file_path = init_logs(self.args)
+        if self.log_server_url and bool(getattr(self.args, "using_mlops", False)):
+            self.start_uploader()
+        return self.log_file_path
+
+    # ---- uploader
+    def log_read(self):
+        import os
+        if not self.log_file_path or not os.path.exists(self.log_file_path):
+            return []
+        with open(self.log_file_path, errors="replace") as fh:
+            lines = fh.readlines()
+        return lines[self.log_line_index:]
+
+    def log_upload(self, run_id=None, edge_id=None) -> int:
+        """One upload tick; returns the number of lines the server accepted."""
+        import time
+        lines = self.log_read()
+        if not lines or not self.log_server_url:
+            return 0
+        now = time.time()
+        eid = self.edge_id if edge_id is None else edge_id
+        req = {"run_id": self.run_id if run_id is None else run_id, "edge_id": eid, "logs": lines, "create_time": now,
+               "update_time": now, "created_by": str(eid), "updated_by": str(eid)}
+        try:
+            _post_json(self.log_server_url, req)
+        except Exception:  # noqa: BLE001 - keep the lines for the next tick
+            return 0
+        self.log_line_index += len(lines)
+        return len(lines)
+
+    def start_uploader(self, interval: float = None):
+        import threading
+        if self._thread is not None:
+            return
+        self._stop = threading.Event()
+        every = float(interval if interval is not None else getattr(self.args, "log_upload_interval", 10.0))
+
+        def loop():
+            while not self._stop.wait(every):
+                self.log_upload()
+            self.log_upload()                       # final flush
+
+        self._thread = threading.Thread(target=loop, daemon=True, name="mlops-log-upload")
+        self._thread.start()
+
+    def stop_uploader(self):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join(timeout=15)
+            self._thread = None
 
 
 class MLOpsConfigs:
@@ -169,9 +263,27 @@ class MLOpsConfigs:
         cls._instance = cls(args)
         return cls._instance
 
+    CONFIG_URLS = {"release": "https://open.fedml.ai/fedmlOpsServer/configs/fetch",
+                   "test": "http://open-test.fedml.ai/fedmlOpsServer/configs/fetch",
+                   "dev": "http://open-dev.fedml.ai/fedmlOpsServer/configs/fetch",
+                   "local": "http://localhost:9000/fedmlOpsServer/configs/fetch"}
+
+    def fetch_remote(self, url=None):
+        """(mqtt_config, s3_config) from the MLOps config service (mlops_configs.py:29-68): POST
+        ``{"config_name": ["mqtt_config", "s3_config"]}``, answer ``{"code": "SUCCESS", "data": {...}}``."""
+        url = url or getattr(self.args, "mlops_config_url", None) or \
+            self.CONFIG_URLS.get(str(getattr(self.args, "config_version", "release")), self.CONFIG_URLS["release"])
+        resp = _post_json(url, {"config_name": ["mqtt_config", "s3_config"]})
+        if resp.get("code") != "SUCCESS":
+            raise RuntimeError(f"config service at {url} answered {resp.get('code')!r}")
+        data = resp.get("data", {})
+        return data.get("mqtt_config", {}), data.get("s3_config", {})
+
     def fetch_configs(self):
         import os
         import yaml
+        if getattr(self.args, "mlops_config_url", None):
+            return self.fetch_remote()
         out = []
         for key in ("mqtt_config_path", "s3_config_path"):
             p = getattr(self.args, key, None)

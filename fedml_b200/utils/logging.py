@@ -28,8 +28,10 @@ def init_logs(args, role=None):
     if getattr(args, "using_mlops", False) or getattr(args, "log_to_file", False):
         d = getattr(args, "log_file_dir", "./log") or "./log"
         os.makedirs(d, exist_ok=True)
-        fh = logging.FileHandler(os.path.join(
-            d, f"fedavg-cross-silo-run-{getattr(args, 'run_id', 0)}-edge-{getattr(args, 'edge_id', rank)}.log"))
+        path = os.path.join(d, f"fedavg-cross-silo-run-{getattr(args, 'run_id', 0)}-edge-{getattr(args, 'edge_id', rank)}.log")
+        fh = logging.FileHandler(path)
         fh._fedml_b200 = True
         fh.setFormatter(logging.Formatter(fmt))
         root.addHandler(fh)
+        return path
+    return None

@@ -482,3 +482,69 @@ def test_trpc_round_trip_between_two_processes(tmp_path):
              for r in (0, 1)]
     outs = [p.communicate(timeout=180)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs) and "TRPC_OK rank 0" in outs[0] and "TRPC_OK rank 1" in outs[1], outs
+
+
+def test_mlops_log_uploader_device_binding_and_package_download(tmp_path):
+    """MLOps side services against a local HTTP server: periodic run-log upload with retry (mlops_runtime_log.py:122-160),
+    edge binding (login.py:482-497), remote broker / S3 configs (mlops_configs.py:29-68), package download over http."""
+    import http.server
+    import logging
+    import zipfile
+    from types import SimpleNamespace
+    from fedml_b200.cli.edge_agent import bind_account_and_device_id, get_device_id, retrieve_package
+    from fedml_b200.core.mlops import MLOpsConfigs, MLOpsRuntimeLog
+    posts, fail_first = [], {"n": 1}
+    pkg = tmp_path / "client-package.zip"
+    with zipfile.ZipFile(pkg, "w") as z:
+        z.writestr("client-package/conf/fedml.yaml", "entry_config: {}\n")
+
+    class H(http.server.BaseHTTPRequestHandler):
+        def log_message(self, *a): pass
+        def do_GET(self):
+            data = pkg.read_bytes()
+            self.send_response(200); self.send_header("Content-Length", str(len(data))); self.end_headers(); self.wfile.write(data)
+        def do_POST(self):
+            body = json.loads(self.rfile.read(int(self.headers["Content-Length"])) or b"{}")
+            if self.path.endswith("/logs/update") and fail_first["n"] > 0:
+                fail_first["n"] -= 1
+                self.send_response(500); self.end_headers(); return
+            posts.append((self.path, body))
+            if self.path.endswith("/edges/binding"):
+                out = {"code": "SUCCESS", "data": {"id": 4711}}
+            elif self.path.endswith("/configs/fetch"):
+                out = {"code": "SUCCESS", "data": {"mqtt_config": {"BROKER_HOST": "h", "BROKER_PORT": 1883}, "s3_config": {"BUCKET_NAME": "b"}}}
+            else:
+                out = {"code": "SUCCESS"}
+            data = json.dumps(out).encode()
+            self.send_response(200); self.send_header("Content-Length", str(len(data))); self.end_headers(); self.wfile.write(data)
+
+    srv = http.server.ThreadingHTTPServer(("127.0.0.1", 0), H)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    base = f"http://127.0.0.1:{srv.server_address[1]}"
+    try:
+        assert bind_account_and_device_id(base + "/fedmlOpsServer/edges/binding", 42, get_device_id()) == 4711
+        assert posts[-1][1]["accountid"] == 42 and posts[-1][1]["deviceid"] == get_device_id()
+        mq, s3 = MLOpsConfigs(SimpleNamespace(mlops_config_url=base + "/fedmlOpsServer/configs/fetch")).fetch_configs()
+        assert mq["BROKER_PORT"] == 1883 and s3["BUCKET_NAME"] == "b"
+        got = retrieve_package(base + "/packages/client-package.zip", str(tmp_path / "dl"))
+        assert zipfile.ZipFile(got).namelist() == ["client-package/conf/fedml.yaml"]
+        # run log: file handler + uploader thread; the first post fails (HTTP 500) and the same lines are sent again
+        args = SimpleNamespace(run_id=77, rank=1, using_mlops=True, log_file_dir=str(tmp_path / "logs"), log_level="INFO",
+                               log_server_url=base + "/fedmlLogsServer/logs/update", log_upload_interval=0.2)
+        rl = MLOpsRuntimeLog.get_instance(args)
+        rl.init_logs()
+        logging.info("first line of the run")
+        logging.info("second line of the run")
+        deadline = time.time() + 10
+        while not [p for p in posts if p[0].endswith("/logs/update")] and time.time() < deadline:
+            time.sleep(0.05)
+        rl.stop_uploader()
+        ups = [b for p, b in posts if p.endswith("/logs/update")]
+        assert ups and ups[0]["run_id"] == 77 and ups[0]["edge_id"] == 1 and ups[0]["created_by"] == "1"
+        text = "".join(line for u in ups for line in u["logs"])
+        assert text.count("first line of the run") == 1 and text.count("second line of the run") == 1 and fail_first["n"] == 0
+    finally:
+        srv.shutdown()
+        for h in list(logging.getLogger().handlers):
+            if getattr(h, "_fedml_b200", False):
+                logging.getLogger().removeHandler(h)
