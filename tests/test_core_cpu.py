@@ -368,3 +368,28 @@ def test_real_dataset_readers_from_files(tmp_path):
     (tmp_path / "fed_cifar100_test.h5").write_bytes(b"not really hdf5")
     with pytest.raises(ImportError, match="h5py"):
         load(dataset="fed_cifar100", model="resnet18_gn")
+
+
+def test_synchronized_batchnorm_equals_batchnorm_on_the_global_batch():
+    """SyncBN over a 2-process gloo group == nn.BatchNorm2d on the concatenated batch: outputs, input / parameter
+    gradients, running statistics, state_dict keys (reference model/cv/batchnorm_utils.py:156-266)."""
+    import os
+    import subprocess
+    import sys
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    worker = os.path.join(os.path.dirname(os.path.abspath(__file__)), "syncbn_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                              env=dict(os.environ, RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port)))
+             for r in range(2)]
+    outs = [p.communicate(timeout=180)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs) and all(f"SYNCBN_OK {r}" in outs[r] for r in range(2)), outs
+    # without a process group it is plain BatchNorm
+    import torch
+    import torch.nn as nn
+    from fedml_b200.models.sync_batchnorm import SynchronizedBatchNorm2d
+    torch.manual_seed(0)
+    a, b = nn.BatchNorm2d(5), SynchronizedBatchNorm2d(5)
+    x = torch.randn(4, 5, 3, 3)
+    torch.testing.assert_close(b(x), a(x), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(b.running_var, a.running_var, rtol=1e-5, atol=1e-6)
