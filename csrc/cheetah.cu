@@ -30,19 +30,37 @@ FB_DEFINE_SPIN_API(fb_dp)
 
 __device__ void dp_body(const FbDpStepParams& p, int block, int nblocks) {
   const int G = p.G, rank = p.rank;
+  const int64_t off = p.offset;          // this launch covers elements [offset, offset + n) of the buckets (one gradient bucket)
   const int64_t nvec = p.n / 4;
   const int64_t S4 = (nvec + G - 1) / G;
   const int64_t lo = (int64_t)rank * S4, hi = min(lo + S4, nvec);
   if (G > 1) dp_signal_wait(p.peer_flags, 0, rank, G, block, p.epoch);
   for (int64_t v = lo + (int64_t)block * blockDim.x + threadIdx.x; v < hi; v += (int64_t)nblocks * blockDim.x) {
-    const int64_t j = v * 4;
+    const int64_t j = off + v * 4;
     float4 g = make_float4(0, 0, 0, 0);
-    for (int q = 0; q < G; ++q) {
-      float4 x;
-      const float* src = p.peer_grad[q] + j;
-      asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-                   : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "l"(src) : "memory");
-      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+    if (G <= 8) {
+      // all peer loads are issued before the first add: G NVLink round trips overlap instead of queueing
+      float4 xs[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (q < G) {
+          const float* src = p.peer_grad[q] + j;
+          asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(xs[q].x), "=f"(xs[q].y), "=f"(xs[q].z), "=f"(xs[q].w) : "l"(src) : "memory");
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (q < G) { g.x += xs[q].x; g.y += xs[q].y; g.z += xs[q].z; g.w += xs[q].w; }
+      }
+    } else {
+      for (int q = 0; q < G; ++q) {
+        float4 x;
+        const float* src = p.peer_grad[q] + j;
+        asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "l"(src) : "memory");
+        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      }
     }
     g.x *= p.inv_world; g.y *= p.inv_world; g.z *= p.inv_world; g.w *= p.inv_world;
     float4 w = *reinterpret_cast<const float4*>(p.peer_param[rank] + j);
@@ -70,10 +88,11 @@ __global__ void __launch_bounds__(DP_THREADS) dp_kernel_emulated(const FbDpStepP
   dp_body(sp, blockIdx.x, gridDim.x);
 }
 
-static int dp_grid(int64_t n, int G, int emulated) {
+static int dp_grid(int64_t n, int G, int emulated, int max_blocks = 0) {
   const int64_t S4 = (n / 4 + G - 1) / G;
   int64_t want = (S4 + DP_THREADS - 1) / DP_THREADS;
   int cap = 2 * fb_num_sms();
+  if (max_blocks > 0 && cap > max_blocks) cap = max_blocks;     // overlapped buckets leave most SMs to the backward pass
   if (emulated > 1) cap /= emulated;
   if (cap > FB_ROUND_MAX_BLOCKS) cap = FB_ROUND_MAX_BLOCKS;
   if (cap < 1) cap = 1;
@@ -82,7 +101,8 @@ static int dp_grid(int64_t n, int G, int emulated) {
 }
 
 static int dp_check(const FbDpStepParams* p) {
-  FB_REQUIRE(p && p->peer_grad && p->peer_param && p->n > 0 && p->n % 4 == 0, "fb_dp_allreduce_step: bad bucket");
+  FB_REQUIRE(p && p->peer_grad && p->peer_param && p->n > 0 && p->n % 4 == 0 && p->offset >= 0 && p->offset % 4 == 0,
+             "fb_dp_allreduce_step: bad bucket");
   FB_REQUIRE(p->G >= 1 && p->G <= 64 && p->rank >= 0 && p->rank < p->G, "fb_dp_allreduce_step: bad rank/G");
   FB_REQUIRE(p->G == 1 || p->peer_flags, "fb_dp_allreduce_step: flags missing");
   return FB_OK;
@@ -93,7 +113,7 @@ extern "C" int fb_dp_allreduce_step(const FbDpStepParams* p, fb_stream_t stream)
   if (rc) return rc;
   FbDpStepParams local = *p;
   void* args[] = {&local};
-  FB_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)dp_kernel, dim3(dp_grid(p->n, p->G, 1)), dim3(DP_THREADS), args, 0,
+  FB_CHECK_CUDA(cudaLaunchCooperativeKernel((const void*)dp_kernel, dim3(dp_grid(p->n, p->G, 1, p->max_blocks)), dim3(DP_THREADS), args, 0,
                                             (cudaStream_t)stream));
   return FB_OK;
 }

@@ -74,7 +74,7 @@ class FbDpStepParams(C.Structure):
         ("peer_grad", C.c_void_p), ("peer_param", C.c_void_p), ("peer_flags", C.c_void_p), ("mom", C.c_void_p),
         ("n", C.c_int64), ("rank", C.c_int32), ("G", C.c_int32), ("epoch", C.c_uint32),
         ("lr", C.c_float), ("momentum", C.c_float), ("weight_decay", C.c_float), ("inv_world", C.c_float),
-        ("nesterov", C.c_int32),
+        ("nesterov", C.c_int32), ("max_blocks", C.c_int32), ("offset", C.c_int64),
     ]
 
 

@@ -6,9 +6,11 @@ peer-visible region (``bind_module_to_flat`` re-points ``p.data`` / ``p.grad`` a
 ``loss.backward()`` the whole gradient is already a contiguous buffer every peer can read.  ``step()`` is ONE
 launch of ``fb_dp_allreduce_step`` (csrc/cheetah.cu): reduce-scatter by pulling peers' gradient shards over
 NVLink, SGD(+momentum, weight decay) on the owned shard, all-gather by pushing the new parameters to every
-rank.  No NCCL call and no per-tensor optimizer kernels on the step path.  With ``overlap=True`` buckets of
-the flat gradient are reduced on a side stream as soon as autograd has produced them (hooks on the last
-parameter of each bucket), overlapping communication with the rest of backward.
+rank.  No NCCL call and no per-tensor optimizer kernels on the step path.  With ``overlap=True`` the flat gradient is
+cut into ``n_buckets`` contiguous buckets (at parameter boundaries); a post-accumulate hook on every parameter counts a
+bucket's parameters down and, when the last one has its gradient, launches that bucket's reduce-scatter -> SGD ->
+all-gather kernel on a side stream with a capped grid, so the transfer of the late layers' gradients runs under the
+backward pass of the early layers; ``step()`` launches whatever is left and joins the side stream.
 On CPU / gloo (tests) the same interface falls back to ``all_reduce`` + the same update rule."""
 from __future__ import annotations
 
@@ -56,6 +58,33 @@ class CheetahEngine:
             self.grad = torch.zeros(self.layout.P, dtype=torch.float32)
         bind_module_to_flat(self.model, self.layout, self.flat, self.grad)
         self.mom = torch.zeros(n, dtype=torch.float32, device=self.device) if momentum else None
+        # ---- gradient buckets (contiguous element ranges of the flat arena, cut at parameter boundaries)
+        self.overlap = bool(overlap) and self.cuda and self.world > 1
+        self.n_buckets = max(1, int(n_buckets)) if self.overlap else 1
+        self.max_blocks_overlap = int(os.environ.get("FB_CHEETAH_OVERLAP_BLOCKS", "48"))
+        segs = [sg for sg in self.layout.segments if sg.kind == "param"]
+        target = (n + self.n_buckets - 1) // self.n_buckets
+        self.buckets: List[List[int]] = []          # [offset, length]
+        start = 0
+        for sg in segs:
+            end = sg.offset + (sg.numel + 3) // 4 * 4
+            if end - start >= target or sg is segs[-1]:
+                self.buckets.append([start, min(end, n) - start])
+                start = min(end, n)
+        self.buckets = [b for b in self.buckets if b[1] > 0]
+        self._bucket_of = {}
+        params = dict(self.model.named_parameters())
+        self._pending = [0] * len(self.buckets)
+        for sg in segs:
+            bi = next(i for i, (o, ln) in enumerate(self.buckets) if o <= sg.offset < o + ln)
+            self._bucket_of[sg.name] = bi
+        self._launched = [False] * len(self.buckets)
+        self._side = torch.cuda.Stream(self.device) if self.overlap else None
+        if self.overlap:
+            for name, p in params.items():
+                if p.requires_grad and name in self._bucket_of:
+                    p.register_post_accumulate_grad_hook(self._make_hook(self._bucket_of[name]))
+            self._arm()
         if self.world > 1:      # replicas start identical
             if self.cuda:
                 self.region.barrier()
@@ -63,6 +92,38 @@ class CheetahEngine:
             if self.cuda:
                 self.region.barrier()
         self.group = group
+
+    # ---- overlap machinery
+    def _arm(self):
+        params = dict(self.model.named_parameters())
+        self._pending = [0] * len(self.buckets)
+        for name, bi in self._bucket_of.items():
+            if params[name].requires_grad:
+                self._pending[bi] += 1
+        self._launched = [False] * len(self.buckets)
+
+    def _make_hook(self, bi):
+        def hook(_param):
+            self._pending[bi] -= 1
+            if self._pending[bi] == 0 and not self._launched[bi]:
+                self._side.wait_stream(torch.cuda.current_stream(self.device))     # the bucket's gradients are complete
+                with torch.cuda.stream(self._side):
+                    self._launch_bucket(bi, self.max_blocks_overlap)
+        return hook
+
+    def _launch_bucket(self, bi, max_blocks=0):
+        from ..ops.native import FbDpStepParams, check, lib, stream_ptr
+        off, ln = self.buckets[bi]
+        self.epoch += 1
+        p = FbDpStepParams()
+        p.peer_grad, p.peer_param, p.peer_flags = self._peer_grad.data_ptr(), self._peer_param.data_ptr(), self._peer_flags.data_ptr()
+        p.mom = self.mom.data_ptr() if self.mom is not None else None
+        p.n, p.offset, p.rank, p.G, p.epoch = ln, off, self.rank, self.world, self.epoch
+        p.lr, p.momentum, p.weight_decay, p.inv_world, p.nesterov = self.lr, self.momentum, self.wd, 1.0 / self.world, int(self.nesterov)
+        p.max_blocks = int(max_blocks)
+        check(lib().fb_dp_allreduce_step(C.byref(p), C.c_void_p(stream_ptr(self.device))), "dp_allreduce_step")
+        self.native.count_launch()
+        self._launched[bi] = True
 
     def zero_grad(self):
         self.grad.zero_()
@@ -82,15 +143,19 @@ class CheetahEngine:
                 d = d + self.momentum * self.mom if self.nesterov else self.mom
             w.sub_(self.lr * d)
             return
-        from ..ops.native import FbDpStepParams, check, lib, stream_ptr
-        self.epoch += 1
-        p = FbDpStepParams()
-        p.peer_grad, p.peer_param, p.peer_flags = self._peer_grad.data_ptr(), self._peer_param.data_ptr(), self._peer_flags.data_ptr()
-        p.mom = self.mom.data_ptr() if self.mom is not None else None
-        p.n, p.rank, p.G, p.epoch = n, self.rank, self.world, self.epoch
-        p.lr, p.momentum, p.weight_decay, p.inv_world, p.nesterov = self.lr, self.momentum, self.wd, 1.0 / self.world, int(self.nesterov)
-        check(lib().fb_dp_allreduce_step(C.byref(p), C.c_void_p(stream_ptr(self.device))), "dp_allreduce_step")
-        self.native.count_launch()
+        if self.overlap:
+            # buckets whose hooks fired are already in flight on the side stream (same order on every rank: autograd visits
+            # the parameters of identical replicas in the same order); launch the rest behind them and join
+            self._side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._side):
+                for bi in reversed(range(len(self.buckets))):
+                    if not self._launched[bi]:
+                        self._launch_bucket(bi, 0)
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._arm()
+            return
+        for bi in range(len(self.buckets)):
+            self._launch_bucket(bi, 0)
 
     def state_dict(self):
         return self.layout.unflatten(self.flat.detach().cpu())

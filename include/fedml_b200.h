@@ -426,6 +426,8 @@ typedef struct {
   uint32_t epoch;
   float lr, momentum, weight_decay, inv_world;
   int32_t nesterov;
+  int32_t max_blocks;         /* > 0: cap on the grid (a bucket reduced while the backward pass still runs) */
+  int64_t offset;             /* elements: the launch covers [offset, offset + n) of the buckets, momentum included */
 } FbDpStepParams;
 int fb_dp_allreduce_step(const FbDpStepParams* p, fb_stream_t stream);
 int fb_dp_allreduce_step_emulated(const FbDpStepParams* params_dev, int32_t G, int64_t n, fb_stream_t stream);

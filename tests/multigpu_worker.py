@@ -68,6 +68,29 @@ def main():
         eng.step()
         torch.cuda.synchronize()
         out[f"cheetah_step{step}"] = float((eng.flat[:eng.n] - ref_w).abs().max())
+    # ---- Cheetah with bucketed overlap (hooks launch each bucket's fused step on a side stream during backward)
+    from fedml_b200.models import resnet56
+    torch.manual_seed(2)
+    net = resnet56(class_num=10)
+    eng2 = CheetahEngine(net, dev, lr=0.05, momentum=0.9, weight_decay=1e-4, n_buckets=6, overlap=True)
+    ref_w2 = eng2.flat[:eng2.n].clone(); ref_m2 = torch.zeros_like(ref_w2)
+    out["cheetah_overlap_buckets"] = len(eng2.buckets)
+    for step in range(3):
+        torch.manual_seed(2000 * step + rank)
+        x = torch.randn(16, 3, 32, 32, device=dev); y = torch.randint(0, 10, (16,), device=dev)
+        eng2.zero_grad()
+        eng2.model.train()
+        torch.nn.functional.cross_entropy(eng2.model(x), y).backward()
+        early = sum(eng2._launched)                      # buckets already in flight when backward returns
+        torch.cuda.synchronize()
+        g = eng2.grad[:eng2.n].clone()
+        eng2.step()
+        dist.all_reduce(g); g /= world
+        d = g + 1e-4 * ref_w2
+        ref_m2 = 0.9 * ref_m2 + d; ref_w2 = ref_w2 - 0.05 * ref_m2
+        torch.cuda.synchronize()
+        out[f"cheetah_overlap_step{step}"] = float((eng2.flat[:eng2.n] - ref_w2).abs().max())
+        out[f"cheetah_overlap_early{step}"] = int(early)
     # ---- NCCL simulator end-to-end on real ranks: robust aggregators over peer rows + G-invariance of the global model
     import fedml_b200 as fedml
     from fedml_b200.arguments import Arguments

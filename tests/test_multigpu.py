@@ -24,8 +24,10 @@ def test_round_engine_and_cheetah_on_real_ranks(tmp_path):
         if k.startswith("round_"):
             assert v["identical"], k
             assert v["err"] < (2e-3 if "adam" in k else 2e-5), (k, v)
-        if k.startswith("cheetah_"):
+        if k.startswith("cheetah_step") or k.startswith("cheetah_overlap_step"):
             assert v < 1e-5, (k, v)
+        if k.startswith("cheetah_overlap_early"):
+            assert v >= 1, (k, v)            # at least one bucket was launched from a hook, before step()
         if k.startswith("sim_"):
             assert v["identical"] and v["finite"], (k, v)
     # the G-rank result equals what one GPU computes for the same seeds (G-invariance of the simulator)
