@@ -125,5 +125,12 @@ def bind_module_to_flat(model: nn.Module, layout: ArenaLayout, flat: torch.Tenso
         v.copy_(b.detach().to(torch.float32))
         mod_name, _, leaf = name.rpartition(".")
         mod = model.get_submodule(mod_name) if mod_name else model
-        mod._buffers[leaf] = v
+        # re-point the existing buffer at the arena through .data: the buffer keeps its OWN autograd version counter.
+        # Installing the view itself would make every buffer share the arena's counter, and cuDNN BatchNorm saves its
+        # running statistics for backward: the next layer's in-place running-stat update would then invalidate them
+        # ("modified by an inplace operation").
+        if isinstance(mod._buffers.get(leaf), torch.Tensor):
+            mod._buffers[leaf].data = v
+        else:
+            mod._buffers[leaf] = v
     return model

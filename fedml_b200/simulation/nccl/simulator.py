@@ -656,6 +656,8 @@ class NCCLSimulator:
         base = sum(len(a) for a in schedule_clients(sizes, self.world)[:self.rank])
         if self.robust in ("median", "trimmed_mean", "krum"):
             return self._aggregate_robust(weights, total, my_pos, sizes, round_idx)
+        if bool(getattr(args, "secure_aggregation", False)):
+            return self._aggregate_secure(weights, total, my_pos, sizes, round_idx, base)
         if self.alg == "FedNova":
             coefs = self._fednova_coefs(sizes, my_pos)
             cw = torch.zeros(self.C_max, dtype=torch.float32)
@@ -713,6 +715,51 @@ class NCCLSimulator:
             self.global_flat[Pt:] = part[Pt:]
         else:
             self.global_flat.copy_(part)
+
+    def _aggregate_secure(self, weights, total, my_pos, sizes, round_idx, base):
+        """``secure_aggregation: true``: every simulated client uploads its weighted model as a quantised field vector
+        under pairwise masks (core/security/secagg.py; masks expanded by ``fb_ff_mask`` from Philox, never materialised),
+        the "server" only ever adds masked vectors (``fb_ff_add``), across GPUs as an integer all-reduce; the pairwise
+        masks cancel in the sum, which de-quantises to the weighted mean.  Key agreement runs once per simulator (public
+        keys only are shared); the round index enters the mask PRG."""
+        from ...core.security.mpc_function import DEFAULT_PRIME
+        from ...core.security.secagg import SecAggClient
+        K = self.K
+        p = DEFAULT_PRIME
+        scale = float(getattr(self.args, "secagg_scale", 2 ** 16))
+        if getattr(self, "_sec_clients", None) is None:
+            rng = np.random.default_rng(int(getattr(self.args, "random_seed", 0)) + 99173)   # same slot keys on every rank
+            self._sec_clients = [SecAggClient(i, p, rng=rng) for i in range(K)]
+            pks = {c.cid: c.pk for c in self._sec_clients}
+            for c in self._sec_clients:
+                c.agree(pks)
+        parts = list(range(K))
+        Pq = self.P
+        acc = None
+        for i, pos in enumerate(my_pos):
+            cl = self._sec_clients[pos]                       # slot `pos` of this round's sample
+            row = self.stack[i]
+            masked = cl.mask(row, float(sizes[pos]) / total, scale, parts, round_idx=round_idx)
+            if acc is None:
+                acc = masked.clone()
+            elif self.cuda:
+                from ... import ops
+                ops.ff_add_(acc, masked, p)
+            else:
+                acc = torch.remainder(acc + masked, p)
+        if acc is None:
+            acc = torch.zeros(Pq, dtype=torch.int32 if self.cuda else torch.int64, device=self.device)
+        if self.world > 1:
+            wide = acc.to(torch.int64)
+            dist.all_reduce(wide)                              # sum of G residues < G * p: no overflow in int64
+            acc = torch.remainder(wide, p).to(acc.dtype)
+        if self.cuda:
+            from ... import ops
+            mean = ops.ff_dequantize(acc, scale, p)
+        else:
+            signed = torch.where(acc > p // 2, acc - p, acc)
+            mean = (signed.double() / scale).to(torch.float32)
+        self.global_flat.copy_(mean.view(-1)[:self.P])
 
     def _aggregate_robust(self, weights, total, my_pos, sizes, round_idx):
         """Median / trimmed mean / Krum over all K client rows (they live on G GPUs)."""

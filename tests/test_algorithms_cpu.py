@@ -384,3 +384,19 @@ def test_darts_second_order_architect_and_gdas():
         ds, model = build(a_)
         r = SimulatorMPI(a_, CPU, ds, model).run()
         assert len(r.history) >= 1 and r.genotype is not None
+
+
+def test_nccl_simulator_secure_aggregation_matches_plain_fedavg():
+    """secure_aggregation in the multi-GPU simulator (CPU path here): pairwise-masked quantised uploads sum to the same
+    global model as plain FedAvg, up to the quantisation step."""
+    from fedml_b200.simulation import SimulatorNCCL
+    outs = []
+    for sec in (False, True):
+        a = mk(backend="NCCL", comm_round=2, client_num_per_round=4, frequency_of_the_test=0, secure_aggregation=sec, using_gpu=False)
+        ds, model = build(a)
+        torch.manual_seed(0)
+        sim = SimulatorNCCL(a, CPU, ds, copy.deepcopy(model)).simulator
+        for r in range(2):
+            sim.train_one_round(r)
+        outs.append(sim.global_flat.clone())
+    assert float((outs[0] - outs[1]).abs().max()) < 4 * 4 / 2 ** 16 and not torch.equal(outs[0], outs[1])

@@ -154,3 +154,28 @@ def test_many_client_median_and_trimmed_mean_sorted_runs(K, P):
         assert torch.equal(out, torch.median(x, dim=0).values)
         ops.robust_select_runs(rows, G * C_max, K, L, 0, P, "trimmed_mean", trim, outs, 1)
         torch.testing.assert_close(out.double(), ref, rtol=1e-5, atol=1e-6)
+
+
+def test_nccl_simulator_secure_aggregation_on_the_field_kernels():
+    """secure_aggregation in the NCCL simulator on the GPU: fb_ff_quantize / fb_ff_mask (round nonce) / fb_ff_add /
+    fb_ff_dequantize give the plain FedAvg model up to the quantisation step."""
+    import fedml_b200 as fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.ops import native
+    from fedml_b200.simulation import SimulatorNCCL
+    outs = []
+    for sec in (False, True):
+        a = fedml.init(Arguments.from_dict(dict(
+            training_type="simulation", backend="NCCL", dataset="mnist", model="lr", client_num_per_round=6, comm_round=2,
+            batch_size=10, learning_rate=0.03, frequency_of_the_test=0, synthetic_train_size=1200, mnist_client_num=12,
+            log_level="ERROR", using_gpu=True, compute_dtype="fp32", secure_aggregation=sec, random_seed=0)))
+        ds, ncls = fedml.data.load(a)
+        torch.manual_seed(0)
+        sim = SimulatorNCCL(a, torch.device(DEV), ds, fedml.models.create(a, ncls)).simulator
+        before = native.LAUNCHES[0]
+        for r in range(2):
+            sim.train_one_round(r)
+        torch.cuda.synchronize()
+        outs.append((sim.global_flat.clone(), native.LAUNCHES[0] - before))
+    assert float((outs[0][0] - outs[1][0]).abs().max()) < 6 * 4 / 2 ** 16
+    assert outs[1][1] > outs[0][1]                       # the field kernels ran
