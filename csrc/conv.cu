@@ -129,10 +129,45 @@ bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict_
                 const float* __restrict__ beta, int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r,
                 const float* __restrict__ active, float momentum, float eps, int relu, int training,
                 float* __restrict__ save_mean, float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n,
-                float* sm /* scale[ch], shift[ch] */, int SP /* slices of `partial` per client (1: complete sums) */) {
+                float* sm /* scale[ch], shift[ch] (+ 2*ch scratch when cpg > 1) */,
+                int SP /* slices of `partial` per client (1: complete sums) */,
+                int cb = 1 /* rows (blockIdx.y) per parameter set: GroupNorm runs one row per (client, sample) */,
+                int cpg = 0 /* > 1: GroupNorm, statistics over the row's pixels x cpg adjacent channels */) {
   float* scale = sm;
   float* shift = sm + ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int cp = c / cb;                 // row of gamma / beta / running statistics
+  if (cpg > 1) {
+    // GroupNorm (reference model/cv/group_normalization.py:7-93): per-channel sums of this (client, sample) row, then the
+    // cpg channels of a group are pooled; no running statistics
+    float* t_su = sm + 2 * ch;
+    float* t_sq = sm + 3 * ch;
+    for (int k = tid; k < ch; k += BN_THREADS) {
+      float su = 0.f, sq = 0.f;
+      for (int j = 0; j < SP; ++j) {
+        su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);
+        sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
+      }
+      t_su[k] = su;
+      t_sq[k] = sq;
+    }
+    __syncthreads();
+    for (int k = tid; k < ch; k += BN_THREADS) {
+      const int g0 = k - k % cpg;
+      float su = 0.f, sq = 0.f;
+      for (int i = 0; i < cpg; ++i) { su += t_su[g0 + i]; sq += t_sq[g0 + i]; }
+      const float n = (float)M * (float)cpg;
+      const float mean = su / n, var = fmaxf(sq / n - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      if (s == 0 && save_mean) {
+        save_mean[(size_t)c * ch + k] = mean;
+        save_rstd[(size_t)c * ch + k] = rstd;
+      }
+      const float g = gamma[(size_t)cp * ld_p + k] * rstd;
+      scale[k] = g;
+      shift[k] = beta[(size_t)cp * ld_p + k] - mean * g;
+    }
+  } else {
   if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
     num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
   for (int k = tid; k < ch; k += BN_THREADS) {
@@ -167,6 +202,7 @@ bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict_
     const float g = gamma[(size_t)c * ld_p + k] * rstd;
     scale[k] = g;
     shift[k] = beta[(size_t)c * ld_p + k] - mean * g;
+  }
   }
   __syncthreads();
   const int64_t rows_per = (M + S - 1) / S;
@@ -248,12 +284,12 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
                 int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                 int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                 float momentum, float eps, int relu, int training, float* __restrict__ save_mean,
-                float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n, int SP) {
+                float* __restrict__ save_rstd, float* num_batches_tracked, int64_t ld_n, int SP, int cb, int cpg) {
   extern __shared__ float sm[];
   pdl_wait();
   pdl_trigger();
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu,
-                training, save_mean, save_rstd, num_batches_tracked, ld_n, sm, SP);
+                training, save_mean, save_rstd, num_batches_tracked, ld_n, sm, SP, cb, cpg);
 }
 
 // Barrier among the S CTAs of one client (blockIdx.y): {arrival count, generation} per client, self-resetting, so
@@ -341,7 +377,7 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
   FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
       (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p,
       running_mean, running_var, ld_r, active, momentum, eps, relu, training ? 1 : 0, save_mean, save_rstd, num_batches_tracked, ld_n,
-      have_stats ? 1 : S));
+      have_stats ? 1 : S, 1, 0));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -354,8 +390,9 @@ bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
                     const T* __restrict__ x,
                     const T* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
-                    int64_t ld_p, int relu, float* __restrict__ partial, float* smem) {
+                    int64_t ld_p, int relu, float* __restrict__ partial, float* smem, int cb = 1) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int cp = c / cb;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = (int64_t)s * rows_per, r1 = min(M, r0 + rows_per);
   const size_t cbase = (size_t)c * M * ch;
@@ -365,8 +402,8 @@ bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const float mu = mean[(size_t)c * ch + coff + i], rs = rstd[(size_t)c * ch + coff + i];
-    g[i] = gamma[(size_t)c * ld_p + coff + i] * rs;
-    k[i] = (beta ? beta[(size_t)c * ld_p + coff + i] : 0.f) - mu * g[i];
+    g[i] = gamma[(size_t)cp * ld_p + coff + i] * rs;
+    k[i] = (beta ? beta[(size_t)cp * ld_p + coff + i] : 0.f) - mu * g[i];
   }
   // partial sums of dy' and dy'*x (raw x): the apply kernel turns them into dbeta and dgamma = rstd*(S_dx - mean*S_d)
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -423,13 +460,50 @@ bn_bwd_apply_body(const T* __restrict__ dy, const T* __restrict__ dy2,
                     int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma,
                     const float* __restrict__ beta, int64_t ld_p, const float* __restrict__ mean,
                     const float* __restrict__ rstd, int relu, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                    int64_t ld_g, float* sm) {
+                    int64_t ld_g, float* sm, int cb = 1, int cpg = 0) {
   // sm, per channel: A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g
   float* s_A = sm;
   float* s_B = sm + ch;
   float* s_C = sm + 2 * ch;
   float* s_K = sm + 3 * ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int cp = c / cb;
+  if (cpg > 1) {
+    // GroupNorm: dx = rstd * (gamma_k d - mean_g(gamma d) - xhat * mean_g(gamma d xhat)), means over the group's
+    // M x cpg elements; per-row dgamma / dbeta go to [rows][ch] and are summed over the samples of a client by the caller
+    float* t_a = sm + 4 * ch;      // gamma_k * sum d
+    float* t_b = sm + 5 * ch;      // gamma_k * sum d * xhat
+    for (int k = tid; k < ch; k += BN_THREADS) {
+      float sd = 0.f, sdx = 0.f;
+      for (int j = 0; j < S; ++j) {
+        sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
+        sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
+      }
+      const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
+      const float dxh = rs * (sdx - mu * sd);                       // sum d * xhat
+      if (s == 0) {
+        dbeta[(size_t)c * ld_g + k] = sd;
+        dgamma[(size_t)c * ld_g + k] = dxh;
+      }
+      const float gm = gamma[(size_t)cp * ld_p + k];
+      t_a[k] = gm * sd;
+      t_b[k] = gm * dxh;
+    }
+    __syncthreads();
+    for (int k = tid; k < ch; k += BN_THREADS) {
+      const int g0 = k - k % cpg;
+      float Ag = 0.f, Bg = 0.f;
+      for (int i = 0; i < cpg; ++i) { Ag += t_a[g0 + i]; Bg += t_b[g0 + i]; }
+      const float n = (float)M * (float)cpg;
+      const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
+      const float g = gamma[(size_t)cp * ld_p + k] * rs;
+      const float B = -rs * rs * Bg / n;
+      s_A[k] = g;
+      s_B[k] = B;
+      s_C[k] = -rs * Ag / n - mu * B;
+      s_K[k] = (beta ? beta[(size_t)cp * ld_p + k] : 0.f) - mu * g;
+    }
+  } else
   for (int k = tid; k < ch; k += BN_THREADS) {
     float sd = 0.f, sdx = 0.f;
     for (int j = 0; j < S; ++j) {
@@ -512,11 +586,11 @@ __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_stats_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x,
                     const T* __restrict__ y, int64_t M, int ch, int S, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
-                    int relu, float* __restrict__ partial) {
+                    int relu, float* __restrict__ partial, int cb) {
   __shared__ float smem[BN_THREADS * 16];
   pdl_wait();
   pdl_trigger();
-  bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
+  bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem, cb);
 }
 template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
@@ -524,11 +598,11 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T
                     const T* __restrict__ y, T* __restrict__ dx, T* __restrict__ dres, int64_t M,
                     int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, int relu,
-                    float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g) {
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t ld_g, int cb, int cpg) {
   extern __shared__ float sm[];
   pdl_wait();
   pdl_trigger();
-  bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
+  bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm, cb, cpg);
 }
 template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
@@ -567,11 +641,11 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
   }
   FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_stats_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(0), (cudaStream_t)stream, 
       (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, M, ch, S, save_mean, save_rstd, gamma,
-      beta, ld_p, relu, scratch));
+      beta, ld_p, relu, scratch, 1));
   FB_CHECK_CUDA(cudaGetLastError());
   FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_apply_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
       (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx,
-      (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+      (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g, 1, 0));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
@@ -666,6 +740,68 @@ static int col2im_impl(const void* cols, void* dx, int32_t n_img, int32_t H, int
       (const T*)cols, (T*)dx, total, H, W, Ho, Wo, ch, stride));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
+}
+
+// ---------------------------------------------------------------- GroupNorm (+residual, +ReLU) on the same kernels
+// A row is one (client, sample): rows = C * B, M = H * W pixels; statistics pool `cpg` adjacent channels of a row
+// (reference model/cv/group_normalization.py:7-93, resnet_gn.py:108-196: two channels per group by default); gamma / beta
+// are per client (row / rows_per_client).  Two launches per direction (statistics, apply); scratch as for BatchNorm
+// (fb_bn_scratch_floats(rows, M, ch)).  save_mean / save_rstd: [rows][ch] (group value repeated per channel).
+// Backward writes per-row dgamma / dbeta [rows][ch]; the caller sums them over the samples of a client.
+template <typename T>
+static int gn_fwd_impl(const void* x, const void* res, void* y, int32_t rows, int64_t M, int32_t ch, const float* gamma,
+                       const float* beta, int64_t ld_p, int32_t rows_per_client, int32_t cpg, float eps, int32_t relu,
+                       float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream) {
+  FB_REQUIRE(x && y && gamma && beta && save_mean && save_rstd && scratch && rows >= 1 && rows <= 65535 && M >= 1,
+             "fb_gn_fwd_stacked: bad arguments (at most 65535 rows)");
+  FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_gn_fwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
+  FB_REQUIRE(cpg >= 2 && ch % cpg == 0 && rows_per_client >= 1 && rows % rows_per_client == 0, "fb_gn_fwd_stacked: bad grouping");
+  const int S = bn_slices(rows, M, ch);
+  FB_CHECK_CUDA(fb_launch_pdl(bn_stats_kernel<T>, dim3(S, rows), dim3(BN_THREADS), (size_t)0, (cudaStream_t)stream, (const T*)x, M, (int)ch, S,
+                              scratch));
+  FB_CHECK_CUDA(fb_launch_pdl(bn_apply_kernel<T>, dim3(S, rows), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream,
+                              (const T*)x, (const T*)res, (T*)y, M, (int)ch, S, (const float*)scratch, gamma, beta, ld_p, (float*)nullptr,
+                              (float*)nullptr, (int64_t)0, (const float*)nullptr, 0.f, eps, (int)relu, 1, save_mean, save_rstd,
+                              (float*)nullptr, (int64_t)0, S, (int)rows_per_client, (int)cpg));
+  return FB_OK;
+}
+template <typename T>
+static int gn_bwd_impl(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t rows, int64_t M,
+                       int32_t ch, const float* gamma, const float* beta, int64_t ld_p, int32_t rows_per_client, int32_t cpg,
+                       const float* save_mean, const float* save_rstd, int32_t relu, float* dgamma_rows, float* dbeta_rows,
+                       float* scratch, fb_stream_t stream) {
+  FB_REQUIRE(dy && x && dx && gamma && save_mean && save_rstd && dgamma_rows && dbeta_rows && scratch && rows >= 1 && rows <= 65535,
+             "fb_gn_bwd_stacked: bad arguments (at most 65535 rows)");
+  FB_REQUIRE(!relu || y || beta, "fb_gn_bwd_stacked: the ReLU mask needs the forward output or beta to recompute it");
+  FB_REQUIRE(ch >= 8 && ch <= 2048 && (2048 % ch) == 0, "fb_gn_bwd_stacked: ch=%d must be a power of two in [8, 2048]", ch);
+  FB_REQUIRE(cpg >= 2 && ch % cpg == 0 && rows_per_client >= 1 && rows % rows_per_client == 0, "fb_gn_bwd_stacked: bad grouping");
+  const int S = bn_slices(rows, M, ch);
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_stats_kernel<T>, dim3(S, rows), dim3(BN_THREADS), (size_t)0, (cudaStream_t)stream, (const T*)dy,
+                              (const T*)dy2, (const T*)x, (const T*)y, M, (int)ch, S, save_mean, save_rstd, gamma, beta, ld_p, (int)relu,
+                              scratch, (int)rows_per_client));
+  FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_apply_kernel<T>, dim3(S, rows), dim3(BN_THREADS), (size_t)(6 * ch * sizeof(float)),
+                              (cudaStream_t)stream, (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, (int)ch, S,
+                              (const float*)scratch, gamma, beta, ld_p, save_mean, save_rstd, (int)relu, dgamma_rows, dbeta_rows,
+                              (int64_t)ch, (int)rows_per_client, (int)cpg));
+  return FB_OK;
+}
+extern "C" int fb_gn_fwd_stacked(const void* x, const void* res, void* y, int32_t act_fp32, int32_t rows, int64_t M, int32_t ch,
+                                 const float* gamma, const float* beta, int64_t ld_p, int32_t rows_per_client, int32_t cpg, float eps,
+                                 int32_t relu, float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream) {
+  if (act_fp32)
+    return gn_fwd_impl<float>(x, res, y, rows, M, ch, gamma, beta, ld_p, rows_per_client, cpg, eps, relu, save_mean, save_rstd, scratch, stream);
+  return gn_fwd_impl<__nv_bfloat16>(x, res, y, rows, M, ch, gamma, beta, ld_p, rows_per_client, cpg, eps, relu, save_mean, save_rstd, scratch,
+                                    stream);
+}
+extern "C" int fb_gn_bwd_stacked(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t act_fp32,
+                                 int32_t rows, int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
+                                 int32_t rows_per_client, int32_t cpg, const float* save_mean, const float* save_rstd, int32_t relu,
+                                 float* dgamma_rows, float* dbeta_rows, float* scratch, fb_stream_t stream) {
+  if (act_fp32)
+    return gn_bwd_impl<float>(dy, dy2, x, y, dx, dres, rows, M, ch, gamma, beta, ld_p, rows_per_client, cpg, save_mean, save_rstd, relu,
+                              dgamma_rows, dbeta_rows, scratch, stream);
+  return gn_bwd_impl<__nv_bfloat16>(dy, dy2, x, y, dx, dres, rows, M, ch, gamma, beta, ld_p, rows_per_client, cpg, save_mean, save_rstd,
+                                    relu, dgamma_rows, dbeta_rows, scratch, stream);
 }
 
 // ---------------------------------------------------------------- C ABI: bf16 and fp32 activation variants

@@ -142,6 +142,43 @@ class TorchBackend:
             dgamma_out.copy_(dgamma); dbeta_out.copy_(dbeta)
         return dx.view(x.shape).to(x.dtype), dres, dgamma, dbeta
 
+    # ---- GroupNorm (+residual, +ReLU): statistics per (client, sample, group of cpg channels) ------------
+    def gn_fwd(self, x, res, gamma, beta, cpg, eps, relu):
+        C, B, ch = x.shape[0], x.shape[1], x.shape[-1]
+        G = ch // cpg
+        xf = x.float().reshape(C, B, -1, G, cpg)
+        mean = xf.mean(dim=(2, 4))                                     # [C,B,G]
+        var = xf.var(dim=(2, 4), unbiased=False)
+        rstd = torch.rsqrt(var + eps)
+        xhat = (xf - mean[:, :, None, :, None]) * rstd[:, :, None, :, None]
+        y = xhat.reshape(C, B, -1, ch) * gamma[:, None, None, :] + beta[:, None, None, :]
+        y = y.view(x.shape)
+        if res is not None:
+            y = y + res.float()
+        if relu:
+            y = torch.relu(y)
+        rep = lambda t: t.repeat_interleave(cpg, dim=2).reshape(C * B, ch)   # noqa: E731
+        return y.to(x.dtype), rep(mean), rep(rstd)
+
+    def gn_bwd(self, dy, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None):
+        C, B, ch = x.shape[0], x.shape[1], x.shape[-1]
+        dyf = (dy[0].float() + dy[1].float()) if isinstance(dy, tuple) else dy.float()
+        if relu:
+            dyf = dyf * (y > 0)
+        dres = dyf.to(x.dtype) if want_dres else None
+        d = dyf.reshape(C, B, -1, ch)
+        mu, rs = mean.view(C, B, 1, ch), rstd.view(C, B, 1, ch)
+        xhat = (x.float().reshape(C, B, -1, ch) - mu) * rs
+        dbeta = d.sum(dim=(1, 2))
+        dgamma = (d * xhat).sum(dim=(1, 2))
+        dxh = d * gamma[:, None, None, :]
+        G = ch // cpg
+        gm = lambda t: t.reshape(C, B, -1, G, cpg).mean(dim=(2, 4), keepdim=True).expand(C, B, t.shape[2], G, cpg).reshape(t.shape)  # noqa: E731
+        dx = rs * (dxh - gm(dxh) - xhat * gm(dxh * xhat))
+        if dgamma_out is not None:
+            dgamma_out.copy_(dgamma); dbeta_out.copy_(dbeta)
+        return dx.view(x.shape).to(x.dtype), dres, dgamma, dbeta
+
     # ---- loss ---------------------------------------------------------------------
     def xent(self, logits, labels, pre_sigmoid=False, row_scale=None):
         """logits [C,B,ncls] fp32, labels [C,B] (-1 = padding row) -> (loss per client [C], dlogits [C,B,ncls]).
@@ -413,6 +450,20 @@ class NativeBackend(TorchBackend):
         self._fb("bn_bwd")
         return super().bn_bwd(dy, x, y, gamma, mean, rstd, relu, want_dres, dgamma_out=dgamma_out, dbeta_out=dbeta_out)
 
+    def gn_fwd(self, x, res, gamma, beta, cpg, eps, relu):
+        if x.dtype in self._ACT and self._bn_ok(x.shape[-1]) and x.shape[0] * x.shape[1] <= 65535 and cpg >= 2:
+            return self.ops.gn_fwd_stacked(x, res, gamma, beta, cpg, eps, relu)
+        self._fb("gn_fwd")
+        return super().gn_fwd(x, res, gamma, beta, cpg, eps, relu)
+
+    def gn_bwd(self, dy, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None):
+        if x.dtype in self._ACT and self._bn_ok(x.shape[-1]) and x.shape[0] * x.shape[1] <= 65535 and cpg >= 2:
+            d1, d2 = dy if isinstance(dy, tuple) else (dy, None)
+            return self.ops.gn_bwd_stacked(d1, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta=beta, dgamma_out=dgamma_out,
+                                           dbeta_out=dbeta_out, dy2=d2)
+        self._fb("gn_bwd")
+        return super().gn_bwd(dy, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta, dgamma_out, dbeta_out)
+
     fused_head = os.environ.get("FB_FUSED_HEAD", "1") != "0"
 
     def head_fwd_bwd(self, h, fc_w, fc_b, labels, row_scale, g_w, g_b):
@@ -619,11 +670,21 @@ class _Conv:
 
 
 class _BN:
-    def __init__(self, name, ch, momentum=0.1, eps=1e-5):
-        self.name, self.ch, self.momentum, self.eps = name, ch, momentum, eps
+    """BatchNorm (cpg = 0) or GroupNorm with ``cpg`` channels per group, each with fused residual add and ReLU."""
+
+    def __init__(self, name, ch, momentum=0.1, eps=1e-5, cpg=0):
+        self.name, self.ch, self.momentum, self.eps, self.cpg = name, ch, momentum if momentum is not None else 0.1, eps, cpg
+
+    @classmethod
+    def of(cls, name, mod):
+        if isinstance(mod, nn.GroupNorm):
+            return cls(name, mod.num_channels, None, mod.eps, cpg=mod.num_channels // mod.num_groups)
+        return cls(name, mod.num_features, mod.momentum, mod.eps)
 
     def fwd(self, be, x, W, active, relu, res=None, training=True, stats=None):
         n = self.name
+        if self.cpg:
+            return be.gn_fwd(x, res, W[n + ".weight"], W[n + ".bias"], self.cpg, self.eps, relu)
         if stats is not None:
             return be.bn_fwd(x, res, W[n + ".weight"], W[n + ".bias"], W[n + ".running_mean"], W[n + ".running_var"],
                              W[n + ".num_batches_tracked"], active, self.momentum, self.eps, relu, training, stats=stats)
@@ -632,6 +693,10 @@ class _BN:
 
     def bwd(self, be, dy, x, y, W, G, mean, rstd, relu, want_dres):
         n = self.name
+        if self.cpg:
+            dx, dres, _, _ = be.gn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, self.cpg, relu, want_dres, beta=W[n + ".bias"],
+                                       dgamma_out=G[n + ".weight"], dbeta_out=G[n + ".bias"])
+            return dx, dres
         dx, dres, _, _ = be.bn_bwd(dy, x, y, W[n + ".weight"], mean, rstd, relu, want_dres, beta=W[n + ".bias"],
                                    had_res=want_dres, dgamma_out=G[n + ".weight"], dbeta_out=G[n + ".bias"])
         return dx, dres
@@ -648,13 +713,12 @@ class _Block:
         for i in range(1, n + 1):
             c = getattr(mod, f"conv{i}")
             self.convs.append(_Conv(f"{prefix}.conv{i}", c.kernel_size[0], c.stride[0], c.in_channels, c.out_channels))
-            self.bns.append(_BN(f"{prefix}.bn{i}", c.out_channels, getattr(mod, f"bn{i}").momentum,
-                                getattr(mod, f"bn{i}").eps))
+            self.bns.append(_BN.of(f"{prefix}.bn{i}", getattr(mod, f"bn{i}")))
         self.ds = None
         if mod.downsample is not None:
             c, b = mod.downsample[0], mod.downsample[1]
             self.ds = (_Conv(f"{prefix}.downsample.0", 1, c.stride[0], c.in_channels, c.out_channels),
-                       _BN(f"{prefix}.downsample.1", c.out_channels, b.momentum, b.eps))
+                       _BN.of(f"{prefix}.downsample.1", b))
 
     def all_convs(self):
         return self.convs + ([self.ds[0]] if self.ds else [])
@@ -762,7 +826,8 @@ class BatchedResNet(BatchedModel):
         pad = 8 if (isinstance(backend, NativeBackend) and c1.in_channels % 8) else None
         self.stem_conv = _Conv("conv1", c1.kernel_size[0], c1.stride[0], c1.in_channels, c1.out_channels, need_dx=False,
                                cin_pad=pad)
-        self.stem_bn = _BN("bn1", c1.out_channels, module.bn1.momentum, module.bn1.eps)
+        self.stem_bn = _BN.of("bn1", module.bn1)
+        self.uses_batch_statistics = not self.stem_bn.cpg          # GroupNorm statistics are per sample: ragged batches are fine
         self.blocks: List[_Block] = []
         for li in range(1, module.num_stages + 1):
             for bi, blk in enumerate(getattr(module, f"layer{li}")):
@@ -1011,7 +1076,7 @@ def make_batched(module: nn.Module, backend: TorchBackend) -> Optional[BatchedMo
     (the simulator then falls back to per-client eager training on arena-bound parameters)."""
     if isinstance(module, LogisticRegression):
         return BatchedLogisticRegression(module, backend)
-    if isinstance(module, ResNet) and module.group_norm == 0 and not module.KD:
+    if isinstance(module, ResNet) and not module.KD:
         try:
             return BatchedResNet(module, backend)
         except NotImplementedError:

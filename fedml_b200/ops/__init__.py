@@ -420,6 +420,49 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgam
     return dx, dres, dgamma, dbeta
 
 
+def gn_fwd_stacked(x, res, gamma, beta, cpg, eps, relu):
+    """GroupNorm(+residual, +ReLU): x [C,B,H,W,ch] bf16 / fp32, gamma / beta fp32 [C, ch] arena views, ``cpg`` channels per
+    group -> (y, save_mean [C*B, ch], save_rstd [C*B, ch])."""
+    Cn, B, ch = x.shape[0], x.shape[1], x.shape[-1]
+    rows = Cn * B
+    M = x.numel() // (rows * ch)
+    x = x.contiguous()
+    y = torch.empty_like(x)
+    mean = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
+    rstd = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
+    scratch = _scratch_for(x.device, rows * 64 * 2 * ch)
+    check(lib().fb_gn_fwd_stacked(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)),
+                                  i32(int(x.dtype == torch.float32)), i32(rows), i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)),
+                                  i64(gamma.stride(0)), i32(B), i32(cpg), f32(eps), i32(int(relu)), vp(ptr(mean)), vp(ptr(rstd)),
+                                  vp(ptr(scratch)), vp(stream_ptr(x.device))), "gn_fwd_stacked")
+    count_launch(2)
+    return y, mean, rstd
+
+
+def gn_bwd_stacked(dy, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta=None, dgamma_out=None, dbeta_out=None, dy2=None):
+    """Backward of :func:`gn_fwd_stacked`; dgamma / dbeta [C, ch] are the per-row results summed over a client's samples
+    (written into ``dgamma_out`` / ``dbeta_out`` when given)."""
+    Cn, B, ch = x.shape[0], x.shape[1], x.shape[-1]
+    rows = Cn * B
+    M = x.numel() // (rows * ch)
+    dy = dy.contiguous()
+    dy2 = dy2.contiguous() if dy2 is not None else None
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    dg_rows = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
+    db_rows = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
+    scratch = _scratch_for(x.device, rows * 64 * 2 * ch)
+    check(lib().fb_gn_bwd_stacked(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)),
+                                  i32(int(x.dtype == torch.float32)), i32(rows), i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)),
+                                  i64(gamma.stride(0)), i32(B), i32(cpg), vp(ptr(mean)), vp(ptr(rstd)), i32(int(relu)),
+                                  vp(ptr(dg_rows)), vp(ptr(db_rows)), vp(ptr(scratch)), vp(stream_ptr(x.device))), "gn_bwd_stacked")
+    count_launch(2)
+    dg, db = dg_rows.view(Cn, B, ch).sum(dim=1), db_rows.view(Cn, B, ch).sum(dim=1)
+    if dgamma_out is not None:
+        dgamma_out.copy_(dg); dbeta_out.copy_(db)
+    return dx, dres, dg, db
+
+
 def im2col3x3(x, stride):
     """x [C,B,H,W,ch] bf16 (ch % 8 == 0) -> cols [C, B*Ho*Wo, 9*ch]"""
     Cn, B, H, W, ch = x.shape

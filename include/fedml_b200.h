@@ -478,6 +478,20 @@ int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, 
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
 
+/* GroupNorm (+residual, +ReLU) forward / backward for client-stacked conv nets, on the BatchNorm kernels: a row is one
+ * (client, sample), rows = C*B, M = H*W pixels, statistics pool `cpg` adjacent channels of a row (reference
+ * model/cv/group_normalization.py:7-93 and resnet_gn.py:108-196, two channels per group for ResNet-18-GN); gamma / beta
+ * belong to client row / rows_per_client.  x, res, y, dy, dx, dres: bf16 (act_fp32 = 0) or fp32 [rows][M][ch];
+ * save_mean / save_rstd fp32 [rows][ch]; scratch as fb_bn_scratch_floats(rows, M, ch); backward writes per-row
+ * dgamma_rows / dbeta_rows [rows][ch] which the caller sums over the samples of a client. */
+int fb_gn_fwd_stacked(const void* x, const void* res, void* y, int32_t act_fp32, int32_t rows, int64_t M, int32_t ch,
+                      const float* gamma, const float* beta, int64_t ld_p, int32_t rows_per_client, int32_t cpg, float eps,
+                      int32_t relu, float* save_mean, float* save_rstd, float* scratch, fb_stream_t stream);
+int fb_gn_bwd_stacked(const void* dy, const void* dy2, const void* x, const void* y, void* dx, void* dres, int32_t act_fp32,
+                      int32_t rows, int64_t M, int32_t ch, const float* gamma, const float* beta, int64_t ld_p,
+                      int32_t rows_per_client, int32_t cpg, const float* save_mean, const float* save_rstd, int32_t relu,
+                      float* dgamma_rows, float* dbeta_rows, float* scratch, fb_stream_t stream);
+
 /* Train-time augmentation of uint8 NHWC image batches: RandomCrop(H, padding = pad, black border) + horizontal flip +
  * Cutout(cutout x cutout, filled with fill_rgba = the per-channel dataset mean, byte c in bits [8c, 8c+8)).  Every
  * random choice of sample i comes from Philox4x32-10(counter = (first_index + i, tag, nonce), key = seed); when

@@ -192,3 +192,35 @@ def test_ragged_batches_with_batchnorm_train_sequentially():
     got = sim.global_state_dict()
     for k, v in acc.items():
         torch.testing.assert_close(got[k].double(), v / tot, rtol=1e-4, atol=1e-5, msg=k)
+
+
+def test_batched_groupnorm_resnet_matches_autograd():
+    """ResNet with GroupNorm (two channels per group, the reference's resnet18_gn normalisation: model/cv/resnet_gn.py,
+    group_normalization.py) trains client-batched: explicit forward / backward == per-client autograd."""
+    C, B = 3, 5
+    mk = lambda: ResNet(BasicBlock, [1, 1, 1], num_classes=10, stem="cifar", group_norm=2)   # noqa: E731
+    models, layout, stack = _stack_clients(mk, C)
+    assert not any("running" in k for k in models[0].state_dict())
+    gstack = torch.zeros_like(stack)
+    W, G = layout.stacked_views(stack), layout.stacked_views(gstack)
+    bm = make_batched(models[0], TorchBackend(torch.float32))
+    assert bm is not None and not bm.uses_batch_statistics
+    torch.manual_seed(1)
+    x_u8 = torch.randint(0, 256, (C, B, 32, 32, 3), dtype=torch.uint8)
+    y = torch.randint(0, 10, (C, B))
+    loss = bm.train_step(x_u8, y, W, G, torch.ones(C))
+    mean = torch.tensor((0.4914, 0.4822, 0.4465)).view(1, 3, 1, 1)
+    std = torch.tensor((0.2470, 0.2435, 0.2616)).view(1, 3, 1, 1)
+    for c, m in enumerate(models):
+        m.train()
+        xin = (x_u8[c].permute(0, 3, 1, 2).float() / 255.0 - mean) / std
+        l = F.cross_entropy(m(xin), y[c])
+        l.backward()
+        assert abs(float(l) - float(loss[c])) < 1e-4
+        for name, p in m.named_parameters():
+            torch.testing.assert_close(G[name][c], p.grad, rtol=2e-3, atol=2e-5, msg=lambda s, n=name: f"{n}: {s}")
+    lg = bm.logits(x_u8, W)
+    for c, m in enumerate(models):
+        m.eval()
+        xin = (x_u8[c].permute(0, 3, 1, 2).float() / 255.0 - mean) / std
+        torch.testing.assert_close(lg[c], m(xin), rtol=1e-3, atol=1e-4)

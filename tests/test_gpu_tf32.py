@@ -406,3 +406,64 @@ def test_augment_kernel_matches_oracle_and_runs_inside_the_training_graph():
     torch.cuda.synchronize()
     assert sim.graph is not None and sim._static.get("aug_nonce") is not None and int(sim._static["aug_nonce"]) > 0
     assert torch.isfinite(sim.global_flat).all() and not torch.equal(before, sim.global_flat)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("ch,HW,cpg,relu,with_res", [(64, 1024, 2, True, False), (128, 64, 2, True, True), (512, 16, 2, False, False),
+                                                      (32, 256, 8, True, True)])
+def test_groupnorm_stacked_kernels(dtype, ch, HW, cpg, relu, with_res):
+    """GroupNorm(+residual, +ReLU) forward / backward on the BatchNorm kernels (rows = client x sample, group pooling in
+    the apply prologue) vs the plain PyTorch formulation."""
+    from fedml_b200 import ops
+    from fedml_b200.models.batched import TorchBackend
+    C, B = 3, 6
+    torch.manual_seed(ch + HW)
+    x = (torch.randn(C, B, 1, HW, ch, device=DEV) * 2 + 0.5).to(dtype)
+    res = torch.randn(C, B, 1, HW, ch, device=DEV).to(dtype) if with_res else None
+    arena = torch.randn(C, 4096, device=DEV)
+    gamma, beta = arena[:, :ch], arena[:, ch:2 * ch]
+    be = TorchBackend(torch.float32)
+    y_ref, mean_ref, rstd_ref = be.gn_fwd(x.float(), None if res is None else res.float(), gamma, beta, cpg, 1e-5, relu)
+    y, mean, rstd = ops.gn_fwd_stacked(x, res, gamma, beta, cpg, 1e-5, relu)
+    tol = dict(rtol=1e-3, atol=1e-3) if dtype == torch.float32 else dict(rtol=2e-2, atol=3e-2)
+    torch.testing.assert_close(mean, mean_ref, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(rstd, rstd_ref, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(y.float(), y_ref, **tol)
+    dy = torch.randn_like(x)
+    dx_ref, dres_ref, dg_ref, db_ref = be.gn_bwd(dy.float(), x.float(), y_ref, gamma, mean_ref, rstd_ref, cpg, relu, with_res)
+    y_mask = y_ref.to(dtype)                                    # same ReLU mask in both arms
+    dx, dres, dg, db = ops.gn_bwd_stacked(dy, x, y_mask, gamma, mean, rstd, cpg, relu, with_res)
+    scale = float(dx_ref.abs().max())
+    gt = dict(rtol=2e-3, atol=2e-2) if dtype == torch.float32 else dict(rtol=3e-2, atol=0.5)
+    torch.testing.assert_close(db, db_ref, **gt)
+    torch.testing.assert_close(dg, dg_ref, **gt)
+    torch.testing.assert_close(dx.float(), dx_ref, rtol=3e-2, atol=(3e-3 if dtype == torch.float32 else 4e-2) * scale)
+    if with_res:
+        torch.testing.assert_close(dres.float(), dres_ref, rtol=1e-2, atol=1e-2)
+
+
+def test_native_groupnorm_resnet18_step_matches_fp32_oracle():
+    """resnet18_gn-style network (BasicBlock, GroupNorm with two channels per group) on the native tf32 path: whole
+    client-batched training step vs the plain PyTorch back-end, no library fallback."""
+    from fedml_b200.models.batched import NativeBackend, TorchBackend, make_batched
+    from fedml_b200.models.cv import BasicBlock, ResNet
+    from fedml_b200.parallel.arena import ArenaLayout
+    torch.manual_seed(0)
+    C, B = 4, 8
+    model = ResNet(BasicBlock, [1, 1, 1], num_classes=10, stem="cifar", group_norm=2)
+    layout = ArenaLayout(model)
+    stack = torch.stack([layout.flatten(model.state_dict()) for _ in range(C)]).to(DEV)
+    stack += 0.01 * torch.randn_like(stack)
+    x = torch.randint(0, 256, (C, B, 32, 32, 3), dtype=torch.uint8, device=DEV)
+    y = torch.randint(0, 10, (C, B), device=DEV)
+    outs = {}
+    for name, be in (("torch", TorchBackend(torch.float32)), ("native", NativeBackend(torch.float32))):
+        st, gst = stack.clone(), torch.zeros_like(stack)
+        bm = make_batched(model, be)
+        loss = bm.train_step(x, y, layout.stacked_views(st), layout.stacked_views(gst), torch.ones(C, device=DEV))
+        outs[name] = (loss.clone(), gst.clone(), dict(getattr(be, "fallbacks", {})))
+    assert not outs["native"][2], outs["native"][2]
+    torch.testing.assert_close(outs["native"][0], outs["torch"][0], rtol=2e-3, atol=2e-3)
+    gn, gt = outs["native"][1][:, :layout.P_train], outs["torch"][1][:, :layout.P_train]
+    cos = torch.nn.functional.cosine_similarity(gn, gt, dim=1)
+    assert float(cos.min()) > 0.999, cos
