@@ -73,9 +73,10 @@ __global__ void __launch_bounds__(SEL_THREADS) robust_select_kernel(const float*
     } else {
       const uint32_t klo = select_rank(keys, K, col, sub, trim);
       const uint32_t khi = select_rank(keys, K, col, sub, K - trim - 1);
-      if (klo == khi) {
-        result = key2f(klo);
-      } else {
+      // every lane runs the sums and the shuffles: coordinates whose K values are all equal (klo == khi, e.g. integer
+      // buffers that every client holds identically) share warps with coordinates that differ, and a full-mask shuffle
+      // inside a branch only some lanes take never completes
+      {
         float sum = 0.f;
         int lt_lo = 0, eq_lo = 0, lt_hi = 0;
         for (int k = sub; k < K; k += SEL_SPLIT) {
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(SEL_THREADS) robust_select_kernel(const float*
         const int n_lo = lt_lo + eq_lo - trim;       // copies of v_lo with rank >= trim
         const int n_hi = (K - trim) - lt_hi;         // copies of v_hi with rank <  K - trim
         sum += (float)n_lo * key2f(klo) + (float)n_hi * key2f(khi);
-        result = sum / (float)(K - 2 * trim);
+        result = klo == khi ? key2f(klo) : sum / (float)(K - 2 * trim);
       }
     }
     if (sub == 0 && col < width) {
@@ -325,9 +326,10 @@ __global__ void __launch_bounds__(SEL_THREADS) robust_select_runs_kernel(const f
     } else {
       const uint32_t klo = select_rank_runs(keys, K, L, col, sub, trim);
       const uint32_t khi = select_rank_runs(keys, K, L, col, sub, K_valid - trim - 1);
-      if (klo == khi) {
-        result = key2f(klo);
-      } else {
+      // every lane runs the sums and the shuffles: coordinates whose K values are all equal (klo == khi, e.g. integer
+      // buffers that every client holds identically) share warps with coordinates that differ, and a full-mask shuffle
+      // inside a branch only some lanes take never completes
+      {
         float sum = 0.f;
         int lt_lo = 0, eq_lo = 0, lt_hi = 0;
         for (int k = sub; k < K; k += SEL_SPLIT) {
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(SEL_THREADS) robust_select_runs_kernel(const f
         const int n_lo = lt_lo + eq_lo - trim;
         const int n_hi = (K_valid - trim) - lt_hi;
         sum += (float)n_lo * key2f(klo) + (float)n_hi * key2f(khi);
-        result = sum / (float)(K_valid - 2 * trim);
+        result = klo == khi ? key2f(klo) : sum / (float)(K_valid - 2 * trim);
       }
     }
     if (sub == 0 && col < width) {

@@ -189,6 +189,7 @@ def test_median_and_trimmed_mean(K):
     torch.manual_seed(K)
     x = torch.randn(K, P, device=DEV)
     x[:, :50] = torch.randint(0, 3, (K, 50), device=DEV).float()   # heavy ties
+    x[:, 50:80:3] = 5.0     # all clients equal on some coordinates, neighbours differ (lanes of one warp take both cases)
     med = ops.coordinate_median(x)
     assert torch.equal(med, torch.median(x, dim=0).values)
     for trim in {0, K // 10, (K - 1) // 2}:

@@ -130,6 +130,7 @@ def test_many_client_median_and_trimmed_mean_sorted_runs(K, P):
     torch.manual_seed(K)
     x = torch.randn(K, P, device=DEV)
     x[:, :64] = torch.randint(-2, 3, (K, 64), device=DEV).float()        # heavy ties
+    x[:, 64:96:3] = 5.0            # coordinates where every client holds the same value, interleaved with ones that differ
     med = ops.coordinate_median(x)
     assert torch.equal(med, torch.median(x, dim=0).values)
     trim = K // 10
