@@ -1,0 +1,377 @@
+// Slab-resident BatchNorm (included by conv.cu after the fused kernels).
+//
+// The fused kernels read every activation twice (statistics, then apply) and count on L2 for the second read; with 100
+// clients in flight the fp32 stage-1 tensors of the bottleneck ResNet (262 MB each) do not fit and the second read comes
+// from HBM (ncu: 524 MB read for a 262 MB input).  Here a CTA keeps its slice of the client's slab in shared memory:
+//   forward : x -> smem (1-D bulk TMA), statistics from smem, per-client barrier, y computed in place, bulk store
+//   backward: dy, x -> smem, d' = mask(dy + dy2) written back in place while the sums are taken, barrier,
+//             dx computed in place over x, dx (and d' as the residual gradient) bulk-stored
+// so every tensor crosses HBM once.  Slices are cut so that two CTAs fit on an SM (one loads while the other computes).
+// Elements move as 16-byte vectors (8 bf16 / 4 fp32): conflict-free in shared memory.
+#pragma once
+
+#define BNR_CHUNK 16384u       // bytes per bulk copy
+
+__device__ __forceinline__ uint32_t bnr_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bnr_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bnr_smem_u32(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bnr_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bnr_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bnr_mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = bnr_smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void bnr_bulk_load(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   bnr_smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(bnr_smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bnr_bulk_store(void* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(bnr_smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+// the first warp moves `bytes` (a multiple of 16) in BNR_CHUNK pieces, one piece per lane and round
+__device__ __forceinline__ void bnr_load_slice(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  const uint32_t lane = threadIdx.x;
+  for (uint32_t off = lane * BNR_CHUNK; off < bytes; off += 32u * BNR_CHUNK)
+    bnr_bulk_load((char*)dst_smem + off, (const char*)src + off, min(BNR_CHUNK, bytes - off), bar);
+}
+__device__ __forceinline__ void bnr_store_slice(void* dst, const void* src_smem, uint32_t bytes) {
+  const uint32_t lane = threadIdx.x;
+  for (uint32_t off = lane * BNR_CHUNK; off < bytes; off += 32u * BNR_CHUNK)
+    bnr_bulk_store((char*)dst + off, (const char*)src_smem + off, min(BNR_CHUNK, bytes - off));
+}
+
+template <typename T> struct Vec16 { static constexpr int N = 16 / (int)sizeof(T); };
+__device__ __forceinline__ void unpack16(const uint4& r, float* f, const __nv_bfloat16*) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ void unpack16(const uint4& r, float* f, const float*) {
+  f[0] = __uint_as_float(r.x); f[1] = __uint_as_float(r.y); f[2] = __uint_as_float(r.z); f[3] = __uint_as_float(r.w);
+}
+__device__ __forceinline__ uint4 pack16(const float* f, const __nv_bfloat16*) {
+  uint4 r;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return r;
+}
+__device__ __forceinline__ uint4 pack16(const float* f, const float*) {
+  return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
+
+// per-channel sums over the threads that share a channel group: a[N], b[N] per thread -> out[2][ch].  red: BN_THREADS*2*N floats
+template <int N>
+__device__ __forceinline__ void bnr_reduce(const float* a, const float* b, int ch, float* red, float* out) {
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    red[tid * 2 * N + i] = a[i];
+    red[tid * 2 * N + N + i] = b[i];
+  }
+  __syncthreads();
+  const int ng = ch / N;
+  for (int t = tid; t < 2 * ch; t += BN_THREADS) {
+    const int q = t / ch, c = t % ch;
+    const int grp = c / N, comp = c % N;
+    float s = 0.f;
+    for (int tt = grp; tt < BN_THREADS; tt += ng) s += red[tt * 2 * N + q * N + comp];
+    out[q * ch + c] = s;
+  }
+  __syncthreads();
+}
+
+// dynamic shared memory: [slices ...][coefficients 4*ch floats][reduction BN_THREADS*2*N floats]
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t M, int ch, int S,
+                       uint32_t slice_cap, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+                       int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
+                       float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
+                       float* num_batches_tracked, int64_t ld_n) {
+  constexpr int N = Vec16<T>::N;
+  extern __shared__ __align__(128) unsigned char dsm[];
+  __shared__ __align__(8) uint64_t bar;
+  uint4* xs = reinterpret_cast<uint4*>(dsm);
+  float* coef = reinterpret_cast<float*>(dsm + slice_cap);
+  float* red = coef + 4 * ch;
+  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int64_t rows_per = (M + S - 1) / S;
+  const int64_t r0 = min(M, (int64_t)s * rows_per), r1 = min(M, r0 + rows_per);
+  const uint32_t bytes = (uint32_t)((r1 - r0) * ch * (int64_t)sizeof(T));
+  const size_t goff = ((size_t)c * M + r0) * ch;
+  if (tid == 0) bnr_mbar_init(&bar, 1);
+  __syncthreads();
+  pdl_wait();
+  pdl_trigger();
+  if (tid < 32) {
+    if (tid == 0) bnr_mbar_expect_tx(&bar, bytes);
+    __syncwarp();
+    bnr_load_slice(xs, x + goff, bytes, &bar);
+  }
+  const int nvec = (int)(bytes / 16u);
+  const int coff = (tid * N) % ch;
+  bnr_mbar_wait(&bar, 0);
+  float a[N], b[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) a[i] = b[i] = 0.f;
+  for (int v = tid; v < nvec; v += BN_THREADS) {
+    float f[N];
+    unpack16(xs[v], f, (const T*)nullptr);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      a[i] += f[i];
+      b[i] += f[i] * f[i];
+    }
+  }
+  bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
+  client_barrier(S);
+  bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
+                 save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S);
+  __syncthreads();
+  float sc[N], sh[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    sc[i] = coef[coff + i];
+    sh[i] = coef[ch + coff + i];
+  }
+  if (res) {
+    const uint4* rg = reinterpret_cast<const uint4*>(res + goff);
+    for (int v = tid; v < nvec; v += 4 * BN_THREADS) {        // four residual vectors in flight per thread
+      uint4 r[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) r[u] = (v + u * BN_THREADS < nvec) ? __ldg(rg + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int vv = v + u * BN_THREADS;
+        if (vv >= nvec) break;
+        float f[N], q[N];
+        unpack16(xs[vv], f, (const T*)nullptr);
+        unpack16(r[u], q, (const T*)nullptr);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          f[i] = f[i] * sc[i] + sh[i] + q[i];
+          if (relu) f[i] = fmaxf(f[i], 0.f);
+        }
+        xs[vv] = pack16(f, (const T*)nullptr);
+      }
+    }
+  } else {
+    for (int v = tid; v < nvec; v += BN_THREADS) {
+      float f[N];
+      unpack16(xs[v], f, (const T*)nullptr);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        f[i] = f[i] * sc[i] + sh[i];
+        if (relu) f[i] = fmaxf(f[i], 0.f);
+      }
+      xs[v] = pack16(f, (const T*)nullptr);
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes visible to the bulk store
+  __syncthreads();
+  if (tid < 32) {
+    bnr_store_slice(y + goff, xs, bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // stores complete before the CTA (and its smem) goes away
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T* __restrict__ x, const T* __restrict__ y,
+                       T* __restrict__ dx, T* __restrict__ dres, int64_t M, int ch, int S, uint32_t slice_cap, float* partial,
+                       const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
+                       const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
+                       float* __restrict__ dbeta, int64_t ld_g) {
+  constexpr int N = Vec16<T>::N;
+  extern __shared__ __align__(128) unsigned char dsm[];
+  __shared__ __align__(8) uint64_t bar;
+  uint4* ds = reinterpret_cast<uint4*>(dsm);                  // dy, then d' = mask(dy + dy2)
+  uint4* xs = reinterpret_cast<uint4*>(dsm + slice_cap);      // x, then dx
+  float* coef = reinterpret_cast<float*>(dsm + 2 * (size_t)slice_cap);
+  float* red = coef + 4 * ch;
+  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int64_t rows_per = (M + S - 1) / S;
+  const int64_t r0 = min(M, (int64_t)s * rows_per), r1 = min(M, r0 + rows_per);
+  const uint32_t bytes = (uint32_t)((r1 - r0) * ch * (int64_t)sizeof(T));
+  const size_t goff = ((size_t)c * M + r0) * ch;
+  if (tid == 0) bnr_mbar_init(&bar, 1);
+  __syncthreads();
+  pdl_wait();
+  pdl_trigger();
+  if (tid < 32) {
+    if (tid == 0) bnr_mbar_expect_tx(&bar, 2 * bytes);
+    __syncwarp();
+    bnr_load_slice(ds, dy + goff, bytes, &bar);
+    bnr_load_slice(xs, x + goff, bytes, &bar);
+  }
+  const int nvec = (int)(bytes / 16u);
+  const int coff = (tid * N) % ch;
+  // ReLU mask recomputed from x when the forward output was not kept: relu input = x*g + k
+  float g[N], k[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    const float mu = mean[(size_t)c * ch + coff + i], rs = rstd[(size_t)c * ch + coff + i];
+    g[i] = gamma[(size_t)c * ld_p + coff + i] * rs;
+    k[i] = (beta ? beta[(size_t)c * ld_p + coff + i] : 0.f) - mu * g[i];
+  }
+  const uint4* d2g = dy2 ? reinterpret_cast<const uint4*>(dy2 + goff) : nullptr;
+  const uint4* yg = (relu && y) ? reinterpret_cast<const uint4*>(y + goff) : nullptr;
+  float a[N], b[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) a[i] = b[i] = 0.f;
+  bnr_mbar_wait(&bar, 0);
+  for (int v = tid; v < nvec; v += 4 * BN_THREADS) {
+    uint4 e[4], m[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool in = v + u * BN_THREADS < nvec;
+      e[u] = (d2g && in) ? __ldg(d2g + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
+      m[u] = (yg && in) ? __ldg(yg + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int vv = v + u * BN_THREADS;
+      if (vv >= nvec) break;
+      float d[N], xv[N];
+      unpack16(ds[vv], d, (const T*)nullptr);
+      unpack16(xs[vv], xv, (const T*)nullptr);
+      if (d2g) {
+        float q[N];
+        unpack16(e[u], q, (const T*)nullptr);
+#pragma unroll
+        for (int i = 0; i < N; ++i) d[i] += q[i];
+      }
+      if (relu) {
+        if (yg) {
+          float q[N];
+          unpack16(m[u], q, (const T*)nullptr);
+#pragma unroll
+          for (int i = 0; i < N; ++i) d[i] = q[i] > 0.f ? d[i] : 0.f;
+        } else {
+#pragma unroll
+          for (int i = 0; i < N; ++i) d[i] = (xv[i] * g[i] + k[i]) > 0.f ? d[i] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        a[i] += d[i];
+        b[i] += d[i] * xv[i];
+      }
+      if (d2g || relu) ds[vv] = pack16(d, (const T*)nullptr);
+    }
+  }
+  bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
+  client_barrier(S);
+  bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef);
+  __syncthreads();
+  float A[N], B[N], Cc[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    A[i] = coef[coff + i];
+    B[i] = coef[ch + coff + i];
+    Cc[i] = coef[2 * ch + coff + i];
+  }
+  for (int v = tid; v < nvec; v += BN_THREADS) {
+    float d[N], xv[N], o[N];
+    unpack16(ds[v], d, (const T*)nullptr);
+    unpack16(xs[v], xv, (const T*)nullptr);
+#pragma unroll
+    for (int i = 0; i < N; ++i) o[i] = d[i] * A[i] + xv[i] * B[i] + Cc[i];     // = g*(d - dbeta/M - xhat*dgamma/M)
+    xs[v] = pack16(o, (const T*)nullptr);
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  if (tid < 32) {
+    bnr_store_slice(dx + goff, xs, bytes);
+    if (dres) bnr_store_slice(dres + goff, ds, bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+}
+
+// ---- host side: slice count and shared-memory budget
+// FB_BN_RESIDENT: 0 = never, 1 = whenever the slab fits, unset = where it measured faster on the 100-client ResNet-56 round
+// (profiles/r2/bn_resident.md: tf32 114.0 -> 106.9 ms with both passes resident; bf16 69.2 -> 66.0 ms with the backward
+// pass only, 66.8 with both): everything in fp32, the backward pass in bf16
+static int bn_resident_mode() {
+  static int v = -2;
+  if (v == -2) {
+    const char* e = getenv("FB_BN_RESIDENT");
+    v = e ? (atoi(e) != 0) : -1;
+  }
+  return v;
+}
+static int bn_resident_budget_kb(int bwd) {     // bytes of slices per CTA; the default leaves room for two CTAs per SM
+  static int kb[2] = {0, 0};
+  if (!kb[bwd]) {
+    const char* e = getenv(bwd ? "FB_BN_RES_KB_BWD" : "FB_BN_RES_KB_FWD");
+    kb[bwd] = e ? atoi(e) : 96;
+    if (kb[bwd] < 8) kb[bwd] = 8;
+    if (kb[bwd] > 200) kb[bwd] = 200;
+  }
+  return kb[bwd];
+}
+// Picks S (slices per client, <= 64: the partial-sum scratch holds 64) and the per-array slice capacity for `arrays`
+// resident arrays; returns false when a client's slab does not fit (the fused / two-pass kernels take over).
+template <typename T>
+static bool bn_resident_plan(int64_t M, int ch, int arrays, int bwd, bool has_res, int* S_out, uint32_t* cap_out,
+                             size_t* smem_out) {
+  constexpr int N = Vec16<T>::N;
+  const int mode = bn_resident_mode();
+  if (!mode || (BN_THREADS * N) % ch != 0) return false;
+  (void)has_res;
+  if (mode < 0 && !bwd && sizeof(T) == 2) return false;
+  const int64_t row_bytes = (int64_t)ch * (int64_t)sizeof(T);
+  const int64_t extra = (int64_t)(4 * ch + BN_THREADS * 2 * N) * 4;
+  for (int pass = 0; pass < 2; ++pass) {
+    const int64_t budget = (pass == 0 ? (int64_t)bn_resident_budget_kb(bwd) : 200) * 1024 - (pass == 0 ? 0 : extra);
+    const int64_t rows_fit = budget / (arrays * row_bytes);
+    if (rows_fit < 1) continue;
+    int64_t S = (M + rows_fit - 1) / rows_fit;
+    if (S > 64) continue;
+    const int64_t rows_per = (M + S - 1) / S;
+    const int64_t cap = (rows_per * row_bytes + 127) / 128 * 128;
+    *S_out = (int)S;
+    *cap_out = (uint32_t)cap;
+    *smem_out = (size_t)(arrays * cap + extra);
+    return *smem_out <= (size_t)220 * 1024;
+  }
+  return false;
+}
+template <typename K>
+static int bn_resident_allow_smem(K kernel, size_t bytes) {
+  // once per kernel instantiation and device: raise the dynamic shared-memory limit to the hardware maximum
+  static bool done[64] = {};
+  int dev = 0;
+  FB_CHECK_CUDA(cudaGetDevice(&dev));
+  (void)bytes;
+  if (dev < 64 && !done[dev]) {
+    FB_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    done[dev] = true;
+  }
+  return FB_OK;
+}

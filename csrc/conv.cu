@@ -121,6 +121,51 @@ bn_stats_body(const T* __restrict__ x, int64_t M, int ch, int S, float* __restri
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
 }
 
+// BatchNorm: finish the statistics of client blockIdx.y from its SP partial sums (every CTA redundantly, SP is small),
+// update the running statistics (slice 0 only) and leave scale / shift per channel in shared memory
+__device__ __forceinline__ void
+bn_scale_shift(int64_t M, int ch, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+               int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
+               float momentum, float eps, int training, float* __restrict__ save_mean, float* __restrict__ save_rstd,
+               float* num_batches_tracked, int64_t ld_n, float* scale, float* shift, int SP) {
+  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
+    num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
+  for (int k = tid; k < ch; k += BN_THREADS) {
+    float mean, var;
+    if (training) {
+      float su = 0.f, sq = 0.f;
+      for (int j = 0; j < SP; ++j) {
+        su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);       // L2: written by sibling CTAs in the fused kernel
+        sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
+      }
+      mean = su / (float)M;
+      var = fmaxf(sq / (float)M - mean * mean, 0.f);
+      if (s == 0) {
+        const float a = active ? active[c] : 1.f;
+        if (a != 0.f) {
+          const float unbiased = var * ((float)M / (float)max((int64_t)1, M - 1));
+          float* rm = running_mean + (size_t)c * ld_r + k;
+          float* rv = running_var + (size_t)c * ld_r + k;
+          *rm += momentum * a * (mean - *rm);
+          *rv += momentum * a * (unbiased - *rv);
+        }
+      }
+    } else {
+      mean = running_mean[(size_t)c * ld_r + k];
+      var = running_var[(size_t)c * ld_r + k];
+    }
+    const float rstd = rsqrtf(var + eps);
+    if (s == 0 && save_mean) {
+      save_mean[(size_t)c * ch + k] = mean;
+      save_rstd[(size_t)c * ch + k] = rstd;
+    }
+    const float g = gamma[(size_t)c * ld_p + k] * rstd;
+    scale[k] = g;
+    shift[k] = beta[(size_t)c * ld_p + k] - mean * g;
+  }
+}
+
 // stage 2: finish the statistics (every CTA redundantly, S is small), update running stats, apply
 template <typename T>
 __device__ __forceinline__ void
@@ -168,41 +213,8 @@ bn_apply_body(const T* __restrict__ x, const T* __restrict__ res, T* __restrict_
       shift[k] = beta[(size_t)cp * ld_p + k] - mean * g;
     }
   } else {
-  if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
-    num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
-  for (int k = tid; k < ch; k += BN_THREADS) {
-    float mean, var;
-    if (training) {
-      float su = 0.f, sq = 0.f;
-      for (int j = 0; j < SP; ++j) {
-        su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);       // L2: written by sibling CTAs in the fused kernel
-        sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
-      }
-      mean = su / (float)M;
-      var = fmaxf(sq / (float)M - mean * mean, 0.f);
-      if (s == 0) {
-        const float a = active ? active[c] : 1.f;
-        if (a != 0.f) {
-          const float unbiased = var * ((float)M / (float)max((int64_t)1, M - 1));
-          float* rm = running_mean + (size_t)c * ld_r + k;
-          float* rv = running_var + (size_t)c * ld_r + k;
-          *rm += momentum * a * (mean - *rm);
-          *rv += momentum * a * (unbiased - *rv);
-        }
-      }
-    } else {
-      mean = running_mean[(size_t)c * ld_r + k];
-      var = running_var[(size_t)c * ld_r + k];
-    }
-    const float rstd = rsqrtf(var + eps);
-    if (s == 0 && save_mean) {
-      save_mean[(size_t)c * ch + k] = mean;
-      save_rstd[(size_t)c * ch + k] = rstd;
-    }
-    const float g = gamma[(size_t)c * ld_p + k] * rstd;
-    scale[k] = g;
-    shift[k] = beta[(size_t)c * ld_p + k] - mean * g;
-  }
+    bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, training,
+                   save_mean, save_rstd, num_batches_tracked, ld_n, scale, shift, SP);
   }
   __syncthreads();
   const int64_t rows_per = (M + S - 1) / S;
@@ -346,6 +358,12 @@ static bool bn_fused_enabled(int64_t act_bytes) {
   return v >= 0 ? v == 1 : act_bytes >= (int64_t)48 << 20;
 }
 
+__device__ __forceinline__ void
+bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+              int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
+              float* __restrict__ dbeta, int64_t ld_g, float* sm);
+#include "bn_resident.cuh"
+
 extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * 64 * 2 * ch; }
 
 template <typename T>
@@ -364,6 +382,17 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
   // epilogue of the convolution that wrote x (FbGroupedGemm.stats): one pass over x instead of two
   const bool have_stats = training == 2;
   if (training == 1 && bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    int Sr = 0;
+    uint32_t cap = 0;
+    size_t smem = 0;
+    if (bn_resident_plan<T>(M, ch, 1, 0, res != nullptr, &Sr, &cap, &smem)) {       // the slab stays in shared memory: x crosses HBM once
+      if (int rc = bn_resident_allow_smem(bn_fwd_resident_kernel<T>, smem)) return rc;
+      FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
+          (const T*)x, (const T*)res, (T*)y, M, ch, Sr, cap, scratch, gamma, beta, ld_p, running_mean,
+          running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
+      FB_CHECK_CUDA(cudaGetLastError());
+      return FB_OK;
+    }
     FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
         running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
@@ -452,6 +481,38 @@ bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
   reduce_channel_pairs(a, b, ch, smem, partial + ((size_t)c * S + s) * 2 * ch);
 }
 
+// BatchNorm backward: finish (sum dy', sum dy'*x) of client blockIdx.y from the S partial sums, write dgamma / dbeta (slice 0)
+// and leave, per channel, A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g in shared memory
+__device__ __forceinline__ void
+bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
+              int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
+              float* __restrict__ dbeta, int64_t ld_g, float* sm) {
+  float* s_A = sm;
+  float* s_B = sm + ch;
+  float* s_C = sm + 2 * ch;
+  float* s_K = sm + 3 * ch;
+  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  for (int k = tid; k < ch; k += BN_THREADS) {
+    float sd = 0.f, sdx = 0.f;
+    for (int j = 0; j < S; ++j) {
+      sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
+      sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
+    }
+    const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
+    const float dbt = sd, dgm = rs * (sdx - mu * sd);
+    if (s == 0) {
+      dbeta[(size_t)c * ld_g + k] = dbt;
+      dgamma[(size_t)c * ld_g + k] = dgm;
+    }
+    const float g = gamma[(size_t)c * ld_p + k] * rs;
+    const float B = -g * rs * dgm / (float)M;
+    s_A[k] = g;
+    s_B[k] = B;
+    s_C[k] = -g * dbt / (float)M - mu * B;
+    s_K[k] = (beta ? beta[(size_t)c * ld_p + k] : 0.f) - mu * g;
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ void
 bn_bwd_apply_body(const T* __restrict__ dy, const T* __restrict__ dy2,
@@ -503,25 +564,8 @@ bn_bwd_apply_body(const T* __restrict__ dy, const T* __restrict__ dy2,
       s_C[k] = -rs * Ag / n - mu * B;
       s_K[k] = (beta ? beta[(size_t)cp * ld_p + k] : 0.f) - mu * g;
     }
-  } else
-  for (int k = tid; k < ch; k += BN_THREADS) {
-    float sd = 0.f, sdx = 0.f;
-    for (int j = 0; j < S; ++j) {
-      sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
-      sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
-    }
-    const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
-    const float dbt = sd, dgm = rs * (sdx - mu * sd);
-    if (s == 0) {
-      dbeta[(size_t)c * ld_g + k] = dbt;
-      dgamma[(size_t)c * ld_g + k] = dgm;
-    }
-    const float g = gamma[(size_t)c * ld_p + k] * rs;
-    const float B = -g * rs * dgm / (float)M;
-    s_A[k] = g;
-    s_B[k] = B;
-    s_C[k] = -g * dbt / (float)M - mu * B;
-    s_K[k] = (beta ? beta[(size_t)c * ld_p + k] : 0.f) - mu * g;
+  } else {
+    bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, sm);
   }
   __syncthreads();
   const int64_t rows_per = (M + S - 1) / S;
@@ -633,6 +677,17 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
   int S = bn_slices(C, M, ch);
   if (bn_forced_slices(1) > 0) S = bn_forced_slices(1);
   if (bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    int Sr = 0;
+    uint32_t cap = 0;
+    size_t smem = 0;
+    if (bn_resident_plan<T>(M, ch, 2, 1, false, &Sr, &cap, &smem)) {       // dy and x stay in shared memory between the two passes
+      if (int rc = bn_resident_allow_smem(bn_bwd_resident_kernel<T>, smem)) return rc;
+      FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
+          (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, ch, Sr, cap, scratch, gamma, beta, ld_p,
+          save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+      FB_CHECK_CUDA(cudaGetLastError());
+      return FB_OK;
+    }
     FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx,
         (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));

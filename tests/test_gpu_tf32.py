@@ -2,6 +2,8 @@
 at (stock ``nn.Conv2d`` under cuDNN's TF32 default, python/fedml/simulation/single_process/fedavg/
 my_model_trainer_classification.py:18-91).  Oracles are plain PyTorch in fp32/fp64 with TF32 disabled; the operand
 truncation of the tensor core (10 mantissa bits kept) bounds the error at ~2^-10 relative per product."""
+import os
+
 import pytest
 import torch
 
@@ -467,3 +469,19 @@ def test_native_groupnorm_resnet18_step_matches_fp32_oracle():
     gn, gt = outs["native"][1][:, :layout.P_train], outs["torch"][1][:, :layout.P_train]
     cos = torch.nn.functional.cosine_similarity(gn, gt, dim=1)
     assert float(cos.min()) > 0.999, cos
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("resident", ["0", "1"])
+def test_bn_single_launch_kernels_small_ragged_shapes(resident):
+    """Fused (per-client barrier) and slab-resident (shared-memory slices, bulk TMA in and out) BatchNorm on shapes whose
+    rows do not divide by the slice count, fp32 and bf16, with / without residual, second gradient, residual gradient and
+    recomputed ReLU mask, against the fp32 PyTorch restatement in tools/bench_bn.py.  The switches are read once per process,
+    hence the subprocess."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, FB_BN_FUSED="1", FB_BN_RESIDENT=resident)
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "bench_bn.py"), "--small"], env=env, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0 and "BN_SMALL_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
