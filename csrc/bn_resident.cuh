@@ -103,20 +103,64 @@ __device__ __forceinline__ void bnr_reduce(const float* a, const float* b, int c
   __syncthreads();
 }
 
-// dynamic shared memory: [slices ...][coefficients 4*ch floats][reduction BN_THREADS*2*N floats]
+// The client's S partial rows [S][2*ch] (L2, written by the sibling CTAs) -> complete sums [2*ch] in shared memory, with
+// every thread loading: a column is shared by BN_THREADS / (2*ch) threads that take every other row, eight loads in flight
+// each (the per-channel loop of the fused kernels walks S rows one after the other: 55 dependent L2 round trips at S = 55).
+// red: BN_THREADS floats.  Deterministic: fixed row order per thread, fixed order across threads.
+__device__ __forceinline__ void bnr_sum_partials(const float* part, int S, int ch, float* red, float* sums) {
+  const int tid = threadIdx.x, cols = 2 * ch;
+  if (cols >= BN_THREADS) {
+    for (int col = tid; col < cols; col += BN_THREADS) {
+      float acc = 0.f;
+      int j = 0;
+      for (; j + 8 <= S; j += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += v[u];
+      }
+      for (; j < S; ++j) acc += __ldcg(part + (size_t)j * cols + col);
+      sums[col] = acc;
+    }
+  } else {
+    const int groups = BN_THREADS / cols, col = tid % cols, grp = tid / cols;
+    float acc = 0.f;
+    int j = grp;
+    for (; j + 7 * groups < S; j += 8 * groups) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc += v[u];
+    }
+    for (; j < S; j += groups) acc += __ldcg(part + (size_t)j * cols + col);
+    red[tid] = acc;
+    __syncthreads();
+    if (tid < cols) {
+      float t = 0.f;
+      for (int g2 = 0; g2 < groups; ++g2) t += red[g2 * cols + tid];
+      sums[tid] = t;
+    }
+  }
+  __syncthreads();
+}
+
+// dynamic shared memory: [slices ...][coefficients 4*ch floats][complete sums 2*ch floats][reduction BN_THREADS*2*N floats]
 template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t M, int ch, int S,
                        uint32_t slice_cap, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                        int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                        float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
-                       float* num_batches_tracked, int64_t ld_n) {
+                       float* num_batches_tracked, int64_t ld_n, int res_smem /* the residual slice is resident too */) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bar;
   uint4* xs = reinterpret_cast<uint4*>(dsm);
-  float* coef = reinterpret_cast<float*>(dsm + slice_cap);
-  float* red = coef + 4 * ch;
+  uint4* rs = reinterpret_cast<uint4*>(dsm + slice_cap);
+  float* coef = reinterpret_cast<float*>(dsm + (size_t)(1 + res_smem) * slice_cap);
+  float* red = coef + 6 * ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = min(M, (int64_t)s * rows_per), r1 = min(M, r0 + rows_per);
@@ -127,9 +171,10 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
   pdl_wait();
   pdl_trigger();
   if (tid < 32) {
-    if (tid == 0) bnr_mbar_expect_tx(&bar, bytes);
+    if (tid == 0) bnr_mbar_expect_tx(&bar, bytes * (uint32_t)(1 + res_smem));
     __syncwarp();
     bnr_load_slice(xs, x + goff, bytes, &bar);
+    if (res_smem) bnr_load_slice(rs, res + goff, bytes, &bar);
   }
   const int nvec = (int)(bytes / 16u);
   const int coff = (tid * N) % ch;
@@ -148,8 +193,9 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
   }
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
   client_barrier(S);
+  bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 2 * ch);
   bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
-                 save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S);
+                 save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S, coef + 2 * ch);
   __syncthreads();
   float sc[N], sh[N];
 #pragma unroll
@@ -157,7 +203,19 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
     sc[i] = coef[coff + i];
     sh[i] = coef[ch + coff + i];
   }
-  if (res) {
+  if (res && res_smem) {
+    for (int v = tid; v < nvec; v += BN_THREADS) {
+      float f[N], q[N];
+      unpack16(xs[v], f, (const T*)nullptr);
+      unpack16(rs[v], q, (const T*)nullptr);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        f[i] = f[i] * sc[i] + sh[i] + q[i];
+        if (relu) f[i] = fmaxf(f[i], 0.f);
+      }
+      xs[v] = pack16(f, (const T*)nullptr);
+    }
+  } else if (res) {
     const uint4* rg = reinterpret_cast<const uint4*>(res + goff);
     for (int v = tid; v < nvec; v += 4 * BN_THREADS) {        // four residual vectors in flight per thread
       uint4 r[4];
@@ -205,14 +263,17 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
                        T* __restrict__ dx, T* __restrict__ dres, int64_t M, int ch, int S, uint32_t slice_cap, float* partial,
                        const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                        const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
-                       float* __restrict__ dbeta, int64_t ld_g) {
+                       float* __restrict__ dbeta, int64_t ld_g, int extras /* bit 0: dy2 resident, bit 1: y resident */) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bar;
+  const int e_d2 = extras & 1, e_y = (extras >> 1) & 1;
   uint4* ds = reinterpret_cast<uint4*>(dsm);                  // dy, then d' = mask(dy + dy2)
   uint4* xs = reinterpret_cast<uint4*>(dsm + slice_cap);      // x, then dx
-  float* coef = reinterpret_cast<float*>(dsm + 2 * (size_t)slice_cap);
-  float* red = coef + 4 * ch;
+  uint4* d2s = reinterpret_cast<uint4*>(dsm + 2 * (size_t)slice_cap);
+  uint4* ys = reinterpret_cast<uint4*>(dsm + (size_t)(2 + e_d2) * slice_cap);
+  float* coef = reinterpret_cast<float*>(dsm + (size_t)(2 + e_d2 + e_y) * slice_cap);
+  float* red = coef + 6 * ch;
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   const int64_t rows_per = (M + S - 1) / S;
   const int64_t r0 = min(M, (int64_t)s * rows_per), r1 = min(M, r0 + rows_per);
@@ -223,10 +284,12 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
   pdl_wait();
   pdl_trigger();
   if (tid < 32) {
-    if (tid == 0) bnr_mbar_expect_tx(&bar, 2 * bytes);
+    if (tid == 0) bnr_mbar_expect_tx(&bar, (uint32_t)(2 + e_d2 + e_y) * bytes);
     __syncwarp();
     bnr_load_slice(ds, dy + goff, bytes, &bar);
     bnr_load_slice(xs, x + goff, bytes, &bar);
+    if (e_d2) bnr_load_slice(d2s, dy2 + goff, bytes, &bar);
+    if (e_y) bnr_load_slice(ys, y + goff, bytes, &bar);
   }
   const int nvec = (int)(bytes / 16u);
   const int coff = (tid * N) % ch;
@@ -249,8 +312,8 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const bool in = v + u * BN_THREADS < nvec;
-      e[u] = (d2g && in) ? __ldg(d2g + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
-      m[u] = (yg && in) ? __ldg(yg + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
+      e[u] = (d2g && in) ? (e_d2 ? d2s[v + u * BN_THREADS] : __ldg(d2g + v + u * BN_THREADS)) : make_uint4(0, 0, 0, 0);
+      m[u] = (yg && in) ? (e_y ? ys[v + u * BN_THREADS] : __ldg(yg + v + u * BN_THREADS)) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -286,7 +349,8 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
   }
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
   client_barrier(S);
-  bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef);
+  bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 4 * ch);
+  bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef, coef + 4 * ch);
   __syncthreads();
   float A[N], B[N], Cc[N];
 #pragma unroll
@@ -325,6 +389,14 @@ static int bn_resident_mode() {
   }
   return v;
 }
+static int bn_resident_extras() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FB_BN_RES_EXTRAS");
+    v = e ? (atoi(e) != 0) : 0;
+  }
+  return v;
+}
 static int bn_resident_budget_kb(int bwd) {     // bytes of slices per CTA; the default leaves room for two CTAs per SM
   static int kb[2] = {0, 0};
   if (!kb[bwd]) {
@@ -346,7 +418,7 @@ static bool bn_resident_plan(int64_t M, int ch, int arrays, int bwd, bool has_re
   (void)has_res;
   if (mode < 0 && !bwd && sizeof(T) == 2) return false;
   const int64_t row_bytes = (int64_t)ch * (int64_t)sizeof(T);
-  const int64_t extra = (int64_t)(4 * ch + BN_THREADS * 2 * N) * 4;
+  const int64_t extra = (int64_t)(6 * ch + BN_THREADS * 2 * N) * 4;
   for (int pass = 0; pass < 2; ++pass) {
     const int64_t budget = (pass == 0 ? (int64_t)bn_resident_budget_kb(bwd) : 200) * 1024 - (pass == 0 ? 0 : extra);
     const int64_t rows_fit = budget / (arrays * row_bytes);

@@ -127,7 +127,8 @@ __device__ __forceinline__ void
 bn_scale_shift(int64_t M, int ch, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                float momentum, float eps, int training, float* __restrict__ save_mean, float* __restrict__ save_rstd,
-               float* num_batches_tracked, int64_t ld_n, float* scale, float* shift, int SP) {
+               float* num_batches_tracked, int64_t ld_n, float* scale, float* shift, int SP,
+               const float* presum = nullptr /* shared memory [2][ch]: the client's complete sums, already added up */) {
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
     num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
@@ -135,9 +136,14 @@ bn_scale_shift(int64_t M, int ch, const float* partial, const float* __restrict_
     float mean, var;
     if (training) {
       float su = 0.f, sq = 0.f;
-      for (int j = 0; j < SP; ++j) {
-        su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);       // L2: written by sibling CTAs in the fused kernel
-        sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
+      if (presum) {
+        su = presum[k];
+        sq = presum[ch + k];
+      } else {
+        for (int j = 0; j < SP; ++j) {
+          su += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + k);       // L2: written by sibling CTAs in the fused kernel
+          sq += __ldcg(partial + ((size_t)c * SP + j) * 2 * ch + ch + k);
+        }
       }
       mean = su / (float)M;
       var = fmaxf(sq / (float)M - mean * mean, 0.f);
@@ -361,7 +367,7 @@ static bool bn_fused_enabled(int64_t act_bytes) {
 __device__ __forceinline__ void
 bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
               int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
-              float* __restrict__ dbeta, int64_t ld_g, float* sm);
+              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum = nullptr);
 #include "bn_resident.cuh"
 
 extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * 64 * 2 * ch; }
@@ -385,11 +391,19 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
-    if (bn_resident_plan<T>(M, ch, 1, 0, res != nullptr, &Sr, &cap, &smem)) {       // the slab stays in shared memory: x crosses HBM once
+    // FB_BN_RES_EXTRAS=1: the residual rides along in shared memory too.  Off by default: twice the slices per client cost more
+    // (per-CTA fixed time) than the bulk load saves - fp32 64ch@32x32 forward 197.8 -> 254.5 us, round 105.7 -> 118.3 ms
+    int res_smem = (res && bn_resident_extras()) ? 1 : 0;
+    bool ok = bn_resident_plan<T>(M, ch, 1 + res_smem, 0, res != nullptr, &Sr, &cap, &smem);
+    if (!ok && res_smem) {
+      res_smem = 0;
+      ok = bn_resident_plan<T>(M, ch, 1, 0, true, &Sr, &cap, &smem);
+    }
+    if (ok) {       // the slab stays in shared memory: x crosses HBM once
       if (int rc = bn_resident_allow_smem(bn_fwd_resident_kernel<T>, smem)) return rc;
       FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
           (const T*)x, (const T*)res, (T*)y, M, ch, Sr, cap, scratch, gamma, beta, ld_p, running_mean,
-          running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
+          running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n, res_smem));
       FB_CHECK_CUDA(cudaGetLastError());
       return FB_OK;
     }
@@ -486,7 +500,7 @@ bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
 __device__ __forceinline__ void
 bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
               int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
-              float* __restrict__ dbeta, int64_t ld_g, float* sm) {
+              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum) {
   float* s_A = sm;
   float* s_B = sm + ch;
   float* s_C = sm + 2 * ch;
@@ -494,9 +508,14 @@ bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __res
   const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
   for (int k = tid; k < ch; k += BN_THREADS) {
     float sd = 0.f, sdx = 0.f;
-    for (int j = 0; j < S; ++j) {
-      sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
-      sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
+    if (presum) {
+      sd = presum[k];
+      sdx = presum[ch + k];
+    } else {
+      for (int j = 0; j < S; ++j) {
+        sd += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + k);
+        sdx += __ldcg(partial + ((size_t)c * S + j) * 2 * ch + ch + k);
+      }
     }
     const float mu = mean[(size_t)c * ch + k], rs = rstd[(size_t)c * ch + k];
     const float dbt = sd, dgm = rs * (sdx - mu * sd);
@@ -680,11 +699,17 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
-    if (bn_resident_plan<T>(M, ch, 2, 1, false, &Sr, &cap, &smem)) {       // dy and x stay in shared memory between the two passes
+    int extras = bn_resident_extras() ? ((dy2 ? 1 : 0) | ((relu && y) ? 2 : 0)) : 0;      // see bn_fwd_impl
+    bool ok = bn_resident_plan<T>(M, ch, 2 + (extras & 1) + (extras >> 1), 1, false, &Sr, &cap, &smem);
+    if (!ok && extras) {
+      extras = 0;
+      ok = bn_resident_plan<T>(M, ch, 2, 1, false, &Sr, &cap, &smem);
+    }
+    if (ok) {       // dy and x stay in shared memory between the two passes
       if (int rc = bn_resident_allow_smem(bn_bwd_resident_kernel<T>, smem)) return rc;
       FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
           (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, ch, Sr, cap, scratch, gamma, beta, ld_p,
-          save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+          save_mean, save_rstd, relu, dgamma, dbeta, ld_g, extras));
       FB_CHECK_CUDA(cudaGetLastError());
       return FB_OK;
     }
