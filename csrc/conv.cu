@@ -11,6 +11,7 @@
 
 #define BN_THREADS 256
 #define BN_VEC 8
+#define BN_MAX_SLICES 128     // slices per client the partial-sum scratch holds (fb_bn_scratch_floats)
 
 // Eight consecutive channels of one pixel: 16 bytes of bf16 or 32 bytes of fp32 (two 16-byte accesses).  Kernels are
 // templated on the activation element type T; all arithmetic is fp32 either way.
@@ -128,8 +129,13 @@ bn_scale_shift(int64_t M, int ch, const float* partial, const float* __restrict_
                int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                float momentum, float eps, int training, float* __restrict__ save_mean, float* __restrict__ save_rstd,
                float* num_batches_tracked, int64_t ld_n, float* scale, float* shift, int SP,
-               const float* presum = nullptr /* shared memory [2][ch]: the client's complete sums, already added up */) {
-  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+               const float* presum = nullptr /* shared memory [2][ch]: the client's complete sums, already added up */,
+               int c = -1, int s = -1 /* client and slice of this CTA's work item (default: blockIdx.y / blockIdx.x) */) {
+  const int tid = threadIdx.x;
+  if (c < 0) {
+    c = blockIdx.y;
+    s = blockIdx.x;
+  }
   if (training && s == 0 && tid == 0 && num_batches_tracked)       // the integer BN counter lives in the arena as fp32
     num_batches_tracked[(size_t)c * ld_n] += active ? active[c] : 1.f;
   for (int k = tid; k < ch; k += BN_THREADS) {
@@ -367,10 +373,11 @@ static bool bn_fused_enabled(int64_t act_bytes) {
 __device__ __forceinline__ void
 bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
               int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
-              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum = nullptr);
+              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum = nullptr, int c = -1, int s = -1);
 #include "bn_resident.cuh"
+#include "bn_persist.cuh"
 
-extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * 64 * 2 * ch; }
+extern "C" int64_t fb_bn_scratch_floats(int32_t C, int64_t M, int32_t ch) { return (int64_t)C * BN_MAX_SLICES * 2 * ch; }
 
 template <typename T>
 static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64_t M, int32_t ch,
@@ -391,6 +398,19 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
+    {
+      int Sp = 0, grid = 0;
+      uint32_t capp = 0;
+      size_t smemp = 0;
+      if (bn_persist_plan<T>(C, M, ch, res ? 2 : 1, &Sp, &capp, &smemp, &grid)) {
+        if (int rc = bn_resident_allow_smem(bn_fwd_persist_kernel<T>, smemp)) return rc;
+        FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_persist_kernel<T>, dim3(grid), dim3(BN_THREADS), smemp, (cudaStream_t)stream,
+            (const T*)x, (const T*)res, (T*)y, M, ch, Sp, (int)C, capp, scratch, gamma, beta, ld_p, running_mean,
+            running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
+        FB_CHECK_CUDA(cudaGetLastError());
+        return FB_OK;
+      }
+    }
     // FB_BN_RES_EXTRAS=1: the residual rides along in shared memory too.  Off by default: twice the slices per client cost more
     // (per-CTA fixed time) than the bulk load saves - fp32 64ch@32x32 forward 197.8 -> 254.5 us, round 105.7 -> 118.3 ms
     int res_smem = (res && bn_resident_extras()) ? 1 : 0;
@@ -500,12 +520,16 @@ bn_bwd_stats_body(const T* __restrict__ dy, const T* __restrict__ dy2,
 __device__ __forceinline__ void
 bn_bwd_coeffs(int64_t M, int ch, int S, const float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
               int64_t ld_p, const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ dgamma,
-              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum) {
+              float* __restrict__ dbeta, int64_t ld_g, float* sm, const float* presum, int c, int s) {
   float* s_A = sm;
   float* s_B = sm + ch;
   float* s_C = sm + 2 * ch;
   float* s_K = sm + 3 * ch;
-  const int c = blockIdx.y, s = blockIdx.x, tid = threadIdx.x;
+  const int tid = threadIdx.x;
+  if (c < 0) {
+    c = blockIdx.y;
+    s = blockIdx.x;
+  }
   for (int k = tid; k < ch; k += BN_THREADS) {
     float sd = 0.f, sdx = 0.f;
     if (presum) {
@@ -699,6 +723,19 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
+    {
+      int Sp = 0, grid = 0;
+      uint32_t capp = 0;
+      size_t smemp = 0;
+      if (bn_persist_plan<T>(C, M, ch, 2 + (dy2 ? 1 : 0) + ((relu && y) ? 1 : 0), &Sp, &capp, &smemp, &grid)) {
+        if (int rc = bn_resident_allow_smem(bn_bwd_persist_kernel<T>, smemp)) return rc;
+        FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_persist_kernel<T>, dim3(grid), dim3(BN_THREADS), smemp, (cudaStream_t)stream,
+            (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, ch, Sp, (int)C, capp, scratch, gamma, beta,
+            ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+        FB_CHECK_CUDA(cudaGetLastError());
+        return FB_OK;
+      }
+    }
     int extras = bn_resident_extras() ? ((dy2 ? 1 : 0) | ((relu && y) ? 2 : 0)) : 0;      // see bn_fwd_impl
     bool ok = bn_resident_plan<T>(M, ch, 2 + (extras & 1) + (extras >> 1), 1, false, &Sr, &cap, &smem);
     if (!ok && extras) {

@@ -385,7 +385,7 @@ def bn_fwd_stacked(x, res, gamma, beta, rm, rv, nbt, active, momentum, eps, relu
     use_stats = training and stats is not None
     if use_stats and not (stats.dtype == torch.float32 and stats.is_contiguous() and stats.numel() == Cn * 2 * ch):
         raise NativeError("bn_fwd_stacked: stats must be contiguous fp32 [C, 2, ch]")
-    scratch = stats if use_stats else _scratch_for(x.device, Cn * 64 * 2 * ch)
+    scratch = stats if use_stats else _scratch_for(x.device, Cn * 128 * 2 * ch)
     fn = lib().fb_bn_fwd_stacked_f32 if x.dtype == torch.float32 else lib().fb_bn_fwd_stacked
     check(fn(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)), i32(Cn),
                                   i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(rm)),
@@ -410,7 +410,7 @@ def bn_bwd_stacked(dy, x, y, gamma, mean, rstd, relu, want_dres, beta=None, dgam
     dgamma = dgamma_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     dbeta = dbeta_out if direct else torch.empty((Cn, ch), dtype=torch.float32, device=x.device)
     ld_g = dgamma.stride(0) if Cn > 1 else max(dgamma.stride(0), ch)
-    scratch = _scratch_for(x.device, Cn * 64 * 2 * ch)
+    scratch = _scratch_for(x.device, Cn * 128 * 2 * ch)
     fn = lib().fb_bn_bwd_stacked_f32 if x.dtype == torch.float32 else lib().fb_bn_bwd_stacked
     check(fn(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)), i32(Cn), i64(M),
                                   i32(ch), vp(ptr(gamma)), vp(ptr(beta)), i64(gamma.stride(0)), vp(ptr(mean)),
@@ -430,7 +430,7 @@ def gn_fwd_stacked(x, res, gamma, beta, cpg, eps, relu):
     y = torch.empty_like(x)
     mean = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
     rstd = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
-    scratch = _scratch_for(x.device, rows * 64 * 2 * ch)
+    scratch = _scratch_for(x.device, rows * 128 * 2 * ch)
     check(lib().fb_gn_fwd_stacked(vp(ptr(x)), vp(ptr(res.contiguous()) if res is not None else 0), vp(ptr(y)),
                                   i32(int(x.dtype == torch.float32)), i32(rows), i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)),
                                   i64(gamma.stride(0)), i32(B), i32(cpg), f32(eps), i32(int(relu)), vp(ptr(mean)), vp(ptr(rstd)),
@@ -451,7 +451,7 @@ def gn_bwd_stacked(dy, x, y, gamma, mean, rstd, cpg, relu, want_dres, beta=None,
     dres = torch.empty_like(x) if want_dres else None
     dg_rows = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
     db_rows = torch.empty((rows, ch), dtype=torch.float32, device=x.device)
-    scratch = _scratch_for(x.device, rows * 64 * 2 * ch)
+    scratch = _scratch_for(x.device, rows * 128 * 2 * ch)
     check(lib().fb_gn_bwd_stacked(vp(ptr(dy)), vp(ptr(dy2)), vp(ptr(x)), vp(ptr(y)), vp(ptr(dx)), vp(ptr(dres)),
                                   i32(int(x.dtype == torch.float32)), i32(rows), i64(M), i32(ch), vp(ptr(gamma)), vp(ptr(beta)),
                                   i64(gamma.stride(0)), i32(B), i32(cpg), vp(ptr(mean)), vp(ptr(rstd)), i32(int(relu)),

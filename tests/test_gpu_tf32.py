@@ -472,7 +472,7 @@ def test_native_groupnorm_resnet18_step_matches_fp32_oracle():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("resident", ["0", "1"])
+@pytest.mark.parametrize("resident", ["0", "1", "persist", "persist64"])
 def test_bn_single_launch_kernels_small_ragged_shapes(resident):
     """Fused (per-client barrier) and slab-resident (shared-memory slices, bulk TMA in and out) BatchNorm on shapes whose
     rows do not divide by the slice count, fp32 and bf16, with / without residual, second gradient, residual gradient and
@@ -481,7 +481,11 @@ def test_bn_single_launch_kernels_small_ragged_shapes(resident):
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, FB_BN_FUSED="1", FB_BN_RESIDENT=resident)
+    env = dict(os.environ, FB_BN_FUSED="1", FB_BN_RESIDENT="1" if resident.startswith("persist") else resident)
+    if resident.startswith("persist"):          # persistent pipelined kernels; 64 KB budget = several items per CTA
+        env["FB_BN_PERSIST"] = "1"
+        if resident == "persist64":
+            env["FB_BN_PERSIST_KB"] = "64"
     r = subprocess.run([sys.executable, os.path.join(root, "tools", "bench_bn.py"), "--small"], env=env, capture_output=True,
                        text=True, timeout=300)
     assert r.returncode == 0 and "BN_SMALL_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

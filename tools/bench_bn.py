@@ -95,7 +95,7 @@ def main():
     build()
     from fedml_b200 import ops
     flush = torch.zeros(64 << 20, device="cuda:0")        # 256 MB > L2
-    env = {k: os.environ.get(k) for k in ("FB_BN_RESIDENT", "FB_BN_FUSED", "FB_BN_RES_KB_FWD", "FB_BN_RES_KB_BWD")}
+    env = {k: os.environ.get(k) for k in ("FB_BN_RESIDENT", "FB_BN_PERSIST", "FB_BN_PERSIST_KB", "FB_BN_FUSED", "FB_BN_RES_KB_FWD", "FB_BN_RES_KB_BWD")}
     print(json.dumps({"env": env}))
     worst = 0.0
     if args.small:
@@ -103,7 +103,9 @@ def main():
         for dtype in (torch.float32, torch.bfloat16):
             cases += [(dtype, 3, 5, 7, 9, 16, True, True, True, True, True), (dtype, 2, 3, 13, 11, 64, False, True, False, False, False),
                       (dtype, 4, 10, 32, 32, 16, False, False, True, True, False), (dtype, 1, 10, 32, 32, 64, True, True, False, True, True),
-                      (dtype, 5, 2, 8, 8, 256, False, True, False, False, True), (dtype, 2, 10, 16, 16, 128, True, True, True, False, True)]
+                      (dtype, 5, 2, 8, 8, 256, False, True, False, False, True), (dtype, 2, 10, 16, 16, 128, True, True, True, False, True),
+                      # more work items than SMs: the persistent kernels pipeline several items per CTA
+                      (dtype, 40, 2, 8, 8, 256, True, True, True, True, True), (dtype, 37, 3, 9, 8, 64, False, True, False, False, False)]
         for cs in cases:
             r = run_case(ops, *cs, flush=flush, timed=False)
             print(json.dumps(r))
