@@ -62,7 +62,7 @@ bn_fwd_persist_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __r
                       uint32_t slice_cap, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                       int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                       float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
-                      float* num_batches_tracked, int64_t ld_n) {
+                      float* num_batches_tracked, int64_t ld_n, int bar_base) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t full[BNP_NB];
@@ -110,7 +110,7 @@ bn_fwd_persist_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __r
     bnr_reduce<N>(a, b, ch, red, partial + ((size_t)it.c * S + it.s) * 2 * ch);      // ends with __syncthreads
     if (tid == 0) {
       unsigned g;
-      bnp_arrive(it.c, S, &g);
+      bnp_arrive(bar_base + it.c, S, &g);
       s_gen[i % BNP_NB] = g;
     }
   };
@@ -124,7 +124,7 @@ bn_fwd_persist_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __r
     // thread 0 is still arriving for item i + 1 while thread 32 polls the barrier of item i (s_gen[i % NB] was written one
     // iteration ago, several __syncthreads back): the two latencies overlap
     const BnpItem it = bnp_item<T>(i, S, M, ch);
-    if (tid == 32) bnp_wait(it.c, S, s_gen[i % BNP_NB]);
+    if (tid == 32) bnp_wait(bar_base + it.c, S, s_gen[i % BNP_NB]);
     __syncthreads();
     bnr_sum_partials(partial + (size_t)it.c * S * 2 * ch, S, ch, red, sums);
     bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
@@ -170,7 +170,7 @@ bn_bwd_persist_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const
                       T* __restrict__ dx, T* __restrict__ dres, int64_t M, int ch, int S, int C, uint32_t slice_cap,
                       float* partial, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                       const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
-                      float* __restrict__ dbeta, int64_t ld_g) {
+                      float* __restrict__ dbeta, int64_t ld_g, int bar_base) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t full[BNP_NB];
@@ -256,7 +256,7 @@ bn_bwd_persist_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const
     bnr_reduce<N>(a, bb, ch, red, partial + ((size_t)it.c * S + it.s) * 2 * ch);
     if (tid == 0) {
       unsigned gen;
-      bnp_arrive(it.c, S, &gen);
+      bnp_arrive(bar_base + it.c, S, &gen);
       s_gen[i % BNP_NB] = gen;
     }
   };
@@ -268,7 +268,7 @@ bn_bwd_persist_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const
   for (int i = 0; i < my_n; ++i) {
     if (i + 1 < my_n) phase_a(i + 1);
     const BnpItem it = bnp_item<T>(i, S, M, ch);
-    if (tid == 32) bnp_wait(it.c, S, s_gen[i % BNP_NB]);
+    if (tid == 32) bnp_wait(bar_base + it.c, S, s_gen[i % BNP_NB]);
     __syncthreads();
     bnr_sum_partials(partial + (size_t)it.c * S * 2 * ch, S, ch, red, sums);
     bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef, sums, it.c, it.s);

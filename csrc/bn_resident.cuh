@@ -153,7 +153,7 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
                        uint32_t slice_cap, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                        int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                        float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
-                       float* num_batches_tracked, int64_t ld_n, int res_smem /* the residual slice is resident too */) {
+                       float* num_batches_tracked, int64_t ld_n, int res_smem /* the residual slice is resident too */, int bar_base) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bar;
@@ -192,7 +192,7 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
     }
   }
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
-  client_barrier(S);
+  client_barrier(S, bar_base);
   bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 2 * ch);
   bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
                  save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S, coef + 2 * ch);
@@ -263,7 +263,7 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
                        T* __restrict__ dx, T* __restrict__ dres, int64_t M, int ch, int S, uint32_t slice_cap, float* partial,
                        const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                        const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
-                       float* __restrict__ dbeta, int64_t ld_g, int extras /* bit 0: dy2 resident, bit 1: y resident */) {
+                       float* __restrict__ dbeta, int64_t ld_g, int extras /* bit 0: dy2 resident, bit 1: y resident */, int bar_base) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) uint64_t bar;
@@ -348,7 +348,7 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
     }
   }
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
-  client_barrier(S);
+  client_barrier(S, bar_base);
   bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 4 * ch);
   bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef, coef + 4 * ch);
   __syncthreads();

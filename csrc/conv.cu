@@ -8,6 +8,7 @@
 #include "common.cuh"
 #include "../include/fedml_b200.h"
 #include <stdlib.h>
+#include <mutex>
 
 #define BN_THREADS 256
 #define BN_VEC 8
@@ -321,10 +322,27 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
 // are dispatched in linear block order (a client's CTAs are adjacent, earlier clients first) and S is far below the
 // number of resident CTA slots.  One BN kernel at a time per device (they share this state and the scratch).
 static __device__ unsigned g_bn_barrier[2 * 65536];
-__device__ __forceinline__ void client_barrier(int S) {
+// BatchNorm calls on different streams (client groups of the simulator) may overlap: each stream gets its own eighth of
+// the barrier array (8192 clients).  More than eight streams, or more than 8192 clients in a call, share region 0 - those
+// calls must then not overlap.
+static int bn_barrier_region(cudaStream_t stream, int C) {
+  static std::mutex mu;
+  static cudaStream_t seen[8];
+  static int n_seen = 0;
+  if (C > 8192) return 0;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < n_seen; ++i)
+    if (seen[i] == stream) return i * 8192;
+  if (n_seen < 8) {
+    seen[n_seen] = stream;
+    return (n_seen++) * 8192;
+  }
+  return 0;
+}
+__device__ __forceinline__ void client_barrier(int S, int bar_base) {
   __syncthreads();
   if (S > 1 && threadIdx.x == 0) {
-    unsigned* st = g_bn_barrier + 2 * blockIdx.y;
+    unsigned* st = g_bn_barrier + 2 * (bar_base + (int)blockIdx.y);
     __threadfence();                                   // publish this CTA's partial sums
     const unsigned gen = ld_acquire_gpu(st + 1);
     if (atomicAdd(st, 1u) == (unsigned)S - 1) {
@@ -347,27 +365,30 @@ bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __res
                     int64_t M, int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta,
                     int64_t ld_p, float* running_mean, float* running_var, int64_t ld_r, const float* __restrict__ active,
                     float momentum, float eps, int relu, float* __restrict__ save_mean, float* __restrict__ save_rstd,
-                    float* num_batches_tracked, int64_t ld_n) {
+                    float* num_batches_tracked, int64_t ld_n, int bar_base) {
   __shared__ float smem[BN_THREADS * 16];
   extern __shared__ float sm[];
   pdl_wait();
   pdl_trigger();
   bn_stats_body(x, M, ch, S, partial, smem);
-  client_barrier(S);
+  client_barrier(S, bar_base);
   bn_apply_body(x, res, y, M, ch, S, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, relu, 1,
                 save_mean, save_rstd, num_batches_tracked, ld_n, sm, S);
 }
 
-// The fused form wins when the layer is large (second pass served by L2, 1-2 % on the 100-client bench) and loses when
-// it is small (the in-kernel barrier costs more than a kernel boundary inside a CUDA graph: +6 % at 13 clients), so
-// it is chosen by activation size.  FB_BN_FUSED=0 / 1 forces one form.
+// One launch per BatchNorm (statistics -> per-client barrier -> apply) for every layer size.  FB_BN_FUSED=0 forces the
+// two-pass kernels.  Round 1 chose by activation size (>= 48 MB) because the in-kernel barrier lost to a kernel boundary
+// on small layers; with the resident kernels and programmatic launch edges the single launch wins everywhere: ResNet-56
+// tf32 round at 13 / 25 / 50 / 100 clients 24.6 -> 21.5, 36.1 -> 32.8, 60.1 -> 56.8, 105.7 -> 104.3 ms; bf16 18.5 -> 17.6,
+// 25.6 -> 24.6, 39.5 -> 38.5, 66.0 -> 66.0 ms.
 static bool bn_fused_enabled(int64_t act_bytes) {
   static int v = -2;
   if (v == -2) {
     const char* e = getenv("FB_BN_FUSED");
     v = e ? (atoi(e) == 0 ? 0 : 1) : -1;
   }
-  return v >= 0 ? v == 1 : act_bytes >= (int64_t)48 << 20;
+  (void)act_bytes;
+  return v >= 0 ? v == 1 : true;
 }
 
 __device__ __forceinline__ void
@@ -395,6 +416,7 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
   // epilogue of the convolution that wrote x (FbGroupedGemm.stats): one pass over x instead of two
   const bool have_stats = training == 2;
   if (training == 1 && bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    const int bar_base = bn_barrier_region((cudaStream_t)stream, C);
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
@@ -406,7 +428,7 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
         if (int rc = bn_resident_allow_smem(bn_fwd_persist_kernel<T>, smemp)) return rc;
         FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_persist_kernel<T>, dim3(grid), dim3(BN_THREADS), smemp, (cudaStream_t)stream,
             (const T*)x, (const T*)res, (T*)y, M, ch, Sp, (int)C, capp, scratch, gamma, beta, ld_p, running_mean,
-            running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
+            running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n, bar_base));
         FB_CHECK_CUDA(cudaGetLastError());
         return FB_OK;
       }
@@ -423,13 +445,13 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
       if (int rc = bn_resident_allow_smem(bn_fwd_resident_kernel<T>, smem)) return rc;
       FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
           (const T*)x, (const T*)res, (T*)y, M, ch, Sr, cap, scratch, gamma, beta, ld_p, running_mean,
-          running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n, res_smem));
+          running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n, res_smem, bar_base));
       FB_CHECK_CUDA(cudaGetLastError());
       return FB_OK;
     }
     FB_CHECK_CUDA(fb_launch_pdl(bn_fwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(2 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const T*)x, (const T*)res, (T*)y, M, ch, S, scratch, gamma, beta, ld_p, running_mean,
-        running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n));
+        running_var, ld_r, active, momentum, eps, relu, save_mean, save_rstd, num_batches_tracked, ld_n, bar_base));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }
@@ -697,13 +719,13 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, const T
                     const T* __restrict__ y, T* __restrict__ dx, T* __restrict__ dres, int64_t M,
                     int ch, int S, float* partial, const float* __restrict__ gamma, const float* __restrict__ beta, int64_t ld_p,
                     const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* __restrict__ dgamma,
-                    float* __restrict__ dbeta, int64_t ld_g) {
+                    float* __restrict__ dbeta, int64_t ld_g, int bar_base) {
   __shared__ float smem[BN_THREADS * 16];
   extern __shared__ float sm[];
   pdl_wait();
   pdl_trigger();
   bn_bwd_stats_body(dy, dy2, x, y, M, ch, S, mean, rstd, gamma, beta, ld_p, relu, partial, smem);
-  client_barrier(S);
+  client_barrier(S, bar_base);
   bn_bwd_apply_body(dy, dy2, x, y, dx, dres, M, ch, S, partial, gamma, beta, ld_p, mean, rstd, relu, dgamma, dbeta, ld_g, sm);
 }
 
@@ -720,6 +742,7 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
   int S = bn_slices(C, M, ch);
   if (bn_forced_slices(1) > 0) S = bn_forced_slices(1);
   if (bn_fused_enabled((int64_t)C * M * ch * (int64_t)sizeof(T))) {
+    const int bar_base = bn_barrier_region((cudaStream_t)stream, C);
     int Sr = 0;
     uint32_t cap = 0;
     size_t smem = 0;
@@ -731,7 +754,7 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
         if (int rc = bn_resident_allow_smem(bn_bwd_persist_kernel<T>, smemp)) return rc;
         FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_persist_kernel<T>, dim3(grid), dim3(BN_THREADS), smemp, (cudaStream_t)stream,
             (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, ch, Sp, (int)C, capp, scratch, gamma, beta,
-            ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+            ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g, bar_base));
         FB_CHECK_CUDA(cudaGetLastError());
         return FB_OK;
       }
@@ -746,13 +769,13 @@ static int bn_bwd_impl(const void* dy, const void* dy2, const void* x, const voi
       if (int rc = bn_resident_allow_smem(bn_bwd_resident_kernel<T>, smem)) return rc;
       FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_resident_kernel<T>, dim3(dim3(Sr, C)), dim3(BN_THREADS), smem, (cudaStream_t)stream,
           (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx, (T*)dres, M, ch, Sr, cap, scratch, gamma, beta, ld_p,
-          save_mean, save_rstd, relu, dgamma, dbeta, ld_g, extras));
+          save_mean, save_rstd, relu, dgamma, dbeta, ld_g, extras, bar_base));
       FB_CHECK_CUDA(cudaGetLastError());
       return FB_OK;
     }
     FB_CHECK_CUDA(fb_launch_pdl(bn_bwd_fused_kernel<T>, dim3(dim3(S, C)), dim3(BN_THREADS), (size_t)(4 * ch * sizeof(float)), (cudaStream_t)stream, 
         (const T*)dy, (const T*)dy2, (const T*)x, (const T*)y, (T*)dx,
-        (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g));
+        (T*)dres, M, ch, S, scratch, gamma, beta, ld_p, save_mean, save_rstd, relu, dgamma, dbeta, ld_g, bar_base));
     FB_CHECK_CUDA(cudaGetLastError());
     return FB_OK;
   }

@@ -356,10 +356,10 @@ _BN_FUSED_ENV = _os.environ.get("FB_BN_FUSED")
 
 
 def _bn_fused(x) -> bool:
-    """Mirror of bn_fused_enabled() in csrc/conv.cu (stats + apply in one launch for large layers)."""
+    """Mirror of bn_fused_enabled() in csrc/conv.cu (stats + apply in one launch unless FB_BN_FUSED=0)."""
     if _BN_FUSED_ENV is not None:
         return _BN_FUSED_ENV != "0"
-    return x.numel() * x.element_size() >= 48 << 20
+    return True
 
 
 def _scratch_for(device, n_floats):

@@ -17,6 +17,14 @@ from fedml_b200.simulation import SimulatorNCCL
 sim = SimulatorNCCL(args, dev, ds, model).simulator
 for r in range(3): sim.train_one_round(r)
 torch.cuda.synchronize()
+if os.environ.get("TIME_ONLY"):          # plain CUDA-event timing of 8 rounds, no profiler
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for r in range(3, 11): sim.train_one_round(r)
+    e1.record(); torch.cuda.synchronize()
+    print(f"TIME K={K} dtype={args.compute_dtype} FB_BN_FUSED={os.environ.get('FB_BN_FUSED')} FB_BN_RESIDENT={os.environ.get('FB_BN_RESIDENT')}: "
+          f"{e0.elapsed_time(e1) / 8:.3f} ms/round")
+    sys.exit(0)
 from torch.profiler import ProfilerActivity, profile
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     sim.train_one_round(3); torch.cuda.synchronize()
