@@ -16,7 +16,7 @@ from ..core.distributed.communication.message import Message
 from ..core.distributed.managers import ServerManager
 from ..simulation.mp.fedavg import MyMessage
 from ..simulation.sp.fedavg_api import client_sampling
-from .mnn_file import read_mnn_as_tensor_dict, read_mnn_like, write_mnn_like, write_tensor_dict_to_mnn
+from .mnn_file import load_into_module, read_mnn_as_tensor_dict, read_mnn_like, write_mnn_like, write_tensor_dict_to_mnn
 
 
 class FedMLAggregatorMNN:
@@ -54,8 +54,7 @@ class FedMLAggregatorMNN:
         return client_sampling(round_idx, total, per_round)
 
     def test_on_server_for_all_clients(self, round_idx):
-        sd = read_mnn_like(self.global_model_file_path)
-        self.model.load_state_dict(A.cast_like(sd, self.model.state_dict()))
+        load_into_module(self.global_model_file_path, self.model)
         self.model.to(self.device).eval()
         correct = loss = total = 0.0
         with torch.no_grad():

@@ -1,39 +1,48 @@
-"""Portable on-disk model container used where the reference uses ``.mnn`` files.
+"""Model files of the cross-device (Beehive) server: genuine MNN ``.mnn`` graphs, read and written without the MNN runtime.
 
-The cross-device server of the reference reads every uploaded ``.mnn`` as ``{layer_idx: tensor}``
-(cross_device/server_mnn/utils.py:11-28), averages, writes the values back into the MNN graph (:31-50) and
-evaluates with the MNN runtime.  MNN 1.1.6 is a third-party binary wheel that cannot be installed here, so
-files named ``*.mnn`` in this framework hold the same information — an ordered list of named tensors — in the
-``Message`` binary codec (magic ``FB2M``).  ``read_mnn_as_tensor_dict`` keeps the reference's
-index-keyed view; a real MNN file is rejected with a clear error."""
+The reference's server reads every uploaded ``.mnn`` as ``{layer_idx: tensor}`` (cross_device/server_mnn/utils.py:11-28),
+averages, writes the values back into the MNN graph (:31-50) and evaluates.  :mod:`.mnn_format` does the same on the
+FlatBuffers bytes (the MNN wheel cannot be installed here): parameters are read in graph order, written back in place, and
+the LeNet-5 / logistic-regression graphs of the reference's mobile models are built from scratch; other architectures are
+stored as a parameters-only MNN graph.  Files written by round 1 of this repo (magic ``FB2M``) are still readable."""
 import os
 from collections import OrderedDict
 
+import numpy as np
 import torch
 
 from ..core.distributed.communication.message import Message
+from . import mnn_format as MF
+
+_LENET_KEYS = ["conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias", "fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias"]
 
 
-def write_mnn_like(path, state_dict):
+def write_mnn_like(path, state_dict, input_dims=None):
+    """``state_dict`` -> ``.mnn``: the full inference graph for LeNet-5 and for pure linear stacks, parameters-only otherwise."""
     os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
-    m = Message()
-    m.add_params("names", list(state_dict.keys()))
-    m.add_params("tensors", [v.detach().cpu() for v in state_dict.values()])
-    tmp = path + ".tmp"
-    with open(tmp, "wb") as fh:
-        fh.write(m.to_bytes())
-    os.replace(tmp, path)
-    return path
+    keys = list(state_dict.keys())
+    arrs = [v.detach().cpu().float().numpy() for v in state_dict.values()]
+    if keys == _LENET_KEYS:
+        return MF.build_lenet5(path, arrs, input_dims or (1, 1, 28, 28))
+    linear = len(keys) % 2 == 0 and all(keys[2 * i].endswith("weight") and keys[2 * i + 1].endswith("bias") and arrs[2 * i].ndim == 2
+                                        and arrs[2 * i + 1].ndim == 1 for i in range(len(keys) // 2))
+    if linear and keys:
+        return MF.build_mlp(path, arrs, input_dims or (1, arrs[0].shape[1]))
+    return MF.build_params_only(path, OrderedDict(zip(keys, arrs)))
+
+
+def _is_legacy(path):
+    with open(path, "rb") as fh:
+        return fh.read(4) == b"FB2M"
 
 
 def read_mnn_like(path) -> "OrderedDict[str, torch.Tensor]":
-    with open(path, "rb") as fh:
-        blob = fh.read()
-    if blob[:4] != b"FB2M":
-        raise ValueError(f"{path} is not a fedml_b200 model container (a genuine MNN graph needs the MNN runtime, "
-                         "which is unavailable on this box)")
-    m = Message.from_bytes(blob)
-    return OrderedDict(zip(m.get("names"), m.get("tensors")))
+    """Ordered ``name -> tensor``; names are the MNN op names (``TrainableParam<n>`` for graphs a device SDK wrote)."""
+    if _is_legacy(path):
+        with open(path, "rb") as fh:
+            m = Message.from_bytes(fh.read())
+        return OrderedDict(zip(m.get("names"), m.get("tensors")))
+    return OrderedDict((k, torch.from_numpy(v)) for k, v in MF.read_params(path).items())
 
 
 def read_mnn_as_tensor_dict(path):
@@ -41,6 +50,34 @@ def read_mnn_as_tensor_dict(path):
 
 
 def write_tensor_dict_to_mnn(path, tensor_params_dict):
+    """Values of ``{layer_idx: tensor}`` into the graph at ``path``, in place (the graph itself is untouched)."""
+    n = len(tensor_params_dict)
+    vals = [np.asarray(tensor_params_dict[i].detach().cpu().float().numpy() if torch.is_tensor(tensor_params_dict[i])
+                       else tensor_params_dict[i]) for i in range(n)]
+    if _is_legacy(path):
+        names = list(read_mnn_like(path).keys())
+        m = Message()
+        m.add_params("names", names)
+        m.add_params("tensors", [torch.as_tensor(v) for v in vals])
+        with open(path + ".tmp", "wb") as fh:
+            fh.write(m.to_bytes())
+        os.replace(path + ".tmp", path)
+        return path
+    return MF.write_params(path, vals)
+
+
+def load_into_module(path, module):
+    """Parameters of the file into ``module``: by name when the names are state-dict keys, else positionally over the
+    module's parameters-and-buffers order restricted to tensors of matching element count (MNN stores linear biases as
+    [1, out] and names parameters ``TrainableParam<n>``)."""
     sd = read_mnn_like(path)
-    names = list(sd.keys())
-    return write_mnn_like(path, OrderedDict((names[i], tensor_params_dict[i]) for i in range(len(names))))
+    own = module.state_dict()
+    if set(sd.keys()) <= set(own.keys()):
+        module.load_state_dict({k: sd[k].reshape(own[k].shape).to(own[k].dtype) for k in sd}, strict=False)
+        return module
+    targets = [k for k, v in own.items() if v.dtype.is_floating_point and not k.endswith("num_batches_tracked")]
+    vals = list(sd.values())
+    if len(vals) != len(targets) or any(vals[i].numel() != own[targets[i]].numel() for i in range(len(vals))):
+        raise ValueError(f"{path}: {len(vals)} parameters do not line up with the model's {len(targets)} tensors")
+    module.load_state_dict({k: vals[i].reshape(own[k].shape).to(own[k].dtype) for i, k in enumerate(targets)}, strict=False)
+    return module

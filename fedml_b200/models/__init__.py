@@ -69,14 +69,17 @@ def create(args, output_dim):
 
 
 def create_mnn_lenet5_model(mnn_file_path, class_num=10):
-    """Cross-device (Beehive) global-model file.  The reference serialises an MNN expression graph
-    (model/mobile/mnn_lenet.py:31); MNN is not installable here, so the on-disk format is the
-    ``.mnn``-named portable tensor container of :mod:`fedml_b200.cross_device.mnn_file`."""
+    """Writes the initial global model file of the cross-device examples (model/mobile/mnn_lenet.py:31): a genuine MNN
+    graph (Input, ConvertTensor, Convolution, ReLU, Pooling, Reshape, MatMul, BinaryOp, Softmax, TrainableParam ops) built
+    by :mod:`fedml_b200.cross_device.mnn_format` - op for op the graph the reference's MNN script saves."""
     from ..cross_device.mnn_file import write_mnn_like
     write_mnn_like(mnn_file_path, LeNet5(class_num).state_dict())
 
 
 def create_mnn_resnet20_model(mnn_file_path, class_num=10):
+    """ResNet-20 (model/mobile/mnn_resnet.py): MNN expands its training-mode BatchNorm into ~10 ops per layer that the
+    builder does not emit, so the file is a parameters-only MNN graph (TrainableParam ops named after the state-dict keys);
+    the server side - read, average, write back - works on it like on any device-written graph."""
     from ..cross_device.mnn_file import write_mnn_like
     from .cv import BasicBlock
     write_mnn_like(mnn_file_path, ResNet(BasicBlock, [3, 3, 3], class_num, "cifar").state_dict())

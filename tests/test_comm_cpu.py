@@ -164,7 +164,8 @@ def test_round_deadline_partial_aggregation(broker, tmp_path):
 
 
 def test_cross_device_server_with_file_models(broker, tmp_path):
-    from fedml_b200.cross_device.mnn_file import read_mnn_as_tensor_dict, read_mnn_like, write_mnn_like
+    import shutil
+    from fedml_b200.cross_device.mnn_file import read_mnn_as_tensor_dict, read_mnn_like, write_tensor_dict_to_mnn
     base = dict(training_type="cross_device", dataset="mnist", model="lenet", client_num_in_total=2, client_num_per_round=2, client_id_list="[1, 2]",
                 comm_round=2, batch_size=10, synthetic_train_size=300, mnist_client_num=2, backend="MQTT_S3_MNN", mqtt_port=broker, log_level="WARNING",
                 run_id="cd-t", object_store_dir=str(tmp_path / "store"), model_file_cache_folder=str(tmp_path / "cache"),
@@ -183,8 +184,9 @@ def test_cross_device_server_with_file_models(broker, tmp_path):
 
         def receive_message(s, t, p):
             if t in (1, 2):
-                sd = {k: v + 0.01 * s.rank for k, v in read_mnn_like(p["model_params"]).items()}
-                path = str(tmp_path / f"phone{s.rank}" / "up.mnn"); write_mnn_like(path, sd)
+                # a phone trains the graph it downloaded and uploads the same graph with new parameter values
+                path = str(tmp_path / f"phone{s.rank}" / "up.mnn"); shutil.copyfile(p["model_params"], path)
+                write_tensor_dict_to_mnn(path, {i: v + 0.01 * s.rank for i, v in read_mnn_as_tensor_dict(path).items()})
                 m = Message(3, s.rank, 0); m.add_params("model_params", path); m.add_params("num_samples", 10 * s.rank); s.cm.send_message(m)
             elif t == 6:
                 s.cm.stop_receive_message()
@@ -194,10 +196,73 @@ def test_cross_device_server_with_file_models(broker, tmp_path):
     init = {k: v.clone() for k, v in model.state_dict().items()}
     agg = srv.run()
     assert len(agg.history) == 2
-    final = read_mnn_like(str(tmp_path / "global.mnn"))
-    # two rounds of (+0.01*1 weighted 10, +0.01*2 weighted 20) => +2 * 0.01 * 5/3
-    k = "fc2.bias"
-    torch.testing.assert_close(final[k], init[k] + 2 * 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)
+    final = list(read_mnn_like(str(tmp_path / "global.mnn")).values())
+    # two rounds of (+0.01*1 weighted 10, +0.01*2 weighted 20) => +2 * 0.01 * 5/3; the last parameter of the MNN graph is fc2's bias
+    torch.testing.assert_close(final[-1].reshape(-1), init["fc2.bias"] + 2 * 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)
+    from fedml_b200.cross_device import mnn_format
+    assert [o["type"] for o in mnn_format.describe(str(tmp_path / "global.mnn"))].count(mnn_format.OP_CONV) == 2     # still the LeNet graph
+
+
+REF_MNN = "/root/reference/python/examples/cross_device/mqtt_s3_fedavg_mnist_lr_example/model_file_cache/global_model.mnn"
+REF_MNN_RESNET = "/root/reference/python/examples/cross_device/mqtt_s3_fedavg_cifar10_lr_example/model_file_cache/global_model.mnn"
+
+
+def test_mnn_format_builder_reader_and_in_place_writer(tmp_path):
+    """``.mnn`` files without the MNN runtime (reference: cross_device/server_mnn/utils.py:11-50, model/mobile/mnn_lenet.py)."""
+    from fedml_b200.cross_device import mnn_format as MF
+    from fedml_b200.cross_device.mnn_file import load_into_module, read_mnn_like, write_mnn_like
+    from fedml_b200.models.cv import LeNet5
+    torch.manual_seed(0)
+    net = LeNet5()
+    path = str(tmp_path / "lenet.mnn")
+    fedml.model.create_mnn_lenet5_model(path)
+    write_mnn_like(path, net.state_dict())
+    ops = MF.describe(path)
+    assert [o["type"] for o in ops][:7] == [MF.OP_INPUT, MF.OP_CONVERT_TENSOR, MF.OP_TRAINABLE_PARAM, MF.OP_TRAINABLE_PARAM, MF.OP_CONV,
+                                            MF.OP_RELU, MF.OP_POOLING]
+    assert ops[4]["conv"] == {"kernel": [5, 5], "stride": [1, 1], "out": 20, "in": 1, "pad_mode": 1} and ops[4]["inputs"] == [1, 2, 3]
+    assert all(o["outputs"] == [i] for i, o in enumerate(ops)) and ops[-1]["type"] == MF.OP_SOFTMAX
+    got = MF.read_params(path)
+    for (k, v), w in zip(net.state_dict().items(), got.values()):
+        np.testing.assert_array_equal(v.numpy().reshape(w.shape), w)
+    # positional load into a fresh module, in-place overwrite, size check
+    other = load_into_module(path, LeNet5())
+    for k, v in net.state_dict().items():
+        torch.testing.assert_close(other.state_dict()[k], v, rtol=0, atol=0)
+    size = os.path.getsize(path)
+    MF.write_params(path, [w * 2 for w in got.values()])
+    assert os.path.getsize(path) == size and MF.describe(path) == ops
+    np.testing.assert_array_equal(list(MF.read_params(path).values())[0], list(got.values())[0] * 2)
+    with pytest.raises(MF.MnnFormatError):
+        MF.write_params(path, [w[..., :1] for w in got.values()])
+    # logistic regression = one linear layer; other architectures = parameters-only graph keyed by state-dict names
+    lr = torch.nn.Linear(784, 10)
+    write_mnn_like(str(tmp_path / "lr.mnn"), lr.state_dict())
+    assert [o["type"] for o in MF.describe(str(tmp_path / "lr.mnn"))] == [MF.OP_INPUT, MF.OP_RESHAPE, MF.OP_TRAINABLE_PARAM, MF.OP_MATMUL,
+                                                                          MF.OP_TRAINABLE_PARAM, MF.OP_BINARY, MF.OP_SOFTMAX]
+    fedml.model.create_mnn_resnet20_model(str(tmp_path / "r20.mnn"))
+    sd = read_mnn_like(str(tmp_path / "r20.mnn"))
+    assert "layer1.0.conv1.weight" in sd and sd["fc.weight"].shape == (10, 64)
+
+
+@pytest.mark.skipif(not os.path.exists(REF_MNN), reason="reference sample .mnn files not present")
+def test_mnn_format_against_files_written_by_the_mnn_sdk(tmp_path):
+    """The two ``.mnn`` files shipped with the reference's cross-device examples were written by MNN itself: the LeNet-5
+    graph built here must decode to the same op list, and both files must survive read -> overwrite -> read."""
+    from fedml_b200.cross_device import mnn_format as MF
+    from fedml_b200.models.cv import LeNet5
+    ref_ops = MF.describe(REF_MNN)
+    mine = str(tmp_path / "mine.mnn")
+    MF.build_lenet5(mine, [v.numpy() for v in LeNet5().state_dict().values()], ref_ops[0]["dims"])
+    assert MF.describe(mine) == ref_ops
+    for src, n_params in ((REF_MNN, 8), (REF_MNN_RESNET, None)):
+        params = MF.read_params(src)
+        assert n_params is None or len(params) == n_params
+        out = str(tmp_path / "patched.mnn")
+        MF.write_params(src, [np.full_like(v, 0.25) for v in params.values()], out_path=out)
+        again = MF.read_params(out)
+        assert list(again) == list(params) and all((v == 0.25).all() for v in again.values())
+        assert os.path.getsize(out) == os.path.getsize(src) and MF.describe(out) == MF.describe(src)
 
 
 def test_mpc_toolbox_and_secure_aggregation():
