@@ -978,3 +978,105 @@ extern "C" int fb_col2im3x3_nhwc_f32(const void* cols, void* dx, int32_t n_img, 
                                      fb_stream_t stream) {
   return col2im_impl<float>(cols, dx, n_img, H, W, ch, stride, stream);
 }
+
+// ---------------------------------------------------------------- 2x2 max pooling (stride 2) on NHWC, optional window offset
+// y[n][i][j][:] = max over x[n][off_h + 2i + {0,1}][off_w + 2j + {0,1}][:]: the offset lets the pool read the interior of a
+// "same"-padded convolution output (a valid convolution is its centre crop) without a cropping copy.  Replaces
+// nn.MaxPool2d(2, stride=2) of the reference CNNs (model/cv/cnn.py:74-142).
+template <typename T>
+__global__ void __launch_bounds__(256)
+maxpool2x2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint32_t total_vec, int H, int W, int ch, int off_h, int off_w,
+                      int Ho, int Wo) {
+  const uint32_t cv = ch / 8, per_row = cv * (uint32_t)Wo, per_img = per_row * (uint32_t)Ho;
+  pdl_wait();
+  pdl_trigger();
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += gridDim.x * blockDim.x) {
+    const uint32_t n = i / per_img, r0 = i - n * per_img;
+    const uint32_t ho = r0 / per_row, r1 = r0 - ho * per_row;
+    const uint32_t wo = r1 / cv, c8 = r1 - wo * cv;
+    const size_t base = (((size_t)n * H + off_h + 2 * ho) * W + off_w + 2 * wo) * ch + (size_t)c8 * 8;
+    float m[8], f[8];
+    unpack8(ldraw(x + base), m);
+    const size_t o[3] = {(size_t)ch, (size_t)W * ch, (size_t)W * ch + ch};
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+      unpack8(ldraw(x + base + o[t]), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], f[e]);
+    }
+    store8(y + (size_t)i * 8, m);
+  }
+}
+// dx (full [H][W] map, zero outside the pooled windows): dy goes to the first maximal element of its window in scan order
+// (the argmax rule of the reference's pooling backward); relu_mask also zeroes it where x <= 0 (pool input = ReLU output)
+template <typename T>
+__global__ void __launch_bounds__(256)
+maxpool2x2_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, uint32_t total_vec, int H, int W,
+                      int ch, int off_h, int off_w, int Ho, int Wo, int relu_mask) {
+  const uint32_t cv = ch / 8, per_row = cv * (uint32_t)W, per_img = per_row * (uint32_t)H;
+  pdl_wait();
+  pdl_trigger();
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += gridDim.x * blockDim.x) {
+    const uint32_t n = i / per_img, r0 = i - n * per_img;
+    const int h = (int)(r0 / per_row);
+    const uint32_t r1 = r0 - (uint32_t)h * per_row;
+    const int w = (int)(r1 / cv);
+    const uint32_t c8 = r1 - (uint32_t)w * cv;
+    float out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const int hh = h - off_h, ww = w - off_w;
+    if (hh >= 0 && ww >= 0 && hh < 2 * Ho && ww < 2 * Wo) {
+      const int ho = hh >> 1, wo = ww >> 1, me = ((hh & 1) << 1) | (ww & 1);      // my position in the window, scan order
+      const size_t base = (((size_t)n * H + off_h + 2 * ho) * W + off_w + 2 * wo) * ch + (size_t)c8 * 8;
+      const size_t o[4] = {0, (size_t)ch, (size_t)W * ch, (size_t)W * ch + ch};
+      float v[4][8], d[8];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) unpack8(ldraw(x + base + o[t]), v[t]);
+      unpack8(ldraw(dy + ((((size_t)n * Ho + ho) * Wo + wo) * ch + (size_t)c8 * 8)), d);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        int arg = 0;
+        float best = v[0][e];
+#pragma unroll
+        for (int t = 1; t < 4; ++t)
+          if (v[t][e] > best) {
+            best = v[t][e];
+            arg = t;
+          }
+        out[e] = (arg == me && (!relu_mask || best > 0.f)) ? d[e] : 0.f;
+      }
+    }
+    store8(dx + (size_t)i * 8, out);
+  }
+}
+template <typename T>
+static int maxpool_impl(const void* x, void* y, const void* dy, void* dx, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+                        int32_t off_h, int32_t off_w, int32_t Ho, int32_t Wo, int32_t relu_mask, fb_stream_t stream) {
+  FB_REQUIRE(x && n_img >= 1 && ch >= 8 && ch % 8 == 0 && Ho >= 1 && Wo >= 1 && off_h >= 0 && off_w >= 0 && off_h + 2 * Ho <= H &&
+                 off_w + 2 * Wo <= W,
+             "fb_maxpool2x2: bad arguments (ch a multiple of 8, windows inside the map)");
+  const int64_t total = dx ? (int64_t)n_img * H * W * (ch / 8) : (int64_t)n_img * Ho * Wo * (ch / 8);
+  FB_REQUIRE(total < 4294967296LL, "fb_maxpool2x2: tensor too large for 32-bit indexing");
+  int64_t grid = (total + 255) / 256, cap = (int64_t)fb_num_sms() * 16;
+  if (dx) {
+    FB_REQUIRE(dy, "fb_maxpool2x2_bwd: dy missing");
+    FB_CHECK_CUDA(fb_launch_pdl(maxpool2x2_bwd_kernel<T>, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)0, (cudaStream_t)stream,
+        (const T*)dy, (const T*)x, (T*)dx, (uint32_t)total, H, W, ch, off_h, off_w, Ho, Wo, relu_mask));
+  } else {
+    FB_REQUIRE(y, "fb_maxpool2x2_fwd: y missing");
+    FB_CHECK_CUDA(fb_launch_pdl(maxpool2x2_fwd_kernel<T>, dim3((int)(grid < cap ? grid : cap)), dim3(256), (size_t)0, (cudaStream_t)stream,
+        (const T*)x, (T*)y, (uint32_t)total, H, W, ch, off_h, off_w, Ho, Wo));
+  }
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
+extern "C" int fb_maxpool2x2_fwd(const void* x, void* y, int32_t act_fp32, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+                                 int32_t off_h, int32_t off_w, int32_t Ho, int32_t Wo, fb_stream_t stream) {
+  return act_fp32 ? maxpool_impl<float>(x, y, nullptr, nullptr, n_img, H, W, ch, off_h, off_w, Ho, Wo, 0, stream)
+                  : maxpool_impl<__nv_bfloat16>(x, y, nullptr, nullptr, n_img, H, W, ch, off_h, off_w, Ho, Wo, 0, stream);
+}
+extern "C" int fb_maxpool2x2_bwd(const void* dy, const void* x, void* dx, int32_t act_fp32, int32_t n_img, int32_t H, int32_t W,
+                                 int32_t ch, int32_t off_h, int32_t off_w, int32_t Ho, int32_t Wo, int32_t relu_mask,
+                                 fb_stream_t stream) {
+  return act_fp32 ? maxpool_impl<float>(x, nullptr, dy, dx, n_img, H, W, ch, off_h, off_w, Ho, Wo, relu_mask, stream)
+                  : maxpool_impl<__nv_bfloat16>(x, nullptr, dy, dx, n_img, H, W, ch, off_h, off_w, Ho, Wo, relu_mask, stream);
+}

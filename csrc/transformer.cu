@@ -40,6 +40,17 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return r;
 }
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// eight consecutive elements of a bf16 or fp32 tensor <-> fp32 registers (kernels templated on the activation type)
+__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float* f) { unpack8(ldg16(p), f); }
+__device__ __forceinline__ void ld8(const float* p, float* f) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
+__device__ __forceinline__ void st8(float* p, const float* f) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(f[0], f[1], f[2], f[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(f[4], f[5], f[6], f[7]);
+}
 __device__ __forceinline__ void ld8f(const float* p, float* f) {
   const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
@@ -454,58 +465,61 @@ __device__ __forceinline__ float gelu_grad(float x) {
 }
 
 // mode 0: ReLU, 1: GELU (erf)
+template <typename T>
 __global__ void __launch_bounds__(TF_THREADS)
-act_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t nvec, int mode) {
+act_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t nvec, int mode) {
   pdl_wait();      // programmatic dependent launch: see common.cuh
   pdl_trigger();
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8];
-    unpack8(ldg16(x + v * 8), f);
+    ld8(x + v * 8, f);
 #pragma unroll
     for (int e = 0; e < 8; ++e) f[e] = mode ? gelu_f(f[e]) : fmaxf(f[e], 0.f);
-    *reinterpret_cast<uint4*>(y + v * 8) = pack8(f);
+    st8(y + v * 8, f);
   }
 }
 // dx = dy * act'(x)   (x = pre-activation)
+template <typename T>
 __global__ void __launch_bounds__(TF_THREADS)
-act_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dx,
-               int64_t nvec, int mode) {
+act_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t nvec, int mode) {
   pdl_wait();      // programmatic dependent launch: see common.cuh
   pdl_trigger();
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8], g[8];
-    unpack8(ldg16(x + v * 8), f);
-    unpack8(ldg16(dy + v * 8), g);
+    ld8(x + v * 8, f);
+    ld8(dy + v * 8, g);
 #pragma unroll
     for (int e = 0; e < 8; ++e) g[e] *= mode ? gelu_grad(f[e]) : (f[e] > 0.f ? 1.f : 0.f);
-    *reinterpret_cast<uint4*>(dx + v * 8) = pack8(g);
+    st8(dx + v * 8, g);
   }
 }
 
 // y = dropout(x (+ x2)): inverted dropout, mask from drop_apply8 over the flattened tensor
+template <typename T>
 __global__ void __launch_bounds__(TF_THREADS)
-dropout_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2, __nv_bfloat16* __restrict__ y,
+dropout_kernel(const T* __restrict__ x, const T* __restrict__ x2, T* __restrict__ y,
                int64_t nvec, float p, uint64_t seed, uint32_t site, const uint32_t* __restrict__ step_dev) {
   pdl_wait();      // programmatic dependent launch: see common.cuh
   pdl_trigger();
   const DropKey key = make_drop_key(p, seed, site, step_dev);
   for (int64_t v = (int64_t)blockIdx.x * TF_THREADS + threadIdx.x; v < nvec; v += (int64_t)gridDim.x * TF_THREADS) {
     float f[8];
-    unpack8(ldg16(x + v * 8), f);
+    ld8(x + v * 8, f);
     if (x2) {
       float t[8];
-      unpack8(ldg16(x2 + v * 8), t);
+      ld8(x2 + v * 8, t);
 #pragma unroll
       for (int e = 0; e < 8; ++e) f[e] += t[e];
     }
     drop_apply8(key, v, f);
-    *reinterpret_cast<uint4*>(y + v * 8) = pack8(f);
+    st8(y + v * 8, f);
   }
 }
 
 // out[c][n] = sum_r x[c][r][n]: 32 row lanes x 8 column vectors per CTA, fixed summation order
+template <typename T>
 __global__ void __launch_bounds__(TF_THREADS)
-colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t R, int N, int64_t ldx, int64_t cs, float* __restrict__ out,
+colsum_kernel(const T* __restrict__ x, int64_t R, int N, int64_t ldx, int64_t cs, float* __restrict__ out,
               int64_t ld_o) {
   pdl_wait();      // programmatic dependent launch: see common.cuh
   pdl_trigger();
@@ -514,10 +528,10 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, int64_t R, int N, int64_t ldx
   const int col = blockIdx.x * 64 + tx * 8;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (col < N) {
-    const __nv_bfloat16* base = x + (size_t)c * cs + col;
+    const T* base = x + (size_t)c * cs + col;
     for (int64_t r = ty; r < R; r += 32) {
       float f[8];
-      unpack8(ldg16(base + (size_t)r * ldx), f);
+      ld8(base + (size_t)r * ldx, f);
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[e] += f[e];
     }
@@ -673,41 +687,74 @@ extern "C" int fb_attn_softmax_bwd(const float* dP, const void* P_bf16, void* dS
   return FB_OK;
 }
 
-extern "C" int fb_act_fwd(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
+template <typename T>
+static int act_fwd_impl(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
   FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(y),
              "fb_act_fwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
-  FB_CHECK_CUDA(fb_launch_pdl(act_fwd_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8, mode));
+  FB_CHECK_CUDA(fb_launch_pdl(act_fwd_kernel<T>, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)x, (T*)y, n / 8, mode));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+extern "C" int fb_act_fwd(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
+  return act_fwd_impl<__nv_bfloat16>(x, y, n, mode, stream);
+}
+extern "C" int fb_act_fwd_f32(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream) {
+  return act_fwd_impl<float>(x, y, n, mode, stream);
+}
 
-extern "C" int fb_act_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream) {
+template <typename T>
+static int act_bwd_impl(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream) {
   FB_REQUIRE(dy && x && dx && n >= 8 && n % 8 == 0 && (mode == 0 || mode == 1) && TF_ALIGNED16(x) && TF_ALIGNED16(dy) &&
                  TF_ALIGNED16(dx),
              "fb_act_bwd: n must be a multiple of 8, buffers 16-byte aligned, mode 0 (ReLU) or 1 (GELU)");
-  FB_CHECK_CUDA(fb_launch_pdl(act_bwd_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
-                                                                       (__nv_bfloat16*)dx, n / 8, mode));
+  FB_CHECK_CUDA(fb_launch_pdl(act_bwd_kernel<T>, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)dy, (const T*)x,
+                              (T*)dx, n / 8, mode));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
+extern "C" int fb_act_bwd(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream) {
+  return act_bwd_impl<__nv_bfloat16>(dy, x, dx, n, mode, stream);
+}
+extern "C" int fb_act_bwd_f32(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream) {
+  return act_bwd_impl<float>(dy, x, dx, n, mode, stream);
+}
 
+template <typename T>
+static int dropout_impl(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
+                        const uint32_t* step_dev, fb_stream_t stream) {
+  FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && p >= 0.f && p < 1.f && TF_ALIGNED16(x) && TF_ALIGNED16(x2) && TF_ALIGNED16(y),
+             "fb_dropout: n must be a multiple of 8, buffers 16-byte aligned, 0 <= p < 1");
+  FB_CHECK_CUDA(fb_launch_pdl(dropout_kernel<T>, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)x, (const T*)x2,
+                              (T*)y, n / 8, p, seed, site, step_dev));
+  FB_CHECK_CUDA(cudaGetLastError());
+  return FB_OK;
+}
 extern "C" int fb_dropout_bf16(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
                                const uint32_t* step_dev, fb_stream_t stream) {
-  FB_REQUIRE(x && y && n >= 8 && n % 8 == 0 && p >= 0.f && p < 1.f && TF_ALIGNED16(x) && TF_ALIGNED16(x2) && TF_ALIGNED16(y),
-             "fb_dropout_bf16: n must be a multiple of 8, buffers 16-byte aligned, 0 <= p < 1");
-  FB_CHECK_CUDA(fb_launch_pdl(dropout_kernel, dim3(ew_grid(n / 8)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)x2,
-                                                                       (__nv_bfloat16*)y, n / 8, p, seed, site, step_dev));
+  return dropout_impl<__nv_bfloat16>(x, x2, y, n, p, seed, site, step_dev, stream);
+}
+extern "C" int fb_dropout_f32(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
+                              const uint32_t* step_dev, fb_stream_t stream) {
+  return dropout_impl<float>(x, x2, y, n, p, seed, site, step_dev, stream);
+}
+
+template <typename T>
+static int colsum_impl(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
+                       int64_t ld_o, fb_stream_t stream) {
+  constexpr int A = 16 / (int)sizeof(T);      // elements per 16 bytes
+  FB_REQUIRE(x && out && C >= 1 && C <= 65535 && R >= 1 && N >= 8 && N % 8 == 0 && ldx % A == 0 && client_stride % A == 0 &&
+                 TF_ALIGNED16(x),
+             "fb_colsum: N a multiple of 8, row and client strides multiples of 16 bytes, x 16-byte aligned");
+  FB_CHECK_CUDA(fb_launch_pdl(colsum_kernel<T>, dim3(dim3((N + 63) / 64, C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const T*)x, R, N, ldx, client_stride,
+                              out, ld_o));
   FB_CHECK_CUDA(cudaGetLastError());
   return FB_OK;
 }
-
 extern "C" int fb_colsum_bf16(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
                               int64_t ld_o, fb_stream_t stream) {
-  FB_REQUIRE(x && out && C >= 1 && C <= 65535 && R >= 1 && N >= 8 && N % 8 == 0 && ldx % 8 == 0 && client_stride % 8 == 0 &&
-                 TF_ALIGNED16(x),
-             "fb_colsum_bf16: N, ldx and the client stride must be multiples of 8, x 16-byte aligned");
-  FB_CHECK_CUDA(fb_launch_pdl(colsum_kernel, dim3(dim3((N + 63) / 64, C)), dim3(TF_THREADS), (size_t)(0), (cudaStream_t)stream, (const __nv_bfloat16*)x, R, N, ldx, client_stride,
-                                                                              out, ld_o));
-  FB_CHECK_CUDA(cudaGetLastError());
-  return FB_OK;
+  return colsum_impl<__nv_bfloat16>(x, C, R, N, ldx, client_stride, out, ld_o, stream);
+}
+extern "C" int fb_colsum_f32(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
+                             int64_t ld_o, fb_stream_t stream) {
+  return colsum_impl<float>(x, C, R, N, ldx, client_stride, out, ld_o, stream);
 }

@@ -303,6 +303,29 @@ class TorchBackend:
         out.copy_(x.float().sum(dim=1))
         return out
 
+    def maxpool2x2_fwd(self, x, off=(0, 0), out_hw=None):
+        """x [C,B,H,W,ch] -> [C,B,Ho,Wo,ch], windows starting at ``off`` (the centre crop of a same-padded conv output)."""
+        C, B, H, W, ch = x.shape
+        Ho, Wo = out_hw or ((H - off[0]) // 2, (W - off[1]) // 2)
+        xw = x[:, :, off[0]:off[0] + 2 * Ho, off[1]:off[1] + 2 * Wo, :]
+        return xw.reshape(C, B, Ho, 2, Wo, 2, ch).amax(dim=(3, 5))
+
+    def maxpool2x2_bwd(self, dy, x, off=(0, 0), relu_mask=False):
+        """dy to the first maximal element of every window (scan order), zero elsewhere and outside the windows."""
+        C, B, H, W, ch = x.shape
+        Ho, Wo = dy.shape[2], dy.shape[3]
+        xw = x[:, :, off[0]:off[0] + 2 * Ho, off[1]:off[1] + 2 * Wo, :].reshape(C, B, Ho, 2, Wo, 2, ch)
+        win = xw.permute(0, 1, 2, 4, 6, 3, 5).reshape(C, B, Ho, Wo, ch, 4).float()
+        idx = win.argmax(dim=-1, keepdim=True)                          # first occurrence
+        d = dy.float()
+        if relu_mask:
+            d = d * (win.gather(-1, idx).squeeze(-1) > 0)
+        dwin = torch.zeros_like(win).scatter_(-1, idx, d.unsqueeze(-1))
+        dxw = dwin.reshape(C, B, Ho, Wo, ch, 2, 2).permute(0, 1, 2, 5, 3, 6, 4).reshape(C, B, 2 * Ho, 2 * Wo, ch)
+        dx = torch.zeros(C, B, H, W, ch, dtype=x.dtype, device=x.device)
+        dx[:, :, off[0]:off[0] + 2 * Ho, off[1]:off[1] + 2 * Wo, :] = dxw.to(x.dtype)
+        return dx
+
 
 class NativeBackend(TorchBackend):
     """sm_100a kernels for the bandwidth-bound primitives; GEMMs go to the tcgen05 grouped GEMM when
@@ -529,7 +552,7 @@ class NativeBackend(TorchBackend):
     def dropout(self, x, p, seed, site, step_dev=None, x2=None):
         if p <= 0 and x2 is None:
             return x
-        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+        if x.dtype in self._ACT and x.numel() % 8 == 0:
             return self._tf().dropout(x, p, seed, site, step_dev, x2)
         self._fb("dropout")
         return super().dropout(x, p, seed, site, step_dev, x2)
@@ -549,22 +572,34 @@ class NativeBackend(TorchBackend):
         return super().softmax_bwd(dP, P, scale, p, seed, site, step_dev)
 
     def act_fwd(self, x, kind):
-        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+        if x.dtype in self._ACT and x.numel() % 8 == 0:
             return self._tf().act_fwd(x, kind)
         self._fb("act_fwd")
         return super().act_fwd(x, kind)
 
     def act_bwd(self, dy, x, kind):
-        if x.dtype == torch.bfloat16 and x.numel() % 8 == 0:
+        if x.dtype in self._ACT and x.numel() % 8 == 0 and dy.dtype == x.dtype:
             return self._tf().act_bwd(dy, x, kind)
         self._fb("act_bwd")
         return super().act_bwd(dy, x, kind)
 
     def colsum(self, x, out):
-        if x.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0:
+        if x.dtype in self._ACT and x.shape[-1] % 8 == 0:
             return self._tf().colsum(x, out)
         self._fb("colsum")
         return super().colsum(x, out)
+
+    def maxpool2x2_fwd(self, x, off=(0, 0), out_hw=None):
+        if x.dtype in self._ACT and x.shape[-1] % 8 == 0:
+            return self.ops.maxpool2x2_fwd(x, off, out_hw)
+        self._fb("maxpool_fwd")
+        return super().maxpool2x2_fwd(x, off, out_hw)
+
+    def maxpool2x2_bwd(self, dy, x, off=(0, 0), relu_mask=False):
+        if x.dtype in self._ACT and x.shape[-1] % 8 == 0 and dy.dtype == x.dtype:
+            return self.ops.maxpool2x2_bwd(dy, x, off, relu_mask)
+        self._fb("maxpool_bwd")
+        return super().maxpool2x2_bwd(dy, x, off, relu_mask)
 
 
 # ============================================================================ layers
@@ -1081,6 +1116,10 @@ def make_batched(module: nn.Module, backend: TorchBackend) -> Optional[BatchedMo
             return BatchedResNet(module, backend)
         except NotImplementedError:
             return None
+    from .cv import CNN_DropOut
+    if isinstance(module, CNN_DropOut):
+        from .batched_cnn import BatchedCNNDropOut
+        return BatchedCNNDropOut(module, backend)
     from .nlp import DistilBertForSequenceClassification
     if isinstance(module, DistilBertForSequenceClassification):
         from .batched_nlp import BatchedDistilBert

@@ -489,6 +489,31 @@ def col2im3x3(dcols, B, H, W, ch, stride):
     return dx
 
 
+def maxpool2x2_fwd(x, off=(0, 0), out_hw=None):
+    """x [C,B,H,W,ch] bf16 / fp32 -> [C,B,Ho,Wo,ch]; windows start at ``off`` (see fb_maxpool2x2_fwd)."""
+    Cn, B, H, W, ch = x.shape
+    Ho, Wo = out_hw or ((H - off[0]) // 2, (W - off[1]) // 2)
+    x = x.contiguous()
+    y = torch.empty((Cn, B, Ho, Wo, ch), dtype=x.dtype, device=x.device)
+    check(lib().fb_maxpool2x2_fwd(vp(ptr(x)), vp(ptr(y)), i32(int(x.dtype == torch.float32)), i32(Cn * B), i32(H), i32(W), i32(ch),
+                                  i32(off[0]), i32(off[1]), i32(Ho), i32(Wo), vp(stream_ptr(x.device))), "maxpool2x2_fwd")
+    count_launch()
+    return y
+
+
+def maxpool2x2_bwd(dy, x, off=(0, 0), relu_mask=False):
+    """Gradient of :func:`maxpool2x2_fwd` w.r.t. the whole map x (zero outside the pooled windows)."""
+    Cn, B, H, W, ch = x.shape
+    Ho, Wo = dy.shape[2], dy.shape[3]
+    dy, x = dy.contiguous(), x.contiguous()
+    dx = torch.empty_like(x)
+    check(lib().fb_maxpool2x2_bwd(vp(ptr(dy)), vp(ptr(x)), vp(ptr(dx)), i32(int(x.dtype == torch.float32)), i32(Cn * B), i32(H), i32(W),
+                                  i32(ch), i32(off[0]), i32(off[1]), i32(Ho), i32(Wo), i32(int(relu_mask)), vp(stream_ptr(x.device))),
+          "maxpool2x2_bwd")
+    count_launch()
+    return dx
+
+
 # --------------------------------------------------------------------------- K9 grouped GEMM (tcgen05 / TMEM / TMA)
 from .native import FbGroupedGemm  # noqa: E402
 

@@ -227,7 +227,8 @@ _ACT = {"relu": 0, "gelu": 1}
 def act_fwd(x: torch.Tensor, kind: str) -> torch.Tensor:
     x = x.contiguous()
     y = torch.empty_like(x)
-    check(lib().fb_act_fwd(vp(ptr(x)), vp(ptr(y)), i64(x.numel()), i32(_ACT[kind]), vp(stream_ptr(x.device))), "act_fwd")
+    fn = lib().fb_act_fwd_f32 if x.dtype == torch.float32 else lib().fb_act_fwd
+    check(fn(vp(ptr(x)), vp(ptr(y)), i64(x.numel()), i32(_ACT[kind]), vp(stream_ptr(x.device))), "act_fwd")
     count_launch()
     return y
 
@@ -235,8 +236,8 @@ def act_fwd(x: torch.Tensor, kind: str) -> torch.Tensor:
 def act_bwd(dy: torch.Tensor, x: torch.Tensor, kind: str) -> torch.Tensor:
     dy, x = dy.contiguous(), x.contiguous()
     dx = torch.empty_like(x)
-    check(lib().fb_act_bwd(vp(ptr(dy)), vp(ptr(x)), vp(ptr(dx)), i64(x.numel()), i32(_ACT[kind]), vp(stream_ptr(x.device))),
-          "act_bwd")
+    fn = lib().fb_act_bwd_f32 if x.dtype == torch.float32 else lib().fb_act_bwd
+    check(fn(vp(ptr(dy)), vp(ptr(x)), vp(ptr(dx)), i64(x.numel()), i32(_ACT[kind]), vp(stream_ptr(x.device))), "act_bwd")
     count_launch()
     return dx
 
@@ -247,8 +248,9 @@ def dropout(x: torch.Tensor, p: float, seed: int, site: int, step_dev: Optional[
     x = x.contiguous()
     x2 = x2.contiguous() if x2 is not None else None
     y = torch.empty_like(x)
-    check(lib().fb_dropout_bf16(vp(ptr(x)), vp(ptr(x2)), vp(ptr(y)), i64(x.numel()), f32(p), _key(seed), u32(site & 0xFFFFFFFF),
-                                vp(ptr(step_dev)), vp(stream_ptr(x.device))), "dropout")
+    fn = lib().fb_dropout_f32 if x.dtype == torch.float32 else lib().fb_dropout_bf16
+    check(fn(vp(ptr(x)), vp(ptr(x2)), vp(ptr(y)), i64(x.numel()), f32(p), _key(seed), u32(site & 0xFFFFFFFF),
+             vp(ptr(step_dev)), vp(stream_ptr(x.device))), "dropout")
     count_launch()
     return y
 
@@ -257,11 +259,12 @@ def colsum(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     """out[c, :] = x[c].sum(0) for bf16 x [C, R, N] (rows may be strided, e.g. a column block of a wider buffer);
     ``out`` fp32 [C, N] (may be rows of the gradient arena)."""
     Cn, R, Nn = x.shape
-    if x.stride(2) != 1 or x.stride(1) % 8 or (Cn > 1 and x.stride(0) % 8) or x.data_ptr() % 16:
+    al = 16 // x.element_size()
+    if x.stride(2) != 1 or x.stride(1) % al or (Cn > 1 and x.stride(0) % al) or x.data_ptr() % 16:
         x = x.contiguous()
     ld_o = out.stride(0) if Cn > 1 else max(out.stride(0), Nn)
     cs = x.stride(0) if Cn > 1 else R * x.stride(1)
-    check(lib().fb_colsum_bf16(vp(ptr(x)), i32(Cn), i64(R), i32(Nn), i64(x.stride(1)), i64(cs), vp(ptr(out)), i64(ld_o),
-                               vp(stream_ptr(x.device))), "colsum")
+    fn = lib().fb_colsum_f32 if x.dtype == torch.float32 else lib().fb_colsum_bf16
+    check(fn(vp(ptr(x)), i32(Cn), i64(R), i32(Nn), i64(x.stride(1)), i64(cs), vp(ptr(out)), i64(ld_o), vp(stream_ptr(x.device))), "colsum")
     count_launch()
     return out

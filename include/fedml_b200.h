@@ -381,6 +381,13 @@ int fb_dropout_bf16(const void* x, const void* x2, void* y, int64_t n, float p, 
 /* bias gradients: out[c][n] = sum_r x[c][r][n], x bf16 rows of stride ldx, clients client_stride apart */
 int fb_colsum_bf16(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
                    int64_t ld_o, fb_stream_t stream);
+/* fp32 forms of the four element-wise kernels above (tf32 / fp32 activation pipelines, e.g. the FEMNIST CNN). */
+int fb_act_fwd_f32(const void* x, void* y, int64_t n, int32_t mode, fb_stream_t stream);
+int fb_act_bwd_f32(const void* dy, const void* x, void* dx, int64_t n, int32_t mode, fb_stream_t stream);
+int fb_dropout_f32(const void* x, const void* x2, void* y, int64_t n, float p, uint64_t seed, uint32_t site,
+                   const uint32_t* step_dev, fb_stream_t stream);
+int fb_colsum_f32(const void* x, int32_t C, int64_t R, int32_t N, int64_t ldx, int64_t client_stride, float* out,
+                  int64_t ld_o, fb_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * K10 helpers: NHWC im2col / col2im for 3x3 convolutions batched over clients, fused per-client
@@ -477,6 +484,15 @@ int fb_stage_conv_weights_f32(const float* arena, int64_t ld, int32_t C, void* s
 int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, const float* scratch, int64_t scratch_ld,
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
+
+/* 2x2 / stride-2 max pooling on NHWC bf16 or fp32 (act_fp32) maps [n_img][H][W][ch], ch a multiple of 8.  The pooled
+ * windows start at (off_h, off_w): y [n_img][Ho][Wo][ch] = max of x[off_h + 2i + {0,1}][off_w + 2j + {0,1}].  Backward
+ * writes the whole dx [n_img][H][W][ch] (zero outside the windows), routes dy to the first maximal element of a window and,
+ * with relu_mask, drops it where that maximum is <= 0.  Reference: nn.MaxPool2d(2, 2) in model/cv/cnn.py:74-142. */
+int fb_maxpool2x2_fwd(const void* x, void* y, int32_t act_fp32, int32_t n_img, int32_t H, int32_t W, int32_t ch,
+                      int32_t off_h, int32_t off_w, int32_t Ho, int32_t Wo, fb_stream_t stream);
+int fb_maxpool2x2_bwd(const void* dy, const void* x, void* dx, int32_t act_fp32, int32_t n_img, int32_t H, int32_t W,
+                      int32_t ch, int32_t off_h, int32_t off_w, int32_t Ho, int32_t Wo, int32_t relu_mask, fb_stream_t stream);
 
 /* GroupNorm (+residual, +ReLU) forward / backward for client-stacked conv nets, on the BatchNorm kernels: a row is one
  * (client, sample), rows = C*B, M = H*W pixels, statistics pool `cpg` adjacent channels of a row (reference

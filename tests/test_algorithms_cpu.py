@@ -179,6 +179,25 @@ def test_nccl_simulator_distilbert_batched_cpu_and_sequential_fallback_agree():
         torch.testing.assert_close(w_b[k].float(), w_s[k].float(), rtol=5e-3, atol=5e-5, msg=lambda m, k=k: f"{k}: {m}")
 
 
+def test_nccl_simulator_femnist_cnn_batched_cpu_and_sequential_fallback_agree():
+    """FEMNIST CNN_DropOut (reference model/cv/cnn.py:74-142): the client-batched executor and per-client eager training give
+    the same global model when dropout is off."""
+    kw = dict(dataset="femnist", model="cnn", client_num_in_total=4, client_num_per_round=2, synthetic_train_size=80,
+              batch_size=8, comm_round=1, frequency_of_the_test=100, backend="NCCL", shuffle_clients=False)
+    a = mk(**kw)
+    ds, out = fedml.data.load(a)
+    torch.manual_seed(0)
+    model = fedml.model.create(a, out)
+    model.dropout_1.p = model.dropout_2.p = 0.0
+    sim_b = SimulatorNCCL(a, CPU, ds, copy.deepcopy(model))
+    assert type(sim_b.simulator.batched).__name__ == "BatchedCNNDropOut"
+    w_b = sim_b.run()
+    a2 = copy.copy(a); a2.batched_clients = False
+    w_s = SimulatorNCCL(a2, CPU, ds, copy.deepcopy(model)).run()
+    for k in w_b:
+        torch.testing.assert_close(w_b[k].float(), w_s[k].float(), rtol=5e-3, atol=5e-5, msg=lambda m, k=k: f"{k}: {m}")
+
+
 def test_nccl_simulator_two_ranks_gloo_is_g_invariant(tmp_path):
     """world_size 2 over gloo on CPU == world_size 1 (same seeds => same sampled clients => same global model)."""
     script = tmp_path / "w.py"

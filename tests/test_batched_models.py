@@ -224,3 +224,57 @@ def test_batched_groupnorm_resnet_matches_autograd():
         m.eval()
         xin = (x_u8[c].permute(0, 3, 1, 2).float() / 255.0 - mean) / std
         torch.testing.assert_close(lg[c], m(xin), rtol=1e-3, atol=1e-4)
+
+
+def _cnn(p1=0.0, p2=0.0, only_digits=False):
+    from fedml_b200.models.cv import CNN_DropOut
+    m = CNN_DropOut(only_digits=only_digits)
+    m.dropout_1.p, m.dropout_2.p = p1, p2
+    return m
+
+
+def test_batched_cnn_dropout_matches_autograd():
+    """FEMNIST CNN (reference model/cv/cnn.py:74-142): valid convolutions as centre crops of same-padded ones, pooling with
+    a window offset, (h, w, c)-ordered fc staging - gradients equal per-client autograd when dropout is off."""
+    C, B = 3, 5
+    models, layout, stack = _stack_clients(lambda: _cnn(), C, seed=5)
+    gstack = torch.zeros_like(stack)
+    bm = make_batched(models[0], TorchBackend(torch.float32))
+    assert type(bm).__name__ == "BatchedCNNDropOut"
+    x = torch.randn(C, B, 784); y = torch.randint(0, 62, (C, B)); y[1, -1] = -1          # one padded row
+    W, G = layout.stacked_views(stack), layout.stacked_views(gstack)
+    loss = bm.train_step(x, y, W, G, torch.ones(C))
+    for c, m in enumerate(models):
+        m.train()
+        keep = y[c] >= 0
+        l = F.cross_entropy(m(x[c][keep]), y[c][keep], reduction="sum") / B
+        m.zero_grad(); l.backward()
+        assert abs(float(loss[c]) - float(l)) < 1e-5
+        for k, p in m.named_parameters():
+            torch.testing.assert_close(G[k][c], p.grad, rtol=2e-4, atol=2e-6, msg=k)
+    with torch.no_grad():
+        torch.testing.assert_close(bm.logits(x, W)[0], models[0].eval()(x[0]), rtol=1e-4, atol=1e-5)
+
+
+def test_batched_cnn_dropout_masks_are_consistent():
+    """Dropout on: the backward pass re-derives the forward's masks (finite-difference probe along the gradient)."""
+    C, B = 2, 4
+    models, layout, stack = _stack_clients(lambda: _cnn(0.25, 0.5, True), C, seed=6)
+    gstack = torch.zeros_like(stack)
+    bm = make_batched(models[0], TorchBackend(torch.float32))
+    x = torch.randn(C, B, 28, 28); y = torch.randint(0, 10, (C, B))
+    l0 = bm.train_step(x, y, layout.stacked_views(stack), layout.stacked_views(gstack), torch.ones(C))
+    step = int(bm._step_dev.item())
+    direction = gstack / gstack.norm()
+    eps = 1e-2
+
+    def probe(sign):
+        bm._step_dev.fill_(step - 1)
+        return bm.train_step(x, y, layout.stacked_views(stack + sign * eps * direction),
+                             layout.stacked_views(torch.zeros_like(gstack)), torch.ones(C)).double().sum()
+
+    fd = float(probe(+1) - probe(-1)) / (2 * eps)
+    an = float((gstack.double() * direction.double()).sum())
+    assert an > 0 and abs(fd - an) < 0.05 * an, (fd, an)
+    l1 = bm.train_step(x, y, layout.stacked_views(stack), layout.stacked_views(gstack), torch.ones(C))
+    assert not torch.equal(l0, l1)                     # next step, new masks
