@@ -6,7 +6,9 @@ For each (model size P, clients per round K, algorithm) it times, on the device 
   nccl    — the "baseline, not the product": local weighted sum with torch ops, dist.all_reduce (NCCL), torch
             server-optimizer step (what a straightforward NCCL simulator does);
 and reports the roofline fraction of the fused path: roofline time = max(local HBM bytes / 6428 GB/s,
-NVLink bytes in+out per GPU / 770 GB/s per direction).
+NVLink bytes in+out per GPU / link peak per direction).  The link peak is MEASURED on the box first (``LINK`` line): every
+rank copies 256 MiB out of the next rank's peer-mapped buffer with a plain device copy (ordinary loads over NVLink, all ranks
+at once); 770 GB/s is only the fallback when there is a single rank.
 """
 import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -26,6 +28,31 @@ def main():
             ("resnet18_fedadam_dp_aggnoise", 11191264, 512, "adam", "agg"), ("distilbert_fedavg", 66968852 // 4 * 4, 256, "none", False)]
     out = []
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    global NVL
+    if world > 1:
+        from fedml_b200.parallel.symmetric import SymmetricRegion, _RawCudaBuffer
+        nb = 256 << 20
+        reg = SymmetricRegion(nb + 4096, dev)
+        reg.carve("buf", nb)
+        reg.tensor("buf", torch.uint8).fill_(rank + 1)
+        reg.barrier()
+        peer = torch.as_tensor(_RawCudaBuffer(reg.peer_ptr("buf", (rank + 1) % world), nb), device=dev)
+        dst = torch.empty(nb, dtype=torch.uint8, device=dev)
+        for _ in range(2):
+            dst.copy_(peer)
+        ts = []
+        for _ in range(5):
+            torch.cuda.synchronize(); dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); dst.copy_(peer); e1.record(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); ts.append(float(t))
+        assert int(dst[12345]) == (rank + 1) % world + 1
+        NVL = nb / (sorted(ts)[2] * 1e-3)
+        if rank == 0:
+            print("LINK " + json.dumps({"G": world, "peer_copy_GBps_per_dir": round(NVL / 1e9, 1), "bytes": nb,
+                                        "how": "dst.copy_(peer-mapped buffer of rank+1), all ranks at once, median of 5, max over ranks"}), flush=True)
+        reg.barrier()
+        del reg, peer, dst
     for name, P, K, opt, dp in cfgs:
         C = max(1, K // world)
         layout = type("L", (), {"P": P, "P_train": P})()
@@ -116,7 +143,7 @@ def main():
                 out.append({"config": name, "G": world, "mode": "two_shot" if two_shot else "one_shot",
                             "multicast": bool(eng._mc_partial) and two_shot, "fused_ms": round(ms, 4),
                             "nccl_allreduce_ms": round(sorted(tn)[2], 4), "nvlink_GBps_per_dir": round(nvl_bytes / ms / 1e6, 1),
-                            "roofline_frac_of_770": round(nvl_bytes / NVL * 1e3 / ms, 3)})
+                            "frac_of_measured_link": round(nvl_bytes / NVL * 1e3 / ms, 3)})
                 del eng
                 torch.cuda.empty_cache()
     if rank == 0:
