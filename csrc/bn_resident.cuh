@@ -11,6 +11,7 @@
 #pragma once
 
 #define BNR_CHUNK 16384u       // bytes per bulk copy
+#define BNR_MAX_CHUNKS 8        // chunks (and mbarriers) a slice is cut into by the chunk-pipelined forward kernel
 
 __device__ __forceinline__ uint32_t bnr_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void bnr_mbar_init(uint64_t* bar, uint32_t count) {
@@ -58,6 +59,24 @@ __device__ __forceinline__ void bnr_store_slice(void* dst, const void* src_smem,
     bnr_bulk_store((char*)dst + off, (const char*)src_smem + off, min(BNR_CHUNK, bytes - off));
 }
 
+// Optional per-CTA timeline (tools/trace_bn.py): when a trace buffer is registered, thread 0 of every forward CTA stores
+// globaltimer stamps [start, loaded, stats, barrier, coeffs, applied, stored, smid] at row blockIdx.y * gridDim.x + blockIdx.x.
+static __device__ unsigned long long* g_bn_trace = nullptr;
+// FB_BN_CHUNKS: chunks per slice.  ResNet-56 tf32 round with 1 / 2 / 4 / 8 chunks: 99.6 / 99.1 / 99.8 / 101.0 ms
+static __device__ unsigned g_bn_chunks = 2;
+__device__ __forceinline__ void bnr_stamp(int slot) {
+  if (g_bn_trace && threadIdx.x == 0) {
+    unsigned long long* row = g_bn_trace + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 8;
+    if (slot == 7) {
+      unsigned sm;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+      row[7] = sm;
+    } else {
+      row[slot] = fb_globaltimer();
+    }
+  }
+}
+
 template <typename T> struct Vec16 { static constexpr int N = 16 / (int)sizeof(T); };
 __device__ __forceinline__ void unpack16(const uint4& r, float* f, const __nv_bfloat16*) {
   const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
@@ -103,6 +122,32 @@ __device__ __forceinline__ void bnr_reduce(const float* a, const float* b, int c
   __syncthreads();
 }
 
+// Barrier among the S CTAs of a client, split into arrive / wait, one global round trip each on the critical path
+// (the generation barrier of the fused kernels costs ~4.9 us per CTA in tools/trace_bn.py: fence, generation load, atomic
+// with return, polling with sleep, fence).  {count, seen} per client: a CTA arrives with a release reduction (no return
+// value), waits until count >= S, and when it is done with the barrier adds itself to `seen`; the CTA that makes
+// seen == S resets both words, so the state is zero again when the kernel ends (the next launch is stream-ordered).
+static __device__ unsigned g_bn_barrier2[2 * 65536];
+__device__ __forceinline__ void client_arrive(int S, int idx) {          // one thread, after the CTA's partials are written
+  if (S > 1) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(g_bn_barrier2 + 2 * idx) : "memory");
+}
+__device__ __forceinline__ void client_wait(int S, int idx) {            // one thread
+  if (S > 1) {
+    const unsigned* st = g_bn_barrier2 + 2 * idx;
+    while (ld_acquire_gpu(st) < (unsigned)S) {
+    }
+  }
+}
+__device__ __forceinline__ void client_leave(int S, int idx) {           // one thread, any time after its client_wait
+  if (S > 1) {
+    unsigned* st = g_bn_barrier2 + 2 * idx;
+    if (atomicAdd(st + 1, 1u) == (unsigned)S - 1) {
+      st[0] = 0;
+      st[1] = 0;
+    }
+  }
+}
+
 // The client's S partial rows [S][2*ch] (L2, written by the sibling CTAs) -> complete sums [2*ch] in shared memory, with
 // every thread loading: a column is shared by BN_THREADS / (2*ch) threads that take every other row, eight loads in flight
 // each (the per-channel loop of the fused kernels walks S rows one after the other: 55 dependent L2 round trips at S = 55).
@@ -113,12 +158,19 @@ __device__ __forceinline__ void bnr_sum_partials(const float* part, int S, int c
     for (int col = tid; col < cols; col += BN_THREADS) {
       float acc = 0.f;
       int j = 0;
-      for (; j + 8 <= S; j += 8) {
-        float v[8];
+      for (; j + 16 <= S; j += 16) {
+        float v[16];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
+        for (int u = 0; u < 16; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
 #pragma unroll
-        for (int u = 0; u < 8; ++u) acc += v[u];
+        for (int u = 0; u < 16; ++u) acc += v[u];
+      }
+      for (; j + 4 <= S; j += 4) {
+        float v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc += v[u];
       }
       for (; j < S; ++j) acc += __ldcg(part + (size_t)j * cols + col);
       sums[col] = acc;
@@ -127,12 +179,19 @@ __device__ __forceinline__ void bnr_sum_partials(const float* part, int S, int c
     const int groups = BN_THREADS / cols, col = tid % cols, grp = tid / cols;
     float acc = 0.f;
     int j = grp;
-    for (; j + 7 * groups < S; j += 8 * groups) {
-      float v[8];
+    for (; j + 15 * groups < S; j += 16 * groups) {
+      float v[16];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
+      for (int u = 0; u < 16; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc += v[u];
+      for (int u = 0; u < 16; ++u) acc += v[u];
+    }
+    for (; j + 3 * groups < S; j += 4 * groups) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc += v[u];
     }
     for (; j < S; j += groups) acc += __ldcg(part + (size_t)j * cols + col);
     red[tid] = acc;
@@ -156,7 +215,7 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
                        float* num_batches_tracked, int64_t ld_n, int res_smem /* the residual slice is resident too */, int bar_base) {
   constexpr int N = Vec16<T>::N;
   extern __shared__ __align__(128) unsigned char dsm[];
-  __shared__ __align__(8) uint64_t bar;
+  __shared__ __align__(8) uint64_t bar[BNR_MAX_CHUNKS];
   uint4* xs = reinterpret_cast<uint4*>(dsm);
   uint4* rs = reinterpret_cast<uint4*>(dsm + slice_cap);
   float* coef = reinterpret_cast<float*>(dsm + (size_t)(1 + res_smem) * slice_cap);
@@ -166,94 +225,165 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
   const int64_t r0 = min(M, (int64_t)s * rows_per), r1 = min(M, r0 + rows_per);
   const uint32_t bytes = (uint32_t)((r1 - r0) * ch * (int64_t)sizeof(T));
   const size_t goff = ((size_t)c * M + r0) * ch;
-  if (tid == 0) bnr_mbar_init(&bar, 1);
+  // the slice moves in <= BNR_MAX_CHUNKS chunks of a multiple of 4 KiB (256 threads x 16 bytes, so a thread keeps its
+  // channels from chunk to chunk): statistics start on chunk 0 while the rest is still in flight, and chunk i of the
+  // output is stored while chunk i + 1 is being computed
+  const uint32_t want_chunks = g_bn_chunks;
+  const uint32_t chunk = ((bytes + want_chunks - 1) / want_chunks + 4095u) / 4096u * 4096u;
+  const int nchunks = bytes ? (int)((bytes + chunk - 1) / chunk) : 0;
+  if (tid < BNR_MAX_CHUNKS) bnr_mbar_init(bar + tid, 1);
   __syncthreads();
   pdl_wait();
   pdl_trigger();
-  if (tid < 32) {
-    if (tid == 0) bnr_mbar_expect_tx(&bar, bytes * (uint32_t)(1 + res_smem));
-    __syncwarp();
-    bnr_load_slice(xs, x + goff, bytes, &bar);
-    if (res_smem) bnr_load_slice(rs, res + goff, bytes, &bar);
+  bnr_stamp(0);
+  bnr_stamp(7);
+  if (tid < nchunks) {
+    const uint32_t off = (uint32_t)tid * chunk, nb = min(chunk, bytes - off);
+    bnr_mbar_expect_tx(bar + tid, nb * (uint32_t)(1 + res_smem));
+    bnr_bulk_load((char*)xs + off, (const char*)(x + goff) + off, nb, bar + tid);
+    if (res_smem) bnr_bulk_load((char*)rs + off, (const char*)(res + goff) + off, nb, bar + tid);
   }
-  const int nvec = (int)(bytes / 16u);
+  const int nvec = (int)(bytes / 16u), cvec = (int)(chunk / 16u);
   const int coff = (tid * N) % ch;
-  bnr_mbar_wait(&bar, 0);
   float a[N], b[N];
 #pragma unroll
   for (int i = 0; i < N; ++i) a[i] = b[i] = 0.f;
-  for (int v = tid; v < nvec; v += BN_THREADS) {
-    float f[N];
-    unpack16(xs[v], f, (const T*)nullptr);
+  for (int k = 0; k < nchunks; ++k) {
+    bnr_mbar_wait(bar + k, 0);
+    const int v1 = min(nvec, (k + 1) * cvec);
+    for (int v = k * cvec + tid; v < v1; v += BN_THREADS) {
+      float f[N];
+      unpack16(xs[v], f, (const T*)nullptr);
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-      a[i] += f[i];
-      b[i] += f[i] * f[i];
+      for (int i = 0; i < N; ++i) {
+        a[i] += f[i];
+        b[i] += f[i] * f[i];
+      }
     }
   }
+  bnr_stamp(1);
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
-  client_barrier(S, bar_base);
-  bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 2 * ch);
-  bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
-                 save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S, coef + 2 * ch);
+  bnr_stamp(2);
+  if (tid == 0) client_arrive(S, bar_base + c);
+  // nothing below depends on the barrier until the partial sums are read: fetch the per-channel inputs of the
+  // coefficients and the first residual vectors while the siblings arrive
+  const bool one_k = ch <= BN_THREADS, mine = one_k && tid < ch;
+  float pg = 0.f, pb = 0.f, prm = 0.f, prv = 0.f, pact = 1.f;
+  if (mine) {
+    pg = gamma[(size_t)c * ld_p + tid];
+    pb = beta[(size_t)c * ld_p + tid];
+    pact = active ? active[c] : 1.f;
+    if (s == 0) {
+      prm = running_mean[(size_t)c * ld_r + tid];
+      prv = running_var[(size_t)c * ld_r + tid];
+    }
+  }
+  const bool res_g = res && !res_smem;
+  const uint4* rg = reinterpret_cast<const uint4*>(res + goff);
+  constexpr int RU = 4;                       // residual vectors per thread and chunk round (cvec = RU * 256 at 16 KiB chunks)
+  uint4 rq[RU];
+#pragma unroll
+  for (int u = 0; u < RU; ++u) rq[u] = make_uint4(0, 0, 0, 0);
+  if (res_g) {
+#pragma unroll
+    for (int u = 0; u < RU; ++u) {
+      const int v = tid + u * BN_THREADS;
+      if (v < min(nvec, cvec) && u * BN_THREADS < cvec) rq[u] = __ldg(rg + v);
+    }
+  }
+  if (tid == 0) client_wait(S, bar_base + c);
   __syncthreads();
+  bnr_stamp(3);
+  bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 2 * ch);
+  if (one_k) {
+    if (mine) {
+      const float su = coef[2 * ch + tid], sq = coef[3 * ch + tid];
+      const float mean = su / (float)M, var = fmaxf(sq / (float)M - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      if (s == 0) {
+        if (pact != 0.f) {
+          const float unbiased = var * ((float)M / (float)max((int64_t)1, M - 1));
+          running_mean[(size_t)c * ld_r + tid] = prm + momentum * pact * (mean - prm);
+          running_var[(size_t)c * ld_r + tid] = prv + momentum * pact * (unbiased - prv);
+        }
+        if (save_mean) {
+          save_mean[(size_t)c * ch + tid] = mean;
+          save_rstd[(size_t)c * ch + tid] = rstd;
+        }
+        if (tid == 0 && num_batches_tracked) num_batches_tracked[(size_t)c * ld_n] += pact;
+      }
+      const float g = pg * rstd;
+      coef[tid] = g;
+      coef[ch + tid] = pb - mean * g;
+    }
+  } else {
+    bn_scale_shift(M, ch, partial, gamma, beta, ld_p, running_mean, running_var, ld_r, active, momentum, eps, 1, save_mean,
+                   save_rstd, num_batches_tracked, ld_n, coef, coef + ch, S, coef + 2 * ch);
+  }
+  __syncthreads();
+  bnr_stamp(4);
   float sc[N], sh[N];
 #pragma unroll
   for (int i = 0; i < N; ++i) {
     sc[i] = coef[coff + i];
     sh[i] = coef[ch + coff + i];
   }
-  if (res && res_smem) {
-    for (int v = tid; v < nvec; v += BN_THREADS) {
-      float f[N], q[N];
-      unpack16(xs[v], f, (const T*)nullptr);
-      unpack16(rs[v], q, (const T*)nullptr);
+  for (int k = 0; k < nchunks; ++k) {
+    const int v0 = k * cvec, v1 = min(nvec, v0 + cvec);
+    for (int vb = v0; vb < v1; vb += RU * BN_THREADS) {        // one round = RU vectors per thread
+      uint4 rn[RU];
 #pragma unroll
-      for (int i = 0; i < N; ++i) {
-        f[i] = f[i] * sc[i] + sh[i] + q[i];
-        if (relu) f[i] = fmaxf(f[i], 0.f);
-      }
-      xs[v] = pack16(f, (const T*)nullptr);
-    }
-  } else if (res) {
-    const uint4* rg = reinterpret_cast<const uint4*>(res + goff);
-    for (int v = tid; v < nvec; v += 4 * BN_THREADS) {        // four residual vectors in flight per thread
-      uint4 r[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) r[u] = (v + u * BN_THREADS < nvec) ? __ldg(rg + v + u * BN_THREADS) : make_uint4(0, 0, 0, 0);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int vv = v + u * BN_THREADS;
-        if (vv >= nvec) break;
-        float f[N], q[N];
-        unpack16(xs[vv], f, (const T*)nullptr);
-        unpack16(r[u], q, (const T*)nullptr);
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-          f[i] = f[i] * sc[i] + sh[i] + q[i];
-          if (relu) f[i] = fmaxf(f[i], 0.f);
+      for (int u = 0; u < RU; ++u) rn[u] = make_uint4(0, 0, 0, 0);
+      if (res_g) {                                               // residual of the next round: in flight during this one
+        int nb = vb + RU * BN_THREADS, ne = v1;
+        if (nb >= v1) {
+          nb = v1;                                               // first round of the next chunk
+          ne = min(nvec, v1 + cvec);
         }
-        xs[vv] = pack16(f, (const T*)nullptr);
-      }
-    }
-  } else {
-    for (int v = tid; v < nvec; v += BN_THREADS) {
-      float f[N];
-      unpack16(xs[v], f, (const T*)nullptr);
 #pragma unroll
-      for (int i = 0; i < N; ++i) {
-        f[i] = f[i] * sc[i] + sh[i];
-        if (relu) f[i] = fmaxf(f[i], 0.f);
+        for (int u = 0; u < RU; ++u) {
+          const int v = nb + tid + u * BN_THREADS;
+          if (v < ne) rn[u] = __ldg(rg + v);
+        }
       }
-      xs[v] = pack16(f, (const T*)nullptr);
+#pragma unroll
+      for (int u = 0; u < RU; ++u) {
+        const int v = vb + tid + u * BN_THREADS;
+        if (v < v1) {
+          float f[N];
+          unpack16(xs[v], f, (const T*)nullptr);
+          if (res) {
+            float q[N];
+            unpack16(res_smem ? rs[v] : rq[u], q, (const T*)nullptr);
+#pragma unroll
+            for (int i = 0; i < N; ++i) f[i] = f[i] * sc[i] + sh[i] + q[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < N; ++i) f[i] = f[i] * sc[i] + sh[i];
+          }
+          if (relu) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          xs[v] = pack16(f, (const T*)nullptr);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < RU; ++u) rq[u] = rn[u];
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes visible to the bulk store
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t off = (uint32_t)k * chunk;
+      bnr_bulk_store((char*)(y + goff) + off, (const char*)xs + off, min(chunk, bytes - off));
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
     }
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes visible to the bulk store
-  __syncthreads();
-  if (tid < 32) {
-    bnr_store_slice(y + goff, xs, bytes);
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");       // stores complete before the CTA (and its smem) goes away
+  bnr_stamp(5);
+  if (tid == 0) {
+    client_leave(S, bar_base + c);
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");    // shared memory must outlive the reads of the bulk stores
+    bnr_stamp(6);
   }
 }
 
@@ -348,9 +478,38 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
     }
   }
   bnr_reduce<N>(a, b, ch, red, partial + ((size_t)c * S + s) * 2 * ch);
-  client_barrier(S, bar_base);
+  if (tid == 0) client_arrive(S, bar_base + c);
+  // per-channel inputs of the coefficients: fetched while the siblings arrive
+  const bool one_k = ch <= BN_THREADS, mine = one_k && tid < ch;
+  float pg = 0.f, pb = 0.f, pmu = 0.f, prs = 0.f;
+  if (mine) {
+    pg = gamma[(size_t)c * ld_p + tid];
+    pb = beta ? beta[(size_t)c * ld_p + tid] : 0.f;
+    pmu = mean[(size_t)c * ch + tid];
+    prs = rstd[(size_t)c * ch + tid];
+  }
+  if (tid == 0) client_wait(S, bar_base + c);
+  __syncthreads();
   bnr_sum_partials(partial + (size_t)c * S * 2 * ch, S, ch, red, coef + 4 * ch);
-  bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef, coef + 4 * ch);
+  if (one_k) {
+    if (mine) {
+      // A = g, B = -g*rstd*dgamma/M, Cc = -g*dbeta/M - mean*B, K = beta - mean*g (bn_bwd_coeffs)
+      const float sd = coef[4 * ch + tid], sdx = coef[5 * ch + tid];
+      const float dbt = sd, dgm = prs * (sdx - pmu * sd);
+      if (s == 0) {
+        dbeta[(size_t)c * ld_g + tid] = dbt;
+        dgamma[(size_t)c * ld_g + tid] = dgm;
+      }
+      const float gg = pg * prs;
+      const float Bk = -gg * prs * dgm / (float)M;
+      coef[tid] = gg;
+      coef[ch + tid] = Bk;
+      coef[2 * ch + tid] = -gg * dbt / (float)M - pmu * Bk;
+      coef[3 * ch + tid] = pb - pmu * gg;
+    }
+  } else {
+    bn_bwd_coeffs(M, ch, S, partial, gamma, beta, ld_p, mean, rstd, dgamma, dbeta, ld_g, coef, coef + 4 * ch);
+  }
   __syncthreads();
   float A[N], B[N], Cc[N];
 #pragma unroll
@@ -373,7 +532,8 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
     bnr_store_slice(dx + goff, xs, bytes);
     if (dres) bnr_store_slice(dres + goff, ds, bytes);
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (tid == 0) client_leave(S, bar_base + c);
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");    // shared memory must outlive the reads of the bulk stores
   }
 }
 

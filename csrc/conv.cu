@@ -421,6 +421,19 @@ static int bn_fwd_impl(const void* x, const void* res, void* y, int32_t C, int64
     uint32_t cap = 0;
     size_t smem = 0;
     {
+      static bool chunks_set = false;
+      if (!chunks_set) {
+        chunks_set = true;
+        const char* e = getenv("FB_BN_CHUNKS");
+        if (e) {
+          unsigned n = (unsigned)atoi(e);
+          if (n < 1) n = 1;
+          if (n > BNR_MAX_CHUNKS) n = BNR_MAX_CHUNKS;
+          FB_CHECK_CUDA(cudaMemcpyToSymbol(g_bn_chunks, &n, sizeof(n)));
+        }
+      }
+    }
+    {
       int Sp = 0, grid = 0;
       uint32_t capp = 0;
       size_t smemp = 0;
@@ -1079,4 +1092,11 @@ extern "C" int fb_maxpool2x2_bwd(const void* dy, const void* x, void* dx, int32_
                                  fb_stream_t stream) {
   return act_fp32 ? maxpool_impl<float>(x, nullptr, dy, dx, n_img, H, W, ch, off_h, off_w, Ho, Wo, relu_mask, stream)
                   : maxpool_impl<__nv_bfloat16>(x, nullptr, dy, dx, n_img, H, W, ch, off_h, off_w, Ho, Wo, relu_mask, stream);
+}
+
+// debugging aid: per-CTA timeline of the resident BatchNorm forward kernel (NULL turns it off); see tools/trace_bn.py
+extern "C" int fb_bn_set_trace(void* buf_u64) {
+  unsigned long long* p = (unsigned long long*)buf_u64;
+  FB_CHECK_CUDA(cudaMemcpyToSymbol(g_bn_trace, &p, sizeof(p)));
+  return FB_OK;
 }
