@@ -538,9 +538,9 @@ bn_bwd_resident_kernel(const T* __restrict__ dy, const T* __restrict__ dy2, cons
 }
 
 // ---- host side: slice count and shared-memory budget
-// FB_BN_RESIDENT: 0 = never, 1 = whenever the slab fits, unset = where it measured faster on the 100-client ResNet-56 round
-// (profiles/r2/bn_resident.md: tf32 114.0 -> 106.9 ms with both passes resident; bf16 69.2 -> 66.0 ms with the backward
-// pass only, 66.8 with both): everything in fp32, the backward pass in bf16
+// FB_BN_RESIDENT=0 turns the resident kernels off (fused kernels instead); default: whenever the slab fits (first version:
+// tf32 round 114.0 -> 106.9 ms, bf16 backward only; with the arrive/wait barrier and two bf16 CTAs per SM the bf16 forward
+// pass wins as well: 64.28 -> 63.16 ms; profiles/r2/bn_resident.md)
 static int bn_resident_mode() {
   static int v = -2;
   if (v == -2) {
@@ -576,11 +576,21 @@ static bool bn_resident_plan(int64_t M, int ch, int arrays, int bwd, bool has_re
   const int mode = bn_resident_mode();
   if (!mode || (BN_THREADS * N) % ch != 0) return false;
   (void)has_res;
-  if (mode < 0 && !bwd && sizeof(T) == 2) return false;
+  (void)bwd;
   const int64_t row_bytes = (int64_t)ch * (int64_t)sizeof(T);
   const int64_t extra = (int64_t)(6 * ch + BN_THREADS * 2 * N) * 4;
+  // FB_BN_RES_TOTAL_KB (default 110): slices + scratch together stay below this many KB per CTA, so that two CTAs share an SM
+  // whatever the scratch size (bf16: 17.9 KB); 0 = the slice budget alone.  bf16 round 64.28 -> 64.03 ms, with the bf16
+  // forward pass resident as well 63.16 ms
+  static int total_kb = -1;
+  if (total_kb < 0) {
+    const char* e = getenv("FB_BN_RES_TOTAL_KB");
+    total_kb = e ? atoi(e) : 110;
+  }
   for (int pass = 0; pass < 2; ++pass) {
-    const int64_t budget = (pass == 0 ? (int64_t)bn_resident_budget_kb(bwd) : 200) * 1024 - (pass == 0 ? 0 : extra);
+    int64_t budget = (pass == 0 ? (int64_t)bn_resident_budget_kb(bwd) : 200) * 1024 - (pass == 0 ? 0 : extra);
+    // only when two CTAs would otherwise not fit on an SM (fp32 keeps its 96 KB slices: 98.24 vs 98.91 ms per round)
+    if (pass == 0 && total_kb > 0 && budget + extra > (int64_t)113 * 1024) budget = (int64_t)total_kb * 1024 - extra;
     const int64_t rows_fit = budget / (arrays * row_bytes);
     if (rows_fit < 1) continue;
     int64_t S = (M + rows_fit - 1) / rows_fit;
