@@ -234,6 +234,8 @@ struct GemmArgs {
   int cv_b_inner_off, cv_b_row_off;               // per-tap coordinate offsets into the weight map
   int cv_sbo, cv_swz;                             // 8-row group stride (bytes) and descriptor swizzle code
   int cv_tpt;                                     // MODE 5: taps per n-tile (9, 3 or 1)
+  int cv_out_cols;                                // MODE 5: columns of an n-tile that are stored (0 = BN); tf32 with 16 input
+                                                  // channels pads every tap to a 32-column tile whose upper half is zero
   // per-column statistics of the output (BatchNorm batch statistics produced by the convolution that feeds it):
   // stats[g][0][n] += sum over rows of D[g][:, n], stats[g][1][n] += sum of squares; group stride stats_gs floats
   float* stats;
@@ -514,13 +516,14 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // TMEM -> registers -> (bias, ReLU, convert) -> swizzled smem rows -> one TMA store per 32-row x chunk box
         const int CW = a.chunk_cols, RB = a.chunk_bytes;
         const int lds = CW / 16;   // tcgen05.ld.x16 per chunk: 4 (bf16, 64 cols), 2 (fp32, 32 cols) or fewer
-        for (int c0 = 0; c0 < a.BN; c0 += CW) {
+        const int out_cols = a.cv_out_cols ? a.cv_out_cols : a.BN;      // columns stored per n-tile = its stride in D
+        for (int c0 = 0; c0 < out_cols; c0 += CW) {
           uint32_t r[64];
 #pragma unroll
           for (int i = 0; i < 4; ++i)
             if (i < lds) tmem_ld16(taddr + (uint32_t)(c0 + 16 * i), r + 16 * i);
           tmem_ld_wait();
-          const int col0 = nt * a.BN + c0;
+          const int col0 = nt * out_cols + c0;
           if (col0 >= a.N) continue;
           uint8_t* buf = my_stage + (size_t)sbuf * 4096;
           // the TMA store that last read this buffer (two chunks ago) must have finished reading it
@@ -1053,8 +1056,13 @@ static int conv3x3_wgrad_impl(const FbConv3x3Wgrad* p, fb_stream_t stream, const
   FB_REQUIRE(p->G >= 1 && p->B >= 1 && p->H >= 1 && p->W >= 1, "fb_conv3x3_wgrad: empty problem");
   FB_REQUIRE(p->stride == 1 || p->stride == 2, "fb_conv3x3_wgrad: stride must be 1 or 2");
   // fp32 operands fed MN-major exist only in the 128-byte-row layout (see the kernel): whole 32-channel blocks
-  FB_REQUIRE(p->cin % 16 == 0 && (p->cin <= BK ? (!tf32 && (p->cin & (p->cin - 1)) == 0) || p->cin == BK : (p->cin % BK == 0)) &&
-                 (p->cin <= 256 || p->cin % 256 == 0),
+  // tf32 with 16 input channels: every tap is its own 32-column tile, the TMA box is 32 channels wide on a 16-channel
+  // tensor (the upper half is zero-filled) and only 16 columns of the tile are stored.  Correct but slow (nine tiles per
+  // client, 320 k-blocks of 32 pixels each: ResNet-56 round 97.8 -> 149.9 ms when the 16-channel layers use it), so the
+  // executor keeps im2col + TN GEMM below 64 channels (FB_IMPLICIT_WGRAD_MIN_CIN)
+  const bool pad16 = tf32 && p->cin == 16;
+  FB_REQUIRE(pad16 || (p->cin % 16 == 0 && (p->cin <= BK ? (!tf32 && (p->cin & (p->cin - 1)) == 0) || p->cin == BK : (p->cin % BK == 0)) &&
+                 (p->cin <= 256 || p->cin % 256 == 0)),
              "fb_conv3x3_wgrad: input channels must fill 32 or 64 bytes, a multiple of 128 bytes up to 256 channels, or a "
              "multiple of 256 channels (got %d)", p->cin);
   FB_REQUIRE(p->cout >= 8 && p->cout % 8 == 0, "fb_conv3x3_wgrad: output channels must be a multiple of 8");
@@ -1074,7 +1082,7 @@ static int conv3x3_wgrad_impl(const FbConv3x3Wgrad* p, fb_stream_t stream, const
   FB_REQUIRE(((uintptr_t)p->x % 16) == 0 && ((uintptr_t)p->dy % 16) == 0 && ((uintptr_t)p->dw % 16) == 0 &&
                  (p->G == 1 || p->dw_gs % 4 == 0),
              "fb_conv3x3_wgrad: operands must be 16-byte aligned");
-  const int kblk = p->cin < BK ? p->cin : BK;
+  const int kblk = pad16 ? BK : (p->cin < BK ? p->cin : BK);
   const int row_bytes = kblk * es;
   GemmArgs a;
   memset(&a, 0, sizeof(a));
@@ -1084,17 +1092,18 @@ static int conv3x3_wgrad_impl(const FbConv3x3Wgrad* p, fb_stream_t stream, const
   a.d_gs = p->dw_gs; a.d_gs2 = 0;
   // taps per n-tile: all nine when they fit one 256-column tile, else three, else one tap (and a channel chunk);
   // dy (the A operand) is then streamed 1 / 3 / 9 times
-  const int tpt = 9 * p->cin <= 256 ? 9 : (3 * p->cin <= 256 ? 3 : 1);
-  const int bn_tap = p->cin < 256 ? p->cin : 256;
+  const int tpt = pad16 ? 1 : (9 * p->cin <= 256 ? 9 : (3 * p->cin <= 256 ? 3 : 1));
+  const int bn_tap = pad16 ? BK : (p->cin < 256 ? p->cin : 256);
   a.cv_tpt = tpt;
+  a.cv_out_cols = pad16 ? 16 : 0;
   a.BN = tpt * bn_tap;
   a.BNpad = (a.BN + BK - 1) / BK * BK;
   a.gi = a.G; a.group_div = S; a.gi_out = p->G;
   a.tma_store = 1;
   a.reduce_add = (S > 1 || p->accumulate) ? 1 : 0;
-  a.chunk_cols = a.BN >= 32 ? 32 : 16;
+  a.chunk_cols = (a.BN >= 32 && !pad16) ? 32 : 16;
   a.chunk_bytes = a.chunk_cols * 4;
-  a.cv_kcs = p->cin / bn_tap;
+  a.cv_kcs = pad16 ? 1 : p->cin / bn_tap;
   a.n_tiles = (9 / tpt) * a.cv_kcs;
   a.m_tiles = (p->cout + GEMM_BM - 1) / GEMM_BM;
   a.k_blocks = Ks / BK;

@@ -776,7 +776,8 @@ def conv3x3_wgrad_supported(x: torch.Tensor, dy: torch.Tensor, stride: int) -> b
     pow2 = lambda v: v >= 1 and (v & (v - 1)) == 0   # noqa: E731
     row = 128 // x.element_size()
     ok_c = (cin * x.element_size() in (32, 64) and x.dtype == torch.bfloat16) or (row <= cin <= 256 and cin % row == 0) \
-        or (cin > 256 and cin % 256 == 0)       # fp32 operands fed MN-major need whole 128-byte channel blocks
+        or (cin > 256 and cin % 256 == 0)       # fp32 operands fed MN-major need whole 128-byte channel blocks ...
+    ok_c = ok_c or (x.dtype == torch.float32 and cin == 16)      # ... except 16 channels: one zero-padded 32-column tile per tap
     return ok_c and cin % 16 == 0 and cout % 8 == 0 and pow2(Ho) and pow2(Wo) and Wo <= 64 and (B * Ho * Wo) % row == 0 \
         and tuple(dy.shape[:4]) == (x.shape[0], B, Ho, Wo)
 
@@ -793,6 +794,8 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, stride: int = 1, out: Optio
     cout = dy.shape[-1]
     Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     tpt = 9 if 9 * cin <= 256 else (3 if 3 * cin <= 256 else 1)     # taps per tile, as in the kernel launcher
+    if x.dtype == torch.float32 and cin == 16:
+        tpt = 1
     tiles = Cn * ((cout + 127) // 128) * (9 // tpt) * (cin // min(cin, 256))
     kb = B * Ho * Wo // (128 // x.element_size())
     S = 1

@@ -104,7 +104,9 @@ def test_implicit_conv3x3_tf32_forward_and_dgrad(B, H, cin, cout, stride):
 
 @pytest.mark.parametrize("C,B,H,cin,cout,stride", [(40, 4, 16, 32, 32, 1), (3, 10, 32, 32, 32, 2),
                                                     (2, 6, 8, 64, 64, 1), (2, 4, 8, 128, 128, 1), (3, 8, 16, 64, 128, 2),
-                                                    (2, 16, 4, 256, 64, 1)])
+                                                    (2, 16, 4, 256, 64, 1),
+                                                    # 16 input channels: one zero-padded 32-column tile per tap, 16 columns stored
+                                                    (13, 10, 32, 16, 16, 1), (3, 4, 16, 16, 32, 2), (100, 2, 8, 16, 64, 1)])
 def test_implicit_conv3x3_tf32_wgrad(C, B, H, cin, cout, stride):
     import torch.nn.functional as F
     from fedml_b200 import ops
