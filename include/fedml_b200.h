@@ -485,6 +485,11 @@ int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, 
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
 
+/* Debugging aid: when `buf_u64` (device memory, 8 x uint64 per CTA of the next resident BatchNorm forward launch) is set,
+ * thread 0 of every CTA stores %globaltimer at [start, loaded, statistics, barrier, coefficients, applied, stored] and its
+ * SM id; NULL turns it off.  tools/trace_bn.py prints the phase table. */
+int fb_bn_set_trace(void* buf_u64);
+
 /* 2x2 / stride-2 max pooling on NHWC bf16 or fp32 (act_fp32) maps [n_img][H][W][ch], ch a multiple of 8.  The pooled
  * windows start at (off_h, off_w): y [n_img][Ho][Wo][ch] = max of x[off_h + 2i + {0,1}][off_w + 2j + {0,1}].  Backward
  * writes the whole dx [n_img][H][W][ch] (zero outside the windows), routes dy to the first maximal element of a window and,
