@@ -1,0 +1,92 @@
+"""Readers of the reference's tabular datasets (UCI streams, NUS-WIDE, Lending Club) on small files written in the original
+formats (reference: data/UCI/data_loader_for_susy_and_ro.py, data/NUS_WIDE/nus_wide_dataset.py,
+data/lending_club_loan/lending_club_dataset.py)."""
+import os
+
+import numpy as np
+import pytest
+
+from fedml_b200.data import tabular_readers as T
+
+
+def test_uci_stream_loader_susy_and_room_occupancy(tmp_path):
+    rs = np.random.RandomState(0)
+    n, clients = 240, [0, 1, 2, 3]
+    centers = rs.randn(4, 18) * 6
+    rows = []
+    for i in range(n):
+        k = i % 4
+        rows.append([float(k % 2)] + list(centers[k] + 0.1 * rs.randn(18)))
+    susy = tmp_path / "SUSY.csv"
+    susy.write_text("\n".join(",".join(f"{v:.6f}" for v in r) for r in rows))
+    streams = T.UCIStreamLoader("SUSY", str(susy), clients, n, beta=0.5).load_datastream()
+    assert sorted(streams) == clients and all(len(v) == n // 4 for v in streams.values())
+    assert streams[0][0]["x"].shape == (18,) and streams[0][0]["y"] in (0, 1)
+    # the clustered half is non-IID: the first samples of a client come from one generating centre
+    for c in clients:
+        first = np.stack([s["x"] for s in streams[c][:20]])
+        assert np.linalg.norm(first - first.mean(0), axis=1).max() < 3.0
+    # beta = 0: round-robin fill only
+    flat = T.UCIStreamLoader("SUSY", str(susy), clients, n, beta=0.0).load_datastream()
+    assert [len(flat[c]) for c in clients] == [60] * 4 and np.allclose(flat[0][0]["x"], rows[0][1:], atol=1e-5)
+    ro = tmp_path / "ro.csv"
+    ro.write_text('"id","date","Temperature","Humidity","Light","CO2","HumidityRatio","Occupancy"\n' + "\n".join(
+        f'"{i}","2015-02-04 17:51:00",{23 + i % 3},{27.2},{426 + i},{721.25},{0.0047},{i % 2}' for i in range(40)))
+    s2 = T.UCIStreamLoader("RO", str(ro), [0, 1], 40, beta=0.25).load_datastream()
+    assert sum(len(v) for v in s2.values()) <= 40 and s2[0][0]["x"].shape == (5,) and set(s["y"] for v in s2.values() for s in v) == {0, 1}
+
+
+def test_nus_wide_vertical_split_readers(tmp_path):
+    pd = pytest.importorskip("pandas")
+    rs = np.random.RandomState(1)
+    n = 50
+    root = tmp_path / "NUS_WIDE"
+    (root / "Groundtruth" / "AllLabels").mkdir(parents=True)
+    (root / "Groundtruth" / "TrainTestLabels").mkdir(parents=True)
+    (root / "Low_Level_Features").mkdir()
+    (root / "NUS_WID_Tags").mkdir()
+    lab = {"sky": (np.arange(n) % 3 == 0), "water": (np.arange(n) % 3 == 1), "cat": (np.arange(n) % 10 == 2)}
+    for k, v in lab.items():
+        (root / "Groundtruth" / "AllLabels" / f"Labels_{k}.txt").write_text("\n".join(str(int(b)) for b in v))
+        (root / "Groundtruth" / "TrainTestLabels" / f"Labels_{k}_Train.txt").write_text("\n".join(str(int(b)) for b in v))
+    for name, width in (("Train_Normalized_CH.dat", 6), ("Train_Normalized_EDH.dat", 4)):
+        (root / "Low_Level_Features" / name).write_text("\n".join(" ".join(f"{x:.4f}" for x in rs.rand(width)) + " " for _ in range(n)))
+    (root / "NUS_WID_Tags" / "Train_Tags1k.dat").write_text("\n".join("\t".join(str(int(x)) for x in rs.rand(8) > 0.5) + "\t" for _ in range(n)))
+    assert set(T.nus_wide_top_k_labels(str(root), 2)) == {"sky", "water"}
+    (xa, xb, y), (xat, xbt, yt) = T.nus_wide_load_two_party_data(str(root), ["sky", "water"], neg_label=0)
+    keep = int((lab["sky"] ^ lab["water"]).sum())                 # rows with exactly one of the two concepts
+    assert xa.shape[0] + xat.shape[0] == keep and xa.shape[1] == 10 and xb.shape[1] == 8 and xa.shape[0] == int(0.8 * keep)
+    assert set(np.unique(np.concatenate([y, yt]))) == {0, 1} and abs(float(np.concatenate([xa, xat]).mean())) < 1e-6
+    tr3, te3 = T.nus_wide_load_three_party_data(str(root), ["sky", "water"])
+    assert [a.shape[1] for a in tr3] == [10, 4, 4, 1] and set(np.unique(tr3[3])) <= {-1, 1}
+
+
+def test_lending_club_vertical_split_readers(tmp_path):
+    pd = pytest.importorskip("pandas")
+    rs = np.random.RandomState(2)
+    n = 60
+    cols = [c for g in T.LOAN_GROUPS.values() for c in g]
+    df = pd.DataFrame({c: rs.rand(n) * 100 for c in cols if c != "annual_inc_comp"})
+    df["grade"] = rs.choice(list("ABCDEFG"), n)
+    df["emp_length"] = rs.choice(["< 1 year", "3 years", "10+ years", None], n)
+    df["home_ownership"] = rs.choice(["RENT", "OWN", "MORTGAGE"], n)
+    df["verification_status"] = rs.choice(["Verified", "Not Verified"], n)
+    df["verification_status_joint"] = rs.choice(["Verified", None], n)
+    df["annual_inc"], df["annual_inc_joint"] = rs.rand(n) * 1e5, rs.rand(n) * 2e5
+    df["term"] = rs.choice([" 36 months", " 60 months"], n)
+    df["initial_list_status"] = rs.choice(["w", "f"], n)
+    df["purpose"] = rs.choice(["credit_card", "car", "small_business"], n)
+    df["application_type"] = rs.choice(["Individual", "Joint App"], n)
+    df["disbursement_method"] = "Cash"
+    df["loan_status"] = rs.choice(["Fully Paid", "Charged Off", "Current", "Late (31-120 days)"], n)
+    df["issue_d"] = ["Mar-2018" if i % 4 else "Mar-2017" for i in range(n)]
+    d = str(tmp_path) + os.sep
+    df.to_csv(d + "loan.csv", index=False)
+    (xa, xb, y), (xat, xbt, yt) = T.loan_load_two_party_data(d)
+    n18 = sum(1 for i in range(n) if i % 4)
+    assert xa.shape == (int(0.8 * n18), 15) and xb.shape[1] == 68 and xat.shape[0] == n18 - int(0.8 * n18)
+    assert set(np.unique(np.concatenate([y, yt]))) <= {0, 1} and os.path.exists(d + "processed_loan.csv")
+    bad = df[df["issue_d"] == "Mar-2018"]["loan_status"].isin(["Charged Off", "Late (31-120 days)"]).sum()
+    assert int(np.concatenate([y, yt]).sum()) == int(bad)
+    tr3, te3 = T.loan_load_three_party_data(d)                      # second call reads the cached processed table
+    assert [a.shape[1] for a in tr3] == [15, 35, 33, 1]
