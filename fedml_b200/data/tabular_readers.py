@@ -228,3 +228,33 @@ def loan_load_two_party_data(data_dir):
 
 def loan_load_three_party_data(data_dir):
     return _loan_parties(data_dir, [("qualification", "loan"), ("debt", "repayment"), ("multi_acc", "mal_behavior")])
+
+
+# ------------------------------------------------------------------------------------------------ entry point for the VFL runners
+def load_vertical_dataset(args):
+    """``(party_dims, (xs, y), (xs_test, y_test))`` as torch tensors for the vertical-FL runners: the real Lending-Club /
+    NUS-WIDE files when ``args.data_cache_dir`` holds them (``dataset: lending_club_loan | NUS_WIDE``, ``vfl_party_num`` 2 or 3,
+    ``nus_wide_labels`` optional), else the synthetic task of the same form (no network here to download anything)."""
+    import torch
+    from .synthetic import make_vertical_tabular
+    name = str(getattr(args, "dataset", "lending_club")).lower()
+    root = str(getattr(args, "data_cache_dir", "") or "")
+    parties = int(getattr(args, "vfl_party_num", 0) or 0)
+    loaded = None
+    if root and "lending" in name and (os.path.exists(os.path.join(root, "loan.csv")) or os.path.exists(os.path.join(root, "processed_loan.csv"))):
+        d = root if root.endswith(os.sep) else root + os.sep
+        loaded = loan_load_two_party_data(d) if parties == 2 else loan_load_three_party_data(d)
+    elif root and "nus" in name and os.path.isdir(os.path.join(root, "Groundtruth", "TrainTestLabels")):
+        labels = list(getattr(args, "nus_wide_labels", None) or nus_wide_top_k_labels(root, 2))
+        n = int(getattr(args, "vfl_samples", -1) or -1)
+        loaded = (nus_wide_load_two_party_data(root, labels, 0, n) if parties == 2
+                  else nus_wide_load_three_party_data(root, labels, 0, n))
+    if loaded is None:
+        dims = tuple(getattr(args, "vfl_party_dims", (32, 24, 24)))
+        (xs, y), (xt, yt) = make_vertical_tabular(int(getattr(args, "vfl_samples", 4000)), dims, int(getattr(args, "random_seed", 0)), name)
+        return dims, (xs, y), (xt, yt)
+    train, test = loaded
+    to_x = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))                       # noqa: E731
+    to_y = lambda a: torch.from_numpy((np.asarray(a).reshape(-1) > 0).astype(np.float32))              # noqa: E731
+    xs, xt = [to_x(a) for a in train[:-1]], [to_x(a) for a in test[:-1]]
+    return tuple(int(x.shape[1]) for x in xs), (xs, to_y(train[-1])), (xt, to_y(test[-1]))

@@ -6,7 +6,7 @@ import torch.nn as nn
 
 from ...core.distributed.communication.message import Message
 from ...core.distributed.managers import ClientManager, ServerManager
-from ...data.synthetic import make_vertical_tabular
+from ...data.tabular_readers import load_vertical_dataset
 from ...models.finance import DenseModel, LocalModel
 
 MSG_H2G_LOGITS, MSG_G2H_GRAD, MSG_FINISH = 1, 2, 6
@@ -26,8 +26,10 @@ class _Party:
 
 
 def _data(args):
-    dims = tuple(getattr(args, "vfl_party_dims", (32, 24, 24)))
-    return dims, make_vertical_tabular(int(getattr(args, "vfl_samples", 2000)), dims, int(getattr(args, "random_seed", 0)))
+    if not hasattr(args, "vfl_samples"):
+        args.vfl_samples = 2000
+    dims, tr, te = load_vertical_dataset(args)
+    return dims, (tr, te)
 
 
 class GuestManager(ServerManager):

@@ -7,7 +7,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-from ...data.synthetic import make_vertical_tabular
+from ...data.tabular_readers import load_vertical_dataset
 from ...models.finance import DenseModel, LocalModel
 
 
@@ -33,10 +33,7 @@ class VFLParty:
 class VerticalFLAPI:
     def __init__(self, args, device=None, dataset=None, model=None, *_, **__):
         self.args = args
-        dims = tuple(getattr(args, "vfl_party_dims", (32, 24, 24)))
-        (self.xs, self.y), (self.xs_te, self.y_te) = make_vertical_tabular(
-            int(getattr(args, "vfl_samples", 4000)), dims, int(getattr(args, "random_seed", 0)),
-            str(getattr(args, "dataset", "lending_club")))
+        dims, (self.xs, self.y), (self.xs_te, self.y_te) = load_vertical_dataset(args)      # real files when present
         lr = float(getattr(args, "learning_rate", 0.05))
         hid = int(getattr(args, "vfl_hidden", 16))
         self.parties = [VFLParty(LocalModel(d, hid, lr), DenseModel(hid, 1, lr, bias=(i == 0)), lr) for i, d in enumerate(dims)]

@@ -90,3 +90,27 @@ def test_lending_club_vertical_split_readers(tmp_path):
     assert int(np.concatenate([y, yt]).sum()) == int(bad)
     tr3, te3 = T.loan_load_three_party_data(d)                      # second call reads the cached processed table
     assert [a.shape[1] for a in tr3] == [15, 35, 33, 1]
+
+
+def test_vertical_fl_runs_on_lending_club_files(tmp_path):
+    """The SP vertical-FL runner picks up a loan.csv in ``data_cache_dir`` (three parties: 15 / 35 / 33 features)."""
+    pd = pytest.importorskip("pandas")
+    import fedml
+    from fedml_b200.arguments import Arguments
+    from fedml_b200.simulation.sp.vertical_fl import VerticalFLAPI
+    rs = np.random.RandomState(3)
+    n = 200
+    cols = [c for g in T.LOAN_GROUPS.values() for c in g]
+    df = pd.DataFrame({c: rs.randn(n) for c in cols if c != "annual_inc_comp"})
+    signal = df["int_rate"] + df["dti"] - df["total_pymnt"]
+    df["loan_status"] = np.where(signal > 0, "Charged Off", "Fully Paid")
+    df["annual_inc"], df["annual_inc_joint"] = rs.rand(n) * 1e5, rs.rand(n) * 1e5
+    df["verification_status_joint"] = None
+    df["issue_d"] = "Jun-2018"
+    df.to_csv(tmp_path / "loan.csv", index=False)
+    args = fedml.init(Arguments.from_dict(dict(training_type="simulation", federated_optimizer="classical_vertical", dataset="lending_club_loan",
+                                               data_cache_dir=str(tmp_path), comm_round=30, epochs=1, batch_size=32, learning_rate=0.1, log_level="WARNING")))
+    api = VerticalFLAPI(args)
+    assert [x.shape[1] for x in api.xs] == [15, 35, 33] and api.y.shape[0] == 160
+    api.train()
+    assert api.history[-1]["test_acc"] > 0.65                      # 40 test rows, 83 noisy features
