@@ -31,7 +31,14 @@ def non_iid_partition_with_dirichlet_distribution(label_list, client_num, classe
     N = len(label_list) if segmentation else label_list.shape[0]
     min_size = 0
     idx_batch = [[] for _ in range(client_num)]
-    while min_size < min_required:
+    # the reference redraws until every client holds min_required samples (noniid_partition.py:44); that cannot end when there
+    # are fewer samples than clients need, so the requirement is lowered to what the sample count allows
+    min_required = min(int(min_required), N // max(int(client_num), 1))
+    tries = 0
+    while tries == 0 or min_size < min_required:
+        tries += 1
+        if tries % 200 == 0:                 # still unlucky after many draws (tiny alpha, many clients): relax by one
+            min_required = max(0, min_required - 1)
         idx_batch = [[] for _ in range(client_num)]
         if segmentation:
             cats = list(classes)

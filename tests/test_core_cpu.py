@@ -393,3 +393,12 @@ def test_synchronized_batchnorm_equals_batchnorm_on_the_global_batch():
     x = torch.randn(4, 5, 3, 3)
     torch.testing.assert_close(b(x), a(x), rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(b.running_var, a.running_var, rtol=1e-5, atol=1e-6)
+
+
+def test_dirichlet_partition_terminates_with_fewer_samples_than_clients():
+    """64 samples over 500 clients: the reference's redraw-until-min-size loop would never end; every sample is still assigned."""
+    from fedml_b200.core.non_iid_partition import non_iid_partition_with_dirichlet_distribution
+    np.random.seed(0)
+    y = np.random.randint(0, 10, 64)
+    part = non_iid_partition_with_dirichlet_distribution(y, 500, 10, 0.1, min_required=10)
+    assert sorted(i for v in part.values() for i in v) == list(range(64))
