@@ -98,8 +98,25 @@ __device__ __forceinline__ float4 opt_apply4(const OptCfg& o, float4 w, float4 a
 
 // ---------------------------------------------------------------- cross-rank per-block flags
 // flags layout on every rank: uint32 [2 phases][G senders][FB_ROUND_MAX_BLOCKS]
+// Race-detection aid (tests/test_gpu_round_hardening.py): with fb_round_set_skew(seed, max_ns) every (rank, block, phase)
+// stalls a pseudo-random time below max_ns before it signals, so ranks and blocks reach the handshakes in shuffled order;
+// the flag protocol must give the same bits whatever the interleaving.  max_ns = 0 (default): one load per handshake.
+static __device__ unsigned g_fb_round_skew[2] = {0u, 0u};     // seed, max_ns
+__device__ __forceinline__ void skew_delay(int phase, int rank, int block) {
+  const unsigned max_ns = *reinterpret_cast<volatile unsigned*>(&g_fb_round_skew[1]);
+  if (max_ns == 0u) return;
+  if (threadIdx.x == 0) {
+    const Philox4 r = philox4x32_10((uint32_t)block, (uint32_t)rank, (uint32_t)phase, 0x5EEDu, g_fb_round_skew[0], 0x9E3779B9u);
+    const unsigned long long wait = r.x % max_ns, t0 = fb_globaltimer();
+    while (fb_globaltimer() - t0 < wait) {
+    }
+  }
+  __syncthreads();
+}
+
 __device__ __forceinline__ void block_signal_and_wait(uint32_t* const* peer_flags, int phase, int rank, int G,
                                                       int block, uint32_t epoch) {
+  skew_delay(phase, rank, block);
   __syncthreads();  // all of this block's data stores are issued
   if ((int)threadIdx.x < G) {
     const int q = threadIdx.x;
@@ -594,6 +611,12 @@ __global__ void peer_barrier_kernel(uint32_t* const* peer_flags, int rank, int G
   }
 }
 FB_DEFINE_SPIN_API(fb_round)
+
+extern "C" int fb_round_set_skew(uint32_t seed, uint32_t max_ns) {
+  const unsigned v[2] = {seed, max_ns};
+  FB_CHECK_CUDA(cudaMemcpyToSymbol(g_fb_round_skew, v, sizeof(v)));
+  return FB_OK;
+}
 extern "C" int64_t fb_peer_barrier_flag_bytes(int32_t G) { return (int64_t)8 * (G < 1 ? 1 : G) * sizeof(uint32_t); }
 extern "C" int fb_peer_barrier(uint32_t* const* peer_flags, int32_t rank, int32_t G, uint32_t epoch, int32_t slot,
                                fb_stream_t stream) {

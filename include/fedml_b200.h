@@ -485,6 +485,10 @@ int fb_sgd_restage_f32(float* arena, const float* grads, int64_t ld, int32_t C, 
                        void* stage_f32, int64_t stage_ld, const int64_t* table_dev, int32_t n_layers, int32_t total_elems,
                        const float* lr_dev, fb_stream_t stream);
 
+/* Race-detection aid for the round kernel's flag protocol: every (rank, block, handshake) stalls a pseudo-random time below
+ * max_ns (Philox of seed) before it signals; 0 turns it off.  Results must not depend on it. */
+int fb_round_set_skew(uint32_t seed, uint32_t max_ns);
+
 /* Debugging aid: when `buf_u64` (device memory, 8 x uint64 per CTA of the next resident BatchNorm forward launch) is set,
  * thread 0 of every CTA stores %globaltimer at [start, loaded, statistics, barrier, coefficients, applied, stored] and its
  * SM id; NULL turns it off.  tools/trace_bn.py prints the phase table. */

@@ -180,3 +180,45 @@ def test_nccl_simulator_secure_aggregation_on_the_field_kernels():
         outs.append((sim.global_flat.clone(), native.LAUNCHES[0] - before))
     assert float((outs[0][0] - outs[1][0]).abs().max()) < 6 * 4 / 2 ** 16
     assert outs[1][1] > outs[0][1]                       # the field kernels ran
+
+
+@pytest.mark.parametrize("two_shot", [False, True])
+def test_flag_protocol_is_insensitive_to_block_and_rank_skew(two_shot):
+    """Race-detection stand-in (compute-sanitizer is closed on this pool): every (rank, block, handshake) of the emulated
+    4-rank round stalls a pseudo-random time below 150 us before it signals, with five different seeds, for three rounds in a
+    row on the same buffers; the result must be bit-identical to the run without delays and identical on every rank."""
+    import ctypes as C
+    from fedml_b200.ops.native import lib
+    from fedml_b200.parallel.round_engine import DPConfig, RoundEngine, ServerOptConfig, emulated_round
+    RoundEngine.set_spin_timeout(5000)
+    G, P, P_train = 4, 4 * 50021, 4 * 50000
+    opt = ServerOptConfig("adam", lr=0.01)
+    dpc = DPConfig(clip=2.0, sigma=0.001, seed=3)
+
+    def run(seed, max_ns):
+        assert lib().fb_round_set_skew(C.c_uint32(seed), C.c_uint32(max_ns)) == 0
+        state, g_cur, outs_all = None, None, []
+        for rnd in range(3):
+            g, clients, weights, total = _mk(G, (3, 1, 4, 2), P, 40 + rnd)
+            if g_cur is None:
+                g_cur = g
+            else:
+                clients = [c - g + g_cur for c in clients]
+            outs, state = emulated_round(clients, weights, g_cur, P_train, 1.0 / total, two_shot, opt=opt, dp=dpc,
+                                         opt_step=rnd + 1, round_idx=rnd, epoch=rnd + 1, state=state)
+            RoundEngine.check_spin_errors()
+            for r in range(1, G):
+                assert torch.equal(outs[0], outs[r])
+            g_cur = outs[0].clone()
+            outs_all.append(g_cur)
+        return outs_all
+
+    try:
+        base = run(0, 0)
+        for seed in range(1, 6):
+            skewed = run(seed, 150_000)
+            for a, b in zip(base, skewed):
+                assert torch.equal(a, b), f"seed {seed}: result depends on the interleaving"
+    finally:
+        lib().fb_round_set_skew(C.c_uint32(0), C.c_uint32(0))
+        RoundEngine.set_spin_timeout(20000)
