@@ -182,7 +182,7 @@ def test_nccl_simulator_distilbert_batched_cpu_and_sequential_fallback_agree():
 def test_nccl_simulator_femnist_cnn_batched_cpu_and_sequential_fallback_agree():
     """FEMNIST CNN_DropOut (reference model/cv/cnn.py:74-142): the client-batched executor and per-client eager training give
     the same global model when dropout is off."""
-    kw = dict(dataset="femnist", model="cnn", client_num_in_total=4, client_num_per_round=2, synthetic_train_size=80,
+    kw = dict(dataset="femnist", model="cnn", client_num_in_total=4, client_num_per_round=2, synthetic_train_size=80, femnist_client_num=8,
               batch_size=8, comm_round=1, frequency_of_the_test=100, backend="NCCL", shuffle_clients=False)
     a = mk(**kw)
     ds, out = fedml.data.load(a)
