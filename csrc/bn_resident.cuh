@@ -153,47 +153,31 @@ __device__ __forceinline__ void client_leave(int S, int idx) {           // one 
 // each (the per-channel loop of the fused kernels walks S rows one after the other: 55 dependent L2 round trips at S = 55).
 // red: BN_THREADS floats.  Deterministic: fixed row order per thread, fixed order across threads.
 __device__ __forceinline__ void bnr_sum_partials(const float* part, int S, int ch, float* red, float* sums) {
+  // rows are taken sixteen at a time with the tail masked, so S <= 16 * groups rows cost ONE round trip to L2 (the tail
+  // loops of the first version made it 3-4 rounds at S = 27 and 6 at S = 54); the summation order per thread is fixed
   const int tid = threadIdx.x, cols = 2 * ch;
   if (cols >= BN_THREADS) {
     for (int col = tid; col < cols; col += BN_THREADS) {
       float acc = 0.f;
-      int j = 0;
-      for (; j + 16 <= S; j += 16) {
+      for (int j = 0; j < S; j += 16) {
         float v[16];
 #pragma unroll
-        for (int u = 0; u < 16; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
+        for (int u = 0; u < 16; ++u) v[u] = (j + u < S) ? __ldcg(part + (size_t)(j + u) * cols + col) : 0.f;
 #pragma unroll
         for (int u = 0; u < 16; ++u) acc += v[u];
       }
-      for (; j + 4 <= S; j += 4) {
-        float v[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = __ldcg(part + (size_t)(j + u) * cols + col);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) acc += v[u];
-      }
-      for (; j < S; ++j) acc += __ldcg(part + (size_t)j * cols + col);
       sums[col] = acc;
     }
   } else {
     const int groups = BN_THREADS / cols, col = tid % cols, grp = tid / cols;
     float acc = 0.f;
-    int j = grp;
-    for (; j + 15 * groups < S; j += 16 * groups) {
+    for (int j = grp; j < S; j += 16 * groups) {
       float v[16];
 #pragma unroll
-      for (int u = 0; u < 16; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
+      for (int u = 0; u < 16; ++u) v[u] = (j + u * groups < S) ? __ldcg(part + (size_t)(j + u * groups) * cols + col) : 0.f;
 #pragma unroll
       for (int u = 0; u < 16; ++u) acc += v[u];
     }
-    for (; j + 3 * groups < S; j += 4 * groups) {
-      float v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = __ldcg(part + (size_t)(j + u * groups) * cols + col);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) acc += v[u];
-    }
-    for (; j < S; j += groups) acc += __ldcg(part + (size_t)j * cols + col);
     red[tid] = acc;
     __syncthreads();
     if (tid < cols) {
@@ -280,7 +264,7 @@ bn_fwd_resident_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __
   }
   const bool res_g = res && !res_smem;
   const uint4* rg = reinterpret_cast<const uint4*>(res + goff);
-  constexpr int RU = 4;                       // residual vectors per thread and chunk round (cvec = RU * 256 at 16 KiB chunks)
+  constexpr int RU = 8;                       // residual vectors per thread and round: two rounds' worth (2 x 8 x 16 B per thread) in flight
   uint4 rq[RU];
 #pragma unroll
   for (int u = 0; u < RU; ++u) rq[u] = make_uint4(0, 0, 0, 0);
