@@ -613,3 +613,34 @@ def test_mlops_log_uploader_device_binding_and_package_download(tmp_path):
         for h in list(logging.getLogger().handlers):
             if getattr(h, "_fedml_b200", False):
                 logging.getLogger().removeHandler(h)
+
+
+def test_interface_helpers_context_manager_timer_and_mixing_matrix(tmp_path):
+    """Helpers that sit on the reference's abstract interfaces: ``with`` support and ``notify`` on a transport, the
+    tick / tock latency table, the mixing matrix of a topology."""
+    from fedml_b200.core.distributed.communication import utils as U
+    from fedml_b200.core.distributed.topology.topology_managers import SymmetricTopologyManager
+    hub = InProcHub()
+    args = Arguments.from_dict(dict(backend="INPROC", inproc_hub=hub, run_id="ctx"))
+    got = []
+
+    class Obs(Observer):
+        def receive_message(self, t, p):
+            got.append((t, p.get("k")))
+
+    with create_comm_manager(args, 0, 2, "INPROC") as cm:
+        cm.add_observer(Obs())
+        m = Message(7, 1, 0); m.add_params("k", 42)
+        cm.notify(m)
+        assert got == [(7, 42)] and len(cm.observers_snapshot()) == 1
+    U.latency_summary(reset=True)
+    U.log_communication_tick(0, 1, timestamp=10.0)
+    assert abs(U.log_communication_tock(0, 1, timestamp=10.25) - 0.25) < 1e-9 and U.log_communication_tock(0, 1) is None
+    with U.comm_timer(2, 3):
+        pass
+    s = U.latency_summary()
+    assert s[(0, 1)]["count"] == 1 and abs(s[(0, 1)]["max"] - 0.25) < 1e-9 and (2, 3) in s
+    topo = SymmetricTopologyManager(6, 2); topo.generate_topology()
+    w = topo.mixing_matrix()
+    assert w.shape == (6, 6) and topo.is_row_stochastic() and np.allclose(w, w.T)
+    assert sorted(j for j, _ in topo.in_neighbors(0)) == sorted(topo.get_in_neighbor_idx_list(0))
