@@ -65,6 +65,14 @@ def create(args, output_dim):
         return MNISTGan()
     if name in ("segnet", "deeplab", "unet"):
         return SegNetSmall(output_dim)
+    if name in ("darts", "darts_search", "darts_gdas"):
+        from .darts import Network, NetworkGDAS
+        return (NetworkGDAS if name.endswith("gdas") else Network)(num_classes=output_dim)
+    if name in ("resnet56_gkt", "resnet8_gkt", "gkt"):
+        from .cv import ResNet8Client, ResNet56Server
+        return ResNet8Client(output_dim), ResNet56Server(output_dim)      # (edge extractor + head, server trunk) for FedGKT
+    # the reference falls back to logistic regression for any other name (model/model_hub.py, last branch); so do we, loudly
+    logging.warning("create_model: unknown model %r for dataset %r, falling back to LogisticRegression(784, %s)", name, dataset, output_dim)
     return LogisticRegression(28 * 28, output_dim)
 
 

@@ -402,3 +402,14 @@ def test_dirichlet_partition_terminates_with_fewer_samples_than_clients():
     y = np.random.randint(0, 10, 64)
     part = non_iid_partition_with_dirichlet_distribution(y, 500, 10, 0.1, min_required=10)
     assert sorted(i for v in part.values() for i in v) == list(range(64))
+
+
+def test_model_factory_names_of_the_nas_and_gkt_algorithms():
+    import fedml
+    from fedml_b200.arguments import Arguments
+    mk = lambda m: fedml.model.create(Arguments.from_dict(dict(model=m, dataset="cifar10", log_level="ERROR")), 10)      # noqa: E731
+    assert type(mk("darts")).__name__ == "Network" and type(mk("darts_gdas")).__name__ == "NetworkGDAS"
+    client, server = mk("resnet56_gkt")
+    logits, feat = client(torch.randn(2, 3, 32, 32))
+    assert logits.shape == (2, 10) and server(feat).shape == (2, 10)
+    assert type(mk("no_such_model")).__name__ == "LogisticRegression"          # the reference's fallback (model_hub.py, last branch)
