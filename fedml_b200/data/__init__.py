@@ -204,6 +204,11 @@ def load(args):
     return dataset8, ds.class_num
 
 
+def load_synthetic_data(args):
+    """The reference's ``load`` is a thin wrapper around this name (data/data_loader.py:29-42); both are kept."""
+    return load(args)
+
+
 def split_data_for_dist_trainers(batches, n_dist_trainer):
     """Chunk one client's batch list over the processes of a silo
     (reference: data/data_loader_cross_silo.py:9-55)."""
