@@ -21,14 +21,50 @@ def _target(fullname):
     return "fedml_b200" + fullname[len("fedml"):]
 
 
+def _compat_entry(fullname):
+    """Reference module paths without a same-named module here (``fedml.simulation.single_process.fedavg.fedavg_api``,
+    ``fedml.model.cv.resnet``, ...): fedml_b200/compat_table.py says which of the module's names exist in this package and where."""
+    try:
+        from fedml_b200.compat_table import TABLE
+    except ImportError:
+        return None
+    return TABLE.get(fullname[len("fedml."):])
+
+
+def _shim_module(fullname, entry):
+    import types
+    mod = types.ModuleType(fullname, f"Compatibility view of the reference module {fullname}: names resolve into fedml_b200.")
+    if entry["pkg"]:
+        mod.__path__ = []
+    names = entry["names"]
+
+    def __getattr__(name):
+        target = names.get(name)
+        if target is None:
+            raise AttributeError(f"{fullname}.{name} has no counterpart in fedml_b200 (see docs/COMPONENTS.md)")
+        tmod, _, attr = target.partition(":")
+        value = getattr(importlib.import_module(tmod), attr)
+        setattr(mod, name, value)
+        return value
+
+    mod.__getattr__ = __getattr__
+    mod.__all__ = sorted(names)
+    return mod
+
+
 class _AliasFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
     def find_spec(self, fullname, path=None, target=None):
         if not fullname.startswith("fedml."):
             return None
+        entry = _compat_entry(fullname)
         try:
             real = importlib.import_module(_target(fullname))
+            if entry is not None and entry["pkg"] and not hasattr(real, "__path__"):
+                real.__path__ = []              # a package in the reference, one module here: sub-module imports go through the table
         except ImportError:
-            return None
+            if entry is None:
+                return None
+            real = _shim_module(fullname, entry)
         spec = importlib.util.spec_from_loader(fullname, self, is_package=hasattr(real, "__path__"))
         spec._fedml_real = real
         return spec
