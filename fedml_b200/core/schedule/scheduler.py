@@ -132,3 +132,18 @@ def schedule_clients(sample_counts: Sequence[int], n_gpus: int, speeds: Sequence
     speeds = np.ones(n_gpus) if speeds is None else np.asarray(speeds, dtype=np.float64)
     cap = (len(sample_counts) + n_gpus - 1) // n_gpus
     return lpt_assign(sample_counts, speeds, max_count=cap)
+
+
+# ``fedml.core.schedule.scheduler`` is both this module and (re-exported by the package) the class of the same name, as in the
+# reference.  Importing the sub-module rebinds the package attribute from the class to the module, so the module is made
+# callable: ``fedml.core.schedule.scheduler(...)`` builds a scheduler whichever of the two the name currently points at.
+import sys as _sys
+import types as _types
+
+
+class _CallableModule(_types.ModuleType):
+    def __call__(self, *args, **kwargs):
+        return scheduler(*args, **kwargs)
+
+
+_sys.modules[__name__].__class__ = _CallableModule
