@@ -263,3 +263,119 @@ class Architect:
         for p, gi in zip(self.model.arch_parameters(), grads):
             p.grad = gi.detach().clone()
         self.optimizer.step()
+
+
+# ============================================================================ evaluation network of a found architecture
+# Published cells as (operation, input state) pairs per node: DARTS first / second order (Liu et al. 2019) and the cell the
+# FedNAS paper reports (reference model/cv/darts/genotypes.py:74-148).
+def _genotype(normal: str, reduce: str) -> Genotype:
+    parse = lambda s: [(op, int(j)) for op, j in (tok.split("@") for tok in s.split())]      # noqa: E731
+    return Genotype(parse(normal), [2, 3, 4, 5], parse(reduce), [2, 3, 4, 5])
+
+
+DARTS_V1 = _genotype("sep_conv_3x3@1 sep_conv_3x3@0 skip_connect@0 sep_conv_3x3@1 skip_connect@0 sep_conv_3x3@1 sep_conv_3x3@0 skip_connect@2",
+                     "max_pool_3x3@0 max_pool_3x3@1 skip_connect@2 max_pool_3x3@0 max_pool_3x3@0 skip_connect@2 skip_connect@2 avg_pool_3x3@0")
+DARTS_V2 = _genotype("sep_conv_3x3@0 sep_conv_3x3@1 sep_conv_3x3@0 sep_conv_3x3@1 sep_conv_3x3@1 skip_connect@0 skip_connect@0 dil_conv_3x3@2",
+                     "max_pool_3x3@0 max_pool_3x3@1 skip_connect@2 max_pool_3x3@1 max_pool_3x3@0 skip_connect@2 skip_connect@2 max_pool_3x3@1")
+DARTS = DARTS_V2
+FedNAS_V1 = _genotype("sep_conv_3x3@1 sep_conv_3x3@0 sep_conv_3x3@2 sep_conv_5x5@0 sep_conv_3x3@1 sep_conv_5x5@3 dil_conv_5x5@3 sep_conv_3x3@4",
+                      "max_pool_3x3@0 skip_connect@1 max_pool_3x3@0 max_pool_3x3@2 max_pool_3x3@0 dil_conv_5x5@1 max_pool_3x3@0 dil_conv_5x5@2")
+
+
+def drop_path(x, drop_prob: float):
+    """Zeroes whole samples of a branch with probability ``drop_prob`` and rescales the rest (training only)."""
+    if drop_prob <= 0.0:
+        return x
+    keep = 1.0 - drop_prob
+    mask = torch.empty(x.size(0), 1, 1, 1, device=x.device, dtype=x.dtype).bernoulli_(keep)
+    return x / keep * mask
+
+
+def _eval_op(name, C, stride):
+    """Operation of a derived cell: affine BatchNorm (the search network uses affine=False so that the architecture weights
+    carry the scale)."""
+    op = OPS[name](C, stride)
+    for m in op.modules():
+        if isinstance(m, nn.BatchNorm2d) and not m.affine:
+            m.affine = True
+            m.weight, m.bias = nn.Parameter(torch.ones(m.num_features)), nn.Parameter(torch.zeros(m.num_features))
+    return op
+
+
+class DerivedCell(nn.Module):
+    def __init__(self, genotype: Genotype, Cpp, Cp, C, reduction, reduction_prev):
+        super().__init__()
+        self.reduction = reduction
+        relu_conv_bn = lambda ci: nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, C, 1, bias=False), nn.BatchNorm2d(C))      # noqa: E731
+        self.pre0 = _FactorizedReduce(Cpp, C) if reduction_prev else relu_conv_bn(Cpp)
+        self.pre1 = relu_conv_bn(Cp)
+        genes, self._concat = (genotype.reduce, list(genotype.reduce_concat)) if reduction else (genotype.normal, list(genotype.normal_concat))
+        self._indices = [j for _, j in genes]
+        self._ops = nn.ModuleList(_eval_op(name, C, 2 if reduction and j < 2 else 1) for name, j in genes)
+        self.multiplier = len(self._concat)
+
+    def forward(self, s0, s1, drop_prob=0.0):
+        states = [self.pre0(s0), self.pre1(s1)]
+        for i in range(len(self._ops) // 2):
+            hs = []
+            for k in (2 * i, 2 * i + 1):
+                h = self._ops[k](states[self._indices[k]])
+                if self.training and drop_prob > 0.0 and not isinstance(self._ops[k], nn.Identity):
+                    h = drop_path(h, drop_prob)
+                hs.append(h)
+            states.append(hs[0] + hs[1])
+        return torch.cat([states[i] for i in self._concat], dim=1)
+
+
+class AuxiliaryHeadCIFAR(nn.Module):
+    """Auxiliary classifier on the 8x8 feature map at two thirds of the depth (training-time regulariser)."""
+
+    def __init__(self, C, num_classes):
+        super().__init__()
+        self.features = nn.Sequential(nn.ReLU(True), nn.AvgPool2d(5, stride=3, padding=0, count_include_pad=False),
+                                      nn.Conv2d(C, 128, 1, bias=False), nn.BatchNorm2d(128), nn.ReLU(True),
+                                      nn.Conv2d(128, 768, 2, bias=False), nn.BatchNorm2d(768), nn.ReLU(True))
+        self.classifier = nn.Linear(768, num_classes)
+
+    def forward(self, x):
+        return self.classifier(self.features(x).flatten(1))
+
+
+class NetworkCIFAR(nn.Module):
+    """The network that is trained from scratch after the search (reference model/cv/darts/model.py:111-176): ``layers`` derived
+    cells of ``genotype`` with reductions at 1/3 and 2/3 of the depth; returns ``(logits, aux_logits)``."""
+
+    def __init__(self, C=36, num_classes=10, layers=20, auxiliary=False, genotype: Genotype = DARTS_V2):
+        super().__init__()
+        self._layers, self._auxiliary, self.drop_path_prob = layers, auxiliary, 0.0
+        Cc = 3 * C
+        self.stem = nn.Sequential(nn.Conv2d(3, Cc, 3, padding=1, bias=False), nn.BatchNorm2d(Cc))
+        Cpp, Cp, Cc = Cc, Cc, C
+        self.cells = nn.ModuleList()
+        red_prev, C_aux = False, None
+        for i in range(layers):
+            red = i in (layers // 3, 2 * layers // 3)
+            if red:
+                Cc *= 2
+            cell = DerivedCell(genotype, Cpp, Cp, Cc, red, red_prev)
+            self.cells.append(cell)
+            red_prev = red
+            Cpp, Cp = Cp, cell.multiplier * Cc
+            if i == 2 * layers // 3:
+                C_aux = Cp
+        self.auxiliary_head = AuxiliaryHeadCIFAR(C_aux, num_classes) if auxiliary else None
+        self.global_pooling = nn.AdaptiveAvgPool2d(1)
+        self.classifier = nn.Linear(Cp, num_classes)
+
+    def forward(self, x):
+        aux = None
+        s0 = s1 = self.stem(x)
+        for i, cell in enumerate(self.cells):
+            s0, s1 = s1, cell(s0, s1, self.drop_path_prob)
+            if i == 2 * self._layers // 3 and self.auxiliary_head is not None and self.training:
+                aux = self.auxiliary_head(s1)
+        return self.classifier(self.global_pooling(s1).flatten(1)), aux
+
+
+def count_parameters_in_MB(model) -> float:      # noqa: N802  (the reference's name)
+    return sum(p.numel() for n, p in model.named_parameters() if "auxiliary" not in n) / 1e6

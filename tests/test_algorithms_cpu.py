@@ -419,3 +419,23 @@ def test_nccl_simulator_secure_aggregation_matches_plain_fedavg():
             sim.train_one_round(r)
         outs.append(sim.global_flat.clone())
     assert float((outs[0] - outs[1]).abs().max()) < 4 * 4 / 2 ** 16 and not torch.equal(outs[0], outs[1])
+
+
+def test_fednas_train_stage_and_derived_network():
+    """After the search, FedNAS trains the derived network (reference model/cv/darts/model.py NetworkCIFAR, FedNASTrainer train
+    stage): published cells build, the full DARTS-V2 network has the paper's 3.35 M parameters, and a federated round runs with
+    the auxiliary head and drop path."""
+    from fedml_b200.models.darts import DARTS_V1, DARTS_V2, FedNAS_V1, Network, NetworkCIFAR, count_parameters_in_MB
+    assert abs(count_parameters_in_MB(NetworkCIFAR(36, 10, 20, True, DARTS_V2)) - 3.35) < 0.02
+    for g in (DARTS_V1, FedNAS_V1, Network(C=8, layers=3).genotype()):
+        net = NetworkCIFAR(8, 10, 5, True, g)
+        net.drop_path_prob = 0.3
+        logits, aux = net.train()(torch.randn(3, 3, 32, 32))
+        assert logits.shape == (3, 10) and aux.shape == (3, 10)
+        assert net.eval()(torch.randn(2, 3, 32, 32))[1] is None
+    a = mk(federated_optimizer="FedNAS", backend="MPI", worker_num=2, client_num_per_round=2, client_num_in_total=2, comm_round=2,
+           synthetic_train_size=32, batch_size=8, run_id="nas-train", dataset="cifar10", stage="train", arch="FedNAS_V1", layers=3,
+           init_channels=4, frequency_of_the_test=1)
+    ds, model = build(a)
+    r = SimulatorMPI(a, CPU, ds, model).run()
+    assert len(r.history) == 2 and np.isfinite(r.history[-1]["test_loss"]) and isinstance(r.trainer.model, NetworkCIFAR)
