@@ -88,6 +88,31 @@ def decode_comm_request(buf: bytes):
     return cid, msg
 
 
+class CommRequest:
+    """The reference's protobuf message (proto/grpc_comm_manager.proto:3-9) without generated code: same field names, same wire
+    bytes (``SerializeToString`` / ``FromString``), so code that builds requests by hand keeps working."""
+
+    def __init__(self, client_id: int = 0, message: bytes = b""):
+        self.client_id, self.message = int(client_id), bytes(message)
+
+    def SerializeToString(self) -> bytes:      # noqa: N802  (protobuf API)
+        return encode_comm_request(self.client_id, self.message)
+
+    @classmethod
+    def FromString(cls, data: bytes):          # noqa: N802
+        return cls(*decode_comm_request(data))
+
+    def __eq__(self, other):
+        return isinstance(other, CommRequest) and (self.client_id, self.message) == (other.client_id, other.message)
+
+    def __repr__(self):
+        return f"{type(self).__name__}(client_id={self.client_id}, message=<{len(self.message)} bytes>)"
+
+
+class CommResponse(CommRequest):
+    """Same two fields (grpc_comm_manager.proto:11-14)."""
+
+
 def pickle_like_reference(msg: Message) -> bytes:
     """``pickle.dumps`` of the message as the reference's class ``fedml.core...message.Message`` (same attributes: type,
     sender_id, receiver_id, msg_params), whatever module this class lives in: protocol-2 stream = GLOBAL class, NEWOBJ,
