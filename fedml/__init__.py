@@ -52,6 +52,18 @@ def _shim_module(fullname, entry):
     return mod
 
 
+def _install_fallback(real, fullname, names):
+    """Same-named module whose reference counterpart has names this one spells differently (``fedml.cli.cli.mlops_login``)."""
+    def __getattr__(name):
+        target = names.get(name)
+        if target is None or target.partition(":")[0] == real.__name__ and target.partition(":")[2] == name:
+            raise AttributeError(f"module {fullname!r} has no attribute {name!r}")
+        tmod, _, attr = target.partition(":")
+        return getattr(importlib.import_module(tmod), attr)
+
+    real.__getattr__ = __getattr__
+
+
 class _AliasFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
     def find_spec(self, fullname, path=None, target=None):
         if not fullname.startswith("fedml."):
@@ -61,6 +73,8 @@ class _AliasFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
             real = importlib.import_module(_target(fullname))
             if entry is not None and entry["pkg"] and not hasattr(real, "__path__"):
                 real.__path__ = []              # a package in the reference, one module here: sub-module imports go through the table
+            if entry is not None and entry["names"] and "__getattr__" not in vars(real):
+                _install_fallback(real, fullname, entry["names"])
         except ImportError:
             if entry is None:
                 return None
