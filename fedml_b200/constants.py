@@ -5,6 +5,7 @@ existing ``fedml_config.yaml`` files keep working, and adds the names the refere
 advertises but never wires (FedNova, robust aggregators, Cheetah).
 """
 
+FEDML_DATA_CACHE_FOLDER = "fedml_data"
 FEDML_TRAINING_PLATFORM_SIMULATION = "simulation"
 FEDML_TRAINING_PLATFORM_CROSS_SILO = "cross_silo"
 FEDML_TRAINING_PLATFORM_CROSS_DEVICE = "cross_device"

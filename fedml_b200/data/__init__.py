@@ -217,6 +217,28 @@ def split_data_for_dist_trainers(batches, n_dist_trainer):
     return [batches[i::n] for i in range(n)]
 
 
+def split_array(array, n_dist_trainer):
+    """Contiguous chunks of a batch list, the last batch repeated until the length divides (data_loader_cross_silo.py:9-19)."""
+    array, n = list(array), max(1, int(n_dist_trainer))
+    while len(array) % n:
+        array.append(array[-1])
+    size = len(array) // n
+    return [array[i * size:(i + 1) * size] for i in range(n)]
+
+
+def split_dl(dl, n_dist_trainer):
+    """One DataLoader per process of a silo over a DistributedSampler (data_loader_cross_silo.py:22-47)."""
+    from torch.utils import data as tud
+    shuffle = isinstance(dl.sampler, tud.RandomSampler)
+    return [tud.DataLoader(dl.dataset, batch_size=dl.batch_size, drop_last=dl.drop_last,
+                           sampler=tud.distributed.DistributedSampler(dl.dataset, num_replicas=int(n_dist_trainer), rank=r, shuffle=shuffle))
+            for r in range(int(n_dist_trainer))]
+
+
+def load_synthetic_data_cross_silo(args):
+    return load_cross_silo(args)
+
+
 def load_cross_silo(args):
     """Like :func:`load`, but each client's train data becomes a list indexed by
     ``proc_rank_in_silo`` when the silo runs several trainer processes (hierarchical scenario)."""

@@ -35,3 +35,7 @@ def init_logs(args, role=None):
         root.addHandler(fh)
         return path
     return None
+
+
+log_levels = {"debug": logging.DEBUG, "info": logging.INFO, "warning": logging.WARNING, "error": logging.ERROR, "critical": logging.CRITICAL}
+logger = logging.getLogger("FedML")          # module-level logger of the reference (utils/logging.py:33)
