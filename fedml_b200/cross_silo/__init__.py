@@ -29,3 +29,11 @@ class Client:
 
 
 __all__ = ["Client", "Server", "FedML_Horizontal"]
+
+
+def __getattr__(name):
+    """``fedml.cross_silo.hierarchical`` without importing torch.distributed at package import time."""
+    if name in ("hierarchical", "horizontal"):
+        import importlib
+        return importlib.import_module(f"{__name__}.{name}")
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
