@@ -95,7 +95,13 @@ def topic_matches(filt: str, topic: str) -> bool:
 class LocalBroker:
     """Threaded MQTT 3.1.1 broker: ``start()`` returns the bound port; ``stop()`` closes everything."""
 
-    def __init__(self, host="127.0.0.1", port=0):
+    def __init__(self, host="127.0.0.1", port=0, certfile=None, keyfile=None):
+        """``certfile`` / ``keyfile``: serve MQTT over TLS (the 8883 flavour) with this certificate chain and private key."""
+        self._tls = None
+        if certfile:
+            import ssl
+            self._tls = ssl.SSLContext(ssl.PROTOCOL_TLS_SERVER)
+            self._tls.load_cert_chain(certfile, keyfile)
         self._srv = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
         self._srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
         self._srv.bind((host, port))
@@ -116,6 +122,12 @@ class LocalBroker:
             except OSError:
                 return
             conn.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+            if self._tls is not None:
+                try:
+                    conn = self._tls.wrap_socket(conn, server_side=True)
+                except (OSError, ValueError):          # failed handshake (plain-text client, unknown CA): drop the connection
+                    conn.close()
+                    continue
             threading.Thread(target=self._serve, args=(conn,), daemon=True).start()
 
     def _send(self, conn, data: bytes):
@@ -220,12 +232,20 @@ class BrokerClient:
     """Minimal MQTT 3.1.1 client.  ``on_message(topic, payload_bytes)`` runs on the network thread."""
 
     def __init__(self, host="127.0.0.1", port=1883, client_id="", will_topic=None, will_payload=None, keepalive=0,
-                 username=None, password=None):
+                 username=None, password=None, tls=False, ca_certs=None, tls_insecure=False):
+        """``tls`` (or a ``ca_certs`` bundle path): MQTT over TLS; the server certificate is verified against ``ca_certs`` (the
+        system store when None) unless ``tls_insecure``."""
         self.client_id = client_id
         self.on_message: Optional[Callable[[str, bytes], None]] = None
         self.on_connect: Optional[Callable[[], None]] = None
         self._sock = socket.create_connection((host, int(port)), timeout=30)
         self._sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+        if tls or ca_certs:
+            import ssl
+            ctx = ssl.create_default_context(cafile=ca_certs)
+            if tls_insecure:
+                ctx.check_hostname, ctx.verify_mode = False, ssl.CERT_NONE
+            self._sock = ctx.wrap_socket(self._sock, server_hostname=host)
         self._wlock = threading.Lock()
         self._acks: Dict[int, threading.Event] = {}
         self._pid = 0

@@ -29,6 +29,13 @@ from .remote_storage import create_store
 _STOP = object()
 
 
+def _tls_kwargs(args):
+    """``mqtt_tls: true`` / ``mqtt_ca_certs: <bundle>`` / ``mqtt_tls_insecure: true`` in the YAML -> TLS options of the native client."""
+    if not (getattr(args, "mqtt_tls", False) or getattr(args, "mqtt_ca_certs", None)) or str(getattr(args, "mqtt_client", "auto")).lower() == "paho":
+        return {}
+    return {"tls": True, "ca_certs": getattr(args, "mqtt_ca_certs", None), "tls_insecure": bool(getattr(args, "mqtt_tls_insecure", False))}
+
+
 def _broker_endpoint(args):
     host, port = getattr(args, "mqtt_host", "127.0.0.1"), int(getattr(args, "mqtt_port", 1883))
     path = getattr(args, "mqtt_config_path", None)
@@ -53,7 +60,7 @@ class _MqttBase(BaseCommunicationManager):
                                                  if self.rank - 1 < len(self.client_real_ids) else self.rank)
         host, port = _broker_endpoint(args)
         self._client = make_client(host, port, kind=getattr(args, "mqtt_client", "auto"), client_id=f"{self.run_id}-{self.edge_id}", will_topic="W/topic",
-                                    will_payload={"ID": self.edge_id, "stat": "Online"})
+                                    will_payload={"ID": self.edge_id, "stat": "Online"}, **_tls_kwargs(args))
         self._client.on_message = self._on_message
         if self.rank == 0:
             for cid in self.client_real_ids:
@@ -170,7 +177,7 @@ class MqttS3StatusManager:
     def __init__(self, args, topic="fedml_status"):
         host, port = _broker_endpoint(args)
         self._client = make_client(host, port, kind=getattr(args, "mqtt_client", "auto"),
-                                   client_id=f"status-{getattr(args, 'run_id', 0)}-{uuid.uuid4().hex[:6]}")
+                                   client_id=f"status-{getattr(args, 'run_id', 0)}-{uuid.uuid4().hex[:6]}", **_tls_kwargs(args))
         self._client.on_message = self._on_message
         self._observers = []
 

@@ -644,3 +644,62 @@ def test_interface_helpers_context_manager_timer_and_mixing_matrix(tmp_path):
     w = topo.mixing_matrix()
     assert w.shape == (6, 6) and topo.is_row_stochastic() and np.allclose(w, w.T)
     assert sorted(j for j, _ in topo.in_neighbors(0)) == sorted(topo.get_in_neighbor_idx_list(0))
+
+
+def test_mqtt_over_tls_with_a_self_signed_certificate(tmp_path):
+    """MQTT 3.1.1 over TLS (the 8883 flavour): bundled broker with a certificate, native client verifying it against a CA bundle;
+    a client that trusts another CA is refused, and the MQTT comm manager takes the options from the YAML keys."""
+    import datetime
+    import ssl
+    from cryptography import x509
+    from cryptography.hazmat.primitives import hashes, serialization
+    from cryptography.hazmat.primitives.asymmetric import rsa
+    from cryptography.x509.oid import NameOID
+    import ipaddress
+
+    def self_signed(prefix):
+        key = rsa.generate_private_key(public_exponent=65537, key_size=2048)
+        name = x509.Name([x509.NameAttribute(NameOID.COMMON_NAME, "127.0.0.1")])
+        now = datetime.datetime.now(datetime.timezone.utc)
+        cert = (x509.CertificateBuilder().subject_name(name).issuer_name(name).public_key(key.public_key())
+                .serial_number(x509.random_serial_number()).not_valid_before(now - datetime.timedelta(minutes=5))
+                .not_valid_after(now + datetime.timedelta(days=1))
+                .add_extension(x509.SubjectAlternativeName([x509.IPAddress(ipaddress.ip_address("127.0.0.1"))]), critical=False)
+                .add_extension(x509.BasicConstraints(ca=True, path_length=None), critical=True).sign(key, hashes.SHA256()))
+        c, k = tmp_path / f"{prefix}.crt", tmp_path / f"{prefix}.key"
+        c.write_bytes(cert.public_bytes(serialization.Encoding.PEM))
+        k.write_bytes(key.private_bytes(serialization.Encoding.PEM, serialization.PrivateFormat.TraditionalOpenSSL, serialization.NoEncryption()))
+        return str(c), str(k)
+
+    crt, key = self_signed("broker")
+    other_crt, _ = self_signed("other")
+    b = LocalBroker(certfile=crt, keyfile=key)
+    port = b.start()
+    got = threading.Event()
+    sub = BrokerClient("127.0.0.1", port, "tls-sub", ca_certs=crt)
+    sub.on_message = lambda t, p: got.set() if (t, p) == ("a/b", b"secret") else None
+    sub.subscribe("a/#")
+    pub = BrokerClient("127.0.0.1", port, "tls-pub", ca_certs=crt)
+    pub.publish("a/b", b"secret")
+    assert got.wait(10)
+    with pytest.raises((ssl.SSLError, ConnectionError, OSError)):
+        BrokerClient("127.0.0.1", port, "tls-bad", ca_certs=other_crt)
+    # through the comm manager: YAML keys mqtt_tls / mqtt_ca_certs
+    base = dict(backend="MQTT", mqtt_host="127.0.0.1", mqtt_port=port, mqtt_tls=True, mqtt_ca_certs=crt, run_id="tlsrun", client_id_list="[1]",
+                client_num_per_round=1)
+    srv = create_comm_manager(Arguments.from_dict(dict(base, rank=0)), 0, 2, "MQTT")
+    cli = create_comm_manager(Arguments.from_dict(dict(base, rank=1)), 1, 2, "MQTT")
+    seen = threading.Event()
+
+    class Obs(Observer):
+        def receive_message(self, t, p):
+            if t == 9:
+                seen.set()
+
+    srv.add_observer(Obs())
+    threading.Thread(target=srv.handle_receive_message, daemon=True).start()
+    time.sleep(0.3)
+    m = Message(9, 1, 0); m.add_params("x", 1)
+    cli.send_message(m)
+    assert seen.wait(10)
+    srv.stop_receive_message(); cli.stop_receive_message(); sub.disconnect(); pub.disconnect(); b.stop()
