@@ -139,6 +139,16 @@ class SysStats:
         return info
 
 
+CA_BUNDLE = None      # path of a certificate bundle for https:// endpoints (the reference ships one per platform version under
+#                       core/mlops/ssl/ and points requests at it: mlops_configs.py:50-56); None = the system trust store
+
+
+def set_ca_bundle(path):
+    """``args.mlops_ca_bundle`` / ``FEDML_CA_BUNDLE``: verify the MLOps https endpoints against this bundle."""
+    global CA_BUNDLE
+    CA_BUNDLE = path or None
+
+
 def _post_json(url: str, obj: dict, timeout: float = 10.0) -> dict:
     """POST a JSON document; ``file://path`` appends it as one line to a local file (offline sink)."""
     import json
@@ -151,7 +161,13 @@ def _post_json(url: str, obj: dict, timeout: float = 10.0) -> dict:
         return {"code": "SUCCESS"}
     import urllib.request
     req = urllib.request.Request(url, data=json.dumps(obj).encode(), headers={"Content-Type": "application/json", "Connection": "close"})
-    with urllib.request.urlopen(req, timeout=timeout) as resp:
+    ctx = None
+    import os as _os
+    bundle = CA_BUNDLE or _os.environ.get("FEDML_CA_BUNDLE")
+    if url.startswith("https://") and bundle:
+        import ssl
+        ctx = ssl.create_default_context(cafile=bundle)
+    with urllib.request.urlopen(req, timeout=timeout, context=ctx) as resp:
         body = resp.read().decode() or "{}"
         if resp.status != 200:
             raise OSError(f"HTTP {resp.status}")
