@@ -54,14 +54,44 @@ class FedMLAggregatorMNN:
         return client_sampling(round_idx, total, per_round)
 
     def test_on_server_for_all_clients(self, round_idx):
-        load_into_module(self.global_model_file_path, self.model)
-        self.model.to(self.device).eval()
+        # the reference evaluates the global .mnn file with the MNN runtime (fedml_aggregator.py:169-228); here the graph is
+        # executed by mnn_format.run_graph when it consists of supported ops, else its parameters are loaded into the
+        # equivalent torch module
+        from . import mnn_format as MF
+        graph_ops = None
+        try:
+            graph_ops = MF.describe(self.global_model_file_path)
+            convs = [o for o in graph_ops if o["type"] == MF.OP_CONV]
+            if not any(o["type"] not in (MF.OP_TRAINABLE_PARAM, MF.OP_INPUT) for o in graph_ops):
+                graph_ops = None                       # parameters-only file: nothing to execute
+        except (MF.MnnFormatError, Exception):  # noqa: BLE001  (legacy container, unreadable file)
+            graph_ops = None
+        if graph_ops is None:
+            load_into_module(self.global_model_file_path, self.model)
+            self.model.to(self.device).eval()
+        self.eval_engine = "mnn_graph" if graph_ops is not None else "torch_module"
         correct = loss = total = 0.0
         with torch.no_grad():
             for x, y in self.test_global:
-                out = self.model(x.to(self.device))
-                loss += float(torch.nn.functional.cross_entropy(out, y.to(self.device), reduction="sum"))
-                correct += float((out.argmax(1).cpu() == y).sum()); total += len(y)
+                if graph_ops is not None:
+                    xin = x.float()
+                    if convs:                           # NCHW input of the first convolution
+                        cin = convs[0]["conv"]["in"]
+                        side = int(round((xin[0].numel() / cin) ** 0.5))
+                        xin = xin.reshape(len(xin), cin, side, side)
+                    try:
+                        probs = MF.run_graph(self.global_model_file_path, xin)
+                    except MF.MnnFormatError:
+                        graph_ops, self.eval_engine = None, "torch_module"
+                        load_into_module(self.global_model_file_path, self.model)
+                        self.model.to(self.device).eval()
+                if graph_ops is not None:
+                    out = probs.clamp_min(1e-12).log()       # the graph ends in a softmax
+                    loss += float(torch.nn.functional.nll_loss(out, y, reduction="sum"))
+                else:
+                    out = self.model(x.to(self.device)).cpu()
+                    loss += float(torch.nn.functional.cross_entropy(out, y, reduction="sum"))
+                correct += float((out.argmax(1) == y).sum()); total += len(y)
         stats = {"round": round_idx, "test_acc": correct / max(total, 1), "test_loss": loss / max(total, 1)}
         self.history.append(stats)
         logging.info("%s", stats)

@@ -165,6 +165,14 @@ def describe(path: str) -> List[dict]:
             if e["main_type"] == PARAM_POOL:
                 iv = lambda i, dflt: r.i32(r.field(m, i)) if r.field(m, i) is not None else dflt      # noqa: E731
                 e["pool"] = {"kernel": [iv(4, 0), iv(3, 0)], "stride": [iv(6, 0), iv(5, 0)]}
+                e["pool_type"] = r.d[r.field(m, 7)] if r.field(m, 7) is not None else 0          # 0 max, 1 average
+            if e["main_type"] == PARAM_MATMUL:
+                e["transpose_a"] = bool(r.d[r.field(m, 1)]) if r.field(m, 1) is not None else False
+                e["transpose_b"] = bool(r.d[r.field(m, 2)]) if r.field(m, 2) is not None else False
+            if e["main_type"] == PARAM_AXIS:
+                e["axis"] = r.i32(r.field(m, 0)) if r.field(m, 0) is not None else 0
+            if e["main_type"] == PARAM_BINARY:
+                e["binary_op"] = r.i32(r.field(m, 0)) if r.field(m, 0) is not None else 0        # 0 add, 1 sub, 2 mul
         ops.append(e)
     return ops
 
@@ -357,3 +365,54 @@ def build_params_only(path: str, named: "OrderedDict[str, np.ndarray]") -> str:
     for k, v in named.items():
         g.param(np.asarray(v, dtype=np.float32), name=k)
     return g.save(path)
+
+
+# ------------------------------------------------------------------------------------------------ executing
+def run_graph(path: str, x, params: Optional[Sequence] = None):
+    """Evaluates an MNN graph made of the ops listed in the module docstring on a torch tensor ``x`` (NCHW) and returns the
+    output of the last op - the server-side evaluation the reference does with the MNN runtime
+    (cross_device/server_mnn/fedml_aggregator.py:169-228), for the graphs this module can build and the LeNet-5 / logistic
+    regression files a device SDK writes.  ``params``: optional replacement values for the trainable parameters, graph order.
+    Raises :class:`MnnFormatError` on an op outside that set."""
+    import torch
+    import torch.nn.functional as F
+    ops = describe(path)
+    stored = iter(read_params(path).values()) if params is None else iter(params)
+    vals: Dict[int, "torch.Tensor"] = {}
+    out = None
+    for o in ops:
+        t, ins = o["type"], [vals[i] for i in o["inputs"]]
+        if t == OP_INPUT:
+            out = x.float()
+        elif t == OP_TRAINABLE_PARAM:
+            out = torch.as_tensor(np.asarray(next(stored)), dtype=torch.float32).reshape(o["dims"])
+        elif t == OP_CONVERT_TENSOR:
+            out = ins[0]                                   # NC4HW4 <-> NCHW is a storage matter of the device runtime
+        elif t == OP_CONV:
+            c = o["conv"]
+            kh, kw = c["kernel"]
+            pad = (kh // 2, kw // 2) if c["pad_mode"] == 2 else 0
+            out = F.conv2d(ins[0], ins[1], ins[2].reshape(-1) if len(ins) > 2 else None, stride=tuple(c["stride"]), padding=pad)
+        elif t == OP_RELU:
+            out = torch.relu(ins[0])
+        elif t == OP_POOLING:
+            pool = F.max_pool2d if o.get("pool_type", 0) == 0 else F.avg_pool2d
+            out = pool(ins[0], tuple(o["pool"]["kernel"]), tuple(o["pool"]["stride"]))
+        elif t == OP_RESHAPE:
+            dims = [ins[0].shape[i] if d == 0 else d for i, d in enumerate(o["dims"])]
+            out = ins[0].reshape(dims)
+        elif t == OP_MATMUL:
+            a, b = ins
+            out = (a.transpose(-1, -2) if o.get("transpose_a") else a) @ (b.transpose(-1, -2) if o.get("transpose_b") else b)
+        elif t == OP_BINARY:
+            op = o.get("binary_op", 0)
+            out = ins[0] + ins[1] if op == 0 else ins[0] - ins[1] if op == 1 else ins[0] * ins[1] if op == 2 else None
+            if out is None:
+                raise MnnFormatError(f"BinaryOp type {op} is not supported")
+        elif t == OP_SOFTMAX:
+            out = torch.softmax(ins[0], dim=o.get("axis", 1))
+        else:
+            raise MnnFormatError(f"op {o['name']!r} (type {t}) is outside the supported set")
+        for idx in o["outputs"]:
+            vals[idx] = out
+    return out

@@ -195,7 +195,7 @@ def test_cross_device_server_with_file_models(broker, tmp_path):
     [threading.Thread(target=p.cm.handle_receive_message, daemon=True).start() for p in phones]
     init = {k: v.clone() for k, v in model.state_dict().items()}
     agg = srv.run()
-    assert len(agg.history) == 2
+    assert len(agg.history) == 2 and agg.eval_engine == "mnn_graph" and np.isfinite(agg.history[-1]["test_loss"])
     final = list(read_mnn_like(str(tmp_path / "global.mnn")).values())
     # two rounds of (+0.01*1 weighted 10, +0.01*2 weighted 20) => +2 * 0.01 * 5/3; the last parameter of the MNN graph is fc2's bias
     torch.testing.assert_close(final[-1].reshape(-1), init["fc2.bias"] + 2 * 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)
@@ -240,6 +240,12 @@ def test_mnn_format_builder_reader_and_in_place_writer(tmp_path):
     write_mnn_like(str(tmp_path / "lr.mnn"), lr.state_dict())
     assert [o["type"] for o in MF.describe(str(tmp_path / "lr.mnn"))] == [MF.OP_INPUT, MF.OP_RESHAPE, MF.OP_TRAINABLE_PARAM, MF.OP_MATMUL,
                                                                           MF.OP_TRAINABLE_PARAM, MF.OP_BINARY, MF.OP_SOFTMAX]
+    # executing the graph = the torch module's forward (softmax on top)
+    x = torch.randn(4, 1, 28, 28)
+    MF.write_params(path, list(got.values()))
+    with torch.no_grad():
+        torch.testing.assert_close(MF.run_graph(path, x), torch.softmax(net(x), 1), rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(MF.run_graph(str(tmp_path / "lr.mnn"), x), torch.softmax(lr(x.flatten(1)), 1), rtol=1e-5, atol=1e-6)
     fedml.model.create_mnn_resnet20_model(str(tmp_path / "r20.mnn"))
     sd = read_mnn_like(str(tmp_path / "r20.mnn"))
     assert "layer1.0.conv1.weight" in sd and sd["fc.weight"].shape == (10, 64)
@@ -263,6 +269,11 @@ def test_mnn_format_against_files_written_by_the_mnn_sdk(tmp_path):
         again = MF.read_params(out)
         assert list(again) == list(params) and all((v == 0.25).all() for v in again.values())
         assert os.path.getsize(out) == os.path.getsize(src) and MF.describe(out) == MF.describe(src)
+    import torch
+    probs = MF.run_graph(REF_MNN, torch.randn(3, 1, 28, 28))          # the LeNet file the MNN SDK wrote executes here
+    assert probs.shape == (3, 10) and torch.allclose(probs.sum(1), torch.ones(3), atol=1e-5)
+    with pytest.raises(MF.MnnFormatError):                            # the ResNet-20 training graph uses ops outside the set
+        MF.run_graph(REF_MNN_RESNET, torch.randn(1, 3, 32, 32))
 
 
 def test_mpc_toolbox_and_secure_aggregation():
