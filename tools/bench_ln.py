@@ -1,3 +1,4 @@
+"""Micro-benchmark of the fused add + LayerNorm forward / backward kernels at DistilBERT shapes against torch.nn.functional.layer_norm."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
