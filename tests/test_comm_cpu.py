@@ -714,3 +714,21 @@ def test_mqtt_over_tls_with_a_self_signed_certificate(tmp_path):
     cli.send_message(m)
     assert seen.wait(10)
     srv.stop_receive_message(); cli.stop_receive_message(); sub.disconnect(); pub.disconnect(); b.stop()
+
+
+def test_callback_and_mailbox_observers():
+    from fedml_b200.core.distributed.communication.observer import CallbackObserver, MailboxObserver, Observer
+    seen = []
+    cb = CallbackObserver(lambda t, p: seen.append((t, p)))
+    box = MailboxObserver()
+    assert isinstance(cb, Observer) and isinstance(box, Observer)
+    cb.receive_message(3, {"a": 1})
+    assert seen == [(3, {"a": 1})]
+    threading.Timer(0.05, box.receive_message, args=(7, "late")).start()
+    box.receive_message(5, "first")
+    box.receive_message(5, "second")
+    assert box.pending() == 2 and box.pending(5) == 2 and box.pending(7) == 0
+    assert box.get(5) == "first" and box.get(7, timeout=2.0) == "late" and box.get(5, 0.1) == "second"
+    with pytest.raises(TimeoutError):
+        box.get(9, timeout=0.05)
+    assert box.received == 3

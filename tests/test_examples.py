@@ -67,3 +67,8 @@ def test_cross_silo_grpc_example_three_processes(tmp_path):
                 p.kill()
     assert all(p.returncode == 0 for p in procs), "\n----\n".join(o[-800:] for o in outs)
     assert os.path.exists(d / "model_file_cache" / "global_model.pt")
+
+
+def test_shipped_configs_are_in_the_documented_layout():
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "annotate_configs.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
