@@ -147,11 +147,14 @@ def load_federated(args) -> FederatedDataset:
     elif name == "shakespeare" and os.path.isdir(os.path.join(cache, "shakespeare", "train")):
         from . import readers as R
         ds = R.load_leaf_shakespeare(cache)
-    elif name in ("fed_shakespeare", "stackoverflow_nwp", "stackoverflow_lr") and any(
-            os.path.isfile(os.path.join(cache, f)) for f in ("shakespeare_train.h5", "stackoverflow_train.h5")):
+    elif name == "fed_shakespeare" and os.path.isfile(os.path.join(cache, "shakespeare_train.h5")):
         from . import readers as R
-        R.need_h5py(os.path.join(cache, "shakespeare_train.h5" if name == "fed_shakespeare" else "stackoverflow_train.h5"))
-        raise NotImplementedError(f"{name}: TFF .h5 text exports need h5py plus the reference's tokeniser tables")
+        ds = R.load_tff_shakespeare_h5(os.path.join(cache, "shakespeare_train.h5"), os.path.join(cache, "shakespeare_test.h5"),
+                                       int(getattr(args, "shakespeare_client_num", 0)))
+    elif name in ("stackoverflow_nwp", "stackoverflow_lr") and os.path.isfile(os.path.join(cache, "stackoverflow_train.h5")):
+        from . import readers as R
+        ds = R.load_tff_stackoverflow_h5(cache, "nwp" if name.endswith("nwp") else "lr",
+                                         int(getattr(args, "stackoverflow_client_num", 1000 if name.endswith("nwp") else 200)))
     elif name in ("shakespeare", "fed_shakespeare"):
         ds = S.make_char_lm(715 if not small else max(4, small // 64), 80, 90, 64, seed, name,
                             next_token_only=(name == "shakespeare"))

@@ -1,0 +1,162 @@
+"""Pure-Python HDF5 reader / writer and the TFF .h5 dataset readers built on it."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from fedml_b200.arguments import Arguments
+from fedml_b200.data import minihdf5 as H
+from fedml_b200.data import readers as R
+from fedml_b200.data import synthetic as S
+from fedml_b200.data import tff_export
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_reads_a_file_written_by_the_hdf5_library():
+    """scipy ships a MATLAB v7.3 file = an HDF5 file behind a 512-byte user block, written by the C library."""
+    import scipy.io
+    path = os.path.join(os.path.dirname(scipy.io.__file__), "matlab", "tests", "data", "testhdf5_7.4_GLNX86.mat")
+    if not os.path.isfile(path):
+        pytest.skip("scipy test data not installed")
+    with H.File(path) as f:
+        assert f.keys() == ["testdouble"]
+        d = f["testdouble"]
+        assert d.shape == (9, 1) and d.dtype == np.dtype("<f8")
+        np.testing.assert_allclose(d[()].ravel(), np.arange(9) * np.pi / 4, rtol=1e-15)
+        assert d.attrs["MATLAB_class"] == b"double"
+        assert np.asarray(d).shape == (9, 1) and d[2:4, 0].tolist() == [np.pi / 2, 3 * np.pi / 4]
+
+
+def test_write_read_round_trip_of_every_supported_storage_form(tmp_path):
+    rs = np.random.RandomState(0)
+    clients = {f"c{i:04d}": {"pixels": rs.rand(1 + i % 4, 5, 5).astype(np.float32), "label": rs.randint(0, 62, (1 + i % 4,)).astype(np.int32)}
+               for i in range(300)}                                   # 300 links: three levels of the group B-tree
+    img = rs.randint(0, 255, (37, 19, 3)).astype(np.uint8)
+    big = np.arange(70 * 40, dtype=np.int64).reshape(70, 40)       # 70 chunks: two levels of the chunk B-tree
+    words = ["hello world", "", "Ünïcode ✓", "x" * 5000]
+    tree = {"examples": clients, "text": {"snippets": words, "raw": [b"ab", b"cde"]},
+            "img": H.H5Data(img, chunks=(8, 8, 3), compression=4, shuffle=True),
+            "big": H.H5Data(big, chunks=(1, 40), compression=1), "plain_chunks": H.H5Data(big.astype(np.float64), chunks=(16, 16)),
+            "f16": np.linspace(0, 1, 7).astype(np.float16), "i16": np.array([[1, -2], [3, 4]], dtype=np.int16),
+            "u64": np.array([2 ** 63 + 5], dtype=np.uint64), "fixed": np.array([b"ab", b"cdef"]), "flag": np.array([True, False]),
+            "scalar": np.float32(3.5), "empty_group": {}, "empty_data": np.zeros((0, 4), np.float32),
+            "chunked_text": H.H5Data([f"s{i}" for i in range(10)], chunks=(4,), compression=6)}
+    path = H.write_hdf5(str(tmp_path / "t.h5"), tree)
+    with H.File(path) as f:
+        assert f.keys() == sorted(tree) and len(f["examples"]) == 300 and "c0007" in f["examples"] and "nope" not in f
+        assert f["examples"].keys() == sorted(clients)
+        for k in ("c0000", "c0008", "c0150", "c0299"):
+            np.testing.assert_array_equal(f["examples"][k]["pixels"][()], clients[k]["pixels"])
+            np.testing.assert_array_equal(f[f"/examples/{k}/label"][()], clients[k]["label"])
+        assert [b.decode("utf8") for b in f["text/snippets"][()]] == words
+        assert list(f["text/snippets"].asstr()) == words and list(f["text"]["raw"][()]) == [b"ab", b"cde"]
+        np.testing.assert_array_equal(f["img"][()], img)
+        np.testing.assert_array_equal(f["big"][()], big)
+        np.testing.assert_array_equal(f["big"][3:5], big[3:5])
+        np.testing.assert_array_equal(f["plain_chunks"][()], big.astype(np.float64))
+        np.testing.assert_array_equal(f["f16"][()], tree["f16"])
+        np.testing.assert_array_equal(f["i16"][()], tree["i16"])
+        assert f["u64"][()][0] == 2 ** 63 + 5 and f["fixed"][()].tolist() == [b"ab", b"cdef"] and f["flag"][()].tolist() == [1, 0]
+        assert f["scalar"][()] == np.float32(3.5) and f["scalar"].shape == ()
+        assert f["empty_group"].keys() == [] and f["empty_data"][()].shape == (0, 4)
+        assert [b.decode() for b in f["chunked_text"][()]] == [f"s{i}" for i in range(10)]
+        seen = []
+        f["text"].visit(seen.append)
+        assert seen == ["raw", "snippets"]
+        with pytest.raises(KeyError):
+            f["examples"]["c9999"]
+    with pytest.raises(H.Hdf5Error):
+        (tmp_path / "junk.h5").write_bytes(b"not an hdf5 file at all" * 10)
+        H.File(str(tmp_path / "junk.h5"))
+
+
+def _args(**kw):
+    base = dict(dataset="femnist", batch_size=8, client_num_in_total=6, client_num_per_round=2, log_level="WARNING")
+    base.update(kw)
+    return Arguments.from_dict(base)
+
+
+def test_fed_emnist_and_fed_cifar100_files_load_through_the_public_loader(tmp_path):
+    import fedml_b200
+    src = S.make_femnist_like(client_num=6, seed=1, total_train=240)
+    d = tmp_path / "femnist"
+    paths = tff_export.export("femnist", src, str(d))
+    assert [os.path.basename(p) for p in paths] == ["fed_emnist_train.h5", "fed_emnist_test.h5"]
+    ds, classes = fedml_b200.data.load(_args(data_cache_dir=str(d)))
+    fed = fedml_b200.data.load_federated(_args(data_cache_dir=str(d)))
+    assert classes == 62 and fed.client_num == 6 and fed.name == "femnist"
+    np.testing.assert_array_equal(fed.client_offsets, src.client_offsets)
+    np.testing.assert_allclose(fed.x.reshape(len(fed.x), -1).numpy(), src.x.reshape(len(src.x), -1).numpy())
+    np.testing.assert_array_equal(fed.y.numpy(), src.y.numpy())
+    assert ds[0] == len(src.x)
+
+    src = S.make_cifar_like(5, "hetero", 0.5, 100, 200, 50, 32, 0, "fed_cifar100", S.CIFAR100_MEAN, S.CIFAR100_STD)
+    d = tmp_path / "fc100"
+    tff_export.export("fed_cifar100", src, str(d))
+    fed = fedml_b200.data.load_federated(_args(dataset="fed_cifar100", data_cache_dir=str(d)))
+    assert fed.client_num == 5 and fed.x.dtype == torch.uint8 and tuple(fed.x.shape[1:]) == (32, 32, 3)
+    np.testing.assert_array_equal(fed.x.numpy(), src.x.numpy())
+    np.testing.assert_array_equal(fed.y.numpy(), src.y.numpy())
+
+
+def test_fed_shakespeare_snippets_become_81_id_rows(tmp_path):
+    import fedml_b200
+    snippets = {"PLAY_A": ["Yonder comes my master, your brother.", "x" * 100], "PLAY_B": ["Is 'old dog' my reward? ~"]}
+    for split in ("train", "test"):
+        H.write_hdf5(str(tmp_path / f"shakespeare_{split}.h5"), {"examples": {k: {"snippets": v} for k, v in snippets.items()}})
+    fed = fedml_b200.data.load_federated(_args(dataset="fed_shakespeare", data_cache_dir=str(tmp_path)))
+    table = {c: i + 1 for i, c in enumerate(R.CHAR_VOCAB)}
+    assert fed.class_num == 90 and fed.client_num == 2 and fed.task == "nwp"
+    assert fed.client_offsets.tolist() == [0, 1 + 2, 4]               # 39 ids -> 1 row; 102 ids -> 2 rows; 28 ids -> 1 row
+    first = [87] + [table[c] for c in snippets["PLAY_A"][0]] + [88]
+    row = first + [0] * (81 - len(first))
+    assert fed.x[0].tolist() == row[:-1] and fed.y[0].tolist() == row[1:]
+    second = [87] + [table["x"]] * 100 + [88]
+    assert fed.x[1].tolist() == second[:80] and fed.x[2].tolist()[:21] == second[81:] and fed.x[2].tolist()[21:] == [0] * 59
+    assert fed.x[3].tolist()[-4:-1] == [0, 0, 0] and 89 in fed.x[3].tolist()      # "~" is out of vocabulary
+    # the exporter's inverse table round-trips plain text
+    assert tff_export.ids_to_snippet(first) == snippets["PLAY_A"][0]
+
+
+def test_stackoverflow_next_word_and_tag_prediction_from_h5(tmp_path):
+    import fedml_b200
+    vocab = [f"w{i}" for i in range(10000)]
+    (tmp_path / "stackoverflow.word_count").write_text("".join(f"{w} {20000 - i}\n" for i, w in enumerate(vocab)) + "rare 1\n")
+    (tmp_path / "stackoverflow.tag_count").write_text(json.dumps({f"t{i}": 1000 - i for i in range(600)}))
+    clients = {"00001": {"tokens": ["w0 w5 zzz", " ".join(["w1"] * 25)], "title": ["w7", "w2 w2"], "tags": ["t0|t499|t599", "t3"]},
+               "00002": {"tokens": ["w9999"], "title": [""], "tags": ["nothing"]}}
+    for split in ("train", "test"):
+        H.write_hdf5(str(tmp_path / f"stackoverflow_{split}.h5"), {"examples": clients})
+    fed = fedml_b200.data.load_federated(_args(dataset="stackoverflow_nwp", data_cache_dir=str(tmp_path)))
+    assert fed.class_num == 10004 and fed.client_offsets.tolist() == [0, 2, 3] and tuple(fed.x.shape) == (3, 20)
+    row = [10001, 1, 6, 10003, 10002] + [0] * 16                      # <bos> w0 w5 oov <eos> pad...
+    assert fed.x[0].tolist() == row[:-1] and fed.y[0].tolist() == row[1:]
+    assert fed.x[1].tolist() == [10001] + [2] * 19 and fed.y[1].tolist() == [2] * 20        # 20 words: no <eos>
+    assert fed.x[2].tolist()[:3] == [10001, 10000, 10002]
+
+    fed = fedml_b200.data.load_federated(_args(dataset="stackoverflow_lr", data_cache_dir=str(tmp_path)))
+    assert tuple(fed.x.shape) == (3, 10000) and tuple(fed.y.shape) == (3, 500) and fed.task == "tag_prediction"
+    x0 = fed.x[0]
+    assert x0[0] == 0.25 and x0[5] == 0.25 and x0[7] == 0.25 and float(x0.sum()) == 0.75        # 4 words, one unknown
+    assert abs(float(fed.x[1][1]) - 25 / 27) < 1e-6 and abs(float(fed.x[1][2]) - 2 / 27) < 1e-6
+    assert fed.y[0].nonzero().flatten().tolist() == [0, 499] and fed.y[1].nonzero().flatten().tolist() == [3] and fed.y[2].sum() == 0
+
+
+def test_export_tool_and_stackoverflow_round_trip(tmp_path):
+    out = tmp_path / "so"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "export_tff_h5.py"), "stackoverflow_nwp", str(out), "--clients", "12"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-800:]
+    assert sorted(os.listdir(out)) == ["stackoverflow.tag_count", "stackoverflow.word_count", "stackoverflow_test.h5", "stackoverflow_train.h5"]
+    src = S.make_char_lm(12, 20, 10001, 32, 0, "stackoverflow_nwp", next_token_only=False)
+    fed = R.load_tff_stackoverflow_h5(str(out), "nwp", 0)
+    assert fed.client_num == 12 and np.array_equal(fed.client_offsets, src.client_offsets)
+    # sentence = the 20 input ids; the loader puts <bos> in front, so its targets are the source's inputs
+    np.testing.assert_array_equal(fed.y.numpy(), src.x.numpy())
+    lr = R.load_tff_stackoverflow_h5(str(out), "lr", 4)
+    assert lr.client_num == 4 and lr.x.shape[1] == 10000 and lr.y.shape[1] == 500 and float(lr.y.sum()) > 0
