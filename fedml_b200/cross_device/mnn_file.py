@@ -3,8 +3,8 @@
 The reference's server reads every uploaded ``.mnn`` as ``{layer_idx: tensor}`` (cross_device/server_mnn/utils.py:11-28),
 averages, writes the values back into the MNN graph (:31-50) and evaluates.  :mod:`.mnn_format` does the same on the
 FlatBuffers bytes (the MNN wheel cannot be installed here): parameters are read in graph order, written back in place, and
-the LeNet-5 / logistic-regression graphs of the reference's mobile models are built from scratch; other architectures are
-stored as a parameters-only MNN graph.  Files written by round 1 of this repo (magic ``FB2M``) are still readable."""
+the graphs of the reference's mobile models (LeNet-5, logistic regression, the ResNet-20 training graph) are built from scratch;
+other architectures are stored as a parameters-only MNN graph.  Files written by round 1 of this repo (magic ``FB2M``) are still readable."""
 import os
 from collections import OrderedDict
 
@@ -18,12 +18,18 @@ _LENET_KEYS = ["conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias", "fc1.
 
 
 def write_mnn_like(path, state_dict, input_dims=None):
-    """``state_dict`` -> ``.mnn``: the full inference graph for LeNet-5 and for pure linear stacks, parameters-only otherwise."""
+    """``state_dict`` -> ``.mnn``: the full graph for LeNet-5, for pure linear stacks and for the CIFAR ResNet-20 (running
+    statistics are not part of MNN's training graph and are left out), parameters-only otherwise."""
     os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
     keys = list(state_dict.keys())
     arrs = [v.detach().cpu().float().numpy() for v in state_dict.values()]
     if keys == _LENET_KEYS:
         return MF.build_lenet5(path, arrs, input_dims or (1, 1, 28, 28))
+    learned = [a for k, a in zip(keys, arrs) if not k.endswith(("running_mean", "running_var", "num_batches_tracked"))]
+    if len(learned) == 65 and learned[0].ndim == 4 and learned[-2].ndim == 2:
+        want = MF.resnet20_param_shapes(learned[-2].shape[0], learned[0].shape[1])
+        if [tuple(a.shape) for a in learned] == want:
+            return MF.build_resnet20(path, learned, input_dims or (1, learned[0].shape[1], 32, 32))
     linear = len(keys) % 2 == 0 and all(keys[2 * i].endswith("weight") and keys[2 * i + 1].endswith("bias") and arrs[2 * i].ndim == 2
                                         and arrs[2 * i + 1].ndim == 1 for i in range(len(keys) // 2))
     if linear and keys:
@@ -77,6 +83,8 @@ def load_into_module(path, module):
         return module
     targets = [k for k, v in own.items() if v.dtype.is_floating_point and not k.endswith("num_batches_tracked")]
     vals = list(sd.values())
+    if len(vals) != len(targets):                              # MNN training graphs carry no BatchNorm running statistics
+        targets = [k for k, _ in module.named_parameters()]
     if len(vals) != len(targets) or any(vals[i].numel() != own[targets[i]].numel() for i in range(len(vals))):
         raise ValueError(f"{path}: {len(vals)} parameters do not line up with the model's {len(targets)} tensors")
     module.load_state_dict({k: vals[i].reshape(own[k].shape).to(own[k].dtype) for i, k in enumerate(targets)}, strict=False)

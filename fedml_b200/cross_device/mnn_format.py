@@ -12,8 +12,10 @@ bytes directly:
 * reading walks vtables; writing parameters overwrites the ``float32s`` payloads in place (sizes are checked), so every
   other byte of the graph - and therefore what the phones execute - stays as the device SDK wrote it;
 * the builder emits a standard-conforming FlatBuffers buffer (vtable before table, children after parents, 4-byte
-  alignment) for graphs made of Input / ConvertTensor / Convolution / ReLU / Pooling / Reshape / MatMul / BinaryOp(add) /
-  Softmax / TrainableParam ops, which covers the reference's LeNet-5 and logistic-regression mobile models.
+  alignment) for graphs made of Input / ConvertTensor / Convolution / ReLU / Pooling / Reshape / MatMul / BinaryOp /
+  UnaryOp / Reduction / Const / Softmax / TrainableParam ops, which covers the reference's mobile models: LeNet-5, logistic
+  regression and the ResNet-20 training graph (model/mobile/mnn_resnet.py:80-135), whose training-mode BatchNorm MNN
+  serialises as mean / subtract / square / mean / +eps / sqrt / reciprocal / multiply / scale / shift primitives.
 """
 from __future__ import annotations
 
@@ -25,9 +27,12 @@ import numpy as np
 
 # OpType / OpParameter union tags of the ops handled here (MNN schema enums)
 OP_BINARY, OP_CONV, OP_INPUT, OP_MATMUL, OP_POOLING, OP_RELU, OP_RESHAPE, OP_SOFTMAX = 7, 12, 34, 39, 47, 69, 73, 85
-OP_CONVERT_TENSOR, OP_TRAINABLE_PARAM, OP_CONST = 129, 266, 6
+OP_CONVERT_TENSOR, OP_TRAINABLE_PARAM, OP_CONST, OP_REDUCTION, OP_UNARY = 129, 266, 11, 68, 101
 PARAM_BINARY, PARAM_BLOB, PARAM_CONV2D, PARAM_INPUT, PARAM_MATMUL, PARAM_POOL, PARAM_RELU, PARAM_RESHAPE = 6, 7, 9, 21, 25, 31, 51, 55
-PARAM_AXIS, PARAM_TENSOR_CONVERT = 4, 66
+PARAM_AXIS, PARAM_TENSOR_CONVERT, PARAM_REDUCTION, PARAM_UNARY = 4, 66, 50, 70
+BINARY_ADD, BINARY_SUB, BINARY_MUL = 0, 1, 2
+UNARY_SQUARE, UNARY_SQRT, UNARY_RSQRT, UNARY_RECIPROCAL = 4, 5, 6, 15
+REDUCE_SUM, REDUCE_MEAN = 0, 3
 FMT_NCHW, FMT_NHWC, FMT_NC4HW4 = 0, 1, 2
 NET_OPLISTS, NET_TENSOR_NAME = 3, 7
 OP_F_INPUTS, OP_F_MAIN_TYPE, OP_F_MAIN, OP_F_NAME, OP_F_OUTPUTS, OP_F_TYPE = 0, 1, 2, 3, 4, 5
@@ -160,12 +165,13 @@ def describe(path: str) -> List[dict]:
             if e["main_type"] == PARAM_CONV2D and r.field(m, 0) is not None:
                 c = r.indirect(r.field(m, 0))
                 iv = lambda i, dflt: r.i32(r.field(c, i)) if r.field(c, i) is not None else dflt      # noqa: E731
-                e["conv"] = {"kernel": [iv(3, 1), iv(2, 1)], "stride": [iv(5, 1), iv(4, 1)], "out": iv(10, 0), "in": iv(11, 0),
+                e["conv"] = {"kernel": [iv(3, 1), iv(2, 1)], "stride": [iv(5, 1), iv(4, 1)], "out": iv(10, 0), "in": iv(11, 0), "pad": [iv(1, 0), iv(0, 0)],
                              "pad_mode": r.d[r.field(c, 8)] if r.field(c, 8) is not None else 0}
             if e["main_type"] == PARAM_POOL:
                 iv = lambda i, dflt: r.i32(r.field(m, i)) if r.field(m, i) is not None else dflt      # noqa: E731
                 e["pool"] = {"kernel": [iv(4, 0), iv(3, 0)], "stride": [iv(6, 0), iv(5, 0)]}
                 e["pool_type"] = r.d[r.field(m, 7)] if r.field(m, 7) is not None else 0          # 0 max, 1 average
+                e["pool_pad"] = r.d[r.field(m, 8)] if r.field(m, 8) is not None else 0           # 0 caffe, 1 valid, 2 same
             if e["main_type"] == PARAM_MATMUL:
                 e["transpose_a"] = bool(r.d[r.field(m, 1)]) if r.field(m, 1) is not None else False
                 e["transpose_b"] = bool(r.d[r.field(m, 2)]) if r.field(m, 2) is not None else False
@@ -173,6 +179,17 @@ def describe(path: str) -> List[dict]:
                 e["axis"] = r.i32(r.field(m, 0)) if r.field(m, 0) is not None else 0
             if e["main_type"] == PARAM_BINARY:
                 e["binary_op"] = r.i32(r.field(m, 0)) if r.field(m, 0) is not None else 0        # 0 add, 1 sub, 2 mul
+            if e["main_type"] == PARAM_UNARY:
+                e["unary_op"] = r.i32(r.field(m, 0)) if r.field(m, 0) is not None else 0         # 4 square, 5 sqrt, 15 1/x
+            if e["main_type"] == PARAM_REDUCTION:
+                e["reduce_op"] = r.d[r.field(m, 0)] if r.field(m, 0) is not None else 0          # 0 sum, 3 mean
+                e["reduce_dims"] = r.ints(r.field(m, 1)) if r.field(m, 1) is not None else []
+                e["keep_dims"] = bool(r.d[r.field(m, 3)]) if r.field(m, 3) is not None else False
+            if e["main_type"] == PARAM_TENSOR_CONVERT:
+                e["dest"] = r.d[r.field(m, 1)] if r.field(m, 1) is not None else 0
+            if e["type"] == OP_CONST and e["main_type"] == PARAM_BLOB and r.field(m, BLOB_FLOATS) is not None:
+                base, n = r.vector(r.field(m, BLOB_FLOATS))
+                e["values"] = np.frombuffer(r.d, dtype="<f4", count=n, offset=base).copy()
         ops.append(e)
     return ops
 
@@ -283,12 +300,52 @@ class MnnGraph:
         return self._add("TrainableParam", OP_TRAINABLE_PARAM, PARAM_BLOB, {BLOB_DIMS: ("ints", list(a.shape)), BLOB_FLOATS: ("floats", a)},
                          [], name)
 
-    def conv(self, x, weight, bias, name=None, valid=True):
+    def conv(self, x, weight, bias, name=None, valid=True, stride=1, pad=0):
+        """``valid`` False = MNN's SAME mode: output ceil(in / stride), padding split with the odd cell at the bottom / right."""
         w = np.asarray(weight)
         cout, cin, kh, kw = w.shape
         common = {2: ("i32", kw), 3: ("i32", kh), 8: ("u8", 1 if valid else 2), 10: ("i32", cout), 11: ("i32", cin)}
-        wi, bi = self.param(weight), self.param(bias)
-        return self._add("Conv", OP_CONV, PARAM_CONV2D, {0: ("table", common)}, [x, wi, bi], name)
+        if stride != 1:
+            common.update({4: ("i32", stride), 5: ("i32", stride)})
+        if pad:
+            common.update({0: ("i32", pad), 1: ("i32", pad)})
+        ins = [x, self.param(weight)]
+        if bias is not None:
+            ins.append(self.param(bias))
+        return self._add("Conv", OP_CONV, PARAM_CONV2D, {0: ("table", common)}, ins, name)
+
+    def const(self, value):
+        a = np.asarray(value, dtype=np.float32)
+        main = {1: ("u8", FMT_NHWC), 2: ("i32", 1), BLOB_FLOATS: ("floats", a)}
+        if a.ndim:
+            main[BLOB_DIMS] = ("ints", list(a.shape))
+        return self._add("Const", OP_CONST, PARAM_BLOB, main, [])
+
+    def binary(self, a, b, op=BINARY_ADD, name=None):
+        return self._add("BinaryOp", OP_BINARY, PARAM_BINARY, {0: ("i32", op), 1: ("i32", 1)} if op else {1: ("i32", 1)}, [a, b], name)
+
+    def unary(self, x, op):
+        return self._add("UnaryOp", OP_UNARY, PARAM_UNARY, {0: ("i32", op), 1: ("i32", 1)}, [x])
+
+    def reduce_mean(self, x, dims, keep_dims=True):
+        return self._add("Reduction", OP_REDUCTION, PARAM_REDUCTION,
+                         {0: ("u8", REDUCE_MEAN), 1: ("ints", list(dims)), 3: ("bool", int(keep_dims)), 4: ("i32", 1)}, [x])
+
+    def avg_pool(self, x, k, s):
+        return self._add("Pooling", OP_POOLING, PARAM_POOL,
+                         {3: ("i32", k), 4: ("i32", k), 5: ("i32", s), 6: ("i32", s), 7: ("u8", 1), 8: ("u8", 1)}, [x])
+
+    def batch_norm_train(self, x_nc4, scale, bias, name=None, eps=1e-5):
+        """Training-mode BatchNorm the way MNN's ``nn.batch_norm`` serialises it: statistics of the batch over (N, H, W),
+        biased variance, on an NCHW copy; the result goes back to NC4HW4."""
+        x = self.convert(x_nc4, FMT_NCHW)
+        centred = self.binary(x, self.reduce_mean(x, [0, 2, 3]), BINARY_SUB)
+        var = self.reduce_mean(self.unary(centred, UNARY_SQUARE), [0, 2, 3])
+        rstd = self.unary(self.unary(self.binary(var, self.const(eps)), UNARY_SQRT), UNARY_RECIPROCAL)
+        y = self.binary(centred, rstd, BINARY_MUL)
+        y = self.binary(y, self.param(np.asarray(scale, dtype=np.float32).reshape(1, -1, 1, 1)), BINARY_MUL)
+        y = self.binary(y, self.param(np.asarray(bias, dtype=np.float32).reshape(1, -1, 1, 1)), BINARY_ADD, name)
+        return self.convert(y, FMT_NC4HW4)
 
     def relu(self, x):
         return self._add("ReLU", OP_RELU, PARAM_RELU, {}, [x])
@@ -304,7 +361,7 @@ class MnnGraph:
         wi = self.param(weight)
         mm = self._add("MatMul", OP_MATMUL, PARAM_MATMUL, {2: ("bool", 1)}, [x, wi])
         bi = self.param(np.asarray(bias, dtype=np.float32).reshape(1, -1))
-        return self._add("BinaryOp", OP_BINARY, PARAM_BINARY, {}, [mm, bi])
+        return self.binary(mm, bi)
 
     def softmax(self, x, axis=1):
         return self._add("Softmax", OP_SOFTMAX, PARAM_AXIS, {0: ("i32", axis)}, [x])
@@ -358,6 +415,50 @@ def build_mlp(path: str, params: Sequence[np.ndarray], input_dims) -> str:
     return g.save(path)
 
 
+RESNET20_STAGES = ((16, 1), (16, 1), (16, 1), (32, 2), (32, 1), (32, 1), (64, 2), (64, 1), (64, 1))
+
+
+def resnet20_param_shapes(class_num: int = 10, in_ch: int = 3) -> List[Tuple[int, ...]]:
+    """Shapes of the 65 trainable tensors in graph order = ``named_parameters()`` order of the torch CIFAR ResNet-20."""
+    shapes = [(16, in_ch, 3, 3), (16,), (16,)]
+    cin = 16
+    for cout, stride in RESNET20_STAGES:
+        shapes += [(cout, cin, 3, 3), (cout,), (cout,), (cout, cout, 3, 3), (cout,), (cout,)]
+        if stride != 1 or cin != cout:
+            shapes += [(cout, cin, 1, 1), (cout,), (cout,)]
+        cin = cout
+    return shapes + [(class_num, 64), (class_num,)]
+
+
+def build_resnet20(path: str, params: Sequence[np.ndarray], input_dims=(1, 3, 32, 32)) -> str:
+    """The reference's mobile ResNet-20 (model/mobile/mnn_resnet.py:7-135) as MNN saves it from training mode: stem conv +
+    BN + ReLU, nine two-convolution residual blocks (a 1x1 stride-2 convolution + BN on the shortcut where the width changes),
+    8x8 average pool, flatten, fc, softmax.  Convolutions have no bias and use SAME padding; the additions run on NCHW
+    tensors, so format conversions sit exactly where MNN's expression builder puts them.  ``params`` in
+    :func:`resnet20_param_shapes` order (BN tensors may be flat)."""
+    it = iter(params)
+    g = MnnGraph()
+    x = g.convert(g.input(input_dims), FMT_NC4HW4)
+    x = g.relu(g.batch_norm_train(g.conv(x, next(it), None, "conv1", valid=False, pad=1), next(it), next(it), "bn1"))
+    x_is_nc4, cin = True, 16
+    for cout, stride in RESNET20_STAGES:
+        xin = x if x_is_nc4 else g.convert(x, FMT_NC4HW4)
+        y = g.conv(xin, next(it), None, "conv1", valid=False, stride=stride, pad=1)
+        y = g.relu(g.batch_norm_train(y, next(it), next(it), "bn1"))
+        y = g.batch_norm_train(g.conv(y, next(it), None, "conv2", valid=False, pad=1), next(it), next(it), "bn2")
+        y = g.convert(y, FMT_NCHW)
+        if stride != 1 or cin != cout:
+            sc = g.conv(g.convert(x, FMT_NC4HW4), next(it), None, "conv_shortcut", valid=False, stride=stride)
+            sc = g.convert(g.batch_norm_train(sc, next(it), next(it), "bn_shortcut"), FMT_NCHW)
+        else:
+            sc = g.convert(x, FMT_NCHW) if x_is_nc4 else x
+        x = g.relu(g.binary(y, sc))
+        x_is_nc4, cin = False, cout
+    x = g.reshape(g.avg_pool(x, 8, 8), [0, -1])
+    g.softmax(g.linear(x, next(it), next(it)), 1)
+    return g.save(path)
+
+
 def build_params_only(path: str, named: "OrderedDict[str, np.ndarray]") -> str:
     """A graph of TrainableParam ops named after the tensors - the container for architectures the op set above does not
     cover (the server only needs the parameters; a phone would need the full graph from its own SDK)."""
@@ -391,8 +492,15 @@ def run_graph(path: str, x, params: Optional[Sequence] = None):
         elif t == OP_CONV:
             c = o["conv"]
             kh, kw = c["kernel"]
-            pad = (kh // 2, kw // 2) if c["pad_mode"] == 2 else 0
-            out = F.conv2d(ins[0], ins[1], ins[2].reshape(-1) if len(ins) > 2 else None, stride=tuple(c["stride"]), padding=pad)
+            xin = ins[0]
+            if c["pad_mode"] == 2:                         # SAME: out = ceil(in / stride), the odd cell goes bottom / right
+                sh, sw = c["stride"]
+                ph = max((-(-xin.shape[2] // sh) - 1) * sh + kh - xin.shape[2], 0)
+                pw = max((-(-xin.shape[3] // sw) - 1) * sw + kw - xin.shape[3], 0)
+                xin = F.pad(xin, (pw // 2, pw - pw // 2, ph // 2, ph - ph // 2))
+            elif c["pad_mode"] == 0 and (c.get("pad", [0, 0]) != [0, 0]):
+                xin = F.pad(xin, (c["pad"][1], c["pad"][1], c["pad"][0], c["pad"][0]))
+            out = F.conv2d(xin, ins[1], ins[2].reshape(-1) if len(ins) > 2 else None, stride=tuple(c["stride"]))
         elif t == OP_RELU:
             out = torch.relu(ins[0])
         elif t == OP_POOLING:
@@ -411,6 +519,19 @@ def run_graph(path: str, x, params: Optional[Sequence] = None):
                 raise MnnFormatError(f"BinaryOp type {op} is not supported")
         elif t == OP_SOFTMAX:
             out = torch.softmax(ins[0], dim=o.get("axis", 1))
+        elif t == OP_CONST:
+            out = torch.as_tensor(o["values"], dtype=torch.float32).reshape(o.get("dims", []))
+        elif t == OP_UNARY:
+            fn = {UNARY_SQUARE: torch.square, UNARY_SQRT: torch.sqrt, UNARY_RSQRT: torch.rsqrt, UNARY_RECIPROCAL: torch.reciprocal,
+                  0: torch.abs, 1: torch.neg, 7: torch.exp, 8: torch.log}.get(o["unary_op"])
+            if fn is None:
+                raise MnnFormatError(f"UnaryOp type {o['unary_op']} is not supported")
+            out = fn(ins[0])
+        elif t == OP_REDUCTION:
+            fn = {REDUCE_SUM: torch.sum, REDUCE_MEAN: torch.mean}.get(o["reduce_op"])
+            if fn is None:
+                raise MnnFormatError(f"Reduction type {o['reduce_op']} is not supported")
+            out = fn(ins[0], dim=tuple(o["reduce_dims"]) or None, keepdim=o["keep_dims"])
         else:
             raise MnnFormatError(f"op {o['name']!r} (type {t}) is outside the supported set")
         for idx in o["outputs"]:

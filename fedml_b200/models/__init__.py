@@ -85,9 +85,9 @@ def create_mnn_lenet5_model(mnn_file_path, class_num=10):
 
 
 def create_mnn_resnet20_model(mnn_file_path, class_num=10):
-    """ResNet-20 (model/mobile/mnn_resnet.py): MNN expands its training-mode BatchNorm into ~10 ops per layer that the
-    builder does not emit, so the file is a parameters-only MNN graph (TrainableParam ops named after the state-dict keys);
-    the server side - read, average, write back - works on it like on any device-written graph."""
+    """ResNet-20 (model/mobile/mnn_resnet.py:80-141): the 416-op training graph MNN itself saves - SAME-padded bias-free
+    convolutions, training-mode BatchNorm expanded into reduction / unary / binary primitives, additions on NCHW copies - emitted
+    op for op by ``mnn_format.build_resnet20`` (checked against the reference's own ``global_model.mnn``)."""
     from ..cross_device.mnn_file import write_mnn_like
     from .cv import BasicBlock
     write_mnn_like(mnn_file_path, ResNet(BasicBlock, [3, 3, 3], class_num, "cifar").state_dict())

@@ -220,7 +220,7 @@ def test_mnn_format_builder_reader_and_in_place_writer(tmp_path):
     ops = MF.describe(path)
     assert [o["type"] for o in ops][:7] == [MF.OP_INPUT, MF.OP_CONVERT_TENSOR, MF.OP_TRAINABLE_PARAM, MF.OP_TRAINABLE_PARAM, MF.OP_CONV,
                                             MF.OP_RELU, MF.OP_POOLING]
-    assert ops[4]["conv"] == {"kernel": [5, 5], "stride": [1, 1], "out": 20, "in": 1, "pad_mode": 1} and ops[4]["inputs"] == [1, 2, 3]
+    assert ops[4]["conv"] == {"kernel": [5, 5], "stride": [1, 1], "out": 20, "in": 1, "pad": [0, 0], "pad_mode": 1} and ops[4]["inputs"] == [1, 2, 3]
     assert all(o["outputs"] == [i] for i, o in enumerate(ops)) and ops[-1]["type"] == MF.OP_SOFTMAX
     got = MF.read_params(path)
     for (k, v), w in zip(net.state_dict().items(), got.values()):
@@ -246,9 +246,16 @@ def test_mnn_format_builder_reader_and_in_place_writer(tmp_path):
     with torch.no_grad():
         torch.testing.assert_close(MF.run_graph(path, x), torch.softmax(net(x), 1), rtol=1e-5, atol=1e-6)
         torch.testing.assert_close(MF.run_graph(str(tmp_path / "lr.mnn"), x), torch.softmax(lr(x.flatten(1)), 1), rtol=1e-5, atol=1e-6)
+    # ResNet-20: the full 416-op training graph; its 65 tensors load back into the torch module by position
+    from fedml_b200.models.cv import BasicBlock, ResNet
     fedml.model.create_mnn_resnet20_model(str(tmp_path / "r20.mnn"))
     sd = read_mnn_like(str(tmp_path / "r20.mnn"))
-    assert "layer1.0.conv1.weight" in sd and sd["fc.weight"].shape == (10, 64)
+    assert len(sd) == 65 and list(sd.values())[-2].shape == (10, 64) and len(MF.describe(str(tmp_path / "r20.mnn"))) == 416
+    r20 = ResNet(BasicBlock, [3, 3, 3], 10, "cifar")
+    write_mnn_like(str(tmp_path / "r20.mnn"), r20.state_dict())
+    back = load_into_module(str(tmp_path / "r20.mnn"), ResNet(BasicBlock, [3, 3, 3], 10, "cifar"))
+    for (k, v), (_, w) in zip(r20.named_parameters(), back.named_parameters()):
+        torch.testing.assert_close(w, v, rtol=0, atol=0)
 
 
 @pytest.mark.skipif(not os.path.exists(REF_MNN), reason="reference sample .mnn files not present")
@@ -272,8 +279,41 @@ def test_mnn_format_against_files_written_by_the_mnn_sdk(tmp_path):
     import torch
     probs = MF.run_graph(REF_MNN, torch.randn(3, 1, 28, 28))          # the LeNet file the MNN SDK wrote executes here
     assert probs.shape == (3, 10) and torch.allclose(probs.sum(1), torch.ones(3), atol=1e-5)
-    with pytest.raises(MF.MnnFormatError):                            # the ResNet-20 training graph uses ops outside the set
-        MF.run_graph(REF_MNN_RESNET, torch.randn(1, 3, 32, 32))
+    # the ResNet-20 training graph MNN wrote: rebuilt op for op from its parameters, and executed against a plain restatement
+    # (SAME padding with the odd cell at the bottom / right, batch statistics, biased variance)
+    import torch.nn.functional as F
+    params = list(MF.read_params(REF_MNN_RESNET).values())
+    assert [int(np.prod(a.shape)) for a in params] == [int(np.prod(sh)) for sh in MF.resnet20_param_shapes()]
+    rebuilt = MF.build_resnet20(str(tmp_path / "r20.mnn"), params)
+    a, b = MF.describe(REF_MNN_RESNET), MF.describe(rebuilt)
+    norm = lambda ops: [{k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in o.items()} for o in ops]      # noqa: E731
+    assert norm(a) == norm(b)
+    it = iter(torch.from_numpy(p) for p in params)
+
+    def conv_bn(x, stride, relu):
+        w = next(it)
+        k = w.shape[-1]
+        need = max((-(-x.shape[-1] // stride) - 1) * stride + k - x.shape[-1], 0)
+        y = F.conv2d(F.pad(x, (need // 2, need - need // 2, need // 2, need - need // 2)), w, stride=stride)
+        y = F.batch_norm(y, None, None, next(it).flatten(), next(it).flatten(), training=True, eps=1e-5)
+        return torch.relu(y) if relu else y
+
+    x = torch.randn(6, 3, 32, 32)
+    h = conv_bn(x, 1, True)
+    cin = 16
+    for cout, stride in MF.RESNET20_STAGES:
+        y = conv_bn(conv_bn(h, stride, True), 1, False)
+        h = torch.relu(y + (conv_bn(h, stride, False) if (stride != 1 or cin != cout) else h))
+        cin = cout
+    w, bias = next(it), next(it)
+    want = torch.softmax(F.avg_pool2d(h, 8).flatten(1) @ w.t() + bias, 1)
+    got = MF.run_graph(REF_MNN_RESNET, x)
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(MF.run_graph(rebuilt, x), got, rtol=0, atol=0)
+    with pytest.raises(MF.MnnFormatError):                            # an op outside the supported set is reported, not skipped
+        g = MF.MnnGraph()
+        g._add("Interp", 99, 0, {}, [g.input([1, 3, 8, 8])])
+        MF.run_graph(g.save(str(tmp_path / "odd.mnn")), torch.randn(1, 3, 8, 8))
 
 
 def test_mpc_toolbox_and_secure_aggregation():
