@@ -114,3 +114,50 @@ def test_vertical_fl_runs_on_lending_club_files(tmp_path):
     assert [x.shape[1] for x in api.xs] == [15, 35, 33] and api.y.shape[0] == 160
     api.train()
     assert api.history[-1]["test_acc"] > 0.65                      # 40 test rows, 83 noisy features
+
+
+def test_image_dataset_helpers_partition_truncated_sets_and_loaders(tmp_path, monkeypatch):
+    """The helper surface of data/cifar10/data_loader.py + datasets.py (same for cifar100 / cinic10)."""
+    import torch
+    from fedml_b200.data import dataset_utils as U
+    monkeypatch.setattr(U, "SYNTHETIC_TRAIN_SIZE", 1500)
+    x, y, xt, yt, idx_map, counts = U.partition_data("cifar10", None, "hetero", 6, 0.5)
+    assert x.shape == (1500, 32, 32, 3) and x.dtype == np.uint8 and xt.shape[0] == 300
+    assert sorted(np.concatenate([np.asarray(v) for v in idx_map.values()]).tolist()) == list(range(1500))
+    assert min(len(v) for v in idx_map.values()) >= 10
+    assert counts == U.record_net_data_stats(y, idx_map) and sum(sum(c.values()) for c in counts.values()) == 1500
+    again = U.partition_data("cifar10", None, "hetero", 6, 0.5)[4]                   # seeded like the reference: reproducible
+    assert all(np.array_equal(idx_map[k], again[k]) for k in idx_map)
+    homo = U.partition_data("cifar10", None, "homo", 6, 0.5)[4]
+    assert sorted(len(v) for v in homo.values()) == [250] * 6
+    # frozen split files round-trip (the "hetero-fix" mode), also when written as JSON
+    m, d = U.write_net_dataidx_map(str(tmp_path / "net_dataidx_map.txt"), idx_map), U.write_data_distribution(str(tmp_path / "distribution.txt"), counts)
+    fixed = U.partition_data("cifar10", None, "hetero-fix", 6, 0.5, dataidx_map_file=m, distribution_file=d)
+    assert {k: list(map(int, v)) for k, v in idx_map.items()} == fixed[4] and fixed[5] == counts
+    import json
+    (tmp_path / "as_json.txt").write_text(json.dumps({str(k): [int(i) for i in v] for k, v in idx_map.items()}, indent=1))
+    assert U.read_net_dataidx_map(str(tmp_path / "as_json.txt")) == fixed[4]
+    with pytest.raises(ValueError):
+        U.partition_data("cifar10", None, "hetero-fix", 6, 0.5)
+    # truncated data set + transforms
+    ds = U.CIFAR10_truncated(None, dataidxs=idx_map[2], train=True, transform=U.data_transforms("cifar10")[0])
+    assert len(ds) == len(idx_map[2]) and np.array_equal(ds.target, y[np.asarray(idx_map[2])])
+    img, label = ds[0]
+    assert img.shape == (3, 32, 32) and img.dtype == torch.float32 and label == int(ds.target[0])
+    ds.truncate_channel([0])
+    assert ds.data[0, :, :, 1:].sum() == 0 and x[np.asarray(idx_map[2])[0], :, :, 1:].sum() > 0        # the source is untouched
+    g = torch.Generator().manual_seed(1)
+    cut = U.Cutout(16, g)(torch.ones(3, 32, 32))
+    zeros = int((cut[0] == 0).sum())
+    assert 64 <= zeros <= 256 and torch.equal(cut[0], cut[1])                                             # clipped at the border
+    plain = U.data_transforms("cifar100")[1](x[0])
+    want = (torch.from_numpy(x[0]).permute(2, 0, 1).float() / 255 - torch.tensor(U.S.CIFAR100_MEAN).view(3, 1, 1)) / torch.tensor(U.S.CIFAR100_STD).view(3, 1, 1)
+    torch.testing.assert_close(plain, want)
+    # loaders: drop_last on both sides, the client's samples only
+    tr, te = U.get_dataloader("cifar10", None, 32, 64, idx_map[0])
+    assert len(tr) == len(idx_map[0]) // 32 and len(te) == 300 // 64
+    xb, yb = next(iter(tr))
+    assert xb.shape == (32, 3, 32, 32) and yb.dtype == torch.int64
+    tr2, te2 = U.get_dataloader_test_CIFAR10(None, 16, 16, idx_map[1], list(range(40)))
+    assert len(te2.dataset) == 40 and len(tr2.dataset) == len(idx_map[1])
+    assert U.CIFAR100_truncated(None, train=False).data.shape[0] == 300 and int(U.CIFAR100_truncated(None).target.max()) > 10
