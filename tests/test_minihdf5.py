@@ -160,3 +160,48 @@ def test_export_tool_and_stackoverflow_round_trip(tmp_path):
     np.testing.assert_array_equal(fed.y.numpy(), src.x.numpy())
     lr = R.load_tff_stackoverflow_h5(str(out), "lr", 4)
     assert lr.client_num == 4 and lr.x.shape[1] == 10000 and lr.y.shape[1] == 500 and float(lr.y.sum()) > 0
+
+
+def test_reference_named_text_helpers(tmp_path):
+    """Same names and call signatures as data/{shakespeare,fed_shakespeare,stackoverflow_*}/..., importable through ``fedml.data``."""
+    from fedml.data.fed_shakespeare.utils import SEQUENCE_LENGTH, char_to_id, get_word_dict, id_to_word, preprocess, split
+    from fedml.data.shakespeare.language_utils import VOCAB_SIZE, bag_of_words, letter_to_index, letter_to_vec, line_to_indices, split_line
+    from fedml.data.stackoverflow_lr.utils import get_tag_dict, preprocess_input, preprocess_target
+    from fedml.data.stackoverflow_nwp.dataset import StackOverflowDataset
+    from fedml.data.stackoverflow_nwp.utils import get_word_dict as so_words, tokenizer
+    from fedml.data.synthetic_1_1.generate_synthetic import generate_synthetic, main as write_synthetic, softmax
+    assert VOCAB_SIZE == 90 and letter_to_index("d") == 0 and letter_to_index("~") == -1 and sum(letter_to_vec("h")) == 1
+    assert split_line("it's ok, right?") == ["it's", "ok", ",", "right", "?"]
+    assert line_to_indices("b a zzz", {"a": 0, "b": 1}, 5) == [1, 0, 2, 2, 2] and bag_of_words("a a b c", {"a": 0, "b": 1}) == [2, 1]
+    table = get_word_dict()
+    assert SEQUENCE_LENGTH == 80 and len(table) == 89 and table["<pad>"] == 0 and table["<bos>"] == 87 and char_to_id("~") == 89
+    assert id_to_word(1) == "d"
+    rows = preprocess(["abc", "x" * 100])
+    x, y = split(rows)
+    assert len(rows) == 3 and x.shape == (3, 80) and y.shape == (3, 80) and rows[0][:5] == [87, char_to_id("a"), char_to_id("b"), char_to_id("c"), 88]
+
+    (tmp_path / "stackoverflow.word_count").write_text("".join(f"w{i} {9 - i}\n" for i in range(8)))
+    (tmp_path / "stackoverflow.tag_count").write_text(json.dumps({"python": 5, "c++": 3, "sql": 1}))
+    d = str(tmp_path)
+    assert list(so_words(d))[:2] == ["<pad>", "w0"] and so_words(d)["<eos>"] == 10 and get_tag_dict(d) == {"python": 0, "c++": 1, "sql": 2}
+    assert tokenizer("w0 w7 nope", d, max_seq_len=5) == [9, 1, 8, 11, 10, 0]
+    np.testing.assert_allclose(preprocess_input("w1 w1 nope w3", d), [0, 0.5, 0, 0.25, 0, 0, 0, 0])
+    assert preprocess_target("sql|python|rust", d).tolist() == [1, 0, 1]
+    H.write_hdf5(str(tmp_path / "stackoverflow_train.h5"),
+                 {"examples": {"u1": {"tokens": ["w0 w1", "w2"], "title": ["w3", "w4"], "tags": ["sql", "c++|python"]}, "u2": {"tokens": ["w5"], "title": [""], "tags": [""]}}})
+    ds = StackOverflowDataset(str(tmp_path / "stackoverflow_train.h5"), 0, "train", lambda s: tokenizer(s, d, 4))
+    assert len(ds) == 2 and ds.client_id == "u1" and [a.tolist() for a in ds[0]] == [[9, 1, 2, 10], [1, 2, 10, 0]]
+    lr = StackOverflowDataset(str(tmp_path / "stackoverflow_train.h5"), 0, "train",
+                              {"input": lambda s: preprocess_input(s, d), "target": lambda t: preprocess_target(t, d)})
+    xin, tgt = lr[1]
+    assert xin[2] == 0.5 and xin[4] == 0.5 and tgt.tolist() == [1, 1, 0]
+
+    assert abs(softmax([1.0, 2.0, 3.0]).sum() - 1) < 1e-12
+    xs, ys = generate_synthetic(1, 1, 0)
+    assert len(xs) == 30 and len(xs[0][0]) == 60 and set(ys[0]) <= set(float(k) for k in range(10)) and min(len(u) for u in ys) >= 50
+    tr, te = write_synthetic(str(tmp_path / "syn"))
+    blob = json.load(open(tr))
+    assert len(blob["users"]) == 30 and blob["users"][0] == "f_00000" and blob["num_samples"][0] == len(blob["user_data"]["f_00000"]["y"])
+    from fedml.data.synthetic_1_1.stats import print_dataset_stats
+    stats = print_dataset_stats("syn", str(tmp_path))
+    assert stats["users"] == 30 and stats["samples"] == sum(blob["num_samples"])
