@@ -231,6 +231,8 @@ def partition_data(dataset, datadir, partition, n_nets, alpha, dataidx_map_file:
     10 samples) - both under ``np.random.seed(10)`` like the reference - or "hetero-fix" (the split stored in
     ``dataidx_map_file`` / ``distribution_file``)."""
     from ..core.non_iid_partition import homo_partition, non_iid_partition_with_dirichlet_distribution
+    if str(dataset).lower() not in _STATS:
+        raise ValueError(f"partition_data: unknown image set {dataset!r} (known: {sorted(_STATS)})")
     x_train, y_train, x_test, y_test = load_image_arrays(dataset, datadir)
     classes = _STATS[str(dataset).lower()][2]
     if partition == "hetero-fix":
@@ -270,6 +272,63 @@ def get_dataloader_test(dataset, datadir, train_bs, test_bs, dataidxs_train=None
     return train_dl, test_dl
 
 
+# ---- the naturally federated sets: the fifth argument is a client index, not a list of sample indices
+_FEDERATED_CACHE: Dict[tuple, object] = {}
+FED_EMNIST_FILES = ("fed_emnist_train.h5", "fed_emnist_test.h5")
+FED_EMNIST_CLIENTS = (3400, 3400)
+FED_CIFAR100_FILES = ("fed_cifar100_train.h5", "fed_cifar100_test.h5")
+FED_CIFAR100_CLIENTS = (500, 100)
+FED_IMAGE_BATCH_SIZE = 20
+
+
+def _federated(name: str, data_dir):
+    key = (name, str(data_dir), SYNTHETIC_TRAIN_SIZE)
+    if key not in _FEDERATED_CACHE:
+        from . import load_federated
+        from ..arguments import Arguments
+        kw = dict(dataset=name, log_level="WARNING")
+        if data_dir:
+            kw["data_cache_dir"] = data_dir
+        if SYNTHETIC_TRAIN_SIZE:
+            kw["synthetic_train_size"] = SYNTHETIC_TRAIN_SIZE
+        _FEDERATED_CACHE[key] = load_federated(Arguments.from_dict(kw))
+    return _FEDERATED_CACHE[key]
+
+
+def federated_dataloader(name: str):
+    """``get_dataloader(dataset, data_dir, train_bs, test_bs, client_idx=None)`` of a naturally federated set (reference:
+    data/FederatedEMNIST/data_loader.py:30-75 and the same function in fed_cifar100 / fed_shakespeare / stackoverflow_*): the
+    loaders of one client, or of the union of all clients when ``client_idx`` is None.  ``dataset`` is ignored like there."""
+    def get_dataloader(dataset, data_dir, train_bs, test_bs, client_idx=None):
+        fed = _federated(name, data_dir)
+        if client_idx is None:
+            (x, y), (xt, yt) = (fed.x, fed.y), (fed.x_test, fed.y_test)
+        else:
+            (x, y), (xt, yt) = fed.client_slice(int(client_idx)), fed.client_test_slice(int(client_idx))
+        prep = fed.transform if fed.transform is not None else (lambda t: t)
+        mk = lambda a, b, bs, sh: torch_data.DataLoader(torch_data.TensorDataset(prep(a), b), batch_size=bs, shuffle=sh) if len(a) else None  # noqa: E731
+        return mk(x, y, train_bs, True), mk(xt, yt, test_bs, False)
+
+    get_dataloader.__name__ = f"get_dataloader_{name}"
+    return get_dataloader
+
+
+get_dataloader_femnist = federated_dataloader("femnist")
+get_dataloader_fed_cifar100 = federated_dataloader("fed_cifar100")
+get_dataloader_fed_shakespeare = federated_dataloader("fed_shakespeare")
+get_dataloader_stackoverflow_nwp = federated_dataloader("stackoverflow_nwp")
+get_dataloader_stackoverflow_lr = federated_dataloader("stackoverflow_lr")
+
+
+def _fixed(name: str, fn):
+    """The reference's per-module functions take a ``dataset`` argument and ignore it; bind the module's own set instead."""
+    def bound(dataset, *a, **k):
+        return fn(name, *a, **k)
+    bound.__name__ = f"{fn.__name__}_{name}"
+    bound.__doc__ = fn.__doc__
+    return bound
+
+
 def get_dataloader_CIFAR10(datadir, train_bs, test_bs, dataidxs=None):  # noqa: N802
     return get_dataloader("cifar10", datadir, train_bs, test_bs, dataidxs)
 
@@ -292,3 +351,10 @@ def get_dataloader_test_CIFAR100(datadir, train_bs, test_bs, dataidxs_train=None
 
 def get_dataloader_test_cinic10(datadir, train_bs, test_bs, dataidxs_train=None, dataidxs_test=None):
     return get_dataloader_test("cinic10", datadir, train_bs, test_bs, dataidxs_train, dataidxs_test)
+
+
+partition_data_cifar10, partition_data_cifar100, partition_data_cinic10 = (_fixed(n, partition_data) for n in ("cifar10", "cifar100", "cinic10"))
+get_dataloader_any_cifar10, get_dataloader_any_cifar100, get_dataloader_any_cinic10 = (
+    _fixed(n, get_dataloader) for n in ("cifar10", "cifar100", "cinic10"))
+get_dataloader_test_any_cifar10, get_dataloader_test_any_cifar100, get_dataloader_test_any_cinic10 = (
+    _fixed(n, get_dataloader_test) for n in ("cifar10", "cifar100", "cinic10"))

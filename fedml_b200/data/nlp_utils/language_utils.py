@@ -65,18 +65,23 @@ def read_data(train_data_dir: str, test_data_dir: str):
 
 
 def batch_data(data: dict, batch_size: int, seed: int = 100):
-    """Shuffles a client's ``{"x": [...], "y": [...]}`` (x and y with the same permutation) and cuts it into tensor batches."""
+    """Shuffles a client's ``{"x": [...], "y": [...]}`` (x and y with the same permutation) and cuts it into tensor batches:
+    text rows (Shakespeare) become character ids, numeric rows (MNIST, synthetic) float features with int64 labels."""
     x, y = list(data["x"]), list(data["y"])
     order = np.random.RandomState(seed).permutation(len(x))
+    text = bool(x) and isinstance(x[0], str)
     out = []
     for i in range(0, len(x), batch_size):
         idx = order[i:i + batch_size]
-        out.append((torch.tensor(process_x([x[j] for j in idx]), dtype=torch.int64),
-                    torch.tensor(process_y([y[j] for j in idx]), dtype=torch.int64)))
+        xb, yb = [x[j] for j in idx], [y[j] for j in idx]
+        if text:
+            out.append((torch.tensor(process_x(xb), dtype=torch.int64), torch.tensor(process_y(yb), dtype=torch.int64)))
+        else:
+            out.append((torch.tensor(np.asarray(xb, dtype=np.float32)), torch.tensor(np.asarray(yb, dtype=np.int64))))
     return out
 
 
-def load_data(name: str, data_dir: str = ".") -> dict:
+def load_leaf_stats(name: str, data_dir: str = ".") -> dict:
     """The merged ``{users, num_samples, user_data}`` of ``<data_dir>/<name>/data/all_data`` or of a train directory."""
     for sub in (os.path.join(data_dir, name, "data", "all_data"), os.path.join(data_dir, name, "train"), data_dir):
         if os.path.isdir(sub) and any(f.endswith(".json") for f in os.listdir(sub)):
@@ -93,7 +98,7 @@ def load_data(name: str, data_dir: str = ".") -> dict:
 
 def print_dataset_stats(name: str, data_dir: str = ".") -> dict:
     """Users, samples, mean / std / skewness of the samples per user (the numbers LEAF's stats.py prints)."""
-    d = load_data(name, data_dir)
+    d = load_leaf_stats(name, data_dir)
     n = np.asarray(d["num_samples"], dtype=np.float64)
     mu, sd = float(n.mean()), float(n.std())
     stats = {"users": len(d["users"]), "samples": int(n.sum()), "mean": mu, "std": sd, "std_over_mean": sd / mu if mu else 0.0,

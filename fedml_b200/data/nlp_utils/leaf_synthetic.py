@@ -32,7 +32,7 @@ def generate_synthetic(alpha, beta, iid, num_user: int = NUM_USER, seed: int = 0
     return xs, ys
 
 
-def main(out_dir: str = ".", alpha: float = 1.0, beta: float = 1.0, iid: int = 0, seed: int = 0) -> Tuple[str, str]:
+def write_leaf_files(out_dir: str = ".", alpha: float = 1.0, beta: float = 1.0, iid: int = 0, seed: int = 0) -> Tuple[str, str]:
     """Writes ``<out_dir>/train/mytrain.json`` and ``<out_dir>/test/mytest.json`` (users ``f_00000`` ..., 90 / 10 split after a
     per-user shuffle)."""
     xs, ys = generate_synthetic(alpha, beta, iid, seed=seed)

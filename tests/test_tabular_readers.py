@@ -161,3 +161,30 @@ def test_image_dataset_helpers_partition_truncated_sets_and_loaders(tmp_path, mo
     tr2, te2 = U.get_dataloader_test_CIFAR10(None, 16, 16, idx_map[1], list(range(40)))
     assert len(te2.dataset) == 40 and len(tr2.dataset) == len(idx_map[1])
     assert U.CIFAR100_truncated(None, train=False).data.shape[0] == 300 and int(U.CIFAR100_truncated(None).target.max()) > 10
+
+
+def test_per_module_loader_functions_through_the_reference_import_paths(monkeypatch):
+    """``fedml.data.<set>.data_loader.get_dataloader`` keeps the reference's calling convention: the dataset argument is ignored,
+    the fifth argument is a list of sample indices for the partitioned sets and a client index for the federated ones."""
+    import torch
+    from fedml_b200.data import dataset_utils as U
+    monkeypatch.setattr(U, "SYNTHETIC_TRAIN_SIZE", 1200)
+    from fedml.data.cifar100.data_loader import get_dataloader as c100_loader, partition_data as c100_partition
+    from fedml.data.FederatedEMNIST.data_loader import DEFAULT_BATCH_SIZE, get_dataloader as femnist_loader
+    from fedml.data.fed_shakespeare.data_loader import DEFAULT_TRAIN_FILE, get_dataloader as shakespeare_loader
+    from fedml.data.MNIST.data_loader import batch_data
+    assert DEFAULT_BATCH_SIZE == 20 and DEFAULT_TRAIN_FILE == "shakespeare_train.h5"
+    _, y, _, _, idx_map, counts = c100_partition("ignored", None, "homo", 4, 0.5)
+    assert int(y.max()) > 10 and len(idx_map) == 4 and len(counts[0]) > 10
+    tr, te = c100_loader("ignored", None, 50, 50, idx_map[1])
+    assert len(tr.dataset) == 300 and next(iter(tr))[0].shape == (50, 3, 32, 32)
+    tr, te = femnist_loader("ignored", None, 16, 16, 3)
+    fed = U._federated("femnist", None)
+    assert len(tr.dataset) == fed.client_size(3) and next(iter(tr))[0].shape[1:] == fed.x.shape[1:]
+    tr_all, _ = femnist_loader("ignored", None, 16, 16)
+    assert len(tr_all.dataset) == len(fed.x)
+    tr, _ = shakespeare_loader("ignored", None, 4, 4, 0)
+    xb, yb = next(iter(tr))
+    assert xb.shape == (4, 80) and yb.shape == (4, 80) and xb.dtype == torch.int64
+    batches = batch_data({"x": [[0.0] * 784] * 5, "y": [1, 2, 3, 4, 5]}, 2)
+    assert [b[0].shape[0] for b in batches] == [2, 2, 1] and batches[0][0].dtype == torch.float32 and batches[0][1].dtype == torch.int64
