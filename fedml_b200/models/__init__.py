@@ -55,10 +55,13 @@ def create(args, output_dim):
     if name == "mobilenet_v3":
         return MobileNetV3(model_mode=str(getattr(args, "model_mode", "LARGE")), num_classes=output_dim)
     if name == "efficientnet":
-        return EfficientNet(num_classes=output_dim)
+        variant = str(getattr(args, "efficientnet_variant", "efficientnet-b0"))
+        return EfficientNet.from_name(variant, num_classes=output_dim, image_size=getattr(args, "image_size", None))
     if name.startswith("vgg"):
         depth = int("".join(ch for ch in name if ch.isdigit()) or 11)
-        return VGG(depth, batch_norm=name.endswith("bn"), num_classes=output_dim)
+        small = str(dataset).lower() in ("cifar10", "cifar100", "cinic10", "fed_cifar100", "mnist", "femnist")
+        # torchvision layout (7x7 pool, 4096-wide head); 32x32 sets get the usual slim head on a 1x1 pool
+        return VGG(depth, num_classes=output_dim, batch_norm=name.endswith("bn"), pool=1 if small else 7, hidden=512 if small else 4096)
     if name in ("distilbert", "distilbert-base-uncased"):
         return distilbert(num_labels=output_dim, tiny=bool(getattr(args, "tiny_model", False)))
     if name == "gan":

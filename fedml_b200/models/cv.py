@@ -285,136 +285,9 @@ class ResNet56Server(nn.Module):
         return self.fc(self.avgpool(x).flatten(1))
 
 
-# ------------------------------------------------------------------ MobileNet / VGG / EfficientNet-lite
-class _DWSep(nn.Sequential):
-    def __init__(self, i, o, stride):
-        super().__init__(nn.Conv2d(i, i, 3, stride, 1, groups=i, bias=False), nn.BatchNorm2d(i), nn.ReLU(inplace=True),
-                         nn.Conv2d(i, o, 1, bias=False), nn.BatchNorm2d(o), nn.ReLU(inplace=True))
-
-
-class MobileNet(nn.Module):
-    """MobileNetV1 (depthwise-separable; reference cv/mobilenet.py:58-150), CIFAR-sized stem."""
-    cfg = [(64, 1), (128, 2), (128, 1), (256, 2), (256, 1), (512, 2)] + [(512, 1)] * 5 + [(1024, 2), (1024, 1)]
-
-    def __init__(self, width_multiplier=1.0, class_num=10):
-        super().__init__()
-        c = lambda v: max(8, int(v * width_multiplier))
-        self.stem = nn.Sequential(nn.Conv2d(3, c(32), 3, 1, 1, bias=False), nn.BatchNorm2d(c(32)), nn.ReLU(inplace=True))
-        blocks, i = [], c(32)
-        for o, s in self.cfg:
-            blocks.append(_DWSep(i, c(o), s)); i = c(o)
-        self.features = nn.Sequential(*blocks)
-        self.avg = nn.AdaptiveAvgPool2d(1)
-        self.fc = nn.Linear(i, class_num)
-
-    def forward(self, x):
-        return self.fc(self.avg(self.features(self.stem(x))).flatten(1))
-
-
-def mobilenet(alpha=1.0, class_num=10):
-    return MobileNet(alpha, class_num)
-
-
-class _SE(nn.Module):
-    def __init__(self, c, r=4):
-        super().__init__()
-        self.fc1, self.fc2 = nn.Conv2d(c, max(8, c // r), 1), nn.Conv2d(max(8, c // r), c, 1)
-
-    def forward(self, x):
-        s = F.adaptive_avg_pool2d(x, 1)
-        return x * F.hardsigmoid(self.fc2(F.relu(self.fc1(s))))
-
-
-class _MBConv(nn.Module):
-    def __init__(self, i, o, k, stride, expand, se, act):
-        super().__init__()
-        mid = i * expand
-        self.use_res = stride == 1 and i == o
-        layers = []
-        if expand != 1:
-            layers += [nn.Conv2d(i, mid, 1, bias=False), nn.BatchNorm2d(mid), act()]
-        layers += [nn.Conv2d(mid, mid, k, stride, k // 2, groups=mid, bias=False), nn.BatchNorm2d(mid), act()]
-        if se:
-            layers.append(_SE(mid))
-        layers += [nn.Conv2d(mid, o, 1, bias=False), nn.BatchNorm2d(o)]
-        self.block = nn.Sequential(*layers)
-
-    def forward(self, x):
-        return x + self.block(x) if self.use_res else self.block(x)
-
-
-class MobileNetV3(nn.Module):
-    """MobileNetV3 (cv/mobilenet_v3.py:148); ``model_mode`` LARGE / SMALL."""
-
-    def __init__(self, model_mode="LARGE", num_classes=10, multiplier=1.0):
-        super().__init__()
-        hs, re = nn.Hardswish, nn.ReLU
-        large = [(16, 3, 1, 1, False, re), (24, 3, 2, 4, False, re), (24, 3, 1, 3, False, re), (40, 5, 2, 3, True, re),
-                 (40, 5, 1, 3, True, re), (80, 3, 2, 6, False, hs), (80, 3, 1, 2, False, hs), (112, 3, 1, 6, True, hs),
-                 (160, 5, 2, 6, True, hs), (160, 5, 1, 6, True, hs)]
-        small = [(16, 3, 2, 1, True, re), (24, 3, 2, 4, False, re), (40, 5, 2, 4, True, hs), (48, 5, 1, 3, True, hs),
-                 (96, 5, 2, 6, True, hs)]
-        cfg = large if model_mode.upper() == "LARGE" else small
-        c = lambda v: max(8, int(v * multiplier))
-        self.stem = nn.Sequential(nn.Conv2d(3, c(16), 3, 1, 1, bias=False), nn.BatchNorm2d(c(16)), hs())
-        blocks, i = [], c(16)
-        for o, k, s, e, se, act in cfg:
-            blocks.append(_MBConv(i, c(o), k, s, e, se, act)); i = c(o)
-        self.blocks = nn.Sequential(*blocks)
-        last = 960 if model_mode.upper() == "LARGE" else 576
-        self.head = nn.Sequential(nn.Conv2d(i, last, 1, bias=False), nn.BatchNorm2d(last), hs())
-        self.classifier = nn.Sequential(nn.Linear(last, 1280), hs(), nn.Dropout(0.2), nn.Linear(1280, num_classes))
-
-    def forward(self, x):
-        x = self.head(self.blocks(self.stem(x)))
-        return self.classifier(F.adaptive_avg_pool2d(x, 1).flatten(1))
-
-
-class EfficientNet(nn.Module):
-    """EfficientNet-B0-shaped MBConv stack (cv/efficientnet.py:179)."""
-
-    def __init__(self, num_classes=10, width=1.0):
-        super().__init__()
-        act = nn.SiLU
-        cfg = [(16, 3, 1, 1), (24, 3, 2, 6), (24, 3, 1, 6), (40, 5, 2, 6), (40, 5, 1, 6), (80, 3, 2, 6), (80, 3, 1, 6),
-               (112, 5, 1, 6), (192, 5, 2, 6), (320, 3, 1, 6)]
-        c = lambda v: max(8, int(v * width))
-        self.stem = nn.Sequential(nn.Conv2d(3, c(32), 3, 1, 1, bias=False), nn.BatchNorm2d(c(32)), act())
-        blocks, i = [], c(32)
-        for o, k, s, e in cfg:
-            blocks.append(_MBConv(i, c(o), k, s, e, True, act)); i = c(o)
-        self.blocks = nn.Sequential(*blocks)
-        self.head = nn.Sequential(nn.Conv2d(i, 1280, 1, bias=False), nn.BatchNorm2d(1280), act())
-        self.fc = nn.Linear(1280, num_classes)
-
-    def forward(self, x):
-        return self.fc(F.adaptive_avg_pool2d(self.head(self.blocks(self.stem(x))), 1).flatten(1))
-
-
-_VGG = {11: [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
-        13: [64, 64, "M", 128, 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
-        16: [64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M"],
-        19: [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512, "M"]}
-
-
-class VGG(nn.Module):
-    def __init__(self, depth=11, batch_norm=False, num_classes=10):
-        super().__init__()
-        layers, i = [], 3
-        for v in _VGG[depth]:
-            if v == "M":
-                layers.append(nn.MaxPool2d(2, 2))
-            else:
-                layers.append(nn.Conv2d(i, v, 3, padding=1))
-                if batch_norm:
-                    layers.append(nn.BatchNorm2d(v))
-                layers.append(nn.ReLU(inplace=True)); i = v
-        self.features = nn.Sequential(*layers)
-        self.classifier = nn.Sequential(nn.Linear(512, 512), nn.ReLU(True), nn.Dropout(), nn.Linear(512, 512),
-                                        nn.ReLU(True), nn.Dropout(), nn.Linear(512, num_classes))
-
-    def forward(self, x):
-        return self.classifier(F.adaptive_avg_pool2d(self.features(x), 1).flatten(1))
+# ------------------------------------------------------------------ MobileNet / MobileNetV3 / EfficientNet / VGG
+# live in cv_zoo.py (state-dict compatible with the reference's files); re-exported here for the older import path
+from .cv_zoo import VGG, EfficientNet, MobileNet, MobileNetV3, mobilenet  # noqa: E402,F401
 
 
 # ------------------------------------------------------------------ GAN (FedGAN)
