@@ -1,8 +1,12 @@
-"""DARTS search space for FedNAS (reference: model/cv/darts/*.py, 2507 LoC: model_search.py, operations.py,
-genotypes.py, architect.py).  A compact but complete differentiable-NAS network: mixed operations over the
-standard primitive set, normal/reduction cells with continuous architecture parameters ``alphas_normal`` /
-``alphas_reduce`` (exposed through ``arch_parameters()``), ``genotype()`` decoding by the top-2 strongest
-non-``none`` edges per node."""
+"""DARTS / GDAS search space, derived networks and genotypes for FedNAS, with the reference's parameter tree.
+
+Reference: model/cv/darts/{operations,genotypes,model_search,model_search_gdas,model,architect,utils}.py.  A FedNAS run exchanges
+``state_dict``s of the search network (weights and ``alphas_*``) between server and clients, and the derived network is trained
+from a ``Genotype``; so module names (``cells.3._ops.5._ops.4.op.1.weight``, ``preprocess0``, ``conv_1`` ...), constructor
+signatures and ``genotype()``'s return value follow the reference, and ``tests/test_model_zoo.py`` loads the reference's files
+next to these and compares outputs.  What is different: one ``Network`` serves DARTS and GDAS (sub-class), the architecture step
+(``Architect``) is functional (no model copy), the factorised reduction also accepts odd feature-map sizes.
+"""
 from collections import namedtuple
 
 import torch
@@ -14,7 +18,50 @@ PRIMITIVES = ["none", "max_pool_3x3", "avg_pool_3x3", "skip_connect", "sep_conv_
               "dil_conv_5x5"]
 
 
-class _Zero(nn.Module):
+# ------------------------------------------------------------------------------------------------ operations
+class ReLUConvBN(nn.Module):
+    def __init__(self, C_in, C_out, kernel_size, stride, padding, affine=True):  # noqa: N803
+        super().__init__()
+        self.op = nn.Sequential(nn.ReLU(inplace=False), nn.Conv2d(C_in, C_out, kernel_size, stride=stride, padding=padding, bias=False),
+                                nn.BatchNorm2d(C_out, affine=affine))
+
+    def forward(self, x):
+        return self.op(x)
+
+
+class DilConv(nn.Module):
+    """ReLU, dilated depthwise convolution, 1x1 convolution, BN."""
+
+    def __init__(self, C_in, C_out, kernel_size, stride, padding, dilation, affine=True):  # noqa: N803
+        super().__init__()
+        self.op = nn.Sequential(
+            nn.ReLU(inplace=False),
+            nn.Conv2d(C_in, C_in, kernel_size, stride=stride, padding=padding, dilation=dilation, groups=C_in, bias=False),
+            nn.Conv2d(C_in, C_out, 1, bias=False), nn.BatchNorm2d(C_out, affine=affine))
+
+    def forward(self, x):
+        return self.op(x)
+
+
+class SepConv(nn.Module):
+    """Two (ReLU, depthwise, pointwise, BN) rounds; only the first one strides."""
+
+    def __init__(self, C_in, C_out, kernel_size, stride, padding, affine=True):  # noqa: N803
+        super().__init__()
+        dw = lambda s: nn.Conv2d(C_in, C_in, kernel_size, stride=s, padding=padding, groups=C_in, bias=False)      # noqa: E731
+        self.op = nn.Sequential(nn.ReLU(inplace=False), dw(stride), nn.Conv2d(C_in, C_in, 1, bias=False), nn.BatchNorm2d(C_in, affine=affine),
+                                nn.ReLU(inplace=False), dw(1), nn.Conv2d(C_in, C_out, 1, bias=False), nn.BatchNorm2d(C_out, affine=affine))
+
+    def forward(self, x):
+        return self.op(x)
+
+
+class Identity(nn.Module):
+    def forward(self, x):
+        return x
+
+
+class Zero(nn.Module):
     def __init__(self, stride):
         super().__init__()
         self.stride = stride
@@ -23,65 +70,83 @@ class _Zero(nn.Module):
         return x.mul(0.0) if self.stride == 1 else x[:, :, ::self.stride, ::self.stride].mul(0.0)
 
 
-class _FactorizedReduce(nn.Module):
-    def __init__(self, ci, co):
+class FactorizedReduce(nn.Module):
+    """Halves the resolution with two 1x1 stride-2 convolutions on the even and the odd pixel grid, concatenated."""
+
+    def __init__(self, C_in, C_out, affine=True):  # noqa: N803
         super().__init__()
-        self.c1 = nn.Conv2d(ci, co // 2, 1, 2, 0, bias=False)
-        self.c2 = nn.Conv2d(ci, co - co // 2, 1, 2, 0, bias=False)
-        self.bn = nn.BatchNorm2d(co, affine=False)
+        assert C_out % 2 == 0
+        self.relu = nn.ReLU(inplace=False)
+        self.conv_1 = nn.Conv2d(C_in, C_out // 2, 1, stride=2, padding=0, bias=False)
+        self.conv_2 = nn.Conv2d(C_in, C_out // 2, 1, stride=2, padding=0, bias=False)
+        self.bn = nn.BatchNorm2d(C_out, affine=affine)
 
     def forward(self, x):
-        x = F.relu(x)
-        shifted = F.pad(x, (0, 1, 0, 1))[:, :, 1:, 1:]
-        return self.bn(torch.cat([self.c1(x), self.c2(shifted)], 1))
-
-
-def _sep(ci, co, k, s, p):
-    return nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, ci, k, s, p, groups=ci, bias=False), nn.Conv2d(ci, ci, 1, bias=False),
-                         nn.BatchNorm2d(ci, affine=False), nn.ReLU(False), nn.Conv2d(ci, ci, k, 1, p, groups=ci, bias=False),
-                         nn.Conv2d(ci, co, 1, bias=False), nn.BatchNorm2d(co, affine=False))
-
-
-def _dil(ci, co, k, s, p, d):
-    return nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, ci, k, s, p, dilation=d, groups=ci, bias=False),
-                         nn.Conv2d(ci, co, 1, bias=False), nn.BatchNorm2d(co, affine=False))
+        x = self.relu(x)
+        odd = F.pad(x, (0, 1, 0, 1))[:, :, 1:, 1:] if (x.shape[2] % 2 or x.shape[3] % 2) else x[:, :, 1:, 1:]
+        return self.bn(torch.cat([self.conv_1(x), self.conv_2(odd)], dim=1))
 
 
 OPS = {
-    "none": lambda C, s: _Zero(s),
-    "avg_pool_3x3": lambda C, s: nn.Sequential(nn.AvgPool2d(3, s, 1, count_include_pad=False), nn.BatchNorm2d(C, affine=False)),
-    "max_pool_3x3": lambda C, s: nn.Sequential(nn.MaxPool2d(3, s, 1), nn.BatchNorm2d(C, affine=False)),
-    "skip_connect": lambda C, s: nn.Identity() if s == 1 else _FactorizedReduce(C, C),
-    "sep_conv_3x3": lambda C, s: _sep(C, C, 3, s, 1),
-    "sep_conv_5x5": lambda C, s: _sep(C, C, 5, s, 2),
-    "dil_conv_3x3": lambda C, s: _dil(C, C, 3, s, 2, 2),
-    "dil_conv_5x5": lambda C, s: _dil(C, C, 5, s, 4, 2),
+    "none": lambda C, stride, affine: Zero(stride),
+    "avg_pool_3x3": lambda C, stride, affine: nn.AvgPool2d(3, stride=stride, padding=1, count_include_pad=False),
+    "max_pool_3x3": lambda C, stride, affine: nn.MaxPool2d(3, stride=stride, padding=1),
+    "skip_connect": lambda C, stride, affine: Identity() if stride == 1 else FactorizedReduce(C, C, affine=affine),
+    "sep_conv_3x3": lambda C, stride, affine: SepConv(C, C, 3, stride, 1, affine=affine),
+    "sep_conv_5x5": lambda C, stride, affine: SepConv(C, C, 5, stride, 2, affine=affine),
+    "sep_conv_7x7": lambda C, stride, affine: SepConv(C, C, 7, stride, 3, affine=affine),
+    "dil_conv_3x3": lambda C, stride, affine: DilConv(C, C, 3, stride, 2, 2, affine=affine),
+    "dil_conv_5x5": lambda C, stride, affine: DilConv(C, C, 5, stride, 4, 2, affine=affine),
+    "conv_7x1_1x7": lambda C, stride, affine: nn.Sequential(
+        nn.ReLU(inplace=False), nn.Conv2d(C, C, (1, 7), stride=(1, stride), padding=(0, 3), bias=False),
+        nn.Conv2d(C, C, (7, 1), stride=(stride, 1), padding=(3, 0), bias=False), nn.BatchNorm2d(C, affine=affine)),
 }
 
 
+def _search_op(primitive, C, stride):
+    """Operation of the search network: no affine BN (the architecture weights carry the scale); pooling gets a BN behind it."""
+    op = OPS[primitive](C, stride, False)
+    return nn.Sequential(op, nn.BatchNorm2d(C, affine=False)) if "pool" in primitive else op
+
+
+# ------------------------------------------------------------------------------------------------ search network
 class MixedOp(nn.Module):
     def __init__(self, C, stride):
         super().__init__()
-        self._ops = nn.ModuleList(OPS[p](C, stride) for p in PRIMITIVES)
+        self._ops = nn.ModuleList(_search_op(p, C, stride) for p in PRIMITIVES)
 
     def forward(self, x, weights):
         return sum(w * op(x) for w, op in zip(weights, self._ops))
 
 
-class Cell(nn.Module):
-    def __init__(self, steps, multiplier, Cpp, Cp, C, reduction, reduction_prev):
+class _CellBase(nn.Module):
+    def __init__(self, steps, multiplier, C_prev_prev, C_prev, C, reduction, reduction_prev):  # noqa: N803
         super().__init__()
         self.reduction, self._steps, self._multiplier = reduction, steps, multiplier
-        self.pre0 = _FactorizedReduce(Cpp, C) if reduction_prev else \
-            nn.Sequential(nn.ReLU(False), nn.Conv2d(Cpp, C, 1, bias=False), nn.BatchNorm2d(C, affine=False))
-        self.pre1 = nn.Sequential(nn.ReLU(False), nn.Conv2d(Cp, C, 1, bias=False), nn.BatchNorm2d(C, affine=False))
+        self.preprocess0 = FactorizedReduce(C_prev_prev, C, affine=False) if reduction_prev else ReLUConvBN(C_prev_prev, C, 1, 1, 0, affine=False)
+        self.preprocess1 = ReLUConvBN(C_prev, C, 1, 1, 0, affine=False)
         self._ops = nn.ModuleList()
-        for i in range(steps):
+        self._bns = nn.ModuleList()
+
+    def _edges(self):
+        """(edge index, input state index, stride) of every edge, node by node."""
+        k = 0
+        for i in range(self._steps):
             for j in range(2 + i):
-                self._ops.append(MixedOp(C, 2 if reduction and j < 2 else 1))
+                yield k, j, 2 if self.reduction and j < 2 else 1
+                k += 1
+
+
+class Cell(_CellBase):
+    """Search cell: every edge is a :class:`MixedOp`; ``weights[k]`` are the (softmax or one-hot) operation weights of edge k."""
+
+    def __init__(self, steps, multiplier, C_prev_prev, C_prev, C, reduction, reduction_prev):  # noqa: N803
+        super().__init__(steps, multiplier, C_prev_prev, C_prev, C, reduction, reduction_prev)
+        for _, _, stride in self._edges():
+            self._ops.append(MixedOp(C, stride))
 
     def forward(self, s0, s1, weights):
-        states, off = [self.pre0(s0), self.pre1(s1)], 0
+        states, off = [self.preprocess0(s0), self.preprocess1(s1)], 0
         for _ in range(self._steps):
             s = sum(self._ops[off + j](h, weights[off + j]) for j, h in enumerate(states))
             off += len(states)
@@ -89,69 +154,154 @@ class Cell(nn.Module):
         return torch.cat(states[-self._multiplier:], dim=1)
 
 
-class Network(nn.Module):
-    """DARTS search network (``model_search.Network``)."""
+class InnerCell(_CellBase):
+    """Cell with the currently strongest operation on every edge (argmax over ``weights``, ``none`` included) - the discrete
+    network whose size ``Network.get_current_model_size`` reports."""
 
-    def __init__(self, C=8, num_classes=10, layers=3, steps=2, multiplier=2, stem_multiplier=3):
+    def __init__(self, steps, multiplier, C_prev_prev, C_prev, C, reduction, reduction_prev, weights):  # noqa: N803
+        super().__init__(steps, multiplier, C_prev_prev, C_prev, C, reduction, reduction_prev)
+        names = list(OPS.keys())
+        for k, _, stride in self._edges():
+            self._ops.append(_search_op(names[int(weights.data[k].argmax())], C, stride))
+
+    def forward(self, s0, s1):
+        states, off = [self.preprocess0(s0), self.preprocess1(s1)], 0
+        for _ in range(self._steps):
+            s = sum(self._ops[off + j](h) for j, h in enumerate(states))
+            off += len(states)
+            states.append(s)
+        return torch.cat(states[-self._multiplier:], dim=1)
+
+
+def _stack(make_cell, C, layers, multiplier, stem_multiplier):
+    """Stem + ``layers`` cells with reductions (channels doubled) at 1/3 and 2/3 of the depth -> (stem, cells, C_out)."""
+    c_curr = stem_multiplier * C
+    stem = nn.Sequential(nn.Conv2d(3, c_curr, 3, padding=1, bias=False), nn.BatchNorm2d(c_curr))
+    c_pp, c_p, c_curr = c_curr, c_curr, C
+    cells, reduction_prev = nn.ModuleList(), False
+    for i in range(layers):
+        reduction = i in (layers // 3, 2 * layers // 3)
+        if reduction:
+            c_curr *= 2
+        cells.append(make_cell(c_pp, c_p, c_curr, reduction, reduction_prev))
+        reduction_prev = reduction
+        c_pp, c_p = c_p, multiplier * c_curr
+    return stem, cells, c_p
+
+
+class ModelForModelSizeMeasure(nn.Module):
+    def __init__(self, C, num_classes, layers, criterion, alphas_normal, alphas_reduce, steps=4, multiplier=4, stem_multiplier=3):  # noqa: N803
         super().__init__()
-        self._steps, self._multiplier = steps, multiplier
-        Cc = stem_multiplier * C
-        self.stem = nn.Sequential(nn.Conv2d(3, Cc, 3, padding=1, bias=False), nn.BatchNorm2d(Cc))
-        Cpp, Cp, Cc = Cc, Cc, C
-        self.cells, red_prev = nn.ModuleList(), False
-        for i in range(layers):
-            red = layers >= 3 and i in (layers // 3, 2 * layers // 3)
-            if red:
-                Cc *= 2
-            self.cells.append(Cell(steps, multiplier, Cpp, Cp, Cc, red, red_prev))
-            red_prev = red
-            Cpp, Cp = Cp, multiplier * Cc
-        self.classifier = nn.Linear(Cp, num_classes)
-        k = sum(2 + i for i in range(steps))
-        self.alphas_normal = nn.Parameter(1e-3 * torch.randn(k, len(PRIMITIVES)))
-        self.alphas_reduce = nn.Parameter(1e-3 * torch.randn(k, len(PRIMITIVES)))
+        mk = lambda pp, p, c, red, red_prev: InnerCell(steps, multiplier, pp, p, c, red, red_prev, alphas_reduce if red else alphas_normal)  # noqa: E731
+        self.stem, self.cells, c_out = _stack(mk, C, layers, multiplier, stem_multiplier)
+        self.global_pooling = nn.AdaptiveAvgPool2d(1)
+        self.classifier = nn.Linear(c_out, num_classes)
+
+    def forward(self, x):
+        s0 = s1 = self.stem(x)
+        for cell in self.cells:
+            s0, s1 = s1, cell(s0, s1)
+        return self.classifier(self.global_pooling(s1).flatten(1))
+
+
+class Network(nn.Module):
+    """DARTS search network: ``Network(C, num_classes, layers, criterion, device, steps=4, multiplier=4, stem_multiplier=3)``."""
+
+    def __init__(self, C=16, num_classes=10, layers=8, criterion=None, device=None, steps=4, multiplier=4, stem_multiplier=3):  # noqa: N803
+        super().__init__()
+        self._C, self._num_classes, self._layers = C, num_classes, layers
+        self._criterion = criterion if criterion is not None else nn.CrossEntropyLoss()
+        self._steps, self._multiplier, self._stem_multiplier = steps, multiplier, stem_multiplier
+        self.device = device if device is not None else torch.device("cpu")
+        mk = lambda pp, p, c, red, red_prev: Cell(steps, multiplier, pp, p, c, red, red_prev)      # noqa: E731
+        self.stem, self.cells, c_out = _stack(mk, C, layers, multiplier, stem_multiplier)
+        self.global_pooling = nn.AdaptiveAvgPool2d(1)
+        self.classifier = nn.Linear(c_out, num_classes)
+        self._initialize_alphas()
+
+    # -- architecture parameters
+    def _edge_count(self):
+        return sum(2 + i for i in range(self._steps))
+
+    def _initialize_alphas(self):
+        k, n = self._edge_count(), len(PRIMITIVES)
+        self.alphas_normal = nn.Parameter(1e-3 * torch.randn(k, n))
+        self.alphas_reduce = nn.Parameter(1e-3 * torch.randn(k, n))
+        self._arch_parameters = [self.alphas_normal, self.alphas_reduce]
 
     def arch_parameters(self):
         return [self.alphas_normal, self.alphas_reduce]
+
+    def new_arch_parameters(self):
+        k, n = self._edge_count(), len(PRIMITIVES)
+        return [nn.Parameter(1e-3 * torch.randn(k, n, device=self.device)) for _ in range(2)]
 
     def weight_parameters(self):
         ids = {id(p) for p in self.arch_parameters()}
         return [p for p in self.parameters() if id(p) not in ids]
 
+    def new(self):
+        """A fresh network of the same shape carrying this one's architecture parameters."""
+        other = type(self)(self._C, self._num_classes, self._layers, self._criterion, self.device, self._steps, self._multiplier,
+                           self._stem_multiplier).to(self.device)
+        for x, y in zip(other.arch_parameters(), self.arch_parameters()):
+            x.data.copy_(y.data)
+        return other
+
+    # -- forward
+    def _weights(self, alphas):
+        return F.softmax(alphas, dim=-1)
+
+    def _run_cell(self, cell, s0, s1, weights):
+        return cell(s0, s1, weights)
+
     def forward(self, x):
         s0 = s1 = self.stem(x)
+        wn, wr = self._weights(self.alphas_normal), self._weights(self.alphas_reduce)
         for cell in self.cells:
-            w = F.softmax(self.alphas_reduce if cell.reduction else self.alphas_normal, dim=-1)
-            s0, s1 = s1, cell(s0, s1, w)
-        return self.classifier(F.adaptive_avg_pool2d(s1, 1).flatten(1))
+            s0, s1 = s1, self._run_cell(cell, s0, s1, wr if cell.reduction else wn)
+        return self.classifier(self.global_pooling(s1).flatten(1))
 
+    def _loss(self, x, target):
+        return self._criterion(self(x), target)
+
+    # -- decoding
     def genotype(self):
+        """``(Genotype, parametric ops in the normal cell, parametric ops in the reduction cell)``: per node the two incoming
+        edges with the strongest non-``none`` operation, each with that operation."""
         none = PRIMITIVES.index("none")
 
         def parse(weights):
-            gene, n, start = [], 2, 0
+            gene, conv_count, start = [], 0, 0
             for i in range(self._steps):
-                end = start + n
-                W = weights[start:end]
-                edges = sorted(range(i + 2), key=lambda x: -max(W[x][k] for k in range(len(W[x])) if k != none))[:2]
-                for j in edges:
-                    k_best = max((k for k in range(len(W[j])) if k != none), key=lambda k: W[j][k])
+                rows = weights[start:start + i + 2]
+                strength = lambda j: max(w for k, w in enumerate(rows[j]) if k != none)      # noqa: E731
+                for j in sorted(range(i + 2), key=lambda j: -strength(j))[:2]:
+                    k_best = max((k for k in range(len(rows[j])) if k != none), key=lambda k: (rows[j][k], -k))
+                    conv_count += k_best >= 4
                     gene.append((PRIMITIVES[k_best], j))
-                start, n = end, n + 1
-            return gene
+                start += i + 2
+            return gene, conv_count
 
-        concat = list(range(2 + self._steps - self._multiplier, self._steps + 2))
-        return Genotype(parse(F.softmax(self.alphas_normal, -1).tolist()), concat,
-                        parse(F.softmax(self.alphas_reduce, -1).tolist()), concat)
+        with torch.no_grad():
+            normal, n_count = parse(F.softmax(self.alphas_normal, dim=-1).tolist())
+            reduce, r_count = parse(F.softmax(self.alphas_reduce, dim=-1).tolist())
+        concat = range(2 + self._steps - self._multiplier, self._steps + 2)
+        return Genotype(normal=normal, normal_concat=concat, reduce=reduce, reduce_concat=concat), n_count, r_count
+
+    def get_current_model_size(self) -> float:
+        """Parameters (in millions, auxiliary heads excluded) of the discrete network the current alphas select."""
+        return count_parameters_in_MB(ModelForModelSizeMeasure(self._C, self._num_classes, self._layers, self._criterion, self.alphas_normal,
+                                                               self.alphas_reduce, self._steps, self._multiplier, self._stem_multiplier))
 
 
 class NetworkGDAS(Network):
-    """GDAS search space (reference: model/cv/darts/model_search_gdas.py): every edge samples ONE operation per forward
-    pass with the Gumbel-softmax straight-through estimator (temperature ``tau``, annealed by the trainer via
-    ``set_tau``), so a step costs one operation per edge instead of all eight, while the architecture parameters still get
-    gradients through the soft probabilities."""
+    """GDAS search space (reference: model/cv/darts/model_search_gdas.py ``Network_GumbelSoftmax``): every edge samples ONE
+    operation per forward pass with the Gumbel-softmax straight-through estimator (temperature ``tau``, annealed by the
+    trainer via ``set_tau``), so a step costs one operation per edge instead of all eight, while the architecture parameters
+    still get gradients through the soft probabilities.  In eval mode the strongest operation is taken (deterministic)."""
 
-    def __init__(self, *a, tau: float = 10.0, **kw):
+    def __init__(self, *a, tau: float = 5.0, **kw):
         super().__init__(*a, **kw)
         self.tau = float(tau)
 
@@ -161,32 +311,27 @@ class NetworkGDAS(Network):
     def get_tau(self) -> float:
         return self.tau
 
-    def _edge_weights(self, alphas):
+    def _weights(self, alphas):
         if not self.training:
             idx = alphas.argmax(dim=-1, keepdim=True)
             return torch.zeros_like(alphas).scatter_(-1, idx, 1.0)
         return F.gumbel_softmax(alphas, tau=self.tau, hard=True, dim=-1)     # one-hot forward, soft backward
 
-    def forward(self, x):
-        s0 = s1 = self.stem(x)
-        wn, wr = self._edge_weights(self.alphas_normal), self._edge_weights(self.alphas_reduce)
-        for cell in self.cells:
-            s0, s1 = s1, _gdas_cell(cell, s0, s1, wr if cell.reduction else wn)
-        return self.classifier(F.adaptive_avg_pool2d(s1, 1).flatten(1))
+    def _run_cell(self, cell, s0, s1, weights):
+        """Cell forward that evaluates only the sampled operation of every edge."""
+        states, off = [cell.preprocess0(s0), cell.preprocess1(s1)], 0
+        for _ in range(cell._steps):
+            acc = 0
+            for j, h in enumerate(states):
+                w = weights[off + j]
+                k = int(w.argmax())
+                acc = acc + w[k] * cell._ops[off + j]._ops[k](h)
+            off += len(states)
+            states.append(acc)
+        return torch.cat(states[-cell._multiplier:], dim=1)
 
 
-def _gdas_cell(cell: Cell, s0, s1, weights):
-    """Cell forward that evaluates only the sampled operation of every edge."""
-    states, off = [cell.pre0(s0), cell.pre1(s1)], 0
-    for _ in range(cell._steps):
-        acc = 0
-        for j, h in enumerate(states):
-            w = weights[off + j]
-            k = int(w.argmax())
-            acc = acc + w[k] * cell._ops[off + j]._ops[k](h)
-        off += len(states)
-        states.append(acc)
-    return torch.cat(states[-cell._multiplier:], dim=1)
+Network_GumbelSoftmax = NetworkGDAS      # noqa: N816  (the reference's class name)
 
 
 class Architect:
@@ -278,6 +423,22 @@ DARTS_V1 = _genotype("sep_conv_3x3@1 sep_conv_3x3@0 skip_connect@0 sep_conv_3x3@
 DARTS_V2 = _genotype("sep_conv_3x3@0 sep_conv_3x3@1 sep_conv_3x3@0 sep_conv_3x3@1 sep_conv_3x3@1 skip_connect@0 skip_connect@0 dil_conv_3x3@2",
                      "max_pool_3x3@0 max_pool_3x3@1 skip_connect@2 max_pool_3x3@1 max_pool_3x3@0 skip_connect@2 skip_connect@2 max_pool_3x3@1")
 DARTS = DARTS_V2
+
+
+def _genotype_n(normal: str, normal_concat, reduce: str, reduce_concat) -> Genotype:
+    parse = lambda s: [(op, int(j)) for op, j in (tok.split("@") for tok in s.split())]      # noqa: E731
+    return Genotype(parse(normal), list(normal_concat), parse(reduce), list(reduce_concat))
+
+
+# five-node cells found by reinforcement learning (Zoph et al. 2018) and by evolution (Real et al. 2018), as DARTS lists them
+NASNet = _genotype_n("sep_conv_5x5@1 sep_conv_3x3@0 sep_conv_5x5@0 sep_conv_3x3@0 avg_pool_3x3@1 skip_connect@0 avg_pool_3x3@0 "
+                     "avg_pool_3x3@0 sep_conv_3x3@1 skip_connect@1", [2, 3, 4, 5, 6],
+                     "sep_conv_5x5@1 sep_conv_7x7@0 max_pool_3x3@1 sep_conv_7x7@0 avg_pool_3x3@1 sep_conv_5x5@0 skip_connect@3 "
+                     "avg_pool_3x3@2 sep_conv_3x3@2 max_pool_3x3@1", [4, 5, 6])
+AmoebaNet = _genotype_n("avg_pool_3x3@0 max_pool_3x3@1 sep_conv_3x3@0 sep_conv_5x5@2 sep_conv_3x3@0 avg_pool_3x3@3 sep_conv_3x3@1 "
+                        "skip_connect@1 skip_connect@0 avg_pool_3x3@1", [4, 5, 6],
+                        "avg_pool_3x3@0 sep_conv_3x3@1 max_pool_3x3@0 sep_conv_7x7@2 sep_conv_7x7@0 avg_pool_3x3@1 max_pool_3x3@0 "
+                        "max_pool_3x3@1 conv_7x1_1x7@0 sep_conv_3x3@5", [3, 4, 6])
 FedNAS_V1 = _genotype("sep_conv_3x3@1 sep_conv_3x3@0 sep_conv_3x3@2 sep_conv_5x5@0 sep_conv_3x3@1 sep_conv_5x5@3 dil_conv_5x5@3 sep_conv_3x3@4",
                       "max_pool_3x3@0 skip_connect@1 max_pool_3x3@0 max_pool_3x3@2 max_pool_3x3@0 dil_conv_5x5@1 max_pool_3x3@0 dil_conv_5x5@2")
 
@@ -291,36 +452,24 @@ def drop_path(x, drop_prob: float):
     return x / keep * mask
 
 
-def _eval_op(name, C, stride):
-    """Operation of a derived cell: affine BatchNorm (the search network uses affine=False so that the architecture weights
-    carry the scale)."""
-    op = OPS[name](C, stride)
-    for m in op.modules():
-        if isinstance(m, nn.BatchNorm2d) and not m.affine:
-            m.affine = True
-            m.weight, m.bias = nn.Parameter(torch.ones(m.num_features)), nn.Parameter(torch.zeros(m.num_features))
-    return op
-
-
 class DerivedCell(nn.Module):
     def __init__(self, genotype: Genotype, Cpp, Cp, C, reduction, reduction_prev):
         super().__init__()
         self.reduction = reduction
-        relu_conv_bn = lambda ci: nn.Sequential(nn.ReLU(False), nn.Conv2d(ci, C, 1, bias=False), nn.BatchNorm2d(C))      # noqa: E731
-        self.pre0 = _FactorizedReduce(Cpp, C) if reduction_prev else relu_conv_bn(Cpp)
-        self.pre1 = relu_conv_bn(Cp)
+        self.preprocess0 = FactorizedReduce(Cpp, C) if reduction_prev else ReLUConvBN(Cpp, C, 1, 1, 0)
+        self.preprocess1 = ReLUConvBN(Cp, C, 1, 1, 0)
         genes, self._concat = (genotype.reduce, list(genotype.reduce_concat)) if reduction else (genotype.normal, list(genotype.normal_concat))
         self._indices = [j for _, j in genes]
-        self._ops = nn.ModuleList(_eval_op(name, C, 2 if reduction and j < 2 else 1) for name, j in genes)
-        self.multiplier = len(self._concat)
+        self._ops = nn.ModuleList(OPS[name](C, 2 if reduction and j < 2 else 1, True) for name, j in genes)
+        self._steps, self.multiplier = len(genes) // 2, len(self._concat)
 
     def forward(self, s0, s1, drop_prob=0.0):
-        states = [self.pre0(s0), self.pre1(s1)]
-        for i in range(len(self._ops) // 2):
+        states = [self.preprocess0(s0), self.preprocess1(s1)]
+        for i in range(self._steps):
             hs = []
             for k in (2 * i, 2 * i + 1):
                 h = self._ops[k](states[self._indices[k]])
-                if self.training and drop_prob > 0.0 and not isinstance(self._ops[k], nn.Identity):
+                if self.training and drop_prob > 0.0 and not isinstance(self._ops[k], Identity):
                     h = drop_path(h, drop_prob)
                 hs.append(h)
             states.append(hs[0] + hs[1])
@@ -363,7 +512,8 @@ class NetworkCIFAR(nn.Module):
             Cpp, Cp = Cp, cell.multiplier * Cc
             if i == 2 * layers // 3:
                 C_aux = Cp
-        self.auxiliary_head = AuxiliaryHeadCIFAR(C_aux, num_classes) if auxiliary else None
+        if auxiliary:
+            self.auxiliary_head = AuxiliaryHeadCIFAR(C_aux, num_classes)
         self.global_pooling = nn.AdaptiveAvgPool2d(1)
         self.classifier = nn.Linear(Cp, num_classes)
 
@@ -372,10 +522,136 @@ class NetworkCIFAR(nn.Module):
         s0 = s1 = self.stem(x)
         for i, cell in enumerate(self.cells):
             s0, s1 = s1, cell(s0, s1, self.drop_path_prob)
-            if i == 2 * self._layers // 3 and self.auxiliary_head is not None and self.training:
+            if i == 2 * self._layers // 3 and self._auxiliary and self.training:
                 aux = self.auxiliary_head(s1)
         return self.classifier(self.global_pooling(s1).flatten(1)), aux
 
 
+class AuxiliaryHeadImageNet(nn.Module):
+    """Auxiliary classifier for 14x14 feature maps (the second convolution has no BN, as published)."""
+
+    def __init__(self, C, num_classes):
+        super().__init__()
+        self.features = nn.Sequential(nn.ReLU(True), nn.AvgPool2d(5, stride=2, padding=0, count_include_pad=False),
+                                      nn.Conv2d(C, 128, 1, bias=False), nn.BatchNorm2d(128), nn.ReLU(True),
+                                      nn.Conv2d(128, 768, 2, bias=False), nn.ReLU(True))
+        self.classifier = nn.Linear(768, num_classes)
+
+    def forward(self, x):
+        return self.classifier(self.features(x).flatten(1))
+
+
+class NetworkImageNet(nn.Module):
+    """Derived network for 224x224 inputs (reference model/cv/darts/model.py:160-216): a three-convolution stem that reduces the
+    resolution eight-fold (``stem0`` 4x, ``stem1`` 2x), then the cells; 7x7 average pool."""
+
+    def __init__(self, C, num_classes, layers, auxiliary, genotype):
+        super().__init__()
+        self._layers, self._auxiliary, self.drop_path_prob = layers, auxiliary, 0.5
+        self.stem0 = nn.Sequential(nn.Conv2d(3, C // 2, 3, stride=2, padding=1, bias=False), nn.BatchNorm2d(C // 2), nn.ReLU(True),
+                                   nn.Conv2d(C // 2, C, 3, stride=2, padding=1, bias=False), nn.BatchNorm2d(C))
+        self.stem1 = nn.Sequential(nn.ReLU(True), nn.Conv2d(C, C, 3, stride=2, padding=1, bias=False), nn.BatchNorm2d(C))
+        Cpp, Cp, Cc = C, C, C
+        self.cells = nn.ModuleList()
+        red_prev, C_aux = True, None
+        for i in range(layers):
+            red = i in (layers // 3, 2 * layers // 3)
+            if red:
+                Cc *= 2
+            cell = DerivedCell(genotype, Cpp, Cp, Cc, red, red_prev)
+            self.cells.append(cell)
+            red_prev = red
+            Cpp, Cp = Cp, cell.multiplier * Cc
+            if i == 2 * layers // 3:
+                C_aux = Cp
+        if auxiliary:
+            self.auxiliary_head = AuxiliaryHeadImageNet(C_aux, num_classes)
+        self.global_pooling = nn.AvgPool2d(7)
+        self.classifier = nn.Linear(Cp, num_classes)
+
+    def forward(self, x):
+        aux = None
+        s0 = self.stem0(x)
+        s1 = self.stem1(s0)
+        for i, cell in enumerate(self.cells):
+            s0, s1 = s1, cell(s0, s1, self.drop_path_prob)
+            if i == 2 * self._layers // 3 and self._auxiliary and self.training:
+                aux = self.auxiliary_head(s1)
+        return self.classifier(self.global_pooling(s1).flatten(1)), aux
+
+
+# ============================================================================ training-script utilities (darts/utils.py)
 def count_parameters_in_MB(model) -> float:      # noqa: N802  (the reference's name)
     return sum(p.numel() for n, p in model.named_parameters() if "auxiliary" not in n) / 1e6
+
+
+class AvgrageMeter:      # (sic) the reference's spelling
+    """Running mean of a metric weighted by batch size."""
+
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self.avg, self.sum, self.cnt = 0, 0, 0
+
+    def update(self, val, n=1):
+        self.sum += val * n
+        self.cnt += n
+        self.avg = self.sum / self.cnt
+
+
+def accuracy(output, target, topk=(1,)):
+    """Top-k accuracies in percent, one 0-dim tensor per k."""
+    _, pred = output.topk(max(topk), dim=1, largest=True, sorted=True)
+    hit = pred.eq(target.view(-1, 1))
+    return [hit[:, :k].any(dim=1).float().sum() * (100.0 / target.size(0)) for k in topk]
+
+
+def save(model, model_path):
+    torch.save(model.state_dict(), model_path)
+
+
+def load(model, model_path):
+    model.load_state_dict(torch.load(model_path, map_location="cpu"))
+
+
+def save_checkpoint(state, is_best, save):  # noqa: A002
+    import os
+    import shutil
+    filename = os.path.join(save, "checkpoint.pth.tar")
+    torch.save(state, filename)
+    if is_best:
+        shutil.copyfile(filename, os.path.join(save, "model_best.pth.tar"))
+
+
+def create_exp_dir(path, scripts_to_save=None):
+    import os
+    import shutil
+    os.makedirs(path, exist_ok=True)
+    if scripts_to_save:
+        os.makedirs(os.path.join(path, "scripts"), exist_ok=True)
+        for script in scripts_to_save:
+            shutil.copyfile(script, os.path.join(path, "scripts", os.path.basename(script)))
+
+
+def plot(genotype, filename=None) -> str:
+    """Graphviz DOT text of one cell (``genotype.normal`` or ``genotype.reduce``: a list of (operation, input) pairs): the two
+    cell inputs ``c_{k-2}``, ``c_{k-1}``, one node per step with its two incoming operation edges, and ``c_{k}`` collecting
+    the steps (reference: model/cv/darts/visualize.py).  Written to ``filename`` (+ ``.dot``) when given; rendering is left to
+    the ``dot`` tool - the python graphviz binding is not required."""
+    steps = len(genotype) // 2
+    lines = ["digraph cell {", "  rankdir=LR;", '  node [style=filled, shape=rect, fontname="times"];',
+             '  "c_{k-2}" [fillcolor=darkseagreen2];', '  "c_{k-1}" [fillcolor=darkseagreen2];']
+    lines += [f'  "{i}" [fillcolor=lightblue];' for i in range(steps)]
+    name = lambda j: "c_{k-2}" if j == 0 else "c_{k-1}" if j == 1 else str(j - 2)      # noqa: E731
+    for i in range(steps):
+        for op, j in genotype[2 * i:2 * i + 2]:
+            lines.append(f'  "{name(j)}" -> "{i}" [label="{op}"];')
+    lines.append('  "c_{k}" [fillcolor=palegoldenrod];')
+    lines += [f'  "{i}" -> "c_{{k}}";' for i in range(steps)]
+    lines.append("}")
+    text = "\n".join(lines) + "\n"
+    if filename:
+        with open(filename if filename.endswith(".dot") else filename + ".dot", "w") as fh:
+            fh.write(text)
+    return text

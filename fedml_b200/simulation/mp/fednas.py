@@ -71,7 +71,14 @@ class FedNASTrainer(ClientTrainer):
                 l += float(nn.functional.cross_entropy(o, y.to(device), reduction="sum"))
                 c += float((o.argmax(1).cpu() == y).sum())
                 n += len(y)
-        return {"test_correct": c, "test_loss": l, "test_total": n, "genotype": str(m.genotype()) if hasattr(m, "genotype") else ""}
+        return {"test_correct": c, "test_loss": l, "test_total": n, "genotype": str(m.genotype()[0]) if hasattr(m, "genotype") else ""}
+
+
+def _search_kwargs(args, class_num):
+    """Search-network shape from the run arguments (reference defaults: 16 channels, 8 layers, 4 steps; the defaults here are the
+    small configuration the CI-sized runs use)."""
+    return dict(C=int(getattr(args, "init_channels", 8)), num_classes=class_num, layers=int(getattr(args, "layers", 3)),
+                steps=int(getattr(args, "nas_steps", 2)), multiplier=int(getattr(args, "nas_multiplier", 2)))
 
 
 def FedML_FedNAS_distributed(args, process_id, worker_number, comm, device, dataset, model=None, model_trainer=None,  # noqa: N802
@@ -87,11 +94,11 @@ def FedML_FedNAS_distributed(args, process_id, worker_number, comm, device, data
                                         model_trainer or FedNASTrainer(model, args), backend=backend, **kw)
     if not isinstance(model, Network) and str(getattr(args, "nas_space", "darts")).lower() == "gdas":
         from ...models.darts import NetworkGDAS
-        model = NetworkGDAS(C=int(getattr(args, "init_channels", 8)), num_classes=dataset[7], layers=int(getattr(args, "layers", 3)))
+        model = NetworkGDAS(**_search_kwargs(args, dataset[7]))
     if not isinstance(model, Network):
-        model = Network(C=int(getattr(args, "init_channels", 8)), num_classes=dataset[7], layers=int(getattr(args, "layers", 3)))
+        model = Network(**_search_kwargs(args, dataset[7]))
     out = FedML_FedAvg_distributed(args, process_id, worker_number, comm, device, dataset, model,
                                    model_trainer or FedNASTrainer(model, args), backend=backend, **kw)
     if process_id == 0:
-        out.genotype = out.trainer.model.genotype()
+        out.genotype, out.normal_cnn_count, out.reduce_cnn_count = out.trainer.model.genotype()
     return out

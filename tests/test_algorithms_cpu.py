@@ -388,12 +388,12 @@ def test_darts_second_order_architect_and_gdas():
     arch.step(xt, yt, xv, yv, eta, None, unrolled=True)
     assert not torch.equal(before[0], net.arch_parameters()[0])
     # GDAS: hard one-hot edge weights in the forward pass, gradients reach the alphas, tau is adjustable
-    g = NetworkGDAS(C=4, num_classes=4, layers=1, steps=2, multiplier=2, tau=5.0)
+    g = NetworkGDAS(C=4, num_classes=4, layers=3, steps=2, multiplier=2, tau=5.0)      # one normal cell, two reduction cells
     g.train()
-    wgt = g._edge_weights(g.alphas_normal)
+    wgt = g._weights(g.alphas_normal)
     assert torch.equal(wgt.sum(-1), torch.ones(wgt.shape[0])) and set(wgt.unique().tolist()) <= {0.0, 1.0}
     torch.nn.functional.cross_entropy(g(xt.float()), yt).backward()
-    assert g.alphas_normal.grad is not None and float(g.alphas_normal.grad.abs().sum()) > 0
+    assert all(a_.grad is not None and float(a_.grad.abs().sum()) > 0 for a_ in g.arch_parameters())
     g.set_tau(1.0); assert g.get_tau() == 1.0
     g.eval(); assert g(xt.float()).shape == (6, 4)
     for kw in (dict(arch_order=2), dict(nas_space="gdas")):
@@ -427,7 +427,7 @@ def test_fednas_train_stage_and_derived_network():
     the auxiliary head and drop path."""
     from fedml_b200.models.darts import DARTS_V1, DARTS_V2, FedNAS_V1, Network, NetworkCIFAR, count_parameters_in_MB
     assert abs(count_parameters_in_MB(NetworkCIFAR(36, 10, 20, True, DARTS_V2)) - 3.35) < 0.02
-    for g in (DARTS_V1, FedNAS_V1, Network(C=8, layers=3).genotype()):
+    for g in (DARTS_V1, FedNAS_V1, Network(C=8, layers=3).genotype()[0]):
         net = NetworkCIFAR(8, 10, 5, True, g)
         net.drop_path_prob = 0.3
         logits, aux = net.train()(torch.randn(3, 3, 32, 32))

@@ -119,3 +119,115 @@ def test_structure_without_the_reference():
     slim = Z.VGG(16, num_classes=10, batch_norm=True, pool=1, hidden=512)
     assert slim(torch.randn(2, 3, 32, 32)).shape == (2, 10) and slim.classifier[0].in_features == 512
     assert len(Z.make_layers(Z.cfgs["E"])) == 16 * 2 + 5 and Z.vgg19_bn.__name__ == "vgg19_bn"
+
+
+# ------------------------------------------------------------------------------------------------ DARTS
+DREF = "/root/reference/python/fedml/model/cv/darts/"
+
+
+def _dref(name):
+    if "refdarts" not in sys.modules:
+        pkg = types.ModuleType("refdarts")
+        pkg.__path__ = [DREF]
+        sys.modules["refdarts"] = pkg
+    full = "refdarts." + name
+    if full not in sys.modules:
+        spec = importlib.util.spec_from_file_location(full, DREF + name + ".py")
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[full] = mod
+        spec.loader.exec_module(mod)
+    return sys.modules[full]
+
+
+@needs_ref
+def test_darts_search_network_matches_reference(capsys):
+    from fedml_b200.models import darts as D
+    for n in ("genotypes", "operations", "utils"):
+        _dref(n)
+    ms = _dref("model_search")
+    crit = torch.nn.CrossEntropyLoss()
+    ref = ms.Network(8, 10, 5, crit, torch.device("cpu"))
+    mine = D.Network(8, 10, 5, crit, torch.device("cpu"))
+    _same(ref, mine, torch.randn(3, 3, 32, 32), train=True)
+    _same(ref, mine, torch.randn(3, 3, 32, 32), train=False)
+    # decoding: same genotype and the same counts of parametric operations
+    torch.manual_seed(3)
+    for p_ref, p_mine in zip(ref.arch_parameters(), mine.arch_parameters()):
+        p_ref.data.normal_()
+        p_mine.data.copy_(p_ref.data)
+    g_ref, n_ref, r_ref = ref.genotype()
+    g_mine, n_mine, r_mine = mine.genotype()
+    assert (g_mine.normal, g_mine.reduce, list(g_mine.normal_concat), n_mine, r_mine) == \
+        (g_ref.normal, g_ref.reduce, list(g_ref.normal_concat), n_ref, r_ref)
+    assert abs(mine.get_current_model_size() - ref.get_current_model_size()) < 1e-9
+    clone = mine.new()
+    assert torch.equal(clone.alphas_normal, mine.alphas_normal) and clone.alphas_normal is not mine.alphas_normal
+    # GDAS: same parameter tree (the forward pass samples, so only the tree is compared)
+    gd = _dref("model_search_gdas").Network_GumbelSoftmax(8, 10, 5, crit, torch.device("cpu"))
+    mine_gd = D.Network_GumbelSoftmax(8, 10, 5, crit, torch.device("cpu"))
+    assert [(k, tuple(v.shape)) for k, v in gd.state_dict().items()] == [(k, tuple(v.shape)) for k, v in mine_gd.state_dict().items()]
+    assert mine_gd.get_tau() == gd.get_tau() == 5
+    capsys.readouterr()
+
+
+@needs_ref
+@pytest.mark.parametrize("arch", ["DARTS_V1", "DARTS_V2", "FedNAS_V1", "NASNet", "AmoebaNet"])
+def test_darts_derived_networks_match_reference(arch, capsys):
+    from fedml_b200.models import darts as D
+    for n in ("genotypes", "operations", "utils"):
+        _dref(n)
+    g_ref, g_mine = getattr(_dref("genotypes"), arch), getattr(D, arch)
+    assert (list(g_ref.normal), list(g_ref.normal_concat), list(g_ref.reduce), list(g_ref.reduce_concat)) == \
+        (list(g_mine.normal), list(g_mine.normal_concat), list(g_mine.reduce), list(g_mine.reduce_concat))
+    m = _dref("model")
+    ref, mine = m.NetworkCIFAR(8, 10, 5, True, g_ref), D.NetworkCIFAR(8, 10, 5, True, g_mine)
+    ref.drop_path_prob = mine.drop_path_prob = 0.0          # the reference's drop_path needs a CUDA tensor
+    a = [(k, tuple(v.shape)) for k, v in ref.state_dict().items()]
+    assert a == [(k, tuple(v.shape)) for k, v in mine.state_dict().items()]
+    mine.load_state_dict(ref.state_dict())
+    x = torch.randn(3, 3, 32, 32)
+    for mode in (True, False):
+        ref.train(mode)
+        mine.train(mode)
+        with torch.no_grad():
+            (la, aa), (lb, ab) = ref(x), mine(x)
+        torch.testing.assert_close(lb, la, rtol=1e-5, atol=1e-6)
+        assert (aa is None) == (ab is None)
+        if aa is not None:
+            torch.testing.assert_close(ab, aa, rtol=1e-5, atol=1e-6)
+    if arch == "DARTS_V2":
+        ri, mi = m.NetworkImageNet(16, 20, 5, True, g_ref), D.NetworkImageNet(16, 20, 5, True, g_mine)
+        ri.drop_path_prob = mi.drop_path_prob = 0.0
+        assert [(k, tuple(v.shape)) for k, v in ri.state_dict().items()] == [(k, tuple(v.shape)) for k, v in mi.state_dict().items()]
+        mi.load_state_dict(ri.state_dict())
+        xi = torch.randn(2, 3, 224, 224)
+        with torch.no_grad():
+            (la, aa), (lb, ab) = ri.train()(xi), mi.train()(xi)
+        torch.testing.assert_close(lb, la, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(ab, aa, rtol=1e-4, atol=1e-5)
+    capsys.readouterr()
+
+
+def test_darts_utilities(tmp_path):
+    from fedml_b200.models import darts as D
+    out = torch.tensor([[0.1, 0.5, 0.4], [0.8, 0.15, 0.05], [0.2, 0.3, 0.5], [0.3, 0.6, 0.1]])
+    top1, top2 = D.accuracy(out, torch.tensor([1, 1, 2, 0]), topk=(1, 2))
+    assert float(top1) == 50.0 and float(top2) == 100.0
+    meter = D.AvgrageMeter()
+    meter.update(2.0, 3)
+    meter.update(4.0, 1)
+    assert meter.avg == 2.5 and meter.cnt == 4
+    net = D.NetworkCIFAR(4, 10, 2, True, D.DARTS_V2)
+    D.save(net, str(tmp_path / "w.pt"))
+    other = D.NetworkCIFAR(4, 10, 2, True, D.DARTS_V2)
+    D.load(other, str(tmp_path / "w.pt"))
+    assert all(torch.equal(a, b) for a, b in zip(net.state_dict().values(), other.state_dict().values()))
+    assert D.count_parameters_in_MB(net) < sum(p.numel() for p in net.parameters()) / 1e6          # auxiliary head excluded
+    D.save_checkpoint({"epoch": 1}, True, str(tmp_path))
+    assert (tmp_path / "model_best.pth.tar").exists()
+    D.create_exp_dir(str(tmp_path / "exp"), [__file__])
+    assert (tmp_path / "exp" / "scripts" / os.path.basename(__file__)).exists()
+    dot = D.plot(D.DARTS_V2.normal, str(tmp_path / "normal"))
+    assert (tmp_path / "normal.dot").read_text() == dot and dot.count("->") == 8 + 4 and '"c_{k-2}" -> "0" [label="sep_conv_3x3"]' in dot
+    # odd feature maps go through the factorised reduction (the reference's slicing only handles even sizes)
+    assert D.FactorizedReduce(4, 8)(torch.randn(2, 4, 7, 7)).shape == (2, 8, 4, 4)
