@@ -347,8 +347,16 @@ class Architect:
 
     def __init__(self, model: Network, criterion=None, arch_learning_rate=3e-4, arch_weight_decay=1e-3, momentum=0.9,
                  weight_decay=3e-4):
+        """Also accepts the reference's form ``Architect(model, criterion, args, device)``: ``args`` then supplies
+        ``arch_learning_rate``, ``arch_weight_decay``, ``momentum`` and ``weight_decay``."""
+        if hasattr(arch_learning_rate, "arch_learning_rate"):
+            args = arch_learning_rate
+            self.device = arch_weight_decay if isinstance(arch_weight_decay, (torch.device, str)) else None
+            arch_learning_rate, arch_weight_decay = float(args.arch_learning_rate), float(getattr(args, "arch_weight_decay", 1e-3))
+            momentum, weight_decay = float(getattr(args, "momentum", 0.9)), float(getattr(args, "weight_decay", 3e-4))
         self.model, self.criterion = model, criterion or nn.CrossEntropyLoss()
         self.momentum, self.weight_decay = float(momentum), float(weight_decay)
+        self.network_momentum, self.network_weight_decay = self.momentum, self.weight_decay
         self.optimizer = torch.optim.Adam(model.arch_parameters(), lr=arch_learning_rate, betas=(0.5, 0.999),
                                           weight_decay=arch_weight_decay)
 
@@ -402,12 +410,46 @@ class Architect:
             out.append(d - eta * (gp - gm) / (2 * eps))
         return out
 
-    def step(self, x_train, y_train, x_valid, y_valid, eta: float, network_optimizer=None, unrolled: bool = False):
-        grads = self.arch_gradient(x_train, y_train, x_valid, y_valid, eta, network_optimizer, unrolled)
+    def _apply(self, grads):
         self.optimizer.zero_grad(set_to_none=True)
         for p, gi in zip(self.model.arch_parameters(), grads):
             p.grad = gi.detach().clone()
         self.optimizer.step()
+
+    def step(self, x_train, y_train, x_valid, y_valid, eta: float, network_optimizer=None, unrolled: bool = False):
+        self._apply(self.arch_gradient(x_train, y_train, x_valid, y_valid, eta, network_optimizer, unrolled))
+
+    # -- mixed-level rules (MiLeNAS; reference architect.py:83-225, 364-455): the architecture follows the validation loss AND,
+    #    weighted by lambda_train, the training loss, which removes the need for the second-order term in practice
+    def _alpha_grad(self, x, y):
+        gs = torch.autograd.grad(self.criterion(self.model(x), y), self.model.arch_parameters(), allow_unused=True)
+        return [torch.zeros_like(p) if g is None else g for g, p in zip(gs, self.model.arch_parameters())]
+
+    def step_v2(self, input_train, target_train, input_valid, target_valid, lambda_train_regularizer=1.0, lambda_valid_regularizer=1.0):
+        """alpha <- Adam(grad_a L_val + lambda_train * grad_a L_train), both at the current weights.  ``lambda_valid`` is part of
+        the reference's signature and, like there, does not enter the first-order rule."""
+        g_train = self._alpha_grad(input_train, target_train)
+        g_val = self._alpha_grad(input_valid, target_valid)
+        self._apply([gv + lambda_train_regularizer * gt for gv, gt in zip(g_val, g_train)])
+
+    def step_wa(self, input_train, target_train, input_valid, target_valid, lambda_regularizer=1.0):
+        self.step_v2(input_train, target_train, input_valid, target_valid, lambda_regularizer)
+
+    def step_single_level(self, input_train, target_train):
+        """Single-level optimisation: the architecture follows the training loss only."""
+        self._apply(self._alpha_grad(input_train, target_train))
+
+    def step_AOS(self, input_train, target_train, input_valid, target_valid):  # noqa: N802
+        """Alternating optimisation, first order: the architecture follows the validation loss only."""
+        self._apply(self._alpha_grad(input_valid, target_valid))
+
+    def step_v2_2ndorder(self, input_train, target_train, input_valid, target_valid, eta, network_optimizer,
+                         lambda_train_regularizer=1.0, lambda_valid_regularizer=1.0):
+        """Mixed-level rule with the unrolled weights: ``lambda_valid * d/da L_val(w', a) + lambda_train * d/da L_train(w', a)``
+        where both terms include the finite-difference second-order correction of :meth:`arch_gradient`."""
+        g_val = self.arch_gradient(input_train, target_train, input_valid, target_valid, eta, network_optimizer, unrolled=True)
+        g_train = self.arch_gradient(input_train, target_train, input_train, target_train, eta, network_optimizer, unrolled=True)
+        self._apply([lambda_valid_regularizer * gv + lambda_train_regularizer * gt for gv, gt in zip(g_val, g_train)])
 
 
 # ============================================================================ evaluation network of a found architecture

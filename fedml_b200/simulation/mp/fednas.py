@@ -36,6 +36,7 @@ class FedNASTrainer(ClientTrainer):
         # arch_order 2 = the unrolled (second-order) architect step of the reference (architect.py), 1 = first order
         unrolled = int(getattr(args, "arch_order", 1) or 1) == 2 or bool(getattr(args, "unrolled", False))
         aux_w = float(getattr(args, "auxiliary_weight", 0.4))
+        lam_train, lam_valid = float(getattr(args, "lambda_train_regularizer", 1.0)), float(getattr(args, "lambda_valid_regularizer", 1.0))
         if not search and hasattr(m, "drop_path_prob"):     # train stage: drop-path probability ramps up over the rounds
             frac = float(getattr(args, "round_idx", 0) or 0) / max(1, int(getattr(args, "comm_round", 1)))
             m.drop_path_prob = float(getattr(args, "drop_path_prob", 0.2)) * frac
@@ -47,7 +48,11 @@ class FedNASTrainer(ClientTrainer):
             for i, (x, y) in enumerate(w_batches):
                 if search:   # alpha step on held-out data (first or second order), then weight step on training data
                     xa, ya = a_batches[i % len(a_batches)]
-                    architect.step(x.to(device), y.to(device), xa.to(device), ya.to(device), lr, w_opt, unrolled=unrolled)
+                    xd, yd, xad, yad = x.to(device), y.to(device), xa.to(device), ya.to(device)
+                    if unrolled:
+                        architect.step(xd, yd, xad, yad, lr, w_opt, unrolled=True)
+                    else:        # the reference's local search: mixed-level first-order rule (FedNASTrainer.py:129-136)
+                        architect.step_v2(xd, yd, xad, yad, lam_train, lam_valid)
                 w_opt.zero_grad(set_to_none=True)
                 out = m(x.to(device))
                 if isinstance(out, tuple):                   # derived network: (logits, auxiliary logits or None)

@@ -231,3 +231,43 @@ def test_darts_utilities(tmp_path):
     assert (tmp_path / "normal.dot").read_text() == dot and dot.count("->") == 8 + 4 and '"c_{k-2}" -> "0" [label="sep_conv_3x3"]' in dot
     # odd feature maps go through the factorised reduction (the reference's slicing only handles even sizes)
     assert D.FactorizedReduce(4, 8)(torch.randn(2, 4, 7, 7)).shape == (2, 8, 4, 4)
+
+
+def test_architect_mixed_level_rules():
+    """step_v2 = Adam on (grad_a L_val + lambda * grad_a L_train); lambda = 0 is the plain first-order rule, and the reference's
+    constructor form ``Architect(model, criterion, args, device)`` is accepted."""
+    import copy
+    from types import SimpleNamespace
+    from fedml_b200.models import darts as D
+    torch.manual_seed(0)
+    base = D.Network(4, 4, 3, steps=2, multiplier=2).double()
+    xt, yt = torch.randn(5, 3, 8, 8, dtype=torch.float64), torch.randint(0, 4, (5,))
+    xv, yv = torch.randn(5, 3, 8, 8, dtype=torch.float64), torch.randint(0, 4, (5,))
+    args = SimpleNamespace(arch_learning_rate=1e-2, arch_weight_decay=0.0, momentum=0.9, weight_decay=3e-4)
+
+    def run(fn):
+        net = copy.deepcopy(base)
+        arch = D.Architect(net, torch.nn.CrossEntropyLoss(), args, torch.device("cpu"))
+        fn(arch)
+        return torch.cat([p.detach().reshape(-1) for p in net.arch_parameters()]), net
+
+    a0 = torch.cat([p.detach().reshape(-1) for p in base.arch_parameters()])
+    mixed, net = run(lambda a: a.step_v2(xt, yt, xv, yv, 1.0, 1.0))
+    val_only, _ = run(lambda a: a.step_v2(xt, yt, xv, yv, 0.0, 1.0))
+    first, _ = run(lambda a: a.step(xt, yt, xv, yv, 0.05, None, unrolled=False))
+    aos, _ = run(lambda a: a.step_AOS(xt, yt, xv, yv))
+    single, _ = run(lambda a: a.step_single_level(xt, yt))
+    wa, _ = run(lambda a: a.step_wa(xt, yt, xv, yv, 1.0))
+    second, _ = run(lambda a: a.step_v2_2ndorder(xt, yt, xv, yv, 0.05, None, 1.0, 1.0))
+    assert torch.equal(val_only, first) and torch.equal(aos, first) and torch.equal(wa, mixed)
+    assert not torch.equal(mixed, first) and not torch.equal(single, first) and not torch.equal(second, mixed)
+    assert all(not torch.equal(v, a0) for v in (mixed, first, single, second))
+    # weights are untouched by architecture steps
+    assert all(torch.equal(p, q) for p, q in zip(net.weight_parameters(), base.weight_parameters()))
+    # the first Adam step moves every coordinate by lr against the sign of the combined gradient
+    crit = torch.nn.CrossEntropyLoss()
+    g = [gv + gt for gv, gt in zip(torch.autograd.grad(crit(base(xv), yv), base.arch_parameters()),
+                                   torch.autograd.grad(crit(base(xt), yt), base.arch_parameters()))]
+    g = torch.cat([t.reshape(-1) for t in g])
+    moved = g.abs() > 1e-9
+    torch.testing.assert_close((mixed - a0)[moved], (-1e-2 * torch.sign(g))[moved], rtol=1e-4, atol=1e-7)
