@@ -7,6 +7,7 @@ import os
 import sys
 import types
 
+import numpy as np
 import pytest
 import torch
 
@@ -271,3 +272,25 @@ def test_architect_mixed_level_rules():
     g = torch.cat([t.reshape(-1) for t in g])
     moved = g.abs() > 1e-9
     torch.testing.assert_close((mixed - a0)[moved], (-1e-2 * torch.sign(g))[moved], rtol=1e-4, atol=1e-7)
+
+
+@pytest.mark.parametrize("extra", [[], ["--optimization", "MiLeNAS"], ["--arch_search_method", "GDAS", "--optimization", "AOS"]])
+def test_centralised_darts_search_script(tmp_path, extra):
+    from fedml_b200.models import darts as D
+    from fedml_b200.models.darts_scripts import search_main
+    hist = search_main(["--epochs", "2", "--layers", "3", "--init_channels", "4", "--train_size", "96", "--batch_size", "16",
+                        "--data", str(tmp_path / "none"), "--save", str(tmp_path / "exp"), "--report_freq", "0"] + extra)
+    assert len(hist) == 2 and hist[1]["lr"] < hist[0]["lr"] and isinstance(hist[-1]["genotype"], D.Genotype)
+    assert len(hist[-1]["genotype"].normal) == 8 and hist[-1]["model_size_mb"] > 0 and (tmp_path / "exp" / "weights.pt").exists()
+    assert all(np.isfinite(h["train_loss"]) and np.isfinite(h["valid_loss"]) for h in hist)
+
+
+def test_centralised_darts_train_script(tmp_path):
+    from fedml_b200.models.darts_scripts import train_main
+    hist = train_main(["--epochs", "2", "--layers", "3", "--init_channels", "4", "--train_size", "64", "--batch_size", "16", "--arch", "FedNAS_V1",
+                       "--auxiliary", "--cutout", "--data", str(tmp_path / "none"), "--save", str(tmp_path / "exp"), "--report_freq", "0"])
+    assert [h["drop_path_prob"] for h in hist] == [0.0, 0.1] and all(np.isfinite(h["train_loss"]) for h in hist)
+    again = train_main(["--epochs", "1", "--layers", "3", "--init_channels", "4", "--train_size", "64", "--batch_size", "16", "--arch", "FedNAS_V1",
+                        "--auxiliary", "--model_path", str(tmp_path / "exp" / "weights.pt"), "--data", str(tmp_path / "none"),
+                        "--save", str(tmp_path / "exp2"), "--report_freq", "0"])
+    assert len(again) == 1
