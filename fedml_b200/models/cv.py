@@ -252,37 +252,103 @@ def resnet50(num_classes=1000, group_norm=0):
 
 
 # ------------------------------------------------------------------ FedGKT split pair
-class ResNet8Client(nn.Module):
-    """Small client-side extractor + head for FedGKT (resnet56_gkt/resnet_client.py): returns
-    ``(logits, feature_map)``; the feature map [B,16,32,32] is what gets uploaded."""
+class _GKTClient(ResNet):
+    """Edge side of FedGKT (reference resnet56_gkt/resnet_client.py:138-259): the CIFAR stem plus ``layer1`` only and a small
+    head; returns ``(logits, feature_map)`` where the feature map [B, 16, 32, 32] - the stem output - is what gets uploaded."""
 
-    def __init__(self, class_num=10):
-        super().__init__()
-        self.conv1 = nn.Conv2d(3, 16, 3, 1, 1, bias=False)
-        self.bn1 = nn.BatchNorm2d(16)
-        self.relu = nn.ReLU(inplace=True)
-        self.layer1 = nn.Sequential(BasicBlock(16, 16), BasicBlock(16, 16))
-        self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
-        self.fc = nn.Linear(16, class_num)
+    def __init__(self, block, blocks, class_num=10, **kw):
+        super().__init__(block, [blocks], num_classes=class_num, stem="cifar", **kw)
+        self.maxpool = nn.MaxPool2d(kernel_size=3, stride=2, padding=1)      # present in the reference module, unused
 
     def forward(self, x):
         feat = self.relu(self.bn1(self.conv1(x)))
-        h = self.layer1(feat)
-        return self.fc(self.avgpool(h).flatten(1)), feat
+        return self.fc(self.avgpool(self.layer1(feat)).flatten(1)), feat
 
 
-class ResNet56Server(nn.Module):
-    """Server-side trunk for FedGKT: consumes the client's [B,16,32,32] feature map."""
+class ResNet8Client(_GKTClient):
+    """``resnet8_56``: two bottleneck blocks (16 -> 64 channels)."""
 
-    def __init__(self, class_num=10, layers=(6, 6, 6)):
-        super().__init__()
-        body = ResNet(Bottleneck, list(layers), num_classes=class_num, stem="cifar")
-        self.layer1, self.layer2, self.layer3 = body.layer1, body.layer2, body.layer3
-        self.avgpool, self.fc = body.avgpool, body.fc
+    def __init__(self, class_num=10, **kw):
+        super().__init__(Bottleneck, 2, class_num, **kw)
+
+
+class ResNet5Client(_GKTClient):
+    """``resnet5_56``: one basic block."""
+
+    def __init__(self, class_num=10, **kw):
+        super().__init__(BasicBlock, 1, class_num, **kw)
+
+
+class ResNet56Server(ResNet):
+    """Server side of FedGKT (resnet56_gkt/resnet_server.py:139-252): the three bottleneck stages of ResNet-56 applied to the
+    client's [B, 16, 32, 32] feature map.  The stem (``conv1`` / ``bn1``) is part of the parameter tree, as in the reference,
+    but not of the forward pass."""
+
+    def __init__(self, class_num=10, layers=(6, 6, 6), **kw):
+        super().__init__(Bottleneck, list(layers), num_classes=class_num, stem="cifar", **kw)
+        self.maxpool = nn.MaxPool2d(kernel_size=3, stride=2, padding=1)
 
     def forward(self, feat):
         x = self.layer3(self.layer2(self.layer1(feat)))
         return self.fc(self.avgpool(x).flatten(1))
+
+
+def _with_checkpoint(model, pretrained, path):
+    return load_pretrained(model, path) if pretrained and path else model
+
+
+def resnet8_56(c, pretrained=False, path=None, **kw):
+    return _with_checkpoint(ResNet8Client(c, **kw), pretrained, path)
+
+
+def resnet5_56(c, pretrained=False, path=None, **kw):
+    return _with_checkpoint(ResNet5Client(c, **kw), pretrained, path)
+
+
+def resnet56_server(c, pretrained=False, path=None, **kw):
+    return _with_checkpoint(ResNet56Server(c, **kw), pretrained, path)
+
+
+class _GKTPretrained(ResNet):
+    """Full CIFAR ResNet that also returns the stem's feature map: ``(logits, feature_map)`` (resnet56_gkt/resnet_pretrained.py)."""
+
+    def __init__(self, block, layers, class_num=10, **kw):
+        super().__init__(block, layers, num_classes=class_num, stem="cifar", **kw)
+        self.maxpool = nn.MaxPool2d(kernel_size=3, stride=2, padding=1)
+
+    def forward(self, x):
+        feat = self.relu(self.bn1(self.conv1(x)))
+        h = self.layer3(self.layer2(self.layer1(feat)))
+        return self.fc(self.avgpool(h).flatten(1)), feat
+
+
+def resnet32_pretrained(c, pretrained=False, path=None, **kw):
+    """Basic blocks, [5, 5, 5] stages (resnet56_gkt/resnet_pretrained.py:261)."""
+    return _with_checkpoint(_GKTPretrained(BasicBlock, [5, 5, 5], c, **kw), pretrained, path)
+
+
+def resnet56_pretrained(c, pretrained=False, path=None, **kw):
+    return _with_checkpoint(_GKTPretrained(Bottleneck, [6, 6, 6], c, **kw), pretrained, path)
+
+
+def resnet101(num_classes=1000, group_norm=0, **kw):
+    return ResNet(Bottleneck, [3, 4, 23, 3], num_classes, "imagenet", group_norm, **kw)
+
+
+def resnet152(num_classes=1000, group_norm=0, **kw):
+    return ResNet(Bottleneck, [3, 8, 36, 3], num_classes, "imagenet", group_norm, **kw)
+
+
+class GroupNorm3d(nn.GroupNorm):
+    """GroupNorm over [N, C, D, H, W] with the constructor of the reference's class (group_normalization.py:165)."""
+
+    def __init__(self, num_features, num_groups=32, eps=1e-5, momentum=0.1, affine=True, track_running_stats=False):
+        super().__init__(num_groups, num_features, eps=eps, affine=affine)
+
+    def forward(self, x):
+        if x.dim() != 5:
+            raise ValueError(f"expected 5D input (got {x.dim()}D input)")
+        return super().forward(x)
 
 
 # ------------------------------------------------------------------ MobileNet / MobileNetV3 / EfficientNet / VGG

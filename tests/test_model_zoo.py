@@ -294,3 +294,33 @@ def test_centralised_darts_train_script(tmp_path):
                         "--auxiliary", "--model_path", str(tmp_path / "exp" / "weights.pt"), "--data", str(tmp_path / "none"),
                         "--save", str(tmp_path / "exp2"), "--report_freq", "0"])
     assert len(again) == 1
+
+
+@needs_ref
+def test_fedgkt_networks_match_reference():
+    from fedml_b200.models import cv as C
+
+    def load(rel, name):
+        spec = importlib.util.spec_from_file_location(name, REF + rel)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[name] = mod
+        spec.loader.exec_module(mod)
+        return mod
+
+    rc, rs, rp = (load(f"resnet56_gkt/resnet_{n}.py", f"ref_gkt_{n}") for n in ("client", "server", "pretrained"))
+    x, feat = torch.randn(2, 3, 32, 32), torch.randn(2, 16, 32, 32)
+    for ref, mine, inp in ((rc.resnet8_56(10), C.resnet8_56(10), x), (rc.resnet5_56(10), C.resnet5_56(10), x),
+                           (rs.resnet56_server(10), C.resnet56_server(10), feat), (rp.resnet32_pretrained(10), C.resnet32_pretrained(10), x),
+                           (rp.resnet56_pretrained(7), C.resnet56_pretrained(7), x)):
+        assert [(k, tuple(v.shape)) for k, v in ref.state_dict().items()] == [(k, tuple(v.shape)) for k, v in mine.state_dict().items()]
+        mine.load_state_dict(ref.state_dict())
+        ref.eval()
+        mine.eval()
+        with torch.no_grad():
+            ya, yb = ref(inp), mine(inp)
+        for p, q in zip(ya if isinstance(ya, tuple) else (ya,), yb if isinstance(yb, tuple) else (yb,)):
+            torch.testing.assert_close(q, p, rtol=1e-5, atol=1e-6)
+    logits, fmap = C.ResNet8Client(10)(x)
+    assert logits.shape == (2, 10) and fmap.shape == (2, 16, 32, 32)
+    assert C.GroupNorm3d(8, 4)(torch.randn(2, 8, 3, 4, 4)).shape == (2, 8, 3, 4, 4)
+    assert sum(p.numel() for p in C.resnet101(10).parameters()) > sum(p.numel() for p in C.resnet50(10).parameters())
