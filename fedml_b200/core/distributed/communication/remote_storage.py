@@ -50,6 +50,13 @@ class LocalObjectStore:
         shutil.copyfile(self._path(key), dst_path)
         return dst_path
 
+    def delete(self, key) -> bool:
+        try:
+            os.remove(self._path(key))
+            return True
+        except FileNotFoundError:
+            return False
+
 
 class S3Storage(LocalObjectStore):
     """Real S3 when boto3 and credentials exist; same interface."""
@@ -78,6 +85,20 @@ class S3Storage(LocalObjectStore):
                 if attempt == retries - 1:
                     raise
                 time.sleep(1)
+
+
+    def upload_file(self, src_path, key) -> str:
+        self.s3.upload_file(src_path, self.bucket, key)
+        return self.s3.generate_presigned_url("get_object", ExpiresIn=60 * 60 * 24 * 5, Params={"Bucket": self.bucket, "Key": key})
+
+    def download_file(self, key, dst_path):
+        os.makedirs(os.path.dirname(os.path.abspath(dst_path)) or ".", exist_ok=True)
+        self.s3.download_file(self.bucket, key, dst_path)
+        return dst_path
+
+    def delete(self, key) -> bool:
+        self.s3.delete_object(Bucket=self.bucket, Key=key)
+        return True
 
 
 def create_store(args):

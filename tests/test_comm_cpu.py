@@ -772,3 +772,91 @@ def test_callback_and_mailbox_observers():
     with pytest.raises(TimeoutError):
         box.get(9, timeout=0.05)
     assert box.received == 3
+def test_generated_code_surface_of_the_grpc_service():
+    """A servicer subclass + stub calls written against grpc_comm_manager_pb2_grpc run on the hand-written classes, and talk to
+    the framework's own gRPC manager (reference wire format)."""
+    from concurrent import futures
+    import grpc
+    import socket
+    from fedml.core.distributed.communication.grpc import grpc_comm_manager_pb2 as pb2, grpc_comm_manager_pb2_grpc as pb2_grpc
+
+    got = []
+
+    class Servicer(pb2_grpc.gRPCCommManagerServicer):
+        def sendMessage(self, request, context):  # noqa: N802
+            got.append((request.client_id, request.message))
+            return pb2.CommResponse(client_id=7, message=b"ack:" + request.message)
+
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=2))
+    pb2_grpc.add_gRPCCommManagerServicer_to_server(Servicer(), server)
+    server.add_insecure_port(f"127.0.0.1:{port}")
+    server.start()
+    try:
+        with grpc.insecure_channel(f"127.0.0.1:{port}") as ch:
+            stub = pb2_grpc.gRPCCommManagerStub(ch)
+            r = stub.sendMessage(pb2.CommRequest(client_id=3, message=b"hello"), timeout=10)
+            assert (r.client_id, r.message) == (7, b"ack:hello") and got == [(3, b"hello")]
+            try:
+                stub.handleReceiveMessage(pb2.CommRequest(client_id=3, message=b"x"), timeout=10)
+                raise AssertionError("expected UNIMPLEMENTED")
+            except grpc.RpcError as e:
+                assert e.code() == grpc.StatusCode.UNIMPLEMENTED
+        r = pb2_grpc.gRPCCommManager.sendMessage(pb2.CommRequest(client_id=4, message=b"once"), f"127.0.0.1:{port}", insecure=True, timeout=10)
+        assert r.message == b"ack:once" and got[-1] == (4, b"once")
+    finally:
+        server.stop(0)
+    assert "gRPCCommManager" in pb2.DESCRIPTOR.services_by_name
+
+
+def test_edge_deployment_helpers(tmp_path, monkeypatch, broker):
+    """MqttManager topic dispatch over the bundled broker, yaml / object-store / login bookkeeping helpers."""
+    from fedml.cli.edge_deployment.mqtt_manager import MqttManager
+    from fedml.cli.edge_deployment.yaml_utils import load_yaml_config
+    from fedml_b200.cli import edge_deployment as E
+    from fedml_b200.core.distributed.communication.broker import BrokerClient
+    host, port = "127.0.0.1", broker
+    mgr = MqttManager(host, port, None, None, 30, 42)
+    got = []
+    ev = threading.Event()
+    mgr.add_message_listener("flserver_agent/42/start_train", lambda t, p: (got.append((t, json.loads(p))), ev.set()))
+    mgr.add_message_listener("custom/topic", lambda t, p: (got.append((t, p)), ev.set()))
+    pub = BrokerClient(host, port, client_id="server-agent")
+    pub.publish("flserver_agent/42/start_train", json.dumps({"runId": 9}))
+    assert ev.wait(5) and got[0] == ("flserver_agent/42/start_train", {"runId": 9})
+    ev.clear()
+    pub.publish("flserver_agent/43/start_train", "{}")           # another edge's topic: not delivered
+    pub.publish("custom/topic", "hi")
+    assert ev.wait(5) and got[1] == ("custom/topic", "hi") and len(got) == 2
+    back = []
+    ev2 = threading.Event()
+    pub.on_message = lambda t, p: (back.append((t, p)), ev2.set())
+    pub.subscribe("fl_client/mlops/status")
+    mgr.send_message_json("fl_client/mlops/status", json.dumps({"edge_id": 42, "status": MqttManager.MSG_MLOPS_CLIENT_STATUS_IDLE}))
+    assert ev2.wait(5) and json.loads(back[0][1])["status"] == "IDLE"
+    mgr.remove_message_listener("custom/topic")
+    mgr.disconnect()
+    pub.disconnect()
+    # yaml
+    (tmp_path / "ok.yaml").write_text("a: {b: 1}\n")
+    (tmp_path / "bad.yaml").write_text("a: [1, 2\n")
+    assert load_yaml_config(str(tmp_path / "ok.yaml")) == {"a": {"b": 1}}
+    with pytest.raises(ValueError, match="Yaml error"):
+        load_yaml_config(str(tmp_path / "bad.yaml"))
+    # object store round trip (directory store)
+    monkeypatch.setenv("FEDML_OBJECT_STORE_DIR", str(tmp_path / "store"))
+    (tmp_path / "pkg.zip").write_bytes(b"PK\x03\x04 payload")
+    assert E.upload_file(str(tmp_path / "pkg.zip"), "run9/pkg.zip") is True
+    E.download_file("run9/pkg.zip", str(tmp_path / "dl" / "pkg.zip"))
+    assert (tmp_path / "dl" / "pkg.zip").read_bytes() == b"PK\x03\x04 payload"
+    E.delete_s3_zip("run9/pkg.zip")
+    assert E.upload_file(str(tmp_path / "missing.zip"), "x") is False
+    with pytest.raises(FileNotFoundError):
+        E.download_file("run9/pkg.zip", str(tmp_path / "dl" / "again.zip"))
+    # login bookkeeping
+    info = E.save_edge_infos("dev-1", 17, home=str(tmp_path / "home"))
+    assert load_yaml_config(info) == {"unique_device_id": "dev-1", "edge_id": 17}
+    assert E.logout(home=str(tmp_path / "home")) is True and E.logout(home=str(tmp_path / "home")) is False
+    monkeypatch.setenv("HOME", str(tmp_path / "h2"))
+    cmd = E.login_with_docker_mode(1234, "dev", run=False)
+    assert cmd[:3] == ["docker", "run", "--rm"] and "ACCOUNT_ID=1234" in cmd and cmd[-1].endswith(":dev")

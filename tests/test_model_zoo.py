@@ -324,3 +324,44 @@ def test_fedgkt_networks_match_reference():
     assert logits.shape == (2, 10) and fmap.shape == (2, 16, 32, 32)
     assert C.GroupNorm3d(8, 4)(torch.randn(2, 8, 3, 4, 4)).shape == (2, 8, 3, 4, 4)
     assert sum(p.numel() for p in C.resnet101(10).parameters()) > sum(p.numel() for p in C.resnet50(10).parameters())
+
+
+def test_efficientnet_utils_surface(tmp_path):
+    from fedml_b200.models import efficientnet_utils as U
+    strings = ["r1_k3_s11_e1_i32_o16_se0.25", "r2_k5_s22_e6_i24_o40_se0.25", "r1_k3_s11_e6_i192_o320_noskip"]
+    blocks = U.BlockDecoder.decode(strings)
+    assert blocks[1] == U.BlockArgs(2, 5, [2], 6, 24, 40, 0.25, True) and blocks[2].id_skip is False and blocks[2].se_ratio is None
+    assert U.BlockDecoder.encode(blocks) == strings
+    b, gp = U.get_model_params("efficientnet-b2", {"num_classes": 7})
+    assert gp.width_coefficient == 1.1 and gp.image_size == 260 and gp.num_classes == 7 and len(b) == 7 and U.round_filters(32, gp) == 32
+    if os.path.isdir(REF):
+        r = _ref("efficientnet_utils")
+        rb, rgp = r.get_model_params("efficientnet-b2", {"num_classes": 7})
+        assert [tuple(x) for x in rb] == [tuple(x) for x in b] and tuple(rgp) == tuple(gp)
+        assert r.BlockDecoder.decode(strings) == blocks
+        x = torch.randn(2, 3, 33, 47)
+        for k, s in ((3, 2), (5, 1), (3, 1), (1, 2)):
+            a, m = r.Conv2dDynamicSamePadding(3, 4, k, s), U.Conv2dDynamicSamePadding(3, 4, k, s)
+            m.load_state_dict(a.state_dict())
+            torch.testing.assert_close(m(x), a(x))
+            pa, pm = r.MaxPool2dDynamicSamePadding(k, s), U.MaxPool2dDynamicSamePadding(k, s)
+            torch.testing.assert_close(pm(x), pa(x))
+            sa, sm = r.MaxPool2dStaticSamePadding(k, s, image_size=(33, 47)), U.MaxPool2dStaticSamePadding(k, s, image_size=(33, 47))
+            torch.testing.assert_close(sm(x), sa(x))
+        assert r.get_same_padding_conv2d(None).__name__ == U.get_same_padding_conv2d(None).__name__
+    conv = U.get_same_padding_conv2d(64)(3, 8, 3, stride=2)
+    assert isinstance(conv, Z.Conv2dStaticSamePadding) and conv(torch.randn(1, 3, 64, 64)).shape == (1, 8, 32, 32)
+    assert U.Conv2dDynamicSamePadding(3, 8, 3, stride=2)(torch.randn(1, 3, 65, 31)).shape == (1, 8, 33, 16)
+    assert U.get_same_padding_maxPool2d(None)(3, 2)(torch.randn(1, 3, 9, 9)).shape == (1, 3, 5, 5)
+    x = torch.randn(5, 3, dtype=torch.float64, requires_grad=True)
+    assert torch.autograd.gradcheck(U.SwishImplementation.apply, (x,))
+    torch.testing.assert_close(U.SwishImplementation.apply(x), x * torch.sigmoid(x))
+    net = Z.EfficientNet.from_name("efficientnet-b0", num_classes=5)
+    torch.save(net.state_dict(), tmp_path / "b0.pth")
+    other = Z.EfficientNet.from_name("efficientnet-b0", num_classes=9)
+    U.load_pretrained_weights(other, "efficientnet-b0", str(tmp_path / "b0.pth"), load_fc=False, verbose=False)
+    assert torch.equal(other._conv_stem.weight, net._conv_stem.weight) and other._fc.weight.shape == (9, 1280)
+    with pytest.raises(FileNotFoundError, match="efficientnet-b0-355c32eb"):
+        U.load_pretrained_weights(other, "efficientnet-b0")
+    with pytest.raises(NotImplementedError):
+        U.get_model_params("resnet50")
