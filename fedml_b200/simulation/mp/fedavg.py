@@ -313,26 +313,59 @@ class FedAVGClientManager(ClientManager):
         self.send_message(m)
 
 
+def FedML_init():  # noqa: N802
+    """``(comm, process_id, worker_number)`` of this process (reference FedAvgAPI.py:12-16).  Under ``mpirun`` with mpi4py:
+    ``MPI.COMM_WORLD`` and its rank / size.  Otherwise the job was started by ``torchrun`` (or any launcher that exports ``RANK`` /
+    ``WORLD_SIZE``): ``comm`` is None and the managers connect the same star over TCP (``args.host_table``, ``args.tcp_base_port``)."""
+    import os
+    from ...core.distributed.communication.mpi_backend import mpi_available
+    if mpi_available():
+        from mpi4py import MPI
+        comm = MPI.COMM_WORLD
+        if comm.Get_size() > 1 or "RANK" not in os.environ:
+            return comm, comm.Get_rank(), comm.Get_size()
+    rank = int(os.environ.get("RANK", os.environ.get("OMPI_COMM_WORLD_RANK", os.environ.get("PMI_RANK", 0))))
+    size = int(os.environ.get("WORLD_SIZE", os.environ.get("OMPI_COMM_WORLD_SIZE", os.environ.get("PMI_SIZE", 1))))
+    return None, rank, size
+
+
+def init_server(args, device, comm, rank, size, model, train_data_num, train_data_global, test_data_global, train_data_local_dict,
+                test_data_local_dict, train_data_local_num_dict, model_trainer=None, preprocessed_sampling_lists=None, backend=None,
+                server_aggregator=None):
+    """Builds the aggregator + server manager of rank 0, sends the first global model and serves until the last round."""
+    trainer = model_trainer or create_model_trainer(model, args)
+    trainer.set_id(-1)
+    agg = FedAVGAggregator(train_data_global, test_data_global, train_data_num, train_data_local_dict, test_data_local_dict,
+                           train_data_local_num_dict, size - 1, device, args, trainer, server_aggregator)
+    mgr = FedAVGServerManager(args, agg, comm, rank, size, backend or getattr(args, "mp_transport", "INPROC"),
+                              is_preprocessed=preprocessed_sampling_lists is not None,
+                              preprocessed_client_lists=preprocessed_sampling_lists)
+    mgr.send_init_msg()
+    mgr.run()
+    return agg
+
+
+def init_client(args, device, comm, process_id, size, model, train_data_num, train_data_local_num_dict, train_data_local_dict,
+                test_data_local_dict, model_trainer=None, backend=None):
+    """Builds the local trainer + client manager of a worker rank and serves until the server says finish."""
+    client_index = process_id - 1
+    trainer = model_trainer or create_model_trainer(model, args)
+    trainer.set_id(client_index)
+    tr = FedAVGTrainer(client_index, train_data_local_dict, train_data_local_num_dict, test_data_local_dict, train_data_num, device, args,
+                       trainer)
+    FedAVGClientManager(args, tr, comm, process_id, size, backend or getattr(args, "mp_transport", "INPROC")).run()
+    return tr
+
+
 def FedML_FedAvg_distributed(args, process_id, worker_number, comm, device, dataset, model, model_trainer=None,  # noqa: N802
                              preprocessed_sampling_lists=None, backend=None, server_aggregator=None):
     """Reference entry point (FedAvgAPI.py:19): builds the server (rank 0) or a client (rank > 0) and runs it."""
     (train_num, test_num, train_global, test_global, local_num, train_local, test_local, class_num) = list(dataset)[:8]
-    backend = backend or getattr(args, "mp_transport", "INPROC")
-    trainer = model_trainer or create_model_trainer(model, args)
     if process_id == 0:
-        agg = FedAVGAggregator(train_global, test_global, train_num, train_local, test_local, local_num, worker_number - 1,
-                               device, args, trainer, server_aggregator)
-        mgr = FedAVGServerManager(args, agg, comm, process_id, worker_number, backend,
-                                  is_preprocessed=preprocessed_sampling_lists is not None,
-                                  preprocessed_client_lists=preprocessed_sampling_lists)
-        mgr.send_init_msg()
-        mgr.run()
-        return agg
-    trainer.set_id(process_id - 1)
-    tr = FedAVGTrainer(process_id - 1, train_local, local_num, test_local, train_num, device, args, trainer)
-    mgr = FedAVGClientManager(args, tr, comm, process_id, worker_number, backend)
-    mgr.run()
-    return tr
+        return init_server(args, device, comm, process_id, worker_number, model, train_num, train_global, test_global, train_local,
+                           test_local, local_num, model_trainer, preprocessed_sampling_lists, backend, server_aggregator)
+    return init_client(args, device, comm, process_id, worker_number, model, train_num, local_num, train_local, test_local, model_trainer,
+                       backend)
 
 
 FedML_FedOpt_distributed = FedML_FedAvg_distributed          # noqa: N816  server optimizer chosen by args

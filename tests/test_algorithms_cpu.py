@@ -439,3 +439,46 @@ def test_fednas_train_stage_and_derived_network():
     ds, model = build(a)
     r = SimulatorMPI(a, CPU, ds, model).run()
     assert len(r.history) == 2 and np.isfinite(r.history[-1]["test_loss"]) and isinstance(r.trainer.model, NetworkCIFAR)
+
+
+def test_reference_style_mpi_launch_script(tmp_path):
+    """The reference's launch idiom - ``comm, process_id, worker_number = FedML_init()`` then ``FedML_FedAvg_distributed(...)`` -
+    run as three processes started by a launcher that exports RANK / WORLD_SIZE (no mpirun here: the star goes over TCP)."""
+    import json
+    import random
+    import subprocess
+    import sys
+    script = tmp_path / "main_fedavg.py"
+    script.write_text('''
+import sys, json, torch
+import fedml
+from fedml.arguments import Arguments
+from fedml.simulation.mpi_p2p_mp.fedavg.FedAvgAPI import FedML_init, FedML_FedAvg_distributed
+
+comm, process_id, worker_number = FedML_init()
+args = Arguments.from_dict(dict(dataset="mnist", model="lr", federated_optimizer="FedAvg", client_num_in_total=8, client_num_per_round=2,
+                                comm_round=2, epochs=1, batch_size=16, learning_rate=0.05, frequency_of_the_test=1, synthetic_train_size=400,
+                                mnist_client_num=8, backend="MPI", mp_transport="TCP", tcp_base_port=int(sys.argv[1]), random_seed=0,
+                                log_level="WARNING", run_id="ref-launch", using_gpu=False))
+dataset, class_num = fedml.data.load(args)
+model = fedml.model.create(args, class_num)
+out = FedML_FedAvg_distributed(args, process_id, worker_number, comm, torch.device("cpu"), dataset, model)
+if process_id == 0:
+    w = out.get_global_model_params()
+    print("RESULT", json.dumps({"rounds": len(out.history) if hasattr(out, "history") else -1, "norm": float(sum(v.float().norm() for v in w.values()))}))
+''')
+    port = random.randint(20000, 45000)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), WORLD_SIZE="3")
+    procs = [subprocess.Popen([sys.executable, str(script), str(port)], env=dict(env, RANK=str(r)), stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(3)]
+    outs = []
+    for p in procs:
+        try:
+            outs.append(p.communicate(timeout=240)[0])
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+    assert all(p.returncode == 0 for p in procs), "\n----\n".join(o[-1500:] for o in outs)
+    line = [ln for ln in outs[0].splitlines() if ln.startswith("RESULT")]
+    assert line and json.loads(line[0][7:])["norm"] > 0
