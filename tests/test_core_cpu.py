@@ -1,5 +1,6 @@
 """CPU tests: config, data contract, model zoo, partitioners, topology, scheduler, aggregation oracles, codec."""
 import copy
+import json
 import os
 
 import numpy as np
@@ -413,3 +414,53 @@ def test_model_factory_names_of_the_nas_and_gkt_algorithms():
     logits, feat = client(torch.randn(2, 3, 32, 32))
     assert logits.shape == (2, 10) and server(feat).shape == (2, 10)
     assert type(mk("no_such_model")).__name__ == "LogisticRegression"          # the reference's fallback (model_hub.py, last branch)
+
+
+def test_algorithm_helper_functions(tmp_path):
+    """Per-algorithm utils of the reference, through its import paths."""
+    from functools import partial
+    from fedml.simulation.mpi_p2p_mp.fedgkt.utils import (RunningAverage, bnwd_optim_params, get_flat_params_from, get_state_dict,
+                                                            save_dict_to_json, set_flat_params_to)
+    from fedml.simulation.mpi_p2p_mp.fedseg.utils import (EvaluationMetricsKeeper, count_parameters, load_from_pickle_file,
+                                                            save_as_pickle_file, str_to_bool)
+    from fedml.simulation.single_process.fednova.comm_helpers import communicate, flatten_tensors, unflatten_tensors
+    from fedml.simulation.single_process.classical_vertical_fl.party_models import sigmoid
+    from fedml.simulation.single_process.classical_vertical_fl.vfl_fixture import compute_correct_prediction
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 4, 3), torch.nn.BatchNorm2d(4), torch.nn.Flatten(), torch.nn.Linear(4, 2))
+    flat = get_flat_params_from(net)
+    assert flat.numel() == count_parameters(net) == 3 * 4 * 9 + 4 + 4 + 4 + 4 * 2 + 2
+    set_flat_params_to(net, torch.arange(flat.numel(), dtype=torch.float32))
+    assert float(net[0].weight.flatten()[5]) == 5.0 and float(net[3].bias[-1]) == flat.numel() - 1
+    with pytest.raises(ValueError):
+        set_flat_params_to(net, torch.zeros(3))
+    params = list(net.parameters())
+    groups = bnwd_optim_params(net, params, params)
+    assert groups[0]["weight_decay"] == 0 and len(groups[0]["params"]) == 2 and len(groups[1]["params"]) == 4
+    torch.optim.SGD(groups, lr=0.1, weight_decay=1e-3)
+    avg = RunningAverage()
+    avg.update(2)
+    avg.update(4)
+    assert avg.value() == 3 and avg() == 3
+    torch.save({"state_dict": net.state_dict()}, tmp_path / "ck.pth")
+    assert "state_dict" in get_state_dict(str(tmp_path / "ck.pth"))
+    save_dict_to_json({"acc": np.float32(0.5), "n": 3}, str(tmp_path / "m.json"))
+    assert json.load(open(tmp_path / "m.json")) == {"acc": 0.5, "n": 3}
+    save_as_pickle_file(str(tmp_path / "x.pkl"), {"a": [1, 2]})
+    assert load_from_pickle_file(str(tmp_path / "x.pkl")) == {"a": [1, 2]}
+    assert str_to_bool("True") is True and str_to_bool("false") is False
+    with pytest.raises(ValueError):
+        str_to_bool("maybe")
+    k = EvaluationMetricsKeeper(0.9, 0.8, 0.7, 0.6, 0.1)
+    assert (k.acc, k.acc_class, k.mIoU, k.FWIoU, k.loss) == (0.9, 0.8, 0.7, 0.6, 0.1)
+    a, b = torch.ones(2, 3), torch.full((4,), 2.0)
+    f = flatten_tensors([a, b])
+    assert f.tolist() == [1.0] * 6 + [2.0] * 4 and [t.shape for t in unflatten_tensors(f, [a, b])] == [a.shape, b.shape]
+
+    def double(tensor):
+        tensor.mul_(2)
+
+    communicate([a, b], partial(double))
+    assert float(a.sum()) == 12.0 and float(b.sum()) == 16.0
+    assert abs(float(sigmoid(0.0)) - 0.5) < 1e-12
+    y_hat, stats = compute_correct_prediction(y_targets=[1, 0, 1, 1], y_prob_preds=[0.9, 0.2, 0.4, 0.7])
+    assert y_hat.tolist() == [1, 0, 0, 1] and stats == [2, 2, 3]
