@@ -188,3 +188,56 @@ def test_per_module_loader_functions_through_the_reference_import_paths(monkeypa
     assert xb.shape == (4, 80) and yb.shape == (4, 80) and xb.dtype == torch.int64
     batches = batch_data({"x": [[0.0] * 784] * 5, "y": [1, 2, 3, 4, 5]}, 2)
     assert [b[0].shape[0] for b in batches] == [2, 2, 1] and batches[0][0].dtype == torch.float32 and batches[0][1].dtype == torch.int64
+
+
+def test_lazy_folder_datasets_imagenet_landmarks(tmp_path):
+    """File-backed data sets of the large image sets (reference data/ImageNet/datasets.py, data/Landmarks/datasets.py)."""
+    import torch
+    from PIL import Image
+    from fedml.data.ImageNet.datasets import ImageNet, ImageNet_truncated, find_classes, has_file_allowed_extension, make_dataset
+    from fedml.data.Landmarks.datasets import Landmarks
+    from fedml_b200.data import folder_datasets as FD
+    rs = np.random.RandomState(0)
+    counts = {"n01": 3, "n02": 2, "n03": 4}
+    for split, mult in (("train", 1), ("val", 1)):
+        for wnid, n in counts.items():
+            d = tmp_path / "imagenet" / split / wnid
+            d.mkdir(parents=True)
+            for i in range(n * mult):
+                Image.fromarray(rs.randint(0, 255, (40 + i, 50, 3), dtype=np.uint8)).save(d / f"img_{i}.JPEG")
+            (d / "notes.txt").write_text("not an image")
+    root = str(tmp_path / "imagenet")
+    classes, class_to_idx = find_classes(os.path.join(root, "train"))
+    assert classes == ["n01", "n02", "n03"] and has_file_allowed_extension("a.JPEG", FD.IMG_EXTENSIONS) and not has_file_allowed_extension("a.txt", FD.IMG_EXTENSIONS)
+    images, num, ranges = make_dataset(os.path.join(root, "train"), class_to_idx, FD.IMG_EXTENSIONS)
+    assert len(images) == 9 and num == {0: 3, 1: 2, 2: 4} and ranges == {0: (0, 3), 1: (3, 5), 2: (5, 9)}
+    full = ImageNet(root, train=True)
+    assert len(full) == 9 and full.get_data_local_num_dict() == num and full.get_net_dataidx_map() == ranges
+    assert len(ImageNet(root, dataidxs=2)) == 4 and len(ImageNet(root, dataidxs=[0, 1])) == 5
+    view = ImageNet_truncated(full, [1, 2], full.get_net_dataidx_map(), transform=FD.image_transforms(32)[0])
+    x, y = view[0]
+    assert len(view) == 6 and x.shape == (3, 32, 32) and x.dtype == torch.float32 and y == 1
+    tr, te = FD.get_dataloader_ImageNet(root, 4, 4, dataidxs=[0, 2], image_size=32)
+    xb, yb = next(iter(tr))
+    assert xb.shape == (4, 3, 32, 32) and set(yb.tolist()) <= {0, 2} and len(te.dataset) == 9
+    ev = FD.image_transforms(32)[1](Image.fromarray(np.full((80, 120, 3), 128, dtype=np.uint8)))
+    assert ev.shape == (3, 32, 32) and float(ev.std(dim=(1, 2)).max()) < 1e-5                      # resize + centre crop of a flat image stays flat
+    # Landmarks: mapping csv -> per-user ranges -> lazy data set
+    (tmp_path / "lm" / "images").mkdir(parents=True)
+    rows = [("7", "a", 0), ("7", "b", 1), ("3", "c", 1), ("7", "d", 2), ("3", "e", 0)]
+    for _, image_id, _ in rows:
+        Image.fromarray(rs.randint(0, 255, (30, 30, 3), dtype=np.uint8)).save(tmp_path / "lm" / "images" / f"{image_id}.jpg")
+    (tmp_path / "lm" / "train.csv").write_text("user_id,image_id,class\n" + "".join(f"{u},{i},{c}\n" for u, i, c in rows))
+    files, per_user, ranges = FD.get_mapping_per_user(str(tmp_path / "lm" / "train.csv"))
+    assert [r["image_id"] for r in files] == ["a", "b", "d", "c", "e"] and per_user == {7: 3, 3: 2} and ranges == {7: (0, 3), 3: (3, 5)}
+    ds = Landmarks(str(tmp_path / "lm" / "images"), files, dataidxs=ranges[3])
+    img, label = ds[0]
+    assert len(ds) == 2 and label == 1 and img.shape == (3, 30, 30)
+    tr, te = FD.get_dataloader_Landmarks(str(tmp_path / "lm" / "images"), files, files, 2, 2, dataidxs=ranges[7], image_size=16)
+    assert len(tr.dataset) == 3 and len(te.dataset) == 5 and next(iter(tr))[0].shape == (2, 3, 16, 16)
+    (tmp_path / "lm" / "bad.csv").write_text("user,image\n1,2\n")
+    with pytest.raises(ValueError, match="user_id, image_id and class"):
+        FD.get_mapping_per_user(str(tmp_path / "lm" / "bad.csv"))
+    # generic folder view with explicit indices
+    sub = FD.ImageFolderTruncated(os.path.join(root, "train"), dataidxs=[0, 3, 8])
+    assert len(sub) == 3 and sub.get_train_labels.tolist() == [0, 1, 2]
