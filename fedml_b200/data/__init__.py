@@ -118,6 +118,13 @@ def load_federated(args) -> FederatedDataset:
         from . import readers as R
         ds = R.load_tff_h5(os.path.join(cache, "fed_cifar100_train.h5"), os.path.join(cache, "fed_cifar100_test.h5"),
                            "image", "label", 100, "fed_cifar100", S.ImageNormalize(S.CIFAR100_MEAN, S.CIFAR100_STD), to_uint8=True)
+        if bool(getattr(args, "fed_cifar100_tff_preprocess", False)):
+            # the reference's recipe (fed_cifar100/utils.py): one 24x24 crop (+ flip) per training image fixed at load time, centre
+            # crop for the test images, every image standardised by its own statistics -> float NCHW, no batch-time transform
+            from .dataset_utils import preprocess_cifar_img
+            g = torch.Generator().manual_seed(seed)
+            ds.x, ds.x_test = preprocess_cifar_img(ds.x, True, g), preprocess_cifar_img(ds.x_test, False)
+            ds.transform = None
     elif name == "fed_cifar100":
         ds = S.make_cifar_like(int(getattr(args, "fed_cifar100_client_num", 500)), "hetero", 0.1, 100,
                                small or 50000, 10000 if not small else max(100, small // 5), 24, seed,

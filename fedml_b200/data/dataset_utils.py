@@ -358,3 +358,37 @@ get_dataloader_any_cifar10, get_dataloader_any_cifar100, get_dataloader_any_cini
     _fixed(n, get_dataloader) for n in ("cifar10", "cifar100", "cinic10"))
 get_dataloader_test_any_cifar10, get_dataloader_test_any_cifar100, get_dataloader_test_any_cinic10 = (
     _fixed(n, get_dataloader_test) for n in ("cifar10", "cifar100", "cinic10"))
+
+
+# ------------------------------------------------------------------------------------------------ fed_cifar100 (TFF recipe)
+def cifar100_transform(img_mean, img_std, train=True, crop_size=(24, 24), generator: Optional[torch.Generator] = None):
+    """Callable on one float CHW image in [0, 1]: random crop + horizontal flip (train) or centre crop (test) to ``crop_size``,
+    then ``(x - img_mean) / img_std`` (reference data/fed_cifar100/utils.py:9-30; the TFF recipe standardises every image with
+    its own statistics)."""
+    ch, cw = crop_size
+
+    def apply(x: torch.Tensor) -> torch.Tensor:
+        h, w = x.shape[-2:]
+        if train:
+            top = int(torch.randint(h - ch + 1, (1,), generator=generator))
+            left = int(torch.randint(w - cw + 1, (1,), generator=generator))
+            x = x[..., top:top + ch, left:left + cw]
+            if float(torch.rand(1, generator=generator)) < 0.5:
+                x = x.flip(-1)
+        else:
+            top, left = int(round((h - ch) / 2.0)), int(round((w - cw) / 2.0))
+            x = x[..., top:top + ch, left:left + cw]
+        return (x - float(img_mean)) / float(img_std)
+
+    return apply
+
+
+def preprocess_cifar_img(img: torch.Tensor, train: bool, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """``[n, 32, 32, 3]`` pixel values 0..255 -> ``[n, 3, 24, 24]`` float: scaled to [0, 1], cropped / flipped, each image
+    standardised by the mean and (unbiased) standard deviation of its own 32x32x3 values."""
+    x = torch.as_tensor(img).double() / 255.0
+    out = []
+    for i in x:
+        t = cifar100_transform(i.mean(), i.std(), train, generator=generator)
+        out.append(t(i.permute(2, 0, 1)))
+    return torch.stack(out).float() if out else torch.zeros((0, 3, 24, 24))

@@ -205,3 +205,15 @@ def test_reference_named_text_helpers(tmp_path):
     from fedml.data.synthetic_1_1.stats import print_dataset_stats
     stats = print_dataset_stats("syn", str(tmp_path))
     assert stats["users"] == 30 and stats["samples"] == sum(blob["num_samples"])
+
+
+def test_fed_cifar100_h5_with_the_tff_preprocessing_switch(tmp_path):
+    import fedml_b200
+    src = S.make_cifar_like(4, "homo", 0.5, 100, 40, 12, 32, 0, "fed_cifar100", S.CIFAR100_MEAN, S.CIFAR100_STD)
+    tff_export.export("fed_cifar100", src, str(tmp_path))
+    fed = fedml_b200.data.load_federated(_args(dataset="fed_cifar100", data_cache_dir=str(tmp_path), fed_cifar100_tff_preprocess=True))
+    assert fed.x.dtype == torch.float32 and tuple(fed.x.shape) == (40, 3, 24, 24) and tuple(fed.x_test.shape[1:]) == (3, 24, 24)
+    assert fed.transform is None and abs(float(fed.x_test[0].mean())) < 0.5
+    ds, k = fedml_b200.data.load(_args(dataset="fed_cifar100", data_cache_dir=str(tmp_path), fed_cifar100_tff_preprocess=True))
+    xb, yb = next(iter(ds[5][0]))
+    assert xb.shape[1:] == (3, 24, 24) and k == 100

@@ -241,3 +241,24 @@ def test_lazy_folder_datasets_imagenet_landmarks(tmp_path):
     # generic folder view with explicit indices
     sub = FD.ImageFolderTruncated(os.path.join(root, "train"), dataidxs=[0, 3, 8])
     assert len(sub) == 3 and sub.get_train_labels.tolist() == [0, 1, 2]
+
+
+def test_fed_cifar100_tff_preprocessing():
+    import torch
+    from fedml.data.fed_cifar100.utils import cifar100_transform, preprocess_cifar_img
+    rs = np.random.RandomState(1)
+    img = torch.from_numpy(rs.randint(0, 256, (5, 32, 32, 3)).astype(np.uint8))
+    test = preprocess_cifar_img(img, train=False)
+    assert test.shape == (5, 3, 24, 24) and test.dtype == torch.float32
+    x0 = img[0].double() / 255
+    want = ((x0 - x0.mean()) / x0.std()).permute(2, 0, 1)[:, 4:28, 4:28].float()
+    torch.testing.assert_close(test[0], want)
+    g = torch.Generator().manual_seed(0)
+    train = preprocess_cifar_img(img, train=True, generator=g)
+    assert train.shape == (5, 3, 24, 24) and not torch.equal(train, test)
+    # every training image is some 24x24 window of the standardised image, possibly mirrored
+    full = ((x0 - x0.mean()) / x0.std()).permute(2, 0, 1).float()
+    windows = [full[:, t:t + 24, l:l + 24] for t in range(9) for l in range(9)]
+    assert any(torch.allclose(train[0], w_, atol=1e-5) or torch.allclose(train[0], w_.flip(-1), atol=1e-5) for w_ in windows)
+    t = cifar100_transform(0.5, 0.25, train=False, crop_size=(8, 8))
+    assert torch.equal(t(torch.full((3, 16, 16), 0.75)), torch.ones(3, 8, 8))
