@@ -88,17 +88,20 @@ class Message(object):
         return f"{self.get_type()}: {{{', '.join(map(str, self.msg_params))}}}"
 
     # -- binary codec ------------------------------------------------------
-    def to_bytes(self) -> bytes:
+    def to_buffers(self) -> list:
+        """The wire form as a list of buffers whose concatenation is ``to_bytes()``: tensor payloads are views of the tensors'
+        own memory (no copy), so a socket transport can hand them to the kernel directly."""
         blobs = []
         header = _encode(self.msg_params, blobs)
         head = msgpack.packb(header, use_bin_type=True) if msgpack else json.dumps(header).encode()
-        out = io.BytesIO()
-        out.write(struct.pack("<4sBIQ", b"FB2M", 1 if msgpack else 0, len(blobs), len(head)))
-        out.write(head)
+        out = [struct.pack("<4sBIQ", b"FB2M", 1 if msgpack else 0, len(blobs), len(head)) + head]
         for b in blobs:
-            out.write(struct.pack("<Q", len(b)))
-            out.write(b)
-        return out.getvalue()
+            out.append(struct.pack("<Q", b.nbytes if isinstance(b, memoryview) else len(b)))
+            out.append(b)
+        return out
+
+    def to_bytes(self) -> bytes:
+        return b"".join(self.to_buffers())
 
     @classmethod
     def from_bytes(cls, data: bytes) -> "Message":
@@ -140,6 +143,16 @@ def _jsonable(obj):
     return obj
 
 
+def _byte_view(a: np.ndarray):
+    """The array's memory as a flat byte view (keeps the array alive); bytes for empty / exotic layouts."""
+    if a.size == 0:
+        return b""
+    try:
+        return memoryview(a.reshape(-1)).cast("B")
+    except (TypeError, ValueError):
+        return a.tobytes()
+
+
 def _encode(obj, blobs):
     import torch
     if isinstance(obj, dict):
@@ -148,13 +161,11 @@ def _encode(obj, blobs):
         return {"__l": [_encode(v, blobs) for v in obj], "t": isinstance(obj, tuple)}
     if isinstance(obj, torch.Tensor):
         t = obj.detach().cpu().contiguous()
-        if t.dtype == torch.bfloat16:
-            blobs.append(t.view(torch.int16).numpy().tobytes())
-            return {"__t": len(blobs) - 1, "dt": "bfloat16", "sh": list(t.shape)}
-        blobs.append(t.numpy().tobytes())
+        raw = t.view(torch.int16) if t.dtype == torch.bfloat16 else t
+        blobs.append(_byte_view(raw.numpy()))
         return {"__t": len(blobs) - 1, "dt": str(t.dtype).replace("torch.", ""), "sh": list(t.shape)}
     if isinstance(obj, np.ndarray):
-        blobs.append(np.ascontiguousarray(obj).tobytes())
+        blobs.append(_byte_view(np.ascontiguousarray(obj)))
         return {"__n": len(blobs) - 1, "dt": str(obj.dtype), "sh": list(obj.shape)}
     if isinstance(obj, np.generic):
         return obj.item()

@@ -20,13 +20,33 @@ _STOP = object()
 
 
 def _recv_exact(sock, n):
-    buf = bytearray()
-    while len(buf) < n:
-        chunk = sock.recv(min(1 << 20, n - len(buf)))
-        if not chunk:
+    """``n`` bytes into one preallocated buffer (no per-chunk concatenation, no final copy)."""
+    buf = bytearray(n)
+    view, got = memoryview(buf), 0
+    while got < n:
+        k = sock.recv_into(view[got:], min(4 << 20, n - got))
+        if not k:
             return None
-        buf += chunk
-    return bytes(buf)
+        got += k
+    return buf
+
+
+def _send_buffers(sock, buffers):
+    """Length prefix + buffers: small pieces are coalesced into one write, large ones (tensor payloads) go to the kernel as they
+    are - the message is never assembled in one Python bytes object."""
+    total = sum(b.nbytes if isinstance(b, memoryview) else len(b) for b in buffers)
+    pending = bytearray(struct.pack("<Q", total))
+    for b in buffers:
+        n = b.nbytes if isinstance(b, memoryview) else len(b)
+        if n < 65536:
+            pending += b
+            continue
+        if pending:
+            sock.sendall(pending)
+            pending = bytearray()
+        sock.sendall(b)
+    if pending:
+        sock.sendall(pending)
 
 
 class TcpCommManager(BaseCommunicationManager):
@@ -81,13 +101,13 @@ class TcpCommManager(BaseCommunicationManager):
                 time.sleep(0.05)
 
     def send_message(self, msg: Message):
-        data = msg.to_bytes()
+        buffers = msg.to_buffers()
         r = int(msg.get_receiver_id())
         with self._out_lock:
             s = self._out.get(r)
             if s is None:
                 s = self._out[r] = self._connect(r)
-            s.sendall(struct.pack("<Q", len(data)) + data)
+            _send_buffers(s, buffers)
 
     def add_observer(self, observer: Observer):
         self._observers.append(observer)
