@@ -263,10 +263,19 @@ def load_cross_silo(args):
 def load_poisoned_dataset_from_edge_case_examples(args):
     """Backdoor ("edge-case") data for the robust-FedAvg runner: a poisoned train loader, a clean
     test loader and a targeted-task test loader (edge_case_examples/data_loader.py:393-).  The
-    real Southwest-airline / ARDIS sets cannot be downloaded; the synthetic stand-in stamps a
-    trigger patch on samples of one class and relabels them to ``target_label``."""
+    real Southwest-airline / ARDIS sets are used when their files are under ``data_cache_dir`` (``data/edge_case.py``); they cannot
+    be downloaded here, so otherwise a synthetic stand-in stamps a trigger patch on samples and relabels them to ``target_label``."""
     ds = getattr(args, "_federated_dataset", None) or load_federated(args)
     bs = int(args.batch_size)
+    # the published sets (Southwest airplanes -> "truck" on CIFAR-10, ARDIS sevens -> "1" on MNIST) when their files are present
+    from .edge_case import load_edge_case_arrays
+    real = load_edge_case_arrays(str(args.dataset), str(getattr(args, "data_cache_dir", "") or ""), ds.x.numpy(), ds.y.numpy(),
+                                 str(getattr(args, "poison_type", "southwest")), str(getattr(args, "attack_case", "edge-case")),
+                                 int(getattr(args, "random_seed", 0))) if getattr(args, "data_cache_dir", None) else None
+    if real is not None:
+        xa, ya, xt, yt = (torch.from_numpy(np.ascontiguousarray(a)) for a in real)
+        return (ds.batches(xa, ya.long(), bs, drop_last=False, train=True), ds.batches(ds.x_test, ds.y_test, bs),
+                ds.batches(xt.to(ds.x_test.dtype), yt.long(), bs), int(xa.shape[0]))
     target = int(getattr(args, "target_label", 9)) % ds.class_num
     g = torch.Generator().manual_seed(int(getattr(args, "random_seed", 0)) + 17)
     n = min(512, ds.x.shape[0])

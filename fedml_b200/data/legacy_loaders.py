@@ -17,6 +17,8 @@ from __future__ import annotations
 
 from ..arguments import Arguments
 
+SYNTHETIC_TRAIN_SIZE = 0          # > 0: cap on the size of the synthetic stand-in (tests, demos); real files are never truncated
+
 
 def _load(dataset, data_dir=None, batch_size=10, partition_method="hetero", partition_alpha=0.5, client_number=None, **extra):
     from . import load
@@ -27,6 +29,8 @@ def _load(dataset, data_dir=None, batch_size=10, partition_method="hetero", part
     if client_number:
         kw["client_num_in_total"] = int(client_number)
         kw.setdefault("client_num_per_round", min(int(client_number), 10))
+    if SYNTHETIC_TRAIN_SIZE:
+        kw["synthetic_train_size"] = SYNTHETIC_TRAIN_SIZE
     kw.update(extra)
     args = Arguments.from_dict(kw)
     ds, class_num = load(args)

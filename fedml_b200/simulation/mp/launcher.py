@@ -74,6 +74,19 @@ class _ThreadedSimulation:
                 errors.append((rank, exc))
                 raise
 
+        # every worker thread that runs CPU kernels gets its own intra-op (OpenMP) team: size the teams so that all ranks together
+        # use the cores once instead of `size` times (restored afterwards; `cpu_threads_per_rank` overrides)
+        import torch
+        saved_threads = torch.get_num_threads()
+        on_cpu = str(getattr(self.device, "type", self.device)) == "cpu"
+        per_rank = int(getattr(self.args, "cpu_threads_per_rank", 0) or 0) or (max(1, saved_threads // size) if on_cpu else saved_threads)
+        torch.set_num_threads(per_rank)
+        try:
+            return self._run_threads(work, size, errors)
+        finally:
+            torch.set_num_threads(saved_threads)
+
+    def _run_threads(self, work, size, errors):
         threads = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(0, size)]
         for t in threads:
             t.start()

@@ -1,7 +1,13 @@
 import os
 import sys
 
-import pytest
+# The CPU suite runs many short torch ops from many Python threads (threaded simulators, transports).  Every such thread owns an
+# OpenMP team; with the default active wait policy the idle teams spin and starve whoever runs next - the same test then takes 5-10x
+# longer late in the session than alone.  Must be set before torch (libgomp) is loaded; inherited by the example subprocesses.
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")
+os.environ.setdefault("GOMP_SPINCOUNT", "0")
+
+import pytest  # noqa: E402
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:

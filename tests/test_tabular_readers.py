@@ -2,6 +2,7 @@
 formats (reference: data/UCI/data_loader_for_susy_and_ro.py, data/NUS_WIDE/nus_wide_dataset.py,
 data/lending_club_loan/lending_club_dataset.py)."""
 import os
+import pickle
 
 import numpy as np
 import pytest
@@ -262,3 +263,48 @@ def test_fed_cifar100_tff_preprocessing():
     assert any(torch.allclose(train[0], w_, atol=1e-5) or torch.allclose(train[0], w_.flip(-1), atol=1e-5) for w_ in windows)
     t = cifar100_transform(0.5, 0.25, train=False, crop_size=(8, 8))
     assert torch.equal(t(torch.full((3, 16, 16), 0.75)), torch.ones(3, 8, 8))
+
+
+def test_edge_case_sets_from_their_original_files(tmp_path):
+    from fedml_b200.data import edge_case as E
+    rs = np.random.RandomState(0)
+    d = tmp_path / "southwest_cifar10"
+    d.mkdir()
+    train, test = rs.randint(0, 255, (150, 32, 32, 3)).astype(np.uint8), rs.randint(0, 255, (30, 32, 32, 3)).astype(np.uint8)
+    pickle.dump(train, open(d / "southwest_images_new_train.pkl", "wb"))
+    pickle.dump(test, open(d / "southwest_images_new_test.pkl", "wb"))
+    got = E.get_southwest_dataset(str(tmp_path), "edge-case")
+    assert np.array_equal(got[0], train) and np.array_equal(got[1], test)
+    assert E.get_southwest_dataset(str(tmp_path), "normal-case") is None
+    with pytest.raises(NotImplementedError):
+        E.get_southwest_dataset(str(tmp_path), "weird")
+    cx, cy = rs.randint(0, 255, (1000, 32, 32, 3)).astype(np.uint8), rs.randint(0, 9, 1000)
+    x, y, xt, yt = E.load_edge_case_arrays("cifar10", str(tmp_path), cx, cy, "southwest", "edge-case", seed=1)
+    assert x.shape == (500, 32, 32, 3) and (y[400:] == 9).all() and (y[:400] < 9).all() and xt.shape[0] == 30 and (yt == 9).all()
+    # the 100 poisoned rows are photos from the file
+    flat = {p.tobytes() for p in train}
+    assert all(r.tobytes() in flat for r in x[400:])
+    # ARDIS csv
+    a = tmp_path / "ARDIS"
+    a.mkdir()
+    for split, n in (("train", 40), ("test", 12)):
+        imgs = rs.randint(0, 255, (n, 784)).astype(np.float32)
+        labs = np.eye(10)[rs.randint(0, 10, n)]
+        labs[:5] = np.eye(10)[7]
+        np.savetxt(a / f"ARDIS_{split}_2828.csv", imgs)
+        np.savetxt(a / f"ARDIS_{split}_labels.csv", labs)
+    sevens = E.get_ardis_dataset(str(tmp_path), "train")
+    assert sevens.shape[1:] == (28, 28) and sevens.dtype == np.uint8 and len(sevens) >= 5
+    mx, my = rs.rand(600, 784).astype(np.float32), rs.randint(0, 10, 600)
+    x, y, xt, yt = E.load_edge_case_arrays("mnist", str(tmp_path), mx, my, "ardis")
+    assert x.shape == (400 + len(sevens), 784) and x.dtype == np.float32 and float(x.max()) <= 1.0 and (y[400:] == 1).all() and (yt == 1).all()
+    assert E.load_edge_case_arrays("cifar10", str(tmp_path / "nowhere"), cx, cy) is None
+
+    # through the public loader: the attacker's batches come from the files, the targeted test set is the photos labelled 9
+    import fedml_b200
+    from fedml_b200.arguments import Arguments
+    a = Arguments.from_dict(dict(dataset="cifar10", data_cache_dir=str(tmp_path), batch_size=50, client_num_in_total=4, client_num_per_round=2,
+                                 synthetic_train_size=800, poison_type="southwest", attack_case="edge-case", log_level="WARNING"))
+    poisoned, clean, targeted, n = fedml_b200.data.load_poisoned_dataset_from_edge_case_examples(a)
+    assert n == 500 and sum(len(y_) for _, y_ in poisoned) == 500 and sum(len(y_) for _, y_ in targeted) == 30
+    assert all((y_ == 9).all() for _, y_ in targeted) and poisoned[0][0].shape[1:] == (3, 32, 32)
