@@ -87,6 +87,7 @@ class _ThreadedSimulation:
             torch.set_num_threads(saved_threads)
 
     def _run_threads(self, work, size, errors):
+        from ...core.distributed.communication.inproc import InProcHub
         threads = [threading.Thread(target=work, args=(r,), daemon=True) for r in range(0, size)]
         for t in threads:
             t.start()

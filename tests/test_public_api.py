@@ -42,3 +42,12 @@ def test_public_api_checklist():
     # CLI commands
     from fedml.cli.cli import cli
     assert {"version", "login", "logout", "build"} <= set(cli.commands)
+
+
+def test_no_undefined_names_in_the_tree():
+    """The reference's CI ran pyflakes; the equivalent check here (tools/check_names.py) needs no third-party linter."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "check_names.py")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
