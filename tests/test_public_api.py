@@ -1,5 +1,6 @@
 """the public API surface of the reference that scripts rely on, item by item."""
 import inspect
+import os
 
 
 def test_public_api_checklist():
