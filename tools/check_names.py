@@ -39,7 +39,7 @@ def check(path, problems):
 
 
 def main():
-    targets = sys.argv[1:] or [os.path.join(ROOT, p) for p in ("fedml_b200", "fedml", "tools", "baseline", "examples", "bench.py", "__graft_entry__.py")]
+    targets = sys.argv[1:] or [os.path.join(ROOT, p) for p in ("fedml_b200", "fedml", "tools", "baseline", "examples", "tests", "bench.py", "__graft_entry__.py")]
     problems = []
     for t in targets:
         if os.path.isfile(t):
