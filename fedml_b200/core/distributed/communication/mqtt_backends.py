@@ -112,10 +112,20 @@ class _MqttBase(BaseCommunicationManager):
 
 
 class MqttCommManager(_MqttBase):
-    """Pure MQTT: whole message as JSON (tensors as nested lists), like ``is_mobile`` in the reference."""
+    """Pure MQTT.  Default payload: the whole message as JSON with tensors as nested lists - the reference's format
+    (mqtt_comm_manager.py:100-124), readable by its mobile SDK.  ``mqtt_binary: true`` publishes the binary tensor codec instead
+    (``Message.to_bytes``; ~100x the throughput, see profiles/r2/comm_latency_cpu.md); receivers recognise either form by the
+    payload's first bytes, so peers with different settings interoperate."""
+
+    def _encode(self, msg: Message) -> bytes:
+        if bool(getattr(self.args, "mqtt_binary", False)):
+            return msg.to_bytes()
+        return super()._encode(msg)
 
     def _decode(self, payload):
         import torch
+        if bytes(payload[:4]) == b"FB2M":
+            return Message.from_bytes(bytes(payload))
         m = super()._decode(payload)
         mp = m.get(Message.MSG_ARG_KEY_MODEL_PARAMS)
         if isinstance(mp, dict):

@@ -44,13 +44,15 @@ class _Collect(Observer):
             self.ev.set()
 
 
-@pytest.mark.parametrize("backend", ["INPROC", "TCP", "GRPC", "MQTT", "MQTT_S3"])
+@pytest.mark.parametrize("backend", ["INPROC", "TCP", "GRPC", "MQTT", "MQTT_BIN", "MQTT_MIXED", "MQTT_S3"])
 def test_transport_roundtrip_with_tensor_payload(backend, broker, tmp_path):
-    args = Arguments.from_dict(dict(run_id=f"rt-{backend}", tcp_base_port=next_port(), grpc_base_port=next_port(), mqtt_port=broker,
-                                    object_store_dir=str(tmp_path / "store"), client_id_list="[1]"))
+    kind, backend = backend, backend.split("_")[0] if backend.startswith("MQTT_") and backend != "MQTT_S3" else backend
+    base = dict(run_id=f"rt-{kind}", tcp_base_port=next_port(), grpc_base_port=next_port(), mqtt_port=broker,
+                object_store_dir=str(tmp_path / "store"), client_id_list="[1]")
+    args = Arguments.from_dict(dict(base, mqtt_binary=kind in ("MQTT_BIN", "MQTT_MIXED")))
     InProcHub.reset(args.run_id)
-    server = create_comm_manager(args, 0, 2, backend)
-    client = create_comm_manager(args, 1, 2, backend)
+    server = create_comm_manager(args, 0, 2, backend)                                  # MQTT_MIXED: binary server, JSON client
+    client = create_comm_manager(Arguments.from_dict(dict(base, mqtt_binary=kind == "MQTT_BIN")), 1, 2, backend)
     cs, cc = _Collect(), _Collect()
     server.add_observer(cs); client.add_observer(cc)
     ts = [threading.Thread(target=m.handle_receive_message, daemon=True) for m in (server, client)]

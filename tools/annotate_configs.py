@@ -83,6 +83,7 @@ KEY_DOC = {
     "mqtt_host": "broker address",
     "mqtt_port": "1883 plain, 8883 with mqtt_tls: true",
     "object_store_dir": "shared directory standing in for the S3 bucket",
+    "mqtt_binary": "true: binary tensor codec on the MQTT topics instead of JSON lists (not readable by the reference's SDK)",
     "grpc_ipconfig_path": "csv of receiver_id,ip",
     "grpc_base_port": "rank r listens on grpc_base_port + r",
     "trpc_master_config_path": "csv holding master ip and port",

@@ -84,6 +84,8 @@ def run_backend(name, sizes, fn, repeat, cuda, broker_port, store_dir):
     backend, extra = name, {}
     if name == "GRPC_REF":                                   # the reference's wire format (protobuf + pickled Message)
         backend, extra = "GRPC", {"grpc_wire_format": "reference", "grpc_allow_pickle": True}
+    if name == "MQTT_BIN":                                   # MQTT carrying the binary tensor codec instead of JSON lists
+        backend, extra = "MQTT", {"mqtt_binary": True}
     args = Arguments.from_dict(dict(run_id=f"bench-{name}-{fn.__name__}", tcp_base_port=free_port(), grpc_base_port=free_port(),
                                     mqtt_port=broker_port, object_store_dir=store_dir, client_id_list="[1]", **extra))
     if backend == "INPROC":
@@ -137,7 +139,7 @@ def run_backend(name, sizes, fn, repeat, cuda, broker_port, store_dir):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--backends", nargs="+", default=["INPROC", "TCP", "GRPC", "GRPC_REF", "MQTT", "MQTT_S3"])
+    ap.add_argument("--backends", nargs="+", default=["INPROC", "TCP", "GRPC", "GRPC_REF", "MQTT", "MQTT_BIN", "MQTT_S3"])
     ap.add_argument("--sizes", nargs="+", type=int, default=[4096, 262144, 4194304, 16777216])
     ap.add_argument("--functions", nargs="+", default=["identity", "heavy"])
     ap.add_argument("--repeat", type=int, default=5)
@@ -165,7 +167,7 @@ def main():
             fh.write(f"# Transport round-trip latency ({'cuda' if a.cuda else 'cpu'} tensors, {NUM_RPC} requests in flight, median of "
                      f"{a.repeat}, both endpoints in one process on localhost)\n\n"
                      "`python tools/bench_comm.py`: the caller sends a float32 tensor, the callee applies the function and returns it.\n"
-                     "GRPC_REF = the reference's wire format (protobuf `CommRequest` + pickled `Message`); GRPC = the binary tensor codec.\n\n"
+                     "GRPC_REF = the reference's wire format (protobuf `CommRequest` + pickled `Message`); GRPC = the binary tensor codec; MQTT = JSON lists (the reference's format), MQTT_BIN = `mqtt_binary: true`.\n\n"
                      "| transport | function | payload | ms / request | MB/s (both directions) |\n|---|---|---:|---:|---:|\n")
             for name, fn_name, n, ms, mbs in rows:
                 fh.write(f"| {name} | {fn_name} | {n} | {ms:.3f} | {mbs:.1f} |\n")
