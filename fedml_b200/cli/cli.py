@@ -58,6 +58,11 @@ def login(userid, version, docker, broker, foreground):
     account_id = userid[0] if userid else "0"
     os.makedirs(HOME, exist_ok=True)
     _kill_old_agent()
+    if docker:                                                # the agent inside a container (reference login_with_docker.py)
+        from .edge_deployment import login_with_docker_mode
+        cmd = login_with_docker_mode(account_id, version)
+        click.echo("docker mode: " + " ".join(cmd) + ("" if shutil.which("docker") else "   (docker is not installed: command not run)"))
+        return 0
     cmd = [sys.executable, "-m", "fedml_b200.cli.edge_agent", "--account", str(account_id), "--version", version,
            "--broker", broker]
     if foreground:

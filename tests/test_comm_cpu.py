@@ -384,6 +384,19 @@ def test_cli_version_build_and_package_materialisation(tmp_path):
     assert str(user["train_args"]["run_id"]) == "42"
 
 
+def test_cli_login_docker_mode_prints_the_container_command(tmp_path, monkeypatch):
+    """``fedml login <id> -d``: the agent in a container; everything the command touches lives under the (redirected) home."""
+    from click.testing import CliRunner
+    import fedml_b200.cli.cli as C
+    monkeypatch.setenv("HOME", str(tmp_path))
+    monkeypatch.setattr(C, "HOME", str(tmp_path / ".fedml_b200"))
+    monkeypatch.setattr(C, "PID_FILE", str(tmp_path / ".fedml_b200" / "edge-process.id"))
+    monkeypatch.setattr(C.shutil, "which", lambda name: None)          # never start a container from a test
+    r = CliRunner().invoke(C.cli, ["login", "77", "-v", "dev", "-d"])
+    assert r.exit_code == 0 and "docker run --rm --name fedml-client-77" in r.output and "ACCOUNT_ID=77" in r.output
+    assert "fedml-b200/client-agent:dev" in r.output and (tmp_path / "fedml-client" / "fedml").is_dir()
+
+
 def test_hs_fft_matches_numpy_oracle():
     from fedml_b200.simulation.sp.hs_fft import amplitude_normalize, amplitude_normalize_numpy
     x = torch.rand(4, 3, 16, 16)
