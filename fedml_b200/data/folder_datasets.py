@@ -285,3 +285,81 @@ def get_dataloader_Landmarks(datadir, train_files, test_files, train_bs, test_bs
     test_ds = Landmarks(datadir, test_files, dataidxs=None, train=False, transform=t_test)
     return (torch_data.DataLoader(train_ds, batch_size=train_bs, shuffle=True, num_workers=num_workers),
             torch_data.DataLoader(test_ds, batch_size=test_bs, shuffle=False, num_workers=num_workers))
+
+
+# ------------------------------------------------------------------------------------------------ ImageNet in one HDF5 file
+class DatasetHDF5(torch_data.Dataset):
+    """``<t>_img`` (uint8 ``[n, H, W, 3]``) and ``<t>_labels`` of one HDF5 file, ``t`` = "train" or "val"; images are read one row
+    at a time (reference data/ImageNet/datasets_hdf5.py:11-35).  Opened with h5py when installed, else with ``minihdf5``."""
+
+    def __init__(self, hdf5fn, t, transform=None, target_transform=None):
+        from .readers import open_h5
+        self.hf, self.t = open_h5(hdf5fn), t
+        self.d = self.hf[f"{t}_img"]
+        self.n_images = self.d.shape[0]
+        self.dlabel = np.asarray(self.hf[f"{t}_labels"][...])
+
+    def __getitem__(self, index):
+        return np.asarray(self.d[int(index)]), np.int64(self.dlabel[index])
+
+    def __len__(self):
+        return self.n_images
+
+
+class ImageNet_hdf5(_FileDataset):  # noqa: N801
+    """Per-class clients over a :class:`DatasetHDF5`: ``net_dataidx_map[class] = [sample indices]``."""
+
+    def __init__(self, data_dir, dataidxs=None, train=True, transform=None, target_transform=None, download=False):
+        self.dataidxs, self.train, self.transform, self.target_transform = dataidxs, train, transform, target_transform
+        self.hdf5fn = os.path.join(data_dir)
+        self.all_data_hdf5 = DatasetHDF5(self.hdf5fn, "train" if train else "val")
+        self.net_dataidx_map: Dict[int, List[int]] = {}
+        for i, label in enumerate(self.all_data_hdf5.dlabel):
+            self.net_dataidx_map.setdefault(int(label), []).append(i)
+        self.data_local_num_dict = {k: len(v) for k, v in self.net_dataidx_map.items()}
+        self.all_data_idx = range(len(self.all_data_hdf5))
+        self.local_data_idx = _select_indices(self.all_data_idx, self.net_dataidx_map, dataidxs)
+
+    def get_net_dataidx_map(self):
+        return self.net_dataidx_map
+
+    def get_data_local_num_dict(self):
+        return self.data_local_num_dict
+
+    def _decode(self, img, target):
+        from PIL import Image
+        img = Image.fromarray(np.asarray(img, dtype=np.uint8))
+        img = self.transform(img) if self.transform is not None else _to_tensor(img)
+        if self.target_transform is not None:
+            target = self.target_transform(target)
+        return img, int(target)
+
+    def __getitem__(self, index):
+        return self._decode(*self.all_data_hdf5[self.local_data_idx[index]])
+
+    def __len__(self):
+        return len(self.local_data_idx)
+
+
+def _select_indices(all_idx, net_dataidx_map, dataidxs):
+    if dataidxs is None:
+        return all_idx
+    if isinstance(dataidxs, (int, np.integer)):
+        return net_dataidx_map[int(dataidxs)]
+    out: List[int] = []
+    for k in dataidxs:
+        out += net_dataidx_map[int(k)]
+    return out
+
+
+class ImageNet_truncated_hdf5(ImageNet_hdf5):  # noqa: N801
+    """View of an :class:`ImageNet_hdf5` restricted to the classes in ``dataidxs`` (shares the open file and the class map)."""
+
+    def __init__(self, imagenet_dataset: ImageNet_hdf5, dataidxs, net_dataidx_map=None, train=True, transform=None,
+                 target_transform=None, download=False):
+        self.dataidxs, self.train, self.transform, self.target_transform = dataidxs, train, transform, target_transform
+        self.all_data_hdf5 = imagenet_dataset.all_data_hdf5
+        self.net_dataidx_map = net_dataidx_map or imagenet_dataset.net_dataidx_map
+        self.data_local_num_dict = imagenet_dataset.data_local_num_dict
+        self.all_data_idx = range(len(self.all_data_hdf5))
+        self.local_data_idx = _select_indices(self.all_data_idx, self.net_dataidx_map, dataidxs)

@@ -391,6 +391,7 @@ class Dataset(_Object):
         self.shape = img.dataspace(sp[0])
         self._type, _ = img.datatype(tp[0])
         self.dtype = self._type.dtype if self._type.dtype is not None else np.dtype(object)
+        self._chunk_index = None
 
     def __len__(self):
         return self.shape[0] if self.shape else 0
@@ -443,12 +444,16 @@ class Dataset(_Object):
                 raise Hdf5Unsupported(f"{self.name}: filter {fid} (only deflate, shuffle and fletcher32 are built in)")
         return raw
 
-    def _read_all(self) -> np.ndarray:
+    def _read_all(self, rows: Optional[Tuple[int, int]] = None) -> np.ndarray:
+        """The whole data set, or rows ``[rows[0], rows[1])`` of its first axis (only those bytes / chunks are touched)."""
         img = self._img
         p, _ = self._first(M_LAYOUT)
         ver = img.buf[p]
         count, esize = self.size, self._type.size
         shape = self.shape
+        if not shape:
+            rows = None
+        cut = (lambda a: a[rows[0]:rows[1]]) if rows else (lambda a: a)
         if ver in (1, 2):
             rank, cls = img.buf[p + 1], img.buf[p + 2]
             q = p + 8
@@ -460,23 +465,23 @@ class Dataset(_Object):
             q += 4 * rank
             if cls == 0:
                 raw = img.buf[q + 4:q + 4 + img.u(q, 4)]
-                return _decode(img, self._type, raw, count).reshape(shape)
+                return cut(_decode(img, self._type, raw, count).reshape(shape))
             if cls == 1:
-                return self._contiguous(address, count, esize)
-            return self._chunked(address, dims[:-1], None)
+                return self._contiguous(address, count, esize, rows)
+            return self._chunked(address, dims[:-1], None, rows)
         cls = img.buf[p + 1]
         if cls == 0:
             n = img.u(p + 2, 2)
-            return _decode(img, self._type, img.buf[p + 4:p + 4 + n], count).reshape(shape)
+            return cut(_decode(img, self._type, img.buf[p + 4:p + 4 + n], count).reshape(shape))
         if cls == 1:
-            return self._contiguous(img.addr(p + 2), count, esize)
+            return self._contiguous(img.addr(p + 2), count, esize, rows)
         if cls != 2:
             raise Hdf5Unsupported(f"{self.name}: layout class {cls}")
         if ver == 3:
             rank = img.buf[p + 2]
             address = img.addr(p + 3)
             dims = [img.u(p + 3 + img.O + 4 * i, 4) for i in range(rank)]
-            return self._chunked(address, dims[:-1], None)
+            return self._chunked(address, dims[:-1], None, rows)
         # version 4: flags, rank, size of a dimension field, dims, index type
         flags, rank, dsz = img.buf[p + 2], img.buf[p + 3], img.buf[p + 4]
         dims = [img.u(p + 5 + dsz * i, dsz) for i in range(rank)]
@@ -488,7 +493,7 @@ class Dataset(_Object):
             if flags & 2:
                 size, mask = img.length(q), img.u(q + img.L, 4)
                 q += img.L + 4
-            return self._chunked(UNDEF, dims[:-1], [(tuple([0] * (rank - 1)), img.addr(q), size, mask)])
+            return self._chunked(UNDEF, dims[:-1], [(tuple([0] * (rank - 1)), img.addr(q), size, mask)], rows)
         if itype == 2:                                          # implicit: chunks back to back, no filters
             base = img.addr(q)
             cdims = dims[:-1]
@@ -497,43 +502,75 @@ class Dataset(_Object):
             chunks = []
             for k, idx in enumerate(np.ndindex(*grid)):
                 chunks.append((tuple(i * c for i, c in zip(idx, cdims)), base + k * per, per, 0))
-            return self._chunked(UNDEF, cdims, chunks)
+            return self._chunked(UNDEF, cdims, chunks, rows)
         raise Hdf5Unsupported(f"{self.name}: chunk index type {itype} (written with libver='latest'); re-save the file with "
                               "the default library version bounds")
 
-    def _contiguous(self, address, count, esize):
+    def _contiguous(self, address, count, esize, rows=None):
+        shape = self.shape
+        if rows:
+            per_row = int(np.prod(shape[1:])) if len(shape) > 1 else 1
+            shape = (rows[1] - rows[0],) + tuple(shape[1:])
+            count = shape[0] * per_row
+            if address != UNDEF:
+                address += rows[0] * per_row * esize
         if address == UNDEF:                                    # never written: fill value (zeros)
             if self._type.vlen:
                 out = np.empty(count, dtype=object)
                 out[:] = b""
-                return out.reshape(self.shape)
-            return np.zeros(self.shape, dtype=self._type.dtype)
+                return out.reshape(shape)
+            return np.zeros(shape, dtype=self._type.dtype)
         raw = self._img.buf[address:address + count * esize]
-        return _decode(self._img, self._type, raw, count).reshape(self.shape)
+        return _decode(self._img, self._type, raw, count).reshape(shape)
 
-    def _chunked(self, btree, cdims, chunks) -> np.ndarray:
+    def _chunked(self, btree, cdims, chunks, rows=None) -> np.ndarray:
         img, typ = self._img, self._type
         rank = len(cdims)
         filters = self._filters()
+        lo, hi = rows if rows else (0, self.shape[0] if self.shape else 1)
+        shape = ((hi - lo,) + tuple(self.shape[1:])) if self.shape else ()
         if typ.vlen:
-            out = np.empty(self.shape, dtype=object)
+            out = np.empty(shape, dtype=object)
             out.fill(b"")
         else:
-            out = np.zeros(self.shape, dtype=typ.dtype)
-        it = chunks if chunks is not None else img.chunk_btree(btree, rank)
+            out = np.zeros(shape, dtype=typ.dtype)
+        if chunks is None:
+            if self._chunk_index is None:                       # the B-tree walk is the expensive part: keep the flat list
+                self._chunk_index = list(img.chunk_btree(btree, rank))
+            chunks = self._chunk_index
         per = int(np.prod(cdims))
-        for offs, address, size, mask in it:
-            if address == UNDEF:
+        for offs, address, size, mask in chunks:
+            if address == UNDEF or (rank and (offs[0] + cdims[0] <= lo or offs[0] >= hi)):
                 continue
             raw = img.buf[address:address + (size if size is not None else per * typ.size)]
             if filters:
                 raw = self._unfilter(raw, filters, mask)
             block = _decode(img, typ, raw, per).reshape(cdims)
-            sel = tuple(slice(o, min(o + c, s)) for o, c, s in zip(offs, cdims, self.shape))
-            out[sel] = block[tuple(slice(0, sl.stop - sl.start) for sl in sel)]
+            if not rank:
+                out[()] = block[()]
+                continue
+            # intersection of the chunk with [lo, hi) x the data set's extent, in data set and in chunk coordinates
+            a0, b0 = max(offs[0], lo), min(offs[0] + cdims[0], hi, self.shape[0])
+            dst = (slice(a0 - lo, b0 - lo),) + tuple(slice(o, min(o + c, s_)) for o, c, s_ in zip(offs[1:], cdims[1:], self.shape[1:]))
+            src = (slice(a0 - offs[0], b0 - offs[0]),) + tuple(slice(0, d.stop - d.start) for d in dst[1:])
+            out[dst] = block[src]
         return out
 
     def __getitem__(self, key):
+        """h5py-style indexing.  An integer or a slice on the first axis reads only those rows from the file."""
+        first, rest = (key[0], key[1:]) if isinstance(key, tuple) and key else (key, ())
+        n = self.shape[0] if self.shape else 0
+        if self.shape and isinstance(first, (int, np.integer)) and not isinstance(first, bool):
+            i = int(first) + (n if first < 0 else 0)
+            if not 0 <= i < n:
+                raise IndexError(f"index {int(first)} out of range for axis 0 with size {n}")
+            row = self._read_all((i, i + 1))[0]
+            return row[rest] if rest else row
+        if self.shape and isinstance(first, slice):
+            lo, hi, step = first.indices(n)
+            if step > 0 and hi > lo:
+                part = self._read_all((lo, hi))[::step]
+                return part[(slice(None),) + rest] if rest else part
         data = self._read_all()
         if key is Ellipsis or (isinstance(key, tuple) and len(key) == 0):
             return data[()] if data.shape == () else data

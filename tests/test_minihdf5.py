@@ -217,3 +217,50 @@ def test_fed_cifar100_h5_with_the_tff_preprocessing_switch(tmp_path):
     ds, k = fedml_b200.data.load(_args(dataset="fed_cifar100", data_cache_dir=str(tmp_path), fed_cifar100_tff_preprocess=True))
     xb, yb = next(iter(ds[5][0]))
     assert xb.shape[1:] == (3, 24, 24) and k == 100
+
+
+def test_row_reads_touch_only_the_requested_rows_and_imagenet_hdf5(tmp_path):
+    rs = np.random.RandomState(2)
+    big = rs.randint(0, 255, (50, 12, 10, 3)).astype(np.uint8)
+    labels = rs.randint(0, 4, 50).astype(np.int64)
+    words = [f"w{i}" for i in range(23)]
+    path = H.write_hdf5(str(tmp_path / "imagenet.h5"), {
+        "train_img": big, "train_labels": labels, "val_img": H.H5Data(big[:20], chunks=(3, 12, 10, 3), compression=2), "val_labels": labels[:20],
+        "ragged": H.H5Data(np.arange(7 * 5).reshape(7, 5), chunks=(2, 3)), "words": H.H5Data(words, chunks=(4,)), "scalar": np.int32(5)})
+    with H.File(path) as f:
+        d = f["train_img"]
+        np.testing.assert_array_equal(d[7], big[7])
+        np.testing.assert_array_equal(d[-1], big[-1])
+        np.testing.assert_array_equal(d[10:31:5], big[10:31:5])
+        np.testing.assert_array_equal(d[3:9, 2:4, :, 1], big[3:9, 2:4, :, 1])
+        np.testing.assert_array_equal(d[4, 1:3], big[4, 1:3])
+        np.testing.assert_array_equal(d[[1, 5, 9]], big[[1, 5, 9]])              # fancy index: whole-array path
+        with pytest.raises(IndexError):
+            d[50]
+        v = f["val_img"]                                                           # chunked + deflate: rows across chunk borders
+        for key in (0, 2, 3, 19, slice(2, 8), slice(17, 20), slice(0, 20, 7)):
+            np.testing.assert_array_equal(v[key], big[:20][key])
+        r = f["ragged"]
+        for key in (0, 6, slice(1, 6), slice(5, 7)):
+            np.testing.assert_array_equal(r[key], np.arange(35).reshape(7, 5)[key])
+        assert [b.decode() for b in f["words"][5:11]] == words[5:11] and f["words"][22] == b"w22" and f["scalar"][()] == 5
+        # only the requested rows are decoded: reading one row of the chunked set decodes one chunk
+        calls = []
+        orig = v._unfilter
+        v._unfilter = lambda raw, filters, mask: (calls.append(1), orig(raw, filters, mask))[1]
+        v[4]
+        assert len(calls) == 1
+    from fedml_b200.data.folder_datasets import DatasetHDF5, ImageNet_hdf5, ImageNet_truncated_hdf5
+    raw = DatasetHDF5(path, "train")
+    img, lab = raw[11]
+    assert len(raw) == 50 and np.array_equal(img, big[11]) and lab == labels[11]
+    ds = ImageNet_hdf5(path, dataidxs=None, train=True)
+    assert len(ds) == 50 and sum(ds.get_data_local_num_dict().values()) == 50
+    cls = int(labels[0])
+    one = ImageNet_hdf5(path, dataidxs=cls, train=True)
+    assert len(one) == int((labels == cls).sum()) and all(one[i][1] == cls for i in range(len(one)))
+    x, y = one[0]
+    assert x.shape == (3, 12, 10) and abs(float(x[0, 0, 0]) - big[np.where(labels == cls)[0][0], 0, 0, 0] / 255) < 1e-6
+    view = ImageNet_truncated_hdf5(ds, [0, 1], ds.get_net_dataidx_map())
+    assert len(view) == int(((labels == 0) | (labels == 1)).sum())
+    assert len(ImageNet_hdf5(path, train=False)) == 20
