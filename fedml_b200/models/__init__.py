@@ -44,6 +44,9 @@ def create(args, output_dim):
         return resnet34(output_dim)
     if name == "resnet50":
         return resnet50(output_dim)
+    if name == "resnet20":          # the mobile ResNet-20 of the cross-device CIFAR-10 example (model/mobile/mnn_resnet.py)
+        from .cv import BasicBlock
+        return ResNet(BasicBlock, [3, 3, 3], output_dim, "cifar")
     if name == "resnet56":
         return resnet56(class_num=output_dim)
     if name == "resnet110":

@@ -205,6 +205,46 @@ def test_cross_device_server_with_file_models(broker, tmp_path):
     assert [o["type"] for o in mnn_format.describe(str(tmp_path / "global.mnn"))].count(mnn_format.OP_CONV) == 2     # still the LeNet graph
 
 
+def test_cross_device_server_with_the_resnet20_training_graph(broker, tmp_path):
+    """The CIFAR-10 cross-device example: the global file is the 416-op ResNet-20 MNN graph; the server averages the uploaded
+    files and evaluates by executing the graph (batch statistics, like a phone in training mode)."""
+    import shutil
+    from fedml_b200.cross_device import mnn_format as MF
+    from fedml_b200.cross_device.mnn_file import read_mnn_as_tensor_dict, read_mnn_like, write_tensor_dict_to_mnn
+    base = dict(training_type="cross_device", dataset="cifar10", model="resnet20", client_num_in_total=2, client_num_per_round=2, client_id_list="[1, 2]",
+                comm_round=1, batch_size=32, synthetic_train_size=200, backend="MQTT_S3_MNN", mqtt_port=broker, log_level="WARNING", partition_method="homo",
+                run_id="cd-r20", object_store_dir=str(tmp_path / "store"), model_file_cache_folder=str(tmp_path / "cache"),
+                global_model_file_path=str(tmp_path / "global.mnn"))
+    args = fedml.init(Arguments.from_dict(base))
+    ds, out = fedml.data.load(args)
+    model = fedml.model.create(args, out)
+    srv = fedml.cross_device.ServerMNN(args, torch.device("cpu"), ds[3], model)
+
+    class Phone(Observer):
+        def __init__(s, rank):
+            a = Arguments.from_dict(dict(base, rank=rank)); a.model_file_cache_folder = str(tmp_path / f"phone{rank}")
+            s.rank, s.cm = rank, create_comm_manager(a, rank, 3, "MQTT_S3_MNN"); s.cm.add_observer(s)
+
+        def receive_message(s, t, p):
+            if t in (1, 2):
+                path = str(tmp_path / f"phone{s.rank}" / "up.mnn"); shutil.copyfile(p["model_params"], path)
+                write_tensor_dict_to_mnn(path, {i: v + 0.01 * s.rank for i, v in read_mnn_as_tensor_dict(path).items()})
+                m = Message(3, s.rank, 0); m.add_params("model_params", path); m.add_params("num_samples", 10 * s.rank); s.cm.send_message(m)
+            elif t == 6:
+                s.cm.stop_receive_message()
+
+    phones = [Phone(1), Phone(2)]
+    [threading.Thread(target=p.cm.handle_receive_message, daemon=True).start() for p in phones]
+    init = [p.detach().clone() for p in model.parameters()]
+    agg = srv.run()
+    assert len(agg.history) == 1 and agg.eval_engine == "mnn_graph" and np.isfinite(agg.history[-1]["test_loss"])
+    assert len(MF.describe(str(tmp_path / "global.mnn"))) == 416
+    final = list(read_mnn_like(str(tmp_path / "global.mnn")).values())
+    assert len(final) == 65
+    torch.testing.assert_close(final[0], init[0] + 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)             # weighted mean of +0.01 and +0.02
+    torch.testing.assert_close(final[-1].reshape(-1), init[-1] + 0.01 * 5 / 3, rtol=1e-4, atol=1e-5)
+
+
 REF_MNN = "/root/reference/python/examples/cross_device/mqtt_s3_fedavg_mnist_lr_example/model_file_cache/global_model.mnn"
 REF_MNN_RESNET = "/root/reference/python/examples/cross_device/mqtt_s3_fedavg_cifar10_lr_example/model_file_cache/global_model.mnn"
 
