@@ -39,7 +39,10 @@ class MqttManager:
         will = json.dumps({"ID": self.mqtt_connection_id, "stat": "Online"})
         try:
             import paho.mqtt.client as mqtt
-            self._paho = mqtt.Client(client_id=self.mqtt_connection_id, clean_session=True)
+            try:
+                self._paho = mqtt.Client(client_id=self.mqtt_connection_id, clean_session=True)
+            except (TypeError, ValueError):                     # paho >= 2.0 wants the callback API version first
+                self._paho = mqtt.Client(mqtt.CallbackAPIVersion.VERSION1, client_id=self.mqtt_connection_id, clean_session=True)
             self._paho.on_connect = self.on_connect
             self._paho.on_message = self.on_message
             self._paho.on_publish, self._paho.on_disconnect = self.on_publish, self.on_disconnect
@@ -47,6 +50,7 @@ class MqttManager:
                 self._paho.username_pw_set(user, pwd)
             self._paho.will_set("W/topic", payload=will, qos=0, retain=True)
             self._paho.connect(self._host, self._port, keepalive_time)
+            self._paho.loop_start()                              # callbacks run on paho's network thread, like the native client
             self._native = None
         except ImportError:
             from ..core.distributed.communication.broker import BrokerClient
@@ -103,14 +107,12 @@ class MqttManager:
         self.send_message(topic, message)
 
     def loop_forever(self):
-        if self._paho is not None:
-            self._paho.loop_forever()
-        else:
-            self._stopped.wait()
+        self._stopped.wait()
 
     def disconnect(self):
         self._stopped.set()
         if self._paho is not None:
+            self._paho.loop_stop()
             self._paho.disconnect()
         else:
             self._native.disconnect()
