@@ -236,7 +236,25 @@ def run_sp_cpu(a, cfg):
     else:
         ms = 1e3 * (time.perf_counter() - t_all) / (a.warmup + a.steps)
     K = cfg["client_num_per_round"]
+    # the same rounds on the client-batched engine (NCCL simulator, CPU tensors): all sampled clients train as one stacked model
+    batched = None
+    try:
+        import copy
+        from fedml_b200.simulation import SimulatorNCCL
+        b_args = copy.copy(args)
+        b_args.backend, b_args.frequency_of_the_test = "NCCL", 0
+        sim = SimulatorNCCL(b_args, torch.device("cpu"), dataset, fedml.models.create(args, class_num)).simulator
+        per_b = []
+        for r in range(a.warmup + a.steps):
+            t0 = time.perf_counter()
+            sim.train_one_round(r)
+            per_b.append(time.perf_counter() - t0)
+        b_ms = 1e3 * sum(per_b[a.warmup:]) / a.steps
+        batched = {"ms_per_step": b_ms, "value": K * 1e3 / b_ms, "engine": "client-batched (simulation.nccl on CPU tensors), same rounds"}
+    except Exception as exc:  # noqa: BLE001 - the headline of this config is the SP simulator above
+        batched = {"error": repr(exc)}
     print(json.dumps({"metric": METRIC, "value": K * 1e3 / ms, "unit": "client-updates/s", "n_gpus": 0, "steps": a.steps,
+                      "client_batched": batched,
                       "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "none",
                       "vs_baseline": None, "dtype": "fp32", "data": "synthetic (MNIST-shaped)", "rounds_per_sec": 1e3 / ms,
                       "config": {"name": a.config, "desc": cfg["desc"], "model": "lr", "clients_per_round": K,
