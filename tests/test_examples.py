@@ -72,3 +72,17 @@ def test_cross_silo_grpc_example_three_processes(tmp_path):
 def test_shipped_configs_are_in_the_documented_layout():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "annotate_configs.py"), "--check"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout
+
+
+def test_bench_cpu_config_prints_the_contract_line(tmp_path):
+    """``bench.py --config sp_mnist_lr`` (BASELINE #1) runs without a GPU: one JSON line with the driver's keys, the SP simulator's
+    number as the value and the client-batched engine next to it."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--config", "sp_mnist_lr", "--steps", "3", "--warmup", "1"],
+                       cwd=str(tmp_path), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-1500:]
+    line = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "dtype", "data", "config"):
+        assert key in line, key
+    assert line["metric"] == "client_updates_per_sec" and line["steps"] == 3 and line["value"] > 0 and line["n_gpus"] == 0
+    assert line["client_batched"]["value"] > 0 and line["gpu_launches"] == 0
