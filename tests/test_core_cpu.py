@@ -464,3 +464,57 @@ def test_algorithm_helper_functions(tmp_path):
     assert abs(float(sigmoid(0.0)) - 0.5) < 1e-12
     y_hat, stats = compute_correct_prediction(y_targets=[1, 0, 1, 1], y_prob_preds=[0.9, 0.2, 0.4, 0.7])
     assert y_hat.tolist() == [1, 0, 0, 1] and stats == [2, 2, 3]
+
+
+def test_replica_synchronized_batchnorm_threads_equal_batchnorm_on_the_whole_batch():
+    """The DataParallel flavour of SyncBN (reference model/cv/batchnorm_utils.py: SyncMaster / SlavePipe / FutureResult +
+    replication callbacks): three replica threads, each with a slice of the batch, normalise like one BatchNorm on all of it."""
+    import threading
+    from fedml_b200.models.sync_batchnorm import (FutureResult, ReplicaSynchronizedBatchNorm, SyncMaster, execute_replication_callbacks)
+    # the message pipe on its own
+    master = SyncMaster(lambda msgs: [(i, sum(m for _, m in msgs) * (i + 1)) for i, _ in sorted(msgs)])
+    pipes = [master.register_slave(i) for i in (1, 2)]
+    got = {}
+    ts = [threading.Thread(target=lambda p=p: got.__setitem__(p.identifier, p.run_slave(10 * p.identifier))) for p in pipes]
+    [t.start() for t in ts]
+    got[0] = master.run_master(5)
+    [t.join() for t in ts]
+    assert got == {0: 35, 1: 70, 2: 105} and master.nr_slaves == 2
+    f = FutureResult()
+    threading.Timer(0.05, f.put, args=("late",)).start()
+    assert f.get() == "late"
+    # the layer
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 4, 3, padding=1), ReplicaSynchronizedBatchNorm(4), torch.nn.ReLU()).double()
+    ref = torch.nn.Sequential(torch.nn.Conv2d(3, 4, 3, padding=1), torch.nn.BatchNorm2d(4), torch.nn.ReLU()).double()
+    ref.load_state_dict(net.state_dict())
+    x = torch.randn(9, 3, 6, 6, dtype=torch.float64)
+    parts = [x[:2], x[2:5], x[5:]]
+    replicas = []
+    for _ in parts:                                     # what DataParallel.replicate does: new module objects, shared parameters
+        rep = torch.nn.Sequential(*[copy.copy(m) for m in net])
+        replicas.append(rep)
+    for rep in replicas[1:]:                            # buffers of replica 0 are the master's own
+        rep[1].running_mean, rep[1].running_var = rep[1].running_mean.clone(), rep[1].running_var.clone()
+    replicas[0][1].running_mean, replicas[0][1].running_var = net[1].running_mean, net[1].running_var
+    execute_replication_callbacks(replicas)
+    outs = [None] * 3
+
+    def run(i):
+        outs[i] = replicas[i](parts[i])
+
+    ts = [threading.Thread(target=run, args=(i,)) for i in range(3)]
+    [t.start() for t in ts]
+    [t.join(30) for t in ts]
+    assert all(o is not None for o in outs)
+    want = ref(x)
+    torch.testing.assert_close(torch.cat(outs), want, rtol=1e-10, atol=1e-12)
+    torch.cat(outs).square().sum().backward()
+    want.square().sum().backward()
+    for (n1, p1), (_, p2) in zip(net.named_parameters(), ref.named_parameters()):
+        torch.testing.assert_close(p1.grad, p2.grad, rtol=1e-8, atol=1e-10, msg=n1)
+    torch.testing.assert_close(net[1].running_mean, ref[1].running_mean, rtol=1e-10, atol=1e-12)
+    torch.testing.assert_close(net[1].running_var, ref[1].running_var, rtol=1e-10, atol=1e-12)
+    # outside replication / in eval mode: plain BatchNorm
+    net.eval(); ref.eval()
+    torch.testing.assert_close(net(x), ref(x), rtol=1e-10, atol=1e-12)
