@@ -140,7 +140,9 @@ class HSFedAvgAPI(SFedAvgAPI):
         data, amp = [], self.amp_global
         for x, y in client.local_training_data:
             if x.dim() == 4:
-                x, amp, _ = amplitude_normalize(x, amp)
+                # hs_fft_window: None (default) swaps the whole amplitude spectrum - the K14 kernel on the GPU; a float L applies
+                # the reference's low-frequency window rule (its process() uses L = 0, i.e. only the DC term)
+                x, amp, _ = amplitude_normalize(x, amp, window=getattr(self.args, "hs_fft_window", None))
             data.append((x, y))
         client.local_training_data = data
         self._client_amps.append(amp)

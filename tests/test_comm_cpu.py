@@ -915,3 +915,38 @@ def test_edge_deployment_helpers(tmp_path, monkeypatch, broker):
     monkeypatch.setenv("HOME", str(tmp_path / "h2"))
     cmd = E.login_with_docker_mode(1234, "dev", run=False)
     assert cmd[:3] == ["docker", "run", "--rm"] and "ACCOUNT_ID=1234" in cmd and cmd[-1].endswith(":dev")
+
+
+def test_hs_fft_low_frequency_window_rule_of_the_reference():
+    """``process`` / ``mutate`` / ``normalize`` with the reference's semantics (only the centred window of the shifted spectrum
+    takes the running amplitude; L = 0 -> the DC term), checked against a per-image restatement and against the torch form."""
+    from fedml.simulation.single_process.hs_fedavg.hs_fft import extract_amp, mutate, normalize, process
+    from fedml_b200.simulation.sp.hs_fft import amplitude_normalize
+    rs = np.random.RandomState(0)
+    x = rs.rand(5, 3, 8, 12).astype(np.float32)
+    run = rs.rand(3, 8, 12).astype(np.float32) + 0.5
+    for L in (0.0, 0.25):
+        out, new_run = process(x.copy(), run.copy(), momentum=0.1, L=L)
+        amp_avg = np.stack([extract_amp(img) for img in x]).astype(np.float32).mean(0)
+        want_run = run * 0.9 + amp_avg * 0.1
+        np.testing.assert_allclose(new_run, want_run, rtol=1e-6)
+        b = int(np.floor(min(8, 12) * L))
+        for i in range(5):
+            f = np.fft.fft2(x[i].astype(np.float64), axes=(-2, -1))
+            a = np.fft.fftshift(np.abs(f), axes=(-2, -1))
+            t = np.fft.fftshift(want_run, axes=(-2, -1))
+            a[:, 4 - b:4 + b + 1, 6 - b:6 + b + 1] = t[:, 4 - b:4 + b + 1, 6 - b:6 + b + 1]
+            img = np.real(np.fft.ifft2(np.fft.ifftshift(a, axes=(-2, -1)) * np.exp(1j * np.angle(f)), axes=(-2, -1)))
+            np.testing.assert_allclose(out[i], img, rtol=1e-4, atol=1e-5)
+        t_out, t_run, _ = amplitude_normalize(torch.from_numpy(x), torch.from_numpy(run), 0.1, window=L)
+        np.testing.assert_allclose(t_out.numpy(), out, rtol=1e-3, atol=1e-4)
+        np.testing.assert_allclose(t_run.numpy(), new_run, rtol=1e-5)
+    # L = 0 changes the mean of every channel (DC term) and nothing else
+    out0, _ = process(x.copy(), run.copy(), L=0.0)
+    d = np.fft.fft2(out0.astype(np.float64) - x, axes=(-2, -1))
+    assert np.abs(d[..., 0, 0]).min() > 1e-3 and np.abs(d.reshape(5, 3, -1)[..., 1:]).max() < 1e-4
+    first, first_run = process(x.copy(), np.zeros_like(run))                  # first batch: the running amplitude is the batch mean
+    np.testing.assert_allclose(first_run, np.stack([extract_amp(i) for i in x]).mean(0), rtol=1e-5)
+    sq, sq_run = x[0, :, :, :8], run[:, :, :8]                                 # 8 x 8: L = 0.5 -> window [0, 9) on both axes = full swap
+    np.testing.assert_allclose(mutate(extract_amp(sq), sq_run, L=0.5), sq_run, rtol=1e-6)
+    assert normalize(x[0], run, L=0.1).shape == x[0].shape
