@@ -153,6 +153,32 @@ def FedML_Hierarchical(args, client_rank, client_num, comm, device, dataset, mod
     return adapter
 
 
+# builder functions of the reference's fedml_hierarchical_api.py:83-167 (scripts that assemble a silo by hand call these)
+def get_trainer_dist_adapter(args, device, client_rank, model, train_data_num, train_data_local_num_dict, train_data_local_dict,
+                             test_data_local_dict, model_trainer=None):
+    return TrainerDistAdapter(args, device, client_rank, model, train_data_num, train_data_local_num_dict, train_data_local_dict,
+                              test_data_local_dict, model_trainer)
+
+
+def get_dist_aggregator(args, device, size, model, train_data_num, train_data_global, test_data_global, train_data_local_dict,
+                        test_data_local_dict, train_data_local_num_dict, model_trainer=None, server_aggregator=None):
+    trainer = model_trainer or create_model_trainer(model, args)
+    return FedMLAggregator(train_data_global, test_data_global, train_data_num, train_data_local_dict, test_data_local_dict,
+                           train_data_local_num_dict, size, device, args, trainer, server_aggregator)
+
+
+def get_server_manager(args, dist_aggregator, comm, rank, size, backend, is_preprocessed=False, preprocessed_client_lists=None):
+    return FedMLServerManager(args, dist_aggregator, comm, rank, size, backend)
+
+
+def get_clinet_manager_master(args, trainer_dist_adapter, comm, client_rank, size, backend):      # (sic) the reference's spelling
+    return ClientMasterManager(args, trainer_dist_adapter, comm, client_rank, size, backend)
+
+
+def get_clinet_manager_salve(args, trainer_dist_adapter):                                        # (sic)
+    return ClientSlaveManager(args, trainer_dist_adapter)
+
+
 class Server:
     def __init__(self, args, device, dataset, model, model_trainer=None, server_aggregator=None):
         self.a = (args, device, dataset, model, model_trainer, server_aggregator)
