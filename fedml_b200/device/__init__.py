@@ -68,3 +68,18 @@ def get_device(args):
             return torch.device("mps")
         return torch.device("cpu")
     return _cuda_or_cpu(getattr(args, "gpu_id", 0)) if using_gpu else torch.device("cpu")
+
+
+def get_gpu_util_map(silo_gpu_util_file: str) -> dict:
+    """``{process index: (host, gpu index)}`` from a silo's yaml ``{host: [processes on gpu 0, processes on gpu 1, ...]}``
+    (reference device/gpu_mapping_cross_silo.py:69-85): processes are numbered host by host, GPU by GPU."""
+    with open(silo_gpu_util_file) as fh:
+        per_host = yaml.safe_load(fh) or {}
+    out, i = {}, 0
+    for host, per_gpu in per_host.items():
+        for gpu, n in enumerate(per_gpu):
+            for _ in range(int(n)):
+                out[i] = (host, gpu)
+                i += 1
+    logging.info("GPU MAPPING: %s", out)
+    return out

@@ -518,3 +518,9 @@ def test_replica_synchronized_batchnorm_threads_equal_batchnorm_on_the_whole_bat
     # outside replication / in eval mode: plain BatchNorm
     net.eval(); ref.eval()
     torch.testing.assert_close(net(x), ref(x), rtol=1e-10, atol=1e-12)
+
+
+def test_gpu_util_map_from_a_silo_yaml(tmp_path):
+    from fedml.device.gpu_mapping_cross_silo import get_gpu_util_map
+    (tmp_path / "m.yaml").write_text("node1: [2, 0, 1]\nnode2: [1]\n")
+    assert get_gpu_util_map(str(tmp_path / "m.yaml")) == {0: ("node1", 0), 1: ("node1", 0), 2: ("node1", 2), 3: ("node2", 0)}
